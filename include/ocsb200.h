@@ -1,0 +1,204 @@
+/*
+ * ocsb200.h -- C ABI of libocsb200.so: the B200-native raster hot path of OCSMesh.
+ *
+ * The reference (noaa-ocs-modeling/OCSMesh) is 100 % Python and has NO
+ * plugin / FFI layer on this path: the arithmetic is inline numpy/scipy inside
+ * Python methods.  Each entry point below therefore replaces the body of one
+ * reference loop ("per window: ...") and cites the reference file:line it
+ * stands in for.  INTEGRATION.md shows the ctypes stub a maintainer would add
+ * at those call sites.
+ *
+ * Conventions
+ *   - every function returns an int32 status: 0 = OK, <0 = error
+ *     (OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_EOVERFLOW); the text of the
+ *     last error on the calling thread is returned by ocsb_last_error().
+ *   - no exception crosses the boundary, no ownership is transferred: the
+ *     caller owns every buffer.  Pointers may be HOST or DEVICE memory (the
+ *     library asks cudaPointerGetAttributes); host buffers are staged through
+ *     device scratch inside the call (that is the "e2e" path of bench.py).
+ *   - a call returns after its work has been *enqueued* on the context's
+ *     stream when all buffers are device buffers, and after completion when
+ *     any buffer was a host buffer.  ocsb_ctx_sync() waits for the stream.
+ *   - "None" for an optional double argument is passed as NaN (OCSB_NONE).
+ *   - one ocsb_ctx per (process, device); calls on one ctx are not re-entrant.
+ *   - pixel buffers are row-major windows: element (row, col) of a window lives
+ *     at base[row * row_stride + col]; `base` points at the window's top-left
+ *     pixel, so a window inside a larger raster is base = raster + row_off *
+ *     W + col_off, row_stride = W.
+ */
+#ifndef OCSB200_H
+#define OCSB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OCSB_OK          0
+#define OCSB_EINVAL     (-1)
+#define OCSB_ENOMEM     (-2)
+#define OCSB_ECUDA      (-3)
+#define OCSB_ENCCL      (-4)
+#define OCSB_EOVERFLOW  (-5)
+
+#define OCSB_ABI_VERSION 1
+
+/* DEM element types (the hfun raster itself is always float32,
+ * ocsmesh/hfun/raster.py:76) */
+#define OCSB_F32 0
+#define OCSB_F64 1
+
+/* Mesh.interpolate methods (ocsmesh/mesh/mesh.py:2306-2336) */
+#define OCSB_INTERP_LINEAR  0
+#define OCSB_INTERP_NEAREST 1
+#define OCSB_INTERP_SPLINE  2
+
+typedef struct ocsb_ctx ocsb_ctx;
+
+/*
+ * One semantic raster window, as the reference sees it:
+ *   (x0, y0, x1, y1) = Raster.get_window_bounds(window)          ocsmesh/raster.py:1642-1662
+ *                      = (west, south, east, north) pixel-EDGE bounds
+ *   pixel column k has x = np.linspace(x0, x1, width)[k]          ocsmesh/raster.py:452-453
+ *   pixel row    j has y = np.linspace(y1, y0, height)[j]         ocsmesh/raster.py:479-480
+ */
+typedef struct ocsb_win {
+    double  x0, y0, x1, y1;
+    int32_t width, height;
+} ocsb_win;
+
+/* ---- library / context -------------------------------------------------- */
+
+int32_t     ocsb_abi_version(void);
+const char *ocsb_last_error(void);
+
+/* device: CUDA ordinal.  stream: a cudaStream_t (NULL = a stream the context
+ * creates and owns).  */
+int32_t ocsb_ctx_create(int32_t device, void *stream, ocsb_ctx **out);
+int32_t ocsb_ctx_destroy(ocsb_ctx *ctx);
+int32_t ocsb_ctx_set_stream(ocsb_ctx *ctx, void *stream);
+int32_t ocsb_ctx_sync(ocsb_ctx *ctx);
+/* number of kernels this context has launched so far (bench "gpu_launches") */
+int64_t ocsb_ctx_launch_count(const ocsb_ctx *ctx);
+/* release cached device scratch */
+int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
+
+/* ---- A1: window list ------------------------------------------------------
+ * get_iter_windows(width, height, chunk_size, overlap)   ocsmesh/raster.py:1891-1939
+ * Raster.iter_windows (chunk_size in [0, None, False] -> one full window)
+ *                                                        ocsmesh/raster.py:1577-1608
+ * out4: cap x 4 int32 (col_off, row_off, width, height), row-major order.
+ * *n receives the number of windows (also when out4 == NULL or cap is too
+ * small, in which case OCSB_EOVERFLOW is returned).  Host-only, no ctx.       */
+int32_t ocsb_windows(int32_t width, int32_t height, int32_t chunk_size,
+                     int32_t overlap, int32_t *out4, int64_t cap, int64_t *n);
+
+/* ---- A2: window coordinates -----------------------------------------------
+ * Raster.get_x / get_y                                   ocsmesh/raster.py:428-480
+ * Writes np.linspace(x0, x1, width) to x_out[width] and np.linspace(y1, y0,
+ * height) to y_out[height], computed ON THE DEVICE with the same
+ * fl(fl(k*step)+start) / pinned-endpoint rule the kernels use in-register
+ * (the reference's (h*w,2) get_xy array is never materialised).              */
+int32_t ocsb_window_coords(ocsb_ctx *ctx, const ocsb_win *win,
+                           double *x_out, double *y_out);
+
+/* ---- A4: hfun initial fill -------------------------------------------------
+ * HfunInputRaster.__set__: every pixel = finfo(float32).max   ocsmesh/hfun/raster.py:57-86 */
+int32_t ocsb_fill_f32(ocsb_ctx *ctx, float *dst, int64_t n, float value);
+
+/* ---- A10: global clamp re-pass ---------------------------------------------
+ * HfunRaster.apply_constraints with no custom constraints     ocsmesh/hfun/raster.py:509-568
+ * (values < hmin -> hmin, values > hmax -> hmax, float32 compares)           */
+int32_t ocsb_hfun_clamp(ocsb_ctx *ctx, float *hfun, int64_t row_stride,
+                        int32_t width, int32_t height,
+                        double hmin, double hmax);
+
+/* ---- A6 + A7: feature / contour distance sizing ----------------------------
+ * Body of the window loop of HfunRaster.add_feature            ocsmesh/hfun/raster.py:1230-1257
+ *   tree = cKDTree(points); d = tree.query(xy[, distance_upper_bound=r])
+ *   v = float32(rate*target*d + target); clamp [hmin,hmax]; new = min(old, v)
+ * verts_xy : nv x 2 float64, the resampled feature vertices ("points", :1230)
+ * hfun_old : window of the PRE-op hfun (the reference reads self.src)
+ * hfun_new : window of the POST-op hfun (may alias hfun_old)
+ * hmin/hmax: the HfunRaster's global bounds, NaN = None.  hmax "truthy"
+ *            (not None, != 0) selects the bounded query, exactly as :1240.
+ * fuse_clamp != 0 additionally applies the A10 clamp to the result (what
+ *            apply_constraints_wrap does right after the op when no custom
+ *            constraint is registered, ocsmesh/features/constraint.py:420-423).
+ * dist_out : optional window (row_stride = width) of float64 distances as
+ *            used by the size law (r where scipy returned inf), or NULL
+ * idx_out  : optional window (row_stride = width) of int64 nearest-vertex
+ *            indices (nv where scipy returned nv), or NULL                    */
+int32_t ocsb_hfun_feature(ocsb_ctx *ctx, const ocsb_win *win,
+                          const double *verts_xy, int64_t nv,
+                          const float *hfun_old, int64_t old_stride,
+                          float *hfun_new, int64_t new_stride,
+                          double expansion_rate, double target_size,
+                          double hmin, double hmax, int32_t fuse_clamp,
+                          double *dist_out, int64_t *idx_out);
+
+/* Nearest-vertex query alone (second cKDTree site, Constraint._apply_rate
+ * ocsmesh/features/constraint.py:104-105): for `nq` arbitrary query points.
+ * r = NaN -> unbounded.  dist_out[nq] float64 (inf on miss), idx_out[nq]
+ * int64 (nv on miss).                                                         */
+int32_t ocsb_nearest_vertex(ocsb_ctx *ctx, const double *verts_xy, int64_t nv,
+                            const double *query_xy, int64_t nq, double r,
+                            double *dist_out, int64_t *idx_out);
+
+/* ---- A8 (+A9): subtidal flow limiter / gradient stencil --------------------
+ * Body of the window loop of HfunRaster.add_subtidal_flow_limiter
+ *                                                         ocsmesh/hfun/raster.py:1396-1435
+ * dem      : window of the DEM band (dem_dtype OCSB_F32 / OCSB_F64)
+ * dx, dy   : Raster.dx, Raster.dy (np.gradient(z, dx, dy): dx spaces axis 0!)
+ * hmin,hmax,lower_bound,upper_bound : the method's arguments, NaN = None
+ * ghmin,ghmax : the HfunRaster's global bounds (self._hmin/_hmax), NaN = None
+ * Zero-gradient pixels follow the masked-array arithmetic of the reference
+ * (raw value 1/3).  The window needs width,height >= 2
+ * (np.gradient raises otherwise -> OCSB_EINVAL).                              */
+int32_t ocsb_hfun_flow_limiter(ocsb_ctx *ctx, const ocsb_win *win,
+                               const void *dem, int32_t dem_dtype,
+                               int64_t dem_stride,
+                               const float *hfun_old, int64_t old_stride,
+                               float *hfun_new, int64_t new_stride,
+                               double dx, double dy,
+                               double hmin, double hmax,
+                               double lower_bound, double upper_bound,
+                               double ghmin, double ghmax,
+                               int32_t fuse_clamp);
+
+/* ---- A12: pixel-wise min of co-registered hfun windows (build-defined) ---- */
+int32_t ocsb_min_combine(ocsb_ctx *ctx, float *dst, int64_t dst_stride,
+                         const float *src, int64_t src_stride,
+                         int32_t width, int32_t height);
+
+/* ---- A14: Mesh.interpolate worker ------------------------------------------
+ * _mesh_interpolate_worker, one (raster, window)             ocsmesh/mesh/mesh.py:2285-2347
+ * dem         : window of the raster band (dem_dtype), row-major
+ * nodata_mask : optional uint8 window (1 = nodata), NULL = no nodata
+ * xy          : K x 2 float64 node coordinates
+ * method      : OCSB_INTERP_LINEAR / NEAREST / SPLINE
+ * touched     : K uint8; set to 1 for every node this raster updates
+ *               (= the boolean mask the worker returns), left alone otherwise
+ * values      : K float64; values[k] is overwritten for touched nodes only,
+ *               so calling this once per raster in list order reproduces the
+ *               reference's last-wins scatter               ocsmesh/mesh/mesh.py:372-376 */
+int32_t ocsb_interp(ocsb_ctx *ctx, const ocsb_win *win,
+                    const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                    const uint8_t *nodata_mask, int64_t mask_stride,
+                    const double *xy, int64_t K, int32_t method,
+                    uint8_t *touched, double *values);
+
+/* Spline prefilter for OCSB_INTERP_SPLINE: builds the tensor-product
+ * not-a-knot cubic B-spline coefficients of RectBivariateSpline(kx=ky=3, s=0)
+ * (ocsmesh/mesh/mesh.py:2306-2314) for one window into coef[width*height]
+ * float64 (device or host).  ocsb_interp(..., SPLINE) calls it internally;
+ * exported for tests.                                                          */
+int32_t ocsb_spline_prefilter(ocsb_ctx *ctx, const ocsb_win *win,
+                              const void *dem, int32_t dem_dtype,
+                              int64_t dem_stride, double *coef);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OCSB200_H */

@@ -1,0 +1,784 @@
+// K1 -- nearest-vertex distance sizing (reference ocsmesh/hfun/raster.py:1230-1257:
+// cKDTree(points).query(xy[, distance_upper_bound=r]) + size law + clamps + min).
+//
+// Design (B200-first, no kd-tree):
+//
+//  * The window is covered by a pyramid of pixel tiles (..., 4096, 1024, 256,
+//    64 px square).  Every tile carries a CANDIDATE LIST of vertex ids that is
+//    a superset of {nearest vertex of p : p pixel of the tile}.  A child list
+//    is filtered from its parent list by two exact, conservative tests:
+//      - radius : drop v if mindist(v, tile rect) > r          (bounded query)
+//      - dominance: drop v if some kept vertex u is at least as close as v at
+//        all four rect corners -- then u is at least as close on the whole
+//        rect (|p-v|^2 - |p-u|^2 is linear in p), so v can never be the
+//        strict nearest neighbour of a pixel in the tile.  Dominators are
+//        the parent candidates nearest to the rect centre and to its corners.
+//    For a shoreline sampled every `target_size` metres this leaves
+//    ~(tile width / target_size + 2) candidates per tile *independently of
+//    the distance to the shoreline*, where a bounding-box test leaves
+//    O(sqrt(distance * tile)).
+//  * The last filtering step (64x64 tile -> 32x8 leaf) is fused into the
+//    evaluation kernel: one warp per leaf, lane = candidate for the filter
+//    (redux.sync min + ballot), then lane = 4x2 pixels for the evaluation
+//    with candidates broadcast by shuffle.
+//  * Everything that decides a result is float64 and FMA-free:
+//    d2 = dx*dx + dy*dy with separately rounded products, d = sqrt_rn(d2),
+//    which is bit-identical to what scipy's cKDTree returns;
+//    pixel coordinates follow numpy.linspace bit for bit.  B200 runs FP64 at
+//    half the FP32 rate, which the pruning makes affordable.
+//  * Epilogue fused: size law in f64 -> f32, [hmin,hmax] clamp, min(old, .),
+//    optional A10 re-clamp, 16-byte hfun loads/stores.
+//
+// Algorithmic HBM bytes: 8 B/px (hfun read + write) + 16 B x N once.
+#include "ocsb_common.cuh"
+
+#include <limits>
+
+namespace {
+
+constexpr int kLeafW = 32, kLeafH = 8;
+constexpr int kTile0 = 64;            // finest list level (pixels)
+constexpr int kEvalThreads = 256;
+constexpr int kCandCap = 1024;        // per-CTA shared staging of a tile list
+constexpr double kDomEps = 1e-12;     // relative safety margin of the tests
+constexpr int kMaxLevels = 12;
+constexpr int kMaxSplit = 64;
+
+struct Geom {
+    LinAxis ax, ay;
+    int w, h;
+};
+
+struct Rect {
+    double xlo, xhi, ylo, yhi;
+};
+
+__device__ __forceinline__ Rect tile_rect(const Geom &g, int c0, int c1, int r0,
+                                          int r1) {
+    double xa = lin_at(g.ax, c0), xb = lin_at(g.ax, c1);
+    double ya = lin_at(g.ay, r0), yb = lin_at(g.ay, r1);
+    Rect q;
+    q.xlo = fmin(xa, xb); q.xhi = fmax(xa, xb);
+    q.ylo = fmin(ya, yb); q.yhi = fmax(ya, yb);
+    return q;
+}
+
+// squared distances of v to the four corners (00 = (xlo,ylo), 01 = (xlo,yhi),
+// 10 = (xhi,ylo), 11 = (xhi,yhi)) and to the rect itself
+struct CornerD2 {
+    double d00, d01, d10, d11;
+};
+
+__device__ __forceinline__ CornerD2 corner_d2(const Rect &q, double2 v) {
+    double a = v.x - q.xlo, b = v.x - q.xhi, c = v.y - q.ylo, d = v.y - q.yhi;
+    a *= a; b *= b; c *= c; d *= d;
+    CornerD2 o;
+    o.d00 = a + c; o.d01 = a + d; o.d10 = b + c; o.d11 = b + d;
+    return o;
+}
+
+__device__ __forceinline__ double rect_d2(const Rect &q, double2 v) {
+    double mx = fmax(fmax(q.xlo - v.x, v.x - q.xhi), 0.0);
+    double my = fmax(fmax(q.ylo - v.y, v.y - q.yhi), 0.0);
+    return mx * mx + my * my;
+}
+
+__device__ __forceinline__ double center_d2(const Rect &q, double2 v) {
+    double cx = 0.5 * (q.xlo + q.xhi), cy = 0.5 * (q.ylo + q.yhi);
+    double dx = v.x - cx, dy = v.y - cy;
+    return dx * dx + dy * dy;
+}
+
+struct Best {
+    double d2;
+    int id;
+};
+__device__ __forceinline__ void best_upd(Best &b, double d2, int id) {
+    if (d2 < b.d2 || (d2 == b.d2 && id < b.id)) { b.d2 = d2; b.id = id; }
+}
+__device__ __forceinline__ Best best_warp_min(Best b) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double d = __shfl_xor_sync(0xffffffffu, b.d2, o);
+        int i = __shfl_xor_sync(0xffffffffu, b.id, o);
+        best_upd(b, d, i);
+    }
+    return b;
+}
+
+// dominator table: squared corner distances (already inflated by 1+eps) of up
+// to 5 dominators
+struct Dom {
+    double c[5][4];
+};
+
+__device__ __forceinline__ bool dominated(const Dom &D, const CornerD2 &v) {
+    bool dom = false;
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+        dom = dom || (v.d00 > D.c[j][0] && v.d01 > D.c[j][1] &&
+                      v.d10 > D.c[j][2] && v.d11 > D.c[j][3]);
+    return dom;
+}
+
+// ---------------------------------------------------------------------------
+// level refinement
+// ---------------------------------------------------------------------------
+struct LevelDev {
+    int tw, th, ntx, nty;   // tile size (px) and tile grid
+    int *off;               // per tile: offset into ids
+    int *cnt;               // per tile: list length
+    int *ids;               // pool
+};
+
+struct RefineArgs {
+    Geom g;
+    LevelDev child;
+    LevelDev parent;        // parent.tw == 0 -> root (ids = 0..n_root-1)
+    int n_root;
+    const double2 *verts;
+    unsigned long long *pool_ctr;   // child pool bump counter
+    unsigned long long pool_cap;
+    int *overflow;
+    double r2lim;           // r^2 (1+eps), +inf if unbounded
+};
+
+__device__ __forceinline__ void child_px(const RefineArgs &A, int t, int *c0,
+                                         int *c1, int *r0, int *r1) {
+    int tx = t % A.child.ntx, ty = t / A.child.ntx;
+    *c0 = tx * A.child.tw;
+    *c1 = min(A.g.w, *c0 + A.child.tw) - 1;
+    *r0 = ty * A.child.th;
+    *r1 = min(A.g.h, *r0 + A.child.th) - 1;
+}
+
+__device__ __forceinline__ void parent_list(const RefineArgs &A, int c0, int r0,
+                                            int *off, int *cnt,
+                                            const int **ids) {
+    if (A.parent.tw == 0) {
+        *off = 0; *cnt = A.n_root; *ids = nullptr;
+    } else {
+        int pt = (r0 / A.parent.th) * A.parent.ntx + (c0 / A.parent.tw);
+        *off = A.parent.off[pt]; *cnt = A.parent.cnt[pt]; *ids = A.parent.ids;
+    }
+}
+
+// block-wide argmin of 5 (d2,id) slots; result valid in all threads via smem
+template <int BT>
+__device__ __forceinline__ void block_best5(Best b[5], Best *s_out /*[5]*/,
+                                            Best *s_tmp /*[BT/32][5]*/) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        Best r = best_warp_min(b[j]);
+        if (lane == 0) s_tmp[wid * 5 + j] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+        Best r = s_tmp[threadIdx.x];
+        for (int k = 1; k < BT / 32; ++k) {
+            Best o = s_tmp[k * 5 + threadIdx.x];
+            best_upd(r, o.d2, o.id);
+        }
+        s_out[threadIdx.x] = r;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void scan_best5(const Rect &q, const double2 *verts,
+                                           const int *ids, int off, int lo,
+                                           int hi, int stride, Best b[5]) {
+    for (int i = lo + (int)threadIdx.x; i < hi; i += stride) {
+        int id = ids ? ids[off + i] : i;
+        double2 v = verts[id];
+        CornerD2 c = corner_d2(q, v);
+        best_upd(b[0], center_d2(q, v), id);
+        best_upd(b[1], c.d00, id);
+        best_upd(b[2], c.d01, id);
+        best_upd(b[3], c.d10, id);
+        best_upd(b[4], c.d11, id);
+    }
+}
+
+__device__ __forceinline__ void build_dom(const Rect &q, const double2 *verts,
+                                          const Best *s_best, Dom *s_dom) {
+    if (threadIdx.x < 5) {
+        int id = s_best[threadIdx.x].id;
+        CornerD2 c = corner_d2(q, verts[id]);
+        const double m = 1.0 + kDomEps;
+        s_dom->c[threadIdx.x][0] = c.d00 * m;
+        s_dom->c[threadIdx.x][1] = c.d01 * m;
+        s_dom->c[threadIdx.x][2] = c.d10 * m;
+        s_dom->c[threadIdx.x][3] = c.d11 * m;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ bool keep_vertex(const Rect &q, const Dom &D,
+                                            double r2lim, double2 v) {
+    if (rect_d2(q, v) > r2lim) return false;
+    CornerD2 c = corner_d2(q, v);
+    return !dominated(D, c);
+}
+
+// fused single-CTA-per-tile refinement (levels with many tiles)
+template <int BT>
+__global__ void __launch_bounds__(BT) refine_fused_kernel(RefineArgs A) {
+    __shared__ Best s_best[5];
+    __shared__ Best s_tmp[(BT / 32) * 5];
+    __shared__ Dom s_dom;
+    __shared__ int s_count, s_pos;
+    __shared__ unsigned long long s_base;
+    if (*A.overflow) return;
+    const int t = blockIdx.x;
+    int c0, c1, r0, r1;
+    child_px(A, t, &c0, &c1, &r0, &r1);
+    const Rect q = tile_rect(A.g, c0, c1, r0, r1);
+    int off, cnt;
+    const int *ids;
+    parent_list(A, c0, r0, &off, &cnt, &ids);
+    if (cnt == 0) {
+        if (threadIdx.x == 0) { A.child.off[t] = 0; A.child.cnt[t] = 0; }
+        return;
+    }
+    Best b[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { b[j].d2 = INFINITY; b[j].id = 0x7fffffff; }
+    scan_best5(q, A.verts, ids, off, 0, cnt, BT, b);
+    block_best5<BT>(b, s_best, s_tmp);
+    build_dom(q, A.verts, s_best, &s_dom);
+    if (threadIdx.x == 0) { s_count = 0; s_pos = 0; }
+    __syncthreads();
+    int local = 0;
+    for (int i = threadIdx.x; i < cnt; i += BT) {
+        int id = ids ? ids[off + i] : i;
+        local += keep_vertex(q, s_dom, A.r2lim, A.verts[id]) ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&s_count, local);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long base = 0;
+        int total = s_count;
+        if (total) {
+            base = atomicAdd(A.pool_ctr, (unsigned long long)total);
+            if (base + total > A.pool_cap) { *A.overflow = 1; total = 0; }
+        }
+        s_base = base;
+        s_count = total;
+        A.child.off[t] = (int)base;
+        A.child.cnt[t] = total;
+    }
+    __syncthreads();
+    if (s_count == 0) return;
+    const unsigned long long base = s_base;
+    for (int i = threadIdx.x; i < cnt; i += BT) {
+        int id = ids ? ids[off + i] : i;
+        if (keep_vertex(q, s_dom, A.r2lim, A.verts[id])) {
+            int pos = atomicAdd(&s_pos, 1);
+            A.child.ids[base + pos] = id;
+        }
+    }
+}
+
+// ---- split path for levels with few tiles and long parent lists ------------
+struct SplitScratch {
+    Best *part;     // [ntiles][nsplit][5]
+    int *counts;    // [ntiles][nsplit]  (count, then exclusive offset)
+    int nsplit;
+};
+
+__device__ __forceinline__ void split_range(int cnt, int nsplit, int s, int *lo,
+                                            int *hi) {
+    int chunk = (cnt + nsplit - 1) / nsplit;
+    *lo = min(cnt, s * chunk);
+    *hi = min(cnt, *lo + chunk);
+}
+
+__global__ void __launch_bounds__(256)
+split_p1_kernel(RefineArgs A, SplitScratch S) {
+    __shared__ Best s_best[5];
+    __shared__ Best s_tmp[8 * 5];
+    const int t = blockIdx.x / S.nsplit, s = blockIdx.x % S.nsplit;
+    int c0, c1, r0, r1;
+    child_px(A, t, &c0, &c1, &r0, &r1);
+    const Rect q = tile_rect(A.g, c0, c1, r0, r1);
+    int off, cnt;
+    const int *ids;
+    parent_list(A, c0, r0, &off, &cnt, &ids);
+    int lo, hi;
+    split_range(cnt, S.nsplit, s, &lo, &hi);
+    Best b[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { b[j].d2 = INFINITY; b[j].id = 0x7fffffff; }
+    scan_best5(q, A.verts, ids, off, lo, hi, 256, b);
+    block_best5<256>(b, s_best, s_tmp);
+    if (threadIdx.x < 5)
+        S.part[((int64_t)t * S.nsplit + s) * 5 + threadIdx.x] = s_best[threadIdx.x];
+}
+
+__device__ __forceinline__ bool split_dom(const RefineArgs &A,
+                                          const SplitScratch &S, int t,
+                                          const Rect &q, Best *s_best,
+                                          Dom *s_dom) {
+    if (threadIdx.x < 5) {
+        Best r; r.d2 = INFINITY; r.id = 0x7fffffff;
+        for (int k = 0; k < S.nsplit; ++k) {
+            Best o = S.part[((int64_t)t * S.nsplit + k) * 5 + threadIdx.x];
+            best_upd(r, o.d2, o.id);
+        }
+        s_best[threadIdx.x] = r;
+    }
+    __syncthreads();
+    if (s_best[0].id == 0x7fffffff) return false;  // empty parent list
+    build_dom(q, A.verts, s_best, s_dom);
+    return true;
+}
+
+__global__ void __launch_bounds__(256)
+split_p2_kernel(RefineArgs A, SplitScratch S) {
+    __shared__ Best s_best[5];
+    __shared__ Dom s_dom;
+    __shared__ int s_count;
+    const int t = blockIdx.x / S.nsplit, s = blockIdx.x % S.nsplit;
+    int c0, c1, r0, r1;
+    child_px(A, t, &c0, &c1, &r0, &r1);
+    const Rect q = tile_rect(A.g, c0, c1, r0, r1);
+    int off, cnt;
+    const int *ids;
+    parent_list(A, c0, r0, &off, &cnt, &ids);
+    if (threadIdx.x == 0) s_count = 0;
+    if (!split_dom(A, S, t, q, s_best, &s_dom)) {
+        if (threadIdx.x == 0) S.counts[(int64_t)t * S.nsplit + s] = 0;
+        return;
+    }
+    int lo, hi;
+    split_range(cnt, S.nsplit, s, &lo, &hi);
+    int local = 0;
+    for (int i = lo + threadIdx.x; i < hi; i += 256) {
+        int id = ids ? ids[off + i] : i;
+        local += keep_vertex(q, s_dom, A.r2lim, A.verts[id]) ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&s_count, local);
+    __syncthreads();
+    if (threadIdx.x == 0) S.counts[(int64_t)t * S.nsplit + s] = s_count;
+}
+
+__global__ void split_p3_kernel(RefineArgs A, SplitScratch S, int ntiles) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    int total = 0;
+    for (int k = 0; k < S.nsplit; ++k) {
+        int c = S.counts[(int64_t)t * S.nsplit + k];
+        S.counts[(int64_t)t * S.nsplit + k] = total;
+        total += c;
+    }
+    unsigned long long base = 0;
+    if (total) {
+        base = atomicAdd(A.pool_ctr, (unsigned long long)total);
+        if (base + total > A.pool_cap) { *A.overflow = 1; total = 0; }
+    }
+    A.child.off[t] = (int)base;
+    A.child.cnt[t] = total;
+}
+
+__global__ void __launch_bounds__(256)
+split_p4_kernel(RefineArgs A, SplitScratch S) {
+    __shared__ Best s_best[5];
+    __shared__ Dom s_dom;
+    __shared__ int s_pos;
+    const int t = blockIdx.x / S.nsplit, s = blockIdx.x % S.nsplit;
+    if (A.child.cnt[t] == 0) return;
+    int c0, c1, r0, r1;
+    child_px(A, t, &c0, &c1, &r0, &r1);
+    const Rect q = tile_rect(A.g, c0, c1, r0, r1);
+    int off, cnt;
+    const int *ids;
+    parent_list(A, c0, r0, &off, &cnt, &ids);
+    if (threadIdx.x == 0) s_pos = 0;
+    if (!split_dom(A, S, t, q, s_best, &s_dom)) return;
+    int lo, hi;
+    split_range(cnt, S.nsplit, s, &lo, &hi);
+    const int64_t base = (int64_t)A.child.off[t] + S.counts[(int64_t)t * S.nsplit + s];
+    for (int i = lo + threadIdx.x; i < hi; i += 256) {
+        int id = ids ? ids[off + i] : i;
+        if (keep_vertex(q, s_dom, A.r2lim, A.verts[id])) {
+            int pos = atomicAdd(&s_pos, 1);
+            A.child.ids[base + pos] = id;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// evaluation: fused leaf filter + exact distance + size law
+// ---------------------------------------------------------------------------
+struct EvalArgs {
+    Geom g;
+    LevelDev lvl;           // the 64-px level
+    const double2 *verts;
+    const float *old_;
+    int64_t os;
+    float *new_;
+    int64_t ns;
+    double *dist;
+    int64_t *idx;
+    int64_t nv;
+    double rate_target, target, r, r2, r2lim;
+    float hmin_f, hmax_f;
+    int has_hmin, has_hmax, fuse_clamp;
+    int vec_old, vec_new;
+    const int *overflow;
+};
+
+template <bool WANT_IDX>
+__global__ void __launch_bounds__(kEvalThreads) eval_kernel(EvalArgs A) {
+    __shared__ double2 s_v[kCandCap];
+    __shared__ int s_id[kCandCap];
+    if (*A.overflow) return;
+    const int t = blockIdx.x;
+    const int tx = t % A.lvl.ntx, ty = t / A.lvl.ntx;
+    const int cnt = A.lvl.cnt[t];
+    const int off = A.lvl.off[t];
+    const bool in_smem = cnt <= kCandCap;
+    if (in_smem) {
+        for (int i = threadIdx.x; i < cnt; i += kEvalThreads) {
+            int id = A.lvl.ids[off + i];
+            s_id[i] = id;
+            s_v[i] = A.verts[id];
+        }
+        __syncthreads();
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const Geom &g = A.g;
+
+    for (int leaf = wid; leaf < 16; leaf += kEvalThreads / 32) {
+        const int c0 = tx * kTile0 + (leaf & 1) * kLeafW;
+        const int r0 = ty * kTile0 + (leaf >> 1) * kLeafH;
+        if (c0 >= g.w || r0 >= g.h) continue;
+        const int c1 = min(g.w, c0 + kLeafW) - 1;
+        const int r1 = min(g.h, r0 + kLeafH) - 1;
+        const Rect q = tile_rect(g, c0, c1, r0, r1);
+
+        // this lane's pixels: 4 consecutive columns x 2 rows (row, row + 4)
+        const int gcol = c0 + (lane & 7) * 4;
+        const int grow0 = r0 + (lane >> 3);
+        const int grow1 = grow0 + 4;
+        double px[4], py[2];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
+        py[0] = lin_at(g.ay, min(grow0, g.h - 1));
+        py[1] = lin_at(g.ay, min(grow1, g.h - 1));
+
+        double best[8];
+        int bid[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { best[k] = INFINITY; bid[k] = 0x7fffffff; }
+
+        if (cnt > 0) {
+            // ---- pass A: dominators (nearest to centre and corners) --------
+            unsigned domkey[5];
+            Dom D;
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+                domkey[j] = 0xffffffffu;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) D.c[j][k] = INFINITY;
+            }
+            for (int b0 = 0; b0 < cnt; b0 += 32) {
+                const int i = b0 + lane;
+                const bool valid = i < cnt;
+                double2 v = make_double2(0.0, 0.0);
+                if (valid) v = in_smem ? s_v[i] : A.verts[A.lvl.ids[off + i]];
+                const CornerD2 c = corner_d2(q, v);
+                const double dc = center_d2(q, v);
+                const double dd[5] = {dc, c.d00, c.d01, c.d10, c.d11};
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    unsigned key = valid ? __float_as_uint((float)dd[j]) : 0xffffffffu;
+                    unsigned m = __reduce_min_sync(0xffffffffu, key);
+                    if (m < domkey[j]) {   // warp-uniform
+                        domkey[j] = m;
+                        int src = __ffs(__ballot_sync(0xffffffffu, key == m)) - 1;
+                        const double mg = 1.0 + kDomEps;
+                        D.c[j][0] = __shfl_sync(0xffffffffu, c.d00, src) * mg;
+                        D.c[j][1] = __shfl_sync(0xffffffffu, c.d01, src) * mg;
+                        D.c[j][2] = __shfl_sync(0xffffffffu, c.d10, src) * mg;
+                        D.c[j][3] = __shfl_sync(0xffffffffu, c.d11, src) * mg;
+                    }
+                }
+            }
+            // ---- pass B: filter, then evaluate survivors -------------------
+            for (int b0 = 0; b0 < cnt; b0 += 32) {
+                const int i = b0 + lane;
+                const bool valid = i < cnt;
+                double2 v = make_double2(0.0, 0.0);
+                int id = 0;
+                if (valid) {
+                    if (in_smem) { v = s_v[i]; id = s_id[i]; }
+                    else { id = A.lvl.ids[off + i]; v = A.verts[id]; }
+                }
+                bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                            !dominated(D, corner_d2(q, v));
+                unsigned mask = __ballot_sync(0xffffffffu, keep);
+                while (mask) {
+                    const int s = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const double vx = __shfl_sync(0xffffffffu, v.x, s);
+                    const double vy = __shfl_sync(0xffffffffu, v.y, s);
+                    int vid = 0;
+                    if (WANT_IDX) vid = __shfl_sync(0xffffffffu, id, s);
+                    double dx2[4], dy2[2];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        double d = __dsub_rn(px[k], vx);
+                        dx2[k] = __dmul_rn(d, d);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        double d = __dsub_rn(py[j], vy);
+                        dy2[j] = __dmul_rn(d, d);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const double d2 = __dadd_rn(dx2[k], dy2[j]);
+                            if (WANT_IDX) {
+                                if (d2 < best[j * 4 + k] ||
+                                    (d2 == best[j * 4 + k] && vid < bid[j * 4 + k])) {
+                                    best[j * 4 + k] = d2;
+                                    bid[j * 4 + k] = vid;
+                                }
+                            } else {
+                                best[j * 4 + k] = fmin(best[j * 4 + k], d2);
+                            }
+                        }
+                }
+            }
+        }
+
+        // ---- epilogue ------------------------------------------------------
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int row = j ? grow1 : grow0;
+            if (row > r1 || gcol > c1) continue;
+            const float *orow = A.old_ + (int64_t)row * A.os;
+            float *nrow = A.new_ + (int64_t)row * A.ns;
+            const bool full = gcol + 3 <= c1;
+            float o[4];
+            if (A.vec_old && full) {
+                float4 v4 = *reinterpret_cast<const float4 *>(orow + gcol);
+                o[0] = v4.x; o[1] = v4.y; o[2] = v4.z; o[3] = v4.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) o[k] = (gcol + k <= c1) ? orow[gcol + k] : 0.f;
+            }
+            float out[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const double d2 = best[j * 4 + k];
+                const bool hit = d2 < A.r2;
+                const double d = hit ? __dsqrt_rn(d2) : A.r;
+                // values = expansion_rate*target_size*distances + target_size
+                const double v64 = __dadd_rn(__dmul_rn(A.rate_target, d), A.target);
+                float vf = (float)v64;
+                vf = clamp_f32(vf, A.has_hmin, A.hmin_f, A.has_hmax, A.hmax_f);
+                float res = np_minimum_f(o[k], vf);
+                if (A.fuse_clamp)
+                    res = clamp_f32(res, A.has_hmin, A.hmin_f, A.has_hmax, A.hmax_f);
+                out[k] = res;
+                if (gcol + k <= c1) {
+                    const int64_t lin = (int64_t)row * g.w + gcol + k;
+                    if (A.dist) A.dist[lin] = d;
+                    if (WANT_IDX) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
+                }
+            }
+            if (A.vec_new && full) {
+                *reinterpret_cast<float4 *>(nrow + gcol) =
+                    make_float4(out[0], out[1], out[2], out[3]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (gcol + k <= c1) nrow[gcol + k] = out[k];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host orchestration
+// ---------------------------------------------------------------------------
+struct LevelHost {
+    int tw, th, ntx, nty;
+    int64_t ntiles;
+};
+
+template <int BT>
+void launch_fused(ocsb_ctx *ctx, const RefineArgs &A, int64_t ntiles) {
+    refine_fused_kernel<BT><<<(unsigned)ntiles, BT, 0, ctx->stream>>>(A);
+    OCSB_LAUNCHED(ctx);
+}
+
+}  // namespace
+
+int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
+                       int64_t nv, const float *old_, int64_t old_stride,
+                       float *new_, int64_t new_stride, double *dist_out,
+                       int64_t *idx_out) {
+    OCSB_REQUIRE(((uintptr_t)verts & 15) == 0,
+                 "ocsb_hfun_feature: verts_xy must be 16-byte aligned");
+    const int w = a.ax.n, h = a.ay.n;
+    Geom g{a.ax, a.ay, w, h};
+
+    // ---- level plan --------------------------------------------------------
+    std::vector<LevelHost> lv;
+    for (int s = kTile0; (int)lv.size() < kMaxLevels; s *= 4) {
+        LevelHost L;
+        L.tw = L.th = s;
+        L.ntx = (w + s - 1) / s;
+        L.nty = (h + s - 1) / s;
+        L.ntiles = (int64_t)L.ntx * L.nty;
+        lv.push_back(L);
+        if (L.ntiles == 1) break;
+        if (s > (1 << 28)) break;
+    }
+    // the coarsest level actually built: the finest one with <= 4 tiles or, if
+    // the parent list is the whole vertex set, any level is fine -- keep all
+    // levels down from the first with ntiles <= 16 so upper lists stay short
+    int top = 0;
+    for (int i = 0; i < (int)lv.size(); ++i) {
+        top = i;
+        if (lv[i].ntiles <= 16) break;
+    }
+
+    const double inf = std::numeric_limits<double>::infinity();
+    const bool bounded = a.r < inf;
+    const double r2 = bounded ? a.r * a.r : inf;
+    const double r2lim = bounded ? (a.r > 0 ? r2 * (1.0 + kDomEps) : -1.0) : inf;
+
+    ScratchGuard sg(ctx);
+    unsigned long long *ctrs = nullptr;   // [kMaxLevels] + overflow flag behind
+    OCSB_TRY(sg.get(&ctrs, kMaxLevels + 2));
+    int *overflow = reinterpret_cast<int *>(ctrs + kMaxLevels);
+
+    std::vector<LevelDev> dev(lv.size());
+    for (int i = 0; i <= top; ++i) {
+        dev[i].tw = lv[i].tw; dev[i].th = lv[i].th;
+        dev[i].ntx = lv[i].ntx; dev[i].nty = lv[i].nty;
+        OCSB_TRY(sg.get(&dev[i].off, (size_t)lv[i].ntiles));
+        OCSB_TRY(sg.get(&dev[i].cnt, (size_t)lv[i].ntiles));
+        dev[i].ids = nullptr;
+    }
+
+    for (int attempt = 0; attempt < 6; ++attempt) {
+        ScratchGuard pools(ctx);
+        OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (kMaxLevels + 2) * sizeof(*ctrs),
+                                  ctx->stream));
+        std::vector<unsigned long long> cap(top + 1);
+        for (int i = 0; i <= top; ++i) {
+            unsigned long long c = 4ull * (unsigned long long)nv +
+                                   48ull * (unsigned long long)lv[i].ntiles +
+                                   (1ull << 16);
+            c <<= (2 * attempt);
+            if (c > 0x7fffffffull) c = 0x7fffffffull;  // int offsets
+            cap[i] = c;
+            OCSB_TRY(pools.get(&dev[i].ids, (size_t)c));
+        }
+        for (int i = top; i >= 0; --i) {
+            RefineArgs A;
+            A.g = g;
+            A.child = dev[i];
+            if (i == top) {
+                A.parent = LevelDev{0, 0, 0, 0, nullptr, nullptr, nullptr};
+            } else {
+                A.parent = dev[i + 1];
+            }
+            A.n_root = (int)nv;
+            A.verts = reinterpret_cast<const double2 *>(verts);
+            A.pool_ctr = ctrs + i;
+            A.pool_cap = cap[i];
+            A.overflow = overflow;
+            A.r2lim = r2lim;
+            const int64_t ntiles = lv[i].ntiles;
+            // long parent lists on few tiles: split each list over several CTAs
+            int nsplit = 1;
+            const int64_t want = 2 * (int64_t)ctx->num_sms;
+            if (ntiles < want && (i == top ? nv : 4096) >= 4096) {
+                int64_t est = (i == top) ? nv : nv / 2;   // parent list scale
+                nsplit = (int)((want + ntiles - 1) / ntiles);
+                int64_t maxs = (est + 2047) / 2048;
+                if (nsplit > maxs) nsplit = (int)maxs;
+                if (nsplit > kMaxSplit) nsplit = kMaxSplit;
+                if (nsplit < 1) nsplit = 1;
+            }
+            if (nsplit > 1) {
+                SplitScratch S;
+                S.nsplit = nsplit;
+                OCSB_TRY(pools.get(&S.part, (size_t)ntiles * nsplit * 5));
+                OCSB_TRY(pools.get(&S.counts, (size_t)ntiles * nsplit));
+                const unsigned gridn = (unsigned)(ntiles * nsplit);
+                split_p1_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
+                OCSB_LAUNCHED(ctx);
+                split_p2_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
+                OCSB_LAUNCHED(ctx);
+                split_p3_kernel<<<(unsigned)((ntiles + 127) / 128), 128, 0,
+                                  ctx->stream>>>(A, S, (int)ntiles);
+                OCSB_LAUNCHED(ctx);
+                split_p4_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
+                OCSB_LAUNCHED(ctx);
+            } else if (i == 0) {
+                launch_fused<32>(ctx, A, ntiles);
+            } else if (i == 1) {
+                launch_fused<64>(ctx, A, ntiles);
+            } else {
+                launch_fused<256>(ctx, A, ntiles);
+            }
+            OCSB_CHECK_LAUNCH();
+        }
+
+        EvalArgs E;
+        E.g = g;
+        E.lvl = dev[0];
+        E.verts = reinterpret_cast<const double2 *>(verts);
+        E.old_ = old_; E.os = old_stride;
+        E.new_ = new_; E.ns = new_stride;
+        E.dist = dist_out; E.idx = idx_out; E.nv = nv;
+        E.rate_target = a.rate_target; E.target = a.target;
+        E.r = a.r; E.r2 = (bounded && a.r <= 0) ? -1.0 : r2; E.r2lim = r2lim;
+        E.hmin_f = a.hmin_f; E.hmax_f = a.hmax_f;
+        E.has_hmin = a.has_hmin; E.has_hmax = a.has_hmax;
+        E.fuse_clamp = a.fuse_clamp;
+        E.vec_old = (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
+        E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
+        E.overflow = overflow;
+        if (idx_out)
+            eval_kernel<true><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
+        else
+            eval_kernel<false><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
+        OCSB_LAUNCHED(ctx);
+        OCSB_CHECK_LAUNCH();
+
+        // candidate pools are bump-allocated with a size guess: read the
+        // overflow flag back and retry with larger pools if it tripped (the
+        // evaluation kernel writes nothing in that case)
+        int *flag_h = reinterpret_cast<int *>(ctx->pinned);
+        int flag_local = 0;
+        if (!flag_h) flag_h = &flag_local;
+        OCSB_CUDA(cudaMemcpyAsync(flag_h, overflow, sizeof(int),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+        OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (*flag_h == 0) return OCSB_OK;
+    }
+    ocsb_set_error("ocsb_hfun_feature: candidate pools overflowed after 6 "
+                   "attempts (degenerate vertex set?)");
+    return OCSB_EOVERFLOW;
+}
+
+int32_t k_nearest_vertex(ocsb_ctx *, const double *, int64_t, const double *,
+                         int64_t, double, double *, int64_t *) {
+    ocsb_set_error("ocsb_nearest_vertex: not implemented in this build");
+    return OCSB_EINVAL;
+}

@@ -1,0 +1,552 @@
+// C ABI entry points of libocsb200.so: argument validation, host<->device
+// staging, context management.  Kernels live in k_*.cu.
+#include "ocsb_common.cuh"
+
+#include <stdarg.h>
+#include <limits>
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+
+void ocsb_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *ocsb_last_error(void) { return g_err; }
+extern "C" int32_t ocsb_abi_version(void) { return OCSB_ABI_VERSION; }
+
+// ---------------------------------------------------------------------------
+// scratch memory: stream-ordered allocation from the device's default pool
+// ---------------------------------------------------------------------------
+int32_t ocsb_alloc(ocsb_ctx *ctx, void **p, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    cudaError_t e = cudaMallocAsync(p, bytes, ctx->stream);
+    if (e != cudaSuccess) {
+        ocsb_set_error("cudaMallocAsync(%zu bytes) -> %s", bytes,
+                       cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return OCSB_ENOMEM;
+    }
+    return OCSB_OK;
+}
+
+void ocsb_free(ocsb_ctx *ctx, void *p) {
+    if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+bool ocsb_is_device_ptr(const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes at;
+    cudaError_t e = cudaPointerGetAttributes(&at, p);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+int32_t Staged::init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
+                     int64_t stride_, size_t elem_, int dir_) {
+    ctx = c;
+    user = const_cast<void *>(p);
+    rows = rows_;
+    width = width_;
+    user_stride = stride_;
+    elem = elem_;
+    dir = dir_;
+    if (!p) {
+        dev = nullptr;
+        return OCSB_OK;
+    }
+    if (ocsb_is_device_ptr(p)) {
+        dev = user;
+        dev_stride = user_stride;
+        staged = false;
+        return OCSB_OK;
+    }
+    staged = true;
+    dev_stride = width;
+    OCSB_TRY(ocsb_alloc(ctx, &dev, (size_t)rows * (size_t)width * elem));
+    if (dir & STAGE_IN) {
+        OCSB_CUDA(cudaMemcpy2DAsync(dev, (size_t)width * elem, user,
+                                    (size_t)user_stride * elem,
+                                    (size_t)width * elem, (size_t)rows,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return OCSB_OK;
+}
+
+int32_t Staged::finish() {
+    if (staged && dev && (dir & STAGE_OUT)) {
+        OCSB_CUDA(cudaMemcpy2DAsync(user, (size_t)user_stride * elem, dev,
+                                    (size_t)width * elem, (size_t)width * elem,
+                                    (size_t)rows, cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+    }
+    return OCSB_OK;
+}
+
+Staged::~Staged() {
+    if (staged && dev) ocsb_free(ctx, dev);
+}
+
+// after the work of one API call was enqueued: if anything was staged the
+// call must not return before the copy-back has landed in the caller's memory
+static int32_t finish_call(ocsb_ctx *ctx, std::initializer_list<Staged *> bufs) {
+    bool any = false;
+    for (Staged *s : bufs) {
+        OCSB_TRY(s->finish());
+        any = any || s->staged;
+    }
+    if (any) OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OCSB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_ctx_create(int32_t device, void *stream,
+                                   ocsb_ctx **out) {
+    OCSB_REQUIRE(out != nullptr, "ocsb_ctx_create: out is NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        (void)cudaGetLastError();
+        ocsb_set_error("ocsb_ctx_create: no CUDA device available (%s); "
+                       "libocsb200 has no CPU fallback",
+                       e != cudaSuccess ? cudaGetErrorString(e) : "0 devices");
+        return OCSB_ECUDA;
+    }
+    OCSB_REQUIRE(device >= 0 && device < ndev,
+                 "ocsb_ctx_create: device %d out of range [0,%d)", device, ndev);
+    OCSB_CUDA(cudaSetDevice(device));
+    ocsb_ctx *c = new ocsb_ctx();
+    c->device = device;
+    if (stream) {
+        c->stream = (cudaStream_t)stream;
+        c->own_stream = false;
+    } else {
+        cudaError_t e2 = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e2 != cudaSuccess) {
+            ocsb_set_error("cudaStreamCreate -> %s", cudaGetErrorString(e2));
+            delete c;
+            return OCSB_ECUDA;
+        }
+        c->own_stream = true;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)
+        c->num_sms = prop.multiProcessorCount;
+    // keep freed scratch in the pool instead of returning it to the driver
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t thr = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    c->pinned_bytes = 4096;
+    if (cudaMallocHost(&c->pinned, c->pinned_bytes) != cudaSuccess) {
+        (void)cudaGetLastError();
+        c->pinned = nullptr;
+    }
+    *out = c;
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
+    if (!ctx) return OCSB_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->spl_coef) cudaFree(ctx->spl_coef);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_ctx_set_stream(ocsb_ctx *ctx, void *stream) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    if (ctx->own_stream) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamDestroy(ctx->stream);
+        ctx->own_stream = false;
+    }
+    ctx->stream = (cudaStream_t)stream;
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_ctx_sync(ocsb_ctx *ctx) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OCSB_OK;
+}
+
+extern "C" int64_t ocsb_ctx_launch_count(const ocsb_ctx *ctx) {
+    return ctx ? ctx->launches : 0;
+}
+
+extern "C" int32_t ocsb_ctx_trim(ocsb_ctx *ctx) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->spl_coef) {
+        cudaFree(ctx->spl_coef);
+        ctx->spl_coef = nullptr;
+        ctx->spl_key = nullptr;
+        ctx->spl_bytes = 0;
+    }
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess)
+        cudaMemPoolTrimTo(pool, 0);
+    return OCSB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// A1 windows (host only)
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_windows(int32_t width, int32_t height,
+                                int32_t chunk_size, int32_t overlap,
+                                int32_t *out4, int64_t cap, int64_t *n) {
+    OCSB_REQUIRE(n != nullptr, "ocsb_windows: n is NULL");
+    OCSB_REQUIRE(width > 0 && height > 0, "ocsb_windows: empty raster %dx%d",
+                 width, height);
+    OCSB_REQUIRE(chunk_size >= 0, "Argument chunk_size must be >= 0.");
+    if (chunk_size == 0) {
+        *n = 1;
+        if (!out4 || cap < 1) return out4 ? OCSB_EOVERFLOW : OCSB_OK;
+        out4[0] = 0; out4[1] = 0; out4[2] = width; out4[3] = height;
+        return OCSB_OK;
+    }
+    int64_t nh = ((int64_t)height + chunk_size - 1) / chunk_size;
+    int64_t nw = ((int64_t)width + chunk_size - 1) / chunk_size;
+    *n = nh * nw;
+    if (!out4) return OCSB_OK;
+    if (cap < *n) {
+        ocsb_set_error("ocsb_windows: %lld windows do not fit cap %lld",
+                       (long long)*n, (long long)cap);
+        return OCSB_EOVERFLOW;
+    }
+    int64_t k = 0;
+    for (int64_t i = 0; i < nh; ++i) {
+        for (int64_t j = 0; j < nw; ++j) {
+            int64_t off_h = i * chunk_size, off_w = j * chunk_size;
+            int64_t h = (int64_t)chunk_size + overlap;
+            if (off_h + h > height) h = h - (off_h + h) % height;
+            int64_t w = (int64_t)chunk_size + overlap;
+            if (off_w + w > width) w = w - (off_w + w) % width;
+            out4[4 * k + 0] = (int32_t)off_w;
+            out4[4 * k + 1] = (int32_t)off_h;
+            out4[4 * k + 2] = (int32_t)w;
+            out4[4 * k + 3] = (int32_t)h;
+            ++k;
+        }
+    }
+    return OCSB_OK;
+}
+
+static int32_t check_win(const ocsb_win *win, const char *who) {
+    OCSB_REQUIRE(win != nullptr, "%s: win is NULL", who);
+    OCSB_REQUIRE(win->width > 0 && win->height > 0, "%s: empty window %dx%d",
+                 who, win->width, win->height);
+    OCSB_REQUIRE(isfinite(win->x0) && isfinite(win->x1) && isfinite(win->y0) &&
+                     isfinite(win->y1),
+                 "%s: non-finite window bounds", who);
+    return OCSB_OK;
+}
+
+static void win_axes(const ocsb_win *win, LinAxis *ax, LinAxis *ay) {
+    *ax = make_axis(win->x0, win->x1, win->width);   // get_x: linspace(x0, x1, w)
+    *ay = make_axis(win->y1, win->y0, win->height);  // get_y: linspace(y1, y0, h)
+}
+
+#define CTX_ENTER(who)                                                         \
+    OCSB_REQUIRE(ctx != nullptr, "%s: ctx is NULL", who);                      \
+    OCSB_CUDA(cudaSetDevice(ctx->device))
+
+// ---------------------------------------------------------------------------
+// A2 coords
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_window_coords(ocsb_ctx *ctx, const ocsb_win *win,
+                                      double *x_out, double *y_out) {
+    CTX_ENTER("ocsb_window_coords");
+    OCSB_TRY(check_win(win, "ocsb_window_coords"));
+    OCSB_REQUIRE(x_out && y_out, "ocsb_window_coords: NULL output");
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    Staged sx, sy;
+    OCSB_TRY(sx.init(ctx, x_out, 1, win->width, win->width, 8, STAGE_OUT));
+    OCSB_TRY(sy.init(ctx, y_out, 1, win->height, win->height, 8, STAGE_OUT));
+    OCSB_TRY(k_coords(ctx, ax, ay, (double *)sx.dev, (double *)sy.dev));
+    return finish_call(ctx, {&sx, &sy});
+}
+
+// ---------------------------------------------------------------------------
+// A4 fill / A10 clamp / A12 min-combine
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_fill_f32(ocsb_ctx *ctx, float *dst, int64_t n,
+                                 float value) {
+    CTX_ENTER("ocsb_fill_f32");
+    OCSB_REQUIRE(n >= 0, "ocsb_fill_f32: negative n");
+    if (n == 0) return OCSB_OK;
+    OCSB_REQUIRE(dst, "ocsb_fill_f32: dst is NULL");
+    Staged s;
+    OCSB_TRY(s.init(ctx, dst, 1, n, n, 4, STAGE_OUT));
+    OCSB_TRY(k_fill_f32(ctx, (float *)s.dev, n, value));
+    return finish_call(ctx, {&s});
+}
+
+extern "C" int32_t ocsb_hfun_clamp(ocsb_ctx *ctx, float *hfun,
+                                   int64_t row_stride, int32_t width,
+                                   int32_t height, double hmin, double hmax) {
+    CTX_ENTER("ocsb_hfun_clamp");
+    OCSB_REQUIRE(hfun && width > 0 && height > 0 && row_stride >= width,
+                 "ocsb_hfun_clamp: bad buffer (%p, %dx%d, stride %lld)",
+                 (void *)hfun, width, height, (long long)row_stride);
+    Staged s;
+    OCSB_TRY(s.init(ctx, hfun, height, width, row_stride, 4, STAGE_INOUT));
+    OCSB_TRY(k_clamp(ctx, (float *)s.dev, s.dev_stride, width, height, hmin,
+                     hmax));
+    return finish_call(ctx, {&s});
+}
+
+extern "C" int32_t ocsb_min_combine(ocsb_ctx *ctx, float *dst,
+                                    int64_t dst_stride, const float *src,
+                                    int64_t src_stride, int32_t width,
+                                    int32_t height) {
+    CTX_ENTER("ocsb_min_combine");
+    OCSB_REQUIRE(dst && src && width > 0 && height > 0 &&
+                     dst_stride >= width && src_stride >= width,
+                 "ocsb_min_combine: bad buffers");
+    Staged d, s;
+    OCSB_TRY(d.init(ctx, dst, height, width, dst_stride, 4, STAGE_INOUT));
+    OCSB_TRY(s.init(ctx, src, height, width, src_stride, 4, STAGE_IN));
+    OCSB_TRY(k_min_combine(ctx, (float *)d.dev, d.dev_stride,
+                           (const float *)s.dev, s.dev_stride, width, height));
+    return finish_call(ctx, {&d, &s});
+}
+
+// ---------------------------------------------------------------------------
+// A6 + A7 feature distance sizing
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_hfun_feature(
+    ocsb_ctx *ctx, const ocsb_win *win, const double *verts_xy, int64_t nv,
+    const float *hfun_old, int64_t old_stride, float *hfun_new,
+    int64_t new_stride, double expansion_rate, double target_size, double hmin,
+    double hmax, int32_t fuse_clamp, double *dist_out, int64_t *idx_out) {
+    CTX_ENTER("ocsb_hfun_feature");
+    OCSB_TRY(check_win(win, "ocsb_hfun_feature"));
+    OCSB_REQUIRE(verts_xy && nv > 0,
+                 "ocsb_hfun_feature: empty vertex set (cKDTree needs a "
+                 "non-empty (N,2) array)");
+    OCSB_REQUIRE(nv < (int64_t)2147483647, "ocsb_hfun_feature: nv too large");
+    OCSB_REQUIRE(hfun_old && hfun_new && old_stride >= win->width &&
+                     new_stride >= win->width,
+                 "ocsb_hfun_feature: bad hfun buffers");
+    OCSB_REQUIRE(!ocsb_is_none(target_size) && target_size > 0,
+                 "Argument target_size must be greater than zero.");
+    OCSB_REQUIRE(!ocsb_is_none(expansion_rate),
+                 "ocsb_hfun_feature: expansion_rate is NaN");
+
+    FeatureArgs a;
+    win_axes(win, &a.ax, &a.ay);
+    a.rate_target = expansion_rate * target_size;
+    a.target = target_size;
+    a.has_hmin = !ocsb_is_none(hmin);
+    a.has_hmax = !ocsb_is_none(hmax);
+    a.hmin_f = a.has_hmin ? (float)hmin : 0.f;
+    a.hmax_f = a.has_hmax ? (float)hmax : 0.f;
+    a.fuse_clamp = fuse_clamp;
+    if (a.has_hmax && hmax != 0.0) {  // `if self.hmax:` hfun/raster.py:1240
+        OCSB_REQUIRE(a.rate_target != 0.0,
+                     "ocsb_hfun_feature: float division by zero "
+                     "(expansion_rate * target_size == 0 with hmax set)");
+        a.r = (hmax - target_size) / a.rate_target;
+    } else {
+        a.r = std::numeric_limits<double>::infinity();
+    }
+
+    const int w = win->width, h = win->height;
+    Staged sv, so, sn, sd, si;
+    OCSB_TRY(sv.init(ctx, verts_xy, 1, nv * 2, nv * 2, 8, STAGE_IN));
+    const bool alias = (const void *)hfun_old == (const void *)hfun_new &&
+                       old_stride == new_stride;
+    if (alias) {
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT));
+    } else {
+        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN));
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT));
+    }
+    OCSB_TRY(sd.init(ctx, dist_out, h, w, w, 8, STAGE_OUT));
+    OCSB_TRY(si.init(ctx, idx_out, h, w, w, 8, STAGE_OUT));
+    const float *oldp = alias ? (const float *)sn.dev : (const float *)so.dev;
+    int64_t olds = alias ? sn.dev_stride : so.dev_stride;
+    OCSB_TRY(k_hfun_feature(ctx, a, (const double *)sv.dev, nv, oldp, olds,
+                            (float *)sn.dev, sn.dev_stride, (double *)sd.dev,
+                            (int64_t *)si.dev));
+    return finish_call(ctx, {&sv, &so, &sn, &sd, &si});
+}
+
+extern "C" int32_t ocsb_nearest_vertex(ocsb_ctx *ctx, const double *verts_xy,
+                                       int64_t nv, const double *query_xy,
+                                       int64_t nq, double r, double *dist_out,
+                                       int64_t *idx_out) {
+    CTX_ENTER("ocsb_nearest_vertex");
+    OCSB_REQUIRE(verts_xy && nv > 0, "ocsb_nearest_vertex: empty vertex set");
+    OCSB_REQUIRE(nv < (int64_t)2147483647, "ocsb_nearest_vertex: nv too large");
+    OCSB_REQUIRE(nq >= 0, "ocsb_nearest_vertex: negative nq");
+    if (nq == 0) return OCSB_OK;
+    OCSB_REQUIRE(query_xy && (dist_out || idx_out),
+                 "ocsb_nearest_vertex: NULL buffers");
+    double rr = ocsb_is_none(r) ? std::numeric_limits<double>::infinity() : r;
+    Staged sv, sq, sd, si;
+    OCSB_TRY(sv.init(ctx, verts_xy, 1, nv * 2, nv * 2, 8, STAGE_IN));
+    OCSB_TRY(sq.init(ctx, query_xy, 1, nq * 2, nq * 2, 8, STAGE_IN));
+    OCSB_TRY(sd.init(ctx, dist_out, 1, nq, nq, 8, STAGE_OUT));
+    OCSB_TRY(si.init(ctx, idx_out, 1, nq, nq, 8, STAGE_OUT));
+    OCSB_TRY(k_nearest_vertex(ctx, (const double *)sv.dev, nv,
+                              (const double *)sq.dev, nq, rr,
+                              (double *)sd.dev, (int64_t *)si.dev));
+    return finish_call(ctx, {&sv, &sq, &sd, &si});
+}
+
+// ---------------------------------------------------------------------------
+// A8 flow limiter
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_hfun_flow_limiter(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, const float *hfun_old, int64_t old_stride,
+    float *hfun_new, int64_t new_stride, double dx, double dy, double hmin,
+    double hmax, double lower_bound, double upper_bound, double ghmin,
+    double ghmax, int32_t fuse_clamp) {
+    CTX_ENTER("ocsb_hfun_flow_limiter");
+    OCSB_TRY(check_win(win, "ocsb_hfun_flow_limiter"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_hfun_flow_limiter: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(win->width >= 2 && win->height >= 2,
+                 "Shape of array too small to calculate a numerical gradient, "
+                 "at least (edge_order + 1) elements are required.");
+    OCSB_REQUIRE(dem && hfun_old && hfun_new && dem_stride >= win->width &&
+                     old_stride >= win->width && new_stride >= win->width,
+                 "ocsb_hfun_flow_limiter: bad buffers");
+    OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
+                 "ocsb_hfun_flow_limiter: dx/dy is NaN");
+    const int w = win->width, h = win->height;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    Staged sz, so, sn;
+    OCSB_TRY(sz.init(ctx, dem, h, w, dem_stride, es, STAGE_IN));
+    const bool alias = (const void *)hfun_old == (const void *)hfun_new &&
+                       old_stride == new_stride;
+    if (alias) {
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT));
+    } else {
+        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN));
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT));
+    }
+    LimiterArgs a{dx, dy, hmin, hmax, lower_bound, upper_bound, ghmin, ghmax,
+                  fuse_clamp};
+    const float *oldp = alias ? (const float *)sn.dev : (const float *)so.dev;
+    int64_t olds = alias ? sn.dev_stride : so.dev_stride;
+    OCSB_TRY(k_flow_limiter(ctx, w, h, sz.dev, dem_dtype, sz.dev_stride, oldp,
+                            olds, (float *)sn.dev, sn.dev_stride, a));
+    return finish_call(ctx, {&sz, &so, &sn});
+}
+
+// ---------------------------------------------------------------------------
+// A14 interpolate
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_spline_prefilter(ocsb_ctx *ctx, const ocsb_win *win,
+                                         const void *dem, int32_t dem_dtype,
+                                         int64_t dem_stride, double *coef) {
+    CTX_ENTER("ocsb_spline_prefilter");
+    OCSB_TRY(check_win(win, "ocsb_spline_prefilter"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_spline_prefilter: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(win->width >= 4 && win->height >= 4,
+                 "ocsb_spline_prefilter: cubic spline needs >= 4 points per "
+                 "axis (m > k must hold)");
+    OCSB_REQUIRE(dem && coef && dem_stride >= win->width,
+                 "ocsb_spline_prefilter: bad buffers");
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    const int w = win->width, h = win->height;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    Staged sz, sc;
+    OCSB_TRY(sz.init(ctx, dem, h, w, dem_stride, es, STAGE_IN));
+    OCSB_TRY(sc.init(ctx, coef, h, w, w, 8, STAGE_OUT));
+    OCSB_TRY(k_spline_prefilter(ctx, ax, ay, sz.dev, dem_dtype, sz.dev_stride,
+                                (double *)sc.dev));
+    return finish_call(ctx, {&sz, &sc});
+}
+
+extern "C" int32_t ocsb_interp(ocsb_ctx *ctx, const ocsb_win *win,
+                               const void *dem, int32_t dem_dtype,
+                               int64_t dem_stride, const uint8_t *nodata_mask,
+                               int64_t mask_stride, const double *xy, int64_t K,
+                               int32_t method, uint8_t *touched,
+                               double *values) {
+    CTX_ENTER("ocsb_interp");
+    OCSB_TRY(check_win(win, "ocsb_interp"));
+    OCSB_REQUIRE(method == OCSB_INTERP_LINEAR || method == OCSB_INTERP_NEAREST ||
+                     method == OCSB_INTERP_SPLINE,
+                 "Invalid value method specified <%d>!", method);
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_interp: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(K >= 0, "ocsb_interp: negative K");
+    if (K == 0) return OCSB_OK;
+    OCSB_REQUIRE(dem && xy && touched && values && dem_stride >= win->width,
+                 "ocsb_interp: bad buffers");
+    OCSB_REQUIRE(!nodata_mask || mask_stride >= win->width,
+                 "ocsb_interp: bad mask stride");
+    const int w = win->width, h = win->height;
+    if (method == OCSB_INTERP_SPLINE) {
+        OCSB_REQUIRE(w >= 4 && h >= 4,
+                     "ocsb_interp: cubic spline needs >= 4 points per axis");
+    } else {
+        OCSB_REQUIRE(w >= 2 && h >= 2,
+                     "ocsb_interp: linear/nearest need >= 2 points per axis");
+    }
+    OCSB_REQUIRE(win->x0 != win->x1 && win->y0 != win->y1,
+                 "ocsb_interp: degenerate window bounds");
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    Staged sz, sm, sxy, st, sval;
+    OCSB_TRY(sz.init(ctx, dem, h, w, dem_stride, es, STAGE_IN));
+    OCSB_TRY(sm.init(ctx, nodata_mask, h, w, mask_stride, 1, STAGE_IN));
+    OCSB_TRY(sxy.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
+    OCSB_TRY(st.init(ctx, touched, 1, K, K, 1, STAGE_INOUT));
+    OCSB_TRY(sval.init(ctx, values, 1, K, K, 8, STAGE_INOUT));
+    if (method == OCSB_INTERP_SPLINE) {
+        // coefficients are cached per (dem pointer, shape) so a list of node
+        // batches against one raster pays the prefilter once
+        size_t need = (size_t)w * h * sizeof(double);
+        bool hit = ctx->spl_key == dem && ctx->spl_bytes == need && !sz.staged;
+        if (!hit) {
+            if (ctx->spl_bytes < need || !ctx->spl_coef) {
+                if (ctx->spl_coef) {
+                    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+                    cudaFree(ctx->spl_coef);
+                    ctx->spl_coef = nullptr;
+                }
+                OCSB_CUDA(cudaMalloc((void **)&ctx->spl_coef, need));
+            }
+            ctx->spl_bytes = need;
+            ctx->spl_key = nullptr;  // never trust the cache across calls:
+                                     // the caller may have rewritten the DEM
+            OCSB_TRY(k_spline_prefilter(ctx, ax, ay, sz.dev, dem_dtype,
+                                        sz.dev_stride, ctx->spl_coef));
+        }
+        OCSB_TRY(k_spline_eval(ctx, ax, ay, ctx->spl_coef,
+                               (const double *)sxy.dev, K, (uint8_t *)st.dev,
+                               (double *)sval.dev));
+    } else {
+        OCSB_TRY(k_interp(ctx, ax, ay, sz.dev, dem_dtype, sz.dev_stride,
+                          (const uint8_t *)sm.dev, sm.dev_stride,
+                          (const double *)sxy.dev, K, method,
+                          (uint8_t *)st.dev, (double *)sval.dev));
+    }
+    return finish_call(ctx, {&sz, &sm, &sxy, &st, &sval});
+}

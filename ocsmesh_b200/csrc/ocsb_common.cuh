@@ -1,0 +1,217 @@
+// Internal shared declarations of libocsb200 (not part of the C ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include <vector>
+#include <string>
+
+#include "ocsb200.h"
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+void ocsb_set_error(const char *fmt, ...);
+
+#define OCSB_CUDA(call)                                                        \
+    do {                                                                       \
+        cudaError_t e__ = (call);                                              \
+        if (e__ != cudaSuccess) {                                              \
+            ocsb_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call,       \
+                           cudaGetErrorString(e__));                           \
+            return e__ == cudaErrorMemoryAllocation ? OCSB_ENOMEM : OCSB_ECUDA;\
+        }                                                                      \
+    } while (0)
+
+#define OCSB_REQUIRE(cond, ...)                                                \
+    do {                                                                       \
+        if (!(cond)) {                                                         \
+            ocsb_set_error(__VA_ARGS__);                                       \
+            return OCSB_EINVAL;                                                \
+        }                                                                      \
+    } while (0)
+
+#define OCSB_TRY(expr)                                                         \
+    do {                                                                       \
+        int32_t s__ = (expr);                                                  \
+        if (s__ != OCSB_OK) return s__;                                        \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+struct ocsb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int num_sms = 148;
+    int64_t launches = 0;
+    // pinned bounce buffer for small D2H reads (flags, counters)
+    void *pinned = nullptr;
+    size_t pinned_bytes = 0;
+    // spline coefficient cache (one raster window)
+    const void *spl_key = nullptr;
+    double *spl_coef = nullptr;
+    size_t spl_bytes = 0;
+};
+
+// stream-ordered scratch allocation (cudaMallocAsync pool, reused across calls)
+int32_t ocsb_alloc(ocsb_ctx *ctx, void **p, size_t bytes);
+void ocsb_free(ocsb_ctx *ctx, void *p);
+
+struct ScratchGuard {
+    ocsb_ctx *ctx;
+    std::vector<void *> ptrs;
+    explicit ScratchGuard(ocsb_ctx *c) : ctx(c) {}
+    ~ScratchGuard() {
+        for (void *p : ptrs) ocsb_free(ctx, p);
+    }
+    template <typename T> int32_t get(T **out, size_t count) {
+        void *p = nullptr;
+        int32_t s = ocsb_alloc(ctx, &p, count * sizeof(T));
+        if (s != OCSB_OK) return s;
+        ptrs.push_back(p);
+        *out = reinterpret_cast<T *>(p);
+        return OCSB_OK;
+    }
+};
+
+static inline bool ocsb_is_none(double v) { return v != v; }
+
+// ---------------------------------------------------------------------------
+// np.linspace(start, stop, n)[k], bit-exact (numpy/_core/function_base.py):
+//   step = (stop - start) / (n - 1);  y[k] = fl(fl(k * step) + start);
+//   y[n-1] = stop (n > 1);  n == 1 -> [start]
+// ---------------------------------------------------------------------------
+struct LinAxis {
+    double start, stop, step;
+    int n;
+};
+
+static inline LinAxis make_axis(double start, double stop, int n) {
+    LinAxis a;
+    a.start = start;
+    a.stop = stop;
+    a.n = n;
+    a.step = n > 1 ? (stop - start) / (double)(n - 1) : 0.0;
+    return a;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ double lin_at(const LinAxis &a, int k) {
+    // separate multiply and add: numpy does y = arange*step; y += start
+    double v = __dadd_rn(__dmul_rn((double)k, a.step), a.start);
+    return (k == a.n - 1 && a.n > 1) ? a.stop : v;
+}
+#endif
+
+#ifdef __CUDACC__
+// np.minimum: NaN-propagating
+__device__ __forceinline__ float np_minimum_f(float a, float b) {
+    return (a != a || b != b) ? __int_as_float(0x7fc00000) : fminf(a, b);
+}
+__device__ __forceinline__ double np_minimum_d(double a, double b) {
+    return (a != a || b != b) ? __longlong_as_double(0x7ff8000000000000LL)
+                              : fmin(a, b);
+}
+// values[values < lo] = lo; values[values > hi] = hi  (float32 compares)
+__device__ __forceinline__ float clamp_f32(float v, int has_lo, float lo,
+                                           int has_hi, float hi) {
+    if (has_lo && v < lo) v = lo;
+    if (has_hi && v > hi) v = hi;
+    return v;
+}
+#endif
+
+static inline double lin_at_host(const LinAxis &a, int k) {
+    volatile double m = (double)k * a.step;
+    double v = m + a.start;
+    return (k == a.n - 1 && a.n > 1) ? a.stop : v;
+}
+
+// ---------------------------------------------------------------------------
+// host/device buffer staging (the C ABI accepts either kind of pointer)
+// ---------------------------------------------------------------------------
+bool ocsb_is_device_ptr(const void *p);
+
+enum StageDir { STAGE_IN = 1, STAGE_OUT = 2, STAGE_INOUT = 3 };
+
+// One 2-D (rows x width, row_stride) buffer of `elem` bytes per element.
+// If `user` is a device pointer, dev == user.  Otherwise a compact device
+// copy (stride = width) is made (STAGE_IN) and written back (STAGE_OUT).
+struct Staged {
+    ocsb_ctx *ctx = nullptr;
+    void *user = nullptr;
+    void *dev = nullptr;
+    int64_t rows = 0, width = 0, user_stride = 0, dev_stride = 0;
+    size_t elem = 0;
+    int dir = 0;
+    bool staged = false;
+    int32_t init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
+                 int64_t stride_, size_t elem_, int dir_);
+    int32_t finish();  // enqueue copy-back (if staged and OUT)
+    ~Staged();
+};
+
+// kernel launch accounting
+#define OCSB_LAUNCHED(ctx) ((ctx)->launches++)
+#define OCSB_CHECK_LAUNCH()                                                    \
+    do {                                                                       \
+        cudaError_t e__ = cudaGetLastError();                                  \
+        if (e__ != cudaSuccess) {                                              \
+            ocsb_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__,   \
+                           cudaGetErrorString(e__));                           \
+            return OCSB_ECUDA;                                                 \
+        }                                                                      \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// kernel launchers (device pointers only), one per translation unit
+// ---------------------------------------------------------------------------
+int32_t k_fill_f32(ocsb_ctx *ctx, float *dst, int64_t n, float v);
+int32_t k_clamp(ocsb_ctx *ctx, float *hfun, int64_t stride, int w, int h,
+                double hmin, double hmax);
+int32_t k_min_combine(ocsb_ctx *ctx, float *dst, int64_t dstride,
+                      const float *src, int64_t sstride, int w, int h);
+int32_t k_coords(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, double *x, double *y);
+
+struct LimiterArgs {
+    double dx, dy;
+    double hmin, hmax, lb, ub, ghmin, ghmax;  // NaN = None
+    int fuse_clamp;
+};
+int32_t k_flow_limiter(ocsb_ctx *ctx, int w, int h, const void *dem,
+                       int dem_dtype, int64_t dem_stride, const float *old_,
+                       int64_t old_stride, float *new_, int64_t new_stride,
+                       const LimiterArgs &a);
+
+struct FeatureArgs {
+    LinAxis ax, ay;         // pixel coordinates of the window
+    double rate_target;     // expansion_rate * target_size (f64 product)
+    double target;
+    double r;               // search radius, +inf if unbounded
+    float hmin_f, hmax_f;   // f32-rounded global bounds
+    int has_hmin, has_hmax;
+    int fuse_clamp;
+};
+int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
+                       const double *verts, int64_t nv, const float *old_,
+                       int64_t old_stride, float *new_, int64_t new_stride,
+                       double *dist_out, int64_t *idx_out);
+int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
+                         const double *q, int64_t nq, double r, double *dist,
+                         int64_t *idx);
+
+int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
+                 int dem_dtype, int64_t dem_stride, const uint8_t *mask,
+                 int64_t mask_stride, const double *xy, int64_t K, int method,
+                 uint8_t *touched, double *values);
+int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
+                           const void *dem, int dem_dtype, int64_t dem_stride,
+                           double *coef);
+int32_t k_spline_eval(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const double *coef,
+                      const double *xy, int64_t K, uint8_t *touched,
+                      double *values);

@@ -1,0 +1,717 @@
+"""CPU restatement of the OCSMesh raster hot path (numpy + scipy).
+
+TEST INFRASTRUCTURE ONLY: this module is the *checker* for the CUDA path and
+the timed CPU baseline of ``bench.py``.  The product package
+(``ocsmesh_b200``) never imports it.
+
+Parity status: **parity pinned only at the known-answer level** -- the
+reference package cannot be imported in the build container (pyproj,
+rasterio, shapely, geopandas, matplotlib are absent), and no
+reference test pins a per-pixel number on this path.  What *is* pinned here:
+
+* ``get_iter_windows``            against the windows the reference formula
+  yields (restated literally from ``ocsmesh/raster.py:1891-1939``),
+* ``repartition_features``        against ``tests/api/test_utils.py:873-916``,
+* ``transform_linestring``        against ``tests/api/test_utils.py:970-979``,
+* ``Raster.get_xy`` ordering      against ``tests/api/test_utils.py:674-700``,
+* constant-raster interpolation   against ``tests/api/test_mesh.py:361-379``.
+
+The arithmetic itself lives in third-party wheels that the reference leaves
+unpinned (``pyproject.toml:24-31``): ``scipy.spatial.cKDTree``,
+``scipy.interpolate.RegularGridInterpolator`` / ``RectBivariateSpline``,
+``numpy.gradient`` / ``numpy.ma``.  This oracle calls the *same* functions
+with identically shaped arguments (numpy 2.3.5 / scipy 1.18.1 in this image),
+so per-pixel parity is "equal to what the reference's call sites compute with
+these library versions".  Per-pixel sizes are otherwise **parity unpinned**.
+
+Every function cites the reference ``file:line`` it follows (paths relative
+to the reference repository root).
+"""
+from __future__ import annotations
+
+import math
+from collections import namedtuple
+from typing import Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+from scipy.interpolate import RectBivariateSpline, RegularGridInterpolator
+from scipy.spatial import cKDTree
+
+__all__ = [
+    "Window", "OracleRaster", "get_iter_windows", "window_transform",
+    "array_bounds", "repartition_features", "transform_linestring",
+    "linestring_length", "feature_points", "hfun_init", "add_feature_window",
+    "add_feature", "flow_limiter_window", "add_subtidal_flow_limiter",
+    "apply_constraints_clamp", "mesh_interpolate_worker", "mesh_interpolate",
+    "OracleHfun", "marching_squares", "get_contour", "nearest_vertex",
+    "min_combine", "apply_rate",
+]
+
+FLT_MAX = np.finfo(np.float32).max
+
+#: stand-in for ``rasterio.windows.Window`` (col_off, row_off, width, height)
+Window = namedtuple("Window", ["col_off", "row_off", "width", "height"])
+
+
+# --------------------------------------------------------------------------
+# windows and affine algebra
+# --------------------------------------------------------------------------
+def get_iter_windows(width: int, height: int, chunk_size: int = 0,
+                     overlap: int = 0, row_off: int = 0, col_off: int = 0
+                     ) -> Iterable[Window]:
+    """``ocsmesh/raster.py:1891-1939`` -- literal restatement."""
+    win_h = chunk_size + overlap  # noqa: F841  (unused in the reference too)
+    win_w = chunk_size + overlap  # noqa: F841
+    n_win_h = math.ceil(height / chunk_size)
+    n_win_w = math.ceil(width / chunk_size)
+    for i in range(n_win_h):
+        for j in range(n_win_w):
+            off_h = i * chunk_size
+            off_w = j * chunk_size
+            h = chunk_size + overlap
+            h = h - (off_h + h) % height if off_h + h > height else h
+            w = chunk_size + overlap
+            w = w - (off_w + w) % width if off_w + w > width else w
+            yield Window(off_w, off_h, w, h)
+
+
+def window_transform(transform: Sequence[float], window: Window):
+    """``rasterio.windows.transform`` as used at ``ocsmesh/raster.py:1683``.
+
+    ``transform`` is the affine six-tuple ``(a, b, c, d, e, f)`` with
+    ``x = a*col + b*row + c`` and ``y = d*col + e*row + f``.
+    rasterio computes ``x, y = T * (col_off, row_off)`` and returns
+    ``Affine.translation(x - T.c, y - T.f) * T``.
+    """
+    a, b, c, d, e, f = transform
+    x = window.col_off * a + window.row_off * b + c
+    y = window.col_off * d + window.row_off * e + f
+    return (a, b, c + (x - c), d, e, f + (y - f))
+
+
+def array_bounds(height: int, width: int, transform: Sequence[float]):
+    """``rasterio.transform.array_bounds`` as used at ``ocsmesh/raster.py:1659-1662``.
+
+    Returns ``(west, south, east, north)``.
+    """
+    a, b, c, d, e, f = transform
+    w, n = c, f
+    east = width * a + height * b + c
+    south = width * d + height * e + f
+    return (w, south, east, n)
+
+
+class OracleRaster:
+    """In-memory stand-in for ``ocsmesh.Raster`` (``ocsmesh/raster.py:213-531``).
+
+    ``values`` is ``(h, w)`` or ``(bands, h, w)``; ``mask`` (same shape,
+    ``True`` = nodata) mirrors rasterio's ``masked=True`` read.
+    """
+
+    def __init__(self, values, transform, chunk_size=None, overlap=None,
+                 mask=None):
+        values = np.asarray(values)
+        if values.ndim == 2:
+            values = values[None]
+        self.bands = values
+        self.transform = tuple(float(t) for t in transform)
+        self.chunk_size = chunk_size
+        self.overlap = 0 if overlap is None else overlap
+        if mask is not None:
+            mask = np.asarray(mask, dtype=bool)
+            if mask.ndim == 2:
+                mask = mask[None]
+        self.mask = mask
+
+    # ocsmesh/raster.py:1789-1803
+    @property
+    def width(self):
+        return self.bands.shape[2]
+
+    @property
+    def height(self):
+        return self.bands.shape[1]
+
+    @property
+    def dx(self):
+        return self.transform[0]
+
+    @property
+    def dy(self):
+        return -self.transform[4]
+
+    def full_window(self) -> Window:
+        return Window(0, 0, self.width, self.height)
+
+    def iter_windows(self, chunk_size=None, overlap=None):
+        """``ocsmesh/raster.py:1577-1608``."""
+        chunk_size = self.chunk_size if chunk_size is None else chunk_size
+        overlap = self.overlap if overlap is None else overlap
+        if chunk_size in [0, None, False]:
+            yield Window(0, 0, self.width, self.height)
+            return
+        yield from get_iter_windows(self.width, self.height, chunk_size, overlap)
+
+    def get_window_transform(self, window):
+        """``ocsmesh/raster.py:1664-1683``."""
+        if window is None:
+            return None
+        return window_transform(self.transform, window)
+
+    def get_window_bounds(self, window):
+        """``ocsmesh/raster.py:1642-1662``."""
+        return array_bounds(window.height, window.width,
+                            self.get_window_transform(window))
+
+    def get_x(self, window=None):
+        """``ocsmesh/raster.py:428-453``."""
+        window = self.full_window() if window is None else window
+        x0, y0, x1, y1 = self.get_window_bounds(window)
+        return np.linspace(x0, x1, window.width)
+
+    def get_y(self, window=None):
+        """``ocsmesh/raster.py:455-480``."""
+        window = self.full_window() if window is None else window
+        x0, y0, x1, y1 = self.get_window_bounds(window)
+        return np.linspace(y1, y0, window.height)
+
+    def get_xy(self, window=None):
+        """``ocsmesh/raster.py:482-500``."""
+        x, y = np.meshgrid(self.get_x(window), self.get_y(window))
+        return np.vstack([x.flatten(), y.flatten()]).T
+
+    def get_values(self, window=None, band=None, masked=False):
+        """``ocsmesh/raster.py:502-531`` (rasterio windowed read)."""
+        i = 1 if band is None else band
+        window = self.full_window() if window is None else window
+        r0, c0 = window.row_off, window.col_off
+        sl = (slice(r0, r0 + window.height), slice(c0, c0 + window.width))
+        vals = self.bands[i - 1][sl]
+        if masked:
+            if self.mask is None:
+                m = np.zeros(vals.shape, dtype=bool)
+            else:
+                m = self.mask[i - 1][sl]
+            return np.ma.MaskedArray(vals, mask=m)
+        return vals
+
+
+# --------------------------------------------------------------------------
+# feature prologue (host side in the reference as well)
+# --------------------------------------------------------------------------
+def repartition_features(coords: np.ndarray, max_verts: int) -> List[np.ndarray]:
+    """``ocsmesh/utils.py:247-277`` with a polyline given as ``(n,2)`` array."""
+    if not isinstance(max_verts, int):
+        raise ValueError("Maximum number of vertices must be an integer!")
+    coords = np.asarray(coords, dtype=float)
+    features = []
+    lstr_len = len(coords)
+    if lstr_len > max_verts:
+        list_lens = [max_verts] * ((lstr_len - 1) // (max_verts - 1))
+        if (lstr_len - 1) % (max_verts - 1) != 0:
+            list_lens += [(lstr_len - 1) % (max_verts - 1) + 1]
+        new_idx = np.cumsum(np.array(list_lens) - 1)
+        last_idx = 0
+        for idx in new_idx:
+            features.append(coords[last_idx:idx + 1])
+            last_idx = idx
+    else:
+        features.append(coords)
+    return features
+
+
+def linestring_length(coords: np.ndarray) -> float:
+    """``LineString.length`` (GEOS): sequential sum of segment lengths."""
+    c = np.asarray(coords, dtype=float)
+    if len(c) < 2:
+        return 0.0
+    seg = ((c[1:] - c[:-1]) ** 2).sum(axis=1) ** 0.5
+    # sequential left-to-right accumulation == np.cumsum's last element
+    return float(np.cumsum(seg)[-1])
+
+
+def transform_linestring(coords: np.ndarray, target_size: float) -> np.ndarray:
+    """``ocsmesh/utils.py:280-312`` with a polyline given as ``(n,2)`` array."""
+    orig_coords = np.asarray(coords, dtype=float)
+    lstr_len = linestring_length(orig_coords)
+    distances = np.cumsum(np.ones(int(lstr_len // target_size)) * target_size)
+    if len(distances) == 0:
+        return orig_coords
+    if distances[-1] < lstr_len:
+        distances = np.append(distances, lstr_len)
+
+    lengths = ((orig_coords[1:] - orig_coords[:-1]) ** 2).sum(axis=1) ** 0.5
+    cum_len = np.cumsum(lengths)
+
+    # ocsmesh/utils.py:301 asserts max(cum_len) == max(distances); the
+    # oracle keeps going either way (the GEOS sum and numpy cumsum agree to
+    # the last bit on all probes).
+    idx = len(cum_len) - (distances[:, None] <= cum_len).sum(axis=1)
+    ratio = ((cum_len[idx] - distances) / lengths[idx])[:, None]
+    interp_coords = orig_coords[idx] * ratio + orig_coords[idx + 1] * (1 - ratio)
+    return np.vstack((orig_coords[0], interp_coords))
+
+
+def feature_points(features: Sequence[np.ndarray], target_size: float,
+                   max_verts: int = 200) -> np.ndarray:
+    """``ocsmesh/hfun/raster.py:1183-1225`` for a projected CRS.
+
+    repartition -> resample every chunk -> concatenate vertex coordinates.
+    """
+    win_feature = []
+    for ls in features:
+        win_feature.extend(repartition_features(ls, max_verts))
+    pts = [transform_linestring(ls, target_size) for ls in win_feature]
+    if not pts:
+        return np.empty((0, 2))
+    return np.concatenate(pts, axis=0)
+
+
+# --------------------------------------------------------------------------
+# hfun ops
+# --------------------------------------------------------------------------
+def hfun_init(shape) -> np.ndarray:
+    """``ocsmesh/hfun/raster.py:57-86``: float32 raster of FLT_MAX."""
+    v = np.empty(shape, dtype=np.float32)
+    v[:] = getattr(np.finfo(np.float32), "max")
+    return v
+
+
+def nearest_vertex(points, xy, r=None, workers=-1):
+    """``cKDTree(points).query(xy[, distance_upper_bound=r])``.
+
+    Call site: ``ocsmesh/hfun/raster.py:1230, 1240-1248``.
+    Returns ``(distances, indices)`` exactly as scipy returns them
+    (``inf`` / ``len(points)`` beyond ``r``).
+    """
+    tree = cKDTree(np.array(points))
+    if r is not None:
+        return tree.query(xy, workers=workers, distance_upper_bound=r)
+    return tree.query(xy, workers=workers)
+
+
+def add_feature_window(old: np.ndarray, points: np.ndarray, xy: np.ndarray,
+                       height: int, width: int, expansion_rate: float,
+                       target_size: float, hmin: Optional[float],
+                       hmax: Optional[float], workers: int = -1,
+                       return_dist: bool = False):
+    """Body of the window loop of ``HfunRaster.add_feature``
+    (``ocsmesh/hfun/raster.py:1230-1257``)."""
+    tree = cKDTree(np.array(points))
+    if hmax:
+        r = (hmax - target_size) / (expansion_rate * target_size)
+        near_dists, neighbors = tree.query(
+            xy, workers=workers, distance_upper_bound=r)
+        distances = r * np.ones(len(xy))
+        mask = np.logical_not(np.isinf(near_dists))
+        distances[mask] = near_dists[mask]
+    else:
+        distances, neighbors = tree.query(xy, workers=workers)
+    values = expansion_rate * target_size * distances + target_size
+    values = values.reshape(height, width).astype(np.float32)
+    if hmin is not None:
+        values[np.where(values < hmin)] = hmin
+    if hmax is not None:
+        values[np.where(values > hmax)] = hmax
+    values = np.minimum(old, values)
+    if return_dist:
+        return values, distances.reshape(height, width), \
+            neighbors.reshape(height, width)
+    return values
+
+
+def flow_limiter_window(topobathy: np.ndarray, old: np.ndarray, dx: float,
+                        dy: float, hmin, hmax, lower_bound, upper_bound,
+                        ghmin, ghmax) -> np.ndarray:
+    """Body of the window loop of ``HfunRaster.add_subtidal_flow_limiter``
+    (``ocsmesh/hfun/raster.py:1398-1435``), literal whole-array restatement.
+
+    Returns a plain or masked float32 array exactly like the reference's
+    ``hfun_values`` right before ``dst.write_band`` (a residual mask marks
+    zero-gradient pixels no clamp has touched; what rasterio writes there is
+    outside the oracle's reach).
+    """
+    import warnings
+    hmin = float(hmin) if hmin is not None else hmin
+    hmax = float(hmax) if hmax is not None else hmax
+    gx, gy = np.gradient(topobathy, dx, dy)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", category=RuntimeWarning)
+        dh = np.sqrt(gx ** 2 + gy ** 2)
+        dh = np.ma.masked_equal(dh, 0.)
+        hfun_values = np.abs((1. / 3.) * (topobathy / dh))
+
+    if hmin is not None:
+        hfun_values[np.where(hfun_values < hmin)] = hmin
+    if hmax is not None:
+        hfun_values[np.where(hfun_values > hmax)] = hmax
+
+    if upper_bound is not None:
+        idxs = np.where(topobathy > upper_bound)
+        hfun_values[idxs] = old[idxs]
+    if lower_bound is not None:
+        idxs = np.where(topobathy < lower_bound)
+        hfun_values[idxs] = old[idxs]
+
+    if ghmin is not None:
+        hfun_values[np.where(hfun_values < ghmin)] = ghmin
+    if ghmax is not None:
+        hfun_values[np.where(hfun_values > ghmax)] = ghmax
+
+    return np.minimum(old, hfun_values).astype(np.float32)
+
+
+def apply_constraints_clamp(values: np.ndarray, hmin, hmax) -> np.ndarray:
+    """``HfunRaster.apply_constraints`` with an empty constraint list
+    (``ocsmesh/hfun/raster.py:509-568``): the global clamp re-pass."""
+    hfun_values = values.copy()
+    if hmin is not None:
+        hfun_values[hfun_values < hmin] = hmin
+    if hmax is not None:
+        hfun_values[hfun_values > hmax] = hmax
+    return hfun_values
+
+
+class OracleHfun:
+    """Stand-in for ``HfunRaster`` (``ocsmesh/hfun/raster.py:92-251``):
+    holds the float32 size raster and applies the ops window by window with
+    the reference's read-old / write-new file semantics."""
+
+    def __init__(self, raster: OracleRaster, hmin=None, hmax=None,
+                 initial_value=None):
+        self.raster = raster
+        self.hmin = float(hmin) if hmin is not None else hmin
+        self.hmax = float(hmax) if hmax is not None else hmax
+        if initial_value is not None:
+            self.values = np.array(initial_value, dtype=np.float32)
+        else:
+            self.values = hfun_init((raster.height, raster.width))
+
+    def _iter(self):
+        # HfunRaster copies chunk_size/overlap from the DEM
+        # (ocsmesh/hfun/raster.py:84-86) and iterates its own windows.
+        return list(self.raster.iter_windows())
+
+    def _clamp_pass(self):
+        """``apply_constraints_wrap`` -> ``apply_added_constraints`` ->
+        ``apply_constraints([])`` (``features/constraint.py:420-423``,
+        ``hfun/raster.py:488-568``)."""
+        new = self.values.copy()
+        for win in self._iter():
+            sl = (slice(win.row_off, win.row_off + win.height),
+                  slice(win.col_off, win.col_off + win.width))
+            new[sl] = apply_constraints_clamp(self.values[sl], self.hmin,
+                                              self.hmax)
+        self.values = new
+
+    def add_feature_points(self, points, expansion_rate, target_size=None,
+                           workers=-1):
+        """``HfunRaster.add_feature`` from the parity boundary
+        (``hfun/raster.py:1230``) on: ``points`` is the resampled ``(N,2)``
+        vertex array."""
+        target_size = self.hmin if target_size is None else target_size
+        if target_size is None:
+            raise ValueError("Argument target_size must be specified if no "
+                             "global hmin has been set.")
+        if target_size <= 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        new = self.values.copy()
+        for win in self._iter():
+            sl = (slice(win.row_off, win.row_off + win.height),
+                  slice(win.col_off, win.col_off + win.width))
+            xy = self.raster.get_xy(win)
+            new[sl] = add_feature_window(
+                self.values[sl], points, xy, win.height, win.width,
+                expansion_rate, target_size, self.hmin, self.hmax,
+                workers=workers)
+        self.values = new
+        self._clamp_pass()
+
+    def add_feature(self, features, expansion_rate, target_size=None,
+                    max_verts=200, workers=-1):
+        """``HfunRaster.add_feature`` (``hfun/raster.py:1084-1261``);
+        ``features`` is a list of ``(n,2)`` polylines."""
+        ts = self.hmin if target_size is None else target_size
+        if ts is None:
+            raise ValueError("Argument target_size must be specified if no "
+                             "global hmin has been set.")
+        if ts <= 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        pts = feature_points(features, ts, max_verts)
+        self.add_feature_points(pts, expansion_rate, target_size, workers)
+
+    def add_contour(self, level, expansion_rate, target_size=None, workers=-1):
+        """``HfunRaster.add_contour`` (``hfun/raster.py:936-1014``)."""
+        if not isinstance(level, list):
+            level = [level]
+        contours = []
+        for _level in level:
+            contours.extend(get_contour(self.raster, _level))
+        if len(contours) == 0:
+            return
+        self.add_feature(contours, expansion_rate, target_size,
+                         workers=workers)
+        self._clamp_pass()  # outer decorator layer
+
+    def add_subtidal_flow_limiter(self, hmin=None, hmax=None,
+                                  lower_bound=None, upper_bound=None):
+        """``HfunRaster.add_subtidal_flow_limiter``
+        (``hfun/raster.py:1315-1436``), projected CRS branch."""
+        new = self.values.copy()
+        for win in self._iter():
+            sl = (slice(win.row_off, win.row_off + win.height),
+                  slice(win.col_off, win.col_off + win.width))
+            z = self.raster.get_values(band=1, window=win)
+            out = flow_limiter_window(
+                z, self.values[sl], self.raster.dx, self.raster.dy, hmin,
+                hmax, lower_bound, upper_bound, self.hmin, self.hmax)
+            new[sl] = np.ma.getdata(out)
+        self.values = new
+        self._clamp_pass()
+
+
+def add_feature(hfun: OracleHfun, *a, **k):
+    return hfun.add_feature(*a, **k)
+
+
+def add_subtidal_flow_limiter(hfun: OracleHfun, *a, **k):
+    return hfun.add_subtidal_flow_limiter(*a, **k)
+
+
+def min_combine(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """Pixel-wise min of two co-registered float32 hfun rasters (build-defined
+    config-3 semantics, SURVEY.md row A12: the reference has no such op)."""
+    return np.minimum(a, b)
+
+
+def apply_rate(values, locations, mask, rate, rate_sign, satisfies):
+    """``Constraint._apply_rate`` (``ocsmesh/features/constraint.py:83-121``)."""
+    if not np.any(mask):
+        return values
+    return_values = values.copy().ravel()
+    coords = locations.reshape(-1, 2)
+    if rate is None:
+        return values
+    mask_r = mask.copy().ravel()
+    nomask_r = np.logical_not(mask_r)
+    points = coords[mask_r]
+    xy = coords[nomask_r]
+    tree = cKDTree(points)
+    near_dists, neighbors = tree.query(xy)
+    temp_values = return_values[mask_r][neighbors] * (
+        1 + near_dists * rate * rate_sign)
+    mask2 = np.logical_not(satisfies(return_values[nomask_r], temp_values))
+    temp_values_2 = return_values[nomask_r]
+    temp_values_2[mask2] = temp_values[mask2]
+    return_values[nomask_r] = temp_values_2
+    return return_values.reshape(values.shape)
+
+
+# --------------------------------------------------------------------------
+# Mesh.interpolate
+# --------------------------------------------------------------------------
+def mesh_interpolate_worker(coords, raster: OracleRaster, chunk_size=None,
+                            method="spline", band=1):
+    """``_mesh_interpolate_worker`` (``ocsmesh/mesh/mesh.py:2232-2349``),
+    same-CRS, ``filter_by_shape=False`` branch."""
+    coords = np.array(coords)
+    idxs = []
+    values = []
+    for window in raster.iter_windows(chunk_size=chunk_size, overlap=2):
+        xi = raster.get_x(window)
+        yi = raster.get_y(window)
+        zi = raster.get_values(window=window, masked=True, band=band)
+        _idxs = np.logical_and(
+            np.logical_and(np.min(xi) <= coords[:, 0],
+                           np.max(xi) >= coords[:, 0]),
+            np.logical_and(np.min(yi) <= coords[:, 1],
+                           np.max(yi) >= coords[:, 1]))
+        interp_mask = None
+        if method == "spline":
+            f = RectBivariateSpline(
+                xi, np.ascontiguousarray(np.flip(yi)), np.flipud(zi).T,
+                kx=3, ky=3, s=0)
+            _values = f.ev(coords[_idxs, 0], coords[_idxs, 1])
+        elif method in ["nearest", "linear"]:
+            if np.any(zi.mask):
+                m_interp = RegularGridInterpolator(
+                    (xi, np.ascontiguousarray(np.flip(yi))),
+                    np.flipud(zi.mask).T.astype(bool), method=method)
+                interp_mask = m_interp(coords[_idxs]) > 0
+            f = RegularGridInterpolator(
+                (xi, np.ascontiguousarray(np.flip(yi))),
+                np.flipud(zi).T, method=method)
+            _values = f(coords[_idxs])
+        else:
+            raise ValueError(f"Invalid value method specified <{method}>!")
+        if interp_mask is not None:
+            helper = np.ones_like(_values).astype(bool)
+            helper[interp_mask] = False
+            _idxs[_idxs] = helper
+            _values = _values[~interp_mask]
+        idxs.append(_idxs)
+        values.append(_values)
+    return (np.hstack(idxs), np.hstack(values))
+
+
+def mesh_interpolate(coords, values, rasters, method="spline", band=1):
+    """``EuclideanMesh2D.interpolate`` (``ocsmesh/mesh/mesh.py:314-376, 425``).
+
+    ``values`` is the mesh's current ``(K,)`` or ``(K,1)`` value array; the
+    result is ``(K,1)`` float64, rasters applied in list order (last wins).
+    """
+    if isinstance(rasters, OracleRaster):
+        rasters = [rasters]
+    res = [mesh_interpolate_worker(coords, r, r.chunk_size, method, band)
+           for r in rasters]
+    values = np.array(values, dtype=float).flatten()
+    for (mask, _values) in res:
+        values[mask] = _values
+    return values.reshape((values.shape[0], 1))
+
+
+# --------------------------------------------------------------------------
+# contour extraction -- input generator, NOT a parity claim
+# --------------------------------------------------------------------------
+def marching_squares(x, y, z, level) -> List[np.ndarray]:
+    """Iso-line polylines of ``z`` (``(h,w)``, row ``j`` at ``y[j]``) at ``level``.
+
+    Stands in for ``ax.contour(x, y, values, levels=[level])`` +
+    ``shapely.ops.linemerge`` (``ocsmesh/raster.py:1453-1470``).  contourpy is
+    not installed here, so this is the oracle's *own* marching squares
+    (linear interpolation along cell edges, saddles resolved by the cell
+    mean).  It only generates inputs; parity is claimed from the resampled
+    vertex array on (``hfun/raster.py:1230``).
+    """
+    z = np.asarray(z, dtype=float)
+    h, w = z.shape
+    above = z > level
+    # edge crossing points: horizontal edges (j, i)-(j, i+1), vertical (j,i)-(j+1,i)
+    # unique id per edge so segments can be stitched by shared edge ids
+    he = above[:, :-1] != above[:, 1:]            # (h, w-1)
+    ve = above[:-1, :] != above[1:, :]            # (h-1, w)
+    n_he = h * (w - 1)
+
+    def h_id(j, i):
+        return j * (w - 1) + i
+
+    def v_id(j, i):
+        return n_he + j * w + i
+
+    c00 = above[:-1, :-1]
+    c01 = above[:-1, 1:]
+    c10 = above[1:, :-1]
+    c11 = above[1:, 1:]
+    code = (c00.astype(np.uint8) | (c01.astype(np.uint8) << 1)
+            | (c11.astype(np.uint8) << 2) | (c10.astype(np.uint8) << 3))
+    jj, ii = np.nonzero((code != 0) & (code != 15))
+    cc = code[jj, ii]
+    top = h_id(jj, ii)          # edge between (j,i)-(j,i+1)
+    bot = h_id(jj + 1, ii)      # (j+1,i)-(j+1,i+1)
+    lef = v_id(jj, ii)          # (j,i)-(j+1,i)
+    rig = v_id(jj, ii + 1)      # (j,i+1)-(j+1,i+1)
+    zc = 0.25 * (z[jj, ii] + z[jj, ii + 1] + z[jj + 1, ii] + z[jj + 1, ii + 1])
+    cen = zc > level
+    seg_a = []
+    seg_b = []
+
+    def emit(sel, ea, eb):
+        seg_a.append(ea[sel])
+        seg_b.append(eb[sel])
+
+    # single-corner / adjacent cases
+    for cs, ea, eb in (
+            ((1, 14), top, lef), ((2, 13), top, rig), ((4, 11), rig, bot),
+            ((8, 7), lef, bot), ((3, 12), lef, rig), ((6, 9), top, bot)):
+        sel = (cc == cs[0]) | (cc == cs[1])
+        emit(sel, ea, eb)
+    # saddles: 5 = c00 & c11 above, 10 = c01 & c10 above
+    s5 = cc == 5
+    emit(s5 & cen, top, rig)
+    emit(s5 & cen, lef, bot)
+    emit(s5 & ~cen, top, lef)
+    emit(s5 & ~cen, rig, bot)
+    s10 = cc == 10
+    emit(s10 & cen, top, lef)
+    emit(s10 & cen, rig, bot)
+    emit(s10 & ~cen, top, rig)
+    emit(s10 & ~cen, lef, bot)
+    seg_a = np.concatenate(seg_a)
+    seg_b = np.concatenate(seg_b)
+    if len(seg_a) == 0:
+        return []
+
+    # crossing coordinates per edge id
+    x = np.asarray(x, dtype=float)
+    y = np.asarray(y, dtype=float)
+    px = np.full(n_he + (h - 1) * w, np.nan)
+    py = np.full(n_he + (h - 1) * w, np.nan)
+    jh, ih = np.nonzero(he)
+    t = (level - z[jh, ih]) / (z[jh, ih + 1] - z[jh, ih])
+    px[h_id(jh, ih)] = x[ih] + t * (x[ih + 1] - x[ih])
+    py[h_id(jh, ih)] = y[jh]
+    jv, iv = np.nonzero(ve)
+    t = (level - z[jv, iv]) / (z[jv + 1, iv] - z[jv, iv])
+    px[v_id(jv, iv)] = x[iv]
+    py[v_id(jv, iv)] = y[jv] + t * (y[jv + 1] - y[jv])
+
+    # stitch: every edge id has degree <= 2
+    ids, inv = np.unique(np.concatenate([seg_a, seg_b]), return_inverse=True)
+    ns = len(seg_a)
+    a = inv[:ns]
+    b = inv[ns:]
+    nn = len(ids)
+    nbr = np.full((nn, 2), -1, dtype=np.int64)
+    deg = np.zeros(nn, dtype=np.int64)
+    order = np.argsort(np.concatenate([a, b]), kind="stable")
+    ends = np.concatenate([a, b])[order]
+    other = np.concatenate([b, a])[order]
+    first = np.ones(len(ends), dtype=bool)
+    first[1:] = ends[1:] != ends[:-1]
+    nbr[ends[first], 0] = other[first]
+    second = ~first
+    nbr[ends[second], 1] = other[second]
+    deg = (nbr >= 0).sum(axis=1)
+
+    visited = np.zeros(nn, dtype=bool)
+    lines = []
+    nbr_l = nbr.tolist()
+
+    def walk(start):
+        path = [start]
+        visited[start] = True
+        prev, cur = -1, start
+        while True:
+            n0, n1 = nbr_l[cur]
+            nxt = n0 if (n0 != prev and n0 >= 0 and not visited[n0]) else n1
+            if nxt < 0 or visited[nxt]:
+                # closed ring?
+                if (n0 == start or n1 == start) and len(path) > 2:
+                    path.append(start)
+                break
+            path.append(nxt)
+            visited[nxt] = True
+            prev, cur = cur, nxt
+        return path
+
+    for s in np.nonzero(deg == 1)[0].tolist():
+        if not visited[s]:
+            lines.append(walk(s))
+    for s in np.nonzero(deg == 2)[0].tolist():
+        if not visited[s]:
+            lines.append(walk(s))
+    out = []
+    for path in lines:
+        e = ids[np.asarray(path)]
+        if len(e) < 2:
+            continue
+        out.append(np.stack([px[e], py[e]], axis=1))
+    return out
+
+
+def get_contour(raster: OracleRaster, level: float) -> List[np.ndarray]:
+    """``Raster.get_contour`` single-window branch
+    (``ocsmesh/raster.py:1340-1372, 1426-1470``) via :func:`marching_squares`."""
+    x, y = raster.get_x(), raster.get_y()
+    values = raster.get_values(band=1)
+    return marching_squares(x, y, values, level)
