@@ -62,10 +62,21 @@ typedef struct ocsb_ctx ocsb_ctx;
  *                      = (west, south, east, north) pixel-EDGE bounds
  *   pixel column k has x = np.linspace(x0, x1, width)[k]          ocsmesh/raster.py:452-453
  *   pixel row    j has y = np.linspace(y1, y0, height)[j]         ocsmesh/raster.py:479-480
+ *
+ * row_begin / row_end select the DEVICE TILE of the semantic window that this
+ * call processes: only pixel rows [row_begin, row_end) are read-modified-
+ * written (row_end == 0 means `height`).  Coordinates, the radius law and the
+ * one-sided gradient differences still refer to the WHOLE window, so a window
+ * split into row bands over several GPUs (or several calls) gives bit-identical
+ * results to one call (semantic windows != device tiles).
+ * Buffers are always addressed relative to the window's top-left pixel; a rank
+ * that holds only its band (+1 halo row of the DEM for the gradient stencil)
+ * passes `band_buffer - first_held_row * row_stride`.
  */
 typedef struct ocsb_win {
     double  x0, y0, x1, y1;
     int32_t width, height;
+    int32_t row_begin, row_end;
 } ocsb_win;
 
 /* ---- library / context -------------------------------------------------- */
@@ -73,8 +84,10 @@ typedef struct ocsb_win {
 int32_t     ocsb_abi_version(void);
 const char *ocsb_last_error(void);
 
-/* device: CUDA ordinal.  stream: a cudaStream_t (NULL = a stream the context
- * creates and owns).  */
+/* device: CUDA ordinal.  stream: a cudaStream_t; NULL = a non-blocking stream
+ * the context creates and owns.  ocsb_ctx_set_stream() takes the handle as
+ * is, so NULL there selects the legacy default stream (what torch uses unless
+ * told otherwise).  */
 int32_t ocsb_ctx_create(int32_t device, void *stream, ocsb_ctx **out);
 int32_t ocsb_ctx_destroy(ocsb_ctx *ctx);
 int32_t ocsb_ctx_set_stream(ocsb_ctx *ctx, void *stream);

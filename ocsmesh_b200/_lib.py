@@ -1,0 +1,253 @@
+"""ctypes binding of libocsb200.so (the C ABI declared in include/ocsb200.h).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device
+is usable, the first call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+import threading
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libocsb200.so")
+
+OCSB_OK = 0
+OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
+OCSB_F32, OCSB_F64 = 0, 1
+INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
+NONE = float("nan")
+
+c_i32, c_i64, c_f64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_double, C.c_float, C.c_void_p
+
+
+class ocsb_win(C.Structure):
+    _fields_ = [("x0", c_f64), ("y0", c_f64), ("x1", c_f64), ("y1", c_f64),
+                ("width", c_i32), ("height", c_i32),
+                ("row_begin", c_i32), ("row_end", c_i32)]
+
+
+class OcsbError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"libocsb200 error {status}: {message}")
+        self.status = status
+        self.message = message
+
+
+#: every symbol include/ocsb200.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "ocsb_abi_version": (c_i32, []),
+    "ocsb_last_error": (C.c_char_p, []),
+    "ocsb_ctx_create": (c_i32, [c_i32, c_vp, C.POINTER(c_vp)]),
+    "ocsb_ctx_destroy": (c_i32, [c_vp]),
+    "ocsb_ctx_set_stream": (c_i32, [c_vp, c_vp]),
+    "ocsb_ctx_sync": (c_i32, [c_vp]),
+    "ocsb_ctx_launch_count": (c_i64, [c_vp]),
+    "ocsb_ctx_trim": (c_i32, [c_vp]),
+    "ocsb_windows": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_vp, c_i64,
+                             C.POINTER(c_i64)]),
+    "ocsb_window_coords": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_vp]),
+    "ocsb_fill_f32": (c_i32, [c_vp, c_vp, c_i64, c_f32]),
+    "ocsb_hfun_clamp": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_i32, c_f64, c_f64]),
+    "ocsb_hfun_feature": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
+                                  c_vp, c_i64, c_vp, c_i64, c_f64, c_f64,
+                                  c_f64, c_f64, c_i32, c_vp, c_vp]),
+    "ocsb_nearest_vertex": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64,
+                                    c_vp, c_vp]),
+    "ocsb_hfun_flow_limiter": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                       c_i64, c_vp, c_i64, c_vp, c_i64,
+                                       c_f64, c_f64, c_f64, c_f64, c_f64,
+                                       c_f64, c_f64, c_f64, c_i32]),
+    "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
+    "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
+                            c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
+    "ocsb_spline_prefilter": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                      c_i64, c_vp]),
+}
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+def load() -> C.CDLL:
+    """dlopen libocsb200.so and bind every declared symbol (fails loudly)."""
+    global _lib
+    with _lib_lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise OcsbError(
+                OCSB_ECUDA,
+                f"{LIB_PATH} is missing: build it with "
+                "`python -m ocsmesh_b200.build` (there is no CPU fallback)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is absent
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+        return lib
+
+
+def check(status: int) -> None:
+    if status != OCSB_OK:
+        msg = load().ocsb_last_error()
+        raise OcsbError(status, msg.decode("utf-8", "replace") if msg else "")
+
+
+def opt(v: Optional[float]) -> float:
+    """None -> NaN (the ABI's encoding of an absent optional double)."""
+    return NONE if v is None else float(v)
+
+
+def ptr(buf) -> Optional[int]:
+    """Address of a numpy array, torch tensor, raw int address, or None."""
+    if buf is None:
+        return None
+    if isinstance(buf, int):
+        return buf
+    if isinstance(buf, np.ndarray):
+        return buf.ctypes.data
+    if hasattr(buf, "data_ptr"):
+        return buf.data_ptr()
+    raise TypeError(f"cannot take the address of {type(buf)!r}")
+
+
+def make_win(bounds, width: int, height: int, row_begin: int = 0,
+             row_end: int = 0) -> ocsb_win:
+    """``bounds`` = Raster.get_window_bounds(window); rows [row_begin, row_end)
+    select the device tile (0, 0 = the whole window)."""
+    x0, y0, x1, y1 = (float(b) for b in bounds)
+    return ocsb_win(x0, y0, x1, y1, int(width), int(height), int(row_begin),
+                    int(row_end))
+
+
+def windows(width: int, height: int, chunk_size: int, overlap: int) -> np.ndarray:
+    """ocsb_windows -> (n, 4) int32 array of (col_off, row_off, w, h)."""
+    lib = load()
+    n = c_i64(0)
+    check(lib.ocsb_windows(width, height, chunk_size, overlap, None, 0, C.byref(n)))
+    out = np.empty((n.value, 4), dtype=np.int32)
+    check(lib.ocsb_windows(width, height, chunk_size, overlap, out.ctypes.data,
+                           n.value, C.byref(n)))
+    return out
+
+
+class Context:
+    """One ocsb_ctx (one CUDA device, one stream)."""
+
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        self.lib = load()
+        h = c_vp()
+        check(self.lib.ocsb_ctx_create(int(device), stream, C.byref(h)))
+        self.handle = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.ocsb_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(self.lib.ocsb_ctx_sync(self.handle))
+
+    def set_stream(self, stream: Optional[int]):
+        check(self.lib.ocsb_ctx_set_stream(self.handle, stream))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.ocsb_ctx_launch_count(self.handle))
+
+    def trim(self):
+        check(self.lib.ocsb_ctx_trim(self.handle))
+
+    # ---- thin typed wrappers (buffers: numpy arrays or torch tensors) ------
+    def window_coords(self, win: ocsb_win, x_out, y_out):
+        check(self.lib.ocsb_window_coords(self.handle, C.byref(win), ptr(x_out),
+                                          ptr(y_out)))
+
+    def fill_f32(self, dst, n: int, value: float):
+        check(self.lib.ocsb_fill_f32(self.handle, ptr(dst), int(n), value))
+
+    def hfun_clamp(self, hfun, stride: int, width: int, height: int, hmin, hmax):
+        check(self.lib.ocsb_hfun_clamp(self.handle, ptr(hfun), int(stride),
+                                       int(width), int(height), opt(hmin),
+                                       opt(hmax)))
+
+    def hfun_feature(self, win, verts, nv, old, old_stride, new, new_stride,
+                     expansion_rate, target_size, hmin, hmax, fuse_clamp=False,
+                     dist_out=None, idx_out=None):
+        check(self.lib.ocsb_hfun_feature(
+            self.handle, C.byref(win), ptr(verts), int(nv), ptr(old),
+            int(old_stride), ptr(new), int(new_stride), float(expansion_rate),
+            float(target_size), opt(hmin), opt(hmax), int(bool(fuse_clamp)),
+            ptr(dist_out), ptr(idx_out)))
+
+    def nearest_vertex(self, verts, nv, query, nq, r, dist_out, idx_out):
+        check(self.lib.ocsb_nearest_vertex(
+            self.handle, ptr(verts), int(nv), ptr(query), int(nq), opt(r),
+            ptr(dist_out), ptr(idx_out)))
+
+    def hfun_flow_limiter(self, win, dem, dem_dtype, dem_stride, old, old_stride,
+                          new, new_stride, dx, dy, hmin, hmax, lower_bound,
+                          upper_bound, ghmin, ghmax, fuse_clamp=False):
+        check(self.lib.ocsb_hfun_flow_limiter(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(old), int(old_stride), ptr(new), int(new_stride), float(dx),
+            float(dy), opt(hmin), opt(hmax), opt(lower_bound), opt(upper_bound),
+            opt(ghmin), opt(ghmax), int(bool(fuse_clamp))))
+
+    def min_combine(self, dst, dst_stride, src, src_stride, width, height):
+        check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),
+                                        ptr(src), int(src_stride), int(width),
+                                        int(height)))
+
+    def interp(self, win, dem, dem_dtype, dem_stride, mask, mask_stride, xy, K,
+               method, touched, values):
+        check(self.lib.ocsb_interp(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(mask), int(mask_stride), ptr(xy), int(K), int(method),
+            ptr(touched), ptr(values)))
+
+    def spline_prefilter(self, win, dem, dem_dtype, dem_stride, coef):
+        check(self.lib.ocsb_spline_prefilter(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(coef)))
+
+
+_default_ctx = {}
+
+
+def default_context(device: Optional[int] = None) -> Context:
+    """Per-device context bound to torch's current stream on that device."""
+    import torch
+    if not torch.cuda.is_available():
+        raise OcsbError(OCSB_ECUDA, "no CUDA device available; ocsmesh_b200 has "
+                                    "no CPU fallback")
+    if device is None:
+        device = torch.cuda.current_device()
+    ctx = _default_ctx.get(device)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    if ctx is None:
+        ctx = Context(device, None)
+        ctx._stream = None
+        _default_ctx[device] = ctx
+    if ctx._stream != stream:
+        # 0 is the legacy default stream, which is what torch uses by default
+        ctx.set_stream(stream)
+        ctx._stream = stream
+    return ctx
+
+
+def isnan(v) -> bool:
+    return isinstance(v, float) and math.isnan(v)

@@ -46,7 +46,8 @@ constexpr int kMaxSplit = 64;
 
 struct Geom {
     LinAxis ax, ay;
-    int w, h;
+    int w, h;     // extent of the device tile (band) in pixels
+    int row0;     // first window row of the band: tile row r is window row row0 + r
 };
 
 struct Rect {
@@ -56,7 +57,7 @@ struct Rect {
 __device__ __forceinline__ Rect tile_rect(const Geom &g, int c0, int c1, int r0,
                                           int r1) {
     double xa = lin_at(g.ax, c0), xb = lin_at(g.ax, c1);
-    double ya = lin_at(g.ay, r0), yb = lin_at(g.ay, r1);
+    double ya = lin_at(g.ay, g.row0 + r0), yb = lin_at(g.ay, g.row0 + r1);
     Rect q;
     q.xlo = fmin(xa, xb); q.xhi = fmax(xa, xb);
     q.ylo = fmin(ya, yb); q.yhi = fmax(ya, yb);
@@ -469,8 +470,8 @@ __global__ void __launch_bounds__(kEvalThreads) eval_kernel(EvalArgs A) {
         double px[4], py[2];
 #pragma unroll
         for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
-        py[0] = lin_at(g.ay, min(grow0, g.h - 1));
-        py[1] = lin_at(g.ay, min(grow1, g.h - 1));
+        py[0] = lin_at(g.ay, g.row0 + min(grow0, g.h - 1));
+        py[1] = lin_at(g.ay, g.row0 + min(grow1, g.h - 1));
 
         double best[8];
         int bid[8];
@@ -565,8 +566,8 @@ __global__ void __launch_bounds__(kEvalThreads) eval_kernel(EvalArgs A) {
         for (int j = 0; j < 2; ++j) {
             const int row = j ? grow1 : grow0;
             if (row > r1 || gcol > c1) continue;
-            const float *orow = A.old_ + (int64_t)row * A.os;
-            float *nrow = A.new_ + (int64_t)row * A.ns;
+            const float *orow = A.old_ + (int64_t)(g.row0 + row) * A.os;
+            float *nrow = A.new_ + (int64_t)(g.row0 + row) * A.ns;
             const bool full = gcol + 3 <= c1;
             float o[4];
             if (A.vec_old && full) {
@@ -591,7 +592,7 @@ __global__ void __launch_bounds__(kEvalThreads) eval_kernel(EvalArgs A) {
                     res = clamp_f32(res, A.has_hmin, A.hmin_f, A.has_hmax, A.hmax_f);
                 out[k] = res;
                 if (gcol + k <= c1) {
-                    const int64_t lin = (int64_t)row * g.w + gcol + k;
+                    const int64_t lin = (int64_t)(g.row0 + row) * g.w + gcol + k;
                     if (A.dist) A.dist[lin] = d;
                     if (WANT_IDX) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
                 }
@@ -630,8 +631,8 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
                        int64_t *idx_out) {
     OCSB_REQUIRE(((uintptr_t)verts & 15) == 0,
                  "ocsb_hfun_feature: verts_xy must be 16-byte aligned");
-    const int w = a.ax.n, h = a.ay.n;
-    Geom g{a.ax, a.ay, w, h};
+    const int w = a.ax.n, h = a.row_end - a.row_begin;
+    Geom g{a.ax, a.ay, w, h, a.row_begin};
 
     // ---- level plan --------------------------------------------------------
     std::vector<LevelHost> lv;

@@ -51,8 +51,9 @@ bool ocsb_is_device_ptr(const void *p) {
 }
 
 int32_t Staged::init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
-                     int64_t stride_, size_t elem_, int dir_) {
+                     int64_t stride_, size_t elem_, int dir_, int64_t row0_) {
     ctx = c;
+    row0 = row0_;
     user = const_cast<void *>(p);
     rows = rows_;
     width = width_;
@@ -71,9 +72,13 @@ int32_t Staged::init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
     }
     staged = true;
     dev_stride = width;
-    OCSB_TRY(ocsb_alloc(ctx, &dev, (size_t)rows * (size_t)width * elem));
+    OCSB_TRY(ocsb_alloc(ctx, &alloc, (size_t)rows * (size_t)width * elem));
+    // virtual address of row 0: only rows >= row0 are ever dereferenced
+    dev = (char *)alloc - (size_t)row0 * (size_t)width * elem;
     if (dir & STAGE_IN) {
-        OCSB_CUDA(cudaMemcpy2DAsync(dev, (size_t)width * elem, user,
+        OCSB_CUDA(cudaMemcpy2DAsync(alloc, (size_t)width * elem,
+                                    (const char *)user +
+                                        (size_t)row0 * (size_t)user_stride * elem,
                                     (size_t)user_stride * elem,
                                     (size_t)width * elem, (size_t)rows,
                                     cudaMemcpyHostToDevice, ctx->stream));
@@ -82,8 +87,10 @@ int32_t Staged::init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
 }
 
 int32_t Staged::finish() {
-    if (staged && dev && (dir & STAGE_OUT)) {
-        OCSB_CUDA(cudaMemcpy2DAsync(user, (size_t)user_stride * elem, dev,
+    if (staged && alloc && (dir & STAGE_OUT)) {
+        OCSB_CUDA(cudaMemcpy2DAsync((char *)user +
+                                        (size_t)row0 * (size_t)user_stride * elem,
+                                    (size_t)user_stride * elem, alloc,
                                     (size_t)width * elem, (size_t)width * elem,
                                     (size_t)rows, cudaMemcpyDeviceToHost,
                                     ctx->stream));
@@ -92,7 +99,7 @@ int32_t Staged::finish() {
 }
 
 Staged::~Staged() {
-    if (staged && dev) ocsb_free(ctx, dev);
+    if (staged && alloc) ocsb_free(ctx, alloc);
 }
 
 // after the work of one API call was enqueued: if anything was staged the
@@ -257,6 +264,16 @@ static int32_t check_win(const ocsb_win *win, const char *who) {
     return OCSB_OK;
 }
 
+// the device tile [rb, re) of a window
+static int32_t win_band(const ocsb_win *win, const char *who, int *rb, int *re) {
+    *rb = win->row_begin;
+    *re = win->row_end == 0 ? win->height : win->row_end;
+    OCSB_REQUIRE(*rb >= 0 && *rb < *re && *re <= win->height,
+                 "%s: bad row band [%d, %d) of a window of height %d", who,
+                 win->row_begin, win->row_end, win->height);
+    return OCSB_OK;
+}
+
 static void win_axes(const ocsb_win *win, LinAxis *ax, LinAxis *ay) {
     *ax = make_axis(win->x0, win->x1, win->width);   // get_x: linspace(x0, x1, w)
     *ay = make_axis(win->y1, win->y0, win->height);  // get_y: linspace(y1, y0, h)
@@ -368,19 +385,24 @@ extern "C" int32_t ocsb_hfun_feature(
         a.r = std::numeric_limits<double>::infinity();
     }
 
-    const int w = win->width, h = win->height;
+    const int w = win->width;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_feature", &rb, &re));
+    a.row_begin = rb;
+    a.row_end = re;
+    const int h = re - rb;
     Staged sv, so, sn, sd, si;
     OCSB_TRY(sv.init(ctx, verts_xy, 1, nv * 2, nv * 2, 8, STAGE_IN));
     const bool alias = (const void *)hfun_old == (const void *)hfun_new &&
                        old_stride == new_stride;
     if (alias) {
-        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT));
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT, rb));
     } else {
-        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN));
-        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT));
+        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN, rb));
+        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT, rb));
     }
-    OCSB_TRY(sd.init(ctx, dist_out, h, w, w, 8, STAGE_OUT));
-    OCSB_TRY(si.init(ctx, idx_out, h, w, w, 8, STAGE_OUT));
+    OCSB_TRY(sd.init(ctx, dist_out, h, w, w, 8, STAGE_OUT, rb));
+    OCSB_TRY(si.init(ctx, idx_out, h, w, w, 8, STAGE_OUT, rb));
     const float *oldp = alias ? (const float *)sn.dev : (const float *)so.dev;
     int64_t olds = alias ? sn.dev_stride : so.dev_stride;
     OCSB_TRY(k_hfun_feature(ctx, a, (const double *)sv.dev, nv, oldp, olds,
@@ -434,22 +456,27 @@ extern "C" int32_t ocsb_hfun_flow_limiter(
     OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
                  "ocsb_hfun_flow_limiter: dx/dy is NaN");
     const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_flow_limiter", &rb, &re));
+    const int hb = re - rb;
+    // DEM rows needed: the band plus one halo row on each side
+    const int zb = rb > 0 ? rb - 1 : 0, ze = re < h ? re + 1 : h;
     const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
     Staged sz, so, sn;
-    OCSB_TRY(sz.init(ctx, dem, h, w, dem_stride, es, STAGE_IN));
+    OCSB_TRY(sz.init(ctx, dem, ze - zb, w, dem_stride, es, STAGE_IN, zb));
     const bool alias = (const void *)hfun_old == (const void *)hfun_new &&
                        old_stride == new_stride;
     if (alias) {
-        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT));
+        OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_INOUT, rb));
     } else {
-        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN));
-        OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT));
+        OCSB_TRY(so.init(ctx, hfun_old, hb, w, old_stride, 4, STAGE_IN, rb));
+        OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_OUT, rb));
     }
     LimiterArgs a{dx, dy, hmin, hmax, lower_bound, upper_bound, ghmin, ghmax,
                   fuse_clamp};
     const float *oldp = alias ? (const float *)sn.dev : (const float *)so.dev;
     int64_t olds = alias ? sn.dev_stride : so.dev_stride;
-    OCSB_TRY(k_flow_limiter(ctx, w, h, sz.dev, dem_dtype, sz.dev_stride, oldp,
+    OCSB_TRY(k_flow_limiter(ctx, w, h, rb, re, sz.dev, dem_dtype, sz.dev_stride, oldp,
                             olds, (float *)sn.dev, sn.dev_stride, a));
     return finish_call(ctx, {&sz, &so, &sn});
 }

@@ -145,13 +145,16 @@ enum StageDir { STAGE_IN = 1, STAGE_OUT = 2, STAGE_INOUT = 3 };
 struct Staged {
     ocsb_ctx *ctx = nullptr;
     void *user = nullptr;
-    void *dev = nullptr;
+    void *dev = nullptr;     // (virtual) device address of row 0
+    void *alloc = nullptr;   // the staging allocation (holds rows row0..)
+    int64_t row0 = 0;
     int64_t rows = 0, width = 0, user_stride = 0, dev_stride = 0;
     size_t elem = 0;
     int dir = 0;
     bool staged = false;
+    // rows [row0_, row0_ + rows_) of the user buffer are (to be) valid
     int32_t init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
-                 int64_t stride_, size_t elem_, int dir_);
+                 int64_t stride_, size_t elem_, int dir_, int64_t row0_ = 0);
     int32_t finish();  // enqueue copy-back (if staged and OUT)
     ~Staged();
 };
@@ -183,13 +186,15 @@ struct LimiterArgs {
     double hmin, hmax, lb, ub, ghmin, ghmax;  // NaN = None
     int fuse_clamp;
 };
-int32_t k_flow_limiter(ocsb_ctx *ctx, int w, int h, const void *dem,
+int32_t k_flow_limiter(ocsb_ctx *ctx, int w, int h, int row_begin, int row_end,
+                       const void *dem,
                        int dem_dtype, int64_t dem_stride, const float *old_,
                        int64_t old_stride, float *new_, int64_t new_stride,
                        const LimiterArgs &a);
 
 struct FeatureArgs {
     LinAxis ax, ay;         // pixel coordinates of the window
+    int row_begin, row_end; // device tile: rows [row_begin, row_end)
     double rate_target;     // expansion_rate * target_size (f64 product)
     double target;
     double r;               // search radius, +inf if unbounded

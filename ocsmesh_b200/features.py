@@ -1,0 +1,245 @@
+"""Host-side feature prologue of ``HfunRaster.add_feature`` / ``add_contour``.
+
+The reference resamples every feature line to ``target_size`` spacing before
+building the kd-tree (``ocsmesh/hfun/raster.py:1183-1225`` calling
+``utils.repartition_features`` ``ocsmesh/utils.py:247-277`` and
+``utils.transform_linestring`` ``ocsmesh/utils.py:280-312``).  That work is
+O(vertices), not O(pixels), so it stays on the host -- and is hoisted out of
+the window loop: for a projected CRS the result does not depend on the window.
+
+shapely is not a dependency; a line is an ``(n, 2)`` float64 array.  Objects
+with ``.coords`` (LineString-like) or ``.geoms`` (MultiLineString-like) are
+accepted wherever the reference accepts shapely geometries.
+"""
+from __future__ import annotations
+
+from typing import Iterable, List, Sequence
+
+import numpy as np
+
+
+def _is_linestring_like(obj) -> bool:
+    return hasattr(obj, "coords") and not hasattr(obj, "geoms")
+
+
+def _is_multilinestring_like(obj) -> bool:
+    return hasattr(obj, "geoms")
+
+
+def as_linestrings(feature) -> List[np.ndarray]:
+    """Flatten a feature argument into a list of ``(n, 2)`` float64 arrays.
+
+    Raises ``TypeError`` for anything that is not line-like -- the
+    reference's check at ``ocsmesh/hfun/raster.py:1155-1158``.
+    """
+    if _is_multilinestring_like(feature):
+        out = []
+        for g in feature.geoms:
+            out.extend(as_linestrings(g))
+        return out
+    if _is_linestring_like(feature):
+        return [np.asarray(feature.coords, dtype=float)[:, :2]]
+    if isinstance(feature, np.ndarray):
+        if feature.ndim == 2 and feature.shape[1] >= 2:
+            return [np.asarray(feature, dtype=float)[:, :2]]
+        raise TypeError("Argument feature must be an (n, 2) array, a "
+                        "LineString or a MultiLineString, not an array of "
+                        f"shape {feature.shape}.")
+    if isinstance(feature, (list, tuple)):
+        if len(feature) == 0:
+            return []
+        if all(isinstance(f, (list, tuple)) and len(f) == 2
+               and all(np.isscalar(v) for v in f) for f in feature):
+            return [np.asarray(feature, dtype=float)]
+        out = []
+        for f in feature:
+            out.extend(as_linestrings(f))
+        return out
+    raise TypeError(
+        "Argument feature must be of type LineString or MultiLineString "
+        f"(or (n, 2) arrays), not type {type(feature)}.")
+
+
+def repartition_features(linestring: np.ndarray, max_verts: int) -> List[np.ndarray]:
+    """``ocsmesh/utils.py:247-277``: cut a line into chunks of at most
+    ``max_verts`` vertices that share their end vertex."""
+    if not isinstance(max_verts, (int, np.integer)) or isinstance(max_verts, bool):
+        raise ValueError("Maximum number of vertices must be an integer!")
+    coords = np.asarray(linestring, dtype=float)
+    n = len(coords)
+    if n <= max_verts:
+        return [coords]
+    step = max_verts - 1
+    list_lens = [max_verts] * ((n - 1) // step)
+    if (n - 1) % step != 0:
+        list_lens.append((n - 1) % step + 1)
+    ends = np.cumsum(np.array(list_lens) - 1)
+    out, last = [], 0
+    for e in ends:
+        out.append(coords[last:e + 1])
+        last = e
+    return out
+
+
+def transform_linestring(linestring: np.ndarray, target_size: float) -> np.ndarray:
+    """``ocsmesh/utils.py:280-312``: points every ``target_size`` along the
+    line (plus both ends); a line shorter than ``target_size`` is unchanged."""
+    c = np.asarray(linestring, dtype=float)
+    if len(c) < 2:
+        return c
+    lengths = ((c[1:] - c[:-1]) ** 2).sum(axis=1) ** 0.5
+    cum_len = np.cumsum(lengths)
+    total = float(cum_len[-1])
+    distances = np.cumsum(np.ones(int(total // target_size)) * target_size)
+    if len(distances) == 0:
+        return c
+    if distances[-1] < total:
+        distances = np.append(distances, total)
+    # index of the segment holding each station: first k with
+    # distances <= cum_len[k]  (== len - count(distances <= cum_len))
+    idx = np.searchsorted(cum_len, distances, side="left")
+    idx = np.minimum(idx, len(cum_len) - 1)
+    ratio = ((cum_len[idx] - distances) / lengths[idx])[:, None]
+    pts = c[idx] * ratio + c[idx + 1] * (1 - ratio)
+    return np.vstack((c[0], pts))
+
+
+def feature_points(features: Sequence[np.ndarray], target_size: float,
+                   max_verts: int = 200) -> np.ndarray:
+    """The ``points`` array handed to the kd-tree at
+    ``ocsmesh/hfun/raster.py:1230`` (projected CRS): repartition, resample each
+    chunk, concatenate."""
+    parts = []
+    for ls in features:
+        for chunk in repartition_features(ls, max_verts):
+            parts.append(transform_linestring(chunk, target_size))
+    if not parts:
+        return np.empty((0, 2), dtype=float)
+    return np.ascontiguousarray(np.concatenate(parts, axis=0))
+
+
+# ---------------------------------------------------------------------------
+# contour tracing (CPU step before the accelerated path)
+# ---------------------------------------------------------------------------
+def marching_squares(x, y, z, level) -> List[np.ndarray]:
+    """Iso-lines of ``z`` (``(h, w)``; row ``j`` at ``y[j]``, column ``i`` at
+    ``x[i]``) at ``level`` as stitched polylines.
+
+    The reference obtains these from matplotlib/contourpy + shapely linemerge
+    (``ocsmesh/raster.py:1426-1470``); neither is available here.  Crossings
+    are placed by linear interpolation along cell edges, saddles are resolved
+    with the cell mean, and segments are stitched through shared cell edges.
+    """
+    z = np.asarray(z, dtype=float)
+    x = np.asarray(x, dtype=float)
+    y = np.asarray(y, dtype=float)
+    h, w = z.shape
+    if h < 2 or w < 2:
+        return []
+    above = z > level
+    n_he = h * (w - 1)
+
+    # corner bits: 1 = (j,i), 2 = (j,i+1), 4 = (j+1,i+1), 8 = (j+1,i)
+    code = (above[:-1, :-1].astype(np.uint8)
+            | (above[:-1, 1:].astype(np.uint8) << 1)
+            | (above[1:, 1:].astype(np.uint8) << 2)
+            | (above[1:, :-1].astype(np.uint8) << 3))
+    jj, ii = np.nonzero((code != 0) & (code != 15))
+    if len(jj) == 0:
+        return []
+    cc = code[jj, ii]
+    top = jj * (w - 1) + ii
+    bot = (jj + 1) * (w - 1) + ii
+    lef = n_he + jj * w + ii
+    rig = n_he + jj * w + ii + 1
+    cen = 0.25 * (z[jj, ii] + z[jj, ii + 1] + z[jj + 1, ii] + z[jj + 1, ii + 1]) > level
+
+    ea, eb = [], []
+
+    def emit(sel, a, b):
+        if np.any(sel):
+            ea.append(a[sel])
+            eb.append(b[sel])
+
+    for (c0, c1), a, b in (((1, 14), top, lef), ((2, 13), top, rig),
+                           ((4, 11), rig, bot), ((8, 7), lef, bot),
+                           ((3, 12), lef, rig), ((6, 9), top, bot)):
+        emit((cc == c0) | (cc == c1), a, b)
+    s5, s10 = cc == 5, cc == 10
+    emit(s5 & cen, top, rig)
+    emit(s5 & cen, lef, bot)
+    emit(s5 & ~cen, top, lef)
+    emit(s5 & ~cen, rig, bot)
+    emit(s10 & cen, top, lef)
+    emit(s10 & cen, rig, bot)
+    emit(s10 & ~cen, top, rig)
+    emit(s10 & ~cen, lef, bot)
+    if not ea:
+        return []
+    ea = np.concatenate(ea)
+    eb = np.concatenate(eb)
+
+    # crossing point of every used edge
+    ids, inv = np.unique(np.concatenate([ea, eb]), return_inverse=True)
+    px = np.empty(len(ids))
+    py = np.empty(len(ids))
+    is_h = ids < n_he
+    hj, hi = np.divmod(ids[is_h], w - 1)
+    t = (level - z[hj, hi]) / (z[hj, hi + 1] - z[hj, hi])
+    px[is_h] = x[hi] + t * (x[hi + 1] - x[hi])
+    py[is_h] = y[hj]
+    vj, vi = np.divmod(ids[~is_h] - n_he, w)
+    t = (level - z[vj, vi]) / (z[vj + 1, vi] - z[vj, vi])
+    px[~is_h] = x[vi]
+    py[~is_h] = y[vj] + t * (y[vj + 1] - y[vj])
+
+    ns = len(ea)
+    a, b = inv[:ns], inv[ns:]
+    nn = len(ids)
+    ends = np.concatenate([a, b])
+    other = np.concatenate([b, a])
+    order = np.argsort(ends, kind="stable")
+    ends, other = ends[order], other[order]
+    first = np.ones(len(ends), dtype=bool)
+    first[1:] = ends[1:] != ends[:-1]
+    nbr = np.full((nn, 2), -1, dtype=np.int64)
+    nbr[ends[first], 0] = other[first]
+    nbr[ends[~first], 1] = other[~first]
+    deg = (nbr >= 0).sum(axis=1)
+
+    visited = np.zeros(nn, dtype=bool)
+    nbr_l = nbr.tolist()
+    lines = []
+
+    def walk(start):
+        path = [start]
+        visited[start] = True
+        cur = start
+        while True:
+            n0, n1 = nbr_l[cur]
+            if n0 >= 0 and not visited[n0]:
+                nxt = n0
+            elif n1 >= 0 and not visited[n1]:
+                nxt = n1
+            else:
+                if len(path) > 2 and start in (n0, n1):
+                    path.append(start)  # closed ring
+                break
+            path.append(nxt)
+            visited[nxt] = True
+            cur = nxt
+        return path
+
+    for s in np.nonzero(deg == 1)[0].tolist():
+        if not visited[s]:
+            lines.append(walk(s))
+    for s in np.nonzero(deg == 2)[0].tolist():
+        if not visited[s]:
+            lines.append(walk(s))
+    out = []
+    for path in lines:
+        if len(path) < 2:
+            continue
+        e = np.asarray(path)
+        out.append(np.stack([px[e], py[e]], axis=1))
+    return out

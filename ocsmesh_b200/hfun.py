@@ -1,0 +1,465 @@
+"""``Hfun`` / ``HfunRaster`` -- the raster size function on the GPU.
+
+Mirror of ``ocsmesh.Hfun`` (factory, ``ocsmesh/hfun/hfun.py:40-64``) and
+``ocsmesh.hfun.raster.HfunRaster`` (``ocsmesh/hfun/raster.py:92-251``) for the
+accelerated path: ``add_contour`` (``:936-1014``), ``add_feature``
+(``:1084-1261``), ``add_subtidal_flow_limiter`` (``:1315-1436``) and the global
+clamp re-pass that ``apply_constraints_wrap`` triggers after every ``add_*``
+(``ocsmesh/features/constraint.py:398-424``, ``hfun/raster.py:488-568``).
+
+Where the reference rewrites a temporary GeoTIFF per operation, the size
+raster here is ONE float32 device buffer (FLT_MAX-initialised by a fill
+kernel) that every operation read-modify-writes in place through the C ABI of
+libocsb200; pixels only come back to the host on ``get_values`` / ``save``.
+Semantic windows (``chunk_size`` / ``overlap`` copied from the DEM,
+``hfun/raster.py:84-86``) are honoured: coordinates are per-window linspaces and
+the gradient stencil is one-sided on window borders, exactly as in the
+reference.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import pathlib
+from contextlib import contextmanager
+from typing import List, Optional, Sequence, Union
+
+import numpy as np
+
+from . import _lib
+from . import features as _features
+from . import geotiff
+from .raster import CRS, Raster, Window
+
+_logger = logging.getLogger(__name__)
+
+FLT_MAX = float(np.finfo(np.float32).max)
+
+
+def _dem_dtype_code(t) -> int:
+    import torch
+    return _lib.OCSB_F32 if t.dtype == torch.float32 else _lib.OCSB_F64
+
+
+class HfunRaster:
+    """Raster based size function (drop-in for the reference class on the
+    contour / feature / flow-limiter path)."""
+
+    def __init__(self, raster: Raster, hmin: Optional[float] = None,
+                 hmax: Optional[float] = None, verbosity: int = 0,
+                 initial_value=None, device: Optional[int] = None,
+                 row_band: Optional[Sequence[int]] = None) -> None:
+        if not isinstance(raster, Raster):
+            raise TypeError(
+                f'Argument raster must be of type {Raster}, not type '
+                f'{type(raster)}.')
+        import torch
+        self._raster = raster
+        self._hmin = float(hmin) if hmin is not None else hmin
+        self._hmax = float(hmax) if hmax is not None else hmax
+        self._verbosity = int(verbosity)
+        self._constraints: List = []
+        self._hold_const = False
+        self._hold_const_hit = 0
+        self._chunk_size = raster.chunk_size
+        self._overlap = raster.overlap
+        self._device = torch.cuda.current_device() if device is None else int(device)
+        # device tile: the rows of the raster this object (rank) owns.  Results
+        # inside the band are bit-identical to the un-banded object.
+        if row_band is None:
+            self._band = (0, raster.height)
+        else:
+            self._band = (int(row_band[0]), int(row_band[1]))
+            if not 0 <= self._band[0] < self._band[1] <= raster.height:
+                raise ValueError(f"bad row_band {row_band}")
+        ctx = self._ctx()
+        h, w = raster.height, raster.width
+        with torch.cuda.device(self._device):
+            self._hfun = torch.empty((h, w), dtype=torch.float32,
+                                     device=f"cuda:{self._device}")
+        if initial_value is not None:
+            if isinstance(initial_value, (str, pathlib.Path, os.PathLike)):
+                info, bands = geotiff.read_geotiff(initial_value)
+                init = np.asarray(bands[0], dtype=np.float32)
+            else:
+                init = np.asarray(initial_value, dtype=np.float32)
+            if init.shape != (h, w):
+                raise ValueError("initial_value does not match the raster shape")
+            self._hfun.copy_(torch.from_numpy(np.ascontiguousarray(init)))
+        else:
+            # hfun/raster.py:75-82: every pixel = finfo(float32).max
+            ctx.fill_f32(self._hfun, h * w, FLT_MAX)
+
+    # ---- plumbing -----------------------------------------------------------
+    def _ctx(self) -> _lib.Context:
+        return _lib.default_context(self._device)
+
+    def _windows(self) -> List[Window]:
+        """HfunRaster iterates ITS OWN windows, built from the DEM's
+        chunk_size / overlap (hfun/raster.py:68-73, 84-86)."""
+        return list(self._raster.iter_windows(self._chunk_size, self._overlap))
+
+    def _band_of(self, window: Window):
+        """Intersection of the owned row band with a window, in window rows."""
+        rb = max(self._band[0], window.row_off) - window.row_off
+        re = min(self._band[1], window.row_off + window.height) - window.row_off
+        return (rb, re) if re > rb else None
+
+    def _needs_double_buffer(self, windows) -> bool:
+        return len(windows) > 1 and (self._overlap or 0) > 0
+
+    def _check_projected(self):
+        crs = self._raster.crs
+        if crs is not None and getattr(crs, "is_geographic", False):
+            raise NotImplementedError(
+                "geographic rasters need the reference's pyproj lon/lat->UTM "
+                "branch (hfun/raster.py:1178-1210), which is outside this "
+                "build: use a projected (metre) CRS")
+
+    # ---- properties ---------------------------------------------------------
+    @property
+    def raster(self) -> Raster:
+        return self._raster
+
+    @property
+    def hmin(self):
+        return self._hmin
+
+    @property
+    def hmax(self):
+        return self._hmax
+
+    @property
+    def verbosity(self):
+        return self._verbosity
+
+    @verbosity.setter
+    def verbosity(self, v):
+        self._verbosity = int(v)
+
+    @property
+    def crs(self):
+        return self._raster.crs
+
+    @property
+    def shape(self):
+        return self._raster.shape
+
+    @property
+    def width(self):
+        return self._raster.width
+
+    @property
+    def height(self):
+        return self._raster.height
+
+    @property
+    def transform(self):
+        return self._raster.transform
+
+    @property
+    def chunk_size(self):
+        return self._chunk_size
+
+    @property
+    def overlap(self):
+        return self._overlap
+
+    @property
+    def device_values(self):
+        """The float32 (h, w) size raster as a CUDA tensor (no copy)."""
+        return self._hfun
+
+    @property
+    def values(self) -> np.ndarray:
+        return self.get_values()
+
+    def iter_windows(self, chunk_size=None, overlap=None):
+        yield from self._raster.iter_windows(
+            self._chunk_size if chunk_size is None else chunk_size,
+            self._overlap if overlap is None else overlap)
+
+    def get_window_bounds(self, window):
+        return self._raster.get_window_bounds(window)
+
+    def get_x(self, window=None):
+        return self._raster.get_x(window)
+
+    def get_y(self, window=None):
+        return self._raster.get_y(window)
+
+    def get_xy(self, window=None):
+        return self._raster.get_xy(window)
+
+    def get_bbox(self, crs=None):
+        return self._raster.get_bbox(crs)
+
+    def get_values(self, window: Optional[Window] = None,
+                   band: Optional[int] = None, **_kwargs) -> np.ndarray:
+        """Size values as a host float32 array (synchronises the stream)."""
+        if band not in (None, 1):
+            raise IndexError("the hfun raster has a single band")
+        t = self._hfun
+        if window is not None:
+            t = t[window.row_off:window.row_off + window.height,
+                  window.col_off:window.col_off + window.width]
+        return t.cpu().numpy()
+
+    def save(self, path):
+        epsg = self.crs.to_epsg() if self.crs is not None else None
+        geographic = bool(self.crs.is_geographic) if self.crs is not None else False
+        geotiff.write_geotiff(path, self.get_values(), self.transform, epsg=epsg,
+                              is_geographic=geographic)
+
+    # ---- constraints (A10) --------------------------------------------------
+    @contextmanager
+    def hold_applying_added_constratins(self):
+        """(sic) ``hfun/raster.py:476-485``."""
+        try:
+            self._hold_const = True
+            yield
+        finally:
+            self._hold_const = False
+            if self._hold_const_hit > 0:
+                self.apply_added_constraints()
+                self._hold_const_hit = 0
+
+    def apply_added_constraints(self) -> None:
+        if self._hold_const:
+            self._hold_const_hit += 1
+            return
+        self.apply_constraints(self._constraints)
+
+    def apply_constraints(self, constraint_list) -> None:
+        """``hfun/raster.py:509-568``.  Custom constraint objects are a
+        "next" row of the scope table; with none registered the pass is the
+        global [hmin, hmax] clamp, one streaming kernel over the owned band."""
+        if len(list(constraint_list)) > 0:
+            raise NotImplementedError(
+                "custom Constraint objects are not part of the accelerated "
+                "path yet (SURVEY.md 8(f) next-2)")
+        if self._hmin is None and self._hmax is None:
+            return
+        w = self.width
+        rb, re = self._band
+        ctx = self._ctx()
+        ctx.hfun_clamp(self._hfun.data_ptr() + rb * w * 4, w, w, re - rb,
+                       self._hmin, self._hmax)
+
+    def _fuse_clamp(self) -> bool:
+        """The decorator's clamp re-pass is folded into the op's own kernel
+        (same per-pixel result: clamp(min(old, new)))."""
+        if self._hold_const:
+            self._hold_const_hit += 1
+            return False
+        return True
+
+    # ---- A5: add_contour ----------------------------------------------------
+    def add_contour(self, level: Union[List[float], float],
+                    expansion_rate: float, target_size: Optional[float] = None,
+                    nprocs: Optional[int] = None) -> None:
+        """``hfun/raster.py:936-1014``: contour lines of the DEM at ``level``
+        become features; returns silently when there is no contour."""
+        if not isinstance(level, list):
+            level = [level]
+        contours = []
+        for _level in level:
+            contours.extend(self._raster.get_contour(_level))
+        if len(contours) == 0:
+            _logger.info('No contours found!')
+            return
+        self.add_feature(contours, expansion_rate, target_size, nprocs=nprocs)
+        # outer decorator layer (idempotent clamp) -- only observable when
+        # constraints are being held
+        if self._hold_const:
+            self._hold_const_hit += 1
+
+    # ---- A6/A7: add_feature -------------------------------------------------
+    def add_feature(self, feature, expansion_rate: float,
+                    target_size: Optional[float] = None, max_verts=200, *,
+                    nprocs: Optional[int] = None, pool=None) -> None:
+        """``hfun/raster.py:1084-1261``.  ``nprocs`` / ``pool`` are accepted
+        for signature compatibility and ignored (the work runs on the GPU)."""
+        del nprocs, pool
+        lines = _features.as_linestrings(feature)
+        target_size = self._hmin if target_size is None else target_size
+        if target_size is None:
+            raise ValueError('Argument target_size must be specified if no '
+                             'global hmin has been set.')
+        if target_size <= 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        self._check_projected()
+        points = _features.feature_points(lines, float(target_size), max_verts)
+        self.add_feature_points(points, expansion_rate, target_size)
+
+    def add_feature_points(self, points, expansion_rate: float,
+                           target_size: Optional[float] = None) -> None:
+        """Entry at the parity boundary ``hfun/raster.py:1230``: ``points`` is
+        the already resampled ``(N, 2)`` float64 vertex array (host array or
+        CUDA tensor) handed to the nearest-vertex search."""
+        import torch
+        target_size = self._hmin if target_size is None else target_size
+        if target_size is None:
+            raise ValueError('Argument target_size must be specified if no '
+                             'global hmin has been set.')
+        if target_size <= 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        if isinstance(points, torch.Tensor):
+            verts = points.to(device=f"cuda:{self._device}",
+                              dtype=torch.float64).contiguous()
+        else:
+            pts = np.ascontiguousarray(np.asarray(points, dtype=np.float64))
+            if pts.ndim != 2 or pts.shape[1] != 2:
+                raise ValueError("points must be an (N, 2) array")
+            verts = torch.from_numpy(pts).to(f"cuda:{self._device}")
+        nv = int(verts.shape[0])
+        if nv == 0:
+            raise ValueError("add_feature needs at least one vertex")
+        ctx = self._ctx()
+        windows = self._windows()
+        fuse = self._fuse_clamp()
+        w = self.width
+        old = self._hfun
+        new = old.clone() if self._needs_double_buffer(windows) else old
+        for win in windows:
+            band = self._band_of(win)
+            if band is None:
+                continue
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            off = (win.row_off * w + win.col_off) * 4
+            ctx.hfun_feature(cw, verts, nv, old.data_ptr() + off, w,
+                             new.data_ptr() + off, w, expansion_rate,
+                             target_size, self._hmin, self._hmax,
+                             fuse_clamp=fuse)
+        self._hfun = new
+        # keep `verts` alive until the stream has consumed it
+        self._last_verts = verts
+
+    # ---- A8/A9: flow limiter / gradient delimiter ----------------------------
+    def add_subtidal_flow_limiter(self, hmin: Optional[float] = None,
+                                  hmax: Optional[float] = None,
+                                  lower_bound: Optional[float] = None,
+                                  upper_bound: Optional[float] = None) -> None:
+        """``hfun/raster.py:1315-1436`` (projected CRS branch)."""
+        self._check_projected()
+        hmin = float(hmin) if hmin is not None else hmin
+        hmax = float(hmax) if hmax is not None else hmax
+        ctx = self._ctx()
+        windows = self._windows()
+        fuse = self._fuse_clamp()
+        w = self.width
+        dem = self._raster.device_band(1, self._device)
+        es = dem.element_size()
+        code = _dem_dtype_code(dem)
+        old = self._hfun
+        new = old.clone() if self._needs_double_buffer(windows) else old
+        dx, dy = self._raster.dx, self._raster.dy
+        for win in windows:
+            band = self._band_of(win)
+            if band is None:
+                continue
+            if win.width < 2 or win.height < 2:
+                raise ValueError(
+                    "Shape of array too small to calculate a numerical "
+                    "gradient, at least (edge_order + 1) elements are required.")
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            poff = win.row_off * w + win.col_off
+            ctx.hfun_flow_limiter(
+                cw, dem.data_ptr() + poff * es, code, w,
+                old.data_ptr() + poff * 4, w, new.data_ptr() + poff * 4, w,
+                dx, dy, hmin, hmax, lower_bound, upper_bound, self._hmin,
+                self._hmax, fuse_clamp=fuse)
+        self._hfun = new
+
+    def add_gradient_delimiter(self, hmin: Optional[float] = None,
+                               hmax: Optional[float] = None) -> None:
+        """Named by BASELINE.json but absent from the reference snapshot
+        (SURVEY.md 0.2): the |z| / (3 |grad z|) limiter without an elevation
+        band, i.e. ``add_subtidal_flow_limiter(hmin, hmax, None, None)``."""
+        self.add_subtidal_flow_limiter(hmin, hmax, None, None)
+
+    # ---- A12: pixel-wise min with another, co-registered hfun window ---------
+    def min_combine(self, other: "HfunRaster", window: Optional[Window] = None,
+                    other_window: Optional[Window] = None) -> None:
+        """hfun[window] = min(hfun[window], other[other_window]) (build-defined
+        multi-raster combine)."""
+        window = Window(0, 0, self.width, self.height) if window is None else window
+        other_window = (Window(0, 0, other.width, other.height)
+                        if other_window is None else other_window)
+        if (window.width, window.height) != (other_window.width, other_window.height):
+            raise ValueError("windows must have the same shape")
+        src = other.device_values
+        if src.device != self._hfun.device:
+            src = src.to(self._hfun.device)
+        ctx = self._ctx()
+        ctx.min_combine(
+            self._hfun.data_ptr() + (window.row_off * self.width + window.col_off) * 4,
+            self.width,
+            src.data_ptr() + (other_window.row_off * other.width + other_window.col_off) * 4,
+            other.width, window.width, window.height)
+
+
+class HfunCollector:
+    """Minimal multi-raster size function: one ``HfunRaster`` per input
+    raster, every ``add_*`` applied to every raster -- the call order of the
+    reference's exact collector (``ocsmesh/hfun/collector.py:1536-1563,
+    1590-1655``): every contour of every raster goes to every hfun."""
+
+    def __init__(self, in_list, base_mesh=None, hmin=None, hmax=None,
+                 nprocs=None, verbosity=0, method='exact', base_as_hfun=True,
+                 base_shape=None, base_shape_crs=None):
+        del base_mesh, nprocs, base_as_hfun, base_shape, base_shape_crs
+        if method not in ('exact',):
+            raise NotImplementedError("only the 'exact' collector method is "
+                                      "part of the accelerated path")
+        self._hfuns = []
+        for r in in_list:
+            if isinstance(r, HfunRaster):
+                self._hfuns.append(r)
+            elif isinstance(r, Raster):
+                self._hfuns.append(HfunRaster(r, hmin, hmax, verbosity))
+            else:
+                raise TypeError(f"unsupported collector input {type(r)}")
+        self._hmin, self._hmax = hmin, hmax
+
+    @property
+    def hfuns(self):
+        return self._hfuns
+
+    def add_contour(self, level, expansion_rate, target_size=None, **_kw):
+        if not isinstance(level, list):
+            level = [level]
+        contours = []
+        for h in self._hfuns:
+            for lv in level:
+                contours.extend(h.raster.get_contour(lv))
+        if not contours:
+            return
+        for h in self._hfuns:
+            h.add_feature(contours, expansion_rate, target_size)
+
+    def add_feature(self, feature, expansion_rate, target_size=None,
+                    max_verts=200, **_kw):
+        for h in self._hfuns:
+            h.add_feature(feature, expansion_rate, target_size, max_verts)
+
+    def add_subtidal_flow_limiter(self, hmin=None, hmax=None,
+                                  lower_bound=None, upper_bound=None, **_kw):
+        for h in self._hfuns:
+            h.add_subtidal_flow_limiter(hmin, hmax, lower_bound, upper_bound)
+
+
+class Hfun:
+    """Factory (``ocsmesh/hfun/hfun.py:40-64``): ``Hfun(Raster) ->
+    HfunRaster``, ``Hfun(list) -> HfunCollector``."""
+
+    def __new__(cls, hfun, **kwargs):
+        if isinstance(hfun, Raster):
+            return HfunRaster(hfun, **kwargs)
+        if isinstance(hfun, (list, tuple)):
+            return HfunCollector(list(hfun), **kwargs)
+        raise TypeError(
+            f'Argument hfun must be of type {Raster} or a list of rasters, '
+            f'not type {type(hfun)}.')

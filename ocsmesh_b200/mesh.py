@@ -1,0 +1,210 @@
+"""``Mesh`` / ``MeshData`` -- DEM -> mesh-node sampling on the GPU.
+
+Mirror of ``ocsmesh.Mesh`` (factory ``ocsmesh/mesh/mesh.py:574-600``),
+``EuclideanMesh2D.interpolate`` (``:314-425``) with its per-raster worker
+``_mesh_interpolate_worker`` (``:2232-2349``) and of ``ocsmesh.MeshData``
+(``ocsmesh/internal.py:44-286``) as far as this path touches them.
+
+The node coordinates are uploaded once per ``interpolate`` call; each raster
+in the list is then one gather-kernel launch that updates the nodes it covers,
+so rasters applied in list order reproduce the reference's "last raster wins"
+scatter (``mesh/mesh.py:372-376``) without any host round trip.
+"""
+from __future__ import annotations
+
+import logging
+from typing import List, Optional, Sequence, Union
+
+import numpy as np
+
+from . import _lib
+from .raster import CRS, Raster, Window
+
+_logger = logging.getLogger(__name__)
+
+_METHODS = {"linear": _lib.INTERP_LINEAR, "nearest": _lib.INTERP_NEAREST,
+            "spline": _lib.INTERP_SPLINE}
+
+
+class MeshData:
+    """Mesh container (``ocsmesh/internal.py:44-286``): ``coords (K,2) f64``,
+    ``tria (T,3)``, ``quad (Q,4)`` int, ``values (K,D) f64``, ``crs``."""
+
+    def __init__(self, coords, tria=None, quad=None, values=None, crs=None):
+        self._coords = None
+        self._values = None
+        self.coords = coords
+        self.tria = tria if tria is not None else np.empty((0, 3), dtype=int)
+        self.quad = quad if quad is not None else np.empty((0, 4), dtype=int)
+        if values is not None:
+            self.values = values
+        self.crs = crs
+
+    @property
+    def coords(self) -> np.ndarray:
+        return self._coords
+
+    @coords.setter
+    def coords(self, val):
+        val = np.array(val, dtype=float)
+        if val.ndim != 2 or val.shape[1] != 2:
+            raise ValueError("coords must be an (N, 2) array")
+        if self._coords is None or len(val) != len(self._coords):
+            self._values = np.zeros((len(val), 1), dtype=float)
+        self._coords = val
+
+    @property
+    def tria(self) -> np.ndarray:
+        return self._tria
+
+    @tria.setter
+    def tria(self, val):
+        val = np.array(val, dtype=int)
+        self._tria = val.reshape(-1, 3) if val.size else np.empty((0, 3), dtype=int)
+
+    @property
+    def quad(self) -> np.ndarray:
+        return self._quad
+
+    @quad.setter
+    def quad(self, val):
+        val = np.array(val, dtype=int)
+        self._quad = val.reshape(-1, 4) if val.size else np.empty((0, 4), dtype=int)
+
+    @property
+    def values(self) -> np.ndarray:
+        return self._values
+
+    @values.setter
+    def values(self, val):
+        val = np.array(val, dtype=float)
+        if val.ndim == 1:
+            val = val.reshape(-1, 1)
+        if val.shape[0] != self.num_nodes:
+            raise ValueError("values must have one row per node")
+        self._values = val
+
+    @property
+    def crs(self):
+        return self._crs
+
+    @crs.setter
+    def crs(self, val):
+        self._crs = None if val is None else CRS.from_user_input(val)
+
+    @property
+    def num_nodes(self) -> int:
+        return len(self._coords)
+
+    @property
+    def num_elements(self) -> int:
+        return len(self._tria) + len(self._quad)
+
+    def __repr__(self):
+        return (f"<MeshData: {self.num_nodes} Nodes, {len(self.tria)} Tria, "
+                f"{len(self.quad)} Quad, Values {self.values.shape}>")
+
+
+class EuclideanMesh2D:
+    """2-D mesh with raster interpolation (``ocsmesh/mesh/mesh.py:129-571``)."""
+
+    def __init__(self, mesh: MeshData) -> None:
+        if not isinstance(mesh, MeshData):
+            raise TypeError(f'Argument mesh must be of type {MeshData}, '
+                            f'not type {type(mesh)}.')
+        self.meshdata = mesh
+
+    # mesh/mesh.py:540-571
+    @property
+    def vert2(self):
+        return self.meshdata.coords
+
+    @property
+    def coord(self):
+        return self.meshdata.coords
+
+    @property
+    def value(self):
+        return self.meshdata.values
+
+    @property
+    def values(self):
+        return self.meshdata.values
+
+    @property
+    def crs(self):
+        return self.meshdata.crs
+
+    @property
+    def tria3(self):
+        return self.meshdata.tria
+
+    @property
+    def quad4(self):
+        return self.meshdata.quad
+
+    def interpolate(self, raster: Union[Raster, List[Raster]],
+                    method: str = 'spline', nprocs: Optional[int] = None,
+                    info_out_path=None, filter_by_shape: bool = False,
+                    band: int = 1, *, device: Optional[int] = None,
+                    node_range: Optional[Sequence[int]] = None) -> None:
+        """Interpolate raster values onto the mesh nodes
+        (``mesh/mesh.py:314-425``).
+
+        ``nprocs`` is accepted and ignored.  ``node_range=(k0, k1)`` restricts
+        the call to a contiguous shard of the nodes (multi-GPU node sharding);
+        untouched nodes keep their value.
+        """
+        import torch
+        del nprocs
+        if isinstance(raster, Raster):
+            raster = [raster]
+        if method not in _METHODS:
+            raise ValueError(f"Invalid value method specified <{method}>!")
+        if filter_by_shape:
+            raise NotImplementedError("filter_by_shape needs shapely")
+        if info_out_path is not None:
+            raise NotImplementedError("info_out_path needs pyproj/pandas glue")
+        dev = torch.cuda.current_device() if device is None else int(device)
+        ctx = _lib.default_context(dev)
+        coords = self.vert2
+        values = self.meshdata.values.flatten()
+        k0, k1 = (0, len(coords)) if node_range is None else map(int, node_range)
+        K = k1 - k0
+        if K > 0:
+            xy = torch.from_numpy(np.ascontiguousarray(coords[k0:k1])).to(f"cuda:{dev}")
+            vals = torch.from_numpy(np.ascontiguousarray(values[k0:k1])).to(f"cuda:{dev}")
+            touched = torch.zeros(K, dtype=torch.uint8, device=f"cuda:{dev}")
+            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev)
+            values[k0:k1] = vals.cpu().numpy()
+        self.meshdata.values = values.reshape((values.shape[0], 1))
+
+    @staticmethod
+    def _interp_device(ctx, rasters, xy, vals, touched, method, band, dev):
+        """All rasters, in list order, against device-resident node arrays."""
+        import torch
+        code = _METHODS[method]
+        K = int(xy.shape[0])
+        for r in rasters:
+            dem = r.device_band(band, dev)
+            mask = r.device_mask(band, dev) if method != "spline" else None
+            es = dem.element_size()
+            dcode = _lib.OCSB_F32 if dem.dtype == torch.float32 else _lib.OCSB_F64
+            # the worker re-opens the raster and iterates
+            # iter_windows(chunk_size, overlap=2) (mesh/mesh.py:2274-2277)
+            for win in r.iter_windows(chunk_size=r.chunk_size, overlap=2):
+                cw = _lib.make_win(r.get_window_bounds(win), win.width, win.height)
+                poff = win.row_off * r.width + win.col_off
+                ctx.interp(cw, dem.data_ptr() + poff * es, dcode, r.width,
+                           None if mask is None else mask.data_ptr() + poff,
+                           r.width, xy, K, code, touched, vals)
+
+
+class Mesh:
+    """Factory (``ocsmesh/mesh/mesh.py:574-600``)."""
+
+    def __new__(cls, mesh: MeshData):
+        if not isinstance(mesh, MeshData):
+            raise TypeError(f'Argument mesh must be of type {MeshData}, '
+                            f'not type {type(mesh)}.')
+        return EuclideanMesh2D(mesh)

@@ -1,0 +1,122 @@
+"""K2 parity: ocsb_hfun_flow_limiter vs the numpy oracle
+(reference ocsmesh/hfun/raster.py:1396-1435)."""
+import itertools
+
+import numpy as np
+import pytest
+
+from oracle import ocsmesh_oracle as O
+from ocsmesh_b200 import _lib, synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+FLT_MAX = np.finfo(np.float32).max
+
+
+def run_gpu(ctx, z, old, dx, dy, hmin, hmax, lb, ub, ghmin, ghmax, band=(0, 0),
+            device=True, fuse=False):
+    import torch
+    h, w = z.shape
+    win = _lib.make_win((0.0, 0.0, float(w), float(h)), w, h, band[0], band[1])
+    code = _lib.OCSB_F32 if z.dtype == np.float32 else _lib.OCSB_F64
+    if device:
+        zd = torch.from_numpy(z).cuda()
+        od = torch.from_numpy(old).cuda()
+        nd = od.clone()
+        ctx.hfun_flow_limiter(win, zd, code, w, od, w, nd, w, dx, dy, hmin,
+                              hmax, lb, ub, ghmin, ghmax, fuse)
+        ctx.sync()
+        return nd.cpu().numpy()
+    new = old.copy()
+    ctx.hfun_flow_limiter(win, z, code, w, old, w, new, w, dx, dy, hmin, hmax,
+                          lb, ub, ghmin, ghmax, fuse)
+    return new
+
+
+def check(out, ref):
+    # sizes within 1e-5 relative in fp32 (BASELINE.json north_star); the
+    # kernel follows numpy's operation order so it is in fact bit-exact
+    ref = np.ma.getdata(ref)
+    assert out.dtype == np.float32
+    np.testing.assert_array_equal(out, ref)
+
+
+@pytest.mark.parametrize("shape", [(2, 2), (3, 5), (64, 128), (257, 515), (33, 1000)])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_shapes_dtypes(ctx, shape, dtype):
+    rng = np.random.default_rng(3)
+    z = (rng.normal(size=shape) * 20).astype(dtype)
+    old = np.full(shape, FLT_MAX, np.float32)
+    old[rng.random(shape) < 0.3] = 700.0
+    ref = O.flow_limiter_window(z, old, 10.0, 12.5, 50.0, 1500.0, -30.0, 0.0,
+                                100.0, 1500.0)
+    out = run_gpu(ctx, z, old, 10.0, 12.5, 50.0, 1500.0, -30.0, 0.0, 100.0, 1500.0)
+    check(out, ref)
+
+
+def test_all_bound_combinations(ctx):
+    rng = np.random.default_rng(11)
+    z = (rng.normal(size=(96, 200)) * 15).astype(np.float32)
+    z[10:20, 30:60] = 4.0                       # plateau: zero gradient
+    old = (rng.random(z.shape) * 2000 + 1).astype(np.float32)
+    opts = [(None, 50.0), (None, 1500.0), (None, -30.0), (None, 0.0),
+            (None, 100.0), (None, 1200.0)]
+    for hmin, hmax, lb, ub, ghmin, ghmax in itertools.product(*opts):
+        if (hmin is None or hmin <= 1 / 3) and (ghmin is None or ghmin <= 1 / 3):
+            # zero-gradient pixels stay masked in the reference: what rasterio
+            # writes there is outside the oracle -> compare
+            # unmasked pixels only
+            ref = O.flow_limiter_window(z, old, 10.0, 10.0, hmin, hmax, lb, ub,
+                                        ghmin, ghmax)
+            out = run_gpu(ctx, z, old, 10.0, 10.0, hmin, hmax, lb, ub, ghmin, ghmax)
+            m = np.ma.getmaskarray(ref)
+            np.testing.assert_array_equal(out[~m], np.ma.getdata(ref)[~m])
+            continue
+        ref = O.flow_limiter_window(z, old, 10.0, 10.0, hmin, hmax, lb, ub,
+                                    ghmin, ghmax)
+        out = run_gpu(ctx, z, old, 10.0, 10.0, hmin, hmax, lb, ub, ghmin, ghmax)
+        check(out, ref)
+
+
+def test_plateau_gives_hmin(ctx):
+    z = np.full((40, 70), -5.0, np.float32)
+    old = np.full(z.shape, FLT_MAX, np.float32)
+    out = run_gpu(ctx, z, old, 10.0, 10.0, 50.0, 1500.0, None, None, 100.0, 1500.0)
+    assert np.all(out == 100.0)   # raw 1/3 -> hmin 50 -> global hmin 100
+
+
+def test_host_buffers_and_bands(ctx):
+    z = S.synth_dem(300, 421, seed=4)
+    old = np.full(z.shape, FLT_MAX, np.float32)
+    ref = np.ma.getdata(O.flow_limiter_window(z, old, 10.0, 10.0, 50.0, 1500.0,
+                                              -30.0, 0.0, 100.0, 1500.0))
+    out = run_gpu(ctx, z, old, 10.0, 10.0, 50.0, 1500.0, -30.0, 0.0, 100.0,
+                  1500.0, device=False)
+    np.testing.assert_array_equal(out, ref)
+    # row bands (device tiles inside one semantic window) == one call
+    for device in (True, False):
+        acc = old.copy()
+        for rb, re in [(0, 1), (1, 97), (97, 299), (299, 300)]:
+            part = run_gpu(ctx, z, old, 10.0, 10.0, 50.0, 1500.0, -30.0, 0.0,
+                           100.0, 1500.0, band=(rb, re), device=device)
+            assert np.array_equal(part[:rb], old[:rb]) and np.array_equal(part[re:], old[re:])
+            acc[rb:re] = part[rb:re]
+        np.testing.assert_array_equal(acc, ref)
+
+
+def test_fused_clamp_equals_clamp_pass(ctx):
+    z = S.synth_dem(128, 256, seed=9)
+    old = np.full(z.shape, FLT_MAX, np.float32)
+    ref = np.ma.getdata(O.flow_limiter_window(z, old, 10.0, 10.0, None, None,
+                                              -30.0, 0.0, 100.0, 1500.0))
+    ref = O.apply_constraints_clamp(ref, 100.0, 1500.0)
+    out = run_gpu(ctx, z, old, 10.0, 10.0, None, None, -30.0, 0.0, 100.0, 1500.0,
+                  fuse=True)
+    np.testing.assert_array_equal(out, ref)
+
+
+def test_errors(ctx):
+    z = np.zeros((1, 8), np.float32)
+    with pytest.raises(_lib.OcsbError):
+        run_gpu(ctx, z, z.copy(), 1.0, 1.0, None, None, None, None, None, None,
+                device=False)
