@@ -88,10 +88,11 @@ def test_distance_index_and_size(ctx, shape, seed, hmax):
 def test_bounded_equals_unbounded_after_clamp(ctx):
     r, pts = make_case(300, 400, 7)
     old = np.full((300, 400), FLT_MAX, np.float32)
-    a = run_gpu(ctx, r, pts, old, 0.002, 50.0, 50.0, 300.0)
+    # r = (300 - 50) / (0.05 * 50) = 100 m: most pixels are beyond the radius
+    a = run_gpu(ctx, r, pts, old, 0.05, 50.0, 50.0, 300.0)
     win = r.full_window()
     xy = r.get_xy(win)
-    ref = O.add_feature_window(old, pts, xy, 300, 400, 0.002, 50.0, 50.0, 300.0)
+    ref = O.add_feature_window(old, pts, xy, 300, 400, 0.05, 50.0, 50.0, 300.0)
     np.testing.assert_array_equal(a, ref)
     assert a.max() == 300.0 and a.min() >= 50.0
 
