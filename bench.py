@@ -1,0 +1,520 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the raster hot path (BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Workload (BASELINE.json configs[1], per GPU): synthetic 20000 x 20000 float32
+DEM (10 m pixels, projected CRS), one "step" = one full HfunRaster pass:
+FLT_MAX init fill + add_contour at 3 levels (-5, 0, 5; expansion_rate 0.001,
+target_size 100, hmin 100, hmax 1500) + add_gradient_delimiter (hmin 50, hmax
+1500).  The contour polylines are traced and resampled once on the host before
+the timed region: the accelerated path starts at the resampled vertex array
+(reference ocsmesh/hfun/raster.py:1230), contour tracing is the CPU step
+before it.
+
+  value : Mpx/s, whole job, DEM + vertices + hfun resident in HBM
+  e2e   : Mpx/s through the public API (ocsmesh_b200.Raster / Hfun) with HOST
+          buffers: DEM and vertices H2D from pinned memory and the size raster
+          D2H inside the timed region
+  secondary.interp : Mesh.interpolate of a 10 M-node cloud from 16 DEM tiles
+          (BASELINE.json configs[3]) in Mnodes/s, linear and nearest
+
+N > 1 (weak scaling): the raster is N x 20000 rows tall, each rank owns one
+20000-row band (one semantic window = the whole raster, so coordinates and
+radius law are global); per step the ranks all-gather their contour vertices
+and exchange 1-row DEM halos over NCCL, then run the same kernels on their band.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LEVELS = [-5.0, 0.0, 5.0]
+RATE, TARGET, HMIN, HMAX = 0.001, 100.0, 100.0, 1500.0
+LIM_HMIN, LIM_HMAX = 50.0, 1500.0
+SEED = 2
+BYTES_PER_PX = {"feature_eval": 8.0, "flow_limiter": 12.0, "fill": 4.0,
+                "clamp": 8.0}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=20000,
+                    help="DEM rows per GPU and columns")
+    ap.add_argument("--nodes", type=int, default=10_000_000)
+    ap.add_argument("--tile", type=int, default=5000, help="interp DEM tile size")
+    ap.add_argument("--cpu-sample", type=int, default=3000,
+                    help="edge of the square crop timed on the CPU")
+    ap.add_argument("--no-interp", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------
+def host_dem(height, width, seed, rows=None, pin=True, full_height=None):
+    """Synthetic DEM block in (pinned) host memory."""
+    import torch
+    from ocsmesh_b200 import synthetic as S
+    r0, r1 = (0, height) if rows is None else rows
+    t = torch.empty((r1 - r0, width), dtype=torch.float32)
+    if pin and torch.cuda.is_available():
+        t = t.pin_memory()
+    a = t.numpy()
+    blk = 2000
+    for s in range(r0, r1, blk):
+        e = min(r1, s + blk)
+        a[s - r0:e - r0] = S.synth_dem(full_height or height, width, seed=seed,
+                                       rows=(s, e))
+    return t
+
+
+def contour_points(z, transform, row0=0):
+    """Contours at LEVELS of the DEM block z (whose first row is raster row
+    row0), resampled to TARGET spacing: the (N, 2) vertex array."""
+    from ocsmesh_b200 import features as F
+    h, w = z.shape
+    a, _, c, _, e, f = transform
+    # the coordinates Raster.get_x / get_y give for a whole-raster window
+    # restricted to these rows are only needed to place the crossings: use
+    # pixel-centre style linspace over the block's edge bounds like get_x/get_y
+    x = np.linspace(c, c + a * w, w)
+    y = np.linspace(f + e * row0, f + e * (row0 + h), h)
+    lines = []
+    for lv in LEVELS:
+        lines.extend(F.marching_squares(x, y, z, lv))
+    return F.feature_points(lines, TARGET)
+
+
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,"
+             "clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}",
+                 "--format=csv,noheader,nounits", "-lms", "50", "-i",
+                 str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.06] or \
+               [l for (_, l) in self.lines]
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                 "sw_power_cap"]
+        for l in rows:
+            p = [v.strip() for v in l.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                smax = float(p[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the oracle restatement on the host cores
+# ---------------------------------------------------------------------------
+def cpu_hfun_sample(z, transform, points, sample, repeats=1):
+    """Time the oracle's full pass on the top-left sample x sample crop.
+    Returns (Mpx/s, seconds per pass, cores)."""
+    from oracle import ocsmesh_oracle as O
+    n = min(sample, z.shape[0], z.shape[1])
+    crop = np.ascontiguousarray(z[:n, :n])
+    r = O.OracleRaster(crop, transform)
+    cores = os.cpu_count() or 1
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        oh = O.OracleHfun(r, hmin=HMIN, hmax=HMAX)
+        oh.add_feature_points(points, RATE, TARGET, workers=-1)
+        oh._clamp_pass()  # add_contour's outer decorator layer
+        oh.add_subtidal_flow_limiter(LIM_HMIN, LIM_HMAX, None, None)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return n * n / best / 1e6, best, cores, oh.values
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle port) on the host
+    cores; under torchrun rank 0 alone runs it."""
+    if rank != 0:
+        return
+    size = args.size
+    from ocsmesh_b200 import synthetic as S
+    tr = S.dem_transform(size * world)
+    n = min(args.cpu_sample, size)
+    # the sample is the top-left n x n crop of rank 0's band; contours come
+    # from a (n + 2000)-row strip so the crop sees realistic vertex density
+    strip = min(size, n + 2000)
+    z = host_dem(size * world, size, SEED, rows=(0, strip), pin=False).numpy()
+    pts = contour_points(z, tr)
+    times = []
+    for i in range(args.warmup + args.steps):
+        mpx, dt, cores, _ = cpu_hfun_sample(z, tr, pts, n)
+        if i >= args.warmup:
+            times.append(dt)
+    t = float(np.mean(times))
+    val = n * n / t / 1e6
+    line = {
+        "impl": "reference", "metric": "hfun_raster_pass_throughput",
+        "value": val, "unit": "Mpx/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 distance / f32 size",
+        "data": "synthetic",
+        "config": workload_config(args, world, sample=f"{n}x{n} crop"),
+        "cpu_baseline": {"value": val, "unit": "Mpx/s", "cores": cores,
+                         "kind": "port",
+                         "sample": f"top-left {n}x{n} crop of the DEM, "
+                                   f"{len(pts)} contour vertices of a "
+                                   f"{strip}-row strip, scipy cKDTree workers=-1"},
+        "e2e": {"value": val, "unit": "Mpx/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world, sample=None):
+    cfg = {
+        "workload": (f"BASELINE.json configs[1]: synthetic {args.size * world}x"
+                     f"{args.size} f32 DEM ({args.size} rows per GPU), "
+                     "HfunRaster full pass = init fill + add_contour(levels "
+                     f"{LEVELS}, rate {RATE}, target {TARGET}, hmin {HMIN}, "
+                     f"hmax {HMAX}) + add_gradient_delimiter(hmin {LIM_HMIN}, "
+                     f"hmax {LIM_HMAX})"),
+        "px_per_gpu": args.size * args.size,
+        "parallelism": f"row bands x{world}",
+        "l2": "inputs (DEM + hfun, 3.2 GB per GPU) exceed the 126 MB L2",
+        "contours": "traced + resampled on the host once, outside the timed "
+                    "region (parity boundary hfun/raster.py:1230)",
+    }
+    if sample:
+        cfg["sample"] = sample
+    return cfg
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import ocsmesh_b200 as ob
+    from ocsmesh_b200 import _lib, synthetic as S, distributed as D
+
+    torch.cuda.set_device(local_rank)
+    dev = local_rank
+    ctx = _lib.default_context(dev)
+    size, W = args.size, args.size
+    H = size * world
+    tr = S.dem_transform(H)
+    r0, r1 = rank * size, (rank + 1) * size
+
+    # ---- inputs (outside the timed region) --------------------------------
+    z_host = host_dem(H, W, SEED, rows=(r0, r1), full_height=H)
+    pts_local = contour_points(z_host.numpy(), tr, row0=r0)
+    pts_pinned = torch.from_numpy(pts_local).pin_memory()
+
+    part = D.RowBands(H, world)
+    raster = D.band_raster(z_host.numpy(), tr, H, part, rank, crs=32618,
+                           device=dev)
+    hfun = ob.HfunRaster(raster, hmin=HMIN, hmax=HMAX, device=dev,
+                         row_band=part.band(rank))
+    verts_local = pts_pinned.to(f"cuda:{dev}")
+
+    def step():
+        # A4 init fill, vertex all-gather, DEM halo rows, A6/A7, A8(A9)
+        hfun.reset()
+        verts = D.all_gather_vertices(verts_local) if world > 1 else verts_local
+        if world > 1:
+            D.exchange_dem_halo(raster, part, rank, dev)
+        hfun.add_feature_points(verts, RATE, TARGET)
+        hfun.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- timed: device-resident -------------------------------------------
+    sampler = ClockSampler(dev)
+    sampler.start()
+    time.sleep(0.15)
+    ctx.reset_timing()
+    ctx.set_timing(True)
+    launches0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    t1 = time.perf_counter()
+    ctx.set_timing(False)
+    clocks = sampler.stop(t0, t1)
+    ms_total = e0.elapsed_time(e1)
+    launches = ctx.launch_count - launches0
+    ktimes = ctx.get_timing()
+    if world > 1:
+        tt = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    px_total = float(H) * W
+    value = px_total / (ms_step * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel -----------------------------------
+    peak, peak_src = measured_peaks()
+    dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else None
+    roofline = None
+    if dom is not None:
+        ms, n = ktimes[dom]
+        avg = ms / n
+        bpp = BYTES_PER_PX.get(dom, 8.0)
+        bytes_launch = bpp * size * W * (args.steps / n) if n else 0.0
+        ach = bytes_launch / (avg * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak,
+                    "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "peak_source": peak_src,
+                    "algorithmic_bytes_per_px": bpp,
+                    "avg_launch_ms": avg,
+                    "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
+                    "kernel_roofline_frac": {
+                        k: (BYTES_PER_PX[k] * size * W / (v[0] / args.steps * 1e-3) / 1e9 / peak)
+                        for k, v in ktimes.items() if k in BYTES_PER_PX}}
+
+    # ---- e2e: public API, host buffers -------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        out_pinned = torch.empty((size, W), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            r = D.band_raster(z_host.numpy(), tr, H, part, rank, crs=32618,
+                              device=dev)            # DEM H2D
+            h = ob.HfunRaster(r, hmin=HMIN, hmax=HMAX, device=dev,
+                              row_band=part.band(rank))
+            v = pts_pinned.to(f"cuda:{dev}", non_blocking=True)   # vertices H2D
+            if world > 1:
+                v = D.all_gather_vertices(v)
+                D.exchange_dem_halo(r, part, rank, dev)
+            h.add_feature_points(v, RATE, TARGET)
+            h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+            h.get_values(out=out_pinned)             # hfun D2H
+            return float(out_pinned[0, 0])
+
+        e2e_steps = max(2, min(args.steps, 5))
+        e2e_step()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        a1.record()
+        barrier()
+        ems = a0.elapsed_time(a1)
+        if world > 1:
+            tt = torch.tensor([ems], dtype=torch.float64, device=f"cuda:{dev}")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ems = float(tt.item())
+        e2e = {"value": px_total / (ems / e2e_steps * 1e-3) / 1e6, "unit": "Mpx/s",
+               "h2d_bytes_per_step": int(z_host.numel() * 4 + pts_pinned.numel() * 8),
+               "d2h_bytes_per_step": int(out_pinned.numel() * 4),
+               "steps": e2e_steps, "ms_per_step": ems / e2e_steps}
+        del out_pinned
+
+    # ---- secondary: Mesh.interpolate ---------------------------------------
+    secondary = {}
+    if not args.no_interp:
+        secondary["interp"] = bench_interp(args, rank, world, dev, ctx, peak)
+
+    # ---- CPU baseline (rank 0, N == 1) --------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        n = min(args.cpu_sample, size)
+        mpx, dt, cores, ref_vals = cpu_hfun_sample(z_host.numpy(), tr, pts_local, n)
+        # the GPU result on the same crop is NOT comparable pixel-for-pixel (a
+        # crop is its own semantic window), so this leg only times the oracle
+        cpu = {"value": mpx, "unit": "Mpx/s", "cores": cores, "kind": "port",
+               "sample": f"top-left {n}x{n} crop of the DEM with the full "
+                         f"{len(pts_local)}-vertex contour set, one pass "
+                         f"({dt:.2f} s), scipy cKDTree workers=-1"}
+
+    if rank == 0:
+        line = {
+            "metric": "hfun_raster_pass_throughput", "value": value,
+            "unit": "Mpx/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 distance / f32 size", "data": "synthetic",
+            "config": workload_config(args, world),
+            "n_vertices": int(len(pts_local)),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(launches), "clocks": clocks,
+            "secondary": secondary,
+        }
+        print(json.dumps(line), flush=True)
+
+
+def bench_interp(args, rank, world, dev, ctx, peak):
+    """BASELINE.json configs[3]: 10 M nodes x 16 DEM tiles, linear + nearest.
+    Nodes are sharded over ranks (contiguous chunks), tiles replicated."""
+    import torch
+    import torch.distributed as dist
+    import ocsmesh_b200 as ob
+    from ocsmesh_b200 import synthetic as S
+    from ocsmesh_b200.mesh import EuclideanMesh2D
+    T, ovl, grid = args.tile, 100, 4
+    rasters = []
+    for k in range(grid * grid):
+        ty, tx = divmod(k, grid)
+        z = S.synth_dem(T, T, seed=20 + k)
+        tr = list(S.dem_transform(T))
+        tr[2] += (T - ovl) * S.PIXEL * tx
+        tr[5] += (T - ovl) * S.PIXEL * ty
+        r = ob.Raster.from_numpy(z, tr, crs=32618)
+        r.device_band(1, dev)
+        rasters.append(r)
+    ext = ((T - ovl) * (grid - 1) + T) * S.PIXEL
+    bbox = (S.X0, S.Y0, S.X0 + ext, S.Y0 + ext)
+    K = args.nodes * world        # weak scaling: nodes per GPU fixed
+    k0, k1 = rank * args.nodes, (rank + 1) * args.nodes
+    xy_host = torch.from_numpy(S.synth_nodes(K, bbox, seed=400, outside_frac=0.02)[k0:k1].copy()).pin_memory()
+    n = k1 - k0
+    xy = xy_host.to(f"cuda:{dev}")
+    vals = torch.full((n,), float("nan"), dtype=torch.float64, device=f"cuda:{dev}")
+    touched = torch.zeros(n, dtype=torch.uint8, device=f"cuda:{dev}")
+    out = {}
+    steps = max(3, min(args.steps, 10))
+    for method, bpn in (("linear", 40.0), ("nearest", 28.0)):
+        for _ in range(3):
+            EuclideanMesh2D._interp_device(ctx, rasters, xy, vals, touched, method, 1, dev)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            EuclideanMesh2D._interp_device(ctx, rasters, xy, vals, touched, method, 1, dev)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / steps
+        # e2e: coords H2D + values D2H through Mesh.interpolate
+        vh = torch.empty(n, dtype=torch.float64).pin_memory()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(2):
+            x2 = xy_host.to(f"cuda:{dev}", non_blocking=True)
+            v2 = torch.full((n,), float("nan"), dtype=torch.float64, device=f"cuda:{dev}")
+            t2 = torch.zeros(n, dtype=torch.uint8, device=f"cuda:{dev}")
+            EuclideanMesh2D._interp_device(ctx, rasters, x2, v2, t2, method, 1, dev)
+            vh.copy_(v2)
+        a1.record()
+        torch.cuda.synchronize(dev)
+        ems = a0.elapsed_time(a1) / 2
+        if world > 1:
+            tt = torch.tensor([ms, ems], dtype=torch.float64, device=f"cuda:{dev}")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms, ems = float(tt[0]), float(tt[1])
+        # one launch per tile scans all nodes: algorithmic bytes count the
+        # coordinates once per tile launch + texels/values per touched node
+        ach = (bpn * n) / (ms * 1e-3) / 1e9
+        out[method] = {"Mnodes_per_s": K / (ms * 1e-3) / 1e6, "ms_per_step": ms,
+                       "e2e_Mnodes_per_s": K / (ems * 1e-3) / 1e6,
+                       "roofline_frac": ach / peak,
+                       "algorithmic_bytes_per_node": bpn}
+    out["config"] = (f"BASELINE.json configs[3]: {K} nodes ({args.nodes}/GPU), "
+                     f"16 tiles {T}x{T} (4x4, {ovl}-px overlap), last wins")
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU "
+                         "fallback (use --impl reference for the CPU arm)")
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

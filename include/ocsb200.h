@@ -97,6 +97,28 @@ int64_t ocsb_ctx_launch_count(const ocsb_ctx *ctx);
 /* release cached device scratch */
 int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 
+/* Per-kernel-class device timing (CUDA events recorded on the context's
+ * stream around every launch of the class while enabled).  get_timing
+ * synchronises the stream, returns the summed duration and the launch count
+ * of `kclass` since the last reset; reset_timing drops all records.          */
+#define OCSB_KC_FILL              0
+#define OCSB_KC_CLAMP             1
+#define OCSB_KC_MIN_COMBINE       2
+#define OCSB_KC_COORDS            3
+#define OCSB_KC_LIMITER           4
+#define OCSB_KC_FEATURE_REFINE    5
+#define OCSB_KC_FEATURE_EVAL      6
+#define OCSB_KC_INTERP            7
+#define OCSB_KC_SPLINE_PREFILTER  8
+#define OCSB_KC_SPLINE_EVAL       9
+#define OCSB_KC_NEAREST          10
+#define OCSB_KC_COUNT            11
+int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
+int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
+                                int64_t *launches);
+int32_t     ocsb_ctx_reset_timing(ocsb_ctx *ctx);
+const char *ocsb_kernel_class_name(int32_t kclass);
+
 /* ---- A1: window list ------------------------------------------------------
  * get_iter_windows(width, height, chunk_size, overlap)   ocsmesh/raster.py:1891-1939
  * Raster.iter_windows (chunk_size in [0, None, False] -> one full window)

@@ -20,6 +20,7 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
+KC_COUNT = 11
 NONE = float("nan")
 
 c_i32, c_i64, c_f64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_double, C.c_float, C.c_void_p
@@ -48,6 +49,11 @@ SIGNATURES = {
     "ocsb_ctx_sync": (c_i32, [c_vp]),
     "ocsb_ctx_launch_count": (c_i64, [c_vp]),
     "ocsb_ctx_trim": (c_i32, [c_vp]),
+    "ocsb_ctx_set_timing": (c_i32, [c_vp, c_i32]),
+    "ocsb_ctx_get_timing": (c_i32, [c_vp, c_i32, C.POINTER(c_f64),
+                                    C.POINTER(c_i64)]),
+    "ocsb_ctx_reset_timing": (c_i32, [c_vp]),
+    "ocsb_kernel_class_name": (C.c_char_p, [c_i32]),
     "ocsb_windows": (c_i32, [c_i32, c_i32, c_i32, c_i32, c_vp, c_i64,
                              C.POINTER(c_i64)]),
     "ocsb_window_coords": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_vp]),
@@ -170,6 +176,24 @@ class Context:
 
     def trim(self):
         check(self.lib.ocsb_ctx_trim(self.handle))
+
+    def set_timing(self, enabled: bool):
+        check(self.lib.ocsb_ctx_set_timing(self.handle, int(bool(enabled))))
+
+    def reset_timing(self):
+        check(self.lib.ocsb_ctx_reset_timing(self.handle))
+
+    def get_timing(self) -> dict:
+        """{kernel class name: (total_ms, launches)} since the last reset."""
+        out = {}
+        for kc in range(KC_COUNT):
+            ms, n = c_f64(0.0), c_i64(0)
+            check(self.lib.ocsb_ctx_get_timing(self.handle, kc, C.byref(ms),
+                                               C.byref(n)))
+            if n.value:
+                name = self.lib.ocsb_kernel_class_name(kc).decode()
+                out[name] = (ms.value, n.value)
+        return out
 
     # ---- thin typed wrappers (buffers: numpy arrays or torch tensors) ------
     def window_coords(self, win: ocsb_win, x_out, y_out):

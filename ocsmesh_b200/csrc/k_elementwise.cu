@@ -99,6 +99,7 @@ inline int vec_ok2d(const void *p, int64_t stride) {
 }  // namespace
 
 int32_t k_fill_f32(ocsb_ctx *ctx, float *dst, int64_t n, float v) {
+    OCSB_TIME(ctx, KC_FILL);
     fill_kernel<<<grid_for(ctx, n / 4 + 1), kThreads, 0, ctx->stream>>>(dst, n, v);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
@@ -110,6 +111,7 @@ int32_t k_clamp(ocsb_ctx *ctx, float *hfun, int64_t stride, int w, int h,
     int has_lo = !ocsb_is_none(hmin), has_hi = !ocsb_is_none(hmax);
     if (!has_lo && !has_hi) return OCSB_OK;
     int64_t items = (int64_t)((w + 3) / 4) * h;
+    OCSB_TIME(ctx, KC_CLAMP);
     clamp_kernel<<<grid_for(ctx, items), kThreads, 0, ctx->stream>>>(
         hfun, stride, w, h, has_lo, (float)hmin, has_hi, (float)hmax,
         vec_ok2d(hfun, stride));
@@ -121,6 +123,7 @@ int32_t k_clamp(ocsb_ctx *ctx, float *hfun, int64_t stride, int w, int h,
 int32_t k_min_combine(ocsb_ctx *ctx, float *dst, int64_t dstride,
                       const float *src, int64_t sstride, int w, int h) {
     int64_t items = (int64_t)((w + 3) / 4) * h;
+    OCSB_TIME(ctx, KC_MIN_COMBINE);
     min_kernel<<<grid_for(ctx, items), kThreads, 0, ctx->stream>>>(
         dst, dstride, src, sstride, w, h,
         vec_ok2d(dst, dstride) && vec_ok2d(src, sstride));
@@ -131,6 +134,7 @@ int32_t k_min_combine(ocsb_ctx *ctx, float *dst, int64_t dstride,
 
 int32_t k_coords(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, double *x, double *y) {
     int n = ax.n > ay.n ? ax.n : ay.n;
+    OCSB_TIME(ctx, KC_COORDS);
     coords_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ax, ay, x, y);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();

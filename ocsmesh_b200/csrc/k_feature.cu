@@ -619,6 +619,7 @@ struct LevelHost {
 
 template <int BT>
 void launch_fused(ocsb_ctx *ctx, const RefineArgs &A, int64_t ntiles) {
+    OCSB_TIME(ctx, KC_FEATURE_REFINE);
     refine_fused_kernel<BT><<<(unsigned)ntiles, BT, 0, ctx->stream>>>(A);
     OCSB_LAUNCHED(ctx);
 }
@@ -721,13 +722,17 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
                 OCSB_TRY(pools.get(&S.part, (size_t)ntiles * nsplit * 5));
                 OCSB_TRY(pools.get(&S.counts, (size_t)ntiles * nsplit));
                 const unsigned gridn = (unsigned)(ntiles * nsplit);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 split_p1_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
                 OCSB_LAUNCHED(ctx);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 split_p2_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
                 OCSB_LAUNCHED(ctx);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 split_p3_kernel<<<(unsigned)((ntiles + 127) / 128), 128, 0,
                                   ctx->stream>>>(A, S, (int)ntiles);
                 OCSB_LAUNCHED(ctx);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 split_p4_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
                 OCSB_LAUNCHED(ctx);
             } else if (i == 0) {
@@ -755,6 +760,7 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         E.vec_old = (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
         E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
         E.overflow = overflow;
+        OCSB_TIME(ctx, KC_FEATURE_EVAL);
         if (idx_out)
             eval_kernel<true><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
         else

@@ -140,6 +140,7 @@ int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
     interp_kernel<T, M><<<(unsigned)blocks, 256, 0, ctx->stream>>>(            \
         gx, gy, xmin, xmax, ymin, ymax, (const T *)dem, dem_stride, mask,      \
         mask_stride, q, K, touched, values)
+    OCSB_TIME(ctx, KC_INTERP);
     if (dem_dtype == OCSB_F32) {
         if (method == OCSB_INTERP_NEAREST) LAUNCH(float, OCSB_INTERP_NEAREST);
         else LAUNCH(float, OCSB_INTERP_LINEAR);

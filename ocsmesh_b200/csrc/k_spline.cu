@@ -253,6 +253,7 @@ int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
     // (ny, nx): element (j, c) = coef[j*nx + c] (c = pixel column)
     {
         const int blocks = (nx + 127) / 128;
+        OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
         if (dem_dtype == OCSB_F32)
             solve_lines_kernel<float><<<blocks, 128, 0, ctx->stream>>>(
                 (const float *)dem, dem_stride, gy.flip, coef, ny, nx, luy);
@@ -265,6 +266,7 @@ int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
     // transpose (ny, nx) -> tmp (nx, ny): tmp[c*ny + j]
     {
         dim3 grid((nx + 31) / 32, (ny + 31) / 32);
+        OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
         transpose_kernel<<<grid, 256, 0, ctx->stream>>>(coef, tmp, ny, nx);
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
@@ -272,6 +274,7 @@ int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
     // pass B: along x (ascending) for every j; source row = pixel column
     {
         const int blocks = (ny + 127) / 128;
+        OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
         solve_lines_kernel<double><<<blocks, 128, 0, ctx->stream>>>(
             tmp, ny, gx.flip, coef, nx, ny, lux);
         OCSB_LAUNCHED(ctx);
@@ -289,6 +292,7 @@ int32_t k_spline_eval(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const double *coef,
     int64_t blocks = (K + 255) / 256;
     int64_t cap = (int64_t)ctx->num_sms * 16;
     if (blocks > cap) blocks = cap;
+    OCSB_TIME(ctx, KC_SPLINE_EVAL);
     spline_eval_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(
         gx, gy, fmin(x_a, x_b), fmax(x_a, x_b), fmin(y_a, y_b), fmax(y_a, y_b),
         coef, reinterpret_cast<const double2 *>(xy), K, touched, values);

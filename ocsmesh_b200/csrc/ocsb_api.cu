@@ -170,6 +170,11 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->spl_coef) cudaFree(ctx->spl_coef);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto &r : ctx->time_recs) {
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    for (auto e : ctx->event_pool) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return OCSB_OK;
@@ -194,6 +199,81 @@ extern "C" int32_t ocsb_ctx_sync(ocsb_ctx *ctx) {
 
 extern "C" int64_t ocsb_ctx_launch_count(const ocsb_ctx *ctx) {
     return ctx ? ctx->launches : 0;
+}
+
+// ---------------------------------------------------------------------------
+// per-kernel-class timing
+// ---------------------------------------------------------------------------
+static cudaEvent_t take_event(ocsb_ctx *ctx) {
+    if (!ctx->event_pool.empty()) {
+        cudaEvent_t e = ctx->event_pool.back();
+        ctx->event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+void ocsb_time_begin(ocsb_ctx *ctx, int kclass) {
+    KTimeRec r;
+    r.kclass = kclass;
+    r.a = take_event(ctx);
+    r.b = take_event(ctx);
+    cudaEventRecord(r.a, ctx->stream);
+    ctx->time_recs.push_back(r);
+    ctx->time_open = true;
+}
+
+void ocsb_time_end(ocsb_ctx *ctx) {
+    cudaEventRecord(ctx->time_recs.back().b, ctx->stream);
+    ctx->time_open = false;
+}
+
+extern "C" int32_t ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    ctx->timing = enabled != 0;
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_ctx_reset_timing(ocsb_ctx *ctx) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (auto &r : ctx->time_recs) {
+        ctx->event_pool.push_back(r.a);
+        ctx->event_pool.push_back(r.b);
+    }
+    ctx->time_recs.clear();
+    ctx->time_open = false;
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass,
+                                       double *total_ms, int64_t *launches) {
+    OCSB_REQUIRE(ctx, "ctx is NULL");
+    OCSB_REQUIRE(kclass >= 0 && kclass < OCSB_KC_COUNT, "bad kernel class %d",
+                 kclass);
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    double sum = 0.0;
+    int64_t n = 0;
+    for (auto &r : ctx->time_recs) {
+        if (r.kclass != kclass) continue;
+        float ms = 0.f;
+        OCSB_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+        sum += ms;
+        ++n;
+    }
+    if (total_ms) *total_ms = sum;
+    if (launches) *launches = n;
+    return OCSB_OK;
+}
+
+extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
+    static const char *names[OCSB_KC_COUNT] = {
+        "fill", "clamp", "min_combine", "coords", "flow_limiter",
+        "feature_refine", "feature_eval", "interp", "spline_prefilter",
+        "spline_eval", "nearest_vertex"};
+    return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
 extern "C" int32_t ocsb_ctx_trim(ocsb_ctx *ctx) {

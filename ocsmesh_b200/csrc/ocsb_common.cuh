@@ -11,6 +11,15 @@
 
 #include "ocsb200.h"
 
+enum {
+    KC_FILL = OCSB_KC_FILL, KC_CLAMP = OCSB_KC_CLAMP,
+    KC_MIN_COMBINE = OCSB_KC_MIN_COMBINE, KC_COORDS = OCSB_KC_COORDS,
+    KC_LIMITER = OCSB_KC_LIMITER, KC_FEATURE_REFINE = OCSB_KC_FEATURE_REFINE,
+    KC_FEATURE_EVAL = OCSB_KC_FEATURE_EVAL, KC_INTERP = OCSB_KC_INTERP,
+    KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
+    KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST
+};
+
 // ---------------------------------------------------------------------------
 // error plumbing
 // ---------------------------------------------------------------------------
@@ -43,12 +52,21 @@ void ocsb_set_error(const char *fmt, ...);
 // ---------------------------------------------------------------------------
 // context
 // ---------------------------------------------------------------------------
+struct KTimeRec {
+    int kclass;
+    cudaEvent_t a, b;
+};
 struct ocsb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     int num_sms = 148;
     int64_t launches = 0;
+    // per-kernel-class CUDA-event timing (off unless ocsb_ctx_set_timing)
+    bool timing = false;
+    bool time_open = false;
+    std::vector<KTimeRec> time_recs;
+    std::vector<cudaEvent_t> event_pool;
     // pinned bounce buffer for small D2H reads (flags, counters)
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
@@ -159,8 +177,19 @@ struct Staged {
     ~Staged();
 };
 
-// kernel launch accounting
-#define OCSB_LAUNCHED(ctx) ((ctx)->launches++)
+// kernel launch accounting: OCSB_TIME(ctx, class) right before a launch,
+// OCSB_LAUNCHED(ctx) right after it
+void ocsb_time_begin(ocsb_ctx *ctx, int kclass);
+void ocsb_time_end(ocsb_ctx *ctx);
+#define OCSB_TIME(ctx, kc)                                                     \
+    do {                                                                       \
+        if ((ctx)->timing) ocsb_time_begin((ctx), (kc));                       \
+    } while (0)
+#define OCSB_LAUNCHED(ctx)                                                     \
+    do {                                                                       \
+        (ctx)->launches++;                                                     \
+        if ((ctx)->time_open) ocsb_time_end((ctx));                            \
+    } while (0)
 #define OCSB_CHECK_LAUNCH()                                                    \
     do {                                                                       \
         cudaError_t e__ = cudaGetLastError();                                  \

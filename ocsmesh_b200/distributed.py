@@ -1,0 +1,166 @@
+"""Multi-GPU plumbing: one process per GPU, ``torch.distributed`` (NCCL over
+NVLink on the GPU box, gloo in the CPU tests).
+
+The raster hot path shards by raster rows:
+
+* **feature / contour distance** -- pixels are independent given the full
+  vertex set: each rank owns a row band of the (single) semantic window and
+  the ranks ``all_gather`` the contour vertices they traced on their own bands
+  (:func:`all_gather_vertices`).
+* **flow limiter / gradient stencil** -- one exchange: a rank needs the DEM row
+  above and below its band (:func:`exchange_dem_halo`, pairwise send/recv of
+  ``W`` floats).  Rows on the border of the *semantic window* get no halo: the
+  kernel switches to numpy's one-sided difference there.
+* **multi-raster min-combine** -- overlap strips are min-reduced
+  (:func:`min_combine_strip`, an ``all_reduce(MIN)`` on the packed strip).
+* **Mesh.interpolate** -- nodes are independent: contiguous node shards,
+  rasters replicated (:func:`node_shard`); results are all-gathered.
+
+Nothing here touches pixel data on the host.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+class RowBands:
+    """Contiguous, near-equal row bands of a raster ``height`` rows tall."""
+
+    def __init__(self, height: int, world: int):
+        if world < 1 or height < world:
+            raise ValueError(f"cannot split {height} rows over {world} ranks")
+        self.height = int(height)
+        self.world = int(world)
+        base, rem = divmod(self.height, self.world)
+        self.starts = [r * base + min(r, rem) for r in range(self.world + 1)]
+
+    def band(self, rank: int) -> Tuple[int, int]:
+        return self.starts[rank], self.starts[rank + 1]
+
+    def stored(self, rank: int) -> Tuple[int, int]:
+        """Rows a rank keeps of the DEM: its band plus one halo row per side
+        (clipped to the raster)."""
+        r0, r1 = self.band(rank)
+        return max(0, r0 - 1), min(self.height, r1 + 1)
+
+    def owner(self, row: int) -> int:
+        for r in range(self.world):
+            if self.starts[r] <= row < self.starts[r + 1]:
+                return r
+        raise IndexError(row)
+
+
+def node_shard(n_nodes: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous node range of a rank for Mesh.interpolate."""
+    base, rem = divmod(int(n_nodes), int(world))
+    k0 = rank * base + min(rank, rem)
+    return k0, k0 + base + (1 if rank < rem else 0)
+
+
+def band_raster(band_values: np.ndarray, transform, full_height: int,
+                part: RowBands, rank: int, crs=None, device: Optional[int] = None):
+    """A ``Raster`` that holds only this rank's band ``band_values`` (rows
+    ``part.band(rank)``) of a raster ``full_height`` rows tall, with its DEM
+    band uploaded to ``device`` into a buffer that has room for the halo rows
+    (filled by :func:`exchange_dem_halo`)."""
+    import torch
+    from .raster import Raster
+    r0, r1 = part.band(rank)
+    if band_values.shape[0] != r1 - r0:
+        raise ValueError("band_values must hold exactly the rank's band rows")
+    r = Raster.from_numpy(band_values, transform, crs=crs, row_origin=r0,
+                          full_height=full_height)
+    if device is not None:
+        s0, s1 = part.stored(rank)
+        w = band_values.shape[1]
+        dtype = torch.float32 if band_values.dtype == np.float32 else torch.float64
+        buf = torch.zeros((s1 - s0, w), dtype=dtype, device=f"cuda:{device}")
+        src = torch.from_numpy(np.ascontiguousarray(band_values))
+        buf[r0 - s0:r1 - s0].copy_(src, non_blocking=True)
+        r.set_device_band(buf, s0, band=1, device=device)
+    return r
+
+
+def exchange_halo_rows(buf, origin: int, part: RowBands, rank: int,
+                       group=None) -> None:
+    """``buf`` holds raster rows ``[origin, origin + len(buf))`` of this rank
+    (its band plus halo slots).  Sends the first / last owned row to the
+    previous / next rank and receives their boundary rows into the halo slots
+    (``W`` elements each; the send/recv pairs are batched in one group)."""
+    import torch.distributed as dist
+    if part.world == 1:
+        return
+    r0, r1 = part.band(rank)
+    ops = []
+    if rank > 0:
+        ops.append(dist.P2POp(dist.isend, buf[r0 - origin], rank - 1, group))
+        ops.append(dist.P2POp(dist.irecv, buf[r0 - 1 - origin], rank - 1, group))
+    if rank < part.world - 1:
+        ops.append(dist.P2POp(dist.isend, buf[r1 - 1 - origin], rank + 1, group))
+        ops.append(dist.P2POp(dist.irecv, buf[r1 - origin], rank + 1, group))
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
+
+
+def exchange_dem_halo(raster, part: RowBands, rank: int, device: Optional[int] = None,
+                      band: int = 1, group=None) -> None:
+    """Fill the halo rows of this rank's device DEM band (see
+    :func:`band_raster`) from its neighbours over NCCL."""
+    import torch
+    if device is None:
+        device = torch.cuda.current_device()
+    exchange_halo_rows(raster.device_band(band, device),
+                       raster.device_band_origin(band, device), part, rank, group)
+
+
+def all_gather_vertices(verts_local, group=None):
+    """All ranks' ``(n_i, 2)`` float64 vertex arrays concatenated in rank
+    order -> ``(sum n_i, 2)`` on every rank (the contour-vertex all-gather).
+    Ragged sizes are handled by padding to the maximum."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    if world == 1:
+        return verts_local
+    n = torch.tensor([verts_local.shape[0]], dtype=torch.int64,
+                     device=verts_local.device)
+    sizes = torch.empty(world, dtype=torch.int64, device=verts_local.device)
+    dist.all_gather_into_tensor(sizes, n, group=group)
+    sizes_h = sizes.tolist()
+    m = max(sizes_h)
+    pad = torch.zeros((m, 2), dtype=verts_local.dtype, device=verts_local.device)
+    pad[:verts_local.shape[0]] = verts_local
+    out = torch.empty((world * m, 2), dtype=verts_local.dtype,
+                      device=verts_local.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    parts = [out[r * m:r * m + sizes_h[r]] for r in range(world)]
+    return torch.cat(parts, dim=0).contiguous()
+
+
+def min_combine_strip(strip, group=None):
+    """Pixel-wise min of a co-registered overlap strip over all ranks of the
+    group, in place (multi-raster combine)."""
+    import torch.distributed as dist
+    dist.all_reduce(strip, op=dist.ReduceOp.MIN, group=group)
+    return strip
+
+
+def all_gather_node_values(values_local, n_nodes: int, group=None):
+    """Concatenate the ranks' contiguous node-value shards (``node_shard``)
+    into the full ``(n_nodes,)`` array on every rank."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    if world == 1:
+        return values_local
+    sizes = [node_shard(n_nodes, world, r) for r in range(world)]
+    m = max(b - a for a, b in sizes)
+    pad = torch.zeros(m, dtype=values_local.dtype, device=values_local.device)
+    pad[:values_local.shape[0]] = values_local
+    out = torch.empty(world * m, dtype=values_local.dtype,
+                      device=values_local.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    return torch.cat([out[r * m:r * m + (b - a)]
+                      for r, (a, b) in enumerate(sizes)]).contiguous()

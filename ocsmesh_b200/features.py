@@ -121,24 +121,16 @@ def feature_points(features: Sequence[np.ndarray], target_size: float,
 # ---------------------------------------------------------------------------
 # contour tracing (CPU step before the accelerated path)
 # ---------------------------------------------------------------------------
-def marching_squares(x, y, z, level) -> List[np.ndarray]:
-    """Iso-lines of ``z`` (``(h, w)``; row ``j`` at ``y[j]``, column ``i`` at
-    ``x[i]``) at ``level`` as stitched polylines.
-
-    The reference obtains these from matplotlib/contourpy + shapely linemerge
-    (``ocsmesh/raster.py:1426-1470``); neither is available here.  Crossings
-    are placed by linear interpolation along cell edges, saddles are resolved
-    with the cell mean, and segments are stitched through shared cell edges.
-    """
+def _ms_block(x, y, z, level, j0, w):
+    """Marching-squares segments of the row block ``z`` (rows j0 .. j0+hb-1 of
+    a raster ``w`` wide).  Returns the two edge-id arrays of the segments and
+    the (id, px, py) crossing table; ids are global: horizontal edge
+    (j, i)-(j, i+1) -> j*(w-1)+i, vertical edge (j, i)-(j+1, i) ->
+    n_he_total + j*w + i (the caller adds n_he_total, here left symbolic by
+    a negative encoding: vertical ids are returned as -(j*w+i) - 1)."""
     z = np.asarray(z, dtype=float)
-    x = np.asarray(x, dtype=float)
-    y = np.asarray(y, dtype=float)
-    h, w = z.shape
-    if h < 2 or w < 2:
-        return []
+    hb = z.shape[0]
     above = z > level
-    n_he = h * (w - 1)
-
     # corner bits: 1 = (j,i), 2 = (j,i+1), 4 = (j+1,i+1), 8 = (j+1,i)
     code = (above[:-1, :-1].astype(np.uint8)
             | (above[:-1, 1:].astype(np.uint8) << 1)
@@ -146,14 +138,16 @@ def marching_squares(x, y, z, level) -> List[np.ndarray]:
             | (above[1:, :-1].astype(np.uint8) << 3))
     jj, ii = np.nonzero((code != 0) & (code != 15))
     if len(jj) == 0:
-        return []
+        e = np.empty(0, dtype=np.int64)
+        return e, e, e, np.empty(0), np.empty(0)
     cc = code[jj, ii]
-    top = jj * (w - 1) + ii
-    bot = (jj + 1) * (w - 1) + ii
-    lef = n_he + jj * w + ii
-    rig = n_he + jj * w + ii + 1
+    gj = jj.astype(np.int64) + j0
+    ii = ii.astype(np.int64)
+    top = gj * (w - 1) + ii
+    bot = (gj + 1) * (w - 1) + ii
+    lef = -(gj * w + ii) - 1
+    rig = -(gj * w + ii + 1) - 1
     cen = 0.25 * (z[jj, ii] + z[jj, ii + 1] + z[jj + 1, ii] + z[jj + 1, ii + 1]) > level
-
     ea, eb = [], []
 
     def emit(sel, a, b):
@@ -174,27 +168,59 @@ def marching_squares(x, y, z, level) -> List[np.ndarray]:
     emit(s10 & cen, rig, bot)
     emit(s10 & ~cen, top, rig)
     emit(s10 & ~cen, lef, bot)
-    if not ea:
-        return []
     ea = np.concatenate(ea)
     eb = np.concatenate(eb)
-
-    # crossing point of every used edge
-    ids, inv = np.unique(np.concatenate([ea, eb]), return_inverse=True)
+    # crossing points of the edges used by this block
+    ids = np.unique(np.concatenate([ea, eb]))
     px = np.empty(len(ids))
     py = np.empty(len(ids))
-    is_h = ids < n_he
+    is_h = ids >= 0
     hj, hi = np.divmod(ids[is_h], w - 1)
-    t = (level - z[hj, hi]) / (z[hj, hi + 1] - z[hj, hi])
+    lj = hj - j0
+    t = (level - z[lj, hi]) / (z[lj, hi + 1] - z[lj, hi])
     px[is_h] = x[hi] + t * (x[hi + 1] - x[hi])
     py[is_h] = y[hj]
-    vj, vi = np.divmod(ids[~is_h] - n_he, w)
-    t = (level - z[vj, vi]) / (z[vj + 1, vi] - z[vj, vi])
+    vj, vi = np.divmod(-ids[~is_h] - 1, w)
+    lj = vj - j0
+    t = (level - z[lj, vi]) / (z[lj + 1, vi] - z[lj, vi])
     px[~is_h] = x[vi]
     py[~is_h] = y[vj] + t * (y[vj + 1] - y[vj])
+    return ea, eb, ids, px, py
 
-    ns = len(ea)
-    a, b = inv[:ns], inv[ns:]
+
+def marching_squares(x, y, z, level, block_rows: int = 2048) -> List[np.ndarray]:
+    """Iso-lines of ``z`` (``(h, w)``; row ``j`` at ``y[j]``, column ``i`` at
+    ``x[i]``) at ``level`` as stitched polylines.
+
+    The reference obtains these from matplotlib/contourpy + shapely linemerge
+    (``ocsmesh/raster.py:1426-1470``); neither is available here.  Crossings
+    are placed by linear interpolation along cell edges, saddles are resolved
+    with the cell mean, and segments are stitched through shared cell edges.
+    The raster is swept in row blocks so a 20000 x 20000 DEM needs no
+    full-size temporaries.
+    """
+    x = np.asarray(x, dtype=float)
+    y = np.asarray(y, dtype=float)
+    h, w = z.shape
+    if h < 2 or w < 2:
+        return []
+    eas, ebs, idl, pxl, pyl = [], [], [], [], []
+    for j0 in range(0, h - 1, block_rows):
+        j1 = min(h, j0 + block_rows + 1)
+        ea, eb, ids, px, py = _ms_block(x, y, z[j0:j1], level, j0, w)
+        if len(ea):
+            eas.append(ea); ebs.append(eb)
+            idl.append(ids); pxl.append(px); pyl.append(py)
+    if not eas:
+        return []
+    ea = np.concatenate(eas)
+    eb = np.concatenate(ebs)
+    all_ids = np.concatenate(idl)
+    ids, first_idx = np.unique(all_ids, return_index=True)
+    px = np.concatenate(pxl)[first_idx]
+    py = np.concatenate(pyl)[first_idx]
+    a = np.searchsorted(ids, ea)
+    b = np.searchsorted(ids, eb)
     nn = len(ids)
     ends = np.concatenate([a, b])
     other = np.concatenate([b, a])

@@ -73,7 +73,9 @@ class HfunRaster:
             if not 0 <= self._band[0] < self._band[1] <= raster.height:
                 raise ValueError(f"bad row_band {row_band}")
         ctx = self._ctx()
-        h, w = raster.height, raster.width
+        # only the owned rows are stored: row 0 of the buffer is raster row
+        # self._band[0]
+        h, w = self._band[1] - self._band[0], raster.width
         with torch.cuda.device(self._device):
             self._hfun = torch.empty((h, w), dtype=torch.float32,
                                      device=f"cuda:{self._device}")
@@ -83,6 +85,8 @@ class HfunRaster:
                 init = np.asarray(bands[0], dtype=np.float32)
             else:
                 init = np.asarray(initial_value, dtype=np.float32)
+            if init.shape == (raster.height, w):
+                init = init[self._band[0]:self._band[1]]
             if init.shape != (h, w):
                 raise ValueError("initial_value does not match the raster shape")
             self._hfun.copy_(torch.from_numpy(np.ascontiguousarray(init)))
@@ -104,6 +108,15 @@ class HfunRaster:
         rb = max(self._band[0], window.row_off) - window.row_off
         re = min(self._band[1], window.row_off + window.height) - window.row_off
         return (rb, re) if re > rb else None
+
+    def reset(self) -> None:
+        """Back to the initial state: every pixel = finfo(float32).max."""
+        self._ctx().fill_f32(self._hfun, self._hfun.numel(), FLT_MAX)
+
+    def _hfun_ptr(self, t, window: Window) -> int:
+        """(Virtual) address of the window's top-left pixel in buffer ``t``."""
+        return t.data_ptr() + ((window.row_off - self._band[0]) * self.width
+                               + window.col_off) * 4
 
     def _needs_double_buffer(self, windows) -> bool:
         return len(windows) > 1 and (self._overlap or 0) > 0
@@ -195,14 +208,21 @@ class HfunRaster:
         return self._raster.get_bbox(crs)
 
     def get_values(self, window: Optional[Window] = None,
-                   band: Optional[int] = None, **_kwargs) -> np.ndarray:
-        """Size values as a host float32 array (synchronises the stream)."""
+                   band: Optional[int] = None, out=None, **_kwargs) -> np.ndarray:
+        """Size values as a host float32 array (synchronises the stream).
+        ``out``: optional (pinned) CPU torch tensor to receive the values."""
         if band not in (None, 1):
             raise IndexError("the hfun raster has a single band")
         t = self._hfun
         if window is not None:
-            t = t[window.row_off:window.row_off + window.height,
+            a = window.row_off - self._band[0]
+            if a < 0 or a + window.height > t.shape[0]:
+                raise IndexError("window outside the rows this object owns")
+            t = t[a:a + window.height,
                   window.col_off:window.col_off + window.width]
+        if out is not None:
+            out.copy_(t)
+            return out.numpy()
         return t.cpu().numpy()
 
     def save(self, path):
@@ -243,8 +263,7 @@ class HfunRaster:
         w = self.width
         rb, re = self._band
         ctx = self._ctx()
-        ctx.hfun_clamp(self._hfun.data_ptr() + rb * w * 4, w, w, re - rb,
-                       self._hmin, self._hmax)
+        ctx.hfun_clamp(self._hfun, w, w, re - rb, self._hmin, self._hmax)
 
     def _fuse_clamp(self) -> bool:
         """The decorator's clamp re-pass is folded into the op's own kernel
@@ -327,9 +346,8 @@ class HfunRaster:
                 continue
             cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
                                win.height, band[0], band[1])
-            off = (win.row_off * w + win.col_off) * 4
-            ctx.hfun_feature(cw, verts, nv, old.data_ptr() + off, w,
-                             new.data_ptr() + off, w, expansion_rate,
+            ctx.hfun_feature(cw, verts, nv, self._hfun_ptr(old, win), w,
+                             self._hfun_ptr(new, win), w, expansion_rate,
                              target_size, self._hmin, self._hmax,
                              fuse_clamp=fuse)
         self._hfun = new
@@ -350,6 +368,7 @@ class HfunRaster:
         fuse = self._fuse_clamp()
         w = self.width
         dem = self._raster.device_band(1, self._device)
+        dem_origin = self._raster.device_band_origin(1, self._device)
         es = dem.element_size()
         code = _dem_dtype_code(dem)
         old = self._hfun
@@ -365,10 +384,10 @@ class HfunRaster:
                     "gradient, at least (edge_order + 1) elements are required.")
             cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
                                win.height, band[0], band[1])
-            poff = win.row_off * w + win.col_off
+            poff = (win.row_off - dem_origin) * w + win.col_off
             ctx.hfun_flow_limiter(
                 cw, dem.data_ptr() + poff * es, code, w,
-                old.data_ptr() + poff * 4, w, new.data_ptr() + poff * 4, w,
+                self._hfun_ptr(old, win), w, self._hfun_ptr(new, win), w,
                 dx, dy, hmin, hmax, lower_bound, upper_bound, self._hmin,
                 self._hmax, fuse_clamp=fuse)
         self._hfun = new
@@ -394,11 +413,9 @@ class HfunRaster:
         if src.device != self._hfun.device:
             src = src.to(self._hfun.device)
         ctx = self._ctx()
-        ctx.min_combine(
-            self._hfun.data_ptr() + (window.row_off * self.width + window.col_off) * 4,
-            self.width,
-            src.data_ptr() + (other_window.row_off * other.width + other_window.col_off) * 4,
-            other.width, window.width, window.height)
+        ctx.min_combine(self._hfun_ptr(self._hfun, window), self.width,
+                        other._hfun_ptr(src, other_window), other.width,
+                        window.width, window.height)
 
 
 class HfunCollector:

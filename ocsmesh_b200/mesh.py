@@ -194,7 +194,8 @@ class EuclideanMesh2D:
             # iter_windows(chunk_size, overlap=2) (mesh/mesh.py:2274-2277)
             for win in r.iter_windows(chunk_size=r.chunk_size, overlap=2):
                 cw = _lib.make_win(r.get_window_bounds(win), win.width, win.height)
-                poff = win.row_off * r.width + win.col_off
+                poff = (win.row_off - r.device_band_origin(band, dev)) * r.width \
+                    + win.col_off
                 ctx.interp(cw, dem.data_ptr() + poff * es, dcode, r.width,
                            None if mask is None else mask.data_ptr() + poff,
                            r.width, xy, K, code, touched, vals)

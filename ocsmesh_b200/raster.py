@@ -149,12 +149,17 @@ class _Source:
     """What ``Raster.src`` exposes of a rasterio dataset on this path."""
 
     def __init__(self, bands: np.ndarray, transform: Affine, crs: CRS,
-                 nodata: Optional[float], mask: Optional[np.ndarray]):
+                 nodata: Optional[float], mask: Optional[np.ndarray],
+                 row_origin: int = 0, full_height: Optional[int] = None):
         self.bands = bands
         self.transform = transform
         self.crs = crs
         self.nodata = nodata
         self._mask = mask
+        # a rank of a multi-GPU job may hold only rows [row_origin,
+        # row_origin + bands.shape[1]) of a raster `full_height` rows tall
+        self.row_origin = int(row_origin)
+        self.full_height = bands.shape[1] if full_height is None else int(full_height)
 
     @property
     def count(self):
@@ -162,7 +167,7 @@ class _Source:
 
     @property
     def height(self):
-        return self.bands.shape[1]
+        return self.full_height
 
     @property
     def width(self):
@@ -171,6 +176,16 @@ class _Source:
     @property
     def shape(self):
         return (self.height, self.width)
+
+    def _rows(self, window):
+        a = window.row_off - self.row_origin
+        b = a + window.height
+        if a < 0 or b > self.bands.shape[1]:
+            raise IndexError(
+                f"rows [{window.row_off}, {window.row_off + window.height}) are "
+                f"not held by this band raster (rows [{self.row_origin}, "
+                f"{self.row_origin + self.bands.shape[1]}))")
+        return slice(a, b)
 
     @property
     def dtypes(self):
@@ -195,7 +210,7 @@ class _Source:
              masked: bool = False, **_kwargs):
         if window is None:
             window = Window(0, 0, self.width, self.height)
-        sl = (slice(window.row_off, window.row_off + window.height),
+        sl = (self._rows(window),
               slice(window.col_off, window.col_off + window.width))
         if i is None:
             vals = np.array(self.bands[(slice(None),) + sl])
@@ -234,12 +249,17 @@ class Raster:
         self._src = _Source(bands, Affine(*info.transform), self._crs,
                             info.nodata, None)
         self._dev_cache = {}
+        self._dev_origin = {}
 
     @classmethod
     def from_numpy(cls, values, transform, crs=None, chunk_size=None,
-                   overlap=None, nodata=None, mask=None) -> "Raster":
+                   overlap=None, nodata=None, mask=None, row_origin: int = 0,
+                   full_height: Optional[int] = None) -> "Raster":
         """In-memory raster: ``values`` is ``(h, w)`` or ``(bands, h, w)``,
-        ``transform`` the affine six-tuple ``(a, b, c, d, e, f)``."""
+        ``transform`` the affine six-tuple ``(a, b, c, d, e, f)`` of the FULL
+        raster.  ``row_origin`` / ``full_height``: ``values`` holds only rows
+        ``[row_origin, row_origin + h)`` of a raster ``full_height`` rows tall
+        (a rank's band of a row-partitioned raster)."""
         self = cls.__new__(cls)
         self.chunk_size = chunk_size
         self.overlap = overlap
@@ -258,8 +278,10 @@ class Raster:
             if mask.ndim == 2:
                 mask = mask[None]
         self._crs = CRS.from_user_input(crs)
-        self._src = _Source(values, Affine(*transform), self._crs, nodata, mask)
+        self._src = _Source(values, Affine(*transform), self._crs, nodata, mask,
+                            row_origin, full_height)
         self._dev_cache = {}
+        self._dev_origin = {}
         return self
 
     # ---- descriptors (ocsmesh/raster.py:80-212) ---------------------------
@@ -461,7 +483,25 @@ class Raster:
             host = np.ascontiguousarray(host)
             t = torch.from_numpy(host).to(f"cuda:{key[1]}", non_blocking=False)
             self._dev_cache[key] = t
+            self._dev_origin[key] = self._src.row_origin
         return t
+
+    def device_band_origin(self, band: int = 1, device=None) -> int:
+        """Raster row held by row 0 of ``device_band(band, device)``."""
+        import torch
+        if device is None:
+            device = torch.cuda.current_device()
+        return self._dev_origin.get((int(band), int(device)), self._src.row_origin)
+
+    def set_device_band(self, tensor, row_origin: int, band: int = 1, device=None):
+        """Install an already device-resident band (rows starting at raster row
+        ``row_origin``), e.g. a rank's band with its halo rows."""
+        import torch
+        if device is None:
+            device = tensor.device.index
+        key = (int(band), int(device))
+        self._dev_cache[key] = tensor
+        self._dev_origin[key] = int(row_origin)
 
     def device_mask(self, band: int = 1, device=None):
         """uint8 nodata mask of a band on the device, or None."""
@@ -482,6 +522,7 @@ class Raster:
 
     def drop_device_cache(self):
         self._dev_cache = {}
+        self._dev_origin = {}
 
 
 def raster_from_numpy(filename, data, mgrid, crs=4326) -> None:
