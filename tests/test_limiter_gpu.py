@@ -120,3 +120,33 @@ def test_errors(ctx):
     with pytest.raises(_lib.OcsbError):
         run_gpu(ctx, z, z.copy(), 1.0, 1.0, None, None, None, None, None, None,
                 device=False)
+
+
+@pytest.mark.parametrize("dxdy", [(7.3, 30.0), (1.0 / 3.0, 1e-3), (10.0, 10.0),
+                                  (123456.789, 0.7)])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_constant_division_is_ieee(ctx, dxdy, dtype):
+    """The gradient divides by loop-invariant constants with Markstein's
+    fma sequence; it must stay bit-identical to numpy's true division, also
+    for zero / tiny / huge differences (slow-path operands)."""
+    rng = np.random.default_rng(17)
+    z = (rng.normal(size=(300, 700)) * 50).astype(dtype)
+    z[:40] = 3.0                                   # zero differences
+    z[40:80] *= dtype(1e-36 if dtype == np.float32 else 1e-300)   # tiny
+    z[80:120] *= dtype(1e30 if dtype == np.float32 else 1e290)    # huge
+    old = np.full(z.shape, FLT_MAX, np.float32)
+    with np.errstate(all="ignore"):
+        ref = O.flow_limiter_window(z, old, dxdy[0], dxdy[1], 50.0, 1500.0,
+                                    None, None, 100.0, 1500.0)
+    out = run_gpu(ctx, z, old, dxdy[0], dxdy[1], 50.0, 1500.0, None, None,
+                  100.0, 1500.0)
+    check(out, ref)
+    # unclamped: the raw |z| / (3 |grad z|) values themselves
+    with np.errstate(all="ignore"):
+        ref = O.flow_limiter_window(z, old, dxdy[0], dxdy[1], None, None,
+                                    None, None, None, None)
+    out = run_gpu(ctx, z, old, dxdy[0], dxdy[1], None, None, None, None, None, None)
+    m = np.ma.getmaskarray(ref)
+    a, b = out[~m], np.ma.getdata(ref)[~m]
+    np.testing.assert_array_equal(np.isnan(a), np.isnan(b))
+    np.testing.assert_array_equal(a[~np.isnan(a)], b[~np.isnan(b)])
