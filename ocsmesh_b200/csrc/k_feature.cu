@@ -413,201 +413,7 @@ split_p4_kernel(RefineArgs A, SplitScratch S) {
     }
 }
 
-// ---------------------------------------------------------------------------
-// evaluation: fused leaf filter + exact distance + size law
-// ---------------------------------------------------------------------------
-struct EvalArgs {
-    Geom g;
-    LevelDev lvl;           // the 64-px level
-    const double2 *verts;
-    const float *old_;
-    int64_t os;
-    float *new_;
-    int64_t ns;
-    double *dist;
-    int64_t *idx;
-    int64_t nv;
-    double rate_target, target, r, r2, r2lim;
-    float hmin_f, hmax_f;
-    int has_hmin, has_hmax, fuse_clamp;
-    int vec_old, vec_new;
-    const int *overflow;
-};
-
-template <bool WANT_IDX>
-__global__ void __launch_bounds__(kEvalThreads) eval_kernel(EvalArgs A) {
-    __shared__ double2 s_v[kCandCap];
-    __shared__ int s_id[kCandCap];
-    if (*A.overflow) return;
-    const int t = blockIdx.x;
-    const int tx = t % A.lvl.ntx, ty = t / A.lvl.ntx;
-    const int cnt = A.lvl.cnt[t];
-    const int off = A.lvl.off[t];
-    const bool in_smem = cnt <= kCandCap;
-    if (in_smem) {
-        for (int i = threadIdx.x; i < cnt; i += kEvalThreads) {
-            int id = A.lvl.ids[off + i];
-            s_id[i] = id;
-            s_v[i] = A.verts[id];
-        }
-        __syncthreads();
-    }
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const Geom &g = A.g;
-
-    for (int leaf = wid; leaf < 16; leaf += kEvalThreads / 32) {
-        const int c0 = tx * kTile0 + (leaf & 1) * kLeafW;
-        const int r0 = ty * kTile0 + (leaf >> 1) * kLeafH;
-        if (c0 >= g.w || r0 >= g.h) continue;
-        const int c1 = min(g.w, c0 + kLeafW) - 1;
-        const int r1 = min(g.h, r0 + kLeafH) - 1;
-        const Rect q = tile_rect(g, c0, c1, r0, r1);
-
-        // this lane's pixels: 4 consecutive columns x 2 rows (row, row + 4)
-        const int gcol = c0 + (lane & 7) * 4;
-        const int grow0 = r0 + (lane >> 3);
-        const int grow1 = grow0 + 4;
-        double px[4], py[2];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
-        py[0] = lin_at(g.ay, g.row0 + min(grow0, g.h - 1));
-        py[1] = lin_at(g.ay, g.row0 + min(grow1, g.h - 1));
-
-        double best[8];
-        int bid[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { best[k] = INFINITY; bid[k] = 0x7fffffff; }
-
-        if (cnt > 0) {
-            // ---- pass A: dominators (nearest to centre and corners) --------
-            unsigned domkey[5];
-            Dom D;
-#pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                domkey[j] = 0xffffffffu;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) D.c[j][k] = INFINITY;
-            }
-            for (int b0 = 0; b0 < cnt; b0 += 32) {
-                const int i = b0 + lane;
-                const bool valid = i < cnt;
-                double2 v = make_double2(0.0, 0.0);
-                if (valid) v = in_smem ? s_v[i] : A.verts[A.lvl.ids[off + i]];
-                const CornerD2 c = corner_d2(q, v);
-                const double dc = center_d2(q, v);
-                const double dd[5] = {dc, c.d00, c.d01, c.d10, c.d11};
-#pragma unroll
-                for (int j = 0; j < 5; ++j) {
-                    unsigned key = valid ? __float_as_uint((float)dd[j]) : 0xffffffffu;
-                    unsigned m = __reduce_min_sync(0xffffffffu, key);
-                    if (m < domkey[j]) {   // warp-uniform
-                        domkey[j] = m;
-                        int src = __ffs(__ballot_sync(0xffffffffu, key == m)) - 1;
-                        const double mg = 1.0 + kDomEps;
-                        D.c[j][0] = __shfl_sync(0xffffffffu, c.d00, src) * mg;
-                        D.c[j][1] = __shfl_sync(0xffffffffu, c.d01, src) * mg;
-                        D.c[j][2] = __shfl_sync(0xffffffffu, c.d10, src) * mg;
-                        D.c[j][3] = __shfl_sync(0xffffffffu, c.d11, src) * mg;
-                    }
-                }
-            }
-            // ---- pass B: filter, then evaluate survivors -------------------
-            for (int b0 = 0; b0 < cnt; b0 += 32) {
-                const int i = b0 + lane;
-                const bool valid = i < cnt;
-                double2 v = make_double2(0.0, 0.0);
-                int id = 0;
-                if (valid) {
-                    if (in_smem) { v = s_v[i]; id = s_id[i]; }
-                    else { id = A.lvl.ids[off + i]; v = A.verts[id]; }
-                }
-                bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
-                            !dominated(D, corner_d2(q, v));
-                unsigned mask = __ballot_sync(0xffffffffu, keep);
-                while (mask) {
-                    const int s = __ffs(mask) - 1;
-                    mask &= mask - 1;
-                    const double vx = __shfl_sync(0xffffffffu, v.x, s);
-                    const double vy = __shfl_sync(0xffffffffu, v.y, s);
-                    int vid = 0;
-                    if (WANT_IDX) vid = __shfl_sync(0xffffffffu, id, s);
-                    double dx2[4], dy2[2];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        double d = __dsub_rn(px[k], vx);
-                        dx2[k] = __dmul_rn(d, d);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        double d = __dsub_rn(py[j], vy);
-                        dy2[j] = __dmul_rn(d, d);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const double d2 = __dadd_rn(dx2[k], dy2[j]);
-                            if (WANT_IDX) {
-                                if (d2 < best[j * 4 + k] ||
-                                    (d2 == best[j * 4 + k] && vid < bid[j * 4 + k])) {
-                                    best[j * 4 + k] = d2;
-                                    bid[j * 4 + k] = vid;
-                                }
-                            } else {
-                                best[j * 4 + k] = fmin(best[j * 4 + k], d2);
-                            }
-                        }
-                }
-            }
-        }
-
-        // ---- epilogue ------------------------------------------------------
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int row = j ? grow1 : grow0;
-            if (row > r1 || gcol > c1) continue;
-            const float *orow = A.old_ + (int64_t)(g.row0 + row) * A.os;
-            float *nrow = A.new_ + (int64_t)(g.row0 + row) * A.ns;
-            const bool full = gcol + 3 <= c1;
-            float o[4];
-            if (A.vec_old && full) {
-                float4 v4 = *reinterpret_cast<const float4 *>(orow + gcol);
-                o[0] = v4.x; o[1] = v4.y; o[2] = v4.z; o[3] = v4.w;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) o[k] = (gcol + k <= c1) ? orow[gcol + k] : 0.f;
-            }
-            float out[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const double d2 = best[j * 4 + k];
-                const bool hit = d2 < A.r2;
-                const double d = hit ? __dsqrt_rn(d2) : A.r;
-                // values = expansion_rate*target_size*distances + target_size
-                const double v64 = __dadd_rn(__dmul_rn(A.rate_target, d), A.target);
-                float vf = (float)v64;
-                vf = clamp_f32(vf, A.has_hmin, A.hmin_f, A.has_hmax, A.hmax_f);
-                float res = np_minimum_f(o[k], vf);
-                if (A.fuse_clamp)
-                    res = clamp_f32(res, A.has_hmin, A.hmin_f, A.has_hmax, A.hmax_f);
-                out[k] = res;
-                if (gcol + k <= c1) {
-                    const int64_t lin = (int64_t)(g.row0 + row) * g.w + gcol + k;
-                    if (A.dist) A.dist[lin] = d;
-                    if (WANT_IDX) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
-                }
-            }
-            if (A.vec_new && full) {
-                *reinterpret_cast<float4 *>(nrow + gcol) =
-                    make_float4(out[0], out[1], out[2], out[3]);
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (gcol + k <= c1) nrow[gcol + k] = out[k];
-            }
-        }
-    }
-}
+#include "k_feature_eval.cuh"
 
 // ---------------------------------------------------------------------------
 // host orchestration
@@ -754,14 +560,21 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         E.dist = dist_out; E.idx = idx_out; E.nv = nv;
         E.rate_target = a.rate_target; E.target = a.target;
         E.r = a.r; E.r2 = (bounded && a.r <= 0) ? -1.0 : r2; E.r2lim = r2lim;
-        E.hmin_f = a.hmin_f; E.hmax_f = a.hmax_f;
-        E.has_hmin = a.has_hmin; E.has_hmax = a.has_hmax;
+        {
+            volatile double m = a.rate_target * a.r;   // no FMA contraction
+            volatile double s = m + a.target;
+            E.v_far = s;
+        }
+        const float finf = std::numeric_limits<float>::infinity();
+        E.lo = a.has_hmin ? a.hmin_f : -finf;
+        E.hi = a.has_hmax ? a.hmax_f : finf;
+        E.fast_ok = (a.rate_target >= 0.0 && a.target >= 0.0) ? 1 : 0;
         E.fuse_clamp = a.fuse_clamp;
         E.vec_old = (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
         E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
         E.overflow = overflow;
         OCSB_TIME(ctx, KC_FEATURE_EVAL);
-        if (idx_out)
+        if (idx_out || dist_out)
             eval_kernel<true><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
         else
             eval_kernel<false><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);

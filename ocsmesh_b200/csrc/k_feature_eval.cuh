@@ -1,0 +1,292 @@
+// K1 evaluation kernel (included by k_feature.cu inside its anonymous
+// namespace): fused leaf filter + exact nearest-vertex distance + size law.
+//
+// One CTA per 64x64 tile, one warp per 32x8-pixel leaf, one lane per 4x2
+// pixels.  Per leaf:
+//   pass A  lane = candidate: the 5 dominators (nearest to the leaf centre and
+//           to its 4 corners) by redux.sync min; their corner distances go to
+//           a per-warp shared table (they are warp-uniform, so keeping them
+//           in registers only cost occupancy)
+//   pass B  lane = candidate: radius + dominance filter, survivors compacted
+//           into per-warp shared memory (ballot + popc), then every lane
+//           evaluates its 8 pixels against each survivor read as one LDS.128
+//           broadcast
+//   epilogue  float32(rate*target*sqrt(d2) + target), clamps, min(old, .)
+//
+// Exactness of the epilogue.  The reference value is
+//   v = float32( fl(fl(rt * RN(sqrt(d2))) + target) )        (all f64)
+// RN(sqrt) in f64 costs ~28 instructions/pixel, which dominated the first
+// version of this kernel.  The fast path computes d = sqrt(d2) to 2^-42
+// relative (MUFU.RSQ seed + one f64 Newton step), forms v64 the same way and
+// accepts it only if the 29 mantissa bits that the f32 rounding drops are not
+// within 2^14 ulp64 of the round-to-nearest tie -- then float32(v64) is
+// provably the reference's float32; otherwise (1 pixel in 16 k) it falls back
+// to __dsqrt_rn.  Requesting dist_out / idx_out selects the exact path.
+#pragma once
+
+struct EvalArgs {
+    Geom g;
+    LevelDev lvl;           // the 64-px level
+    const double2 *verts;
+    const float *old_;
+    int64_t os;
+    float *new_;
+    int64_t ns;
+    double *dist;
+    int64_t *idx;
+    int64_t nv;
+    double rate_target, target, r, r2, r2lim;
+    double v_far;           // fl(fl(rate_target * r) + target): beyond the radius
+    float lo, hi;           // f32-rounded [hmin, hmax], -/+inf when None
+    int fuse_clamp;
+    int fast_ok;            // rate_target >= 0 && target >= 0: error bound holds
+    int vec_old, vec_new;
+    const int *overflow;
+};
+
+struct WarpScratch {
+    double dom[5][4];       // dominator corner distances (inflated by 1+eps)
+    double2 sv[32];         // compacted survivors of one 32-candidate chunk
+    int sid[32];
+};
+
+__device__ __forceinline__ float min_nan_f32(float a, float b) {
+    float r;   // np.minimum: NaN-propagating
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ bool dominated_smem(const WarpScratch &W,
+                                               const CornerD2 &v) {
+    bool dom = false;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const double2 a = *reinterpret_cast<const double2 *>(&W.dom[j][0]);
+        const double2 b = *reinterpret_cast<const double2 *>(&W.dom[j][2]);
+        dom = dom || (v.d00 > a.x && v.d01 > a.y && v.d10 > b.x && v.d11 > b.y);
+    }
+    return dom;
+}
+
+// float32 of the size law for squared distance d2 (see header comment)
+__device__ __forceinline__ float size_law_f32(double d2, const EvalArgs &A) {
+    const bool hit = d2 < A.r2;
+    // fast path (evaluated for every lane; garbage for out-of-range d2)
+    const float y32 = rsqrt_approx((float)d2);
+    const double y = (double)y32;
+    const double g = d2 * y;
+    const double e = fma(-g, g, d2);
+    const double d = fma(e, 0.5 * y, g);
+    double v64 = __dadd_rn(__dmul_rn(A.rate_target, d), A.target);
+    const unsigned low = (unsigned)__double2loint(v64) & 0x1fffffffu;
+    const bool near_tie = (unsigned)abs((int)low - 0x10000000) < (1u << 14);
+    const bool in_range = d2 > 1e-30 && d2 < 1e30;
+    if (hit && (near_tie || !in_range || !A.fast_ok)) {
+        const double dd = __dsqrt_rn(d2);
+        v64 = __dadd_rn(__dmul_rn(A.rate_target, dd), A.target);
+    }
+    return (float)(hit ? v64 : A.v_far);
+}
+
+template <bool WANT_OUT>
+__global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
+    __shared__ double2 s_v[kCandCap];
+    __shared__ int s_id[kCandCap];
+    __shared__ WarpScratch s_w[kEvalThreads / 32];
+    if (*A.overflow) return;
+    const int t = blockIdx.x;
+    const int tx = t % A.lvl.ntx, ty = t / A.lvl.ntx;
+    const int cnt = A.lvl.cnt[t];
+    const int off = A.lvl.off[t];
+    const bool in_smem = cnt <= kCandCap;
+    if (in_smem) {
+        for (int i = threadIdx.x; i < cnt; i += kEvalThreads) {
+            int id = A.lvl.ids[off + i];
+            s_id[i] = id;
+            s_v[i] = A.verts[id];
+        }
+        __syncthreads();
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const Geom &g = A.g;
+    WarpScratch &W = s_w[wid];
+
+    for (int leaf = wid; leaf < 16; leaf += kEvalThreads / 32) {
+        const int c0 = tx * kTile0 + (leaf & 1) * kLeafW;
+        const int r0 = ty * kTile0 + (leaf >> 1) * kLeafH;
+        if (c0 >= g.w || r0 >= g.h) continue;
+        const int c1 = min(g.w, c0 + kLeafW) - 1;
+        const int r1 = min(g.h, r0 + kLeafH) - 1;
+
+        // this lane's pixels: 4 consecutive columns x 2 rows (row, row + 4)
+        const int gcol = c0 + (lane & 7) * 4;
+        const int grow[2] = {r0 + (lane >> 3), r0 + (lane >> 3) + 4};
+        const bool full = gcol + 3 <= c1;
+
+        // old hfun values: issued first, consumed in the epilogue
+        float o[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o[j][k] = 0.f;
+            if (grow[j] > r1 || gcol > c1) continue;
+            const float *orow = A.old_ + (int64_t)(g.row0 + grow[j]) * A.os;
+            if (A.vec_old && full) {
+                const float4 v4 = __ldcs(reinterpret_cast<const float4 *>(orow + gcol));
+                o[j][0] = v4.x; o[j][1] = v4.y; o[j][2] = v4.z; o[j][3] = v4.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (gcol + k <= c1) o[j][k] = orow[gcol + k];
+            }
+        }
+
+        double best[8];
+        int bid[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { best[k] = INFINITY; bid[k] = 0x7fffffff; }
+
+        if (cnt > 0) {
+            const Rect q = tile_rect(g, c0, c1, r0, r1);
+            // ---- pass A: dominators (nearest to centre and corners) --------
+            unsigned domkey[5];
+#pragma unroll
+            for (int j = 0; j < 5; ++j) domkey[j] = 0xffffffffu;
+            for (int b0 = 0; b0 < cnt; b0 += 32) {
+                const int i = b0 + lane;
+                const bool valid = i < cnt;
+                double2 v = make_double2(0.0, 0.0);
+                if (valid) v = in_smem ? s_v[i] : A.verts[A.lvl.ids[off + i]];
+                const CornerD2 c = corner_d2(q, v);
+                const double dd[5] = {center_d2(q, v), c.d00, c.d01, c.d10, c.d11};
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    const unsigned key = valid ? __float_as_uint((float)dd[j]) : 0xffffffffu;
+                    const unsigned m = __reduce_min_sync(0xffffffffu, key);
+                    if (m < domkey[j]) {   // warp-uniform
+                        domkey[j] = m;
+                        const int src = __ffs(__ballot_sync(0xffffffffu, key == m)) - 1;
+                        if (lane == src) {
+                            const double mg = 1.0 + kDomEps;
+                            W.dom[j][0] = c.d00 * mg; W.dom[j][1] = c.d01 * mg;
+                            W.dom[j][2] = c.d10 * mg; W.dom[j][3] = c.d11 * mg;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+
+            // this lane's pixel coordinates
+            double px[4], py[2];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                py[j] = lin_at(g.ay, g.row0 + min(grow[j], g.h - 1));
+
+            // ---- pass B: filter, compact, evaluate survivors ----------------
+            for (int b0 = 0; b0 < cnt; b0 += 32) {
+                const int i = b0 + lane;
+                const bool valid = i < cnt;
+                double2 v = make_double2(0.0, 0.0);
+                int id = 0;
+                if (valid) {
+                    if (in_smem) { v = s_v[i]; id = s_id[i]; }
+                    else { id = A.lvl.ids[off + i]; v = A.verts[id]; }
+                }
+                const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                                  !dominated_smem(W, corner_d2(q, v));
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                if (keep) {
+                    const int pos = __popc(mask & lt_mask);
+                    W.sv[pos] = v;
+                    if (WANT_OUT) W.sid[pos] = id;
+                }
+                __syncwarp();
+                const int ns = __popc(mask);
+                for (int s = 0; s < ns; ++s) {
+                    const double2 sv = W.sv[s];
+                    int vid = 0;
+                    if (WANT_OUT) vid = W.sid[s];
+                    double dx2[4], dy2[2];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const double d = __dsub_rn(px[k], sv.x);
+                        dx2[k] = __dmul_rn(d, d);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const double d = __dsub_rn(py[j], sv.y);
+                        dy2[j] = __dmul_rn(d, d);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const double d2 = __dadd_rn(dx2[k], dy2[j]);
+                            if (WANT_OUT) {
+                                if (d2 < best[j * 4 + k] ||
+                                    (d2 == best[j * 4 + k] && vid < bid[j * 4 + k])) {
+                                    best[j * 4 + k] = d2;
+                                    bid[j * 4 + k] = vid;
+                                }
+                            } else {
+                                best[j * 4 + k] = fmin(best[j * 4 + k], d2);
+                            }
+                        }
+                }
+                __syncwarp();
+            }
+        }
+
+        // ---- epilogue ------------------------------------------------------
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int row = grow[j];
+            if (row > r1 || gcol > c1) continue;
+            float *nrow = A.new_ + (int64_t)(g.row0 + row) * A.ns;
+            float out[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const double d2 = best[j * 4 + k];
+                float vf;
+                if (WANT_OUT) {
+                    const bool hit = d2 < A.r2;
+                    const double d = hit ? __dsqrt_rn(d2) : A.r;
+                    // values = expansion_rate*target_size*distances + target_size
+                    vf = (float)__dadd_rn(__dmul_rn(A.rate_target, d), A.target);
+                    if (gcol + k <= c1) {
+                        const int64_t lin = (int64_t)(g.row0 + row) * g.w + gcol + k;
+                        if (A.dist) A.dist[lin] = d;
+                        if (A.idx) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
+                    }
+                } else {
+                    vf = size_law_f32(d2, A);
+                }
+                vf = (vf < A.lo) ? A.lo : vf;
+                vf = (vf > A.hi) ? A.hi : vf;
+                float res = min_nan_f32(o[j][k], vf);
+                if (A.fuse_clamp) {
+                    res = (res < A.lo) ? A.lo : res;
+                    res = (res > A.hi) ? A.hi : res;
+                }
+                out[k] = res;
+            }
+            if (A.vec_new && full) {
+                __stcs(reinterpret_cast<float4 *>(nrow + gcol),
+                       make_float4(out[0], out[1], out[2], out[3]));
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (gcol + k <= c1) nrow[gcol + k] = out[k];
+            }
+        }
+    }
+}

@@ -162,3 +162,21 @@ def test_errors(ctx):
         run_gpu(ctx, r, pts, old, 0.001, -1.0, None, None, device=False)
     with pytest.raises(_lib.OcsbError):
         run_gpu(ctx, r, pts[:0], old, 0.001, 100.0, None, None, device=False)
+
+
+@pytest.mark.parametrize("rate,target,hmin,hmax", [
+    (0.001, 100.0, 100.0, 1500.0), (0.0137, 73.1, None, None),
+    (0.3, 5.0, 1.0, 4000.0)])
+def test_fast_size_law_is_bit_exact(ctx, rate, target, hmin, hmax):
+    """Without dist/idx outputs the epilogue uses the checked fast sqrt
+    (k_feature_eval.cuh); its float32 sizes must equal the f64 reference
+    path bit for bit on a few million pixels."""
+    h, w = 1500, 1400
+    r, pts = make_case(h, w, 12, n_lines=3, target=target)
+    old = np.full((h, w), FLT_MAX, np.float32)
+    ref = O.add_feature_window(old, pts, r.get_xy(), h, w, rate, target, hmin, hmax)
+    out = run_gpu(ctx, r, pts, old, rate, target, hmin, hmax)
+    np.testing.assert_array_equal(out, ref)
+    # and the exact (dist/idx) variant agrees with the fast one
+    out2, _, _ = run_gpu(ctx, r, pts, old, rate, target, hmin, hmax, want=True)
+    np.testing.assert_array_equal(out2, out)
