@@ -224,6 +224,30 @@ int32_t ocsb_interp(ocsb_ctx *ctx, const ocsb_win *win,
                     const double *xy, int64_t K, int32_t method,
                     uint8_t *touched, double *values);
 
+/* ---- A13: EuclideanMesh2D.interpolate over a raster LIST -------------------
+ * values[mask] = vals for every raster in list order, last raster wins
+ *                                                        ocsmesh/mesh/mesh.py:365-376
+ * One (raster, window) pair of the list; same fields as ocsb_interp.          */
+typedef struct ocsb_interp_raster {
+    ocsb_win       win;
+    const void    *dem;
+    int32_t        dem_dtype;
+    int64_t        dem_stride;
+    const uint8_t *nodata_mask;   /* NULL = no nodata */
+    int64_t        mask_stride;
+} ocsb_interp_raster;
+
+/* Equivalent to calling ocsb_interp once per entry in list order, but the node
+ * coordinates are read (and the values written) once: every node walks the
+ * list from the last entry to the first and stops at the first entry that
+ * yields a value.  source (optional, K int32) receives the index of that
+ * entry and is left alone for untouched nodes.  Linear / nearest run as ONE
+ * kernel launch; spline entries are prefiltered and evaluated one by one.     */
+int32_t ocsb_interp_multi(ocsb_ctx *ctx, const ocsb_interp_raster *rasters,
+                          int32_t n_rasters, const double *xy, int64_t K,
+                          int32_t method, uint8_t *touched, double *values,
+                          int32_t *source);
+
 /* Spline prefilter for OCSB_INTERP_SPLINE: builds the tensor-product
  * not-a-knot cubic B-spline coefficients of RectBivariateSpline(kx=ky=3, s=0)
  * (ocsmesh/mesh/mesh.py:2306-2314) for one window into coef[width*height]

@@ -32,6 +32,12 @@ class ocsb_win(C.Structure):
                 ("row_begin", c_i32), ("row_end", c_i32)]
 
 
+class ocsb_interp_raster(C.Structure):
+    _fields_ = [("win", ocsb_win), ("dem", c_vp), ("dem_dtype", c_i32),
+                ("dem_stride", c_i64), ("nodata_mask", c_vp),
+                ("mask_stride", c_i64)]
+
+
 class OcsbError(RuntimeError):
     def __init__(self, status: int, message: str):
         super().__init__(f"libocsb200 error {status}: {message}")
@@ -71,6 +77,8 @@ SIGNATURES = {
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
+    "ocsb_interp_multi": (c_i32, [c_vp, C.POINTER(ocsb_interp_raster), c_i32,
+                                  c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "ocsb_spline_prefilter": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_vp]),
 }
@@ -242,6 +250,21 @@ class Context:
             self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
             ptr(mask), int(mask_stride), ptr(xy), int(K), int(method),
             ptr(touched), ptr(values)))
+
+    def interp_multi(self, entries, xy, K, method, touched, values, source=None):
+        """``entries``: list of (win, dem, dem_dtype, dem_stride, mask,
+        mask_stride) in raster-list order (last valid hit wins)."""
+        arr = (ocsb_interp_raster * len(entries))()
+        for a, (win, dem, dt, ds, mask, ms) in zip(arr, entries):
+            a.win = win
+            a.dem = ptr(dem)
+            a.dem_dtype = int(dt)
+            a.dem_stride = int(ds)
+            a.nodata_mask = ptr(mask)
+            a.mask_stride = int(ms)
+        check(self.lib.ocsb_interp_multi(self.handle, arr, len(entries), ptr(xy),
+                                         int(K), int(method), ptr(touched),
+                                         ptr(values), ptr(source)))
 
     def spline_prefilter(self, win, dem, dem_dtype, dem_stride, coef):
         check(self.lib.ocsb_spline_prefilter(

@@ -657,3 +657,71 @@ extern "C" int32_t ocsb_interp(ocsb_ctx *ctx, const ocsb_win *win,
     }
     return finish_call(ctx, {&sz, &sm, &sxy, &st, &sval});
 }
+
+extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
+                                     const ocsb_interp_raster *rasters,
+                                     int32_t n_rasters, const double *xy,
+                                     int64_t K, int32_t method,
+                                     uint8_t *touched, double *values,
+                                     int32_t *source) {
+    CTX_ENTER("ocsb_interp_multi");
+    OCSB_REQUIRE(method == OCSB_INTERP_LINEAR || method == OCSB_INTERP_NEAREST ||
+                     method == OCSB_INTERP_SPLINE,
+                 "Invalid value method specified <%d>!", method);
+    OCSB_REQUIRE(n_rasters >= 0 && K >= 0, "ocsb_interp_multi: negative count");
+    if (K == 0 || n_rasters == 0) return OCSB_OK;
+    OCSB_REQUIRE(rasters && xy && touched && values,
+                 "ocsb_interp_multi: NULL buffers");
+    if (method == OCSB_INTERP_SPLINE) {
+        // per-raster coefficient arrays: one prefilter + evaluation per entry;
+        // `source` follows from the touched flags of each pass
+        for (int32_t i = 0; i < n_rasters; ++i) {
+            const ocsb_interp_raster &r = rasters[i];
+            OCSB_TRY(ocsb_interp(ctx, &r.win, r.dem, r.dem_dtype, r.dem_stride,
+                                 nullptr, 0, xy, K, method, touched, values));
+        }
+        OCSB_REQUIRE(source == nullptr,
+                     "ocsb_interp_multi: source is not available for spline");
+        return OCSB_OK;
+    }
+    std::vector<Staged> sz(n_rasters), sm(n_rasters);
+    std::vector<InterpRaster> rs(n_rasters);
+    for (int32_t i = 0; i < n_rasters; ++i) {
+        const ocsb_interp_raster &r = rasters[i];
+        OCSB_TRY(check_win(&r.win, "ocsb_interp_multi"));
+        OCSB_REQUIRE(r.dem_dtype == OCSB_F32 || r.dem_dtype == OCSB_F64,
+                     "ocsb_interp_multi: unsupported DEM dtype %d", r.dem_dtype);
+        const int w = r.win.width, h = r.win.height;
+        OCSB_REQUIRE(w >= 2 && h >= 2 && r.dem && r.dem_stride >= w,
+                     "ocsb_interp_multi: bad raster %d", i);
+        OCSB_REQUIRE(!r.nodata_mask || r.mask_stride >= w,
+                     "ocsb_interp_multi: bad mask stride of raster %d", i);
+        OCSB_REQUIRE(r.win.x0 != r.win.x1 && r.win.y0 != r.win.y1,
+                     "ocsb_interp_multi: degenerate window bounds");
+        const size_t es = r.dem_dtype == OCSB_F32 ? 4 : 8;
+        OCSB_TRY(sz[i].init(ctx, r.dem, h, w, r.dem_stride, es, STAGE_IN));
+        OCSB_TRY(sm[i].init(ctx, r.nodata_mask, h, w, r.mask_stride, 1, STAGE_IN));
+        win_axes(&r.win, &rs[i].ax, &rs[i].ay);
+        rs[i].dem = sz[i].dev;
+        rs[i].dem_dtype = r.dem_dtype;
+        rs[i].dem_stride = sz[i].dev_stride;
+        rs[i].mask = (const uint8_t *)sm[i].dev;
+        rs[i].mask_stride = sm[i].dev_stride;
+    }
+    Staged sxy, st, sval, ssrc;
+    OCSB_TRY(sxy.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
+    OCSB_TRY(st.init(ctx, touched, 1, K, K, 1, STAGE_INOUT));
+    OCSB_TRY(sval.init(ctx, values, 1, K, K, 8, STAGE_INOUT));
+    OCSB_TRY(ssrc.init(ctx, source, 1, K, K, 4, STAGE_INOUT));
+    OCSB_TRY(k_interp_multi(ctx, rs.data(), n_rasters, (const double *)sxy.dev, K,
+                            method, (uint8_t *)st.dev, (double *)sval.dev,
+                            (int32_t *)ssrc.dev));
+    bool any = sxy.staged || st.staged || sval.staged || ssrc.staged;
+    for (auto &s : sz) any = any || s.staged;
+    for (auto &s : sm) any = any || s.staged;
+    OCSB_TRY(st.finish());
+    OCSB_TRY(sval.finish());
+    OCSB_TRY(ssrc.finish());
+    if (any) OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OCSB_OK;
+}

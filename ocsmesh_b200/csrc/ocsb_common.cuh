@@ -243,6 +243,19 @@ int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
                  int dem_dtype, int64_t dem_stride, const uint8_t *mask,
                  int64_t mask_stride, const double *xy, int64_t K, int method,
                  uint8_t *touched, double *values);
+struct InterpRaster {
+    LinAxis ax, ay;
+    const void *dem;
+    int dem_dtype;
+    int64_t dem_stride;
+    const uint8_t *mask;
+    int64_t mask_stride;
+};
+// rasters in list order, last valid hit wins; source (optional) receives the
+// index of the raster that set each node
+int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
+                       const double *xy, int64_t K, int method, uint8_t *touched,
+                       double *values, int32_t *source);
 int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
                            const void *dem, int dem_dtype, int64_t dem_stride,
                            double *coef);

@@ -185,6 +185,7 @@ class EuclideanMesh2D:
         import torch
         code = _METHODS[method]
         K = int(xy.shape[0])
+        entries = []
         for r in rasters:
             dem = r.device_band(band, dev)
             mask = r.device_mask(band, dev) if method != "spline" else None
@@ -196,9 +197,12 @@ class EuclideanMesh2D:
                 cw = _lib.make_win(r.get_window_bounds(win), win.width, win.height)
                 poff = (win.row_off - r.device_band_origin(band, dev)) * r.width \
                     + win.col_off
-                ctx.interp(cw, dem.data_ptr() + poff * es, dcode, r.width,
-                           None if mask is None else mask.data_ptr() + poff,
-                           r.width, xy, K, code, touched, vals)
+                entries.append((cw, dem.data_ptr() + poff * es, dcode, r.width,
+                                None if mask is None else mask.data_ptr() + poff,
+                                r.width))
+        # one launch for the whole list (linear / nearest): every node walks the
+        # entries from last to first and stops at its first valid hit
+        ctx.interp_multi(entries, xy, K, code, touched, vals)
 
 
 class Mesh:

@@ -1,0 +1,116 @@
+"""N > 1 host logic on CPU: world_size-2 (and 3) gloo process groups exercise
+the same collectives the GPU ranks run over NCCL (vertex all-gather, DEM halo
+rows, min-combine, node shards)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from ocsmesh_b200 import distributed as D, synthetic as S
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, fn, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ret[rank] = fn(rank, world)
+    finally:
+        dist.destroy_process_group()
+
+
+def run_ranks(fn, world=2):
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), fn, ret), nprocs=world, join=True)
+    return [ret[r] for r in range(world)]
+
+
+def test_row_bands_and_node_shards():
+    p = D.RowBands(20000, 8)
+    assert [p.band(r) for r in range(8)][:2] == [(0, 2500), (2500, 5000)]
+    assert p.stored(0) == (0, 2501) and p.stored(3) == (7499, 10001)
+    assert p.stored(7) == (17499, 20000)
+    p = D.RowBands(10, 3)
+    assert [p.band(r) for r in range(3)] == [(0, 4), (4, 7), (7, 10)]
+    assert [p.owner(r) for r in (0, 3, 4, 9)] == [0, 0, 1, 2]
+    with pytest.raises(ValueError):
+        D.RowBands(2, 3)
+    shards = [D.node_shard(10, 4, r) for r in range(4)]
+    assert shards == [(0, 3), (3, 6), (6, 8), (8, 10)]
+
+
+def _gather_case(rank, world):
+    rng = np.random.default_rng(100 + rank)
+    n = [5, 0, 9][rank % 3] + rank          # ragged, one rank may be empty
+    v = torch.from_numpy(rng.random((n, 2)))
+    out = D.all_gather_vertices(v)
+    return v.numpy(), out.numpy()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_all_gather_vertices_ragged(world):
+    res = run_ranks(_gather_case, world)
+    expect = np.concatenate([r[0] for r in res])
+    for _, got in res:
+        np.testing.assert_array_equal(got, expect)
+
+
+def _halo_case(rank, world):
+    H, W = 41, 37
+    z = S.synth_dem(H, W, seed=3)
+    part = D.RowBands(H, world)
+    r0, r1 = part.band(rank)
+    s0, s1 = part.stored(rank)
+    buf = torch.zeros((s1 - s0, W), dtype=torch.float32)
+    buf[r0 - s0:r1 - s0] = torch.from_numpy(z[r0:r1])
+    D.exchange_halo_rows(buf, s0, part, rank)
+    # after the exchange the stored rows equal the raster rows, so the band's
+    # np.gradient (with halos) equals the full-window gradient on owned rows
+    ok = np.array_equal(buf.numpy(), z[s0:s1])
+    g_full = np.gradient(z, 10.0, 10.0)[0][r0:r1]
+    g_band = np.gradient(buf.numpy(), 10.0, 10.0)[0][r0 - s0:r1 - s0]
+    interior = slice(1 if rank == 0 else 0, (r1 - r0) - (1 if rank == world - 1 else 0))
+    return ok and np.array_equal(g_full[interior], g_band[interior])
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_dem_halo_exchange(world):
+    assert all(run_ranks(_halo_case, world))
+
+
+def _min_case(rank, world):
+    rng = np.random.default_rng(rank)
+    strip = torch.from_numpy(rng.random((6, 9)).astype(np.float32))
+    mine = strip.clone()
+    D.min_combine_strip(strip)
+    return mine.numpy(), strip.numpy()
+
+
+def test_min_combine_strip():
+    res = run_ranks(_min_case, 2)
+    expect = np.minimum(res[0][0], res[1][0])
+    for _, got in res:
+        np.testing.assert_array_equal(got, expect)
+
+
+def _nodes_case(rank, world):
+    n = 11
+    k0, k1 = D.node_shard(n, world, rank)
+    vals = torch.arange(k0, k1, dtype=torch.float64) * 1.5
+    return D.all_gather_node_values(vals, n).numpy()
+
+
+def test_all_gather_node_values():
+    for got in run_ranks(_nodes_case, 3):
+        np.testing.assert_array_equal(got, np.arange(11) * 1.5)

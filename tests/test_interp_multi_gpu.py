@@ -1,0 +1,100 @@
+"""ocsb_interp_multi (one launch for a raster list, last valid hit wins) ==
+ocsb_interp called once per raster in list order == the oracle's
+EuclideanMesh2D.interpolate restatement (ocsmesh/mesh/mesh.py:365-376)."""
+import numpy as np
+import pytest
+
+from oracle import ocsmesh_oracle as O
+from ocsmesh_b200 import _lib, synthetic as S
+
+pytestmark = pytest.mark.gpu
+METHOD = {"linear": _lib.INTERP_LINEAR, "nearest": _lib.INTERP_NEAREST,
+          "spline": _lib.INTERP_SPLINE}
+
+
+def make_list(n, h, w, mask_frac, dtype=np.float32):
+    rasters = []
+    for k in range(n):
+        z = S.synth_dem(h, w, seed=60 + k).astype(dtype)
+        tr = list(S.dem_transform(h))
+        tr[2] += 0.6 * w * S.PIXEL * (k % 3)
+        tr[5] += 0.5 * h * S.PIXEL * (k // 3)
+        mask = None
+        if mask_frac and k % 2 == 1:
+            mask = np.random.default_rng(k).random((h, w)) < mask_frac
+            z = z.copy()
+            z[mask] = -99999.0
+        rasters.append(O.OracleRaster(z, tr, mask=mask))
+    return rasters
+
+
+def entries_of(rasters, device):
+    import torch
+    keep, entries = [], []
+    for r in rasters:
+        z = np.ascontiguousarray(r.bands[0])
+        h, w = z.shape
+        m = None if r.mask is None else np.ascontiguousarray(r.mask[0]).astype(np.uint8)
+        if device:
+            z = torch.from_numpy(z).cuda()
+            m = None if m is None else torch.from_numpy(m).cuda()
+        keep.append((z, m))
+        code = _lib.OCSB_F32 if r.bands.dtype == np.float32 else _lib.OCSB_F64
+        win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h)
+        entries.append((win, z, code, w, m, w))
+    return entries, keep
+
+
+@pytest.mark.parametrize("method", ["linear", "nearest"])
+@pytest.mark.parametrize("device", [True, False])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_multi_equals_sequential_and_oracle(ctx, method, device, dtype):
+    import torch
+    rasters = make_list(5, 90, 110, 0.15, dtype)
+    x0, y0, x1, y1 = rasters[0].get_window_bounds(rasters[0].full_window())
+    xy = S.synth_nodes(40000, (x0 - 100, y0 - 100, x1 + 1500, y1 + 600), seed=9)
+    init = np.full(len(xy), np.nan)
+    ref = O.mesh_interpolate(xy, init, rasters, method=method)[:, 0]
+    entries, keep = entries_of(rasters, device)
+    K = len(xy)
+    if device:
+        xyd = torch.from_numpy(xy).cuda()
+        vals = torch.from_numpy(init.copy()).cuda()
+        touched = torch.zeros(K, dtype=torch.uint8, device="cuda")
+        src = torch.full((K,), -1, dtype=torch.int32, device="cuda")
+        ctx.interp_multi(entries, xyd, K, METHOD[method], touched, vals, src)
+        ctx.sync()
+        vals, touched, src = vals.cpu().numpy(), touched.cpu().numpy(), src.cpu().numpy()
+    else:
+        vals, touched = init.copy(), np.zeros(K, np.uint8)
+        src = np.full(K, -1, np.int32)
+        ctx.interp_multi(entries, xy, K, METHOD[method], touched, vals, src)
+    nan = np.isnan(ref)
+    np.testing.assert_array_equal(np.isnan(vals), nan)
+    np.testing.assert_array_equal(vals[~nan], ref[~nan])
+    np.testing.assert_array_equal(touched.astype(bool), ~nan)
+    # source = index of the LAST raster in list order that covers the node
+    exp_src = np.full(K, -1, np.int32)
+    for k, r in enumerate(rasters):
+        mask, _ = O.mesh_interpolate_worker(xy, r, None, method)
+        exp_src[mask] = k
+    np.testing.assert_array_equal(src, exp_src)
+
+
+def test_multi_spline_and_errors(ctx):
+    rasters = make_list(3, 70, 80, 0.0)
+    x0, y0, x1, y1 = rasters[0].get_window_bounds(rasters[0].full_window())
+    xy = S.synth_nodes(5000, (x0, y0, x1 + 900, y1), seed=2)
+    init = np.full(len(xy), np.nan)
+    ref = O.mesh_interpolate(xy, init, rasters, method="spline")[:, 0]
+    entries, keep = entries_of(rasters, False)
+    vals, touched = init.copy(), np.zeros(len(xy), np.uint8)
+    ctx.interp_multi(entries, xy, len(xy), METHOD["spline"], touched, vals)
+    nan = np.isnan(ref)
+    np.testing.assert_array_equal(np.isnan(vals), nan)
+    assert np.abs(vals[~nan] - ref[~nan]).max() < 1e-8
+    with pytest.raises(_lib.OcsbError, match="Invalid value method"):
+        ctx.interp_multi(entries, xy, len(xy), 9, touched, vals)
+    # empty list / no nodes are no-ops
+    ctx.interp_multi([], xy, len(xy), 0, touched, vals)
+    ctx.interp_multi(entries, xy, 0, 0, touched, vals)
