@@ -112,7 +112,8 @@ int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 #define OCSB_KC_SPLINE_PREFILTER  8
 #define OCSB_KC_SPLINE_EVAL       9
 #define OCSB_KC_NEAREST          10
-#define OCSB_KC_COUNT            11
+#define OCSB_KC_BUCKET           11
+#define OCSB_KC_COUNT            12
 int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
 int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
                                 int64_t *launches);
@@ -242,11 +243,24 @@ typedef struct ocsb_interp_raster {
  * list from the last entry to the first and stops at the first entry that
  * yields a value.  source (optional, K int32) receives the index of that
  * entry and is left alone for untouched nodes.  Linear / nearest run as ONE
- * kernel launch; spline entries are prefiltered and evaluated one by one.     */
+ * kernel launch; spline entries are prefiltered and evaluated one by one.
+ * perm (optional, K int32, linear / nearest only): see ocsb_bucket_nodes.     */
 int32_t ocsb_interp_multi(ocsb_ctx *ctx, const ocsb_interp_raster *rasters,
                           int32_t n_rasters, const double *xy, int64_t K,
                           int32_t method, uint8_t *touched, double *values,
-                          int32_t *source);
+                          int32_t *source, const int32_t *perm);
+
+/* Spatial bucketing of nodes (BASELINE.json north_star: "mesh nodes are sharded
+ * by spatial bucket"): counting sort of the K nodes by the cell of a uniform
+ * grid of `cell_size` over bbox = (xmin, ymin, xmax, ymax).  perm_out[i] (K
+ * int32) is the original index of the i-th node in bucket order and
+ * xy_sorted_out (K x 2 float64) the coordinates in that order.  Passing both to
+ * ocsb_interp_multi (xy = xy_sorted, perm = perm) makes a warp's gathers hit
+ * neighbouring texels while touched / values / source are still written at
+ * the ORIGINAL node index, so results are independent of the bucketing.      */
+int32_t ocsb_bucket_nodes(ocsb_ctx *ctx, const double *xy, int64_t K,
+                          const double *bbox4, double cell_size,
+                          int32_t *perm_out, double *xy_sorted_out);
 
 /* Spline prefilter for OCSB_INTERP_SPLINE: builds the tensor-product
  * not-a-knot cubic B-spline coefficients of RectBivariateSpline(kx=ky=3, s=0)

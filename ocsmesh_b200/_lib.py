@@ -20,7 +20,7 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
-KC_COUNT = 11
+KC_COUNT = 12
 NONE = float("nan")
 
 c_i32, c_i64, c_f64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_double, C.c_float, C.c_void_p
@@ -78,7 +78,8 @@ SIGNATURES = {
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
     "ocsb_interp_multi": (c_i32, [c_vp, C.POINTER(ocsb_interp_raster), c_i32,
-                                  c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
+                                  c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "ocsb_bucket_nodes": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_f64, c_vp, c_vp]),
     "ocsb_spline_prefilter": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_vp]),
 }
@@ -251,7 +252,14 @@ class Context:
             ptr(mask), int(mask_stride), ptr(xy), int(K), int(method),
             ptr(touched), ptr(values)))
 
-    def interp_multi(self, entries, xy, K, method, touched, values, source=None):
+    def bucket_nodes(self, xy, K, bbox, cell_size, perm_out, xy_sorted_out):
+        b = (c_f64 * 4)(*[float(v) for v in bbox])
+        check(self.lib.ocsb_bucket_nodes(self.handle, ptr(xy), int(K), b,
+                                         float(cell_size), ptr(perm_out),
+                                         ptr(xy_sorted_out)))
+
+    def interp_multi(self, entries, xy, K, method, touched, values, source=None,
+                     perm=None):
         """``entries``: list of (win, dem, dem_dtype, dem_stride, mask,
         mask_stride) in raster-list order (last valid hit wins)."""
         arr = (ocsb_interp_raster * len(entries))()
@@ -264,7 +272,7 @@ class Context:
             a.mask_stride = int(ms)
         check(self.lib.ocsb_interp_multi(self.handle, arr, len(entries), ptr(xy),
                                          int(K), int(method), ptr(touched),
-                                         ptr(values), ptr(source)))
+                                         ptr(values), ptr(source), ptr(perm)))
 
     def spline_prefilter(self, win, dem, dem_dtype, dem_stride, coef):
         check(self.lib.ocsb_spline_prefilter(

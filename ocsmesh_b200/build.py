@@ -25,6 +25,7 @@ SOURCES = [
     "k_elementwise.cu",
     "k_limiter.cu",
     "k_interp.cu",
+    "k_bucket.cu",
     "k_spline.cu",
     "k_feature.cu",
 ]

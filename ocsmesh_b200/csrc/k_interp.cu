@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(256)
 interp_kernel(const RasterDev *__restrict__ rasters, int n_rasters,
               const double2 *__restrict__ xy, int64_t K,
               uint8_t *__restrict__ touched, double *__restrict__ values,
-              int32_t *__restrict__ source) {
+              int32_t *__restrict__ source, const int32_t *__restrict__ perm) {
     extern __shared__ unsigned char s_raw[];
     RasterDev *s_r = reinterpret_cast<RasterDev *>(s_raw);
     for (int i = threadIdx.x; i < n_rasters * (int)(sizeof(RasterDev) / 8);
@@ -150,9 +150,11 @@ interp_kernel(const RasterDev *__restrict__ rasters, int n_rasters,
                                  ? sample<float, METHOD>(R, p, &v)
                                  : sample<double, METHOD>(R, p, &v);
             if (hit) {
-                __stcs(values + k, v);
-                touched[k] = 1;
-                if (source) source[k] = r;
+                // bucketed input: results go back to the original node index
+                const int64_t o = perm ? (int64_t)__ldg(perm + k) : k;
+                __stcs(values + o, v);
+                touched[o] = 1;
+                if (source) source[o] = r;
                 break;
             }
         }
@@ -170,7 +172,7 @@ AscAxis make_asc(const LinAxis &a) {
 
 int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
                        const double *xy, int64_t K, int method, uint8_t *touched,
-                       double *values, int32_t *source) {
+                       double *values, int32_t *source, const int32_t *perm) {
     std::vector<RasterDev> host(n);
     for (int i = 0; i < n; ++i) {
         RasterDev &R = host[i];
@@ -201,10 +203,10 @@ int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
     OCSB_TIME(ctx, KC_INTERP);
     if (method == OCSB_INTERP_NEAREST)
         interp_kernel<OCSB_INTERP_NEAREST><<<(unsigned)blocks, 256, smem, ctx->stream>>>(
-            dev, n, q, K, touched, values, source);
+            dev, n, q, K, touched, values, source, perm);
     else
         interp_kernel<OCSB_INTERP_LINEAR><<<(unsigned)blocks, 256, smem, ctx->stream>>>(
-            dev, n, q, K, touched, values, source);
+            dev, n, q, K, touched, values, source, perm);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;
@@ -215,5 +217,6 @@ int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
                  int64_t mask_stride, const double *xy, int64_t K, int method,
                  uint8_t *touched, double *values) {
     InterpRaster r{ax, ay, dem, dem_dtype, dem_stride, mask, mask_stride};
-    return k_interp_multi(ctx, &r, 1, xy, K, method, touched, values, nullptr);
+    return k_interp_multi(ctx, &r, 1, xy, K, method, touched, values, nullptr,
+                          nullptr);
 }

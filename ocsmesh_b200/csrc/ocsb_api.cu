@@ -272,7 +272,7 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
     static const char *names[OCSB_KC_COUNT] = {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
-        "spline_eval", "nearest_vertex"};
+        "spline_eval", "nearest_vertex", "bucket_nodes"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
@@ -663,7 +663,7 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
                                      int32_t n_rasters, const double *xy,
                                      int64_t K, int32_t method,
                                      uint8_t *touched, double *values,
-                                     int32_t *source) {
+                                     int32_t *source, const int32_t *perm) {
     CTX_ENTER("ocsb_interp_multi");
     OCSB_REQUIRE(method == OCSB_INTERP_LINEAR || method == OCSB_INTERP_NEAREST ||
                      method == OCSB_INTERP_SPLINE,
@@ -680,8 +680,9 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
             OCSB_TRY(ocsb_interp(ctx, &r.win, r.dem, r.dem_dtype, r.dem_stride,
                                  nullptr, 0, xy, K, method, touched, values));
         }
-        OCSB_REQUIRE(source == nullptr,
-                     "ocsb_interp_multi: source is not available for spline");
+        OCSB_REQUIRE(source == nullptr && perm == nullptr,
+                     "ocsb_interp_multi: source / perm are not available for "
+                     "spline");
         return OCSB_OK;
     }
     std::vector<Staged> sz(n_rasters), sm(n_rasters);
@@ -708,15 +709,16 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
         rs[i].mask = (const uint8_t *)sm[i].dev;
         rs[i].mask_stride = sm[i].dev_stride;
     }
-    Staged sxy, st, sval, ssrc;
+    Staged sxy, st, sval, ssrc, sperm;
+    OCSB_TRY(sperm.init(ctx, perm, 1, K, K, 4, STAGE_IN));
     OCSB_TRY(sxy.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
     OCSB_TRY(st.init(ctx, touched, 1, K, K, 1, STAGE_INOUT));
     OCSB_TRY(sval.init(ctx, values, 1, K, K, 8, STAGE_INOUT));
     OCSB_TRY(ssrc.init(ctx, source, 1, K, K, 4, STAGE_INOUT));
     OCSB_TRY(k_interp_multi(ctx, rs.data(), n_rasters, (const double *)sxy.dev, K,
                             method, (uint8_t *)st.dev, (double *)sval.dev,
-                            (int32_t *)ssrc.dev));
-    bool any = sxy.staged || st.staged || sval.staged || ssrc.staged;
+                            (int32_t *)ssrc.dev, (const int32_t *)sperm.dev));
+    bool any = sperm.staged || sxy.staged || st.staged || sval.staged || ssrc.staged;
     for (auto &s : sz) any = any || s.staged;
     for (auto &s : sm) any = any || s.staged;
     OCSB_TRY(st.finish());
@@ -724,4 +726,24 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
     OCSB_TRY(ssrc.finish());
     if (any) OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
     return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_bucket_nodes(ocsb_ctx *ctx, const double *xy, int64_t K,
+                                     const double *bbox4, double cell_size,
+                                     int32_t *perm_out, double *xy_sorted_out) {
+    CTX_ENTER("ocsb_bucket_nodes");
+    OCSB_REQUIRE(K >= 0 && K < (int64_t)2147483647, "ocsb_bucket_nodes: bad K");
+    if (K == 0) return OCSB_OK;
+    OCSB_REQUIRE(xy && bbox4 && perm_out && xy_sorted_out,
+                 "ocsb_bucket_nodes: NULL buffers");
+    OCSB_REQUIRE(cell_size > 0 && isfinite(cell_size) && isfinite(bbox4[0]) &&
+                     isfinite(bbox4[1]) && isfinite(bbox4[2]) && isfinite(bbox4[3]),
+                 "ocsb_bucket_nodes: bad grid");
+    Staged sxy, sp, ss;
+    OCSB_TRY(sxy.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
+    OCSB_TRY(sp.init(ctx, perm_out, 1, K, K, 4, STAGE_OUT));
+    OCSB_TRY(ss.init(ctx, xy_sorted_out, 1, K * 2, K * 2, 8, STAGE_OUT));
+    OCSB_TRY(k_bucket_nodes(ctx, (const double *)sxy.dev, K, bbox4, cell_size,
+                            (int32_t *)sp.dev, (double *)ss.dev));
+    return finish_call(ctx, {&sxy, &sp, &ss});
 }

@@ -17,7 +17,8 @@ enum {
     KC_LIMITER = OCSB_KC_LIMITER, KC_FEATURE_REFINE = OCSB_KC_FEATURE_REFINE,
     KC_FEATURE_EVAL = OCSB_KC_FEATURE_EVAL, KC_INTERP = OCSB_KC_INTERP,
     KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
-    KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST
+    KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
+    KC_BUCKET = OCSB_KC_BUCKET
 };
 
 // ---------------------------------------------------------------------------
@@ -255,7 +256,11 @@ struct InterpRaster {
 // index of the raster that set each node
 int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
                        const double *xy, int64_t K, int method, uint8_t *touched,
-                       double *values, int32_t *source);
+                       double *values, int32_t *source, const int32_t *perm);
+// counting sort of nodes by grid cell: perm[i] = original index of sorted node i
+int32_t k_bucket_nodes(ocsb_ctx *ctx, const double *xy, int64_t K,
+                       const double bbox[4], double cell, int32_t *perm,
+                       double *xy_sorted);
 int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
                            const void *dem, int dem_dtype, int64_t dem_stride,
                            double *coef);

@@ -175,13 +175,39 @@ class EuclideanMesh2D:
             xy = torch.from_numpy(np.ascontiguousarray(coords[k0:k1])).to(f"cuda:{dev}")
             vals = torch.from_numpy(np.ascontiguousarray(values[k0:k1])).to(f"cuda:{dev}")
             touched = torch.zeros(K, dtype=torch.uint8, device=f"cuda:{dev}")
-            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev)
+            perm = None
+            if method != "spline" and K >= self.BUCKET_MIN_NODES:
+                # spatial buckets: a warp's gathers then hit neighbouring texels
+                xy, perm = self.bucket_nodes(ctx, raster, xy, dev)
+            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev,
+                                perm=perm)
             values[k0:k1] = vals.cpu().numpy()
         self.meshdata.values = values.reshape((values.shape[0], 1))
 
+    #: below this many nodes the bucketing pass costs more than it saves
+    BUCKET_MIN_NODES = 200_000
+
     @staticmethod
-    def _interp_device(ctx, rasters, xy, vals, touched, method, band, dev):
-        """All rasters, in list order, against device-resident node arrays."""
+    def bucket_nodes(ctx, rasters, xy, dev, cell_px: int = 64):
+        """Counting-sort the device node array ``xy`` into cells of ``cell_px``
+        raster pixels over the union of the raster bounding boxes.  Returns
+        ``(xy_sorted, perm)`` for :meth:`_interp_device`."""
+        import torch
+        boxes = np.array([r.get_bbox() for r in rasters])
+        bbox = (boxes[:, 0].min(), boxes[:, 1].min(), boxes[:, 2].max(), boxes[:, 3].max())
+        cell = cell_px * max(abs(rasters[0].dx), abs(rasters[0].dy))
+        K = int(xy.shape[0])
+        perm = torch.empty(K, dtype=torch.int32, device=xy.device)
+        xy_sorted = torch.empty_like(xy)
+        ctx.bucket_nodes(xy, K, bbox, cell, perm, xy_sorted)
+        return xy_sorted, perm
+
+    @staticmethod
+    def _interp_device(ctx, rasters, xy, vals, touched, method, band, dev,
+                       perm=None):
+        """All rasters, in list order, against device-resident node arrays.
+        With ``perm`` the nodes ``xy`` are in bucket order and results are
+        written at the original node index ``perm[i]``."""
         import torch
         code = _METHODS[method]
         K = int(xy.shape[0])
@@ -202,7 +228,7 @@ class EuclideanMesh2D:
                                 r.width))
         # one launch for the whole list (linear / nearest): every node walks the
         # entries from last to first and stops at its first valid hit
-        ctx.interp_multi(entries, xy, K, code, touched, vals)
+        ctx.interp_multi(entries, xy, K, code, touched, vals, perm=perm)
 
 
 class Mesh:

@@ -98,3 +98,46 @@ def test_multi_spline_and_errors(ctx):
     # empty list / no nodes are no-ops
     ctx.interp_multi([], xy, len(xy), 0, touched, vals)
     ctx.interp_multi(entries, xy, 0, 0, touched, vals)
+
+
+def test_bucketed_nodes_give_identical_results(ctx):
+    """ocsb_bucket_nodes + perm: results are written at the original node
+    index, bit-identical to the unbucketed call; perm is a permutation and the
+    sorted coordinates are the permuted input."""
+    import torch
+    rasters = make_list(4, 120, 140, 0.1)
+    boxes = np.array([r.get_window_bounds(r.full_window()) for r in rasters])
+    bbox = (boxes[:, 0].min(), boxes[:, 1].min(), boxes[:, 2].max(), boxes[:, 3].max())
+    xy = S.synth_nodes(300000, (bbox[0] - 300, bbox[1] - 300, bbox[2] + 300, bbox[3] + 300),
+                       seed=5)
+    xy[7] = np.nan                      # NaN coordinates stay untouched
+    K = len(xy)
+    entries, keep = entries_of(rasters, True)
+    xyd = torch.from_numpy(xy).cuda()
+    perm = torch.empty(K, dtype=torch.int32, device="cuda")
+    xys = torch.empty_like(xyd)
+    ctx.bucket_nodes(xyd, K, bbox, 64 * 10.0, perm, xys)
+    ctx.sync()
+    p = perm.cpu().numpy()
+    np.testing.assert_array_equal(np.sort(p), np.arange(K))
+    np.testing.assert_array_equal(xys.cpu().numpy(), xy[p])
+    for method in ("linear", "nearest"):
+        out = []
+        for use_perm in (False, True):
+            vals = torch.full((K,), float("nan"), dtype=torch.float64, device="cuda")
+            touched = torch.zeros(K, dtype=torch.uint8, device="cuda")
+            src = torch.full((K,), -1, dtype=torch.int32, device="cuda")
+            if use_perm:
+                ctx.interp_multi(entries, xys, K, METHOD[method], touched, vals, src, perm)
+            else:
+                ctx.interp_multi(entries, xyd, K, METHOD[method], touched, vals, src)
+            ctx.sync()
+            out.append((vals.cpu().numpy(), touched.cpu().numpy(), src.cpu().numpy()))
+        np.testing.assert_array_equal(out[0][0], out[1][0])
+        np.testing.assert_array_equal(out[0][1], out[1][1])
+        np.testing.assert_array_equal(out[0][2], out[1][2])
+    # host buffers through the C ABI
+    ph = np.zeros(1000, np.int32)
+    xh = np.zeros((1000, 2))
+    ctx.bucket_nodes(xy[:1000].copy(), 1000, bbox, 640.0, ph, xh)
+    np.testing.assert_array_equal(np.sort(ph), np.arange(1000))
