@@ -155,7 +155,10 @@ int32_t ocsb_hfun_clamp(ocsb_ctx *ctx, float *hfun, int64_t row_stride,
  *   tree = cKDTree(points); d = tree.query(xy[, distance_upper_bound=r])
  *   v = float32(rate*target*d + target); clamp [hmin,hmax]; new = min(old, v)
  * verts_xy : nv x 2 float64, the resampled feature vertices ("points", :1230)
- * hfun_old : window of the PRE-op hfun (the reference reads self.src)
+ * hfun_old : window of the PRE-op hfun (the reference reads self.src), or
+ *            NULL = the raster is still in its A4 initial state (every pixel
+ *            finfo(float32).max, ocsmesh/hfun/raster.py:75-82): the kernel
+ *            then neither needs the fill pass nor reads 4 B/px
  * hfun_new : window of the POST-op hfun (may alias hfun_old)
  * hmin/hmax: the HfunRaster's global bounds, NaN = None.  hmax "truthy"
  *            (not None, != 0) selects the bounded query, exactly as :1240.
@@ -186,6 +189,7 @@ int32_t ocsb_nearest_vertex(ocsb_ctx *ctx, const double *verts_xy, int64_t nv,
  * Body of the window loop of HfunRaster.add_subtidal_flow_limiter
  *                                                         ocsmesh/hfun/raster.py:1396-1435
  * dem      : window of the DEM band (dem_dtype OCSB_F32 / OCSB_F64)
+ * hfun_old : as for ocsb_hfun_feature (NULL = A4 initial state)
  * dx, dy   : Raster.dx, Raster.dy (np.gradient(z, dx, dy): dx spaces axis 0!)
  * hmin,hmax,lower_bound,upper_bound : the method's arguments, NaN = None
  * ghmin,ghmax : the HfunRaster's global bounds (self._hmin/_hmax), NaN = None

@@ -568,16 +568,35 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         const float finf = std::numeric_limits<float>::infinity();
         E.lo = a.has_hmin ? a.hmin_f : -finf;
         E.hi = a.has_hmax ? a.hmax_f : finf;
-        E.fast_ok = (a.rate_target >= 0.0 && a.target >= 0.0) ? 1 : 0;
+        // the fast size law needs v64 = rt*d + target to be a normal float32
+        // with |error| <= 2^-39 v64: rt, target >= 0, target not tiny, no
+        // overflow for d <= 1e15
+        E.fast_ok = (a.rate_target >= 0.0 && a.rate_target <= 1e15 &&
+                     a.target >= 1e-30 && a.target <= 1e30) ? 1 : 0;
+        {
+            auto hi_word = [](double v) {
+                uint64_t b; memcpy(&b, &v, 8); return (uint32_t)(b >> 32);
+            };
+            const double d2max = (bounded && r2 < 1e30) ? r2 : 1e30;
+            const uint32_t lo = hi_word(1e-30) + 1, hi = hi_word(d2max);
+            E.hi_lo = lo;
+            E.hi_span = (E.fast_ok && d2max > 1e-29 && hi > lo) ? hi - lo : 0u;
+            E.v_far_f = (float)E.v_far;
+            E.old_const = std::numeric_limits<float>::max();
+        }
         E.fuse_clamp = a.fuse_clamp;
-        E.vec_old = (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
+        E.vec_old = old_ && (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
         E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
         E.overflow = overflow;
         OCSB_TIME(ctx, KC_FEATURE_EVAL);
-        if (idx_out || dist_out)
-            eval_kernel<true><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
-        else
-            eval_kernel<false><<<(unsigned)lv[0].ntiles, kEvalThreads, 0, ctx->stream>>>(E);
+        const unsigned egrid = (unsigned)lv[0].ntiles;
+        if (idx_out || dist_out) {
+            if (old_) eval_kernel<true, true><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
+            else eval_kernel<true, false><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
+        } else {
+            if (old_) eval_kernel<false, true><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
+            else eval_kernel<false, false><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
+        }
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
 

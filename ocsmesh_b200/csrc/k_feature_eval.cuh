@@ -16,12 +16,18 @@
 // Exactness of the epilogue.  The reference value is
 //   v = float32( fl(fl(rt * RN(sqrt(d2))) + target) )        (all f64)
 // RN(sqrt) in f64 costs ~28 instructions/pixel, which dominated the first
-// version of this kernel.  The fast path computes d = sqrt(d2) to 2^-42
-// relative (MUFU.RSQ seed + one f64 Newton step), forms v64 the same way and
-// accepts it only if the 29 mantissa bits that the f32 rounding drops are not
-// within 2^14 ulp64 of the round-to-nearest tie -- then float32(v64) is
-// provably the reference's float32; otherwise (1 pixel in 16 k) it falls back
-// to __dsqrt_rn.  Requesting dist_out / idx_out selects the exact path.
+// version of this kernel.  The fast path computes d = sqrt(d2) to 2^-39.4
+// relative (MUFU.RSQ64H seed, measured 2^-20.0 on B200 by tools/ubench, + one
+// f64 Newton step), forms v64 the same way and accepts it only if the 29
+// mantissa bits that the f32 rounding drops are not within 2^15 ulp64 of the
+// round-to-nearest tie -- then float32(v64) is provably the reference's
+// float32; otherwise (1 pixel in 8 k) it falls back to __dsqrt_rn.  The
+// domain of the fast path (1e-30 < d2 < min(r^2, 1e30), decided on the high
+// word) and the tie test are integer ops on the two halves of the doubles:
+// on sm_100 the XU pipe (F2F, MUFU) issues one warp instruction per 8 cycles
+// and the ALU pipe one per 2, so conversions and compare+select pairs are
+// what the epilogue has to avoid.  Requesting dist_out / idx_out selects the
+// exact path.
 #pragma once
 
 struct EvalArgs {
@@ -39,7 +45,10 @@ struct EvalArgs {
     double v_far;           // fl(fl(rate_target * r) + target): beyond the radius
     float lo, hi;           // f32-rounded [hmin, hmax], -/+inf when None
     int fuse_clamp;
-    int fast_ok;            // rate_target >= 0 && target >= 0: error bound holds
+    int fast_ok;            // parameters in the range the error bound covers
+    unsigned hi_lo, hi_span;  // fast domain on the high word of d2
+    float v_far_f;          // float32(v_far)
+    float old_const;        // pre-op value everywhere when old_ == nullptr
     int vec_old, vec_new;
     const int *overflow;
 };
@@ -56,12 +65,6 @@ __device__ __forceinline__ float min_nan_f32(float a, float b) {
     return r;
 }
 
-__device__ __forceinline__ float rsqrt_approx(float x) {
-    float r;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-
 __device__ __forceinline__ bool dominated_smem(const WarpScratch &W,
                                                const CornerD2 &v) {
     bool dom = false;
@@ -74,27 +77,44 @@ __device__ __forceinline__ bool dominated_smem(const WarpScratch &W,
     return dom;
 }
 
-// float32 of the size law for squared distance d2 (see header comment)
-__device__ __forceinline__ float size_law_f32(double d2, const EvalArgs &A) {
-    const bool hit = d2 < A.r2;
-    // fast path (evaluated for every lane; garbage for out-of-range d2)
-    const float y32 = rsqrt_approx((float)d2);
-    const double y = (double)y32;
-    const double g = d2 * y;
-    const double e = fma(-g, g, d2);
-    const double d = fma(e, 0.5 * y, g);
-    double v64 = __dadd_rn(__dmul_rn(A.rate_target, d), A.target);
-    const unsigned low = (unsigned)__double2loint(v64) & 0x1fffffffu;
-    const bool near_tie = (unsigned)abs((int)low - 0x10000000) < (1u << 14);
-    const bool in_range = d2 > 1e-30 && d2 < 1e30;
-    if (hit && (near_tie || !in_range || !A.fast_ok)) {
-        const double dd = __dsqrt_rn(d2);
-        v64 = __dadd_rn(__dmul_rn(A.rate_target, dd), A.target);
-    }
-    return (float)(hit ? v64 : A.v_far);
+__device__ __forceinline__ float max_nan_f32(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
 }
 
-template <bool WANT_OUT>
+__device__ __forceinline__ double rsqrt_approx_f64(double x) {
+    double r;   // MUFU.RSQ64H: ~20-bit seed from the high word, no conversions
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    return r;
+}
+
+// float32 of the size law for squared distance d2 (see header comment)
+__device__ __forceinline__ float size_law_f32(double d2, const EvalArgs &A) {
+    // fast path, evaluated unconditionally (garbage outside its domain)
+    const double y = rsqrt_approx_f64(d2);
+    const double g = d2 * y;
+    const double e = fma(-g, g, d2);
+    const double d = fma(e * y, 0.5, g);
+    const double v64 = __dadd_rn(__dmul_rn(A.rate_target, d), A.target);
+    // domain: hi_lo <= hi(d2) < hi_lo + hi_span  (1e-30 < d2 < min(r2, 1e30))
+    const bool in_dom = (unsigned)(__double2hiint(d2) - (int)A.hi_lo) < A.hi_span;
+    // the 29 dropped bits, shifted to the top of a word: tie at 2^31
+    const unsigned t = ((unsigned)__double2loint(v64) << 3) - (0x80000000u - (1u << 18));
+    const bool near_tie = t < (1u << 19);
+    float vf = (float)v64;
+    if (!in_dom || near_tie) {
+        if (d2 < A.r2) {
+            const double dd = __dsqrt_rn(d2);
+            vf = (float)__dadd_rn(__dmul_rn(A.rate_target, dd), A.target);
+        } else {
+            vf = A.v_far_f;
+        }
+    }
+    return vf;
+}
+
+template <bool WANT_OUT, bool HAS_OLD>
 __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
     __shared__ double2 s_v[kCandCap];
     __shared__ int s_id[kCandCap];
@@ -135,7 +155,8 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) o[j][k] = 0.f;
+            for (int k = 0; k < 4; ++k) o[j][k] = A.old_const;
+            if (!HAS_OLD) continue;
             if (grow[j] > r1 || gcol > c1) continue;
             const float *orow = A.old_ + (int64_t)(g.row0 + grow[j]) * A.os;
             if (A.vec_old && full) {
@@ -238,7 +259,10 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
                                     bid[j * 4 + k] = vid;
                                 }
                             } else {
-                                best[j * 4 + k] = fmin(best[j * 4 + k], d2);
+                                // d2 is never NaN (finite coordinates): a
+                                // compare + select, not the 7-op IEEE fmin
+                                best[j * 4 + k] =
+                                    (d2 < best[j * 4 + k]) ? d2 : best[j * 4 + k];
                             }
                         }
                 }
@@ -270,12 +294,17 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
                 } else {
                     vf = size_law_f32(d2, A);
                 }
-                vf = (vf < A.lo) ? A.lo : vf;
-                vf = (vf > A.hi) ? A.hi : vf;
-                float res = min_nan_f32(o[j][k], vf);
+                // reference: clamp(vf); min(old, .); [A10: clamp again].  The
+                // clamp is monotone and idempotent, so with A10 fused
+                // clamp(min(old, clamp(vf))) == clamp(min(old, vf)); max.NaN /
+                // min.NaN keep NaN like the reference's compares do.
+                float res;
                 if (A.fuse_clamp) {
-                    res = (res < A.lo) ? A.lo : res;
-                    res = (res > A.hi) ? A.hi : res;
+                    res = min_nan_f32(o[j][k], vf);
+                    res = min_nan_f32(max_nan_f32(res, A.lo), A.hi);
+                } else {
+                    vf = min_nan_f32(max_nan_f32(vf, A.lo), A.hi);
+                    res = min_nan_f32(o[j][k], vf);
                 }
                 out[k] = res;
             }

@@ -439,8 +439,8 @@ extern "C" int32_t ocsb_hfun_feature(
                  "ocsb_hfun_feature: empty vertex set (cKDTree needs a "
                  "non-empty (N,2) array)");
     OCSB_REQUIRE(nv < (int64_t)2147483647, "ocsb_hfun_feature: nv too large");
-    OCSB_REQUIRE(hfun_old && hfun_new && old_stride >= win->width &&
-                     new_stride >= win->width,
+    OCSB_REQUIRE(hfun_new && new_stride >= win->width &&
+                     (!hfun_old || old_stride >= win->width),
                  "ocsb_hfun_feature: bad hfun buffers");
     OCSB_REQUIRE(!ocsb_is_none(target_size) && target_size > 0,
                  "Argument target_size must be greater than zero.");
@@ -478,7 +478,9 @@ extern "C" int32_t ocsb_hfun_feature(
     if (alias) {
         OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_INOUT, rb));
     } else {
-        OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN, rb));
+        // hfun_old == NULL: the pre-op raster is the A4 initial state
+        if (hfun_old)
+            OCSB_TRY(so.init(ctx, hfun_old, h, w, old_stride, 4, STAGE_IN, rb));
         OCSB_TRY(sn.init(ctx, hfun_new, h, w, new_stride, 4, STAGE_OUT, rb));
     }
     OCSB_TRY(sd.init(ctx, dist_out, h, w, w, 8, STAGE_OUT, rb));
@@ -530,8 +532,9 @@ extern "C" int32_t ocsb_hfun_flow_limiter(
     OCSB_REQUIRE(win->width >= 2 && win->height >= 2,
                  "Shape of array too small to calculate a numerical gradient, "
                  "at least (edge_order + 1) elements are required.");
-    OCSB_REQUIRE(dem && hfun_old && hfun_new && dem_stride >= win->width &&
-                     old_stride >= win->width && new_stride >= win->width,
+    OCSB_REQUIRE(dem && hfun_new && dem_stride >= win->width &&
+                     (!hfun_old || old_stride >= win->width) &&
+                     new_stride >= win->width,
                  "ocsb_hfun_flow_limiter: bad buffers");
     OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
                  "ocsb_hfun_flow_limiter: dx/dy is NaN");
@@ -549,7 +552,8 @@ extern "C" int32_t ocsb_hfun_flow_limiter(
     if (alias) {
         OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_INOUT, rb));
     } else {
-        OCSB_TRY(so.init(ctx, hfun_old, hb, w, old_stride, 4, STAGE_IN, rb));
+        if (hfun_old)
+            OCSB_TRY(so.init(ctx, hfun_old, hb, w, old_stride, 4, STAGE_IN, rb));
         OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_OUT, rb));
     }
     LimiterArgs a{dx, dy, hmin, hmax, lower_bound, upper_bound, ghmin, ghmax,

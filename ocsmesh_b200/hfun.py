@@ -90,9 +90,13 @@ class HfunRaster:
             if init.shape != (h, w):
                 raise ValueError("initial_value does not match the raster shape")
             self._hfun.copy_(torch.from_numpy(np.ascontiguousarray(init)))
+            self._pristine = False
         else:
-            # hfun/raster.py:75-82: every pixel = finfo(float32).max
-            ctx.fill_f32(self._hfun, h * w, FLT_MAX)
+            # hfun/raster.py:75-82: every pixel = finfo(float32).max.  The
+            # fill is folded into the first add_* (the kernels take "pre-op
+            # raster = initial state" as a NULL old pointer); it only runs
+            # as a kernel of its own when someone looks at the raster first.
+            self._pristine = True
 
     # ---- plumbing -----------------------------------------------------------
     def _ctx(self) -> _lib.Context:
@@ -111,7 +115,18 @@ class HfunRaster:
 
     def reset(self) -> None:
         """Back to the initial state: every pixel = finfo(float32).max."""
-        self._ctx().fill_f32(self._hfun, self._hfun.numel(), FLT_MAX)
+        self._pristine = True
+
+    def _materialize(self) -> None:
+        """Write the pending initial fill (A4) if no op has absorbed it."""
+        if self._pristine:
+            self._ctx().fill_f32(self._hfun, self._hfun.numel(), FLT_MAX)
+            self._pristine = False
+
+    def _old_ptr(self, t, window: Window):
+        """Pre-op window pointer, or None while the raster is still in its
+        initial state (every pixel finfo(float32).max)."""
+        return None if self._pristine else self._hfun_ptr(t, window)
 
     def _hfun_ptr(self, t, window: Window) -> int:
         """(Virtual) address of the window's top-left pixel in buffer ``t``."""
@@ -181,6 +196,7 @@ class HfunRaster:
     @property
     def device_values(self):
         """The float32 (h, w) size raster as a CUDA tensor (no copy)."""
+        self._materialize()
         return self._hfun
 
     @property
@@ -213,6 +229,7 @@ class HfunRaster:
         ``out``: optional (pinned) CPU torch tensor to receive the values."""
         if band not in (None, 1):
             raise IndexError("the hfun raster has a single band")
+        self._materialize()
         t = self._hfun
         if window is not None:
             a = window.row_off - self._band[0]
@@ -263,6 +280,7 @@ class HfunRaster:
         w = self.width
         rb, re = self._band
         ctx = self._ctx()
+        self._materialize()
         ctx.hfun_clamp(self._hfun, w, w, re - rb, self._hmin, self._hmax)
 
     def _fuse_clamp(self) -> bool:
@@ -339,18 +357,21 @@ class HfunRaster:
         fuse = self._fuse_clamp()
         w = self.width
         old = self._hfun
-        new = old.clone() if self._needs_double_buffer(windows) else old
+        new = old
+        if not self._pristine and self._needs_double_buffer(windows):
+            new = old.clone()
         for win in windows:
             band = self._band_of(win)
             if band is None:
                 continue
             cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
                                win.height, band[0], band[1])
-            ctx.hfun_feature(cw, verts, nv, self._hfun_ptr(old, win), w,
+            ctx.hfun_feature(cw, verts, nv, self._old_ptr(old, win), w,
                              self._hfun_ptr(new, win), w, expansion_rate,
                              target_size, self._hmin, self._hmax,
                              fuse_clamp=fuse)
         self._hfun = new
+        self._pristine = False
         # keep `verts` alive until the stream has consumed it
         self._last_verts = verts
 
@@ -372,7 +393,9 @@ class HfunRaster:
         es = dem.element_size()
         code = _dem_dtype_code(dem)
         old = self._hfun
-        new = old.clone() if self._needs_double_buffer(windows) else old
+        new = old
+        if not self._pristine and self._needs_double_buffer(windows):
+            new = old.clone()
         dx, dy = self._raster.dx, self._raster.dy
         for win in windows:
             band = self._band_of(win)
@@ -387,10 +410,11 @@ class HfunRaster:
             poff = (win.row_off - dem_origin) * w + win.col_off
             ctx.hfun_flow_limiter(
                 cw, dem.data_ptr() + poff * es, code, w,
-                self._hfun_ptr(old, win), w, self._hfun_ptr(new, win), w,
+                self._old_ptr(old, win), w, self._hfun_ptr(new, win), w,
                 dx, dy, hmin, hmax, lower_bound, upper_bound, self._hmin,
                 self._hmax, fuse_clamp=fuse)
         self._hfun = new
+        self._pristine = False
 
     def add_gradient_delimiter(self, hmin: Optional[float] = None,
                                hmax: Optional[float] = None) -> None:
@@ -410,6 +434,7 @@ class HfunRaster:
         if (window.width, window.height) != (other_window.width, other_window.height):
             raise ValueError("windows must have the same shape")
         src = other.device_values
+        self._materialize()
         if src.device != self._hfun.device:
             src = src.to(self._hfun.device)
         ctx = self._ctx()

@@ -180,3 +180,41 @@ def test_fast_size_law_is_bit_exact(ctx, rate, target, hmin, hmax):
     # and the exact (dist/idx) variant agrees with the fast one
     out2, _, _ = run_gpu(ctx, r, pts, old, rate, target, hmin, hmax, want=True)
     np.testing.assert_array_equal(out2, out)
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+@pytest.mark.parametrize("hmax", [1500.0, None])
+def test_null_old_is_initial_state(ctx, fuse, hmax):
+    """hfun_old == NULL means "the raster is still finfo(float32).max
+    everywhere" (A4): same bits as passing that buffer, device and host."""
+    import torch
+    h, w = 515, 389
+    r, pts = make_case(h, w, 21, n_lines=3)
+    old = np.full((h, w), FLT_MAX, np.float32)
+    ref = run_gpu(ctx, r, pts, old, 0.001, 100.0, 100.0, hmax, fuse=fuse)
+    win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, 0, 0)
+    nd = torch.full((h, w), -7.0, dtype=torch.float32, device="cuda")
+    vd = torch.from_numpy(np.ascontiguousarray(pts)).cuda()
+    ctx.hfun_feature(win, vd, len(pts), None, w, nd, w, 0.001, 100.0, 100.0,
+                     hmax, fuse)
+    ctx.sync()
+    np.testing.assert_array_equal(nd.cpu().numpy(), ref)
+    new = np.full((h, w), -7.0, np.float32)
+    ctx.hfun_feature(win, np.ascontiguousarray(pts), len(pts), None, w, new, w,
+                     0.001, 100.0, 100.0, hmax, fuse)
+    np.testing.assert_array_equal(new, ref)
+
+
+def test_fast_size_law_edge_distances(ctx):
+    """Pixels that coincide with a vertex (d = 0), sit beyond the radius, or
+    make the size law land next to a float32 rounding tie all leave the fast
+    path; a dense vertex lattice makes the first two common."""
+    h, w = 257, 300
+    r, _ = make_case(h, w, 1)
+    xy = r.get_xy()
+    pts = np.ascontiguousarray(xy.reshape(h, w, 2)[::16, ::16].reshape(-1, 2))
+    old = np.full((h, w), FLT_MAX, np.float32)
+    for rate, target, hmin, hmax in [(0.01, 10.0, 1.0, 10.5), (0.5, 3.0, None, None)]:
+        ref = O.add_feature_window(old, pts, xy, h, w, rate, target, hmin, hmax)
+        out = run_gpu(ctx, r, pts, old, rate, target, hmin, hmax)
+        np.testing.assert_array_equal(out, ref)

@@ -150,3 +150,66 @@ def test_constant_division_is_ieee(ctx, dxdy, dtype):
     a, b = out[~m], np.ma.getdata(ref)[~m]
     np.testing.assert_array_equal(np.isnan(a), np.isnan(b))
     np.testing.assert_array_equal(a[~np.isnan(a)], b[~np.isnan(b)])
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+@pytest.mark.parametrize("band", [(None, None), (-30.0, 0.0)])
+def test_fast_path_fallbacks(ctx, fuse, band):
+    """The float32 fast path (unguarded sqrt/div/Markstein sequences + one
+    range test per 4-pixel group) must hand every group it cannot prove to the
+    IEEE path: plateaus that do not line up with the 4-pixel groups, exact
+    zeros on a slope, subnormal / tiny / huge elevations, nodata-like
+    -3.4e38 blocks, all inside an otherwise ordinary DEM."""
+    rng = np.random.default_rng(23)
+    z = S.synth_dem(333, 1031, seed=6)
+    z[20:41, 33:71] = 2.5                      # plateau, ragged w.r.t. groups
+    z[60:64, 101:107] = 0.0                    # zeros next to a slope
+    z[90, 200:260] = 0.0                       # zero row on a slope
+    z[100:130, 300:350] *= np.float32(1e-36)   # subnormal differences
+    z[140:170, 400:460] *= np.float32(1e-22)   # tiny but normal
+    z[180:200, 500:540] *= np.float32(1e28)    # huge
+    z[210:240, 600:650] = np.float32(-3.4028235e38)   # nodata-like block
+    z[250:260, 700:710] = rng.normal(size=(10, 10)).astype(np.float32) * np.float32(1e19)
+    old = (rng.random(z.shape) * 3000 + 1).astype(np.float32)
+    old[rng.random(z.shape) < 0.5] = FLT_MAX
+    lb, ub = band
+    with np.errstate(all="ignore"):
+        ref = O.flow_limiter_window(z, old, 10.0, 10.0, 50.0, 1500.0, lb, ub,
+                                    100.0, 1500.0)
+        ref = np.ma.getdata(ref)
+        if fuse:
+            ref = O.apply_constraints_clamp(ref, 100.0, 1500.0)
+    out = run_gpu(ctx, z, old, 10.0, 10.0, 50.0, 1500.0, lb, ub, 100.0, 1500.0,
+                  fuse=fuse)
+    np.testing.assert_array_equal(out, ref)
+    # raw values, no bounds at all (nothing hides a wrong bit)
+    with np.errstate(all="ignore"):
+        ref = O.flow_limiter_window(z, old, 10.0, 10.0, None, None, None, None,
+                                    None, None)
+    out = run_gpu(ctx, z, old, 10.0, 10.0, None, None, None, None, None, None)
+    m = np.ma.getmaskarray(ref)
+    a, b = out[~m], np.ma.getdata(ref)[~m]
+    np.testing.assert_array_equal(np.isnan(a), np.isnan(b))
+    np.testing.assert_array_equal(a[~np.isnan(a)], b[~np.isnan(b)])
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+def test_null_old_is_initial_state(ctx, fuse):
+    import torch
+    z = S.synth_dem(301, 517, seed=8)
+    old = np.full(z.shape, FLT_MAX, np.float32)
+    h, w = z.shape
+    for lb, ub in [(None, None), (-30.0, 0.0)]:
+        ref = run_gpu(ctx, z, old, 10.0, 10.0, 50.0, 1500.0, lb, ub, 100.0,
+                      1500.0, fuse=fuse)
+        win = _lib.make_win((0.0, 0.0, float(w), float(h)), w, h, 0, 0)
+        nd = torch.full((h, w), -7.0, dtype=torch.float32, device="cuda")
+        ctx.hfun_flow_limiter(win, torch.from_numpy(z).cuda(), _lib.OCSB_F32, w,
+                              None, w, nd, w, 10.0, 10.0, 50.0, 1500.0, lb, ub,
+                              100.0, 1500.0, fuse)
+        ctx.sync()
+        np.testing.assert_array_equal(nd.cpu().numpy(), ref)
+        new = np.full((h, w), -7.0, np.float32)
+        ctx.hfun_flow_limiter(win, z, _lib.OCSB_F32, w, None, w, new, w, 10.0,
+                              10.0, 50.0, 1500.0, lb, ub, 100.0, 1500.0, fuse)
+        np.testing.assert_array_equal(new, ref)
