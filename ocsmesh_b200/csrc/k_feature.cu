@@ -589,7 +589,7 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
         E.overflow = overflow;
         OCSB_TIME(ctx, KC_FEATURE_EVAL);
-        const unsigned egrid = (unsigned)lv[0].ntiles;
+        const dim3 egrid((unsigned)lv[0].ntx, (unsigned)lv[0].nty);
         if (idx_out || dist_out) {
             if (old_) eval_kernel<true, true><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
             else eval_kernel<true, false><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);

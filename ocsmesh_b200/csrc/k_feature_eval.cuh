@@ -1,8 +1,8 @@
 // K1 evaluation kernel (included by k_feature.cu inside its anonymous
 // namespace): fused leaf filter + exact nearest-vertex distance + size law.
 //
-// One CTA per 64x64 tile, one warp per 32x8-pixel leaf, one lane per 4x2
-// pixels.  Per leaf:
+// One CTA per 64x64 tile, one warp per 32x16-pixel rect = two 32x8 leaves, one
+// lane per 4x2 pixels of a leaf.  Per rect:
 //   pass A  lane = candidate: the 5 dominators (nearest to the leaf centre and
 //           to its 4 corners) by redux.sync min; their corner distances go to
 //           a per-warp shared table (they are warp-uniform, so keeping them
@@ -11,6 +11,10 @@
 //           into per-warp shared memory (ballot + popc), then every lane
 //           evaluates its 8 pixels against each survivor read as one LDS.128
 //           broadcast
+//   Both passes run once per 32x16 rect (two stacked leaves): the filter is
+//   warp-level work that does not shrink with the rect, the survivor list
+//   barely grows, so sharing it between the two leaves halves its cost per
+//   pixel.  More than kSurvCap survivors -> the leaves re-filter chunk-wise.
 //   epilogue  float32(rate*target*sqrt(d2) + target), clamps, min(old, .)
 //
 // Exactness of the epilogue.  The reference value is
@@ -53,10 +57,13 @@ struct EvalArgs {
     const int *overflow;
 };
 
+constexpr int kSubH = 16;   // filter rect: kLeafW x kSubH px = two stacked leaves
+constexpr int kSurvCap = 64;
+
 struct WarpScratch {
     double dom[5][4];       // dominator corner distances (inflated by 1+eps)
-    double2 sv[32];         // compacted survivors of one 32-candidate chunk
-    int sid[32];
+    double2 sv[kSurvCap];   // compacted survivors of the warp's filter rect
+    int sid[kSurvCap];
 };
 
 __device__ __forceinline__ float min_nan_f32(float a, float b) {
@@ -120,8 +127,8 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
     __shared__ int s_id[kCandCap];
     __shared__ WarpScratch s_w[kEvalThreads / 32];
     if (*A.overflow) return;
-    const int t = blockIdx.x;
-    const int tx = t % A.lvl.ntx, ty = t / A.lvl.ntx;
+    const int tx = blockIdx.x, ty = blockIdx.y;
+    const int t = ty * A.lvl.ntx + tx;
     const int cnt = A.lvl.cnt[t];
     const int off = A.lvl.off[t];
     const bool in_smem = cnt <= kCandCap;
@@ -138,45 +145,26 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
     const Geom &g = A.g;
     WarpScratch &W = s_w[wid];
 
-    for (int leaf = wid; leaf < 16; leaf += kEvalThreads / 32) {
-        const int c0 = tx * kTile0 + (leaf & 1) * kLeafW;
-        const int r0 = ty * kTile0 + (leaf >> 1) * kLeafH;
-        if (c0 >= g.w || r0 >= g.h) continue;
+    // candidate i of the tile list (lane = candidate)
+    auto load_cand = [&](int i, double2 &v, int &id) {
+        if (in_smem) { v = s_v[i]; id = s_id[i]; }
+        else { id = A.lvl.ids[off + i]; v = A.verts[id]; }
+    };
+
+    for (int sub = wid; sub < 2 * (kTile0 / kSubH); sub += kEvalThreads / 32) {
+        const int c0 = tx * kTile0 + (sub & 1) * kLeafW;
+        const int R0 = ty * kTile0 + (sub >> 1) * kSubH;
+        if (c0 >= g.w || R0 >= g.h) continue;
         const int c1 = min(g.w, c0 + kLeafW) - 1;
-        const int r1 = min(g.h, r0 + kLeafH) - 1;
-
-        // this lane's pixels: 4 consecutive columns x 2 rows (row, row + 4)
+        const int R1 = min(g.h, R0 + kSubH) - 1;
         const int gcol = c0 + (lane & 7) * 4;
-        const int grow[2] = {r0 + (lane >> 3), r0 + (lane >> 3) + 4};
         const bool full = gcol + 3 <= c1;
+        const Rect q = tile_rect(g, c0, c1, R0, R1);
 
-        // old hfun values: issued first, consumed in the epilogue
-        float o[2][4];
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) o[j][k] = A.old_const;
-            if (!HAS_OLD) continue;
-            if (grow[j] > r1 || gcol > c1) continue;
-            const float *orow = A.old_ + (int64_t)(g.row0 + grow[j]) * A.os;
-            if (A.vec_old && full) {
-                const float4 v4 = __ldcs(reinterpret_cast<const float4 *>(orow + gcol));
-                o[j][0] = v4.x; o[j][1] = v4.y; o[j][2] = v4.z; o[j][3] = v4.w;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (gcol + k <= c1) o[j][k] = orow[gcol + k];
-            }
-        }
-
-        double best[8];
-        int bid[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { best[k] = INFINITY; bid[k] = 0x7fffffff; }
-
+        // ---- pass A: dominators (nearest to centre and corners) ------------
+        int ns = 0;
+        bool refilter = false;
         if (cnt > 0) {
-            const Rect q = tile_rect(g, c0, c1, r0, r1);
-            // ---- pass A: dominators (nearest to centre and corners) --------
             unsigned domkey[5];
 #pragma unroll
             for (int j = 0; j < 5; ++j) domkey[j] = 0xffffffffu;
@@ -184,7 +172,8 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
                 const int i = b0 + lane;
                 const bool valid = i < cnt;
                 double2 v = make_double2(0.0, 0.0);
-                if (valid) v = in_smem ? s_v[i] : A.verts[A.lvl.ids[off + i]];
+                int id = 0;
+                if (valid) load_cand(i, v, id);
                 const CornerD2 c = corner_d2(q, v);
                 const double dd[5] = {center_d2(q, v), c.d00, c.d01, c.d10, c.d11};
 #pragma unroll
@@ -203,119 +192,179 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
                 }
             }
             __syncwarp();
+        }
 
-            // this lane's pixel coordinates
-            double px[4], py[2];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-                py[j] = lin_at(g.ay, g.row0 + min(grow[j], g.h - 1));
-
-            // ---- pass B: filter, compact, evaluate survivors ----------------
+        // ---- pass B: radius + dominance filter of one 32-candidate chunk;
+        // survivors are appended at W.sv[base ...]; returns their number (they
+        // are only stored while they fit)
+        auto filter_chunk = [&](int b0, int base) -> int {
+            const int i = b0 + lane;
+            const bool valid = i < cnt;
+            double2 v = make_double2(0.0, 0.0);
+            int id = 0;
+            if (valid) load_cand(i, v, id);
+            const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                              !dominated_smem(W, corner_d2(q, v));
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            const int n = __popc(mask);
+            if (keep && base + n <= kSurvCap) {
+                const int pos = base + __popc(mask & lt_mask);
+                W.sv[pos] = v;
+                if (WANT_OUT) W.sid[pos] = id;
+            }
+            return n;
+        };
+        if (cnt > 0) {
             for (int b0 = 0; b0 < cnt; b0 += 32) {
-                const int i = b0 + lane;
-                const bool valid = i < cnt;
-                double2 v = make_double2(0.0, 0.0);
-                int id = 0;
-                if (valid) {
-                    if (in_smem) { v = s_v[i]; id = s_id[i]; }
-                    else { id = A.lvl.ids[off + i]; v = A.verts[id]; }
+                const int n = filter_chunk(b0, ns);
+                if (ns + n > kSurvCap) { refilter = true; break; }
+                ns += n;
+            }
+            __syncwarp();
+        }
+
+        // this lane's pixel columns
+        double px[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) px[k] = lin_at(g.ax, min(gcol + k, g.w - 1));
+
+        for (int half = 0; half < kSubH / kLeafH; ++half) {
+            const int r0 = R0 + half * kLeafH;
+            if (r0 > R1) break;
+            const int r1 = min(R1, r0 + kLeafH - 1);
+            // this lane's pixels: 4 consecutive columns x 2 rows (row, row + 4)
+            const int grow[2] = {r0 + (lane >> 3), r0 + (lane >> 3) + 4};
+
+            // old hfun values: issued first, consumed in the epilogue
+            float o[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) o[j][k] = A.old_const;
+                if (!HAS_OLD) continue;
+                if (grow[j] > r1 || gcol > c1) continue;
+                const float *orow = A.old_ + (int64_t)(g.row0 + grow[j]) * A.os;
+                if (A.vec_old && full) {
+                    const float4 v4 = __ldcs(reinterpret_cast<const float4 *>(orow + gcol));
+                    o[j][0] = v4.x; o[j][1] = v4.y; o[j][2] = v4.z; o[j][3] = v4.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (gcol + k <= c1) o[j][k] = orow[gcol + k];
                 }
-                const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
-                                  !dominated_smem(W, corner_d2(q, v));
-                const unsigned mask = __ballot_sync(0xffffffffu, keep);
-                if (keep) {
-                    const int pos = __popc(mask & lt_mask);
-                    W.sv[pos] = v;
-                    if (WANT_OUT) W.sid[pos] = id;
-                }
-                __syncwarp();
-                const int ns = __popc(mask);
-                for (int s = 0; s < ns; ++s) {
-                    const double2 sv = W.sv[s];
-                    int vid = 0;
-                    if (WANT_OUT) vid = W.sid[s];
-                    double dx2[4], dy2[2];
+            }
+
+            double best[8];
+            int bid[8];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const double d = __dsub_rn(px[k], sv.x);
-                        dx2[k] = __dmul_rn(d, d);
-                    }
+            for (int k = 0; k < 8; ++k) { best[k] = INFINITY; bid[k] = 0x7fffffff; }
+
+            if (cnt > 0) {
+                double py[2];
 #pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        const double d = __dsub_rn(py[j], sv.y);
-                        dy2[j] = __dmul_rn(d, d);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
+                for (int j = 0; j < 2; ++j)
+                    py[j] = lin_at(g.ay, g.row0 + min(grow[j], g.h - 1));
+
+                // every lane evaluates its 8 pixels against survivors
+                // W.sv[0 .. n), each read as one LDS.128 broadcast
+                auto eval_survivors = [&](int n) {
+                    for (int s = 0; s < n; ++s) {
+                        const double2 sv = W.sv[s];
+                        int vid = 0;
+                        if (WANT_OUT) vid = W.sid[s];
+                        double dx2[4], dy2[2];
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
-                            const double d2 = __dadd_rn(dx2[k], dy2[j]);
-                            if (WANT_OUT) {
-                                if (d2 < best[j * 4 + k] ||
-                                    (d2 == best[j * 4 + k] && vid < bid[j * 4 + k])) {
-                                    best[j * 4 + k] = d2;
-                                    bid[j * 4 + k] = vid;
-                                }
-                            } else {
-                                // d2 is never NaN (finite coordinates): a
-                                // compare + select, not the 7-op IEEE fmin
-                                best[j * 4 + k] =
-                                    (d2 < best[j * 4 + k]) ? d2 : best[j * 4 + k];
-                            }
+                            const double d = __dsub_rn(px[k], sv.x);
+                            dx2[k] = __dmul_rn(d, d);
                         }
-                }
-                __syncwarp();
-            }
-        }
-
-        // ---- epilogue ------------------------------------------------------
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int row = grow[j];
-            if (row > r1 || gcol > c1) continue;
-            float *nrow = A.new_ + (int64_t)(g.row0 + row) * A.ns;
-            float out[4];
+                        for (int j = 0; j < 2; ++j) {
+                            const double d = __dsub_rn(py[j], sv.y);
+                            dy2[j] = __dmul_rn(d, d);
+                        }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const double d2 = best[j * 4 + k];
-                float vf;
-                if (WANT_OUT) {
-                    const bool hit = d2 < A.r2;
-                    const double d = hit ? __dsqrt_rn(d2) : A.r;
-                    // values = expansion_rate*target_size*distances + target_size
-                    vf = (float)__dadd_rn(__dmul_rn(A.rate_target, d), A.target);
-                    if (gcol + k <= c1) {
-                        const int64_t lin = (int64_t)(g.row0 + row) * g.w + gcol + k;
-                        if (A.dist) A.dist[lin] = d;
-                        if (A.idx) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
+                        for (int j = 0; j < 2; ++j)
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const double d2 = __dadd_rn(dx2[k], dy2[j]);
+                                if (WANT_OUT) {
+                                    if (d2 < best[j * 4 + k] ||
+                                        (d2 == best[j * 4 + k] && vid < bid[j * 4 + k])) {
+                                        best[j * 4 + k] = d2;
+                                        bid[j * 4 + k] = vid;
+                                    }
+                                } else {
+                                    // d2 is never NaN (finite coordinates): a
+                                    // compare + select, not the 7-op IEEE fmin
+                                    best[j * 4 + k] =
+                                        (d2 < best[j * 4 + k]) ? d2 : best[j * 4 + k];
+                                }
+                            }
                     }
+                };
+                if (!refilter) {
+                    eval_survivors(ns);
                 } else {
-                    vf = size_law_f32(d2, A);
+                    // more than kSurvCap survivors: filter and evaluate chunk
+                    // by chunk (the leaves share the rect's filter criteria)
+                    for (int b0 = 0; b0 < cnt; b0 += 32) {
+                        const int n = filter_chunk(b0, 0);
+                        __syncwarp();
+                        eval_survivors(n);
+                        __syncwarp();
+                    }
                 }
-                // reference: clamp(vf); min(old, .); [A10: clamp again].  The
-                // clamp is monotone and idempotent, so with A10 fused
-                // clamp(min(old, clamp(vf))) == clamp(min(old, vf)); max.NaN /
-                // min.NaN keep NaN like the reference's compares do.
-                float res;
-                if (A.fuse_clamp) {
-                    res = min_nan_f32(o[j][k], vf);
-                    res = min_nan_f32(max_nan_f32(res, A.lo), A.hi);
-                } else {
-                    vf = min_nan_f32(max_nan_f32(vf, A.lo), A.hi);
-                    res = min_nan_f32(o[j][k], vf);
-                }
-                out[k] = res;
             }
-            if (A.vec_new && full) {
-                __stcs(reinterpret_cast<float4 *>(nrow + gcol),
-                       make_float4(out[0], out[1], out[2], out[3]));
-            } else {
+
+            // ---- epilogue --------------------------------------------------
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (gcol + k <= c1) nrow[gcol + k] = out[k];
+            for (int j = 0; j < 2; ++j) {
+                const int row = grow[j];
+                if (row > r1 || gcol > c1) continue;
+                float *nrow = A.new_ + (int64_t)(g.row0 + row) * A.ns;
+                float out[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const double d2 = best[j * 4 + k];
+                    float vf;
+                    if (WANT_OUT) {
+                        const bool hit = d2 < A.r2;
+                        const double d = hit ? __dsqrt_rn(d2) : A.r;
+                        // values = expansion_rate*target_size*distances + target_size
+                        vf = (float)__dadd_rn(__dmul_rn(A.rate_target, d), A.target);
+                        if (gcol + k <= c1) {
+                            const int64_t lin = (int64_t)(g.row0 + row) * g.w + gcol + k;
+                            if (A.dist) A.dist[lin] = d;
+                            if (A.idx) A.idx[lin] = hit ? (int64_t)bid[j * 4 + k] : A.nv;
+                        }
+                    } else {
+                        vf = size_law_f32(d2, A);
+                    }
+                    // reference: clamp(vf); min(old, .); [A10: clamp again].  The
+                    // clamp is monotone and idempotent, so with A10 fused
+                    // clamp(min(old, clamp(vf))) == clamp(min(old, vf)); max.NaN /
+                    // min.NaN keep NaN like the reference's compares do.
+                    float res;
+                    if (A.fuse_clamp) {
+                        res = min_nan_f32(o[j][k], vf);
+                        res = min_nan_f32(max_nan_f32(res, A.lo), A.hi);
+                    } else {
+                        vf = min_nan_f32(max_nan_f32(vf, A.lo), A.hi);
+                        res = min_nan_f32(o[j][k], vf);
+                    }
+                    out[k] = res;
+                }
+                if (A.vec_new && full) {
+                    __stcs(reinterpret_cast<float4 *>(nrow + gcol),
+                           make_float4(out[0], out[1], out[2], out[3]));
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (gcol + k <= c1) nrow[gcol + k] = out[k];
+                }
             }
         }
+        __syncwarp();   // W is reused by the warp's next rect
     }
 }

@@ -34,6 +34,7 @@ for r in rows:
 ti = sum(a[0] for a in agg.values()) or 1
 ts = sum(a[1] for a in agg.values()) or 1
 print(f"kernel: {first_fn}\ntotal warp-instructions {ti}, samples {ts}")
-for (f, l), (n, s, src, st) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+bys = len(sys.argv) > 4 and sys.argv[4] == "samples"
+for (f, l), (n, s, src, st) in sorted(agg.items(), key=lambda kv: -kv[1][1 if bys else 0])[:top]:
     top_st = ",".join(f"{k[6:]}:{v}" for k, v in st.most_common(2))
     print(f"{100*n/ti:5.1f}%i {100*s/ts:5.1f}%s {f}:{l:<4d} {src.strip()[:70]:70s} {top_st}")
