@@ -71,6 +71,8 @@ struct ocsb_ctx {
     // pinned bounce buffer for small D2H reads (flags, counters)
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
+    // one-time cudaFuncSetAttribute calls already made on this device
+    unsigned func_attr_done = 0;
     // spline coefficient cache (one raster window)
     const void *spl_key = nullptr;
     double *spl_coef = nullptr;
