@@ -42,7 +42,7 @@ extern "C" {
 #define OCSB_ENCCL      (-4)
 #define OCSB_EOVERFLOW  (-5)
 
-#define OCSB_ABI_VERSION 1
+#define OCSB_ABI_VERSION 2
 
 /* DEM element types (the hfun raster itself is always float32,
  * ocsmesh/hfun/raster.py:76) */
@@ -206,6 +206,47 @@ int32_t ocsb_hfun_flow_limiter(ocsb_ctx *ctx, const ocsb_win *win,
                                double lower_bound, double upper_bound,
                                double ghmin, double ghmax,
                                int32_t fuse_clamp);
+
+/* ---- A4 + A6..A10 as ONE streamed pass --------------------------------------
+ * The reference applies every add_* to the whole raster before the next one
+ * starts, rewriting a GeoTIFF each time (ocsmesh/hfun/raster.py:1257-1260,
+ * :1432-1435).  Every op on this path is pixel-local given the DEM (+1 halo
+ * row) and the vertex set, so the same result is obtained band by band:
+ * ocsb_hfun_pass runs the whole op list on one row band after the other and,
+ * for HOST buffers, overlaps the H2D copy of band k+1, the kernels of band k
+ * and the D2H copy of band k-1 on three streams (full-duplex PCIe), with two
+ * device band buffers instead of whole-raster staging.  It is also the way to
+ * process rasters that do not fit in HBM.
+ *   ops[i]   : OCSB_OP_FEATURE (verts_xy, nv, expansion_rate, target_size) =
+ *              one ocsb_hfun_feature call; OCSB_OP_LIMITER (hmin, hmax,
+ *              lower_bound, upper_bound) = one ocsb_hfun_flow_limiter call;
+ *              fuse_clamp as in those calls.  Applied in list order.
+ *   hfun_in  : pre-pass raster window, NULL = A4 initial state
+ *   hfun_out : post-pass raster window (may alias hfun_in)
+ *   dem      : DEM window (only needed when a limiter op is present)
+ *   ghmin/ghmax : the HfunRaster's global bounds, NaN = None
+ *   band_rows: rows per streamed band, 0 = automatic (~64 MB of hfun)
+ * win->row_begin/row_end restrict the pass to a device tile as everywhere.
+ * Bit-identical to the op-by-op calls (tests/test_pass_gpu.py).              */
+#define OCSB_OP_FEATURE 0
+#define OCSB_OP_LIMITER 1
+typedef struct ocsb_hfun_op {
+    int32_t       kind;
+    int32_t       fuse_clamp;
+    const double *verts_xy;       /* FEATURE */
+    int64_t       nv;
+    double        expansion_rate, target_size;
+    double        hmin, hmax;     /* LIMITER: the method's arguments */
+    double        lower_bound, upper_bound;
+} ocsb_hfun_op;
+
+int32_t ocsb_hfun_pass(ocsb_ctx *ctx, const ocsb_win *win,
+                       const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                       const float *hfun_in, int64_t in_stride,
+                       float *hfun_out, int64_t out_stride,
+                       double dx, double dy, double ghmin, double ghmax,
+                       const ocsb_hfun_op *ops, int32_t n_ops,
+                       int32_t band_rows);
 
 /* ---- A12: pixel-wise min of co-registered hfun windows (build-defined) ---- */
 int32_t ocsb_min_combine(ocsb_ctx *ctx, float *dst, int64_t dst_stride,

@@ -38,6 +38,16 @@ class ocsb_interp_raster(C.Structure):
                 ("mask_stride", c_i64)]
 
 
+class ocsb_hfun_op(C.Structure):
+    _fields_ = [("kind", c_i32), ("fuse_clamp", c_i32), ("verts_xy", c_vp),
+                ("nv", c_i64), ("expansion_rate", c_f64), ("target_size", c_f64),
+                ("hmin", c_f64), ("hmax", c_f64), ("lower_bound", c_f64),
+                ("upper_bound", c_f64)]
+
+
+OP_FEATURE, OP_LIMITER = 0, 1
+
+
 class OcsbError(RuntimeError):
     def __init__(self, status: int, message: str):
         super().__init__(f"libocsb200 error {status}: {message}")
@@ -74,6 +84,9 @@ SIGNATURES = {
                                        c_i64, c_vp, c_i64, c_vp, c_i64,
                                        c_f64, c_f64, c_f64, c_f64, c_f64,
                                        c_f64, c_f64, c_f64, c_i32]),
+    "ocsb_hfun_pass": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
+                               c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64,
+                               c_f64, C.POINTER(ocsb_hfun_op), c_i32, c_i32]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -239,6 +252,31 @@ class Context:
             ptr(old), int(old_stride), ptr(new), int(new_stride), float(dx),
             float(dy), opt(hmin), opt(hmax), opt(lower_bound), opt(upper_bound),
             opt(ghmin), opt(ghmax), int(bool(fuse_clamp))))
+
+    def hfun_pass(self, win, dem, dem_dtype, dem_stride, hfun_in, in_stride,
+                  hfun_out, out_stride, dx, dy, ghmin, ghmax, ops, band_rows=0):
+        """``ops``: list of ("feature", verts, nv, rate, target, fuse) /
+        ("limiter", hmin, hmax, lower_bound, upper_bound, fuse) tuples."""
+        arr = (ocsb_hfun_op * len(ops))()
+        for o, t in zip(arr, ops):
+            if t[0] == "feature":
+                _, verts, nv, rate, target, fuse = t
+                o.kind, o.fuse_clamp = OP_FEATURE, int(bool(fuse))
+                o.verts_xy, o.nv = ptr(verts), int(nv)
+                o.expansion_rate, o.target_size = float(rate), float(target)
+                o.hmin = o.hmax = o.lower_bound = o.upper_bound = NONE
+            else:
+                _, hmin, hmax, lb, ub, fuse = t
+                o.kind, o.fuse_clamp = OP_LIMITER, int(bool(fuse))
+                o.verts_xy, o.nv = None, 0
+                o.expansion_rate = o.target_size = NONE
+                o.hmin, o.hmax = opt(hmin), opt(hmax)
+                o.lower_bound, o.upper_bound = opt(lb), opt(ub)
+        check(self.lib.ocsb_hfun_pass(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(hfun_in), int(in_stride), ptr(hfun_out), int(out_stride),
+            float(dx), float(dy), opt(ghmin), opt(ghmax), arr, len(ops),
+            int(band_rows)))
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

@@ -471,6 +471,8 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
     unsigned long long *ctrs = nullptr;   // [kMaxLevels] + overflow flag behind
     OCSB_TRY(sg.get(&ctrs, kMaxLevels + 2));
     int *overflow = reinterpret_cast<int *>(ctrs + kMaxLevels);
+    const bool async_mode = a.ext_overflow != nullptr;
+    if (async_mode) overflow = a.ext_overflow;
 
     std::vector<LevelDev> dev(lv.size());
     for (int i = 0; i <= top; ++i) {
@@ -491,6 +493,7 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
                                    48ull * (unsigned long long)lv[i].ntiles +
                                    (1ull << 16);
             c <<= (2 * attempt);
+            if (async_mode) c <<= 1;   // one shot: start with doubled pools
             if (c > 0x7fffffffull) c = 0x7fffffffull;  // int offsets
             cap[i] = c;
             OCSB_TRY(pools.get(&dev[i].ids, (size_t)c));
@@ -599,6 +602,9 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         }
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
+
+        // asynchronous mode: the caller inspects *ext_overflow later
+        if (async_mode) return OCSB_OK;
 
         // candidate pools are bump-allocated with a size guess: read the
         // overflow flag back and retry with larger pools if it tripped (the

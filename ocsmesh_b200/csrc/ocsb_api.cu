@@ -175,6 +175,14 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
         cudaEventDestroy(r.b);
     }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
+    if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
+    if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
+    for (int i = 0; i < OCSB_PASS_SETS; ++i) {
+        if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+        if (ctx->ev_comp[i]) cudaEventDestroy(ctx->ev_comp[i]);
+        if (ctx->ev_out[i]) cudaEventDestroy(ctx->ev_out[i]);
+    }
+    if (ctx->ev_alloc) cudaEventDestroy(ctx->ev_alloc);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return OCSB_OK;
@@ -750,4 +758,320 @@ extern "C" int32_t ocsb_bucket_nodes(ocsb_ctx *ctx, const double *xy, int64_t K,
     OCSB_TRY(k_bucket_nodes(ctx, (const double *)sxy.dev, K, bbox4, cell_size,
                             (int32_t *)sp.dev, (double *)ss.dev));
     return finish_call(ctx, {&sxy, &sp, &ss});
+}
+
+// ---------------------------------------------------------------------------
+// A4 + A6..A10 as one streamed pass (see ocsb200.h)
+// ---------------------------------------------------------------------------
+namespace {
+
+// one pixel buffer of the pass: used in place when it is device memory,
+// otherwise streamed through two device band buffers
+struct PassBuf {
+    const char *user = nullptr;   // window row 0 (host or device)
+    int64_t stride = 0;           // elements
+    size_t elem = 4;
+    bool host = false;
+    char *band[OCSB_PASS_SETS] = {};      // compact (stride = w) band scratch
+};
+
+int32_t pass_streams(ocsb_ctx *ctx) {
+    if (ctx->s_h2d) return OCSB_OK;
+    OCSB_CUDA(cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking));
+    OCSB_CUDA(cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < OCSB_PASS_SETS; ++i) {
+        OCSB_CUDA(cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+        OCSB_CUDA(cudaEventCreateWithFlags(&ctx->ev_comp[i], cudaEventDisableTiming));
+        OCSB_CUDA(cudaEventCreateWithFlags(&ctx->ev_out[i], cudaEventDisableTiming));
+    }
+    OCSB_CUDA(cudaEventCreateWithFlags(&ctx->ev_alloc, cudaEventDisableTiming));
+    return OCSB_OK;
+}
+
+// the op list on rows [a, b) of the window; pointers are (virtual) addresses
+// of window row 0
+int32_t pass_ops(ocsb_ctx *ctx, const ocsb_win *win, int a, int b,
+                 const void *dem, int dem_dtype, int64_t dem_stride,
+                 const float *in, int64_t in_stride, float *out,
+                 int64_t out_stride, double dx, double dy, double ghmin,
+                 double ghmax, const ocsb_hfun_op *ops, int n_ops,
+                 const std::vector<const double *> &verts,
+                 int *flags /* device, n_ops ints; nullptr = synchronous */) {
+    const float *oldp = in;
+    int64_t olds = in_stride;
+    for (int i = 0; i < n_ops; ++i) {
+        const ocsb_hfun_op &op = ops[i];
+        if (op.kind == OCSB_OP_FEATURE) {
+            FeatureArgs fa;
+            win_axes(win, &fa.ax, &fa.ay);
+            fa.rate_target = op.expansion_rate * op.target_size;
+            fa.target = op.target_size;
+            fa.has_hmin = !ocsb_is_none(ghmin);
+            fa.has_hmax = !ocsb_is_none(ghmax);
+            fa.hmin_f = fa.has_hmin ? (float)ghmin : 0.f;
+            fa.hmax_f = fa.has_hmax ? (float)ghmax : 0.f;
+            fa.fuse_clamp = op.fuse_clamp;
+            fa.r = (fa.has_hmax && ghmax != 0.0)
+                       ? (ghmax - op.target_size) / fa.rate_target
+                       : std::numeric_limits<double>::infinity();
+            fa.row_begin = a;
+            fa.row_end = b;
+            fa.ext_overflow = flags ? flags + i : nullptr;
+            OCSB_TRY(k_hfun_feature(ctx, fa, verts[i], op.nv, oldp, olds, out,
+                                    out_stride, nullptr, nullptr));
+        } else {
+            LimiterArgs la{dx, dy, op.hmin, op.hmax, op.lower_bound,
+                           op.upper_bound, ghmin, ghmax, op.fuse_clamp};
+            OCSB_TRY(k_flow_limiter(ctx, win->width, win->height, a, b, dem,
+                                    dem_dtype, dem_stride, oldp, olds, out,
+                                    out_stride, la));
+        }
+        oldp = out;
+        olds = out_stride;
+    }
+    return OCSB_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t ocsb_hfun_pass(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, const float *hfun_in, int64_t in_stride,
+    float *hfun_out, int64_t out_stride, double dx, double dy, double ghmin,
+    double ghmax, const ocsb_hfun_op *ops, int32_t n_ops, int32_t band_rows) {
+    CTX_ENTER("ocsb_hfun_pass");
+    OCSB_TRY(check_win(win, "ocsb_hfun_pass"));
+    OCSB_REQUIRE(ops && n_ops > 0, "ocsb_hfun_pass: empty op list");
+    OCSB_REQUIRE(hfun_out && out_stride >= win->width &&
+                     (!hfun_in || in_stride >= win->width),
+                 "ocsb_hfun_pass: bad hfun buffers");
+    OCSB_REQUIRE(band_rows >= 0, "ocsb_hfun_pass: negative band_rows");
+    const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_pass", &rb, &re));
+    bool need_dem = false;
+    for (int i = 0; i < n_ops; ++i) {
+        const ocsb_hfun_op &op = ops[i];
+        if (op.kind == OCSB_OP_FEATURE) {
+            OCSB_REQUIRE(op.verts_xy && op.nv > 0 && op.nv < (int64_t)2147483647,
+                         "ocsb_hfun_pass: op %d: bad vertex set", i);
+            OCSB_REQUIRE(!ocsb_is_none(op.target_size) && op.target_size > 0,
+                         "Argument target_size must be greater than zero.");
+            OCSB_REQUIRE(!ocsb_is_none(op.expansion_rate),
+                         "ocsb_hfun_pass: op %d: expansion_rate is NaN", i);
+            if (!ocsb_is_none(ghmax) && ghmax != 0.0)
+                OCSB_REQUIRE(op.expansion_rate * op.target_size != 0.0,
+                             "ocsb_hfun_pass: op %d: float division by zero "
+                             "(expansion_rate * target_size == 0 with hmax set)", i);
+        } else if (op.kind == OCSB_OP_LIMITER) {
+            need_dem = true;
+        } else {
+            OCSB_REQUIRE(false, "ocsb_hfun_pass: op %d: unknown kind %d", i, op.kind);
+        }
+    }
+    if (need_dem) {
+        OCSB_REQUIRE(dem && dem_stride >= w &&
+                         (dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64),
+                     "ocsb_hfun_pass: a limiter op needs the DEM window");
+        OCSB_REQUIRE(w >= 2 && h >= 2,
+                     "Shape of array too small to calculate a numerical gradient, "
+                     "at least (edge_order + 1) elements are required.");
+        OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
+                     "ocsb_hfun_pass: dx/dy is NaN");
+    }
+
+    // vertex sets: staged once, whole
+    std::vector<Staged> sv(n_ops);
+    std::vector<const double *> verts(n_ops, nullptr);
+    for (int i = 0; i < n_ops; ++i)
+        if (ops[i].kind == OCSB_OP_FEATURE) {
+            OCSB_TRY(sv[i].init(ctx, ops[i].verts_xy, 1, ops[i].nv * 2,
+                                ops[i].nv * 2, 8, STAGE_IN));
+            verts[i] = (const double *)sv[i].dev;
+        }
+
+    PassBuf bz, bi, bo;
+    bz.user = (const char *)dem; bz.stride = dem_stride;
+    bz.elem = dem_dtype == OCSB_F64 ? 8 : 4;
+    bz.host = need_dem && !ocsb_is_device_ptr(dem);
+    bi.user = (const char *)hfun_in; bi.stride = in_stride;
+    bi.host = hfun_in && !ocsb_is_device_ptr(hfun_in);
+    bo.user = (const char *)hfun_out; bo.stride = out_stride;
+    bo.host = !ocsb_is_device_ptr(hfun_out);
+
+    if (!bz.host && !bi.host && !bo.host) {
+        // everything resident: one band, no copies
+        return pass_ops(ctx, win, rb, re, dem, dem_dtype, dem_stride, hfun_in,
+                        in_stride, hfun_out, out_stride, dx, dy, ghmin, ghmax,
+                        ops, n_ops, verts, nullptr);
+    }
+
+    // ---- streamed: H2D(k+1, k+2) | ops(k) | D2H(k-1) -------------------------
+    // Nothing below waits on the host until the final drain: the candidate-pool
+    // overflow flags of the feature ops stay on the device and are checked
+    // once at the end (a band that overflowed is redone synchronously).
+    OCSB_TRY(pass_streams(ctx));
+    int rows = band_rows;
+    if (rows == 0) {
+        rows = (int)((80ll << 20) / (4ll * w));
+        rows = rows / 64 * 64;          // whole 64-px tiles of the K1 pyramid
+        if (rows < 64) rows = 64;
+    }
+    if (rows > re - rb) rows = re - rb;
+    // band schedule: the first H2D and the last D2H cannot overlap with
+    // anything, so the bands ramp up from / down to 128 rows at both ends
+    std::vector<int> cuts;   // band k = rows [cuts[k], cuts[k+1])
+    {
+        std::vector<int> head, tail;
+        int lo = rb, hi = re;
+        for (int sz = 128; sz < rows && hi - lo > 4 * rows; sz *= 2) {
+            head.push_back(lo); lo += sz;
+            hi -= sz; tail.push_back(hi);
+        }
+        cuts = head;
+        for (int a = lo; a < hi; a += rows) cuts.push_back(a);
+        for (size_t i = tail.size(); i-- > 0;) cuts.push_back(tail[i]);
+        cuts.push_back(re);
+    }
+    const int nb = (int)cuts.size() - 1;
+    // an aliased host in/out window travels through ONE device buffer
+    const bool alias = hfun_in && (const void *)hfun_in == (const void *)hfun_out &&
+                       in_stride == out_stride;
+    ScratchGuard sg(ctx);
+    constexpr int NS = OCSB_PASS_SETS;
+    int *flags = nullptr;
+    OCSB_TRY(sg.get(&flags, (size_t)nb * n_ops));
+    OCSB_CUDA(cudaMemsetAsync(flags, 0, (size_t)nb * n_ops * sizeof(int), ctx->stream));
+    for (int s = 0; s < (nb < NS ? nb : NS); ++s) {
+        if (bz.host) OCSB_TRY(sg.get(&bz.band[s], (size_t)(rows + 2) * w * bz.elem));
+        if (bo.host) OCSB_TRY(sg.get(&bo.band[s], (size_t)rows * w * 4));
+        if (bi.host && !alias) OCSB_TRY(sg.get(&bi.band[s], (size_t)rows * w * 4));
+    }
+    OCSB_CUDA(cudaEventRecord(ctx->ev_alloc, ctx->stream));
+    OCSB_CUDA(cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_alloc, 0));
+    OCSB_CUDA(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_alloc, 0));
+
+    auto band_of = [&](int k, int *a, int *b) {
+        *a = cuts[k];
+        *b = cuts[k + 1];
+    };
+    auto issue_h2d = [&](int k) -> int32_t {
+        const int s = k % NS;
+        int a, b;
+        band_of(k, &a, &b);
+        // the buffers of set s were last used by band k-NS: its D2H (which
+        // follows its kernels) must have drained
+        if (k >= NS) OCSB_CUDA(cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_out[s], 0));
+        if (bz.host) {
+            const int za = a > 0 ? a - 1 : 0, zb = b < h ? b + 1 : h;
+            OCSB_CUDA(cudaMemcpy2DAsync(
+                bz.band[s], (size_t)w * bz.elem,
+                bz.user + (size_t)za * bz.stride * bz.elem, (size_t)bz.stride * bz.elem,
+                (size_t)w * bz.elem, (size_t)(zb - za), cudaMemcpyHostToDevice,
+                ctx->s_h2d));
+        }
+        if (bi.host) {
+            char *dst = alias ? bo.band[s] : bi.band[s];
+            OCSB_CUDA(cudaMemcpy2DAsync(
+                dst, (size_t)w * 4, bi.user + (size_t)a * bi.stride * 4,
+                (size_t)bi.stride * 4, (size_t)w * 4, (size_t)(b - a),
+                cudaMemcpyHostToDevice, ctx->s_h2d));
+        }
+        OCSB_CUDA(cudaEventRecord(ctx->ev_in[s], ctx->s_h2d));
+        return OCSB_OK;
+    };
+
+    int32_t status = issue_h2d(0);
+    if (status == OCSB_OK && nb > 1) status = issue_h2d(1);
+    for (int k = 0; k < nb && status == OCSB_OK; ++k) {
+        const int s = k % NS;
+        int a, b;
+        band_of(k, &a, &b);
+        if (k + 2 < nb) status = issue_h2d(k + 2);
+        if (status != OCSB_OK) break;
+        // (virtual) addresses of window row 0 of this band's buffers
+        const int za = a > 0 ? a - 1 : 0;
+        const void *zp = dem;
+        int64_t zs = dem_stride;
+        if (bz.host) { zp = bz.band[s] - (size_t)za * w * bz.elem; zs = w; }
+        float *op_ = hfun_out;
+        int64_t os_ = out_stride;
+        if (bo.host) { op_ = (float *)(bo.band[s] - (size_t)a * w * 4); os_ = w; }
+        const float *ip = hfun_in;
+        int64_t is_ = in_stride;
+        if (bi.host) {
+            ip = alias ? op_ : (const float *)(bi.band[s] - (size_t)a * w * 4);
+            is_ = w;
+        }
+        cudaError_t e = cudaStreamWaitEvent(ctx->stream, ctx->ev_in[s], 0);
+        // device-resident output written in place: band k's kernels must not
+        // overtake nothing -- they run in stream order on ctx->stream
+        if (e != cudaSuccess) { status = OCSB_ECUDA; ocsb_set_error("cudaStreamWaitEvent -> %s", cudaGetErrorString(e)); break; }
+        status = pass_ops(ctx, win, a, b, zp, dem_dtype, zs, ip, is_, op_, os_, dx,
+                          dy, ghmin, ghmax, ops, n_ops, verts,
+                          flags + (size_t)k * n_ops);
+        if (status != OCSB_OK) break;
+        cudaEventRecord(ctx->ev_comp[s], ctx->stream);
+        cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_comp[s], 0);
+        if (bo.host) {
+            e = cudaMemcpy2DAsync((char *)hfun_out + (size_t)a * out_stride * 4,
+                                  (size_t)out_stride * 4, bo.band[s], (size_t)w * 4,
+                                  (size_t)w * 4, (size_t)(b - a),
+                                  cudaMemcpyDeviceToHost, ctx->s_d2h);
+            if (e != cudaSuccess) { status = OCSB_ECUDA; ocsb_set_error("D2H -> %s", cudaGetErrorString(e)); break; }
+        }
+        cudaEventRecord(ctx->ev_out[s], ctx->s_d2h);
+    }
+    // drain all three streams before the scratch is released / the caller reads
+    cudaStreamSynchronize(ctx->s_h2d);
+    cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->s_d2h);
+    if (status == OCSB_OK && e != cudaSuccess) {
+        ocsb_set_error("ocsb_hfun_pass: %s", cudaGetErrorString(e));
+        status = OCSB_ECUDA;
+    }
+    if (status != OCSB_OK) return status;
+
+    // ---- bands whose candidate pools overflowed: redo them synchronously ------
+    std::vector<int> hflags((size_t)nb * n_ops, 0);
+    OCSB_CUDA(cudaMemcpy(hflags.data(), flags, hflags.size() * sizeof(int),
+                         cudaMemcpyDeviceToHost));
+    for (int k = 0; k < nb; ++k) {
+        bool bad = false;
+        for (int i = 0; i < n_ops; ++i) bad = bad || hflags[(size_t)k * n_ops + i];
+        if (!bad) continue;
+        int a, b;
+        band_of(k, &a, &b);
+        ocsb_win bw = *win;
+        bw.row_begin = a;
+        bw.row_end = b;
+        // the single-band call: everything resident, or one streamed band
+        // (rows == b - a) through the synchronous retrying path
+        if (!bz.host && !bi.host && !bo.host) {
+            OCSB_TRY(pass_ops(ctx, win, a, b, dem, dem_dtype, dem_stride, hfun_in,
+                              in_stride, hfun_out, out_stride, dx, dy, ghmin,
+                              ghmax, ops, n_ops, verts, nullptr));
+        } else {
+            Staged sz, si, so;
+            const int za = a > 0 ? a - 1 : 0, zb = b < h ? b + 1 : h;
+            if (need_dem)
+                OCSB_TRY(sz.init(ctx, dem, zb - za, w, dem_stride, bz.elem, STAGE_IN, za));
+            const bool al = hfun_in && (const void *)hfun_in == (const void *)hfun_out &&
+                            in_stride == out_stride;
+            if (al) {
+                OCSB_TRY(so.init(ctx, hfun_out, b - a, w, out_stride, 4, STAGE_INOUT, a));
+            } else {
+                if (hfun_in) OCSB_TRY(si.init(ctx, hfun_in, b - a, w, in_stride, 4, STAGE_IN, a));
+                OCSB_TRY(so.init(ctx, hfun_out, b - a, w, out_stride, 4, STAGE_OUT, a));
+            }
+            const float *ip = al ? (const float *)so.dev : (const float *)si.dev;
+            const int64_t is_ = al ? so.dev_stride : si.dev_stride;
+            OCSB_TRY(pass_ops(ctx, win, a, b, sz.dev, dem_dtype,
+                              need_dem ? sz.dev_stride : 0, ip, is_,
+                              (float *)so.dev, so.dev_stride, dx, dy, ghmin,
+                              ghmax, ops, n_ops, verts, nullptr));
+            OCSB_TRY(finish_call(ctx, {&sz, &si, &so}));
+        }
+    }
+    return OCSB_OK;
 }

@@ -53,6 +53,9 @@ void ocsb_set_error(const char *fmt, ...);
 // ---------------------------------------------------------------------------
 // context
 // ---------------------------------------------------------------------------
+// band buffer sets of ocsb_hfun_pass: H2D(k+1..k+2) | ops(k) | D2H(k-1)
+#define OCSB_PASS_SETS 3
+
 struct KTimeRec {
     int kclass;
     cudaEvent_t a, b;
@@ -71,6 +74,10 @@ struct ocsb_ctx {
     // pinned bounce buffer for small D2H reads (flags, counters)
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
+    // copy streams + events of ocsb_hfun_pass (created on first use)
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaEvent_t ev_in[OCSB_PASS_SETS] = {}, ev_comp[OCSB_PASS_SETS] = {},
+                ev_out[OCSB_PASS_SETS] = {}, ev_alloc = nullptr;
     // one-time cudaFuncSetAttribute calls already made on this device
     unsigned func_attr_done = 0;
     // spline coefficient cache (one raster window)
@@ -233,6 +240,11 @@ struct FeatureArgs {
     float hmin_f, hmax_f;   // f32-rounded global bounds
     int has_hmin, has_hmax;
     int fuse_clamp;
+    // non-null: asynchronous mode.  One attempt with generous pools, no
+    // host read-back; the pool-overflow flag is left in *ext_overflow (device
+    // int, zeroed by the caller), and the evaluation kernel writes nothing if
+    // it is set -- the caller checks later and redoes the band synchronously.
+    int *ext_overflow = nullptr;
 };
 int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
                        const double *verts, int64_t nv, const float *old_,

@@ -48,7 +48,8 @@ class HfunRaster:
     def __init__(self, raster: Raster, hmin: Optional[float] = None,
                  hmax: Optional[float] = None, verbosity: int = 0,
                  initial_value=None, device: Optional[int] = None,
-                 row_band: Optional[Sequence[int]] = None) -> None:
+                 row_band: Optional[Sequence[int]] = None,
+                 deferred: bool = False) -> None:
         if not isinstance(raster, Raster):
             raise TypeError(
                 f'Argument raster must be of type {Raster}, not type '
@@ -72,13 +73,17 @@ class HfunRaster:
             self._band = (int(row_band[0]), int(row_band[1]))
             if not 0 <= self._band[0] < self._band[1] <= raster.height:
                 raise ValueError(f"bad row_band {row_band}")
-        ctx = self._ctx()
-        # only the owned rows are stored: row 0 of the buffer is raster row
-        # self._band[0]
-        h, w = self._band[1] - self._band[0], raster.width
-        with torch.cuda.device(self._device):
-            self._hfun = torch.empty((h, w), dtype=torch.float32,
-                                     device=f"cuda:{self._device}")
+        # deferred=True: add_* calls are queued and run as ONE streamed pass
+        # (ocsb_hfun_pass) when the raster is next looked at -- band by band,
+        # H2D / kernels / D2H overlapped, straight into the caller's host
+        # buffer on get_values(out=...).  Results are bit-identical to the
+        # eager mode; the default stays eager (every add_* is synchronous
+        # like the reference's).
+        self._deferred = bool(deferred)
+        self._queue: List = []
+        self._keep: List = []
+        self._host_vals = None      # result of a host-bound pass not yet on the device
+        self._hfun_buf = None
         if initial_value is not None:
             if isinstance(initial_value, (str, pathlib.Path, os.PathLike)):
                 info, bands = geotiff.read_geotiff(initial_value)
@@ -87,6 +92,7 @@ class HfunRaster:
                 init = np.asarray(initial_value, dtype=np.float32)
             if init.shape == (raster.height, w):
                 init = init[self._band[0]:self._band[1]]
+            h, w = self._band[1] - self._band[0], raster.width
             if init.shape != (h, w):
                 raise ValueError("initial_value does not match the raster shape")
             self._hfun.copy_(torch.from_numpy(np.ascontiguousarray(init)))
@@ -102,6 +108,22 @@ class HfunRaster:
     def _ctx(self) -> _lib.Context:
         return _lib.default_context(self._device)
 
+    @property
+    def _hfun(self):
+        """The float32 device raster of the owned rows (row 0 = raster row
+        ``self._band[0]``), allocated on first use."""
+        if self._hfun_buf is None:
+            import torch
+            h, w = self._band[1] - self._band[0], self._raster.width
+            with torch.cuda.device(self._device):
+                self._hfun_buf = torch.empty((h, w), dtype=torch.float32,
+                                             device=f"cuda:{self._device}")
+        return self._hfun_buf
+
+    @_hfun.setter
+    def _hfun(self, t):
+        self._hfun_buf = t
+
     def _windows(self) -> List[Window]:
         """HfunRaster iterates ITS OWN windows, built from the DEM's
         chunk_size / overlap (hfun/raster.py:68-73, 84-86)."""
@@ -116,12 +138,100 @@ class HfunRaster:
     def reset(self) -> None:
         """Back to the initial state: every pixel = finfo(float32).max."""
         self._pristine = True
+        self._queue = []
+        self._keep = []
+        self._host_vals = None
 
     def _materialize(self) -> None:
-        """Write the pending initial fill (A4) if no op has absorbed it."""
+        """Make the device raster current: run queued ops, upload a result
+        that a host-bound pass left on the host, write the pending initial
+        fill (A4) if no op has absorbed it."""
+        if self._queue:
+            self._run_pass(None)
+        if self._host_vals is not None:
+            import torch
+            self._hfun.copy_(torch.from_numpy(self._host_vals))
+            self._host_vals = None
         if self._pristine:
             self._ctx().fill_f32(self._hfun, self._hfun.numel(), FLT_MAX)
             self._pristine = False
+
+    # ---- deferred mode: the op queue and its streamed execution ---------------
+    def _can_defer(self) -> bool:
+        """Queued execution runs the whole op list window by window, which
+        equals the reference's op-by-op order unless windows overlap."""
+        if not self._deferred:
+            return False
+        return not ((self._overlap or 0) > 0 and len(self._windows()) > 1)
+
+    def flush(self) -> None:
+        """Run the queued ops now (into the device raster)."""
+        if self._queue:
+            self._run_pass(None)
+
+    def _dem_source(self):
+        """(address of raster row `origin`, dtype code, element size, origin)
+        of the DEM band: the cached device band if there is one, else the
+        host array (streamed by the pass)."""
+        r = self._raster
+        t = r._dev_cache.get((1, self._device))
+        if t is not None:
+            return t, t.data_ptr(), _dem_dtype_code(t), t.element_size(), \
+                r._dev_origin.get((1, self._device), 0)
+        host = np.asarray(r._src.bands[0])
+        if host.dtype != np.float32:
+            host = host.astype(np.float64, copy=False)
+        host = np.ascontiguousarray(host)
+        code = _lib.OCSB_F32 if host.dtype == np.float32 else _lib.OCSB_F64
+        return host, host.ctypes.data, code, host.itemsize, r._src.row_origin
+
+    def _run_pass(self, dst) -> None:
+        """ocsb_hfun_pass over every window.  ``dst``: None = the device
+        raster, else a C-contiguous float32 host array (numpy or CPU torch
+        tensor, ideally pinned) of the owned rows that receives the result."""
+        ops, self._queue = self._queue, []
+        ctx = self._ctx()
+        w = self.width
+        b0 = self._band[0]
+        need_dem = any(o[0] == "limiter" for o in ops)
+        dem_keep, dem_addr, code, es, origin = (None, 0, _lib.OCSB_F32, 4, 0)
+        if need_dem:
+            dem_keep, dem_addr, code, es, origin = self._dem_source()
+        if self._pristine:
+            in_addr = None
+        elif self._host_vals is not None:
+            in_addr = self._host_vals.ctypes.data
+        else:
+            in_addr = self._hfun.data_ptr()
+        if dst is None:
+            out_addr = self._hfun.data_ptr()
+        else:
+            out_addr = _lib.ptr(dst)
+        dx, dy = self._raster.dx, self._raster.dy
+        for win in self._windows():
+            band = self._band_of(win)
+            if band is None:
+                continue
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            off = ((win.row_off - b0) * w + win.col_off) * 4
+            ctx.hfun_pass(
+                cw, (dem_addr + ((win.row_off - origin) * w + win.col_off) * es)
+                if need_dem else None, code, w,
+                None if in_addr is None else in_addr + off, w, out_addr + off, w,
+                dx, dy, self._hmin, self._hmax, ops)
+        del dem_keep
+        self._keep = []
+        self._pristine = False
+        if dst is None:
+            self._host_vals = None
+        else:
+            self._host_vals = dst.numpy() if hasattr(dst, "numpy") else dst
+
+    def _materialize_queue(self) -> None:
+        """Eager ops need the queue drained and the raster on the device."""
+        if self._queue or self._host_vals is not None:
+            self._materialize()
 
     def _old_ptr(self, t, window: Window):
         """Pre-op window pointer, or None while the raster is still in its
@@ -229,6 +339,20 @@ class HfunRaster:
         ``out``: optional (pinned) CPU torch tensor to receive the values."""
         if band not in (None, 1):
             raise IndexError("the hfun raster has a single band")
+        if window is None and (self._queue or self._host_vals is not None):
+            # deferred mode: stream the pass straight into the host buffer
+            import torch
+            h, w = self._band[1] - self._band[0], self.width
+            if out is None:
+                out = np.empty((h, w), np.float32)
+            elif tuple(out.shape) != (h, w):
+                raise ValueError("out does not match the owned rows")
+            arr = out.numpy() if isinstance(out, torch.Tensor) else out
+            if self._queue:
+                self._run_pass(out)
+            elif arr is not self._host_vals:
+                np.copyto(arr, self._host_vals)
+            return arr
         self._materialize()
         t = self._hfun
         if window is not None:
@@ -341,6 +465,21 @@ class HfunRaster:
                              'global hmin has been set.')
         if target_size <= 0:
             raise ValueError("Argument target_size must be greater than zero.")
+        if self._can_defer():
+            if isinstance(points, torch.Tensor):
+                pts = points.to(dtype=torch.float64).contiguous()
+            else:
+                pts = np.ascontiguousarray(np.asarray(points, dtype=np.float64))
+            if pts.ndim != 2 or pts.shape[1] != 2:
+                raise ValueError("points must be an (N, 2) array")
+            if int(pts.shape[0]) == 0:
+                raise ValueError("add_feature needs at least one vertex")
+            self._keep.append(pts)
+            self._queue.append(("feature", pts, int(pts.shape[0]),
+                                float(expansion_rate), float(target_size),
+                                self._fuse_clamp()))
+            return
+        self._materialize_queue()
         if isinstance(points, torch.Tensor):
             verts = points.to(device=f"cuda:{self._device}",
                               dtype=torch.float64).contiguous()
@@ -384,6 +523,15 @@ class HfunRaster:
         self._check_projected()
         hmin = float(hmin) if hmin is not None else hmin
         hmax = float(hmax) if hmax is not None else hmax
+        if self._can_defer():
+            if self.width < 2 or self.height < 2:
+                raise ValueError(
+                    "Shape of array too small to calculate a numerical "
+                    "gradient, at least (edge_order + 1) elements are required.")
+            self._queue.append(("limiter", hmin, hmax, lower_bound, upper_bound,
+                                self._fuse_clamp()))
+            return
+        self._materialize_queue()
         ctx = self._ctx()
         windows = self._windows()
         fuse = self._fuse_clamp()

@@ -1,0 +1,161 @@
+"""ocsb_hfun_pass (one streamed pass over the op list, band by band with
+H2D / kernels / D2H overlapped) must be bit-identical to the op-by-op calls,
+which tests/test_feature_gpu.py and tests/test_limiter_gpu.py pin to the
+oracle (reference ocsmesh/hfun/raster.py:1230-1257, 1396-1435)."""
+import numpy as np
+import pytest
+
+import ocsmesh_b200 as ob
+from oracle import ocsmesh_oracle as O
+from ocsmesh_b200 import _lib, features as F, synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+FLT_MAX = np.finfo(np.float32).max
+
+
+def make_inputs(h, w, seed, dtype=np.float32):
+    z = S.synth_dem(h, w, seed=seed).astype(dtype)
+    tr = S.dem_transform(h)
+    r = O.OracleRaster(z, tr)
+    lines = S.synth_shoreline(h, w, seed=seed, n_lines=2)
+    pts = np.ascontiguousarray(F.feature_points(lines, 100.0))
+    pts2 = np.ascontiguousarray(F.feature_points(
+        S.synth_shoreline(h, w, seed=seed + 50, n_lines=1), 60.0))
+    return z, r, pts, pts2
+
+
+def op_by_op(ctx, z, r, ops, old, ghmin, ghmax, band=(0, 0)):
+    """Reference sequence through the single-op entry points (host buffers)."""
+    h, w = z.shape
+    win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, *band)
+    code = _lib.OCSB_F32 if z.dtype == np.float32 else _lib.OCSB_F64
+    cur = None if old is None else old.copy()
+    new = np.full((h, w), -1.0, np.float32) if old is None else old.copy()
+    for op in ops:
+        if op[0] == "feature":
+            _, pts, nv, rate, target, fuse = op
+            ctx.hfun_feature(win, pts, nv, cur, w, new, w, rate, target, ghmin,
+                             ghmax, fuse)
+        else:
+            _, hmin, hmax, lb, ub, fuse = op
+            ctx.hfun_flow_limiter(win, z, code, w, cur, w, new, w, 10.0, 10.0,
+                                  hmin, hmax, lb, ub, ghmin, ghmax, fuse)
+        cur = new
+    return new
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("band_rows", [0, 37, 64, 1000])
+def test_pass_equals_op_by_op_host(ctx, dtype, band_rows):
+    h, w = 301, 517
+    z, r, pts, pts2 = make_inputs(h, w, 3, dtype)
+    ops = [("feature", pts, len(pts), 0.001, 100.0, True),
+           ("limiter", 50.0, 1500.0, -30.0, 0.0, True),
+           ("feature", pts2, len(pts2), 0.01, 60.0, False),
+           ("limiter", None, None, None, None, False)]
+    ref = op_by_op(ctx, z, r, ops, None, 100.0, 1500.0)
+    win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, 0, 0)
+    code = _lib.OCSB_F32 if dtype == np.float32 else _lib.OCSB_F64
+    out = np.full((h, w), -1.0, np.float32)
+    ctx.hfun_pass(win, z, code, w, None, w, out, w, 10.0, 10.0, 100.0, 1500.0,
+                  ops, band_rows)
+    np.testing.assert_array_equal(out, ref)
+
+
+def test_pass_with_input_aliasing_and_strides(ctx):
+    import torch
+    h, w = 257, 300
+    z, r, pts, _ = make_inputs(h, w, 5)
+    rng = np.random.default_rng(0)
+    old = (rng.random((h, w)) * 2000 + 1).astype(np.float32)
+    ops = [("limiter", 50.0, 1500.0, None, None, False),
+           ("feature", pts, len(pts), 0.001, 100.0, False)]
+    ref = op_by_op(ctx, z, r, ops, old, None, 1500.0)
+    win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, 0, 0)
+    # separate host in / out
+    out = np.zeros((h, w), np.float32)
+    ctx.hfun_pass(win, z, _lib.OCSB_F32, w, old, w, out, w, 10.0, 10.0, None,
+                  1500.0, ops, 50)
+    np.testing.assert_array_equal(out, ref)
+    # aliased (in place), pinned
+    buf = torch.from_numpy(old.copy()).pin_memory()
+    ctx.hfun_pass(win, z, _lib.OCSB_F32, w, buf, w, buf, w, 10.0, 10.0, None,
+                  1500.0, ops, 50)
+    np.testing.assert_array_equal(buf.numpy(), ref)
+    # padded rows (window inside a wider buffer), DEM on the device, out host
+    W = w + 13
+    zpad = np.zeros((h, W), np.float32); zpad[:, :w] = z
+    opad = np.zeros((h, W), np.float32); opad[:, :w] = old
+    res = np.full((h, W), -3.0, np.float32)
+    zd = torch.from_numpy(zpad).cuda()
+    ctx.hfun_pass(win, zd, _lib.OCSB_F32, W, opad, W, res, W, 10.0, 10.0, None,
+                  1500.0, ops, 64)
+    np.testing.assert_array_equal(res[:, :w], ref)
+    assert np.all(res[:, w:] == -3.0)
+    # everything on the device
+    od = torch.from_numpy(old).cuda()
+    nd = torch.empty_like(od)
+    ctx.hfun_pass(win, zd, _lib.OCSB_F32, W, od, w, nd, w, 10.0, 10.0, None,
+                  1500.0, ops, 0)
+    ctx.sync()
+    np.testing.assert_array_equal(nd.cpu().numpy(), ref)
+
+
+def test_pass_row_band(ctx):
+    h, w = 300, 260
+    z, r, pts, _ = make_inputs(h, w, 8)
+    ops = [("feature", pts, len(pts), 0.001, 100.0, True),
+           ("limiter", 50.0, 1500.0, -30.0, 0.0, True)]
+    ref = op_by_op(ctx, z, r, ops, None, 100.0, 1500.0)
+    acc = np.full((h, w), -1.0, np.float32)
+    for rb, re in [(0, 7), (7, 130), (130, 300)]:
+        win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, rb, re)
+        ctx.hfun_pass(win, z, _lib.OCSB_F32, w, None, w, acc, w, 10.0, 10.0,
+                      100.0, 1500.0, ops, 40)
+    np.testing.assert_array_equal(acc, ref)
+
+
+def test_pass_errors(ctx):
+    h, w = 40, 40
+    z, r, pts, _ = make_inputs(h, w, 1)
+    win = _lib.make_win(r.get_window_bounds(r.full_window()), w, h, 0, 0)
+    out = np.zeros((h, w), np.float32)
+    with pytest.raises(_lib.OcsbError):      # limiter without a DEM
+        ctx.hfun_pass(win, None, _lib.OCSB_F32, w, None, w, out, w, 10.0, 10.0,
+                      None, None, [("limiter", None, None, None, None, False)])
+    with pytest.raises(_lib.OcsbError):      # target_size <= 0
+        ctx.hfun_pass(win, z, _lib.OCSB_F32, w, None, w, out, w, 10.0, 10.0,
+                      None, None, [("feature", pts, len(pts), 0.1, 0.0, False)])
+
+
+@pytest.mark.parametrize("chunk", [None, 128])
+def test_deferred_hfun_equals_eager(chunk):
+    """Python API: HfunRaster(deferred=True) queues add_* and streams the pass
+    into the caller's (pinned) buffer on get_values."""
+    import torch
+    h, w = 384, 512
+    z = S.synth_dem(h, w, seed=4)
+    tr = S.dem_transform(h)
+    pts = F.feature_points(S.synth_shoreline(h, w, seed=4, n_lines=2), 100.0)
+
+    def build(deferred):
+        r = ob.Raster.from_numpy(z, tr, crs=32618, chunk_size=chunk)
+        hf = ob.HfunRaster(r, hmin=100, hmax=1500, deferred=deferred)
+        hf.add_feature_points(pts, 0.001, 100.0)
+        hf.add_subtidal_flow_limiter(hmin=50, hmax=1500, lower_bound=-30,
+                                     upper_bound=0)
+        return hf
+
+    ref = build(False).get_values()
+    hd = build(True)
+    out = torch.empty((h, w), dtype=torch.float32).pin_memory()
+    got = hd.get_values(out=out)
+    np.testing.assert_array_equal(got, ref)
+    # the result can be looked at again and extended eagerly afterwards
+    np.testing.assert_array_equal(hd.get_values(), ref)
+    hd.add_gradient_delimiter(hmin=80, hmax=900)
+    he = build(False)
+    he.add_gradient_delimiter(hmin=80, hmax=900)
+    np.testing.assert_array_equal(hd.get_values(), he.get_values())
+    np.testing.assert_array_equal(hd.device_values.cpu().numpy(), he.get_values())
