@@ -64,7 +64,10 @@ int32_t Staged::init(ocsb_ctx *c, const void *p, int64_t rows_, int64_t width_,
         dev = nullptr;
         return OCSB_OK;
     }
-    if (ocsb_is_device_ptr(p)) {
+    // `p` is the (virtual) address of window row 0; only rows >= row0 exist
+    // (a rank's band buffer starts at its first held row), so the memory kind
+    // is asked of the first row that does
+    if (ocsb_is_device_ptr((const char *)p + (size_t)row0_ * (size_t)stride_ * elem_)) {
         dev = user;
         dev_stride = user_stride;
         staged = false;
@@ -893,11 +896,16 @@ extern "C" int32_t ocsb_hfun_pass(
     PassBuf bz, bi, bo;
     bz.user = (const char *)dem; bz.stride = dem_stride;
     bz.elem = dem_dtype == OCSB_F64 ? 8 : 4;
-    bz.host = need_dem && !ocsb_is_device_ptr(dem);
+    // memory kind of the first row that exists (see Staged::init)
+    auto first_row = [](const void *p, int64_t row, int64_t stride, size_t elem) {
+        return (const void *)((const char *)p + (size_t)row * (size_t)stride * elem);
+    };
+    const int zrow0 = rb > 0 ? rb - 1 : 0;
+    bz.host = need_dem && !ocsb_is_device_ptr(first_row(dem, zrow0, dem_stride, bz.elem));
     bi.user = (const char *)hfun_in; bi.stride = in_stride;
-    bi.host = hfun_in && !ocsb_is_device_ptr(hfun_in);
+    bi.host = hfun_in && !ocsb_is_device_ptr(first_row(hfun_in, rb, in_stride, 4));
     bo.user = (const char *)hfun_out; bo.stride = out_stride;
-    bo.host = !ocsb_is_device_ptr(hfun_out);
+    bo.host = !ocsb_is_device_ptr(first_row(hfun_out, rb, out_stride, 4));
 
     if (!bz.host && !bi.host && !bo.host) {
         // everything resident: one band, no copies
