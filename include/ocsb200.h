@@ -42,7 +42,7 @@ extern "C" {
 #define OCSB_ENCCL      (-4)
 #define OCSB_EOVERFLOW  (-5)
 
-#define OCSB_ABI_VERSION 2
+#define OCSB_ABI_VERSION 3
 
 /* DEM element types (the hfun raster itself is always float32,
  * ocsmesh/hfun/raster.py:76) */
@@ -113,7 +113,8 @@ int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 #define OCSB_KC_SPLINE_EVAL       9
 #define OCSB_KC_NEAREST          10
 #define OCSB_KC_BUCKET           11
-#define OCSB_KC_COUNT            12
+#define OCSB_KC_CONSTRAINT       12
+#define OCSB_KC_COUNT            13
 int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
 int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
                                 int64_t *launches);
@@ -206,6 +207,60 @@ int32_t ocsb_hfun_flow_limiter(ocsb_ctx *ctx, const ocsb_win *win,
                                double lower_bound, double upper_bound,
                                double ghmin, double ghmax,
                                int32_t fuse_clamp);
+
+/* ---- 8(f) next-2: add_constant_value ----------------------------------------
+ * Body of the window loop of HfunRaster.add_constant_value  ocsmesh/hfun/raster.py:1489-1498
+ *   v = old; v[(dem > lower_bound) & (dem < upper_bound)] = value; new = min(old, v)
+ * The compares run in the DEM dtype, `value` is rounded to float32 (numpy's
+ * casting of Python scalars).  lower/upper_bound: +-inf = None.  hfun_old,
+ * ghmin/ghmax/fuse_clamp as for ocsb_hfun_feature.                             */
+int32_t ocsb_hfun_constant_value(ocsb_ctx *ctx, const ocsb_win *win,
+                                 const void *dem, int32_t dem_dtype,
+                                 int64_t dem_stride,
+                                 const float *hfun_old, int64_t old_stride,
+                                 float *hfun_new, int64_t new_stride,
+                                 double value, double lower_bound,
+                                 double upper_bound, double ghmin, double ghmax,
+                                 int32_t fuse_clamp);
+
+/* ---- 8(f) next-2: topography constraints ------------------------------------
+ * TopoConstConstraint.apply / TopoFuncConstraint.apply     ocsmesh/features/constraint.py:164-177, 207-224
+ * followed by Constraint._apply_rate                       ocsmesh/features/constraint.py:83-121
+ *   mask = (dem > lower_bound) & (dem < upper_bound) & ~satisfies(hfun, val)
+ *   hfun[mask] = val
+ *   rate != NaN: every non-mask pixel p with nearest mask pixel m (cKDTree of
+ *   the window's mask pixels, Euclidean, window coordinates):
+ *       t = hfun[m] * (1 + |p - m| * rate * sign);  hfun[p] = t unless
+ *       satisfies(hfun[p], t)          (sign = -1 for MIN, +1 for MAX)
+ * satisfies = np.greater for OCSB_VT_MIN, np.less for OCSB_VT_MAX.
+ * values   : NULL -> the constant `value` (TopoConst; compared in float32),
+ *            else a window of per-pixel values (TopoFunc: func(dem) evaluated
+ *            by the caller; values_dtype OCSB_F32 / OCSB_F64)
+ * hfun     : read-modify-written in place (the global [hmin, hmax] clamp of
+ *            apply_constraints is a separate ocsb_hfun_clamp call)
+ * A rate needs the whole window on one device (row_begin/row_end unset).      */
+#define OCSB_VT_MIN 0
+#define OCSB_VT_MAX 1
+int32_t ocsb_hfun_topo_constraint(ocsb_ctx *ctx, const ocsb_win *win,
+                                  const void *dem, int32_t dem_dtype,
+                                  int64_t dem_stride,
+                                  float *hfun, int64_t hfun_stride,
+                                  const void *values, int32_t values_dtype,
+                                  int64_t values_stride, double value,
+                                  double lower_bound, double upper_bound,
+                                  int32_t value_type, double rate);
+
+/* CourantNumConstraint.apply                               ocsmesh/features/constraint.py:254-313
+ * (utils.py:1677-1835: linear-wave particle velocity, characteristic
+ * velocity, element size for a Courant number).  Arithmetic in the DEM dtype
+ * like numpy; pixels whose approximate Courant number does not satisfy
+ * `courant` (np.greater for MIN, np.less for MAX) get the size that does.     */
+int32_t ocsb_hfun_courant_constraint(ocsb_ctx *ctx, const ocsb_win *win,
+                                     const void *dem, int32_t dem_dtype,
+                                     int64_t dem_stride,
+                                     float *hfun, int64_t hfun_stride,
+                                     double courant, double timestep,
+                                     double wave_amplitude, int32_t value_type);
 
 /* ---- A4 + A6..A10 as ONE streamed pass --------------------------------------
  * The reference applies every add_* to the whole raster before the next one

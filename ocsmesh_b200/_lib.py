@@ -20,7 +20,8 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
-KC_COUNT = 12
+KC_COUNT = 13
+VT_MIN, VT_MAX = 0, 1
 NONE = float("nan")
 
 c_i32, c_i64, c_f64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_double, C.c_float, C.c_void_p
@@ -87,6 +88,16 @@ SIGNATURES = {
     "ocsb_hfun_pass": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                                c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64,
                                c_f64, C.POINTER(ocsb_hfun_op), c_i32, c_i32]),
+    "ocsb_hfun_constant_value": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                         c_i64, c_vp, c_i64, c_vp, c_i64,
+                                         c_f64, c_f64, c_f64, c_f64, c_f64,
+                                         c_i32]),
+    "ocsb_hfun_topo_constraint": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                          c_i64, c_vp, c_i64, c_vp, c_i32, c_i64,
+                                          c_f64, c_f64, c_f64, c_i32, c_f64]),
+    "ocsb_hfun_courant_constraint": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp,
+                                             c_i32, c_i64, c_vp, c_i64, c_f64,
+                                             c_f64, c_f64, c_i32]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -277,6 +288,33 @@ class Context:
             ptr(hfun_in), int(in_stride), ptr(hfun_out), int(out_stride),
             float(dx), float(dy), opt(ghmin), opt(ghmax), arr, len(ops),
             int(band_rows)))
+
+    def hfun_constant_value(self, win, dem, dem_dtype, dem_stride, old,
+                            old_stride, new, new_stride, value, lower_bound,
+                            upper_bound, ghmin, ghmax, fuse_clamp=False):
+        check(self.lib.ocsb_hfun_constant_value(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(old), int(old_stride), ptr(new), int(new_stride), float(value),
+            float(lower_bound), float(upper_bound), opt(ghmin), opt(ghmax),
+            int(bool(fuse_clamp))))
+
+    def hfun_topo_constraint(self, win, dem, dem_dtype, dem_stride, hfun,
+                             hfun_stride, values, values_dtype, values_stride,
+                             value, lower_bound, upper_bound, value_type, rate):
+        """``value_type``: VT_MIN / VT_MAX; ``rate`` None = no relaxation."""
+        check(self.lib.ocsb_hfun_topo_constraint(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(hfun), int(hfun_stride), ptr(values), int(values_dtype),
+            int(values_stride), opt(value), float(lower_bound),
+            float(upper_bound), int(value_type), opt(rate)))
+
+    def hfun_courant_constraint(self, win, dem, dem_dtype, dem_stride, hfun,
+                                hfun_stride, courant, timestep, wave_amplitude,
+                                value_type):
+        check(self.lib.ocsb_hfun_courant_constraint(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(hfun), int(hfun_stride), float(courant), float(timestep),
+            float(wave_amplitude), int(value_type)))
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

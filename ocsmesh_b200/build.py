@@ -28,6 +28,8 @@ SOURCES = [
     "k_bucket.cu",
     "k_spline.cu",
     "k_feature.cu",
+    "k_nearest.cu",
+    "k_constraint.cu",
 ]
 
 NVCC_FLAGS = [

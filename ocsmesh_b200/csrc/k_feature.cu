@@ -591,9 +591,13 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         E.vec_old = old_ && (((uintptr_t)old_ & 15) == 0) && (old_stride % 4 == 0);
         E.vec_new = (((uintptr_t)new_ & 15) == 0) && (new_stride % 4 == 0);
         E.overflow = overflow;
+        E.rate_vals = a.rate_vals; E.rate_mask = a.rate_mask;
+        E.rate = a.rate; E.rate_sign = a.rate_sign; E.rate_is_min = a.rate_is_min;
+        OCSB_REQUIRE(!a.rate_vals || (old_ && a.rate_mask),
+                     "k_hfun_feature: rate epilogue needs old values and a mask");
         OCSB_TIME(ctx, KC_FEATURE_EVAL);
         const dim3 egrid((unsigned)lv[0].ntx, (unsigned)lv[0].nty);
-        if (idx_out || dist_out) {
+        if (idx_out || dist_out || a.rate_vals) {
             if (old_) eval_kernel<true, true><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
             else eval_kernel<true, false><<<egrid, kEvalThreads, 0, ctx->stream>>>(E);
         } else {
@@ -620,10 +624,4 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
     ocsb_set_error("ocsb_hfun_feature: candidate pools overflowed after 6 "
                    "attempts (degenerate vertex set?)");
     return OCSB_EOVERFLOW;
-}
-
-int32_t k_nearest_vertex(ocsb_ctx *, const double *, int64_t, const double *,
-                         int64_t, double, double *, int64_t *) {
-    ocsb_set_error("ocsb_nearest_vertex: not implemented in this build");
-    return OCSB_EINVAL;
 }

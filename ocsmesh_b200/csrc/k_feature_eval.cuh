@@ -55,6 +55,11 @@ struct EvalArgs {
     float old_const;        // pre-op value everywhere when old_ == nullptr
     int vec_old, vec_new;
     const int *overflow;
+    // Constraint._apply_rate epilogue (exact path only, see FeatureArgs)
+    const float *rate_vals;
+    const uint8_t *rate_mask;
+    double rate, rate_sign;
+    int rate_is_min;
 };
 
 constexpr int kSubH = 16;   // filter rect: kLeafW x kSubH px = two stacked leaves
@@ -331,6 +336,24 @@ __global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
                     if (WANT_OUT) {
                         const bool hit = d2 < A.r2;
                         const double d = hit ? __dsqrt_rn(d2) : A.r;
+                        if (A.rate_vals) {
+                            // temp = values[mask][neighbors] * (1 + d*rate*sign);
+                            // non-mask pixels that do not satisfy it take it
+                            // (features/constraint.py:106-117); no clamp, no min
+                            float res = o[j][k];
+                            if (gcol + k <= c1 &&
+                                !A.rate_mask[(int64_t)(g.row0 + row) * g.w + gcol + k]) {
+                                const double f = __dadd_rn(
+                                    1.0, __dmul_rn(__dmul_rn(d, A.rate), A.rate_sign));
+                                const double t =
+                                    __dmul_rn((double)A.rate_vals[bid[j * 4 + k]], f);
+                                const bool sat = A.rate_is_min ? ((double)res > t)
+                                                               : ((double)res < t);
+                                if (!sat) res = (float)t;
+                            }
+                            out[k] = res;
+                            continue;
+                        }
                         // values = expansion_rate*target_size*distances + target_size
                         vf = (float)__dadd_rn(__dmul_rn(A.rate_target, d), A.target);
                         if (gcol + k <= c1) {

@@ -283,7 +283,7 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
     static const char *names[OCSB_KC_COUNT] = {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
-        "spline_eval", "nearest_vertex", "bucket_nodes"};
+        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
@@ -574,6 +574,167 @@ extern "C" int32_t ocsb_hfun_flow_limiter(
     OCSB_TRY(k_flow_limiter(ctx, w, h, rb, re, sz.dev, dem_dtype, sz.dev_stride, oldp,
                             olds, (float *)sn.dev, sn.dev_stride, a));
     return finish_call(ctx, {&sz, &so, &sn});
+}
+
+// ---------------------------------------------------------------------------
+// next-2: add_constant_value, Topo / Courant constraints (+ _apply_rate)
+// ---------------------------------------------------------------------------
+namespace {
+inline char *row_ptr(void *base, int64_t row, int64_t stride, size_t elem) {
+    return base ? (char *)base + (size_t)row * (size_t)stride * elem : nullptr;
+}
+}  // namespace
+
+extern "C" int32_t ocsb_hfun_constant_value(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, const float *hfun_old, int64_t old_stride,
+    float *hfun_new, int64_t new_stride, double value, double lower_bound,
+    double upper_bound, double ghmin, double ghmax, int32_t fuse_clamp) {
+    CTX_ENTER("ocsb_hfun_constant_value");
+    OCSB_TRY(check_win(win, "ocsb_hfun_constant_value"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_hfun_constant_value: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(dem && hfun_new && dem_stride >= win->width &&
+                     (!hfun_old || old_stride >= win->width) &&
+                     new_stride >= win->width,
+                 "ocsb_hfun_constant_value: bad buffers");
+    OCSB_REQUIRE(!ocsb_is_none(value) && !ocsb_is_none(lower_bound) &&
+                     !ocsb_is_none(upper_bound),
+                 "ocsb_hfun_constant_value: NaN argument");
+    const int w = win->width;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_constant_value", &rb, &re));
+    const int hb = re - rb;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    Staged sz, so, sn;
+    OCSB_TRY(sz.init(ctx, dem, hb, w, dem_stride, es, STAGE_IN, rb));
+    const bool alias = (const void *)hfun_old == (const void *)hfun_new &&
+                       old_stride == new_stride;
+    if (alias) {
+        OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_INOUT, rb));
+    } else {
+        if (hfun_old)
+            OCSB_TRY(so.init(ctx, hfun_old, hb, w, old_stride, 4, STAGE_IN, rb));
+        OCSB_TRY(sn.init(ctx, hfun_new, hb, w, new_stride, 4, STAGE_OUT, rb));
+    }
+    void *oldb = alias ? sn.dev : so.dev;
+    const int64_t olds = alias ? sn.dev_stride : so.dev_stride;
+    OCSB_TRY(k_constant_value(
+        ctx, w, hb, row_ptr(sz.dev, rb, sz.dev_stride, es), dem_dtype,
+        sz.dev_stride, (const float *)row_ptr(oldb, rb, olds, 4), olds,
+        (float *)row_ptr(sn.dev, rb, sn.dev_stride, 4), sn.dev_stride, value,
+        lower_bound, upper_bound, ghmin, ghmax, fuse_clamp));
+    return finish_call(ctx, {&sz, &so, &sn});
+}
+
+extern "C" int32_t ocsb_hfun_topo_constraint(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, float *hfun, int64_t hfun_stride, const void *values,
+    int32_t values_dtype, int64_t values_stride, double value,
+    double lower_bound, double upper_bound, int32_t value_type, double rate) {
+    CTX_ENTER("ocsb_hfun_topo_constraint");
+    OCSB_TRY(check_win(win, "ocsb_hfun_topo_constraint"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_hfun_topo_constraint: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(value_type == OCSB_VT_MIN || value_type == OCSB_VT_MAX,
+                 "Invalid value type for constraint!");
+    OCSB_REQUIRE(dem && hfun && dem_stride >= win->width &&
+                     hfun_stride >= win->width,
+                 "ocsb_hfun_topo_constraint: bad buffers");
+    OCSB_REQUIRE(!values || ((values_dtype == OCSB_F32 || values_dtype == OCSB_F64) &&
+                             values_stride >= win->width),
+                 "ocsb_hfun_topo_constraint: bad values array");
+    OCSB_REQUIRE(values || !ocsb_is_none(value),
+                 "ocsb_hfun_topo_constraint: value is NaN");
+    OCSB_REQUIRE(!ocsb_is_none(lower_bound) && !ocsb_is_none(upper_bound),
+                 "ocsb_hfun_topo_constraint: NaN bound");
+    const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_topo_constraint", &rb, &re));
+    const int hb = re - rb;
+    const bool with_rate = !ocsb_is_none(rate);
+    // _apply_rate looks for the nearest mask pixel of the WHOLE window
+    OCSB_REQUIRE(!with_rate || (rb == 0 && re == h),
+                 "ocsb_hfun_topo_constraint: a rate needs the whole window on "
+                 "one device (row band [%d, %d) of %d rows given)", rb, re, h);
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    const size_t vs = values_dtype == OCSB_F64 ? 8 : 4;
+    Staged sz, sh, sv;
+    OCSB_TRY(sz.init(ctx, dem, hb, w, dem_stride, es, STAGE_IN, rb));
+    OCSB_TRY(sh.init(ctx, hfun, hb, w, hfun_stride, 4, STAGE_INOUT, rb));
+    if (values)
+        OCSB_TRY(sv.init(ctx, values, hb, w, values_stride, vs, STAGE_IN, rb));
+    ScratchGuard sg(ctx);
+    uint8_t *mask = nullptr;
+    if (with_rate) OCSB_TRY(sg.get(&mask, (size_t)w * hb));
+    const int is_min = value_type == OCSB_VT_MIN;
+    float *hb_ptr = (float *)row_ptr(sh.dev, rb, sh.dev_stride, 4);
+    OCSB_TRY(k_topo_mask(ctx, w, hb, row_ptr(sz.dev, rb, sz.dev_stride, es),
+                         dem_dtype, sz.dev_stride, hb_ptr, sh.dev_stride,
+                         row_ptr(sv.dev, rb, sv.dev_stride, vs), values_dtype,
+                         sv.dev_stride, value, lower_bound, upper_bound, is_min,
+                         mask, nullptr));
+    if (with_rate) {
+        LinAxis ax, ay;
+        win_axes(win, &ax, &ay);
+        double *verts = nullptr;
+        float *vals = nullptr;
+        int64_t nvb = 0;
+        OCSB_TRY(k_mask_boundary(ctx, sg, mask, w, h, ax, ay, hb_ptr,
+                                 sh.dev_stride, &verts, &vals, &nvb));
+        // `if not np.any(mask): return values` (constraint.py:87-88); a mask
+        // covering the whole window has no boundary and no pixel to relax
+        if (nvb > 0) {
+            FeatureArgs fa;
+            fa.ax = ax; fa.ay = ay;
+            fa.rate_target = 0.0; fa.target = 1.0;
+            fa.has_hmin = fa.has_hmax = 0;
+            fa.hmin_f = fa.hmax_f = 0.f;
+            fa.fuse_clamp = 0;
+            fa.r = std::numeric_limits<double>::infinity();
+            fa.row_begin = 0; fa.row_end = h;
+            fa.rate_vals = vals;
+            fa.rate_mask = mask;
+            fa.rate = rate;
+            fa.rate_sign = is_min ? -1.0 : 1.0;
+            fa.rate_is_min = is_min;
+            OCSB_TRY(k_hfun_feature(ctx, fa, verts, nvb, hb_ptr, sh.dev_stride,
+                                    hb_ptr, sh.dev_stride, nullptr, nullptr));
+        }
+    }
+    return finish_call(ctx, {&sz, &sh, &sv});
+}
+
+extern "C" int32_t ocsb_hfun_courant_constraint(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, float *hfun, int64_t hfun_stride, double courant,
+    double timestep, double wave_amplitude, int32_t value_type) {
+    CTX_ENTER("ocsb_hfun_courant_constraint");
+    OCSB_TRY(check_win(win, "ocsb_hfun_courant_constraint"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_hfun_courant_constraint: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(value_type == OCSB_VT_MIN || value_type == OCSB_VT_MAX,
+                 "Invalid value type for constraint!");
+    OCSB_REQUIRE(dem && hfun && dem_stride >= win->width &&
+                     hfun_stride >= win->width,
+                 "ocsb_hfun_courant_constraint: bad buffers");
+    OCSB_REQUIRE(!ocsb_is_none(courant) && !ocsb_is_none(timestep) &&
+                     !ocsb_is_none(wave_amplitude),
+                 "ocsb_hfun_courant_constraint: NaN argument");
+    const int w = win->width;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_courant_constraint", &rb, &re));
+    const int hb = re - rb;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    Staged sz, sh;
+    OCSB_TRY(sz.init(ctx, dem, hb, w, dem_stride, es, STAGE_IN, rb));
+    OCSB_TRY(sh.init(ctx, hfun, hb, w, hfun_stride, 4, STAGE_INOUT, rb));
+    OCSB_TRY(k_courant(ctx, w, hb, row_ptr(sz.dev, rb, sz.dev_stride, es),
+                       dem_dtype, sz.dev_stride,
+                       (float *)row_ptr(sh.dev, rb, sh.dev_stride, 4),
+                       sh.dev_stride, courant, timestep, wave_amplitude,
+                       value_type == OCSB_VT_MIN));
+    return finish_call(ctx, {&sz, &sh});
 }
 
 // ---------------------------------------------------------------------------

@@ -18,7 +18,7 @@ enum {
     KC_FEATURE_EVAL = OCSB_KC_FEATURE_EVAL, KC_INTERP = OCSB_KC_INTERP,
     KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
     KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
-    KC_BUCKET = OCSB_KC_BUCKET
+    KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT
 };
 
 // ---------------------------------------------------------------------------
@@ -245,6 +245,13 @@ struct FeatureArgs {
     // int, zeroed by the caller), and the evaluation kernel writes nothing if
     // it is set -- the caller checks later and redoes the band synchronously.
     int *ext_overflow = nullptr;
+    // Constraint._apply_rate epilogue instead of the size law (exact path):
+    //   t = vals[idx] * (1 + d*rate*sign); new = satisfies(old, t) ? old : t
+    // for pixels outside `rate_mask` (features/constraint.py:104-117).
+    const float *rate_vals = nullptr;    // per-vertex values, nv floats
+    const uint8_t *rate_mask = nullptr;  // window row 0, stride = width
+    double rate = 0.0, rate_sign = 0.0;
+    int rate_is_min = 0;
 };
 int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
                        const double *verts, int64_t nv, const float *old_,
@@ -253,6 +260,25 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
 int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
                          const double *q, int64_t nq, double r, double *dist,
                          int64_t *idx);
+
+// k_constraint.cu
+int32_t k_constant_value(ocsb_ctx *ctx, int w, int h, const void *dem,
+                         int dem_dtype, int64_t zs, const float *old_,
+                         int64_t os, float *new_, int64_t ns, double value,
+                         double lb, double ub, double ghmin, double ghmax,
+                         int fuse_clamp);
+int32_t k_topo_mask(ocsb_ctx *ctx, int w, int h, const void *dem, int dem_dtype,
+                    int64_t zs, float *hfun, int64_t hs, const void *vals,
+                    int vals_dtype, int64_t vs, double vconst, double lb,
+                    double ub, int is_min, uint8_t *mask,
+                    unsigned long long *nmask);
+int32_t k_courant(ocsb_ctx *ctx, int w, int h, const void *dem, int dem_dtype,
+                  int64_t zs, float *hfun, int64_t hs, double cval, double dt,
+                  double nu, int is_min);
+int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
+                        int w, int h, LinAxis ax, LinAxis ay, const float *hfun,
+                        int64_t hs, double **verts_out, float **vals_out,
+                        int64_t *nv_out);
 
 int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
                  int dem_dtype, int64_t dem_stride, const uint8_t *mask,
