@@ -1,0 +1,170 @@
+"""Size-function constraints on the raster path.
+
+Mirror of ``ocsmesh/features/constraint.py``: same class names, constructor
+arguments and ``value_type`` / ``rate`` semantics.  ``HfunRaster`` applies them
+window by window on the device (``apply_constraints``,
+``ocsmesh/hfun/raster.py:509-568``) through ``ocsb_hfun_topo_constraint`` /
+``ocsb_hfun_courant_constraint``; there is no host implementation here.
+``RegionConstraint`` needs shapely's point-in-polygon test and is outside this
+build.
+"""
+from __future__ import annotations
+
+from enum import Enum
+from typing import Callable
+
+import numpy as np
+
+from . import _lib
+
+ConstraintValueType = Enum("ConstraintValueType", "MIN MAX")
+
+
+class Constraint:
+    """``features/constraint.py:17-80`` (value type, rate sign)."""
+
+    def __init__(self, value_type: str = 'min', rate: float = 0.1):
+        self._rate = rate
+        if isinstance(value_type, ConstraintValueType):
+            self._val_type = value_type
+        elif isinstance(value_type, str):
+            self._val_type = ConstraintValueType[value_type.upper()]
+        else:
+            raise ValueError("Invalid input for value type!")
+
+    @property
+    def type(self):
+        return type(self)
+
+    @property
+    def value_type(self):
+        return self._val_type
+
+    @property
+    def satisfies(self):
+        if self.value_type == ConstraintValueType.MIN:
+            return np.greater
+        if self.value_type == ConstraintValueType.MAX:
+            return np.less
+        raise ValueError("Invalid value type for constraint!")
+
+    @property
+    def rate_sign(self):
+        if self.value_type == ConstraintValueType.MIN:
+            return -1
+        if self.value_type == ConstraintValueType.MAX:
+            return +1
+        raise ValueError("Invalid value type for constraint!")
+
+    @property
+    def _vt_code(self) -> int:
+        return (_lib.VT_MIN if self.value_type == ConstraintValueType.MIN
+                else _lib.VT_MAX)
+
+    def apply(self, *args, **kwargs):
+        raise NotImplementedError(
+            "constraints run on the device through HfunRaster."
+            "apply_constraints; ocsmesh_b200 has no host implementation")
+
+    # one (semantic window, device tile) of an HfunRaster; ``dem`` / ``hfun``
+    # are (address of the window's top-left pixel, row stride in elements)
+    def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                      hfun_stride, dem_view):
+        raise NotImplementedError
+
+
+class TopoConstConstraint(Constraint):
+    """``features/constraint.py:135-177``."""
+
+    def __init__(self, value, upper_bound=np.inf, lower_bound=-np.inf,
+                 value_type: str = 'min', rate=None):
+        super().__init__(value_type, rate)
+        if np.ndim(value) != 0:
+            raise NotImplementedError(
+                "matrix-valued TopoConstConstraint is outside this build")
+        self._lb = lower_bound
+        self._ub = upper_bound
+        self._val = value
+
+    @property
+    def value(self):
+        return self._val
+
+    @property
+    def topo_bounds(self):
+        return self._lb, self._ub
+
+    def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                      hfun_stride, dem_view):
+        ctx.hfun_topo_constraint(
+            cwin, dem, dem_code, dem_stride, hfun, hfun_stride, None,
+            _lib.OCSB_F32, 0, float(self._val), float(self._lb),
+            float(self._ub), self._vt_code, self._rate)
+
+
+class TopoFuncConstraint(Constraint):
+    """``features/constraint.py:180-224``.  ``function`` is the caller's
+    Python: it is offered the DEM window as a CUDA tensor first (arithmetic
+    lambdas such as the default ``i / 2.0`` stay on the device) and, if it
+    cannot take one, the window as a numpy array."""
+
+    def __init__(self, function: Callable = lambda i: i / 2.0,
+                 upper_bound=np.inf, lower_bound=-np.inf,
+                 value_type: str = 'min', rate=None):
+        super().__init__(value_type, rate)
+        self._lb = lower_bound
+        self._ub = upper_bound
+        self._func = lambda i: i / 2.0
+        if callable(function):
+            self._func = function
+
+    @property
+    def topo_bounds(self):
+        return self._lb, self._ub
+
+    def _values(self, dem_view):
+        import torch
+        try:
+            vals = self._func(dem_view)
+            if not isinstance(vals, torch.Tensor):
+                raise TypeError("function did not return a tensor")
+        except Exception:  # pylint: disable=broad-except
+            host = self._func(dem_view.cpu().numpy())
+            vals = torch.from_numpy(np.ascontiguousarray(host)).to(dem_view.device)
+        if vals.dtype not in (torch.float32, torch.float64):
+            vals = vals.to(torch.float64)
+        if tuple(vals.shape) != tuple(dem_view.shape):
+            vals = vals.expand(dem_view.shape)
+        return vals.contiguous()
+
+    def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                      hfun_stride, dem_view):
+        import torch
+        vals = self._values(dem_view)
+        code = _lib.OCSB_F32 if vals.dtype == torch.float32 else _lib.OCSB_F64
+        # `vals` covers the device tile only; the ABI wants window row 0
+        rb = cwin.row_begin
+        base = vals.data_ptr() - rb * vals.shape[1] * vals.element_size()
+        ctx.hfun_topo_constraint(
+            cwin, dem, dem_code, dem_stride, hfun, hfun_stride, base, code,
+            vals.shape[1], None, float(self._lb), float(self._ub),
+            self._vt_code, self._rate)
+        ctx.sync()   # `vals` is freed on return
+
+
+class CourantNumConstraint(Constraint):
+    """``features/constraint.py:227-313``."""
+
+    def __init__(self, value: float, timestep: float = 150,
+                 wave_amplitude: float = 2.0, value_type: str = 'max'):
+        super().__init__(value_type, rate=None)
+        self._value = value
+        self._dt = timestep
+        self._nu = wave_amplitude
+
+    def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                      hfun_stride, dem_view):
+        ctx.hfun_courant_constraint(
+            cwin, dem, dem_code, dem_stride, hfun, hfun_stride,
+            float(self._value), float(self._dt), float(self._nu),
+            self._vt_code)

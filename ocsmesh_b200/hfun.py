@@ -27,6 +27,7 @@ from typing import List, Optional, Sequence, Union
 import numpy as np
 
 from . import _lib
+from . import constraint as _constraint
 from . import features as _features
 from . import geotiff
 from .raster import CRS, Raster, Window
@@ -160,7 +161,7 @@ class HfunRaster:
     def _can_defer(self) -> bool:
         """Queued execution runs the whole op list window by window, which
         equals the reference's op-by-op order unless windows overlap."""
-        if not self._deferred:
+        if not self._deferred or self._constraints:
             return False
         return not ((self._overlap or 0) > 0 and len(self._windows()) > 1)
 
@@ -392,28 +393,159 @@ class HfunRaster:
         self.apply_constraints(self._constraints)
 
     def apply_constraints(self, constraint_list) -> None:
-        """``hfun/raster.py:509-568``.  Custom constraint objects are a
-        "next" row of the scope table; with none registered the pass is the
-        global [hmin, hmax] clamp, one streaming kernel over the owned band."""
-        if len(list(constraint_list)) > 0:
-            raise NotImplementedError(
-                "custom Constraint objects are not part of the accelerated "
-                "path yet (SURVEY.md 8(f) next-2)")
-        if self._hmin is None and self._hmax is None:
-            return
+        """``hfun/raster.py:509-568``: per window run every constraint on the
+        (hfun, DEM) pair, then clamp to the global [hmin, hmax].  With no
+        constraint registered the pass is the clamp alone, one streaming
+        kernel over the owned band."""
+        constraint_list = list(constraint_list)
         w = self.width
         rb, re = self._band
         ctx = self._ctx()
+        if len(constraint_list) == 0:
+            if self._hmin is None and self._hmax is None:
+                return
+            self._materialize()
+            ctx.hfun_clamp(self._hfun, w, w, re - rb, self._hmin, self._hmax)
+            return
+        for c in constraint_list:
+            if not isinstance(c, _constraint.Constraint):
+                raise TypeError(f"not a device constraint: {type(c)!r}")
+        self._check_projected()
         self._materialize()
-        ctx.hfun_clamp(self._hfun, w, w, re - rb, self._hmin, self._hmax)
+        windows = self._windows()
+        dem = self._raster.device_band(1, self._device)
+        dem_origin = self._raster.device_band_origin(1, self._device)
+        es = dem.element_size()
+        code = _dem_dtype_code(dem)
+        old = self._hfun
+        new = old
+        if self._needs_double_buffer(windows):
+            # every window reads the PRE-pass raster, the later window wins
+            new = old.clone()
+        for win in windows:
+            band = self._band_of(win)
+            if band is None:
+                continue
+            r0 = win.row_off + band[0] - rb
+            r1 = win.row_off + band[1] - rb
+            cs = slice(win.col_off, win.col_off + win.width)
+            if new is not old:
+                new[r0:r1, cs].copy_(old[r0:r1, cs])
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            poff = (win.row_off - dem_origin) * w + win.col_off
+            d0 = win.row_off + band[0] - dem_origin
+            dem_view = dem[d0:d0 + (band[1] - band[0]), cs]
+            for c in constraint_list:
+                c._apply_device(ctx, cw, dem.data_ptr() + poff * es, code, w,
+                                self._hfun_ptr(new, win), w, dem_view)
+            if self._hmin is not None or self._hmax is not None:
+                ctx.hfun_clamp(self._hfun_ptr(new, win) + band[0] * w * 4, w,
+                               win.width, band[1] - band[0], self._hmin,
+                               self._hmax)
+        self._hfun = new
 
     def _fuse_clamp(self) -> bool:
         """The decorator's clamp re-pass is folded into the op's own kernel
-        (same per-pixel result: clamp(min(old, new)))."""
+        (same per-pixel result: clamp(min(old, new))) -- unless constraints
+        are held or registered, in which case ``_after_op`` runs the pass."""
         if self._hold_const:
             self._hold_const_hit += 1
             return False
-        return True
+        return len(self._constraints) == 0
+
+    def _after_op(self, fused: bool) -> None:
+        """``apply_constraints_wrap`` (``features/constraint.py:398-424``)
+        for an op whose kernel did not absorb the clamp."""
+        if not fused and not self._hold_const:
+            self.apply_constraints(self._constraints)
+
+    def _register(self, constraint) -> None:
+        self._constraints.append(constraint)
+        self.apply_added_constraints()
+
+    def add_topo_bound_constraint(self, value, upper_bound: float = np.inf,
+                                  lower_bound: float = -np.inf,
+                                  value_type: str = 'min',
+                                  rate: float = 0.01) -> None:
+        """``hfun/raster.py:571-623``."""
+        self._register(_constraint.TopoConstConstraint(
+            value, upper_bound, lower_bound, value_type, rate))
+
+    def add_topo_func_constraint(self, func=lambda i: i / 2.0,
+                                 upper_bound: float = np.inf,
+                                 lower_bound: float = -np.inf,
+                                 value_type: str = 'min',
+                                 rate: float = 0.01) -> None:
+        """``hfun/raster.py:625-677``."""
+        self._register(_constraint.TopoFuncConstraint(
+            func, upper_bound, lower_bound, value_type, rate))
+
+    def add_courant_num_constraint(self, upper_bound: Optional[float] = 0.9,
+                                   lower_bound: Optional[float] = None,
+                                   timestep: float = 150,
+                                   wave_amplitude: float = 2) -> None:
+        """``hfun/raster.py:679-736``."""
+        if upper_bound is None and lower_bound is None:
+            raise ValueError(
+                "Both upper and lower Courant bounds can NOT be None!")
+        if upper_bound is not None:
+            self._constraints.append(_constraint.CourantNumConstraint(
+                value=upper_bound, timestep=timestep,
+                wave_amplitude=wave_amplitude, value_type='max'))
+        if lower_bound is not None:
+            self._constraints.append(_constraint.CourantNumConstraint(
+                value=lower_bound, timestep=timestep,
+                wave_amplitude=wave_amplitude, value_type='min'))
+        self.apply_added_constraints()
+
+    def add_region_constraint(self, *args, **kwargs) -> None:
+        raise NotImplementedError(
+            "RegionConstraint needs shapely's point-in-polygon test "
+            "(hfun/raster.py:738-800); outside this build")
+
+    def add_patch(self, *args, **kwargs) -> None:
+        raise NotImplementedError(
+            "add_patch rasterises polygons with GDAL (rasterio.mask."
+            "raster_geometry_mask, hfun/raster.py:890-933); outside this build")
+
+    # ---- add_constant_value -------------------------------------------------
+    def add_constant_value(self, value: float,
+                           lower_bound: Optional[float] = None,
+                           upper_bound: Optional[float] = None) -> None:
+        """``hfun/raster.py:1438-1502``."""
+        lower_bound = -float('inf') if lower_bound is None \
+            else float(lower_bound)
+        upper_bound = float('inf') if upper_bound is None \
+            else float(upper_bound)
+        self._materialize_queue()
+        ctx = self._ctx()
+        windows = self._windows()
+        fuse = self._fuse_clamp()
+        w = self.width
+        dem = self._raster.device_band(1, self._device)
+        dem_origin = self._raster.device_band_origin(1, self._device)
+        es = dem.element_size()
+        code = _dem_dtype_code(dem)
+        old = self._hfun
+        new = old
+        if not self._pristine and self._needs_double_buffer(windows):
+            new = old.clone()
+        for win in windows:
+            band = self._band_of(win)
+            if band is None:
+                continue
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            poff = (win.row_off - dem_origin) * w + win.col_off
+            ctx.hfun_constant_value(
+                cw, dem.data_ptr() + poff * es, code, w,
+                self._old_ptr(old, win), w, self._hfun_ptr(new, win), w,
+                value, lower_bound, upper_bound, self._hmin, self._hmax,
+                fuse_clamp=fuse)
+        self._hfun = new
+        self._pristine = False
+        self._after_op(fuse)
 
     # ---- A5: add_contour ----------------------------------------------------
     def add_contour(self, level: Union[List[float], float],
@@ -513,6 +645,7 @@ class HfunRaster:
         self._pristine = False
         # keep `verts` alive until the stream has consumed it
         self._last_verts = verts
+        self._after_op(fuse)
 
     # ---- A8/A9: flow limiter / gradient delimiter ----------------------------
     def add_subtidal_flow_limiter(self, hmin: Optional[float] = None,
@@ -563,6 +696,7 @@ class HfunRaster:
                 self._hmax, fuse_clamp=fuse)
         self._hfun = new
         self._pristine = False
+        self._after_op(fuse)
 
     def add_gradient_delimiter(self, hmin: Optional[float] = None,
                                hmax: Optional[float] = None) -> None:

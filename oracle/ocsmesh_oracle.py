@@ -44,7 +44,8 @@ __all__ = [
     "add_feature", "flow_limiter_window", "add_subtidal_flow_limiter",
     "apply_constraints_clamp", "mesh_interpolate_worker", "mesh_interpolate",
     "OracleHfun", "marching_squares", "get_contour", "nearest_vertex",
-    "min_combine", "apply_rate",
+    "min_combine", "apply_rate", "add_constant_value_window",
+    "TopoConstConstraint", "TopoFuncConstraint", "CourantNumConstraint",
 ]
 
 FLT_MAX = np.finfo(np.float32).max
@@ -394,15 +395,75 @@ class OracleHfun:
 
     def _clamp_pass(self):
         """``apply_constraints_wrap`` -> ``apply_added_constraints`` ->
-        ``apply_constraints([])`` (``features/constraint.py:420-423``,
-        ``hfun/raster.py:488-568``)."""
+        ``apply_constraints(self._constraints)``
+        (``features/constraint.py:420-423``, ``hfun/raster.py:488-568``)."""
+        self.apply_constraints(getattr(self, "_constraints", []))
+
+    def apply_constraints(self, constraint_list):
+        """``HfunRaster.apply_constraints`` (``hfun/raster.py:509-568``),
+        projected-CRS branch (``xy = self.get_xy(window)``)."""
         new = self.values.copy()
         for win in self._iter():
             sl = (slice(win.row_off, win.row_off + win.height),
                   slice(win.col_off, win.col_off + win.width))
-            new[sl] = apply_constraints_clamp(self.values[sl], self.hmin,
+            hfun_values = self.values[sl].copy()
+            if len(constraint_list):
+                rast_values = self.raster.get_values(band=1, window=win)
+                xy = self.raster.get_xy(win)
+                for constraint in constraint_list:
+                    hfun_values = constraint.apply(
+                        rast_values, hfun_values, locations=xy, crs=None)
+            new[sl] = apply_constraints_clamp(hfun_values, self.hmin,
                                               self.hmax)
         self.values = new
+
+    def add_topo_bound_constraint(self, value, upper_bound=np.inf,
+                                  lower_bound=-np.inf, value_type='min',
+                                  rate=0.01):
+        """``hfun/raster.py:571-623``."""
+        if not hasattr(self, "_constraints"):
+            self._constraints = []
+        self._constraints.append(TopoConstConstraint(
+            value, upper_bound, lower_bound, value_type, rate))
+        self._clamp_pass()
+
+    def add_topo_func_constraint(self, func=lambda i: i / 2.0,
+                                 upper_bound=np.inf, lower_bound=-np.inf,
+                                 value_type='min', rate=0.01):
+        """``hfun/raster.py:625-677``."""
+        if not hasattr(self, "_constraints"):
+            self._constraints = []
+        self._constraints.append(TopoFuncConstraint(
+            func, upper_bound, lower_bound, value_type, rate))
+        self._clamp_pass()
+
+    def add_courant_num_constraint(self, upper_bound=0.9, lower_bound=None,
+                                   timestep=150, wave_amplitude=2):
+        """``hfun/raster.py:679-736``."""
+        if upper_bound is None and lower_bound is None:
+            raise ValueError(
+                "Both upper and lower Courant bounds can NOT be None!")
+        if not hasattr(self, "_constraints"):
+            self._constraints = []
+        if upper_bound is not None:
+            self._constraints.append(CourantNumConstraint(
+                upper_bound, timestep, wave_amplitude, 'max'))
+        if lower_bound is not None:
+            self._constraints.append(CourantNumConstraint(
+                lower_bound, timestep, wave_amplitude, 'min'))
+        self._clamp_pass()
+
+    def add_constant_value(self, value, lower_bound=None, upper_bound=None):
+        """``HfunRaster.add_constant_value`` (``hfun/raster.py:1438-1502``)."""
+        new = self.values.copy()
+        for win in self._iter():
+            sl = (slice(win.row_off, win.row_off + win.height),
+                  slice(win.col_off, win.col_off + win.width))
+            rast = self.raster.get_values(band=1, window=win)
+            new[sl] = add_constant_value_window(self.values[sl], rast, value,
+                                                lower_bound, upper_bound)
+        self.values = new
+        self._clamp_pass()
 
     def add_feature_points(self, points, expansion_rate, target_size=None,
                            workers=-1):
@@ -505,6 +566,141 @@ def apply_rate(values, locations, mask, rate, rate_sign, satisfies):
     temp_values_2[mask2] = temp_values[mask2]
     return_values[nomask_r] = temp_values_2
     return return_values.reshape(values.shape)
+
+
+def add_constant_value_window(old: np.ndarray, rast_values: np.ndarray,
+                              value: float, lower_bound=None,
+                              upper_bound=None) -> np.ndarray:
+    """Body of the window loop of ``HfunRaster.add_constant_value``
+    (``ocsmesh/hfun/raster.py:1482-1498``)."""
+    lower_bound = -float('inf') if lower_bound is None else float(lower_bound)
+    upper_bound = float('inf') if upper_bound is None else float(upper_bound)
+    hfun_values = old.copy()
+    hfun_values[np.where(np.logical_and(
+        rast_values > lower_bound,
+        rast_values < upper_bound))] = value
+    return np.minimum(old, hfun_values.astype(np.float32))
+
+
+G_STD = 9.80665  # scipy.constants.g
+
+
+class OracleConstraint:
+    """``Constraint`` (``ocsmesh/features/constraint.py:17-121``)."""
+
+    def __init__(self, value_type: str = 'min', rate=0.1):
+        self._rate = rate
+        vt = value_type.upper()
+        if vt not in ("MIN", "MAX"):
+            raise ValueError("Invalid input for value type!")
+        self._val_type = vt
+
+    @property
+    def satisfies(self):
+        return np.greater if self._val_type == "MIN" else np.less
+
+    @property
+    def rate_sign(self):
+        return -1 if self._val_type == "MIN" else +1
+
+    def _apply_rate(self, ref_values, values, locations, mask):
+        return apply_rate(values, locations, mask, self._rate, self.rate_sign,
+                          self.satisfies)
+
+
+class TopoConstConstraint(OracleConstraint):
+    """``features/constraint.py:135-177``."""
+
+    def __init__(self, value, upper_bound=np.inf, lower_bound=-np.inf,
+                 value_type='min', rate=None):
+        super().__init__(value_type, rate)
+        self._lb, self._ub, self._val = lower_bound, upper_bound, value
+
+    def apply(self, ref_values, old_values, locations=None, crs=None):
+        return_values = old_values.copy()
+        mask = ((ref_values > self._lb) & (ref_values < self._ub) &
+                (np.logical_not(self.satisfies(return_values, self._val))))
+        return_values[mask] = self._val
+        return self._apply_rate(ref_values, return_values, locations, mask)
+
+
+class TopoFuncConstraint(OracleConstraint):
+    """``features/constraint.py:180-224``."""
+
+    def __init__(self, function=lambda i: i / 2.0, upper_bound=np.inf,
+                 lower_bound=-np.inf, value_type='min', rate=None):
+        super().__init__(value_type, rate)
+        self._lb, self._ub = lower_bound, upper_bound
+        self._func = function if callable(function) else (lambda i: i / 2.0)
+
+    def apply(self, ref_values, old_values, locations=None, crs=None):
+        return_values = old_values.copy()
+        temp_values = self._func(ref_values)
+        mask = ((ref_values > self._lb) & (ref_values < self._ub) &
+                (np.logical_not(self.satisfies(return_values, temp_values))))
+        return_values[mask] = temp_values[mask]
+        return self._apply_rate(ref_values, return_values, locations, mask)
+
+
+def _linear_wave_ok(depth, wave_amplitude=2):
+    """``utils.can_velocity_be_approximated_by_linear_wave_theory``
+    (``ocsmesh/utils.py:1707-1741``)."""
+    return depth <= -abs(wave_amplitude)
+
+
+def _particle_velocity(depth, wave_amplitude=2):
+    """``utils.estimate_particle_velocity_from_depth``
+    (``ocsmesh/utils.py:1744-1787``)."""
+    if not isinstance(depth, np.ndarray):
+        depth = np.array(depth)
+    dep_shape = depth.shape
+    depth = depth.ravel()
+    depth_mask = _linear_wave_ok(depth, wave_amplitude)
+    velocity = np.zeros_like(depth)
+    velocity[depth_mask] = wave_amplitude * np.sqrt(
+        G_STD / np.abs(depth[depth_mask]))
+    velocity[~depth_mask] = np.sqrt(G_STD * wave_amplitude)
+    return velocity.reshape(dep_shape)
+
+
+def _courant_for_depth(depth, timestep, element_size, wave_amplitude=2):
+    """``utils.approximate_courant_number_for_depth``
+    (``ocsmesh/utils.py:1790-1835``)."""
+    if np.any(element_size == 0):
+        raise ValueError(
+            "Element size(s) for Courant number approximation include zero!")
+    if depth.shape != element_size.shape:
+        raise ValueError("Shapes of depths and sizes arrays don't match!")
+    depth_mask = _linear_wave_ok(depth, wave_amplitude)
+    particle_velocity = _particle_velocity(depth, wave_amplitude)
+    cvm = particle_velocity + np.sqrt(G_STD * np.abs(depth))
+    cvm[~depth_mask] = 2 * particle_velocity[~depth_mask]
+    return cvm * timestep / element_size
+
+
+class CourantNumConstraint(OracleConstraint):
+    """``features/constraint.py:227-313``."""
+
+    def __init__(self, value, timestep=150, wave_amplitude=2.0,
+                 value_type='max'):
+        super().__init__(value_type, rate=None)
+        self._value, self._dt, self._nu = value, timestep, wave_amplitude
+
+    def apply(self, ref_values, old_values, *args, **kwargs):
+        if ref_values.shape != old_values.shape:
+            raise ValueError("Shapes of depths and sizes arrays don't match")
+        return_values = old_values.copy()
+        u_mag = _particle_velocity(ref_values, self._nu)
+        depth_mask = _linear_wave_ok(ref_values, self._nu)
+        char_vel = u_mag + np.sqrt(G_STD * np.abs(ref_values))
+        char_vel[~depth_mask] = 2 * u_mag[~depth_mask]
+        # utils.get_element_size_courant (ocsmesh/utils.py:1677-1704)
+        temp_values = char_vel * self._dt / self._value
+        old_C_apprx = _courant_for_depth(ref_values, self._dt, old_values,
+                                         self._nu)
+        value_mask = np.logical_not(self.satisfies(old_C_apprx, self._value))
+        return_values[value_mask] = temp_values[value_mask]
+        return return_values
 
 
 # --------------------------------------------------------------------------
