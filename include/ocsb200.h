@@ -114,7 +114,8 @@ int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 #define OCSB_KC_NEAREST          10
 #define OCSB_KC_BUCKET           11
 #define OCSB_KC_CONSTRAINT       12
-#define OCSB_KC_COUNT            13
+#define OCSB_KC_CONTOUR          13
+#define OCSB_KC_COUNT            14
 int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
 int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
                                 int64_t *launches);
@@ -261,6 +262,26 @@ int32_t ocsb_hfun_courant_constraint(ocsb_ctx *ctx, const ocsb_win *win,
                                      float *hfun, int64_t hfun_stride,
                                      double courant, double timestep,
                                      double wave_amplitude, int32_t value_type);
+
+/* ---- 8(f) next-1: contour extraction, the per-pixel half --------------------
+ * Raster.get_contour -> _get_raster_contour_windowed        ocsmesh/raster.py:1340-1372, 1426-1470
+ * (matplotlib/contourpy tracing restated as marching squares: linear
+ * interpolation along cell edges, cell mean decides saddles).  One sweep of
+ * the DEM window classifies every 2x2 cell and compacts its 0/1/2 segments in
+ * cell (row-major) order:
+ *   edges : n x 2 int64, the two GLOBAL EDGE IDS of each segment
+ *           (horizontal (j,i)-(j,i+1): j*(width-1)+i; vertical (j,i)-(j+1,i):
+ *           -(j*width+i)-1) -- segments sharing an id are joined by the caller
+ *   pts   : n x 4 float64 (xa, ya, xb, yb), the crossing points in window
+ *           coordinates (the window's linspace axes, A2)
+ * *n receives the segment count.  edges == NULL (or pts == NULL): count only.
+ * cap < n: OCSB_EOVERFLOW, nothing written.  win->row_begin/row_end select
+ * the cell rows [row_begin, min(row_end, height-1)); the DEM pointer is the
+ * (virtual) address of window row 0 and row min(row_end, height-1) is read.   */
+int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
+                              const void *dem, int32_t dem_dtype,
+                              int64_t dem_stride, double level, int64_t cap,
+                              int64_t *edges, double *pts, int64_t *n);
 
 /* ---- A4 + A6..A10 as ONE streamed pass --------------------------------------
  * The reference applies every add_* to the whole raster before the next one

@@ -20,7 +20,7 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
-KC_COUNT = 13
+KC_COUNT = 14
 VT_MIN, VT_MAX = 0, 1
 NONE = float("nan")
 
@@ -98,6 +98,9 @@ SIGNATURES = {
     "ocsb_hfun_courant_constraint": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp,
                                              c_i32, c_i64, c_vp, c_i64, c_f64,
                                              c_f64, c_f64, c_i32]),
+    "ocsb_contour_segments": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                      c_i64, c_f64, c_i64, c_vp, c_vp,
+                                      C.POINTER(c_i64)]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -315,6 +318,22 @@ class Context:
             self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
             ptr(hfun), int(hfun_stride), float(courant), float(timestep),
             float(wave_amplitude), int(value_type)))
+
+    def contour_segments(self, win, dem, dem_dtype, dem_stride, level):
+        """-> (edges (n, 2) int64, pts (n, 4) float64) host arrays: count pass,
+        then emit pass into exactly sized buffers."""
+        n = c_i64(0)
+        check(self.lib.ocsb_contour_segments(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            float(level), 0, None, None, C.byref(n)))
+        edges = np.empty((n.value, 2), dtype=np.int64)
+        pts = np.empty((n.value, 4), dtype=np.float64)
+        if n.value:
+            check(self.lib.ocsb_contour_segments(
+                self.handle, C.byref(win), ptr(dem), int(dem_dtype),
+                int(dem_stride), float(level), n.value, edges.ctypes.data,
+                pts.ctypes.data, C.byref(n)))
+        return edges, pts
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

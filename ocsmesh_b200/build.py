@@ -30,6 +30,7 @@ SOURCES = [
     "k_feature.cu",
     "k_nearest.cu",
     "k_constraint.cu",
+    "k_contour.cu",
 ]
 
 NVCC_FLAGS = [

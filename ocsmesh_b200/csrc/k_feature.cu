@@ -33,6 +33,7 @@
 #include "ocsb_common.cuh"
 
 #include <limits>
+#include <cstdlib>
 
 namespace {
 
@@ -283,6 +284,97 @@ __global__ void __launch_bounds__(BT) refine_fused_kernel(RefineArgs A) {
     }
 }
 
+// warp-per-tile refinement for the finest levels (short parent lists, very
+// many tiles): a one-warp CTA per tile is capped at 32 resident tiles per SM by
+// the CTA limit, WPB tiles per CTA fill all 64 warp slots.  No block-level
+// synchronisation; survivors are compacted in list order (ballot + popc).
+template <int WPB>
+__global__ void __launch_bounds__(WPB * 32) refine_warp_kernel(RefineArgs A, int ntiles) {
+    __shared__ Dom s_dom[WPB];
+    if (*A.overflow) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int t = blockIdx.x * WPB + wid;
+    if (t >= ntiles) return;
+    int c0, c1, r0, r1;
+    child_px(A, t, &c0, &c1, &r0, &r1);
+    const Rect q = tile_rect(A.g, c0, c1, r0, r1);
+    int off, cnt;
+    const int *ids;
+    parent_list(A, c0, r0, &off, &cnt, &ids);
+    if (cnt == 0) {
+        if (lane == 0) { A.child.off[t] = 0; A.child.cnt[t] = 0; }
+        return;
+    }
+    Best b[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { b[j].d2 = INFINITY; b[j].id = 0x7fffffff; }
+    for (int i = lane; i < cnt; i += 32) {
+        const int id = ids ? ids[off + i] : i;
+        const double2 v = A.verts[id];
+        const CornerD2 c = corner_d2(q, v);
+        best_upd(b[0], center_d2(q, v), id);
+        best_upd(b[1], c.d00, id);
+        best_upd(b[2], c.d01, id);
+        best_upd(b[3], c.d10, id);
+        best_upd(b[4], c.d11, id);
+    }
+    Dom &D = s_dom[wid];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const Best r = best_warp_min(b[j]);
+        if (lane == j) {
+            const CornerD2 c = corner_d2(q, A.verts[r.id]);
+            const double m = 1.0 + kDomEps;
+            D.c[j][0] = c.d00 * m; D.c[j][1] = c.d01 * m;
+            D.c[j][2] = c.d10 * m; D.c[j][3] = c.d11 * m;
+        }
+    }
+    __syncwarp();
+    // keep flags of the first 4 chunks are remembered, longer lists re-test
+    unsigned keepm[4] = {0u, 0u, 0u, 0u};
+    int total = 0;
+    for (int b0 = 0, ch = 0; b0 < cnt; b0 += 32, ++ch) {
+        const int i = b0 + lane;
+        bool k = false;
+        if (i < cnt) {
+            const int id = ids ? ids[off + i] : i;
+            k = keep_vertex(q, D, A.r2lim, A.verts[id]);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, k);
+        if (ch < 4) keepm[ch] = m;
+        total += __popc(m);
+    }
+    unsigned long long base = 0;
+    if (lane == 0) {
+        if (total) {
+            base = atomicAdd(A.pool_ctr, (unsigned long long)total);
+            if (base + total > A.pool_cap) { *A.overflow = 1; total = 0; }
+        }
+        A.child.off[t] = (int)base;
+        A.child.cnt[t] = total;
+    }
+    total = __shfl_sync(0xffffffffu, total, 0);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (total == 0) return;
+    int run = 0;
+    for (int b0 = 0, ch = 0; b0 < cnt; b0 += 32, ++ch) {
+        const int i = b0 + lane;
+        int id = 0;
+        if (i < cnt) id = ids ? ids[off + i] : i;
+        unsigned m;
+        if (ch < 4) {
+            m = keepm[ch];
+        } else {
+            bool k = false;
+            if (i < cnt) k = keep_vertex(q, D, A.r2lim, A.verts[id]);
+            m = __ballot_sync(0xffffffffu, k);
+        }
+        if ((m >> lane) & 1u)
+            A.child.ids[base + run + __popc(m & ((1u << lane) - 1u))] = id;
+        run += __popc(m);
+    }
+}
+
 // ---- split path for levels with few tiles and long parent lists ------------
 struct SplitScratch {
     Best *part;     // [ntiles][nsplit][5]
@@ -430,6 +522,20 @@ void launch_fused(ocsb_ctx *ctx, const RefineArgs &A, int64_t ntiles) {
     OCSB_LAUNCHED(ctx);
 }
 
+void launch_warp(ocsb_ctx *ctx, const RefineArgs &A, int64_t ntiles) {
+    constexpr int WPB = 8;
+    OCSB_TIME(ctx, KC_FEATURE_REFINE);
+    refine_warp_kernel<WPB><<<(unsigned)((ntiles + WPB - 1) / WPB), WPB * 32, 0,
+                              ctx->stream>>>(A, (int)ntiles);
+    OCSB_LAUNCHED(ctx);
+}
+
+// development knobs (tools/sweep_pass.py); defaults are the measured optimum
+int knob(const char *name, int dflt) {
+    const char *e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+
 }  // namespace
 
 int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
@@ -456,10 +562,18 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
     // the coarsest level actually built: the finest one with <= 4 tiles or, if
     // the parent list is the whole vertex set, any level is fine -- keep all
     // levels down from the first with ntiles <= 16 so upper lists stay short
+    // ... but the top level scans the WHOLE vertex set once per tile, and each
+    // further level costs a launch chain: start at the finest level whose
+    // root scan (ntiles x nv vertex tests) stays within a fixed budget
     int top = 0;
     for (int i = 0; i < (int)lv.size(); ++i) {
         top = i;
         if (lv[i].ntiles <= 16) break;
+    }
+    {
+        static const double budget = (double)knob("OCSB_REFINE_BUDGET_M", 4) * 1e6;
+        for (int i = 0; i < top; ++i)
+            if ((double)lv[i].ntiles * (double)nv <= budget) { top = i; break; }
     }
 
     const double inf = std::numeric_limits<double>::infinity();
@@ -517,9 +631,14 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
             // long parent lists on few tiles: split each list over several CTAs
             int nsplit = 1;
             const int64_t want = 2 * (int64_t)ctx->num_sms;
-            if (ntiles < want && (i == top ? nv : 4096) >= 4096) {
+            static const int topsplit = knob("OCSB_REFINE_TOPSPLIT", 0);
+            if ((ntiles < want && (i == top ? nv : 4096) >= 4096) ||
+                (topsplit && i == top && nv >= 8192)) {
                 int64_t est = (i == top) ? nv : nv / 2;   // parent list scale
                 nsplit = (int)((want + ntiles - 1) / ntiles);
+                // a root scan is long whatever the tile count: split it too
+                if (i == top && topsplit && nsplit < (int)((nv + 4095) / 4096))
+                    nsplit = (int)((nv + 4095) / 4096);
                 int64_t maxs = (est + 2047) / 2048;
                 if (nsplit > maxs) nsplit = (int)maxs;
                 if (nsplit > kMaxSplit) nsplit = kMaxSplit;
@@ -545,9 +664,15 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
                 split_p4_kernel<<<gridn, 256, 0, ctx->stream>>>(A, S);
                 OCSB_LAUNCHED(ctx);
             } else if (i == 0) {
-                launch_fused<32>(ctx, A, ntiles);
-            } else if (i == 1) {
-                launch_fused<64>(ctx, A, ntiles);
+                static const int warp0 = knob("OCSB_REFINE_WARP0", 1);
+                if (i == top && nv > 1024) launch_fused<256>(ctx, A, ntiles);
+                else if (warp0) launch_warp(ctx, A, ntiles);
+                else launch_fused<32>(ctx, A, ntiles);
+            } else if (i == 1 && i != top) {
+                static const int bt1 = knob("OCSB_REFINE_BT1", 256);
+                if (bt1 == 64) launch_fused<64>(ctx, A, ntiles);
+                else if (bt1 == 128) launch_fused<128>(ctx, A, ntiles);
+                else launch_fused<256>(ctx, A, ntiles);
             } else {
                 launch_fused<256>(ctx, A, ntiles);
             }

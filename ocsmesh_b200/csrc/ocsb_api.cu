@@ -283,7 +283,7 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
     static const char *names[OCSB_KC_COUNT] = {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
-        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint"};
+        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
@@ -735,6 +735,44 @@ extern "C" int32_t ocsb_hfun_courant_constraint(
                        sh.dev_stride, courant, timestep, wave_amplitude,
                        value_type == OCSB_VT_MIN));
     return finish_call(ctx, {&sz, &sh});
+}
+
+// ---------------------------------------------------------------------------
+// next-1: contour segments
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
+                                         const void *dem, int32_t dem_dtype,
+                                         int64_t dem_stride, double level,
+                                         int64_t cap, int64_t *edges,
+                                         double *pts, int64_t *n) {
+    CTX_ENTER("ocsb_contour_segments");
+    OCSB_TRY(check_win(win, "ocsb_contour_segments"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_contour_segments: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(dem && n && dem_stride >= win->width && cap >= 0,
+                 "ocsb_contour_segments: bad buffers");
+    OCSB_REQUIRE(!ocsb_is_none(level), "ocsb_contour_segments: level is NaN");
+    const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_contour_segments", &rb, &re));
+    *n = 0;
+    const int je = re < h - 1 ? re : h - 1;   // cell rows [rb, je)
+    if (w < 2 || je <= rb) return OCSB_OK;
+    const bool emit = edges && pts && cap > 0;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    Staged sz, se, sp;
+    OCSB_TRY(sz.init(ctx, dem, je + 1 - rb, w, dem_stride, es, STAGE_IN, rb));
+    if (emit) {
+        OCSB_TRY(se.init(ctx, edges, 1, cap * 2, cap * 2, 8, STAGE_OUT));
+        OCSB_TRY(sp.init(ctx, pts, 1, cap * 4, cap * 4, 8, STAGE_OUT));
+    }
+    OCSB_TRY(k_contour_segments(ctx, sz.dev, dem_dtype, sz.dev_stride, w, rb, je,
+                                level, ax, ay, emit ? cap : 0,
+                                emit ? (int64_t *)se.dev : nullptr,
+                                emit ? (double *)sp.dev : nullptr, n));
+    return finish_call(ctx, {&sz, &se, &sp});
 }
 
 // ---------------------------------------------------------------------------

@@ -18,7 +18,8 @@ enum {
     KC_FEATURE_EVAL = OCSB_KC_FEATURE_EVAL, KC_INTERP = OCSB_KC_INTERP,
     KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
     KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
-    KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT
+    KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT,
+    KC_CONTOUR = OCSB_KC_CONTOUR
 };
 
 // ---------------------------------------------------------------------------
@@ -260,6 +261,12 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
 int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
                          const double *q, int64_t nq, double r, double *dist,
                          int64_t *idx);
+
+// k_contour.cu
+int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
+                           int64_t zs, int w, int jb, int je, double level,
+                           LinAxis ax, LinAxis ay, int64_t cap, int64_t *edges,
+                           double *pts, int64_t *n_out);
 
 // k_constraint.cu
 int32_t k_constant_value(ocsb_ctx *ctx, int w, int h, const void *dem,

@@ -219,6 +219,31 @@ def marching_squares(x, y, z, level, block_rows: int = 2048) -> List[np.ndarray]
     ids, first_idx = np.unique(all_ids, return_index=True)
     px = np.concatenate(pxl)[first_idx]
     py = np.concatenate(pyl)[first_idx]
+    return _stitch(ea, eb, ids, px, py)
+
+
+def stitch_segments(edges, pts) -> List[np.ndarray]:
+    """Polylines from the output of ``ocsb_contour_segments``: ``edges``
+    ``(n, 2)`` int64 global edge ids, ``pts`` ``(n, 4)`` float64 crossing
+    points ``(xa, ya, xb, yb)``.  Same stitching (and therefore the same
+    polylines, vertex for vertex) as :func:`marching_squares`."""
+    edges = np.asarray(edges, dtype=np.int64).reshape(-1, 2)
+    pts = np.asarray(pts, dtype=np.float64).reshape(-1, 4)
+    if len(edges) == 0:
+        return []
+    ids, first_idx = np.unique(edges.ravel(), return_index=True)
+    xy = pts.reshape(-1, 2)[first_idx]
+    return _stitch(edges[:, 0], edges[:, 1], ids, xy[:, 0], xy[:, 1])
+
+
+def _stitch(ea, eb, ids, px, py) -> List[np.ndarray]:
+    """Join segments (edge-id pairs) that share a cell edge into polylines.
+    The segment list is put into a canonical order first, so the result does
+    not depend on the order the segments were produced in (host blocks by
+    case, device in cell order)."""
+    lo, hi = np.minimum(ea, eb), np.maximum(ea, eb)
+    canon = np.lexsort((hi, lo))
+    ea, eb = lo[canon], hi[canon]
     a = np.searchsorted(ids, ea)
     b = np.searchsorted(ids, eb)
     nn = len(ids)

@@ -448,17 +448,38 @@ class Raster:
         data = self._src.read(band, masked=masked, window=window)
         return x, y, data
 
-    def get_contour(self, level: float, window: Optional[Window] = None
-                    ) -> List[np.ndarray]:
+    def get_contour(self, level: float, window: Optional[Window] = None,
+                    device: Optional[int] = None) -> List[np.ndarray]:
         """Iso-lines of band 1 at ``level`` as a list of ``(n, 2)`` polylines
         (stands in for ``Raster.get_contour`` ``ocsmesh/raster.py:1340-1372``,
         which returns a shapely (Multi)LineString traced by matplotlib).
-        Host-side marching squares: contour tracing is the CPU step *before*
-        the accelerated path."""
+        The sweep over the pixels runs on the device (``ocsb_contour_segments``:
+        cell classification, crossing points, ordered compaction); the host
+        stitches the O(segments) list into polylines."""
+        from . import _lib
         window = self._full(window)
-        return _features.marching_squares(
-            self.get_x(window), self.get_y(window),
-            self.get_values(window=window, band=1), level)
+        ctx = _lib.default_context(device)
+        dev = ctx.device
+        dem = self.device_band(1, dev)
+        origin = self.device_band_origin(1, dev)
+        code = _lib.OCSB_F32 if dem.element_size() == 4 else _lib.OCSB_F64
+        w = self.width
+        rows = dem.shape[0]
+        # the rows of the window held on this device (a band-local raster
+        # contributes the segments of its own cell rows)
+        rb = max(0, origin - window.row_off)
+        re = min(window.height, origin + rows - window.row_off)
+        if re - rb < 2 or window.width < 2:
+            return []
+        # cell row j needs DEM rows j and j + 1: a band that stops short of
+        # the window's last row gives up its last row of cells
+        cw = _lib.make_win(self.get_window_bounds(window), window.width,
+                           window.height, rb,
+                           re - 1 if re < window.height else 0)
+        addr = dem.data_ptr() + ((window.row_off - origin) * w
+                                 + window.col_off) * dem.element_size()
+        edges, pts = ctx.contour_segments(cw, addr, code, w, level)
+        return _features.stitch_segments(edges, pts)
 
     def save(self, path):
         epsg = self.crs.to_epsg() if self.crs is not None else None

@@ -1,0 +1,109 @@
+"""ocsb_contour_segments (marching-squares sweep on the
+device) vs the host sweep of ocsmesh_b200.features / the oracle's independent
+marching squares (restating ocsmesh/raster.py:1426-1470)."""
+import numpy as np
+import pytest
+
+import ocsmesh_b200 as ob
+from oracle import ocsmesh_oracle as O
+from ocsmesh_b200 import _lib, features as F, synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+
+def canon(lines):
+    """Order-free fingerprint of a set of polylines: sorted segment set."""
+    segs = []
+    for ln in lines:
+        a, b = ln[:-1], ln[1:]
+        s = np.concatenate([a, b], axis=1)
+        swap = (s[:, 0] > s[:, 2]) | ((s[:, 0] == s[:, 2]) & (s[:, 1] > s[:, 3]))
+        s[swap] = s[swap][:, [2, 3, 0, 1]]
+        segs.append(s)
+    s = np.concatenate(segs) if segs else np.empty((0, 4))
+    return s[np.lexsort(s.T[::-1])]
+
+
+@pytest.mark.parametrize("shape", [(2, 2), (3, 7), (64, 64), (257, 515), (1000, 33)])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("level", [0.0, -2.5])
+def test_segments_match_host_sweep(ctx, shape, dtype, level):
+    h, w = shape
+    z = S.synth_dem(max(h, 8), max(w, 8), seed=h + w)[:h, :w].astype(dtype)
+    z[0, 0] = level              # a value exactly on the level: not "above"
+    tr = S.dem_transform(h)
+    r = ob.Raster.from_numpy(z, tr, crs=32618)
+    got = r.get_contour(level)
+    ref = F.marching_squares(r.get_x(), r.get_y(), z, level)
+    assert len(got) == len(ref)
+    for p, q in zip(got, ref):
+        np.testing.assert_array_equal(p, q)       # vertex for vertex, bit-exact
+
+
+def test_saddles_and_plateaus(ctx):
+    rng = np.random.default_rng(5)
+    z = rng.integers(-1, 2, size=(120, 150)).astype(np.float32)   # many saddles, ties
+    r = ob.Raster.from_numpy(z, S.dem_transform(120), crs=32618)
+    for level in (0.0, 0.5, -0.5):
+        got = r.get_contour(level)
+        ref = F.marching_squares(r.get_x(), r.get_y(), z, level)
+        assert len(got) == len(ref)
+        for p, q in zip(got, ref):
+            np.testing.assert_array_equal(p, q)
+
+
+def test_against_oracle_marching_squares(ctx):
+    """Independent restatement in oracle/: same segment set (stitch order and
+    ring start points are implementation choices)."""
+    z = S.synth_dem(300, 420, seed=21)
+    r = ob.Raster.from_numpy(z, S.dem_transform(300), crs=32618)
+    got = r.get_contour(0.0)
+    ref = O.marching_squares(r.get_x(), r.get_y(), z, 0.0)
+    a, b = canon(got), canon(ref)
+    assert a.shape == b.shape
+    np.testing.assert_allclose(a, b, rtol=0, atol=1e-9)
+
+
+def test_window_and_band(ctx):
+    z = S.synth_dem(200, 260, seed=8)
+    r = ob.Raster.from_numpy(z, S.dem_transform(200), crs=32618)
+    win = ob.Window(30, 20, 100, 90)
+    got = r.get_contour(0.0, window=win)
+    ref = F.marching_squares(r.get_x(win), r.get_y(win),
+                             z[20:110, 30:130], 0.0)
+    assert len(got) == len(ref)
+    for p, q in zip(got, ref):
+        np.testing.assert_array_equal(p, q)
+    # raw ABI with a row band: the segments of cell rows [40, 120) only
+    import torch
+    zd = torch.from_numpy(z).cuda()
+    full = _lib.make_win(r.get_window_bounds(ob.Window(0, 0, 260, 200)), 260, 200)
+    e_all, p_all = ctx.contour_segments(full, zd, _lib.OCSB_F32, 260, 0.0)
+    band = _lib.make_win(r.get_window_bounds(ob.Window(0, 0, 260, 200)), 260, 200, 40, 120)
+    e_b, p_b = ctx.contour_segments(band, zd, _lib.OCSB_F32, 260, 0.0)
+    # cell row of a segment: from its horizontal / vertical edge ids
+    def cell_row(e):
+        top = np.where(e >= 0, e // 259, (-e - 1) // 260)
+        return top
+    rows = np.minimum(cell_row(e_all[:, 0]), cell_row(e_all[:, 1]))
+    sel = (rows >= 40) & (rows < 120)
+    np.testing.assert_array_equal(e_b, e_all[sel])
+    np.testing.assert_array_equal(p_b, p_all[sel])
+
+
+def test_overflow_and_count_only(ctx):
+    import ctypes as C
+    z = S.synth_dem(64, 64, seed=3)
+    win = _lib.make_win((0.0, 0.0, 640.0, 640.0), 64, 64)
+    n = C.c_int64(0)
+    lib = ctx.lib
+    assert lib.ocsb_contour_segments(ctx.handle, C.byref(win), z.ctypes.data,
+                                     _lib.OCSB_F32, 64, 0.0, 0, None, None,
+                                     C.byref(n)) == 0
+    assert n.value > 1
+    e = np.empty((1, 2), np.int64)
+    p = np.empty((1, 4))
+    rc = lib.ocsb_contour_segments(ctx.handle, C.byref(win), z.ctypes.data,
+                                   _lib.OCSB_F32, 64, 0.0, 1, e.ctypes.data,
+                                   p.ctypes.data, C.byref(n))
+    assert rc != 0 and b"capacity" in lib.ocsb_last_error()

@@ -188,3 +188,27 @@ def test_synthetic_dem_row_blocks_are_consistent():
     np.testing.assert_array_equal(full[120:180], part)
     g0, g1 = np.gradient(full, 10.0, 10.0)
     assert not np.any((g0 == 0) & (g1 == 0))
+
+
+def test_stitch_is_order_independent():
+    """features._stitch canonicalises the segment order: the device emits
+    segments in cell order, the host block sweep by case."""
+    rng = np.random.default_rng(0)
+    z = S.synth_dem(90, 120, seed=12)
+    x = np.linspace(0.0, 1190.0, 120)
+    y = np.linspace(890.0, 0.0, 90)
+    ref = F.marching_squares(x, y, z, 0.0)
+    ea, eb, ids, px, py = F._ms_block(x, y, z, 0.0, 0, 120)
+    lut = {int(i): k for k, i in enumerate(ids)}
+    perm = rng.permutation(len(ea))
+    flip = rng.random(len(ea)) < 0.5
+    a, b = ea[perm], eb[perm]
+    a, b = np.where(flip, b, a), np.where(flip, a, b)
+    edges = np.stack([a, b], axis=1)
+    ka = np.array([lut[int(i)] for i in a])
+    kb = np.array([lut[int(i)] for i in b])
+    pts = np.stack([px[ka], py[ka], px[kb], py[kb]], axis=1)
+    got = F.stitch_segments(edges, pts)
+    assert len(got) == len(ref) > 0
+    for p, q in zip(got, ref):
+        np.testing.assert_array_equal(p, q)
