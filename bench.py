@@ -161,6 +161,21 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def ncu_traffic(kclass, px_per_launch):
+    """DRAM bytes per launch of the dominant kernel from the committed
+    ``ncu --set full`` capture (profiles/traffic.json: dram__bytes_read.sum +
+    dram__bytes_write.sum per pixel of that capture), scaled to this launch's
+    pixel count; None when no capture is committed for the kernel."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                        "traffic.json")
+    try:
+        with open(path) as f:
+            rec = json.load(f).get(kclass)
+        return float(rec["dram_bytes_per_px"]) * px_per_launch if rec else None
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -338,7 +353,8 @@ def run_ours(args, rank, world, local_rank):
         bytes_launch = bpp * size * W * (args.steps / n) if n else 0.0
         ach = bytes_launch / (avg * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak,
-                    "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "unit": "GB/s", "frac": ach / peak,
+                    "traffic": ncu_traffic(dom, size * W * (args.steps / n) if n else 0),
                     "peak_source": peak_src,
                     "algorithmic_bytes_per_px": bpp,
                     "avg_launch_ms": avg,

@@ -319,21 +319,28 @@ class Context:
             ptr(hfun), int(hfun_stride), float(courant), float(timestep),
             float(wave_amplitude), int(value_type)))
 
-    def contour_segments(self, win, dem, dem_dtype, dem_stride, level):
-        """-> (edges (n, 2) int64, pts (n, 4) float64) host arrays: count pass,
-        then emit pass into exactly sized buffers."""
+    def contour_segments(self, win, dem, dem_dtype, dem_stride, level,
+                         cap: Optional[int] = None):
+        """-> (edges (n, 2) int64, pts (n, 4) float64) host arrays.  One sweep
+        when ``cap`` (default: 16 segments per row + column of the window)
+        holds the result; on OCSB_EOVERFLOW the call reports the exact count
+        and is repeated once with buffers of that size."""
+        if cap is None:
+            cap = 16 * (win.width + win.height) + 1024
         n = c_i64(0)
-        check(self.lib.ocsb_contour_segments(
-            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
-            float(level), 0, None, None, C.byref(n)))
-        edges = np.empty((n.value, 2), dtype=np.int64)
-        pts = np.empty((n.value, 4), dtype=np.float64)
-        if n.value:
-            check(self.lib.ocsb_contour_segments(
+        for _ in range(2):
+            edges = np.empty((cap, 2), dtype=np.int64)
+            pts = np.empty((cap, 4), dtype=np.float64)
+            rc = self.lib.ocsb_contour_segments(
                 self.handle, C.byref(win), ptr(dem), int(dem_dtype),
-                int(dem_stride), float(level), n.value, edges.ctypes.data,
-                pts.ctypes.data, C.byref(n)))
-        return edges, pts
+                int(dem_stride), float(level), cap, edges.ctypes.data,
+                pts.ctypes.data, C.byref(n))
+            if rc == OCSB_EOVERFLOW and n.value > cap:
+                cap = n.value
+                continue
+            check(rc)
+            break
+        return edges[:n.value], pts[:n.value]
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

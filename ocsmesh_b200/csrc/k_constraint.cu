@@ -214,12 +214,14 @@ inline int vec_ok(const void *p, int64_t stride, size_t elem) {
 // ---------------------------------------------------------------------------
 namespace {
 
-constexpr int kCompThreads = 1024;   // one pixel per thread, row-major chunks
+constexpr int kCompThreads = 1024;   // one pixel per thread; a CTA = 1024
+                                     // consecutive pixels of ONE row, CTAs in
+                                     // row-major order (so is the output)
 
 __device__ __forceinline__ bool boundary_px(const uint8_t *mask, int w, int h,
-                                            int64_t p) {
+                                            int row, int col) {
+    const int64_t p = (int64_t)row * w + col;
     if (!mask[p]) return false;
-    const int row = (int)(p / w), col = (int)(p - (int64_t)row * w);
     bool nb = false;
     if (col > 0) nb = nb || !mask[p - 1];
     if (col + 1 < w) nb = nb || !mask[p + 1];
@@ -229,22 +231,24 @@ __device__ __forceinline__ bool boundary_px(const uint8_t *mask, int w, int h,
 }
 
 __global__ void __launch_bounds__(kCompThreads)
-boundary_count_kernel(const uint8_t *__restrict__ mask, int w, int h,
+boundary_count_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
                       int *__restrict__ counts) {
-    const int64_t p = (int64_t)blockIdx.x * kCompThreads + threadIdx.x;
-    const bool f = p < (int64_t)w * h && boundary_px(mask, w, h, p);
+    const int row = blockIdx.x / nbx;
+    const int col = (blockIdx.x - row * nbx) * kCompThreads + threadIdx.x;
+    const bool f = col < w && boundary_px(mask, w, h, row, col);
     const int c = __syncthreads_count(f);
     if (threadIdx.x == 0) counts[blockIdx.x] = c;
 }
 
 __global__ void __launch_bounds__(kCompThreads)
-boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h,
+boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
                      const int *__restrict__ offsets, LinAxis ax, LinAxis ay,
                      const float *__restrict__ hfun, int64_t hs,
                      double2 *__restrict__ verts, float *__restrict__ vals) {
     __shared__ int s_warp[kCompThreads / 32];
-    const int64_t p = (int64_t)blockIdx.x * kCompThreads + threadIdx.x;
-    const bool f = p < (int64_t)w * h && boundary_px(mask, w, h, p);
+    const int row = blockIdx.x / nbx;
+    const int col = (blockIdx.x - row * nbx) * kCompThreads + threadIdx.x;
+    const bool f = col < w && boundary_px(mask, w, h, row, col);
     const unsigned b = __ballot_sync(0xffffffffu, f);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (lane == 0) s_warp[wid] = __popc(b);
@@ -262,7 +266,6 @@ boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h,
     if (!f) return;
     const int pos = offsets[blockIdx.x] + (wid ? s_warp[wid - 1] : 0) +
                     __popc(b & ((1u << lane) - 1u));
-    const int row = (int)(p / w), col = (int)(p - (int64_t)row * w);
     verts[pos] = make_double2(lin_at(ax, col), lin_at(ay, row));
     vals[pos] = hfun[(int64_t)row * hs + col];
 }
@@ -353,18 +356,21 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
                         int w, int h, LinAxis ax, LinAxis ay, const float *hfun,
                         int64_t hs, double **verts_out, float **vals_out,
                         int64_t *nv_out) {
-    const int64_t npx = (int64_t)w * h;
-    const int64_t nblk = (npx + kCompThreads - 1) / kCompThreads;
-    int *counts = nullptr;
+    const int nbx = (w + kCompThreads - 1) / kCompThreads;
+    const int64_t nblk = (int64_t)nbx * h;
+    OCSB_REQUIRE(nblk < 2147483647ll, "_apply_rate: window too large");
+    int *counts = nullptr, *sums = nullptr;
     unsigned long long *total = nullptr;
     OCSB_TRY(sg.get(&counts, (size_t)nblk));
+    OCSB_TRY(sg.get(&sums, (size_t)((nblk + 1023) / 1024)));
     OCSB_TRY(sg.get(&total, 1));
     OCSB_TIME(ctx, KC_CONSTRAINT);
-    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(mask, w, h, counts);
+    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(mask, w, h, nbx, counts);
     OCSB_LAUNCHED(ctx);
     OCSB_TIME(ctx, KC_CONSTRAINT);
-    scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(counts, nblk, total);
+    scan_counts(counts, nblk, sums, total, ctx->stream);
     OCSB_LAUNCHED(ctx);
+    ctx->launches += 2;
     OCSB_CHECK_LAUNCH();
     unsigned long long host_total = 0;
     unsigned long long *bounce = ctx->pinned ? (unsigned long long *)ctx->pinned : &host_total;
@@ -384,7 +390,7 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
     OCSB_TRY(sg.get(&vals, (size_t)host_total));
     OCSB_TIME(ctx, KC_CONSTRAINT);
     boundary_emit_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(
-        mask, w, h, counts, ax, ay, hfun, hs, verts, vals);
+        mask, w, h, nbx, counts, ax, ay, hfun, hs, verts, vals);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     *verts_out = reinterpret_cast<double *>(verts);

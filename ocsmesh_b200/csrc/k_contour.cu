@@ -9,6 +9,9 @@
 // coordinates.  Stitching the O(segments) list into polylines stays on the
 // host (ocsmesh_b200/features.py), as does the arc-length resampling.
 //
+// A CTA = 256 threads x 4 consecutive cells of ONE cell row (float4 loads of
+// the two DEM rows), CTAs in row-major order.
+//
 //   corner bits : 1 = (j,i)  2 = (j,i+1)  4 = (j+1,i+1)  8 = (j+1,i), z > level
 //   edge ids    : horizontal (j,i)-(j,i+1) ->  j*(w-1) + i
 //                 vertical   (j,i)-(j+1,i) -> -(j*w + i) - 1
@@ -18,88 +21,121 @@
 
 namespace {
 
-constexpr int kCellThreads = 1024;
+constexpr int kCellsPerThread = 4;
+constexpr int kCellThreads = 256;
+constexpr int kCellsPerCta = kCellsPerThread * kCellThreads;   // 1024 cells of ONE cell row
 
-struct CellSegs {
-    int n;              // 0, 1, 2
-    int e[2][2];        // per segment: two edge slots (0 top, 1 rig, 2 bot, 3 lef)
-};
+enum { TOP = 0, RIG = 1, BOT = 2, LEF = 3 };
 
-template <typename T>
-__device__ __forceinline__ CellSegs classify(const T *__restrict__ dem, int64_t zs,
-                                             int j, int i, double level,
-                                             double z4[4]) {
-    const T *r0 = dem + (int64_t)j * zs + i;
-    const T *r1 = r0 + zs;
-    const double z00 = (double)r0[0], z01 = (double)r0[1];
-    const double z10 = (double)r1[0], z11 = (double)r1[1];
-    z4[0] = z00; z4[1] = z01; z4[2] = z11; z4[3] = z10;
+// segments of one cell, packed: bits 0-1 = count, then (a, b) edge slots of
+// segment 0 in bits 2-3 / 4-5 and of segment 1 in bits 6-7 / 8-9
+__device__ __forceinline__ unsigned pack1(int a, int b) { return 1u | (a << 2) | (b << 4); }
+__device__ __forceinline__ unsigned pack2(int a, int b, int c, int d) {
+    return 2u | (a << 2) | (b << 4) | (c << 6) | (d << 8);
+}
+
+__device__ __forceinline__ unsigned classify(double z00, double z01, double z10,
+                                             double z11, double level) {
     const int code = (z00 > level ? 1 : 0) | (z01 > level ? 2 : 0) |
                      (z11 > level ? 4 : 0) | (z10 > level ? 8 : 0);
-    CellSegs s;
-    s.n = 0;
-    s.e[0][0] = s.e[0][1] = s.e[1][0] = s.e[1][1] = 0;
-    auto seg = [&](int a, int b) { s.e[s.n][0] = a; s.e[s.n][1] = b; ++s.n; };
-    enum { TOP = 0, RIG = 1, BOT = 2, LEF = 3 };
     switch (code) {
-    case 1: case 14: seg(TOP, LEF); break;
-    case 2: case 13: seg(TOP, RIG); break;
-    case 4: case 11: seg(RIG, BOT); break;
-    case 8: case 7:  seg(LEF, BOT); break;
-    case 3: case 12: seg(LEF, RIG); break;
-    case 6: case 9:  seg(TOP, BOT); break;
+    case 1: case 14: return pack1(TOP, LEF);
+    case 2: case 13: return pack1(TOP, RIG);
+    case 4: case 11: return pack1(RIG, BOT);
+    case 8: case 7:  return pack1(LEF, BOT);
+    case 3: case 12: return pack1(LEF, RIG);
+    case 6: case 9:  return pack1(TOP, BOT);
     case 5: case 10: {
         // saddle: the cell mean decides (sum in numpy's left-to-right order)
         const double m = 0.25 * (((z00 + z01) + z10) + z11);
         const bool cen = m > level;
-        if ((code == 5) == cen) { seg(TOP, RIG); seg(LEF, BOT); }
-        else { seg(TOP, LEF); seg(RIG, BOT); }
-        break;
+        return ((code == 5) == cen) ? pack2(TOP, RIG, LEF, BOT)
+                                    : pack2(TOP, LEF, RIG, BOT);
     }
-    default: break;
+    default: return 0u;
     }
-    return s;
+}
+
+// rows j and j + 1, columns i .. i + 4 (the 4 cells of one thread), as f64;
+// columns past the raster are filled with the last valid value (their cells
+// are never classified)
+template <typename T>
+__device__ __forceinline__ void load_rows(const T *__restrict__ dem, int64_t zs,
+                                          int j, int i, int w, bool vec,
+                                          double r0[5], double r1[5]) {
+    const T *p0 = dem + (int64_t)j * zs + i;
+    const T *p1 = p0 + zs;
+    if (vec && i + 4 < w && sizeof(T) == 4) {
+        const float4 a = *reinterpret_cast<const float4 *>(p0);
+        const float4 b = *reinterpret_cast<const float4 *>(p1);
+        r0[0] = a.x; r0[1] = a.y; r0[2] = a.z; r0[3] = a.w; r0[4] = (double)p0[4];
+        r1[0] = b.x; r1[1] = b.y; r1[2] = b.z; r1[3] = b.w; r1[4] = (double)p1[4];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int c = min(i + k, w - 1) - i;
+            r0[k] = (double)p0[c];
+            r1[k] = (double)p1[c];
+        }
+    }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(kCellThreads)
-contour_count_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int je,
-                     double level, int *__restrict__ counts) {
-    const int64_t ncell = (int64_t)(je - jb) * (w - 1);
-    const int64_t c = (int64_t)blockIdx.x * kCellThreads + threadIdx.x;
+contour_count_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
+                     double level, int vec, int *__restrict__ counts) {
+    __shared__ int s_warp[kCellThreads / 32];
+    const int jr = blockIdx.x / nbx;
+    const int j = jb + jr;
+    const int i = (blockIdx.x - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
     int n = 0;
-    if (c < ncell) {
-        const int j = jb + (int)(c / (w - 1)), i = (int)(c % (w - 1));
-        double z4[4];
-        n = classify(dem, zs, j, i, level, z4).n;
+    if (i < w - 1) {
+        double r0[5], r1[5];
+        load_rows(dem, zs, j, i, w, vec != 0, r0, r1);
+#pragma unroll
+        for (int k = 0; k < kCellsPerThread; ++k)
+            if (i + k < w - 1)
+                n += (int)(classify(r0[k], r0[k + 1], r1[k], r1[k + 1], level) & 3u);
     }
-    // block sum of n in {0,1,2}
-    const int n1 = __syncthreads_count(n >= 1);
-    const int n2 = __syncthreads_count(n == 2);
-    if (threadIdx.x == 0) counts[blockIdx.x] = n1 + n2;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < kCellThreads / 32; ++k) t += s_warp[k];
+        counts[blockIdx.x] = t;
+    }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(kCellThreads)
-contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int je,
-                    double level, LinAxis ax, LinAxis ay,
+contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
+                    double level, int vec, LinAxis ax, LinAxis ay,
                     const int *__restrict__ offsets, int64_t *__restrict__ edges,
                     double *__restrict__ pts) {
     __shared__ int s_warp[kCellThreads / 32];
-    const int64_t ncell = (int64_t)(je - jb) * (w - 1);
-    const int64_t c = (int64_t)blockIdx.x * kCellThreads + threadIdx.x;
-    CellSegs s;
-    s.n = 0;
-    double z4[4] = {0, 0, 0, 0};
-    int j = 0, i = 0;
-    if (c < ncell) {
-        j = jb + (int)(c / (w - 1));
-        i = (int)(c % (w - 1));
-        s = classify(dem, zs, j, i, level, z4);
+    const int jr = blockIdx.x / nbx;
+    const int j = jb + jr;
+    const int i = (blockIdx.x - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
+    double r0[5], r1[5];
+    unsigned pk[kCellsPerThread];
+    int n = 0;
+#pragma unroll
+    for (int k = 0; k < kCellsPerThread; ++k) pk[k] = 0u;
+    if (i < w - 1) {
+        load_rows(dem, zs, j, i, w, vec != 0, r0, r1);
+#pragma unroll
+        for (int k = 0; k < kCellsPerThread; ++k)
+            if (i + k < w - 1) {
+                pk[k] = classify(r0[k], r0[k + 1], r1[k], r1[k + 1], level);
+                n += (int)(pk[k] & 3u);
+            }
     }
-    // exclusive scan of s.n within the CTA
+    // exclusive scan of n within the CTA
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    int x = s.n;
+    int x = n;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const int y = __shfl_up_sync(0xffffffffu, x, o);
@@ -107,59 +143,56 @@ contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int je
     }
     if (lane == 31) s_warp[wid] = x;
     __syncthreads();
-    if (wid == 0) {
-        int t = s_warp[lane];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int y = __shfl_up_sync(0xffffffffu, t, o);
-            if (lane >= o) t += y;
-        }
-        s_warp[lane] = t;
-    }
-    __syncthreads();
-    if (s.n == 0) return;
-    int64_t pos = (int64_t)offsets[blockIdx.x] + (wid ? s_warp[wid - 1] : 0) + (x - s.n);
-    const double x0 = lin_at(ax, i), x1 = lin_at(ax, i + 1);
+    int before = x - n;
+    for (int k = 0; k < wid; ++k) before += s_warp[k];
+    if (n == 0) return;
+    int64_t pos = (int64_t)offsets[blockIdx.x] + before;
     const double y0 = lin_at(ay, j), y1 = lin_at(ay, j + 1);
-    // z4 = (j,i), (j,i+1), (j+1,i+1), (j+1,i)
-    auto cross = [&](int slot, int64_t *id, double *px, double *py) {
-        double za, zb;
-        switch (slot) {
-        case 0:  // top: (j,i)-(j,i+1)
-            za = z4[0]; zb = z4[1];
-            *id = (int64_t)j * (w - 1) + i;
-            *px = __dadd_rn(x0, __dmul_rn(__ddiv_rn(level - za, zb - za), x1 - x0));
-            *py = y0;
-            break;
-        case 2:  // bottom: (j+1,i)-(j+1,i+1)
-            za = z4[3]; zb = z4[2];
-            *id = (int64_t)(j + 1) * (w - 1) + i;
-            *px = __dadd_rn(x0, __dmul_rn(__ddiv_rn(level - za, zb - za), x1 - x0));
-            *py = y1;
-            break;
-        case 3:  // left: (j,i)-(j+1,i)
-            za = z4[0]; zb = z4[3];
-            *id = -((int64_t)j * w + i) - 1;
-            *px = x0;
-            *py = __dadd_rn(y0, __dmul_rn(__ddiv_rn(level - za, zb - za), y1 - y0));
-            break;
-        default:  // right: (j,i+1)-(j+1,i+1)
-            za = z4[1]; zb = z4[2];
-            *id = -((int64_t)j * w + i + 1) - 1;
-            *px = x1;
-            *py = __dadd_rn(y0, __dmul_rn(__ddiv_rn(level - za, zb - za), y1 - y0));
-            break;
+#pragma unroll
+    for (int k = 0; k < kCellsPerThread; ++k) {
+        const int ns = (int)(pk[k] & 3u);
+        if (ns == 0) continue;
+        const int ic = i + k;
+        const double x0 = lin_at(ax, ic), x1 = lin_at(ax, ic + 1);
+        const double z00 = r0[k], z01 = r0[k + 1], z10 = r1[k], z11 = r1[k + 1];
+        auto cross = [&](int slot, int64_t *id, double *px, double *py) {
+            double za, zb;
+            switch (slot) {
+            case TOP:  // (j,i)-(j,i+1)
+                za = z00; zb = z01;
+                *id = (int64_t)j * (w - 1) + ic;
+                *px = __dadd_rn(x0, __dmul_rn(__ddiv_rn(level - za, zb - za), x1 - x0));
+                *py = y0;
+                break;
+            case BOT:  // (j+1,i)-(j+1,i+1)
+                za = z10; zb = z11;
+                *id = (int64_t)(j + 1) * (w - 1) + ic;
+                *px = __dadd_rn(x0, __dmul_rn(__ddiv_rn(level - za, zb - za), x1 - x0));
+                *py = y1;
+                break;
+            case LEF:  // (j,i)-(j+1,i)
+                za = z00; zb = z10;
+                *id = -((int64_t)j * w + ic) - 1;
+                *px = x0;
+                *py = __dadd_rn(y0, __dmul_rn(__ddiv_rn(level - za, zb - za), y1 - y0));
+                break;
+            default:   // RIG: (j,i+1)-(j+1,i+1)
+                za = z01; zb = z11;
+                *id = -((int64_t)j * w + ic + 1) - 1;
+                *px = x1;
+                *py = __dadd_rn(y0, __dmul_rn(__ddiv_rn(level - za, zb - za), y1 - y0));
+                break;
+            }
+        };
+        for (int q = 0; q < ns; ++q, ++pos) {
+            int64_t ia, ib;
+            double ax_, ay_, bx_, by_;
+            cross((pk[k] >> (2 + 4 * q)) & 3u, &ia, &ax_, &ay_);
+            cross((pk[k] >> (4 + 4 * q)) & 3u, &ib, &bx_, &by_);
+            reinterpret_cast<longlong2 *>(edges)[pos] = make_longlong2(ia, ib);
+            reinterpret_cast<double2 *>(pts)[2 * pos] = make_double2(ax_, ay_);
+            reinterpret_cast<double2 *>(pts)[2 * pos + 1] = make_double2(bx_, by_);
         }
-    };
-    for (int k = 0; k < s.n; ++k, ++pos) {
-        int64_t ia, ib;
-        double ax_, ay_, bx_, by_;
-        cross(s.e[k][0], &ia, &ax_, &ay_);
-        cross(s.e[k][1], &ib, &bx_, &by_);
-        edges[2 * pos] = ia;
-        edges[2 * pos + 1] = ib;
-        pts[4 * pos + 0] = ax_; pts[4 * pos + 1] = ay_;
-        pts[4 * pos + 2] = bx_; pts[4 * pos + 3] = by_;
     }
 }
 
@@ -172,24 +205,30 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
                            double *pts, int64_t *n_out) {
     *n_out = 0;
     if (je <= jb || w < 2) return OCSB_OK;
-    const int64_t ncell = (int64_t)(je - jb) * (w - 1);
-    const int64_t nblk = (ncell + kCellThreads - 1) / kCellThreads;
+    OCSB_REQUIRE((((uintptr_t)edges | (uintptr_t)pts) & 15) == 0,
+                 "ocsb_contour_segments: edges / pts must be 16-byte aligned");
+    const int nbx = (w - 1 + kCellsPerCta - 1) / kCellsPerCta;
+    const int vec = (((uintptr_t)dem & 15) == 0 && zs % 4 == 0) ? 1 : 0;
+    const int64_t nblk = (int64_t)nbx * (je - jb);
+    OCSB_REQUIRE(nblk < 2147483647ll, "ocsb_contour_segments: window too large");
     ScratchGuard sg(ctx);
-    int *counts = nullptr;
+    int *counts = nullptr, *sums = nullptr;
     unsigned long long *total = nullptr;
     OCSB_TRY(sg.get(&counts, (size_t)nblk));
+    OCSB_TRY(sg.get(&sums, (size_t)((nblk + 1023) / 1024)));
     OCSB_TRY(sg.get(&total, 1));
     OCSB_TIME(ctx, KC_CONTOUR);
     if (dem_dtype == OCSB_F32)
         contour_count_kernel<float><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const float *)dem, zs, w, jb, je, level, counts);
+            (const float *)dem, zs, w, jb, nbx, level, vec, counts);
     else
         contour_count_kernel<double><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const double *)dem, zs, w, jb, je, level, counts);
+            (const double *)dem, zs, w, jb, nbx, level, vec, counts);
     OCSB_LAUNCHED(ctx);
     OCSB_TIME(ctx, KC_CONTOUR);
-    scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(counts, nblk, total);
+    scan_counts(counts, nblk, sums, total, ctx->stream);
     OCSB_LAUNCHED(ctx);
+    ctx->launches += 2;
     OCSB_CHECK_LAUNCH();
     unsigned long long host_total = 0;
     unsigned long long *bounce =
@@ -210,10 +249,10 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
     OCSB_TIME(ctx, KC_CONTOUR);
     if (dem_dtype == OCSB_F32)
         contour_emit_kernel<float><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const float *)dem, zs, w, jb, je, level, ax, ay, counts, edges, pts);
+            (const float *)dem, zs, w, jb, nbx, level, vec, ax, ay, counts, edges, pts);
     else
         contour_emit_kernel<double><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const double *)dem, zs, w, jb, je, level, ax, ay, counts, edges, pts);
+            (const double *)dem, zs, w, jb, nbx, level, vec, ax, ay, counts, edges, pts);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;

@@ -772,6 +772,9 @@ extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
                                 level, ax, ay, emit ? cap : 0,
                                 emit ? (int64_t *)se.dev : nullptr,
                                 emit ? (double *)sp.dev : nullptr, n));
+    // copy back only the segments that exist, not the whole capacity
+    se.width = *n * 2;
+    sp.width = *n * 4;
     return finish_call(ctx, {&sz, &se, &sp});
 }
 

@@ -132,7 +132,10 @@ static inline LinAxis make_axis(double start, double stop, int n) {
 #ifdef __CUDACC__
 __device__ __forceinline__ double lin_at(const LinAxis &a, int k) {
     // separate multiply and add: numpy does y = arange*step; y += start
-    double v = __dadd_rn(__dmul_rn((double)k, a.step), a.start);
+    // (double)k for 0 <= k < 2^32 without the XU-pipe I2F (one issue slot per
+    // 8 cycles on sm_100): 2^52 + k is exact, so is the subtraction
+    const double kd = __dsub_rn(__hiloint2double(0x43300000, k), 4503599627370496.0);
+    double v = __dadd_rn(__dmul_rn(kd, a.step), a.start);
     return (k == a.n - 1 && a.n > 1) ? a.stop : v;
 }
 #endif
