@@ -115,7 +115,8 @@ int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 #define OCSB_KC_BUCKET           11
 #define OCSB_KC_CONSTRAINT       12
 #define OCSB_KC_CONTOUR          13
-#define OCSB_KC_COUNT            14
+#define OCSB_KC_SAMPLE           14
+#define OCSB_KC_COUNT            15
 int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
 int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
                                 int64_t *launches);
@@ -282,6 +283,28 @@ int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
                               const void *dem, int32_t dem_dtype,
                               int64_t dem_stride, double level, int64_t cap,
                               int64_t *edges, double *pts, int64_t *n);
+
+/* ---- 8(f) next-3: sampling side of HfunRaster.msh_t ---------------------------
+ * source points of the background size mesh                 ocsmesh/hfun/raster.py:345-377
+ *   coords = get_xy(window)[::stride, ::stride]  (row-major, (ny*nx, 2) float64)
+ *   values = float64(hfun[::stride, ::stride]), clamped to [hmin, hmax] in f64
+ * with nx = ceil(width/stride), ny = ceil(height/stride).  coords or values
+ * may be NULL.  hmin/hmax: NaN = None.                                         */
+int32_t ocsb_hfun_sample_source(ocsb_ctx *ctx, const ocsb_win *win,
+                                const float *hfun, int64_t hfun_stride,
+                                int32_t stride, double hmin, double hmax,
+                                double *coords_out, double *values_out);
+
+/* utils.interpolate(src, dst, method='nearest')             ocsmesh/utils.py:1122-1140
+ * = scipy griddata nearest = cKDTree(src.coords).query(dst.coords): every
+ * node gets the (clamped, float64) value of its Euclidean-nearest SOURCE point
+ * of ocsb_hfun_sample_source, without materialising the source arrays.
+ * xy: K x 2 float64 (16-byte aligned if on the device), values_out: K float64. */
+int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
+                                 const float *hfun, int64_t hfun_stride,
+                                 int32_t stride, double hmin, double hmax,
+                                 const double *xy, int64_t K,
+                                 double *values_out);
 
 /* ---- A4 + A6..A10 as ONE streamed pass --------------------------------------
  * The reference applies every add_* to the whole raster before the next one

@@ -20,7 +20,7 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
-KC_COUNT = 14
+KC_COUNT = 15
 VT_MIN, VT_MAX = 0, 1
 NONE = float("nan")
 
@@ -101,6 +101,10 @@ SIGNATURES = {
     "ocsb_contour_segments": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_f64, c_i64, c_vp, c_vp,
                                       C.POINTER(c_i64)]),
+    "ocsb_hfun_sample_source": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
+                                        c_i32, c_f64, c_f64, c_vp, c_vp]),
+    "ocsb_hfun_sample_nearest": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
+                                         c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -341,6 +345,18 @@ class Context:
             check(rc)
             break
         return edges[:n.value], pts[:n.value]
+
+    def hfun_sample_source(self, win, hfun, hfun_stride, stride, hmin, hmax,
+                           coords_out, values_out):
+        check(self.lib.ocsb_hfun_sample_source(
+            self.handle, C.byref(win), ptr(hfun), int(hfun_stride), int(stride),
+            opt(hmin), opt(hmax), ptr(coords_out), ptr(values_out)))
+
+    def hfun_sample_nearest(self, win, hfun, hfun_stride, stride, hmin, hmax,
+                            xy, K, values_out):
+        check(self.lib.ocsb_hfun_sample_nearest(
+            self.handle, C.byref(win), ptr(hfun), int(hfun_stride), int(stride),
+            opt(hmin), opt(hmax), ptr(xy), int(K), ptr(values_out)))
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

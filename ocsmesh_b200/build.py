@@ -31,6 +31,7 @@ SOURCES = [
     "k_nearest.cu",
     "k_constraint.cu",
     "k_contour.cu",
+    "k_sample.cu",
 ]
 
 NVCC_FLAGS = [

@@ -283,7 +283,7 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
     static const char *names[OCSB_KC_COUNT] = {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
-        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour"};
+        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour", "sample"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
@@ -776,6 +776,60 @@ extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
     se.width = *n * 2;
     sp.width = *n * 4;
     return finish_call(ctx, {&sz, &se, &sp});
+}
+
+// ---------------------------------------------------------------------------
+// next-3: msh_t sampling side
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_hfun_sample_source(ocsb_ctx *ctx, const ocsb_win *win,
+                                           const float *hfun, int64_t hfun_stride,
+                                           int32_t stride, double hmin, double hmax,
+                                           double *coords_out, double *values_out) {
+    CTX_ENTER("ocsb_hfun_sample_source");
+    OCSB_TRY(check_win(win, "ocsb_hfun_sample_source"));
+    OCSB_REQUIRE(stride >= 1, "ocsb_hfun_sample_source: stride must be >= 1");
+    OCSB_REQUIRE(hfun && hfun_stride >= win->width && (coords_out || values_out),
+                 "ocsb_hfun_sample_source: bad buffers");
+    const int w = win->width, h = win->height;
+    const int64_t nx = (w + stride - 1) / stride, ny = (h + stride - 1) / stride;
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    Staged sh, sc, sv;
+    OCSB_TRY(sh.init(ctx, hfun, h, w, hfun_stride, 4, STAGE_IN));
+    OCSB_TRY(sc.init(ctx, coords_out, 1, nx * ny * 2, nx * ny * 2, 8, STAGE_OUT));
+    OCSB_TRY(sv.init(ctx, values_out, 1, nx * ny, nx * ny, 8, STAGE_OUT));
+    OCSB_REQUIRE(((uintptr_t)sc.dev & 15) == 0,
+                 "ocsb_hfun_sample_source: coords_out must be 16-byte aligned");
+    OCSB_TRY(k_sample_source(ctx, ax, ay, (const float *)sh.dev, sh.dev_stride,
+                             stride, hmin, hmax, (double *)sc.dev, (double *)sv.dev));
+    return finish_call(ctx, {&sh, &sc, &sv});
+}
+
+extern "C" int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
+                                            const float *hfun, int64_t hfun_stride,
+                                            int32_t stride, double hmin, double hmax,
+                                            const double *xy, int64_t K,
+                                            double *values_out) {
+    CTX_ENTER("ocsb_hfun_sample_nearest");
+    OCSB_TRY(check_win(win, "ocsb_hfun_sample_nearest"));
+    OCSB_REQUIRE(stride >= 1, "ocsb_hfun_sample_nearest: stride must be >= 1");
+    OCSB_REQUIRE(K >= 0, "ocsb_hfun_sample_nearest: negative K");
+    if (K == 0) return OCSB_OK;
+    OCSB_REQUIRE(hfun && hfun_stride >= win->width && xy && values_out,
+                 "ocsb_hfun_sample_nearest: bad buffers");
+    const int w = win->width, h = win->height;
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    Staged sh, sx, sv;
+    OCSB_TRY(sh.init(ctx, hfun, h, w, hfun_stride, 4, STAGE_IN));
+    OCSB_TRY(sx.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
+    OCSB_TRY(sv.init(ctx, values_out, 1, K, K, 8, STAGE_OUT));
+    OCSB_REQUIRE(((uintptr_t)sx.dev & 15) == 0,
+                 "ocsb_hfun_sample_nearest: xy must be 16-byte aligned");
+    OCSB_TRY(k_sample_nearest(ctx, ax, ay, (const float *)sh.dev, sh.dev_stride,
+                              stride, hmin, hmax, (const double *)sx.dev, K,
+                              (double *)sv.dev));
+    return finish_call(ctx, {&sh, &sx, &sv});
 }
 
 // ---------------------------------------------------------------------------

@@ -19,7 +19,7 @@ enum {
     KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
     KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
     KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT,
-    KC_CONTOUR = OCSB_KC_CONTOUR
+    KC_CONTOUR = OCSB_KC_CONTOUR, KC_SAMPLE = OCSB_KC_SAMPLE
 };
 
 // ---------------------------------------------------------------------------
@@ -264,6 +264,14 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
 int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
                          const double *q, int64_t nq, double r, double *dist,
                          int64_t *idx);
+
+// k_sample.cu
+int32_t k_sample_nearest(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const float *hfun,
+                         int64_t hs, int step, double hmin, double hmax,
+                         const double *xy, int64_t K, double *out);
+int32_t k_sample_source(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const float *hfun,
+                        int64_t hs, int step, double hmin, double hmax,
+                        double *coords, double *values);
 
 // k_contour.cu
 int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,

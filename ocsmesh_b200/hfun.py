@@ -705,6 +705,62 @@ class HfunRaster:
         band, i.e. ``add_subtidal_flow_limiter(hmin, hmax, None, None)``."""
         self.add_subtidal_flow_limiter(hmin, hmax, None, None)
 
+    # ---- msh_t sampling side (8f next-3) ---------------------------------------
+    def _sample_win(self, window: Optional[Window]):
+        window = Window(0, 0, self.width, self.height) if window is None else window
+        rb, re = self._band
+        if window.row_off < rb or window.row_off + window.height > re:
+            raise ValueError("the window must lie inside the owned row band")
+        cw = _lib.make_win(self._raster.get_window_bounds(window), window.width,
+                           window.height)
+        return window, cw
+
+    def sizing_source(self, window: Optional[Window] = None,
+                      stride: Optional[int] = None):
+        """The point cloud ``msh_t`` hands to the mesh engine for one window
+        (``hfun/raster.py:345-377``, the ``tria=None`` branch): coordinates
+        ``get_xy(window)[::stride, ::stride]`` and float64 sizes clamped to
+        ``[hmin, hmax]``.  Returns ``(coords (n, 2), values (n, 1))`` CUDA
+        tensors; nothing leaves the device."""
+        import torch
+        step = int(stride) if stride is not None else 1
+        window, cw = self._sample_win(window)
+        self._materialize()
+        nx = -(-window.width // step)
+        ny = -(-window.height // step)
+        dev = f"cuda:{self._device}"
+        coords = torch.empty((nx * ny, 2), dtype=torch.float64, device=dev)
+        values = torch.empty((nx * ny, 1), dtype=torch.float64, device=dev)
+        self._ctx().hfun_sample_source(
+            cw, self._hfun_ptr(self._hfun, window), self.width, step,
+            self._hmin, self._hmax, coords, values)
+        return coords, values
+
+    def sample_nearest(self, coords, window: Optional[Window] = None,
+                       stride: Optional[int] = None):
+        """``utils.interpolate(win_sizes, mesh, method='nearest')``
+        (``hfun/raster.py:429-430``, ``utils.py:1122-1140``): the size of the
+        Euclidean-nearest source point of :meth:`sizing_source` for every
+        node of ``coords`` (host array -> host array, CUDA tensor -> CUDA
+        tensor), float64."""
+        import torch
+        step = int(stride) if stride is not None else 1
+        window, cw = self._sample_win(window)
+        self._materialize()
+        on_dev = isinstance(coords, torch.Tensor) and coords.is_cuda
+        if on_dev:
+            xy = coords.to(dtype=torch.float64).contiguous()
+            out = torch.empty(xy.shape[0], dtype=torch.float64, device=xy.device)
+        else:
+            xy = np.ascontiguousarray(np.asarray(coords, dtype=np.float64))
+            out = np.empty(xy.shape[0], dtype=np.float64)
+        if xy.ndim != 2 or xy.shape[1] != 2:
+            raise ValueError("coords must be an (K, 2) array")
+        self._ctx().hfun_sample_nearest(
+            cw, self._hfun_ptr(self._hfun, window), self.width, step,
+            self._hmin, self._hmax, xy, int(xy.shape[0]), out)
+        return out
+
     # ---- A12: pixel-wise min with another, co-registered hfun window ---------
     def min_combine(self, other: "HfunRaster", window: Optional[Window] = None,
                     other_window: Optional[Window] = None) -> None:

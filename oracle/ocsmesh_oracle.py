@@ -46,6 +46,7 @@ __all__ = [
     "OracleHfun", "marching_squares", "get_contour", "nearest_vertex",
     "min_combine", "apply_rate", "add_constant_value_window",
     "TopoConstConstraint", "TopoFuncConstraint", "CourantNumConstraint",
+    "msh_t_source", "interpolate_nearest",
 ]
 
 FLT_MAX = np.finfo(np.float32).max
@@ -701,6 +702,36 @@ class CourantNumConstraint(OracleConstraint):
         value_mask = np.logical_not(self.satisfies(old_C_apprx, self._value))
         return_values[value_mask] = temp_values[value_mask]
         return return_values
+
+
+def msh_t_source(hfun_values: np.ndarray, xy: np.ndarray, height: int,
+                 width: int, hmin=None, hmax=None, stride=None):
+    """Source side of ``HfunRaster.msh_t`` for one window
+    (``ocsmesh/hfun/raster.py:345-377``): ``hfun_values`` is the window of the
+    float32 size raster, ``xy`` its ``get_xy`` array.  Returns
+    ``(rast_coords (n, 2), rast_values (n, 1) float64)``."""
+    step = stride if stride is not None else 1
+    if step > 1:
+        full_xy = xy.reshape(height, width, 2)
+        rast_coords = full_xy[::step, ::step, :].reshape(-1, 2)
+        sub_vals = hfun_values[::step, ::step]
+        rast_values = sub_vals.flatten().reshape(-1, 1).astype(float)
+    else:
+        rast_coords = xy
+        rast_values = np.array(hfun_values.flatten().reshape(-1, 1), dtype=float)
+    if hmin is not None:
+        rast_values[rast_values < hmin] = hmin
+    if hmax is not None:
+        rast_values[rast_values > hmax] = hmax
+    return rast_coords, rast_values
+
+
+def interpolate_nearest(src_coords, src_values, dst_coords):
+    """``utils.interpolate(src, dst, method='nearest')``
+    (``ocsmesh/utils.py:1122-1140``): scipy ``griddata`` nearest."""
+    from scipy.interpolate import griddata
+    return griddata(src_coords, np.asarray(src_values).flatten(), dst_coords,
+                    method='nearest', fill_value=np.nan)
 
 
 # --------------------------------------------------------------------------
