@@ -214,60 +214,98 @@ inline int vec_ok(const void *p, int64_t stride, size_t elem) {
 // ---------------------------------------------------------------------------
 namespace {
 
-constexpr int kCompThreads = 1024;   // one pixel per thread; a CTA = 1024
-                                     // consecutive pixels of ONE row, CTAs in
-                                     // row-major order (so is the output)
+constexpr int kCompThreads = 256;    // x 4 consecutive pixels per thread: a CTA
+constexpr int kCompPx = 1024;        // = 1024 consecutive pixels of ONE row,
+                                     // CTAs in row-major order (so is the output)
 
-__device__ __forceinline__ bool boundary_px(const uint8_t *mask, int w, int h,
-                                            int row, int col) {
-    const int64_t p = (int64_t)row * w + col;
-    if (!mask[p]) return false;
-    bool nb = false;
-    if (col > 0) nb = nb || !mask[p - 1];
-    if (col + 1 < w) nb = nb || !mask[p + 1];
-    if (row > 0) nb = nb || !mask[p - w];
-    if (row + 1 < h) nb = nb || !mask[p + w];
-    return nb;
+// boundary flags (bit k = pixel col + k) of 4 consecutive pixels of one row
+__device__ __forceinline__ unsigned boundary4(const uint8_t *__restrict__ mask, int w,
+                                              int h, int row, int col, bool vec) {
+    const uint8_t *p = mask + (int64_t)row * w + col;
+    unsigned c = 0, up = 0xf, dn = 0xf;      // bit k: pixel is a mask pixel
+    if (vec && col + 4 <= w) {
+        const uchar4 m = *reinterpret_cast<const uchar4 *>(p);
+        c = (m.x ? 1u : 0u) | (m.y ? 2u : 0u) | (m.z ? 4u : 0u) | (m.w ? 8u : 0u);
+        if (!c) return 0u;
+        if (row > 0) {
+            const uchar4 u = *reinterpret_cast<const uchar4 *>(p - w);
+            up = (u.x ? 1u : 0u) | (u.y ? 2u : 0u) | (u.z ? 4u : 0u) | (u.w ? 8u : 0u);
+        }
+        if (row + 1 < h) {
+            const uchar4 d = *reinterpret_cast<const uchar4 *>(p + w);
+            dn = (d.x ? 1u : 0u) | (d.y ? 2u : 0u) | (d.z ? 4u : 0u) | (d.w ? 8u : 0u);
+        }
+    } else {
+        up = dn = 0u;
+        for (int k = 0; k < 4 && col + k < w; ++k) {
+            c |= (p[k] ? 1u : 0u) << k;
+            up |= ((row > 0) ? (p[k - w] ? 1u : 0u) : 1u) << k;
+            dn |= ((row + 1 < h) ? (p[k + w] ? 1u : 0u) : 1u) << k;
+        }
+        if (!c) return 0u;
+    }
+    // horizontal neighbours: out-of-window counts as mask (no query pixel there)
+    const unsigned lf = (col > 0) ? (p[-1] ? 1u : 0u) : 1u;
+    const unsigned rt = (col + 4 < w) ? (p[4] ? 1u : 0u) : 1u;
+    const unsigned left = ((c << 1) | lf) & 0xfu;            // bit k: pixel k-1 is mask
+    unsigned right = (c >> 1) | (rt << 3);                   // bit k: pixel k+1 is mask
+    // pixels past the row end have no right neighbour inside the window
+    for (int k = 0; k < 4; ++k)
+        if (col + k + 1 >= w) right |= 1u << k;
+    return c & ~(left & right & up & dn) & 0xfu;
 }
 
 __global__ void __launch_bounds__(kCompThreads)
 boundary_count_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
-                      int *__restrict__ counts) {
+                      int vec, int *__restrict__ counts) {
+    __shared__ int s_warp[kCompThreads / 32];
     const int row = blockIdx.x / nbx;
-    const int col = (blockIdx.x - row * nbx) * kCompThreads + threadIdx.x;
-    const bool f = col < w && boundary_px(mask, w, h, row, col);
-    const int c = __syncthreads_count(f);
-    if (threadIdx.x == 0) counts[blockIdx.x] = c;
+    const int col = (blockIdx.x - row * nbx) * kCompPx + threadIdx.x * 4;
+    int n = 0;
+    if (col < w) n = __popc(boundary4(mask, w, h, row, col, vec != 0));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < kCompThreads / 32; ++k) t += s_warp[k];
+        counts[blockIdx.x] = t;
+    }
 }
 
 __global__ void __launch_bounds__(kCompThreads)
-boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
+boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx, int vec,
                      const int *__restrict__ offsets, LinAxis ax, LinAxis ay,
                      const float *__restrict__ hfun, int64_t hs,
                      double2 *__restrict__ verts, float *__restrict__ vals) {
     __shared__ int s_warp[kCompThreads / 32];
     const int row = blockIdx.x / nbx;
-    const int col = (blockIdx.x - row * nbx) * kCompThreads + threadIdx.x;
-    const bool f = col < w && boundary_px(mask, w, h, row, col);
-    const unsigned b = __ballot_sync(0xffffffffu, f);
+    const int col = (blockIdx.x - row * nbx) * kCompPx + threadIdx.x * 4;
+    unsigned f = 0;
+    if (col < w) f = boundary4(mask, w, h, row, col, vec != 0);
+    const int n = __popc(f);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) s_warp[wid] = __popc(b);
-    __syncthreads();
-    if (wid == 0) {
-        int t = s_warp[lane];
+    int x = n;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int y = __shfl_up_sync(0xffffffffu, t, o);
-            if (lane >= o) t += y;
-        }
-        s_warp[lane] = t;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
     }
+    if (lane == 31) s_warp[wid] = x;
     __syncthreads();
     if (!f) return;
-    const int pos = offsets[blockIdx.x] + (wid ? s_warp[wid - 1] : 0) +
-                    __popc(b & ((1u << lane) - 1u));
-    verts[pos] = make_double2(lin_at(ax, col), lin_at(ay, row));
-    vals[pos] = hfun[(int64_t)row * hs + col];
+    int pos = offsets[blockIdx.x] + (x - n);
+    for (int k = 0; k < wid; ++k) pos += s_warp[k];
+    const double y = lin_at(ay, row);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if ((f >> k) & 1u) {
+            verts[pos] = make_double2(lin_at(ax, col + k), y);
+            vals[pos] = hfun[(int64_t)row * hs + col + k];
+            ++pos;
+        }
 }
 
 }  // namespace
@@ -356,8 +394,9 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
                         int w, int h, LinAxis ax, LinAxis ay, const float *hfun,
                         int64_t hs, double **verts_out, float **vals_out,
                         int64_t *nv_out) {
-    const int nbx = (w + kCompThreads - 1) / kCompThreads;
+    const int nbx = (w + kCompPx - 1) / kCompPx;
     const int64_t nblk = (int64_t)nbx * h;
+    const int vec = (((uintptr_t)mask & 3) == 0 && (w & 3) == 0) ? 1 : 0;
     OCSB_REQUIRE(nblk < 2147483647ll, "_apply_rate: window too large");
     int *counts = nullptr, *sums = nullptr;
     unsigned long long *total = nullptr;
@@ -365,7 +404,7 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
     OCSB_TRY(sg.get(&sums, (size_t)((nblk + 1023) / 1024)));
     OCSB_TRY(sg.get(&total, 1));
     OCSB_TIME(ctx, KC_CONSTRAINT);
-    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(mask, w, h, nbx, counts);
+    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(mask, w, h, nbx, vec, counts);
     OCSB_LAUNCHED(ctx);
     OCSB_TIME(ctx, KC_CONSTRAINT);
     scan_counts(counts, nblk, sums, total, ctx->stream);
@@ -390,7 +429,7 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
     OCSB_TRY(sg.get(&vals, (size_t)host_total));
     OCSB_TIME(ctx, KC_CONSTRAINT);
     boundary_emit_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(
-        mask, w, h, nbx, counts, ax, ay, hfun, hs, verts, vals);
+        mask, w, h, nbx, vec, counts, ax, ay, hfun, hs, verts, vals);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     *verts_out = reinterpret_cast<double *>(verts);

@@ -19,6 +19,8 @@
 #include "ocsb_common.cuh"
 #include "k_scan.cuh"
 
+#include <algorithm>
+
 namespace {
 
 constexpr int kCellsPerThread = 4;
@@ -34,10 +36,22 @@ __device__ __forceinline__ unsigned pack2(int a, int b, int c, int d) {
     return 2u | (a << 2) | (b << 4) | (c << 6) | (d << 8);
 }
 
-__device__ __forceinline__ unsigned classify(double z00, double z01, double z10,
-                                             double z11, double level) {
-    const int code = (z00 > level ? 1 : 0) | (z01 > level ? 2 : 0) |
-                     (z11 > level ? 4 : 0) | (z10 > level ? 8 : 0);
+// corner code of a cell.  `lt` is the threshold in the DEM dtype: for a
+// float32 DEM the largest float <= level, so that z > lt  <=>  (double)z > level
+// holds exactly and the sweep needs no f32 -> f64 conversions (XU pipe).
+template <typename T>
+__device__ __forceinline__ int cell_code(T z00, T z01, T z10, T z11, T lt) {
+    return (z00 > lt ? 1 : 0) | (z01 > lt ? 2 : 0) | (z11 > lt ? 4 : 0) |
+           (z10 > lt ? 8 : 0);
+}
+
+__device__ __forceinline__ int code_count(int code) {
+    // 0, 15 -> 0; 5, 10 (saddles) -> 2; everything else -> 1
+    return (code == 0 || code == 15) ? 0 : ((code == 5 || code == 10) ? 2 : 1);
+}
+
+__device__ __forceinline__ unsigned classify(int code, double z00, double z01,
+                                             double z10, double z11, double level) {
     switch (code) {
     case 1: case 14: return pack1(TOP, LEF);
     case 2: case 13: return pack1(TOP, RIG);
@@ -62,20 +76,20 @@ __device__ __forceinline__ unsigned classify(double z00, double z01, double z10,
 template <typename T>
 __device__ __forceinline__ void load_rows(const T *__restrict__ dem, int64_t zs,
                                           int j, int i, int w, bool vec,
-                                          double r0[5], double r1[5]) {
+                                          T r0[5], T r1[5]) {
     const T *p0 = dem + (int64_t)j * zs + i;
     const T *p1 = p0 + zs;
     if (vec && i + 4 < w && sizeof(T) == 4) {
         const float4 a = *reinterpret_cast<const float4 *>(p0);
         const float4 b = *reinterpret_cast<const float4 *>(p1);
-        r0[0] = a.x; r0[1] = a.y; r0[2] = a.z; r0[3] = a.w; r0[4] = (double)p0[4];
-        r1[0] = b.x; r1[1] = b.y; r1[2] = b.z; r1[3] = b.w; r1[4] = (double)p1[4];
+        r0[0] = (T)a.x; r0[1] = (T)a.y; r0[2] = (T)a.z; r0[3] = (T)a.w; r0[4] = p0[4];
+        r1[0] = (T)b.x; r1[1] = (T)b.y; r1[2] = (T)b.z; r1[3] = (T)b.w; r1[4] = p1[4];
     } else {
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
             const int c = min(i + k, w - 1) - i;
-            r0[k] = (double)p0[c];
-            r1[k] = (double)p1[c];
+            r0[k] = p0[c];
+            r1[k] = p1[c];
         }
     }
 }
@@ -83,43 +97,56 @@ __device__ __forceinline__ void load_rows(const T *__restrict__ dem, int64_t zs,
 template <typename T>
 __global__ void __launch_bounds__(kCellThreads)
 contour_count_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
-                     double level, int vec, int *__restrict__ counts) {
-    __shared__ int s_warp[kCellThreads / 32];
-    const int jr = blockIdx.x / nbx;
-    const int j = jb + jr;
-    const int i = (blockIdx.x - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
-    int n = 0;
-    if (i < w - 1) {
-        double r0[5], r1[5];
-        load_rows(dem, zs, j, i, w, vec != 0, r0, r1);
+                     int nblk, T lt, int vec, int *__restrict__ counts) {
+    __shared__ int s_warp[2][kCellThreads / 32];
+    int buf = 0;
+    // persistent CTAs: chunk b = 1024 cells of one cell row, row-major
+    for (int b = blockIdx.x; b < nblk; b += gridDim.x, buf ^= 1) {
+        const int jr = b / nbx;
+        const int j = jb + jr;
+        const int i = (b - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
+        int n = 0;
+        if (i < w - 1) {
+            T r0[5], r1[5];
+            load_rows(dem, zs, j, i, w, vec != 0, r0, r1);
 #pragma unroll
-        for (int k = 0; k < kCellsPerThread; ++k)
-            if (i + k < w - 1)
-                n += (int)(classify(r0[k], r0[k + 1], r1[k], r1[k + 1], level) & 3u);
-    }
+            for (int k = 0; k < kCellsPerThread; ++k)
+                if (i + k < w - 1)
+                    n += code_count(cell_code(r0[k], r0[k + 1], r1[k], r1[k + 1], lt));
+        }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = n;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int t = 0;
+        for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+        if ((threadIdx.x & 31) == 0) s_warp[buf][threadIdx.x >> 5] = n;
+        __syncthreads();   // double-buffered: one barrier per chunk is enough
+        if (threadIdx.x == 0) {
+            int t = 0;
 #pragma unroll
-        for (int k = 0; k < kCellThreads / 32; ++k) t += s_warp[k];
-        counts[blockIdx.x] = t;
+            for (int k = 0; k < kCellThreads / 32; ++k) t += s_warp[buf][k];
+            counts[b] = t;
+        }
     }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(kCellThreads)
 contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
-                    double level, int vec, LinAxis ax, LinAxis ay,
-                    const int *__restrict__ offsets, int64_t *__restrict__ edges,
-                    double *__restrict__ pts) {
-    __shared__ int s_warp[kCellThreads / 32];
-    const int jr = blockIdx.x / nbx;
+                    int nblk, double level, T lt, int vec, LinAxis ax, LinAxis ay,
+                    const int *__restrict__ offsets,
+                    const unsigned long long *__restrict__ total,
+                    int64_t *__restrict__ edges, double *__restrict__ pts) {
+    __shared__ int s_warp[2][kCellThreads / 32];
+    int buf = 0;
+    const int ntot = (int)*total;
+    for (int b = blockIdx.x; b < nblk; b += gridDim.x) {
+    // the count pass already knows which chunks hold segments: the others
+    // (the vast majority) cost two integer loads
+    const int off_b = offsets[b];
+    if ((b + 1 < nblk ? offsets[b + 1] : ntot) == off_b) continue;
+    buf ^= 1;
+    const int jr = b / nbx;
     const int j = jb + jr;
-    const int i = (blockIdx.x - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
-    double r0[5], r1[5];
+    const int i = (b - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
+    T r0[5], r1[5];
     unsigned pk[kCellsPerThread];
     int n = 0;
 #pragma unroll
@@ -129,7 +156,10 @@ contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nb
 #pragma unroll
         for (int k = 0; k < kCellsPerThread; ++k)
             if (i + k < w - 1) {
-                pk[k] = classify(r0[k], r0[k + 1], r1[k], r1[k + 1], level);
+                const int code = cell_code(r0[k], r0[k + 1], r1[k], r1[k + 1], lt);
+                if (code != 0 && code != 15)
+                    pk[k] = classify(code, (double)r0[k], (double)r0[k + 1],
+                                     (double)r1[k], (double)r1[k + 1], level);
                 n += (int)(pk[k] & 3u);
             }
     }
@@ -141,12 +171,12 @@ contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nb
         const int y = __shfl_up_sync(0xffffffffu, x, o);
         if (lane >= o) x += y;
     }
-    if (lane == 31) s_warp[wid] = x;
+    if (lane == 31) s_warp[buf][wid] = x;
     __syncthreads();
     int before = x - n;
-    for (int k = 0; k < wid; ++k) before += s_warp[k];
-    if (n == 0) return;
-    int64_t pos = (int64_t)offsets[blockIdx.x] + before;
+    for (int k = 0; k < wid; ++k) before += s_warp[buf][k];
+    if (n == 0) continue;
+    int64_t pos = (int64_t)off_b + before;
     const double y0 = lin_at(ay, j), y1 = lin_at(ay, j + 1);
 #pragma unroll
     for (int k = 0; k < kCellsPerThread; ++k) {
@@ -154,7 +184,8 @@ contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nb
         if (ns == 0) continue;
         const int ic = i + k;
         const double x0 = lin_at(ax, ic), x1 = lin_at(ax, ic + 1);
-        const double z00 = r0[k], z01 = r0[k + 1], z10 = r1[k], z11 = r1[k + 1];
+        const double z00 = (double)r0[k], z01 = (double)r0[k + 1];
+        const double z10 = (double)r1[k], z11 = (double)r1[k + 1];
         auto cross = [&](int slot, int64_t *id, double *px, double *py) {
             double za, zb;
             switch (slot) {
@@ -194,6 +225,7 @@ contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nb
             reinterpret_cast<double2 *>(pts)[2 * pos + 1] = make_double2(bx_, by_);
         }
     }
+    }
 }
 
 }  // namespace
@@ -211,6 +243,10 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
     const int vec = (((uintptr_t)dem & 15) == 0 && zs % 4 == 0) ? 1 : 0;
     const int64_t nblk = (int64_t)nbx * (je - jb);
     OCSB_REQUIRE(nblk < 2147483647ll, "ocsb_contour_segments: window too large");
+    const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)ctx->num_sms * 8);
+    // largest float <= level: z > ltf  <=>  (double)z > level for every float z
+    float ltf = (float)level;
+    if ((double)ltf > level) ltf = nextafterf(ltf, -INFINITY);
     ScratchGuard sg(ctx);
     int *counts = nullptr, *sums = nullptr;
     unsigned long long *total = nullptr;
@@ -219,11 +255,11 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
     OCSB_TRY(sg.get(&total, 1));
     OCSB_TIME(ctx, KC_CONTOUR);
     if (dem_dtype == OCSB_F32)
-        contour_count_kernel<float><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const float *)dem, zs, w, jb, nbx, level, vec, counts);
+        contour_count_kernel<float><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const float *)dem, zs, w, jb, nbx, (int)nblk, ltf, vec, counts);
     else
-        contour_count_kernel<double><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const double *)dem, zs, w, jb, nbx, level, vec, counts);
+        contour_count_kernel<double><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const double *)dem, zs, w, jb, nbx, (int)nblk, level, vec, counts);
     OCSB_LAUNCHED(ctx);
     OCSB_TIME(ctx, KC_CONTOUR);
     scan_counts(counts, nblk, sums, total, ctx->stream);
@@ -248,11 +284,13 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
     }
     OCSB_TIME(ctx, KC_CONTOUR);
     if (dem_dtype == OCSB_F32)
-        contour_emit_kernel<float><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const float *)dem, zs, w, jb, nbx, level, vec, ax, ay, counts, edges, pts);
+        contour_emit_kernel<float><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const float *)dem, zs, w, jb, nbx, (int)nblk, level, ltf, vec, ax, ay, counts, total,
+            edges, pts);
     else
-        contour_emit_kernel<double><<<(unsigned)nblk, kCellThreads, 0, ctx->stream>>>(
-            (const double *)dem, zs, w, jb, nbx, level, vec, ax, ay, counts, edges, pts);
+        contour_emit_kernel<double><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const double *)dem, zs, w, jb, nbx, (int)nblk, level, level, vec, ax, ay, counts, total,
+            edges, pts);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;

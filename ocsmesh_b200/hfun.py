@@ -91,7 +91,7 @@ class HfunRaster:
                 init = np.asarray(bands[0], dtype=np.float32)
             else:
                 init = np.asarray(initial_value, dtype=np.float32)
-            if init.shape == (raster.height, w):
+            if init.shape == (raster.height, raster.width):
                 init = init[self._band[0]:self._band[1]]
             h, w = self._band[1] - self._band[0], raster.width
             if init.shape != (h, w):

@@ -78,3 +78,15 @@ def test_oracle_matches_reference_source(gold):
                 oh.add_subtidal_flow_limiter(30.0, 900.0, None, None)
                 np.testing.assert_array_equal(
                     oh.values, gold[f"{name}_topo_min_rate_then_limiter"])
+
+
+def test_msh_t_sampling_matches_reference_source(gold):
+    """utils.interpolate(method='nearest') lifted from ocsmesh/utils.py:1122-1140."""
+    col, row, w, h = (int(v) for v in gold["msh_win"])
+    r = O.OracleRaster(gold["dem"], gold["dem_transform"])
+    win = O.Window(col, row, w, h)
+    vals = gold["msh_hfun"][row:row + h, col:col + w]
+    for step in (1, 3):
+        c, v = O.msh_t_source(vals, r.get_xy(win), h, w, 80.0, 900.0, step)
+        got = O.interpolate_nearest(c, v, gold["msh_nodes"])
+        np.testing.assert_array_equal(got, gold[f"msh_nearest_stride{step}"])

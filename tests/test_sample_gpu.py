@@ -71,3 +71,19 @@ def test_device_nodes_and_unclamped(ctx):
     assert got.is_cuda
     ref = O.interpolate_nearest(src_c, src_v, nodes)
     np.testing.assert_array_equal(got.cpu().numpy(), ref)
+
+
+def test_golden_reference_source(ctx):
+    """Against utils.interpolate lifted from the reference
+    (tests/golden/make_golden_constraints.py)."""
+    from test_oracle_constraints import GOLD
+    gold = np.load(GOLD)
+    col, row, w, h = (int(v) for v in gold["msh_win"])
+    r = ob.Raster.from_numpy(gold["dem"], tuple(gold["dem_transform"]), crs=32618)
+    hf = ob.Hfun(r, hmin=80.0, hmax=900.0, initial_value=gold["msh_hfun"])
+    for step in (1, 3):
+        got = hf.sample_nearest(gold["msh_nodes"], ob.Window(col, row, w, h), step)
+        ref = gold[f"msh_nearest_stride{step}"]
+        assert (got != ref).mean() < 1e-3     # exact ties only
+        np.testing.assert_allclose(got, ref, rtol=0, atol=900.0)
+        assert np.count_nonzero(got != ref) <= 2

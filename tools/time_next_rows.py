@@ -108,3 +108,23 @@ report("apply_constraints([TopoConst min 400 in (-10, 0), rate 0.01]) + clamp (+
        ms, kt, 12.0 + 1.0 + 8.0, "feature_eval",
        {"note": "mask (13 B/px incl. u8 mask) + boundary compaction + K1 refine/eval with the "
                 "rate epilogue (8 B/px hfun + 1 B/px mask)"})
+
+# ---- next-3: msh_t sampling side ------------------------------------------------------
+K = 10_000_000
+x0, y0, x1, y1 = r.get_window_bounds(ob.Window(0, 0, n, n))
+rng = np.random.default_rng(4)
+nodes = torch.from_numpy(np.stack([x0 + rng.random(K) * (x1 - x0),
+                                   y0 + rng.random(K) * (y1 - y0)], axis=1)).cuda()
+restore()
+ms, kt = timed(lambda: hf.sample_nearest(nodes, None, None))
+rec = {"op": "sample_nearest(10 M random nodes, stride 1)", "nodes": K, "ms_call": round(ms, 4),
+       "kernel_ms": kt, "algorithmic_bytes_per_node": 28.0,
+       "roofline_frac_kernels": round(28.0 * K / (kt.get("sample", ms) * 1e-3) / 1e9 / peak, 4),
+       "Mnodes_per_s_call": round(K / (ms * 1e-3) / 1e6, 1),
+       "note": "random (unbucketed) nodes: one 32 B sector per 4 B texel"}
+print(json.dumps(rec), flush=True)
+ms, kt = timed(lambda: hf.sizing_source(None, 4))
+rec = {"op": "sizing_source(stride 4): 25 M source points, coords + values", "ms_call": round(ms, 4),
+       "kernel_ms": kt, "bytes_out": 25_000_000 * 24,
+       "GBps_out": round(25_000_000 * 24 / (kt.get("sample", ms) * 1e-3) / 1e9, 1)}
+print(json.dumps(rec), flush=True)
