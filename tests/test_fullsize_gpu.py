@@ -1,0 +1,171 @@
+"""Parity at BASELINE.json's FULL sizes (configs[1]: 20000 x 20000 DEM, contours
+at 3 levels + gradient delimiter; configs[3]: 10 M nodes x 16 DEM tiles), where
+the whole-raster oracle would take minutes: the CUDA results are checked
+bit-exactly against the oracle on SAMPLES of the full-size result (random
+pixels through an exact kd-tree query, row strips through the numpy stencil,
+random nodes through scipy's interpolator) and through size-independent
+properties (idempotence of the min-combine, band independence of the contour
+sweep)."""
+import numpy as np
+import pytest
+from scipy.spatial import cKDTree
+
+import ocsmesh_b200 as ob
+from oracle import ocsmesh_oracle as O
+from ocsmesh_b200 import _lib, features as F, synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+N = 20000
+HMIN, HMAX, RATE, TARGET = 100.0, 1500.0, 0.001, 100.0
+LEVELS = [-5.0, 0.0, 5.0]
+
+
+@pytest.fixture(scope="module")
+def big(ctx):
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    if free < 24e9:
+        pytest.skip("needs 24 GB of free device memory")
+    z = np.empty((N, N), np.float32)
+    for s in range(0, N, 2000):
+        z[s:s + 2000] = S.synth_dem(N, N, seed=2, rows=(s, s + 2000))
+    tr = S.dem_transform(N)
+    r = ob.Raster.from_numpy(z, tr, crs=32618)
+    lines = []
+    for lv in LEVELS:
+        lines.extend(r.get_contour(lv))           # device sweep at full size
+    pts = F.feature_points(lines, TARGET)
+    hf = ob.Hfun(r, hmin=HMIN, hmax=HMAX)
+    hf.add_feature_points(pts, RATE, TARGET)
+    feat = hf.device_values.clone()
+    hf.add_gradient_delimiter(hmin=50.0, hmax=1500.0)
+    yield {"z": z, "tr": tr, "r": r, "pts": pts, "hf": hf, "feat": feat,
+           "lines": lines}
+    r.drop_device_cache()
+
+
+def test_feature_pass_exact_on_sampled_pixels(big):
+    """A6/A7 at 400 Mpx: 20000 random pixels + the four corners, distance from
+    an exact kd-tree query, size law and clamps restated from
+    hfun/raster.py:1240-1257 -- bit-exact."""
+    rng = np.random.default_rng(0)
+    rows = np.concatenate([rng.integers(0, N, 20000), [0, 0, N - 1, N - 1]])
+    cols = np.concatenate([rng.integers(0, N, 20000), [0, N - 1, 0, N - 1]])
+    b = O.array_bounds(N, N, big["tr"])                # (x0, y0, x1, y1)
+    x = np.linspace(b[0], b[2], N)                     # Raster.get_x
+    y = np.linspace(b[3], b[1], N)                     # Raster.get_y
+    xy = np.stack([x[cols], y[rows]], axis=1)
+    old = np.full((1, len(rows)), np.finfo(np.float32).max, np.float32)
+    ref = O.add_feature_window(old, big["pts"], xy, 1, len(rows), RATE, TARGET,
+                               HMIN, HMAX)
+    ref = O.apply_constraints_clamp(ref, HMIN, HMAX)[0]
+    got = big["feat"][rows, cols].cpu().numpy()
+    np.testing.assert_array_equal(got, ref)
+    assert np.unique(got).size > 1000                # not a constant raster
+
+
+def test_limiter_exact_on_row_strips(big):
+    """A8/A9 at 400 Mpx: np.gradient is local, so a 3-row strip of the DEM
+    reproduces the middle row of the full-size stencil (and the window border
+    rows with their one-sided differences)."""
+    z, hf = big["z"], big["hf"]
+    final = hf.device_values
+    rng = np.random.default_rng(1)
+    strips = [(0, 3, [0, 1]), (N - 3, N, [1, 2])]
+    strips += [(r - 1, r + 2, [1]) for r in rng.integers(1, N - 1, 12)]
+    for a, b, keep in strips:
+        old = big["feat"][a:b].cpu().numpy()
+        ref = O.flow_limiter_window(z[a:b], old, big["r"].dx, big["r"].dy, 50.0,
+                                    1500.0, None, None, HMIN, HMAX)
+        ref = O.apply_constraints_clamp(np.ma.getdata(ref), HMIN, HMAX)
+        got = final[a:b].cpu().numpy()
+        # rows whose vertical neighbours are inside the strip (or the window
+        # border itself) see the same stencil as the full raster
+        if a == 0:
+            keep_rows = [0, 1]
+        elif b == N:
+            keep_rows = [1, 2]
+        else:
+            keep_rows = keep
+        for k in keep_rows:
+            np.testing.assert_array_equal(got[k], ref[k], err_msg=f"strip {a}:{b} row {k}")
+
+
+def test_min_combine_is_idempotent(big):
+    """Re-applying the same ops must not change a single pixel (min and the
+    clamps are idempotent): checksum of the 1.6 GB raster before / after."""
+    import torch
+    hf = big["hf"]
+    before = hf.device_values.clone()
+    hf.add_feature_points(big["pts"], RATE, TARGET)
+    hf.add_gradient_delimiter(hmin=50.0, hmax=1500.0)
+    assert torch.equal(before, hf.device_values)
+    # and the limiter only ever lowers the feature pass
+    assert bool((before <= big["feat"]).all())
+    assert float(before.min()) >= HMIN and float(before.max()) <= HMAX
+
+
+def test_contour_sweep_band_independent_and_matches_host_strips(big, ctx):
+    """next-1 at 400 Mpx: the segments of a band of cell rows equal the
+    host sweep of the same rows, vertex for vertex; bands partition the
+    full sweep."""
+    r, z = big["r"], big["z"]
+    dem = r.device_band(1, 0)
+    bounds = r.get_window_bounds(ob.Window(0, 0, N, N))
+    full = _lib.make_win(bounds, N, N)
+    e_all, p_all = ctx.contour_segments(full, dem, _lib.OCSB_F32, N, 0.0)
+    assert len(e_all) > 100000
+    x, y = r.get_x(), r.get_y()
+    total = 0
+    for a, b in [(0, 700), (700, 9001), (9001, 19999)]:
+        w = _lib.make_win(bounds, N, N, a, b)
+        e, p = ctx.contour_segments(w, dem, _lib.OCSB_F32, N, 0.0)
+        total += len(e)
+        if b - a > 1000:
+            continue
+        ea, eb, ids, px, py = F._ms_block(x, y, z[a:b + 1], 0.0, a, N)
+        lut = dict(zip(ids.tolist(), range(len(ids))))
+        host = set()
+        for u, v in zip(ea.tolist(), eb.tolist()):
+            host.add((min(u, v), max(u, v)))
+        dev = set((min(u, v), max(u, v)) for u, v in e.tolist())
+        assert dev == host
+        # crossing coordinates, bit-exact
+        k = np.array([lut[i] for i in e[:, 0].tolist()])
+        np.testing.assert_array_equal(p[:, 0], px[k])
+        np.testing.assert_array_equal(p[:, 1], py[k])
+    assert total == len(e_all)
+
+
+def test_interpolate_10m_nodes_16_tiles_sampled(big, ctx):
+    """configs[3] at full size: 10 M nodes, 16 tiles of 5000 x 5000 (views of
+    the big DEM), linear and nearest; 20000 sampled nodes against
+    scipy's RegularGridInterpolator path of the oracle, bit-exact."""
+    z, tr = big["z"], big["tr"]
+    T = 5000
+    rasters, orasters = [], []
+    for ty in range(4):
+        for tx in range(4):
+            sub = z[ty * T:(ty + 1) * T, tx * T:(tx + 1) * T]
+            t = list(tr)
+            t[2] = tr[2] + tr[0] * tx * T
+            t[5] = tr[5] + tr[4] * ty * T
+            rasters.append(ob.Raster.from_numpy(sub, tuple(t), crs=32618))
+            orasters.append(O.OracleRaster(sub, tuple(t)))
+    b = O.array_bounds(N, N, tr)
+    K = 10_000_000
+    rng = np.random.default_rng(7)
+    xy = np.stack([b[0] - 500 + rng.random(K) * (b[2] - b[0] + 1000),
+                   b[1] - 500 + rng.random(K) * (b[3] - b[1] + 1000)], axis=1)
+    sample = rng.choice(K, 20000, replace=False)
+    for method in ("linear", "nearest"):
+        mesh = ob.Mesh(ob.MeshData(xy, values=np.full(K, -7.5)))
+        mesh.interpolate(rasters, method=method)
+        got = np.asarray(mesh.value).reshape(-1)[sample]
+        ref = O.mesh_interpolate(xy[sample], np.full(len(sample), -7.5), orasters,
+                                 method=method).reshape(-1)
+        np.testing.assert_array_equal(got, ref, err_msg=method)
+        assert (got != -7.5).mean() > 0.9
+    for r_ in rasters:
+        r_.drop_device_cache()
