@@ -62,6 +62,9 @@ def parse_args():
     ap.add_argument("--no-interp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--deferred", action="store_true",
+                    help="device-resident leg through the queued op list "
+                         "(ocsb_hfun_pass) instead of the eager add_* calls")
     return ap.parse_args()
 
 
@@ -292,7 +295,7 @@ def run_ours(args, rank, world, local_rank):
     raster = D.band_raster(z_host.numpy(), tr, H, part, rank, crs=32618,
                            device=dev)
     hfun = ob.HfunRaster(raster, hmin=HMIN, hmax=HMAX, device=dev,
-                         row_band=part.band(rank))
+                         row_band=part.band(rank), deferred=args.deferred)
     verts_local = pts_pinned.to(f"cuda:{dev}")
 
     def step():
@@ -303,6 +306,7 @@ def run_ours(args, rank, world, local_rank):
             D.exchange_dem_halo(raster, part, rank, dev)
         hfun.add_feature_points(verts, RATE, TARGET)
         hfun.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+        hfun.flush()
 
     def barrier():
         if world > 1:

@@ -597,10 +597,24 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
         dev[i].ids = nullptr;
     }
 
+    bool hook_done = false;
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (kMaxLevels + 2) * sizeof(*ctrs),
                                   ctx->stream));
+        // fork: the refinement launches below go to a.refine_stream
+        struct StreamSwap {
+            ocsb_ctx *c; cudaStream_t saved; bool on = false;
+            void swap(cudaStream_t s) { saved = c->stream; c->stream = s; on = true; }
+            void restore() { if (on) { c->stream = saved; on = false; } }
+            ~StreamSwap() { restore(); }
+        } sw{ctx, nullptr};
+        const bool fork = a.refine_stream && a.between && !hook_done;
+        if (fork) {
+            OCSB_CUDA(cudaEventRecord(a.ev_fork, ctx->stream));
+            OCSB_CUDA(cudaStreamWaitEvent(a.refine_stream, a.ev_fork, 0));
+            sw.swap(a.refine_stream);
+        }
         std::vector<unsigned long long> cap(top + 1);
         for (int i = 0; i <= top; ++i) {
             unsigned long long c = 4ull * (unsigned long long)nv +
@@ -679,6 +693,14 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
             OCSB_CHECK_LAUNCH();
         }
 
+        if (fork) {
+            // join: other ops of the list first, then wait for the pyramid
+            OCSB_CUDA(cudaEventRecord(a.ev_join, a.refine_stream));
+            sw.restore();
+            hook_done = true;
+            OCSB_TRY((*a.between)());
+            OCSB_CUDA(cudaStreamWaitEvent(ctx->stream, a.ev_join, 0));
+        }
         EvalArgs E;
         E.g = g;
         E.lvl = dev[0];

@@ -1058,8 +1058,45 @@ int32_t pass_ops(ocsb_ctx *ctx, const ocsb_win *win, int a, int b,
                  int *flags /* device, n_ops ints; nullptr = synchronous */) {
     const float *oldp = in;
     int64_t olds = in_stride;
+    // Resident lists that start with a feature op: every op is a monotone
+    // clamp of min(old, f(pixel)), so with one fuse_clamp setting the order of
+    // the ops does not change a single bit.  The vertex-independent ops
+    // (limiters) CAN then run first, on the context's stream, while the first
+    // feature op's candidate pyramid is refined on a second stream.
+    int n_other = 0;
+    bool same_fuse = true;
+    for (int i = 0; i < n_ops; ++i) {
+        if (ops[i].kind != OCSB_OP_FEATURE) ++n_other;
+        same_fuse = same_fuse && ops[i].fuse_clamp == ops[0].fuse_clamp;
+    }
+    // Measured on B200 (profiles/r1f_overlap.txt): NOT a win -- the limiter
+    // already fills the machine, so the refinement kernels are starved (0.27 ->
+    // 1.07 ms) and the feature op loses its "pre-op raster = initial state"
+    // shortcut (evaluation 0.94 -> 1.21 ms): 2.19 -> 2.37 ms per 400 Mpx.  Off
+    // unless OCSB_PASS_OVERLAP=1.
+    const char *ov = getenv("OCSB_PASS_OVERLAP");
+    const bool overlap_on = ov && atoi(ov) != 0;
+    const bool overlap = overlap_on && flags == nullptr && n_ops >= 2 &&
+                         ops[0].kind == OCSB_OP_FEATURE && n_other > 0 &&
+                         same_fuse && pass_streams(ctx) == OCSB_OK;
+    auto run_limiter = [&](const ocsb_hfun_op &op) -> int32_t {
+        LimiterArgs la{dx, dy, op.hmin, op.hmax, op.lower_bound,
+                       op.upper_bound, ghmin, ghmax, op.fuse_clamp};
+        OCSB_TRY(k_flow_limiter(ctx, win->width, win->height, a, b, dem,
+                                dem_dtype, dem_stride, oldp, olds, out,
+                                out_stride, la));
+        oldp = out;
+        olds = out_stride;
+        return OCSB_OK;
+    };
+    std::function<int32_t()> between = [&]() -> int32_t {
+        for (int k = 0; k < n_ops; ++k)
+            if (ops[k].kind != OCSB_OP_FEATURE) OCSB_TRY(run_limiter(ops[k]));
+        return OCSB_OK;
+    };
     for (int i = 0; i < n_ops; ++i) {
         const ocsb_hfun_op &op = ops[i];
+        if (overlap && op.kind != OCSB_OP_FEATURE) continue;   // ran in `between`
         if (op.kind == OCSB_OP_FEATURE) {
             FeatureArgs fa;
             win_axes(win, &fa.ax, &fa.ay);
@@ -1076,14 +1113,22 @@ int32_t pass_ops(ocsb_ctx *ctx, const ocsb_win *win, int a, int b,
             fa.row_begin = a;
             fa.row_end = b;
             fa.ext_overflow = flags ? flags + i : nullptr;
+            if (overlap && i == 0) {
+                fa.refine_stream = ctx->s_h2d;
+                fa.ev_fork = ctx->ev_alloc;
+                fa.ev_join = ctx->ev_comp[0];
+                fa.between = &between;
+                // the limiters write `out` first: this op's pre-op raster is `out`
+                OCSB_TRY(k_hfun_feature(ctx, fa, verts[i], op.nv, out, out_stride,
+                                        out, out_stride, nullptr, nullptr));
+                oldp = out;
+                olds = out_stride;
+                continue;
+            }
             OCSB_TRY(k_hfun_feature(ctx, fa, verts[i], op.nv, oldp, olds, out,
                                     out_stride, nullptr, nullptr));
         } else {
-            LimiterArgs la{dx, dy, op.hmin, op.hmax, op.lower_bound,
-                           op.upper_bound, ghmin, ghmax, op.fuse_clamp};
-            OCSB_TRY(k_flow_limiter(ctx, win->width, win->height, a, b, dem,
-                                    dem_dtype, dem_stride, oldp, olds, out,
-                                    out_stride, la));
+            OCSB_TRY(run_limiter(op));
         }
         oldp = out;
         olds = out_stride;

@@ -8,6 +8,7 @@
 #include <math.h>
 #include <vector>
 #include <string>
+#include <functional>
 
 #include "ocsb200.h"
 
@@ -252,6 +253,13 @@ struct FeatureArgs {
     // Constraint._apply_rate epilogue instead of the size law (exact path):
     //   t = vals[idx] * (1 + d*rate*sign); new = satisfies(old, t) ? old : t
     // for pixels outside `rate_mask` (features/constraint.py:104-117).
+    // Overlap hook (resident op lists, ocsb_hfun_pass): the candidate-pyramid
+    // refinement runs on `refine_stream` while `*between` (the caller's other,
+    // vertex-independent ops of the list) is enqueued on the context's stream;
+    // the evaluation kernel joins both.  Called exactly once.
+    cudaStream_t refine_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    std::function<int32_t()> *between = nullptr;
     const float *rate_vals = nullptr;    // per-vertex values, nv floats
     const uint8_t *rate_mask = nullptr;  // window row 0, stride = width
     double rate = 0.0, rate_sign = 0.0;

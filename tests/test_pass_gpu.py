@@ -159,3 +159,44 @@ def test_deferred_hfun_equals_eager(chunk):
     he.add_gradient_delimiter(hmin=80, hmax=900)
     np.testing.assert_array_equal(hd.get_values(), he.get_values())
     np.testing.assert_array_equal(hd.device_values.cpu().numpy(), he.get_values())
+
+
+@pytest.mark.parametrize("ops_order", ["FL", "FLL", "FFL", "LF", "FLF"])
+@pytest.mark.parametrize("pristine", [True, False])
+def test_resident_pass_overlap_equals_eager(ops_order, pristine, monkeypatch):
+    """Resident op lists that start with a feature op run the limiters first
+    (on the context's stream) while the candidate pyramid is refined on a
+    second stream: bit-identical to the eager, in-order calls."""
+    monkeypatch.setenv("OCSB_PASS_OVERLAP", "1")      # opt-in knob, read per call
+    h, w = 700, 900
+    z = S.synth_dem(h, w, seed=14)
+    tr = S.dem_transform(h)
+    pa = F.feature_points(S.synth_shoreline(h, w, seed=14, n_lines=2), 100.0)
+    pb = F.feature_points(S.synth_shoreline(h, w, seed=15, n_lines=1), 60.0)
+
+    def build(deferred):
+        r = ob.Raster.from_numpy(z, tr, crs=32618)
+        r.device_band(1, 0)                        # resident DEM
+        hf = ob.HfunRaster(r, hmin=60, hmax=1500, deferred=False)
+        if not pristine:
+            hf.add_constant_value(900.0, -2.0, 2.0)
+            hf.device_values                       # materialised
+        hf._deferred = deferred
+        nf = nl = 0
+        for o in ops_order:
+            if o == "F":
+                hf.add_feature_points(pa if nf == 0 else pb, 0.002, 100.0 if nf == 0 else 60.0)
+                nf += 1
+            else:
+                if nl == 0:
+                    hf.add_gradient_delimiter(hmin=80, hmax=1200)
+                else:
+                    hf.add_subtidal_flow_limiter(hmin=70, hmax=1000, lower_bound=-20,
+                                                 upper_bound=1)
+                nl += 1
+        hf.flush()
+        return hf.device_values.cpu().numpy()
+
+    got = build(True)
+    monkeypatch.setenv("OCSB_PASS_OVERLAP", "0")
+    np.testing.assert_array_equal(got, build(False))
