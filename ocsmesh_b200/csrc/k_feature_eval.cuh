@@ -127,7 +127,7 @@ __device__ __forceinline__ float size_law_f32(double d2, const EvalArgs &A) {
 }
 
 template <bool WANT_OUT, bool HAS_OLD>
-__global__ void __launch_bounds__(kEvalThreads, 3) eval_kernel(EvalArgs A) {
+__global__ void __launch_bounds__(kEvalThreads, WANT_OUT ? 3 : 4) eval_kernel(EvalArgs A) {
     __shared__ double2 s_v[kCandCap];
     __shared__ int s_id[kCandCap];
     __shared__ WarpScratch s_w[kEvalThreads / 32];
