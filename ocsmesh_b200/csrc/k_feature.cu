@@ -33,6 +33,7 @@
 #include "ocsb_common.cuh"
 
 #include <limits>
+#include <algorithm>
 #include <cstdlib>
 
 namespace {
@@ -657,6 +658,20 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
                 if (nsplit > maxs) nsplit = (int)maxs;
                 if (nsplit > kMaxSplit) nsplit = kMaxSplit;
                 if (nsplit < 1) nsplit = 1;
+            }
+            // dense vertex sets (configs[4]: 5 M vertices): the parent lists of
+            // the upper levels hold ~ nv x (parent tile area / raster area)
+            // entries whatever the tile count; one CTA per 8 k expected
+            // entries keeps every scan short (empty splits exit at once)
+            if (nv >= 262144) {
+                double frac = 1.0;
+                if (i != top)
+                    frac = 4.0 * ((double)lv[i + 1].tw * (double)lv[i + 1].th) /
+                           ((double)w * (double)h);
+                if (frac > 1.0) frac = 1.0;
+                const double est_len = frac * (double)nv;
+                int by_len = (int)std::min<double>((double)kMaxSplit, est_len / 8192.0);
+                if (est_len >= 65536.0 && by_len > nsplit) nsplit = by_len;
             }
             if (nsplit > 1) {
                 SplitScratch S;
