@@ -210,6 +210,20 @@ int32_t ocsb_hfun_flow_limiter(ocsb_ctx *ctx, const ocsb_win *win,
                                double ghmin, double ghmax,
                                int32_t fuse_clamp);
 
+/* Host half of the contour path: join the segments of ocsb_contour_segments
+ * that share an edge id into polylines (what matplotlib's path walk +
+ * shapely.ops.linemerge do in the reference, ocsmesh/raster.py:1426-1470,
+ * 1340-1372).  Pure host code, no ctx.  Open lines come first (walked from
+ * their lower edge id end), then closed rings (first vertex repeated at the
+ * end); lines are ordered by their start node.
+ *   xy_out      : cap_xy x 2 float64, the polylines' vertices back to back
+ *   offsets_out : cap_lines + 1 int64, line k = xy_out[offsets[k] : offsets[k+1]]
+ * cap_xy = 2 n and cap_lines = n always suffice.                               */
+int32_t ocsb_stitch_segments(const int64_t *edges, const double *pts, int64_t n,
+                             double *xy_out, int64_t cap_xy,
+                             int64_t *offsets_out, int64_t cap_lines,
+                             int64_t *n_xy, int64_t *n_lines);
+
 /* ---- 8(f) next-2: add_constant_value ----------------------------------------
  * Body of the window loop of HfunRaster.add_constant_value  ocsmesh/hfun/raster.py:1489-1498
  *   v = old; v[(dem > lower_bound) & (dem < upper_bound)] = value; new = min(old, v)

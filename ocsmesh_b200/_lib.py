@@ -105,6 +105,8 @@ SIGNATURES = {
                                         c_i32, c_f64, c_f64, c_vp, c_vp]),
     "ocsb_hfun_sample_nearest": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
                                          c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
+    "ocsb_stitch_segments": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64,
+                                     C.POINTER(c_i64), C.POINTER(c_i64)]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -181,6 +183,23 @@ def windows(width: int, height: int, chunk_size: int, overlap: int) -> np.ndarra
     check(lib.ocsb_windows(width, height, chunk_size, overlap, out.ctypes.data,
                            n.value, C.byref(n)))
     return out
+
+
+def stitch_segments(edges: np.ndarray, pts: np.ndarray):
+    """ocsb_stitch_segments (host code of the library) -> list of (k, 2)
+    float64 polylines."""
+    edges = np.ascontiguousarray(edges, dtype=np.int64).reshape(-1, 2)
+    pts = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 4)
+    n = len(edges)
+    if n == 0:
+        return []
+    xy = np.empty((2 * n, 2), dtype=np.float64)
+    off = np.empty(n + 1, dtype=np.int64)
+    nxy, nl = c_i64(0), c_i64(0)
+    check(load().ocsb_stitch_segments(edges.ctypes.data, pts.ctypes.data, n,
+                                      xy.ctypes.data, 2 * n, off.ctypes.data, n,
+                                      C.byref(nxy), C.byref(nl)))
+    return [xy[off[k]:off[k + 1]].copy() for k in range(nl.value)]
 
 
 class Context:

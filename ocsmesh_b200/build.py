@@ -32,6 +32,7 @@ SOURCES = [
     "k_constraint.cu",
     "k_contour.cu",
     "k_sample.cu",
+    "h_stitch.cu",
 ]
 
 NVCC_FLAGS = [

@@ -208,7 +208,9 @@ def test_stitch_is_order_independent():
     ka = np.array([lut[int(i)] for i in a])
     kb = np.array([lut[int(i)] for i in b])
     pts = np.stack([px[ka], py[ka], px[kb], py[kb]], axis=1)
-    got = F.stitch_segments(edges, pts)
-    assert len(got) == len(ref) > 0
-    for p, q in zip(got, ref):
-        np.testing.assert_array_equal(p, q)
+    for native in (False, True):     # numpy walk and the library's host code
+        got = F.stitch_segments(edges, pts, native=native)
+        assert len(got) == len(ref) > 0
+        for p, q in zip(got, ref):
+            np.testing.assert_array_equal(p, q)
+    assert F.stitch_segments(np.empty((0, 2), np.int64), np.empty((0, 4))) == []
