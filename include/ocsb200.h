@@ -224,6 +224,20 @@ int32_t ocsb_stitch_segments(const int64_t *edges, const double *pts, int64_t n,
                              int64_t *offsets_out, int64_t cap_lines,
                              int64_t *n_xy, int64_t *n_lines);
 
+/* Feature prologue of add_feature (host code): repartition every polyline into
+ * chunks of at most max_verts vertices that share their end vertex
+ * (utils.repartition_features, ocsmesh/utils.py:247-277) and place a point every
+ * target_size metres along each chunk, plus both chunk ends
+ * (utils.transform_linestring, ocsmesh/utils.py:280-312): the `points` array of
+ * ocsmesh/hfun/raster.py:1219-1230.
+ *   xy, offsets : n_lines polylines, line k = xy[offsets[k] : offsets[k+1]] (x, y)
+ *   out         : cap x 2 float64 or NULL (count only); *n_out = number of points;
+ *                 cap < *n_out: OCSB_EOVERFLOW, nothing usable written          */
+int32_t ocsb_feature_points(const double *xy, const int64_t *offsets,
+                            int64_t n_lines, double target_size,
+                            int32_t max_verts, double *out, int64_t cap,
+                            int64_t *n_out);
+
 /* ---- 8(f) next-2: add_constant_value ----------------------------------------
  * Body of the window loop of HfunRaster.add_constant_value  ocsmesh/hfun/raster.py:1489-1498
  *   v = old; v[(dem > lower_bound) & (dem < upper_bound)] = value; new = min(old, v)

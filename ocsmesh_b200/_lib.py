@@ -107,6 +107,8 @@ SIGNATURES = {
                                          c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
     "ocsb_stitch_segments": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64,
                                      C.POINTER(c_i64), C.POINTER(c_i64)]),
+    "ocsb_feature_points": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i64,
+                                    C.POINTER(c_i64)]),
     "ocsb_min_combine": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_i32]),
     "ocsb_interp": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                             c_vp, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp]),
@@ -200,6 +202,28 @@ def stitch_segments(edges: np.ndarray, pts: np.ndarray):
                                       xy.ctypes.data, 2 * n, off.ctypes.data, n,
                                       C.byref(nxy), C.byref(nl)))
     return [xy[off[k]:off[k + 1]].copy() for k in range(nl.value)]
+
+
+def feature_points(lines, target_size: float, max_verts: int = 200) -> np.ndarray:
+    """ocsb_feature_points (host code of the library): the (N, 2) vertex array
+    add_feature hands to the nearest-vertex search."""
+    lines = [np.ascontiguousarray(np.asarray(l, dtype=np.float64)).reshape(-1, 2)
+             for l in lines]
+    if not lines:
+        return np.empty((0, 2), dtype=np.float64)
+    off = np.zeros(len(lines) + 1, dtype=np.int64)
+    np.cumsum([len(l) for l in lines], out=off[1:])
+    xy = np.ascontiguousarray(np.concatenate(lines, axis=0))
+    n = c_i64(0)
+    lib = load()
+    check(lib.ocsb_feature_points(xy.ctypes.data, off.ctypes.data, len(lines),
+                                  float(target_size), int(max_verts), None, 0,
+                                  C.byref(n)))
+    out = np.empty((n.value, 2), dtype=np.float64)
+    check(lib.ocsb_feature_points(xy.ctypes.data, off.ctypes.data, len(lines),
+                                  float(target_size), int(max_verts),
+                                  out.ctypes.data, n.value, C.byref(n)))
+    return out
 
 
 class Context:

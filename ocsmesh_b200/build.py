@@ -40,7 +40,7 @@ NVCC_FLAGS = [
     "-lineinfo", "-O3", "-std=c++17",
     # IEEE division / sqrt, no FMA contraction: results must match numpy/scipy
     "-prec-div=true", "-prec-sqrt=true", "-fmad=false",
-    "-Xcompiler", "-fPIC,-O2,-Wall",
+    "-Xcompiler", "-fPIC,-O2,-Wall,-ffp-contract=off",
     "-I", INCLUDE, "-I", CSRC,
 ]
 

@@ -105,10 +105,19 @@ def transform_linestring(linestring: np.ndarray, target_size: float) -> np.ndarr
 
 
 def feature_points(features: Sequence[np.ndarray], target_size: float,
-                   max_verts: int = 200) -> np.ndarray:
+                   max_verts: int = 200, native: bool = True) -> np.ndarray:
     """The ``points`` array handed to the kd-tree at
     ``ocsmesh/hfun/raster.py:1230`` (projected CRS): repartition, resample each
-    chunk, concatenate."""
+    chunk, concatenate.  ``native`` runs the library's host code
+    (``ocsb_feature_points``, h_stitch.cu: bit-identical, ~10x faster); the
+    numpy walk below stays as its cross-check (tests/test_host_cpu.py)."""
+    if native:
+        if not isinstance(max_verts, (int, np.integer)) or isinstance(max_verts, bool):
+            raise ValueError("Maximum number of vertices must be an integer!")
+        if not float(target_size) > 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        from . import _lib
+        return _lib.feature_points(features, float(target_size), int(max_verts))
     parts = []
     for ls in features:
         for chunk in repartition_features(ls, max_verts):

@@ -86,12 +86,37 @@ def test_feature_prologue_matches_reference(gold):
     chunks = F.repartition_features(line, 200)
     np.testing.assert_array_equal([len(c) for c in chunks], gold["pro_chunk_lens"])
     np.testing.assert_array_equal(F.feature_points([line], 100.0, 200), gold["pro_points"])
+    np.testing.assert_array_equal(F.feature_points([line], 100.0, 200, native=False),
+                                  gold["pro_points"])
     np.testing.assert_array_equal(F.transform_linestring(line[:3], 1e6), gold["pro_short"])
     # reference tests/api/test_utils.py:873-916
     res = F.repartition_features(np.array([[i, i] for i in range(100000)], float), 200)
     assert (len(res), len(res[0]), len(res[-1])) == (503, 200, 102)
     with pytest.raises(ValueError, match="must be an integer"):
         F.repartition_features(line, 2.5)
+
+
+def test_native_feature_points_bit_identical_to_numpy_walk():
+    """ocsb_feature_points (host code of the library) against the numpy
+    restatement of utils.py:247-312 on ragged random polylines: single
+    vertices, lines shorter than target_size, chunk cuts at every max_verts."""
+    rng = np.random.default_rng(3)
+    for _ in range(60):
+        lines = []
+        for _ in range(int(rng.integers(1, 6))):
+            m = int(rng.integers(1, 700))
+            step = rng.choice([0.5, 7.0, 40.0, 350.0])
+            lines.append(np.cumsum(rng.normal(0, step, (m, 2)), axis=0)
+                         + [500000.0, 4100000.0])
+        tgt = float(rng.choice([1.0, 33.3, 100.0, 1000.0]))
+        mv = int(rng.choice([2, 3, 50, 200]))
+        np.testing.assert_array_equal(F.feature_points(lines, tgt, mv, native=True),
+                                      F.feature_points(lines, tgt, mv, native=False))
+    assert F.feature_points([], 100.0).shape == (0, 2)
+    with pytest.raises(ValueError, match="must be an integer"):
+        F.feature_points([np.zeros((3, 2))], 100.0, 2.5)
+    with pytest.raises(ValueError, match="greater than zero"):
+        F.feature_points([np.zeros((3, 2))], 0.0)
 
 
 def test_feature_argument_types():
