@@ -174,8 +174,11 @@ def ncu_traffic(kclass, px_per_launch):
     try:
         with open(path) as f:
             rec = json.load(f).get(kclass)
-        return float(rec["dram_bytes_per_px"]) * px_per_launch if rec else None
-    except (OSError, ValueError, KeyError):
+        if not rec:
+            return None
+        per = rec.get("dram_bytes_per_px", rec.get("dram_bytes_per_node"))
+        return float(per) * px_per_launch
+    except (OSError, ValueError, KeyError, TypeError):
         return None
 
 
@@ -529,7 +532,13 @@ def bench_interp(args, rank, world, dev, ctx, peak):
         # one launch serves all tiles: coordinates read once, 4 (1) texels and
         # one value per node
         ach = (bpn * n) / (ms * 1e-3) / 1e9
+        # what the gather really moves (committed ncu capture): a touched DEM
+        # row costs a 64-byte DRAM access whatever part of it is used
+        traffic = ncu_traffic("interp_" + method, n)
         out[method] = {"Mnodes_per_s": K / (ms * 1e-3) / 1e6, "ms_per_step": ms,
+                       "traffic": traffic,
+                       "traffic_frac_of_peak": (traffic / (ms * 1e-3) / 1e9 / peak
+                                                if traffic else None),
                        "e2e_Mnodes_per_s": K / (ems * 1e-3) / 1e6,
                        "roofline_frac": ach / peak,
                        "algorithmic_bytes_per_node": bpn,

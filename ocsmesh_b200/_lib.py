@@ -14,7 +14,8 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libocsb200.so")
+#: OCSB_LIB points the tools/ sweeps at an alternative build of the SAME library
+LIB_PATH = os.environ.get("OCSB_LIB") or os.path.join(_HERE, "libocsb200.so")
 
 OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5

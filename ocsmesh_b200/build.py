@@ -52,9 +52,9 @@ def _nvcc() -> str:
     return exe
 
 
-def _digest(paths) -> str:
+def _digest(paths, extra=()) -> str:
     h = hashlib.sha256()
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(NVCC_FLAGS + list(extra)).encode())
     for p in sorted(paths):
         with open(p, "rb") as f:
             h.update(p.encode())
@@ -68,16 +68,16 @@ def _headers():
     return hs
 
 
-def _compile_one(src: str, verbose: bool) -> str:
+def _compile_one(src: str, verbose: bool, extra=(), objdir: str = OBJDIR) -> str:
     path = os.path.join(CSRC, src)
-    obj = os.path.join(OBJDIR, src.replace(".cu", ".o"))
+    obj = os.path.join(objdir, src.replace(".cu", ".o"))
     stamp = obj + ".sha"
-    dig = _digest([path] + _headers())
+    dig = _digest([path] + _headers(), extra)
     if os.path.exists(obj) and os.path.exists(stamp):
         with open(stamp) as f:
             if f.read().strip() == dig:
                 return obj
-    cmd = [_nvcc()] + NVCC_FLAGS + ["-c", path, "-o", obj]
+    cmd = [_nvcc()] + NVCC_FLAGS + list(extra) + ["-c", path, "-o", obj]
     if verbose:
         print(" ".join(cmd), flush=True)
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -90,8 +90,14 @@ def _compile_one(src: str, verbose: bool) -> str:
     return obj
 
 
-def build(verbose: bool = False, force: bool = False) -> str:
-    """Compile every CUDA source for sm_100a and link libocsb200.so."""
+def build(verbose: bool = False, force: bool = False, extra=(), lib: str = LIB,
+          objdir: str = OBJDIR) -> str:
+    """Compile every CUDA source for sm_100a and link libocsb200.so.
+
+    ``extra`` (more nvcc flags, e.g. ``-DOCSB_INTERP_MIN_CTAS=5``), ``lib`` and
+    ``objdir`` build a tuning variant beside the product library for the
+    tools/ sweeps (loaded through ``OCSB_LIB``)."""
+    LIB, OBJDIR = lib, objdir  # noqa: N806 (shadow the module defaults)
     os.makedirs(OBJDIR, exist_ok=True)
     if force:
         for f in os.listdir(OBJDIR):
@@ -101,7 +107,7 @@ def build(verbose: bool = False, force: bool = False) -> str:
     if missing:
         raise RuntimeError(f"missing CUDA sources: {sorted(missing)}")
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        objs = list(ex.map(lambda s: _compile_one(s, verbose), srcs))
+        objs = list(ex.map(lambda s: _compile_one(s, verbose, extra, OBJDIR), srcs))
     newest = max(os.path.getmtime(o) for o in objs)
     if (not os.path.exists(LIB)) or os.path.getmtime(LIB) < newest or force:
         cmd = [_nvcc(), "-shared", "-o", LIB] + objs + [

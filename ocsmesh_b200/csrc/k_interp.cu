@@ -14,6 +14,17 @@
 // node coordinates are read once and the value written once, instead of once
 // per raster (16 tiles x 10 M nodes: 2.6 GB of coordinate re-reads saved).
 //
+// Raster selection: the host lays a coarse SEL_G x SEL_G grid over the union
+// of the window bounding boxes; each cell holds the bit set of the rasters
+// whose box touches the cell grown by one cell on every side (so the cell
+// lookup may be computed sloppily), and a node tests only those boxes -- in
+// f64, highest index first -- instead of walking the whole list.
+//
+// Index search: the analytic guess floor((v - lo) * (1/|step|)) is checked
+// against the exact linspace values of its two grid lines and walked when it
+// is off (rare); nearest needs no division at all: t <= 0.5 is decided
+// exactly by  v - g[i] <= 0.5 * (g[i+1] - g[i]).
+//
 // Grid convention: scipy always works on ASCENDING grids (descending inputs
 // are flipped together with the values), so for each axis we build the
 // ascending view asc[m] = L[m] (step > 0) or L[n-1-m] (step < 0) of the
@@ -22,9 +33,18 @@
 
 namespace {
 
+#ifndef OCSB_INTERP_MIN_CTAS
+#define OCSB_INTERP_MIN_CTAS 4
+#endif
+constexpr int SEL_G = 64;          // selection grid: SEL_G x SEL_G cells
+constexpr int SEL_MAX_RASTERS = 64;  // one bit per raster
+
 struct AscAxis {
     LinAxis a;
-    int flip;  // 1: ascending index m <-> linspace index n-1-m
+    double lo;   // asc[0]
+    double inv;  // 1 / |step|
+    int flip;    // 1: ascending index m <-> linspace index n-1-m
+    int pad;
 };
 
 struct RasterDev {
@@ -35,6 +55,12 @@ struct RasterDev {
     const uint8_t *mask;
     int64_t ms;
     int dtype;
+    int pad;
+};
+
+struct SelGrid {
+    double x0, y0, inv_x, inv_y;   // cell = (p - origin) * inv
+    const uint64_t *cells;         // SEL_G * SEL_G bit sets, NULL: walk the list
 };
 
 __device__ __forceinline__ double asc_at(const AscAxis &g, int m) {
@@ -45,22 +71,32 @@ __device__ __forceinline__ int asc_to_pix(const AscAxis &g, int m) {
 }
 
 // interval i with asc[i] <= v < asc[i+1], clipped to [0, n-2]
-// (== clip(searchsorted(asc, v, 'right') - 1, 0, n-2)), plus
-// t = (v - asc[i]) / (asc[i+1] - asc[i])
-__device__ __forceinline__ void find_cell(const AscAxis &g, double v, int *i_out,
-                                          double *t_out) {
+// (== clip(searchsorted(asc, v, 'right') - 1, 0, n-2)); *num = v - asc[i],
+// *den = asc[i+1] - asc[i]  (t = num / den)
+__device__ __forceinline__ int find_cell(const AscAxis &g, double v, double *num,
+                                         double *den) {
     const int n = g.a.n;
-    const double lo = asc_at(g, 0);
-    const double astep = fabs(g.a.step);
-    int i = (int)floor((v - lo) / astep);
+    int i = __double2int_rd(__dmul_rn(__dsub_rn(v, g.lo), g.inv));
     i = max(0, min(n - 2, i));
-    // correct the analytic guess against the exact grid values
-    while (i > 0 && v < asc_at(g, i)) --i;
-    while (i < n - 2 && v >= asc_at(g, i + 1)) ++i;
-    const double gi = asc_at(g, i);
-    const double gi1 = asc_at(g, i + 1);
-    *i_out = i;
-    *t_out = __ddiv_rn(__dsub_rn(v, gi), __dsub_rn(gi1, gi));
+    double gi = asc_at(g, i);
+    double gi1 = asc_at(g, i + 1);
+    // the guess is exact except within an ulp or so of a grid line
+    if (v < gi) {
+        while (i > 0 && v < gi) {
+            --i;
+            gi1 = gi;
+            gi = asc_at(g, i);
+        }
+    } else if (v >= gi1) {
+        while (i < n - 2 && v >= gi1) {
+            ++i;
+            gi = gi1;
+            gi1 = asc_at(g, i + 1);
+        }
+    }
+    *num = __dsub_rn(v, gi);
+    *den = __dsub_rn(gi1, gi);
+    return i;
 }
 
 template <typename T>
@@ -71,13 +107,14 @@ __device__ __forceinline__ double texel(const RasterDev &R, int64_t row, int64_t
 // one raster, one node: true (and *out) if this raster sets the node's value
 template <typename T, int METHOD>
 __device__ __forceinline__ bool sample(const RasterDev &R, double2 p, double *out) {
-    int i, j;
-    double tx, ty;
-    find_cell(R.gx, p.x, &i, &tx);
-    find_cell(R.gy, p.y, &j, &ty);
+    double nx, dx, ny, dy;
+    const int i = find_cell(R.gx, p.x, &nx, &dx);
+    const int j = find_cell(R.gy, p.y, &ny, &dy);
     if (METHOD == OCSB_INTERP_NEAREST) {
-        const int ii = (tx <= 0.5) ? i : i + 1;
-        const int jj = (ty <= 0.5) ? j : j + 1;
+        // t = fl(num / den) <= 0.5  <=>  num <= den / 2: the halving is exact
+        // and a quotient above 1/2 exceeds it by more than half an ulp of 1/2
+        const int ii = (nx <= __dmul_rn(0.5, dx)) ? i : i + 1;
+        const int jj = (ny <= __dmul_rn(0.5, dy)) ? j : j + 1;
         const int64_t col = asc_to_pix(R.gx, ii);
         const int64_t row = asc_to_pix(R.gy, jj);
         if (R.mask && R.mask[row * R.ms + col]) return false;  // picked texel is nodata
@@ -86,6 +123,12 @@ __device__ __forceinline__ bool sample(const RasterDev &R, double2 p, double *ou
     }
     const int64_t c0 = asc_to_pix(R.gx, i), c1 = asc_to_pix(R.gx, i + 1);
     const int64_t r0 = asc_to_pix(R.gy, j), r1 = asc_to_pix(R.gy, j + 1);
+    // the four texels first: their latency hides the two divisions
+    const double v00 = texel<T>(R, r0, c0);
+    const double v01 = texel<T>(R, r1, c0);
+    const double v10 = texel<T>(R, r0, c1);
+    const double v11 = texel<T>(R, r1, c1);
+    const double tx = __ddiv_rn(nx, dx), ty = __ddiv_rn(ny, dy);
     const double ux = __dsub_rn(1.0, tx), uy = __dsub_rn(1.0, ty);
     if (R.mask) {
         // node is dropped iff the same interpolation of the 0/1 mask is > 0:
@@ -100,10 +143,6 @@ __device__ __forceinline__ bool sample(const RasterDev &R, double2 p, double *ou
     // V[i,j] = z[row(j), col(i)];  hypercube order of _evaluate_linear:
     // (i,j) (i,j+1) (i+1,j) (i+1,j+1), weights (1-tx)(1-ty) ... tx*ty,
     // summed left to right starting from 0.0, no FMA contraction
-    const double v00 = texel<T>(R, r0, c0);
-    const double v01 = texel<T>(R, r1, c0);
-    const double v10 = texel<T>(R, r0, c1);
-    const double v11 = texel<T>(R, r1, c1);
     double acc;
     if (sizeof(T) == 4) {
         // generic python path: term = V * (w0 * w1)
@@ -123,9 +162,22 @@ __device__ __forceinline__ bool sample(const RasterDev &R, double2 p, double *ou
     return true;
 }
 
-template <int METHOD>
-__global__ void __launch_bounds__(256)
-interp_kernel(const RasterDev *__restrict__ rasters, int n_rasters,
+// DT: OCSB_F32 / OCSB_F64 = every raster of the list has that dtype, 2 = mixed
+template <int METHOD, int DT>
+__device__ __forceinline__ bool try_raster(const RasterDev &R, double2 p, double *v) {
+    // inclusive bbox test against min/max of the window coordinates
+    // (mesh.py:2290-2297); NaN coordinates fail every compare
+    if (!(R.xmin <= p.x && R.xmax >= p.x && R.ymin <= p.y && R.ymax >= p.y))
+        return false;
+    if (DT == OCSB_F32) return sample<float, METHOD>(R, p, v);
+    if (DT == OCSB_F64) return sample<double, METHOD>(R, p, v);
+    return (R.dtype == OCSB_F32) ? sample<float, METHOD>(R, p, v)
+                                 : sample<double, METHOD>(R, p, v);
+}
+
+template <int METHOD, int DT, bool SEL>
+__global__ void __launch_bounds__(256, OCSB_INTERP_MIN_CTAS)
+interp_kernel(const RasterDev *__restrict__ rasters, int n_rasters, SelGrid sel,
               const double2 *__restrict__ xy, int64_t K,
               uint8_t *__restrict__ touched, double *__restrict__ values,
               int32_t *__restrict__ source, const int32_t *__restrict__ perm) {
@@ -139,24 +191,37 @@ interp_kernel(const RasterDev *__restrict__ rasters, int n_rasters,
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < K;
          k += (int64_t)gridDim.x * blockDim.x) {
         const double2 p = __ldcs(xy + k);
-        for (int r = n_rasters - 1; r >= 0; --r) {
-            const RasterDev &R = s_r[r];
-            // inclusive bbox test against min/max of the window coordinates
-            // (mesh.py:2290-2297); NaN coordinates fail every compare
-            if (!(R.xmin <= p.x && R.xmax >= p.x && R.ymin <= p.y && R.ymax >= p.y))
-                continue;
-            double v;
-            const bool hit = (R.dtype == OCSB_F32)
-                                 ? sample<float, METHOD>(R, p, &v)
-                                 : sample<double, METHOD>(R, p, &v);
-            if (hit) {
-                // bucketed input: results go back to the original node index
-                const int64_t o = perm ? (int64_t)__ldg(perm + k) : k;
-                __stcs(values + o, v);
-                touched[o] = 1;
-                if (source) source[o] = r;
-                break;
+        double v;
+        int hit = -1;
+        if (SEL) {
+            // sloppy cell lookup (the cell sets carry a one-cell margin);
+            // NaN -> cell 0, whose boxes then reject the node exactly
+            const float fx = (float)__dmul_rn(__dsub_rn(p.x, sel.x0), sel.inv_x);
+            const float fy = (float)__dmul_rn(__dsub_rn(p.y, sel.y0), sel.inv_y);
+            const int cx = max(0, min(SEL_G - 1, __float2int_rd(fx)));
+            const int cy = max(0, min(SEL_G - 1, __float2int_rd(fy)));
+            uint64_t m = __ldg(sel.cells + cy * SEL_G + cx);
+            while (m) {
+                const int r = 63 - __clzll((long long)m);
+                m ^= 1ull << r;
+                if (try_raster<METHOD, DT>(s_r[r], p, &v)) {
+                    hit = r;
+                    break;
+                }
             }
+        } else {
+            for (int r = n_rasters - 1; r >= 0; --r)
+                if (try_raster<METHOD, DT>(s_r[r], p, &v)) {
+                    hit = r;
+                    break;
+                }
+        }
+        if (hit >= 0) {
+            // bucketed input: results go back to the original node index
+            const int64_t o = perm ? (int64_t)__ldg(perm + k) : k;
+            __stcs(values + o, v);
+            touched[o] = 1;
+            if (source) source[o] = hit;
         }
     }
 }
@@ -165,7 +230,38 @@ AscAxis make_asc(const LinAxis &a) {
     AscAxis g;
     g.a = a;
     g.flip = a.step < 0.0;
+    g.lo = lin_at_host(a, g.flip ? a.n - 1 : 0);
+    g.inv = a.step != 0.0 ? 1.0 / fabs(a.step) : 0.0;
+    g.pad = 0;
     return g;
+}
+
+template <int METHOD, int DT>
+void launch_dt(unsigned blocks, size_t smem, cudaStream_t st, const RasterDev *dev,
+               int n, const SelGrid &sel, const double2 *q, int64_t K,
+               uint8_t *touched, double *values, int32_t *source,
+               const int32_t *perm) {
+    if (sel.cells)
+        interp_kernel<METHOD, DT, true><<<blocks, 256, smem, st>>>(
+            dev, n, sel, q, K, touched, values, source, perm);
+    else
+        interp_kernel<METHOD, DT, false><<<blocks, 256, smem, st>>>(
+            dev, n, sel, q, K, touched, values, source, perm);
+}
+
+template <int METHOD>
+void launch(int dt, unsigned blocks, size_t smem, cudaStream_t st, const RasterDev *dev,
+            int n, const SelGrid &sel, const double2 *q, int64_t K, uint8_t *touched,
+            double *values, int32_t *source, const int32_t *perm) {
+    if (dt == OCSB_F32)
+        launch_dt<METHOD, OCSB_F32>(blocks, smem, st, dev, n, sel, q, K, touched, values,
+                                    source, perm);
+    else if (dt == OCSB_F64)
+        launch_dt<METHOD, OCSB_F64>(blocks, smem, st, dev, n, sel, q, K, touched, values,
+                                    source, perm);
+    else
+        launch_dt<METHOD, 2>(blocks, smem, st, dev, n, sel, q, K, touched, values, source,
+                             perm);
 }
 
 }  // namespace
@@ -174,6 +270,8 @@ int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
                        const double *xy, int64_t K, int method, uint8_t *touched,
                        double *values, int32_t *source, const int32_t *perm) {
     std::vector<RasterDev> host(n);
+    int dt = n > 0 ? rs[0].dem_dtype : OCSB_F32;
+    double ux0 = INFINITY, uy0 = INFINITY, ux1 = -INFINITY, uy1 = -INFINITY;
     for (int i = 0; i < n; ++i) {
         RasterDev &R = host[i];
         R.gx = make_asc(rs[i].ax);
@@ -186,6 +284,10 @@ int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
         R.dem = rs[i].dem; R.ds = rs[i].dem_stride;
         R.mask = rs[i].mask; R.ms = rs[i].mask_stride;
         R.dtype = rs[i].dem_dtype;
+        R.pad = 0;
+        if (R.dtype != dt) dt = 2;
+        ux0 = fmin(ux0, R.xmin); ux1 = fmax(ux1, R.xmax);
+        uy0 = fmin(uy0, R.ymin); uy1 = fmax(uy1, R.ymax);
     }
     static_assert(sizeof(RasterDev) % 8 == 0, "RasterDev is copied as 64-bit words");
     ScratchGuard sg(ctx);
@@ -194,6 +296,32 @@ int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
     // pageable source: the copy has been staged when cudaMemcpyAsync returns
     OCSB_CUDA(cudaMemcpyAsync(dev, host.data(), sizeof(RasterDev) * n,
                               cudaMemcpyHostToDevice, ctx->stream));
+    // selection grid (only worth it for a list; needs finite, non-empty extent)
+    SelGrid sel{0.0, 0.0, 0.0, 0.0, nullptr};
+    std::vector<uint64_t> cells;
+    if (n >= 3 && n <= SEL_MAX_RASTERS && ux1 > ux0 && uy1 > uy0 &&
+        std::isfinite(ux1 - ux0) && std::isfinite(uy1 - uy0)) {
+        const double cw = (ux1 - ux0) / SEL_G, ch = (uy1 - uy0) / SEL_G;
+        cells.assign((size_t)SEL_G * SEL_G, 0);
+        for (int i = 0; i < n; ++i) {
+            const RasterDev &R = host[i];
+            // cells touched by the box, grown by one cell on every side
+            int a = (int)floor((R.xmin - ux0) / cw) - 1, b = (int)floor((R.xmax - ux0) / cw) + 1;
+            int c = (int)floor((R.ymin - uy0) / ch) - 1, d = (int)floor((R.ymax - uy0) / ch) + 1;
+            a = std::max(a, 0); c = std::max(c, 0);
+            b = std::min(b, SEL_G - 1); d = std::min(d, SEL_G - 1);
+            for (int cy = c; cy <= d; ++cy)
+                for (int cx = a; cx <= b; ++cx)
+                    cells[(size_t)cy * SEL_G + cx] |= 1ull << i;
+        }
+        uint64_t *dcells = nullptr;
+        OCSB_TRY(sg.get(&dcells, cells.size()));
+        OCSB_CUDA(cudaMemcpyAsync(dcells, cells.data(), cells.size() * sizeof(uint64_t),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+        sel.x0 = ux0; sel.y0 = uy0;
+        sel.inv_x = 1.0 / cw; sel.inv_y = 1.0 / ch;
+        sel.cells = dcells;
+    }
     int64_t blocks = (K + 255) / 256;
     const int64_t cap = (int64_t)ctx->num_sms * 8;
     if (blocks > cap) blocks = cap;
@@ -202,11 +330,11 @@ int32_t k_interp_multi(ocsb_ctx *ctx, const InterpRaster *rs, int n,
     const double2 *q = reinterpret_cast<const double2 *>(xy);
     OCSB_TIME(ctx, KC_INTERP);
     if (method == OCSB_INTERP_NEAREST)
-        interp_kernel<OCSB_INTERP_NEAREST><<<(unsigned)blocks, 256, smem, ctx->stream>>>(
-            dev, n, q, K, touched, values, source, perm);
+        launch<OCSB_INTERP_NEAREST>(dt, (unsigned)blocks, smem, ctx->stream, dev, n, sel, q,
+                                    K, touched, values, source, perm);
     else
-        interp_kernel<OCSB_INTERP_LINEAR><<<(unsigned)blocks, 256, smem, ctx->stream>>>(
-            dev, n, q, K, touched, values, source, perm);
+        launch<OCSB_INTERP_LINEAR>(dt, (unsigned)blocks, smem, ctx->stream, dev, n, sel, q,
+                                   K, touched, values, source, perm);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;
