@@ -164,3 +164,66 @@ def all_gather_node_values(values_local, n_nodes: int, group=None):
     dist.all_gather_into_tensor(out, pad, group=group)
     return torch.cat([out[r * m:r * m + (b - a)]
                       for r, (a, b) in enumerate(sizes)]).contiguous()
+
+
+# ---------------------------------------------------------------------------
+# host placement: the streamed pass (ocsb_hfun_pass) moves 8 B/px over PCIe,
+# so on a multi-socket box each rank's pinned buffers must live on the NUMA
+# node its GPU hangs off
+# ---------------------------------------------------------------------------
+def parse_cpulist(text: str) -> List[int]:
+    """``"0-3,8,10-11"`` (sysfs cpulist format) -> ``[0, 1, 2, 3, 8, 10, 11]``."""
+    cpus: List[int] = []
+    for part in text.strip().split(","):
+        part = part.strip()
+        if not part:
+            continue
+        if "-" in part:
+            a, b = part.split("-", 1)
+            cpus.extend(range(int(a), int(b) + 1))
+        else:
+            cpus.append(int(part))
+    return cpus
+
+
+def gpu_pci_address(device: int) -> Optional[str]:
+    """``domain:bus:device.0`` of a CUDA device as sysfs spells it."""
+    import torch
+    try:
+        p = torch.cuda.get_device_properties(device)
+        return f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+    except (AttributeError, RuntimeError):
+        return None
+
+
+def bind_to_gpu_numa(device: int, sysfs: str = "/sys/bus/pci/devices") -> dict:
+    """Pin the calling thread (and the threads it creates later) to the CPUs
+    local to ``device``, so that memory it allocates and pins afterwards --
+    the DEM / hfun staging buffers of the streamed pass -- is node-local to the
+    GPU's PCIe root.  No-op (and says so) when sysfs has no locality to offer.
+    Call it before the first pinned allocation."""
+    import os
+    info = {"device": int(device), "bound": False}
+    addr = gpu_pci_address(device)
+    info["pci"] = addr
+    if addr is None or not hasattr(os, "sched_setaffinity"):
+        return info
+    try:
+        with open(os.path.join(sysfs, addr, "local_cpulist")) as f:
+            local = set(parse_cpulist(f.read()))
+        try:
+            with open(os.path.join(sysfs, addr, "numa_node")) as f:
+                info["numa_node"] = int(f.read().strip())
+        except (OSError, ValueError):
+            pass
+    except (OSError, ValueError):
+        return info
+    allowed = os.sched_getaffinity(0)
+    cpus = sorted(local & allowed)
+    info["local_cpus"] = len(local)
+    if not cpus or len(cpus) == len(allowed):
+        return info                       # no locality information / already local
+    os.sched_setaffinity(0, cpus)
+    info["bound"] = True
+    info["cpus"] = len(cpus)
+    return info

@@ -114,3 +114,29 @@ def _nodes_case(rank, world):
 def test_all_gather_node_values():
     for got in run_ranks(_nodes_case, 3):
         np.testing.assert_array_equal(got, np.arange(11) * 1.5)
+
+
+def test_cpulist_parsing_and_numa_binding_without_gpu(tmp_path, monkeypatch):
+    """Host placement helper: sysfs cpulist format, and binding is a no-op
+    (reported as such) when the device has no sysfs entry."""
+    from ocsmesh_b200 import distributed as D
+    assert D.parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert D.parse_cpulist("") == []
+    import os
+    before = os.sched_getaffinity(0)
+    monkeypatch.setattr(D, "gpu_pci_address", lambda d: "0000:1b:00.0")
+    info = D.bind_to_gpu_numa(0, sysfs=str(tmp_path))       # no such device dir
+    assert info["bound"] is False and os.sched_getaffinity(0) == before
+    # a device whose local CPUs are a strict subset of ours: bound to them
+    if len(before) > 1:
+        d = tmp_path / "0000:1b:00.0"
+        d.mkdir()
+        keep = sorted(before)[:1]
+        (d / "local_cpulist").write_text(",".join(map(str, keep)) + "\n")
+        (d / "numa_node").write_text("1\n")
+        try:
+            info = D.bind_to_gpu_numa(0, sysfs=str(tmp_path))
+            assert info["bound"] and info["numa_node"] == 1
+            assert os.sched_getaffinity(0) == set(keep)
+        finally:
+            os.sched_setaffinity(0, before)
