@@ -11,8 +11,10 @@ The raster hot path shards by raster rows:
   above and below its band (:func:`exchange_dem_halo`, pairwise send/recv of
   ``W`` floats).  Rows on the border of the *semantic window* get no halo: the
   kernel switches to numpy's one-sided difference there.
-* **multi-raster min-combine** -- overlap strips are min-reduced
-  (:func:`min_combine_strip`, an ``all_reduce(MIN)`` on the packed strip).
+* **multi-raster min-combine** -- raster ``r`` lives on rank ``r % world``;
+  every overlapping pair swaps its overlap strips and takes the min
+  (:func:`min_combine_overlaps`); a strip shared by all ranks can also be
+  min-reduced in one ``all_reduce(MIN)`` (:func:`min_combine_strip`).
 * **Mesh.interpolate** -- nodes are independent: contiguous node shards,
   rasters replicated (:func:`node_shard`); results are all-gathered.
 
@@ -145,6 +147,61 @@ def min_combine_strip(strip, group=None):
     import torch.distributed as dist
     dist.all_reduce(strip, op=dist.ReduceOp.MIN, group=group)
     return strip
+
+
+def raster_owner(index: int, world: int) -> int:
+    """Multi-raster runs (BASELINE.json configs[2]): raster ``index`` lives on
+    rank ``index % world``."""
+    return int(index) % int(world)
+
+
+def min_combine_overlaps(geoms, owners: Sequence[int], rank: int, get_window,
+                         combine, group=None) -> int:
+    """Multi-rank form of ``HfunCollector.min_combine_overlaps``: ``geoms[i]`` =
+    ``HfunRaster.geometry()`` of raster ``i`` (known to every rank), raster ``i``
+    lives on rank ``owners[i]``.  Three phases: (1) every overlap window of an
+    owned raster is snapshotted, (2) the strips of pairs split over two ranks
+    are swapped in ONE batched isend/irecv, in the same pair order on every
+    rank, (3) every owned window takes the min with its partner's snapshot.
+    Because the partners' PRE-combine values are used, a pixel covered by any
+    number of rasters ends up with the min over all of them.
+
+    ``get_window(i, window)`` -> contiguous tensor of an owned raster's window,
+    ``combine(i, window, tensor)`` -> raster ``i``'s window = min(window, tensor).
+    Returns the number of overlapping pairs."""
+    import torch
+    import torch.distributed as dist
+    from .hfun import overlap_windows
+    n = 0
+    todo = []        # (raster, window, partner's strip)
+    p2p, pending = [], []
+    for i in range(len(geoms)):
+        for j in range(i + 1, len(geoms)):
+            ov = overlap_windows(geoms[i], geoms[j])
+            if ov is None:
+                continue
+            n += 1
+            wi, wj = ov
+            oi, oj = owners[i], owners[j]
+            if rank != oi and rank != oj:
+                continue
+            if oi == oj:
+                si, sj = get_window(i, wi), get_window(j, wj)
+                todo.append((i, wi, sj))
+                todo.append((j, wj, si))
+                continue
+            mine, win, peer = (i, wi, oj) if rank == oi else (j, wj, oi)
+            send = get_window(mine, win)
+            recv = torch.empty_like(send)
+            p2p.append(dist.P2POp(dist.isend, send, peer, group))
+            p2p.append(dist.P2POp(dist.irecv, recv, peer, group))
+            pending.append((mine, win, recv))
+    if p2p:
+        for req in dist.batch_isend_irecv(p2p):
+            req.wait()
+    for i, w, t in todo + pending:
+        combine(i, w, t)
+    return n
 
 
 def all_gather_node_values(values_local, n_nodes: int, group=None):

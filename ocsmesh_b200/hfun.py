@@ -781,6 +781,53 @@ class HfunRaster:
                         window.width, window.height)
 
 
+    def min_combine_values(self, window: Window, src) -> None:
+        """hfun[window] = min(hfun[window], src) for a device float32 tensor
+        ``src`` of the window's shape (a strip received from another rank)."""
+        if tuple(src.shape) != (window.height, window.width):
+            raise ValueError("src must have the window's shape")
+        self._materialize()
+        src = src.contiguous()
+        if src.device != self._hfun.device:
+            src = src.to(self._hfun.device)
+        self._ctx().min_combine(self._hfun_ptr(self._hfun, window), self.width,
+                                src.data_ptr(), window.width, window.width,
+                                window.height)
+
+    def window_values(self, window: Window):
+        """Contiguous device copy of the window (the strip to send)."""
+        a = window.row_off - self._band[0]
+        return self.device_values[a:a + window.height,
+                                  window.col_off:window.col_off + window.width].contiguous()
+
+    def geometry(self):
+        """``(transform, width, height)``: all :func:`overlap_windows` needs."""
+        return (tuple(self.transform)[:6], self.width, self.height)
+
+
+def overlap_windows(geom_a, geom_b, tol: float = 1e-6):
+    """Co-registered overlap of two north-up rasters given as ``(transform,
+    width, height)``: ``(window_in_a, window_in_b)`` or ``None`` when they do
+    not overlap.  Raises when the pixel grids do not line up (different pixel
+    size, or an offset that is not a whole number of pixels) -- a pixel-wise
+    min is only defined for co-registered rasters."""
+    (ta, wa, ha), (tb, wb, hb) = geom_a, geom_b
+    if abs(ta[0] - tb[0]) > tol * abs(ta[0]) or abs(ta[4] - tb[4]) > tol * abs(ta[4]) \
+            or ta[1] or ta[3] or tb[1] or tb[3]:
+        raise ValueError("rasters are not co-registered (pixel size / rotation)")
+    fc = (tb[2] - ta[2]) / ta[0]
+    fr = (tb[5] - ta[5]) / ta[4]
+    oc, orow = int(round(fc)), int(round(fr))
+    if abs(fc - oc) > 1e-3 or abs(fr - orow) > 1e-3:
+        raise ValueError("rasters are not co-registered (sub-pixel offset)")
+    c0, c1 = max(0, oc), min(wa, oc + wb)
+    r0, r1 = max(0, orow), min(ha, orow + hb)
+    if c1 <= c0 or r1 <= r0:
+        return None
+    return (Window(c0, r0, c1 - c0, r1 - r0),
+            Window(c0 - oc, r0 - orow, c1 - c0, r1 - r0))
+
+
 class HfunCollector:
     """Minimal multi-raster size function: one ``HfunRaster`` per input
     raster, every ``add_*`` applied to every raster -- the call order of the
@@ -829,6 +876,30 @@ class HfunCollector:
                                   lower_bound=None, upper_bound=None, **_kw):
         for h in self._hfuns:
             h.add_subtidal_flow_limiter(hmin, hmax, lower_bound, upper_bound)
+
+    def add_gradient_delimiter(self, hmin=None, hmax=None, **_kw):
+        for h in self._hfuns:
+            h.add_gradient_delimiter(hmin=hmin, hmax=hmax)
+
+    def min_combine_overlaps(self) -> int:
+        """Pixel-wise min over the co-registered overlaps of the member rasters
+        (BASELINE.json configs[2]; build-defined): afterwards
+        every pixel of every raster holds the minimum over all rasters covering
+        it.  Every pair is visited once and both sides take the pair's min, so
+        any number of rasters may cover a pixel.  Returns the number of
+        overlapping pairs.  The multi-rank form is
+        :func:`ocsmesh_b200.distributed.min_combine_overlaps`."""
+        n = 0
+        for i, a in enumerate(self._hfuns):
+            for b in self._hfuns[i + 1:]:
+                ov = overlap_windows(a.geometry(), b.geometry())
+                if ov is None:
+                    continue
+                wa, wb = ov
+                a.min_combine(b, wa, wb)
+                b.min_combine(a, wb, wa)
+                n += 1
+        return n
 
 
 class Hfun:

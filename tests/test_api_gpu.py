@@ -132,3 +132,43 @@ def test_collector_min_combine(ctx):
     ref = O.min_combine(ohs[0].values[:, 150:], ohs[1].values[:, :50])
     a.min_combine(b, wa, wb)
     np.testing.assert_array_equal(a.get_values()[:, 150:], ref)
+
+
+def test_config3_eight_rasters_min_combined(ctx):
+    """BASELINE.json configs[2] scaled down: 8 overlapping rasters (4 x 2,
+    corners covered by four), every contour to every raster, limiter, then the
+    overlaps min-combined: each raster must equal its view of the mosaic min of
+    the oracle's per-raster results."""
+    th, tw, ovl, nx, ny = 130, 160, 30, 4, 2
+    rs, ohs, offs = [], [], []
+    for k in range(nx * ny):
+        ty, tx = divmod(k, nx)
+        x0 = S.X0 + (tw - ovl) * S.PIXEL * tx
+        y0 = S.Y0 - (th - ovl) * S.PIXEL * ty
+        z = S.synth_dem(th, tw, seed=10 + k, x0=x0, y0=y0)
+        tr = S.dem_transform(th, x0=x0, y0=y0)
+        rs.append(ob.Raster.from_numpy(z, tr, crs=32618))
+        ohs.append(O.OracleHfun(O.OracleRaster(z, tr), 100, 1500))
+        offs.append(((th - ovl) * ty, (tw - ovl) * tx))
+    coll = ob.Hfun(rs, hmin=100, hmax=1500)
+    coll.add_contour(0, 0.001, 100)
+    coll.add_subtidal_flow_limiter(hmin=50, hmax=1500, lower_bound=-30, upper_bound=0)
+    contours = []
+    for h in coll.hfuns:
+        contours.extend(h.raster.get_contour(0))
+    assert contours
+    for oh in ohs:
+        oh.add_feature(contours, 0.001, 100)
+        oh._clamp_pass()
+        oh.add_subtidal_flow_limiter(50, 1500, -30, 0)
+    assert coll.min_combine_overlaps() == 16     # 6 E-W + 4 N-S + 6 diagonal pairs
+    H, W = (th - ovl) * (ny - 1) + th, (tw - ovl) * (nx - 1) + tw
+    G = np.full((H, W), np.inf, dtype=np.float32)
+    for (r, c), oh in zip(offs, ohs):
+        G[r:r + th, c:c + tw] = O.min_combine(G[r:r + th, c:c + tw], oh.values)
+    for (r, c), h in zip(offs, coll.hfuns):
+        np.testing.assert_array_equal(h.get_values(), G[r:r + th, c:c + tw])
+    # idempotent
+    coll.min_combine_overlaps()
+    for (r, c), h in zip(offs, coll.hfuns):
+        np.testing.assert_array_equal(h.get_values(), G[r:r + th, c:c + tw])

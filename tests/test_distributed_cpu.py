@@ -140,3 +140,87 @@ def test_cpulist_parsing_and_numa_binding_without_gpu(tmp_path, monkeypatch):
             assert os.sched_getaffinity(0) == set(keep)
         finally:
             os.sched_setaffinity(0, before)
+
+
+# ---- configs[2]: rasters on rank r % world, pairwise overlap strips -----------
+def _c3_layout(tile_h=40, tile_w=50, ovl=10, nx=4, ny=2):
+    geoms = []
+    for k in range(nx * ny):
+        ty, tx = divmod(k, nx)
+        tr = list(S.dem_transform(tile_h))
+        tr[2] += (tile_w - ovl) * S.PIXEL * tx
+        tr[5] -= (tile_h - ovl) * S.PIXEL * ty      # next row of tiles lies south
+        geoms.append((tuple(tr), tile_w, tile_h))
+    return geoms
+
+
+def _c3_values(k, h, w):
+    return np.random.default_rng(100 + k).random((h, w)).astype(np.float32)
+
+
+def _c3_expected(geoms):
+    """Global mosaic min, then each raster's view of it."""
+    base = geoms[0]
+    # offsets of every raster in the pixel grid of raster 0
+    offs = []
+    for (tr, w, h) in geoms:
+        oc = int(round((tr[2] - base[0][2]) / base[0][0]))
+        orow = int(round((tr[5] - base[0][5]) / base[0][4]))
+        offs.append((orow, oc))
+    H = max(o[0] + g[2] for o, g in zip(offs, geoms))
+    W = max(o[1] + g[1] for o, g in zip(offs, geoms))
+    G = np.full((H, W), np.inf, dtype=np.float32)
+    for k, ((r, c), (_, w, h)) in enumerate(zip(offs, geoms)):
+        G[r:r + h, c:c + w] = np.minimum(G[r:r + h, c:c + w], _c3_values(k, h, w))
+    return [G[r:r + h, c:c + w].copy() for (r, c), (_, w, h) in zip(offs, geoms)]
+
+
+def _c3_case(rank, world):
+    geoms = _c3_layout()
+    owners = [D.raster_owner(k, world) for k in range(len(geoms))]
+    owned = {k: torch.from_numpy(_c3_values(k, g[2], g[1]))
+             for k, g in enumerate(geoms) if owners[k] == rank}
+
+    def get_window(i, w):
+        return owned[i][w.row_off:w.row_off + w.height,
+                        w.col_off:w.col_off + w.width].contiguous()
+
+    def combine(i, w, t):
+        v = owned[i][w.row_off:w.row_off + w.height, w.col_off:w.col_off + w.width]
+        torch.minimum(v, t, out=v)
+
+    n = D.min_combine_overlaps(geoms, owners, rank, get_window, combine)
+    return n, {k: v.numpy() for k, v in owned.items()}
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_min_combine_overlaps_pairwise_exchange(world):
+    """8 rasters 4x2 with overlaps (corners covered by 4 rasters) spread over
+    the ranks: after the pairwise strip swaps every raster equals its view of
+    the global mosaic min -- whatever the rank count."""
+    geoms = _c3_layout()
+    want = _c3_expected(geoms)
+    res = run_ranks(_c3_case, world)
+    seen = set()
+    for n, owned in res:
+        assert n == 4 * 1 + 3 * 2 + 2 * 3      # E-W, N-S and diagonal neighbours
+        for k, v in owned.items():
+            np.testing.assert_array_equal(v, want[k])
+            seen.add(k)
+    assert seen == set(range(len(geoms)))
+
+
+def test_overlap_windows_geometry():
+    from ocsmesh_b200.hfun import overlap_windows
+    from ocsmesh_b200 import Window
+    g = _c3_layout()
+    wa, wb = overlap_windows(g[0], g[1])          # east neighbour
+    assert wa == Window(40, 0, 10, 40) and wb == Window(0, 0, 10, 40)
+    wa, wb = overlap_windows(g[0], g[4])          # south neighbour
+    assert wa == Window(0, 30, 50, 10) and wb == Window(0, 0, 50, 10)
+    wa, wb = overlap_windows(g[5], g[0])          # diagonal, reversed order
+    assert wa == Window(0, 0, 10, 10) and wb == Window(40, 30, 10, 10)
+    assert overlap_windows(g[0], g[2]) is None
+    bad = (tuple(np.array(g[1][0]) + [0, 0, 3.0, 0, 0, 0]), 50, 40)
+    with pytest.raises(ValueError, match="co-registered"):
+        overlap_windows(g[0], bad)
