@@ -169,3 +169,24 @@ def test_interpolate_10m_nodes_16_tiles_sampled(big, ctx):
         assert (got != -7.5).mean() > 0.9
     for r_ in rasters:
         r_.drop_device_cache()
+
+
+def test_config1_whole_case_every_pixel_and_node(ctx):
+    """BASELINE.json configs[0] at its real size (2000 x 2000 DEM, 200 k nodes):
+    the oracle runs the whole case, so all 4 M sizes are compared bit for bit,
+    linear / nearest elevations bit for bit, spline (the reference's default
+    method) to 1e-9 relative."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        "run_c1", os.path.join(os.path.dirname(os.path.dirname(
+            os.path.abspath(__file__))), "tools", "run_c1.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    res = mod.run(2000, 200_000, repeat=1)
+    assert res["hfun_px"] == 4_000_000 and res["hfun_mismatched_px"] == 0
+    for m in ("linear", "nearest"):
+        assert res[f"interp_{m}_mismatched_nodes"] == 0
+        assert res[f"interp_{m}_same_untouched_set"]
+    assert res["interp_spline_same_untouched_set"]
+    assert res["interp_spline_max_rel_err"] <= 1e-9

@@ -1,0 +1,115 @@
+"""BASELINE.json configs[0] at its real size, product against oracle, end to end:
+
+    synthetic 2000 x 2000 DEM: Hfun(raster).add_contour(level=0,
+    expansion_rate=0.001, target_size=100) + add_subtidal_flow_limiter, then
+    Mesh.interpolate onto a 200 k-node mesh (spline -- the reference's default --
+    linear and nearest)
+
+The oracle (numpy/scipy restatement, all host cores) runs the whole case, so
+every one of the 4 M pixels and 200 k nodes is compared, and both are timed by
+wall clock through their public calls (the product's time includes the DEM
+upload and the result download).  Prints one JSON line.
+
+    python tools/run_c1.py [--size 2000] [--nodes 200000]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ocsmesh_b200 as ob
+from ocsmesh_b200 import synthetic as S
+from oracle import ocsmesh_oracle as O
+
+RATE, TARGET, HMIN, HMAX = 0.001, 100.0, 100.0, 1500.0
+LIM = dict(hmin=50.0, hmax=1500.0, lower_bound=-30.0, upper_bound=0.0)
+
+
+def wall(fn, sync=True):
+    if sync:
+        torch.cuda.synchronize()
+    t = time.perf_counter()
+    out = fn()
+    if sync:
+        torch.cuda.synchronize()
+    return out, time.perf_counter() - t
+
+
+def run(size=2000, nodes=200_000, repeat=3):
+    z = S.synth_dem(size, size, seed=1)
+    tr = S.dem_transform(size)
+    b = O.array_bounds(size, size, tr)
+    xy = S.synth_nodes(nodes, b, seed=100, outside_frac=0.02)
+    res = {"config": f"BASELINE.json configs[0]: {size}x{size} DEM, add_contour(0, "
+                     f"{RATE}, {TARGET}) + add_subtidal_flow_limiter, "
+                     f"Mesh.interpolate onto {nodes} nodes",
+           "host_cores": os.cpu_count()}
+
+    def product_hfun():
+        r = ob.Raster.from_numpy(z, tr, crs=32618)
+        h = ob.Hfun(r, hmin=HMIN, hmax=HMAX)
+        h.add_contour(level=0, expansion_rate=RATE, target_size=TARGET)
+        h.add_subtidal_flow_limiter(**LIM)
+        return r, h, h.get_values()
+
+    product_hfun()                                       # warm-up (pools, module load)
+    best = None
+    for _ in range(repeat):
+        (r, h, got), dt = wall(product_hfun)
+        best = dt if best is None else min(best, dt)
+    res["hfun_product_s"] = round(best, 5)
+
+    def oracle_hfun():
+        orr = O.OracleRaster(z, tr)
+        oh = O.OracleHfun(orr, hmin=HMIN, hmax=HMAX)
+        # parity boundary: the oracle consumes the contour the product traced
+        oh.add_feature(r.get_contour(0), RATE, TARGET)
+        oh._clamp_pass()
+        oh.add_subtidal_flow_limiter(LIM["hmin"], LIM["hmax"], LIM["lower_bound"],
+                                     LIM["upper_bound"])
+        return orr, oh.values
+
+    (orr, want), dt = wall(oracle_hfun, sync=False)
+    res["hfun_oracle_s"] = round(dt, 4)
+    res["hfun_px"] = int(want.size)
+    res["hfun_mismatched_px"] = int((got != want).sum())
+    res["hfun_speedup_wall"] = round(dt / best, 1)
+
+    for method in ("spline", "linear", "nearest"):
+        def product_interp():
+            mesh = ob.Mesh(ob.MeshData(xy, values=np.full(nodes, np.nan)))
+            mesh.interpolate(r, method=method)
+            return np.asarray(mesh.value).reshape(-1)
+
+        product_interp()
+        best = None
+        for _ in range(repeat):
+            gv, dt = wall(product_interp)
+            best = dt if best is None else min(best, dt)
+        ov, odt = wall(lambda: O.mesh_interpolate(xy, np.full(nodes, np.nan), orr,
+                                                  method=method).reshape(-1), sync=False)
+        same_nan = np.array_equal(np.isnan(gv), np.isnan(ov))
+        ok = ~np.isnan(ov)
+        if method == "spline":
+            err = float(np.max(np.abs(gv[ok] - ov[ok]) / np.maximum(np.abs(ov[ok]), 1.0)))
+            res[f"interp_{method}_max_rel_err"] = err
+        else:
+            res[f"interp_{method}_mismatched_nodes"] = int((gv[ok] != ov[ok]).sum())
+        res[f"interp_{method}_same_untouched_set"] = bool(same_nan)
+        res[f"interp_{method}_product_s"] = round(best, 5)
+        res[f"interp_{method}_oracle_s"] = round(odt, 4)
+        res[f"interp_{method}_speedup_wall"] = round(odt / best, 1)
+    return res
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--size", type=int, default=2000)
+    ap.add_argument("--nodes", type=int, default=200_000)
+    a = ap.parse_args()
+    print(json.dumps(run(a.size, a.nodes)), flush=True)
