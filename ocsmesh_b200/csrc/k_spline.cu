@@ -10,11 +10,22 @@
 // host in O(n) (no pivoting is needed: the pivots stay >= 1/3) and every
 // raster line is then a forward/back substitution on the device.
 //
-//   pass A  one thread per raster column: solve along y (ascending),
-//           DEM (any dtype) -> f64, coalesced across columns
-//   transpose (32x32 shared tiles)
-//   pass B  one thread per y index: solve along x (ascending), writes the
-//           coefficients in scipy's layout  c[i * ny + j]
+// The triangular solves are first-order-dominated recurrences whose memory
+// decays like (2 - sqrt 3)^k = 0.268^k (the ratio l1 = u1/d of the cubic
+// B-spline collocation matrix), so a line need not be walked end to end by one
+// thread: it is cut into chunks of R points and every chunk warms its
+// recurrence up over the kWarm = 48 points before it from a zero state --
+// 0.268^48 = 4e-28 relative, far below the f64 rounding of the walk itself
+// (a chunk that starts at the end of the line needs no warm-up and is exact).
+// That turns n dependent steps on nx threads (5000 threads for a 5000 x 5000
+// tile: 1 % of the machine, latency-bound) into R + 48 steps on nx * n / R
+// threads, all loads coalesced across the fast axis:
+//
+//   fwd A   L y = b    along y (ascending), DEM (any dtype) -> f64   src  -> coef
+//   bwd A   U x = y    along y                                       coef -> tmp
+//   transpose (32x32 shared tiles), (ny, nx) -> (nx, ny)             tmp  -> coef
+//   fwd B / bwd B      along x (ascending)                  coef -> tmp -> coef
+//   result in scipy's layout  c[i * ny + j]
 //   eval    one thread per node: knot interval from the linspace axes,
 //           de Boor (fpbspl) basis, 4x4 coefficient gather (88 B/node)
 //
@@ -22,6 +33,7 @@
 // evaluation 16 + 16*... see DESIGN.md.
 #include "ocsb_common.cuh"
 
+#include <cstring>
 #include <vector>
 
 namespace {
@@ -70,9 +82,12 @@ __host__ __device__ __forceinline__ void bspl3(KnotF t, int l, double x,
     double hh[3];
     h[0] = 1.0;
     h[1] = h[2] = h[3] = 0.0;
+#pragma unroll
     for (int j = 1; j <= 3; ++j) {
+#pragma unroll
         for (int i = 0; i < j; ++i) hh[i] = h[i];
         h[0] = 0.0;
+#pragma unroll
         for (int i = 0; i < j; ++i) {
             const int li = l + i + 1, lj = li - j;
             const double tli = t(li), tlj = t(lj);
@@ -134,36 +149,67 @@ int32_t factor_axis(const AscAxisS &g, std::vector<double> *out) {
     return OCSB_OK;
 }
 
-// Solve along the slow axis of a (n, m) f64 array `dst` (element (i, k) at
-// dst[i*m + k]) for every k.  Source element (i, k) is read from
-//   src[(src_flip ? n-1-i : i) * ss + k]   (type T).
+constexpr int kWarm = 48;   // warm-up points of a chunked recurrence (see header)
+
+// Forward substitution L y = b along the slow axis of an (n, m) array for every
+// fast index k, chunk blockIdx.y of R slow indices: y(i, k) -> dst[i*m + k].
+// Source element (i, k) is src[(src_flip ? n-1-i : i) * ss + k]  (type T).
 template <typename T>
 __global__ void __launch_bounds__(128)
-solve_lines_kernel(const T *__restrict__ src, int64_t ss, int src_flip,
-                   double *__restrict__ dst, int n, int m,
-                   const double *__restrict__ lu) {
+solve_fwd_kernel(const T *__restrict__ src, int64_t ss, int src_flip,
+                 double *__restrict__ dst, int n, int m, int R,
+                 const double *__restrict__ lu) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= m) return;
+    const int a = blockIdx.y * R;
+    const int b = min(n, a + R);
+    const int s = max(0, a - kWarm);
     double y1 = 0.0, y2 = 0.0;  // y[i-1], y[i-2]
-    for (int i = 0; i < n; ++i) {
+#pragma unroll 4
+    for (int i = s; i < b; ++i) {
         const int64_t si = src_flip ? (n - 1 - i) : i;
-        const double b = (double)src[si * ss + k];
+        const double v = (double)__ldg(src + si * ss + k);
         const double l2 = __ldg(lu + (int64_t)i * 5 + 0);
         const double l1 = __ldg(lu + (int64_t)i * 5 + 1);
-        const double y = b - l1 * y1 - l2 * y2;
-        dst[(int64_t)i * m + k] = y;
+        // one dependent FMA per step: the y2 term does not wait for y1
+        const double y = fma(-l1, y1, fma(-l2, y2, v));
+        if (i >= a) dst[(int64_t)i * m + k] = y;
         y2 = y1; y1 = y;
     }
+}
+
+// Back substitution U x = y along the slow axis, same chunking, walking down
+// from kWarm points above the chunk: x(i, k) -> dst[i*m + k].
+__global__ void __launch_bounds__(128)
+solve_bwd_kernel(const double *__restrict__ ysrc, double *__restrict__ dst, int n,
+                 int m, int R, const double *__restrict__ lu) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    const int a = blockIdx.y * R;
+    const int b = min(n, a + R);
+    const int e = min(n, b + kWarm);
     double x1 = 0.0, x2 = 0.0;  // x[i+1], x[i+2]
-    for (int i = n - 1; i >= 0; --i) {
+#pragma unroll 4
+    for (int i = e - 1; i >= a; --i) {
         const double invd = __ldg(lu + (int64_t)i * 5 + 2);
         const double u1 = __ldg(lu + (int64_t)i * 5 + 3);
         const double u2 = __ldg(lu + (int64_t)i * 5 + 4);
-        const double y = dst[(int64_t)i * m + k];
-        const double x = (y - u1 * x1 - u2 * x2) * invd;
-        dst[(int64_t)i * m + k] = x;
+        const double y = __ldg(ysrc + (int64_t)i * m + k);
+        // x = (y - u1 x1 - u2 x2) / d with only one FMA on the x1 chain
+        const double x = fma(-(u1 * invd), x1, fma(-u2, x2, y) * invd);
+        if (i < b) dst[(int64_t)i * m + k] = x;
         x2 = x1; x1 = x;
     }
+}
+
+// chunk length: enough threads to fill the machine, warm-up overhead bounded
+inline int chunk_rows(int n, int m, int num_sms) {
+    const int64_t want = (int64_t)num_sms * 2048;          // resident threads
+    int64_t r = ((int64_t)n * m + want - 1) / want;
+    r = (r + 31) / 32 * 32;
+    if (r < 32) r = 32;
+    if (r > 256) r = 256;
+    return (int)r;
 }
 
 // out[c * rows + r] = in[r * cols + c]
@@ -184,47 +230,90 @@ transpose_kernel(const double *__restrict__ in, double *__restrict__ out,
     }
 }
 
-// data interval i with g[i] <= v < g[i+1] clipped to [0, n-2]
-__device__ __forceinline__ int find_interval(const AscAxisS &g, double v) {
+// data interval i with g[i] <= v < g[i+1] clipped to [0, n-2]; the analytic
+// guess is checked against the exact grid lines and walked when it is off
+__device__ __forceinline__ int find_interval(const AscAxisS &g, double v, double lo,
+                                             double inv) {
     const int n = g.a.n;
-    const double lo = asc_at(g, 0);
-    int i = (int)floor((v - lo) / fabs(g.a.step));
+    int i = __double2int_rd((v - lo) * inv);
     i = max(0, min(n - 2, i));
     while (i > 0 && v < asc_at(g, i)) --i;
     while (i < n - 2 && v >= asc_at(g, i + 1)) ++i;
     return i;
 }
 
+// the six knots t[l-2 .. l+3] around knot interval l, read once
+struct LocalKnots {
+    double t[6];
+    int l;
+    __device__ double operator()(int p) const { return t[p - l + 2]; }
+};
+
+__device__ __forceinline__ LocalKnots local_knots(const AscAxisS &g, int l) {
+    const DevKnots k{g};
+    LocalKnots L;
+    L.l = l;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) L.t[q] = k(l - 2 + q);
+    return L;
+}
+
+struct SplineRaster {
+    AscAxisS gx, gy;
+    double xmin, xmax, ymin, ymax;
+    double lox, invx, loy, invy;   // asc[0] and 1/|step| per axis
+    const double *coef;
+};
+
+// RectBivariateSpline.ev of one raster at p (fpbisp order: i over x, j over y)
+__device__ __forceinline__ double spline_at(const SplineRaster &R, double2 p) {
+    const int nx = R.gx.a.n, ny = R.gy.a.n;
+    // knot interval: l = clamp(i + 2, 3, n - 1) (see header comment)
+    int lx = find_interval(R.gx, p.x, R.lox, R.invx) + 2;
+    lx = max(3, min(nx - 1, lx));
+    int ly = find_interval(R.gy, p.y, R.loy, R.invy) + 2;
+    ly = max(3, min(ny - 1, ly));
+    double hx[4], hy[4];
+    bspl3(local_knots(R.gx, lx), lx, p.x, hx);
+    bspl3(local_knots(R.gy, ly), ly, p.y, hy);
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const double *row = R.coef + (int64_t)(lx - 3 + i) * ny + (ly - 3);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            acc = acc + __ldg(row + j) * hx[i] * hy[j];
+    }
+    return acc;
+}
+
+// One launch for a list of rasters: the reference applies them in list order
+// and the last one whose window contains the node wins (mesh.py:372-376; the
+// spline branch has no nodata rule), so every node walks the list backwards
+// and evaluates exactly one spline -- instead of one launch per raster in
+// which 15 of 16 lanes of a warp of randomly ordered nodes sit idle.
 __global__ void __launch_bounds__(256)
-spline_eval_kernel(AscAxisS gx, AscAxisS gy, double xmin, double xmax,
-                   double ymin, double ymax, const double *__restrict__ coef,
+spline_eval_kernel(const SplineRaster *__restrict__ rasters, int n_rasters,
                    const double2 *__restrict__ xy, int64_t K,
                    uint8_t *__restrict__ touched, double *__restrict__ values) {
-    const int nx = gx.a.n, ny = gy.a.n;
+    extern __shared__ unsigned char s_raw[];
+    SplineRaster *s_r = reinterpret_cast<SplineRaster *>(s_raw);
+    for (int i = threadIdx.x; i < n_rasters * (int)(sizeof(SplineRaster) / 8);
+         i += blockDim.x)
+        reinterpret_cast<uint64_t *>(s_r)[i] =
+            reinterpret_cast<const uint64_t *>(rasters)[i];
+    __syncthreads();
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < K;
          k += (int64_t)gridDim.x * blockDim.x) {
         const double2 p = __ldcs(xy + k);
-        if (!(xmin <= p.x && xmax >= p.x && ymin <= p.y && ymax >= p.y))
-            continue;
-        // knot interval: l = clamp(i + 2, 3, n - 1) (see header comment)
-        int lx = find_interval(gx, p.x) + 2;
-        lx = max(3, min(nx - 1, lx));
-        int ly = find_interval(gy, p.y) + 2;
-        ly = max(3, min(ny - 1, ly));
-        double hx[4], hy[4];
-        bspl3(DevKnots{gx}, lx, p.x, hx);
-        bspl3(DevKnots{gy}, ly, p.y, hy);
-        // fpbisp accumulation order: i over x, j over y
-        double acc = 0.0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const double *row = coef + (int64_t)(lx - 3 + i) * ny + (ly - 3);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                acc = acc + __ldg(row + j) * hx[i] * hy[j];
+        for (int r = n_rasters - 1; r >= 0; --r) {
+            const SplineRaster &R = s_r[r];
+            if (!(R.xmin <= p.x && R.xmax >= p.x && R.ymin <= p.y && R.ymax >= p.y))
+                continue;
+            values[k] = spline_at(R, p);
+            touched[k] = 1;
+            break;
         }
-        values[k] = acc;
-        touched[k] = 1;
     }
 }
 
@@ -249,54 +338,92 @@ int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
     OCSB_CUDA(cudaMemcpyAsync(luy, fy.data(), fy.size() * 8,
                               cudaMemcpyHostToDevice, ctx->stream));
     OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
-    // pass A: along y for every pixel column.  Result in `coef` viewed as
-    // (ny, nx): element (j, c) = coef[j*nx + c] (c = pixel column)
+    const dim3 tb(128);
+    // along y for every pixel column c: (ny, nx) arrays, element (j, c) at [j*nx + c]
     {
-        const int blocks = (nx + 127) / 128;
+        const int R = chunk_rows(ny, nx, ctx->num_sms);
+        const dim3 grid((nx + 127) / 128, (ny + R - 1) / R);
         OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
         if (dem_dtype == OCSB_F32)
-            solve_lines_kernel<float><<<blocks, 128, 0, ctx->stream>>>(
-                (const float *)dem, dem_stride, gy.flip, coef, ny, nx, luy);
+            solve_fwd_kernel<float><<<grid, tb, 0, ctx->stream>>>(
+                (const float *)dem, dem_stride, gy.flip, coef, ny, nx, R, luy);
         else
-            solve_lines_kernel<double><<<blocks, 128, 0, ctx->stream>>>(
-                (const double *)dem, dem_stride, gy.flip, coef, ny, nx, luy);
+            solve_fwd_kernel<double><<<grid, tb, 0, ctx->stream>>>(
+                (const double *)dem, dem_stride, gy.flip, coef, ny, nx, R, luy);
+        OCSB_LAUNCHED(ctx);
+        OCSB_CHECK_LAUNCH();
+        OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
+        solve_bwd_kernel<<<grid, tb, 0, ctx->stream>>>(coef, tmp, ny, nx, R, luy);
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
     }
-    // transpose (ny, nx) -> tmp (nx, ny): tmp[c*ny + j]
+    // transpose tmp (ny, nx) -> coef (nx, ny): coef[c*ny + j]
     {
         dim3 grid((nx + 31) / 32, (ny + 31) / 32);
         OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
-        transpose_kernel<<<grid, 256, 0, ctx->stream>>>(coef, tmp, ny, nx);
+        transpose_kernel<<<grid, 256, 0, ctx->stream>>>(tmp, coef, ny, nx);
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
     }
-    // pass B: along x (ascending) for every j; source row = pixel column
+    // along x (ascending) for every j; source row = pixel column
     {
-        const int blocks = (ny + 127) / 128;
+        const int R = chunk_rows(nx, ny, ctx->num_sms);
+        const dim3 grid((ny + 127) / 128, (nx + R - 1) / R);
         OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
-        solve_lines_kernel<double><<<blocks, 128, 0, ctx->stream>>>(
-            tmp, ny, gx.flip, coef, nx, ny, lux);
+        solve_fwd_kernel<double><<<grid, tb, 0, ctx->stream>>>(
+            coef, ny, gx.flip, tmp, nx, ny, R, lux);
+        OCSB_LAUNCHED(ctx);
+        OCSB_CHECK_LAUNCH();
+        OCSB_TIME(ctx, KC_SPLINE_PREFILTER);
+        solve_bwd_kernel<<<grid, tb, 0, ctx->stream>>>(tmp, coef, nx, ny, R, lux);
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
     }
     return OCSB_OK;
 }
 
-int32_t k_spline_eval(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const double *coef,
-                      const double *xy, int64_t K, uint8_t *touched,
-                      double *values) {
-    const AscAxisS gx = make_asc(ax), gy = make_asc(ay);
-    double x_a = lin_at_host(ax, 0), x_b = lin_at_host(ax, ax.n - 1);
-    double y_a = lin_at_host(ay, 0), y_b = lin_at_host(ay, ay.n - 1);
+int32_t k_spline_eval_multi(ocsb_ctx *ctx, const SplineEvalRaster *rs, int n,
+                            const double *xy, int64_t K, uint8_t *touched,
+                            double *values) {
+    std::vector<SplineRaster> host(n);
+    for (int i = 0; i < n; ++i) {
+        SplineRaster &R = host[i];
+        memset(&R, 0, sizeof(R));
+        R.gx = make_asc(rs[i].ax);
+        R.gy = make_asc(rs[i].ay);
+        const LinAxis &ax = rs[i].ax, &ay = rs[i].ay;
+        const double x_a = lin_at_host(ax, 0), x_b = lin_at_host(ax, ax.n - 1);
+        const double y_a = lin_at_host(ay, 0), y_b = lin_at_host(ay, ay.n - 1);
+        R.xmin = fmin(x_a, x_b); R.xmax = fmax(x_a, x_b);
+        R.ymin = fmin(y_a, y_b); R.ymax = fmax(y_a, y_b);
+        R.lox = asc_at_host(R.gx, 0); R.loy = asc_at_host(R.gy, 0);
+        R.invx = ax.step != 0.0 ? 1.0 / fabs(ax.step) : 0.0;
+        R.invy = ay.step != 0.0 ? 1.0 / fabs(ay.step) : 0.0;
+        R.coef = rs[i].coef;
+    }
+    static_assert(sizeof(SplineRaster) % 8 == 0, "copied as 64-bit words");
+    const size_t smem = sizeof(SplineRaster) * n;
+    OCSB_REQUIRE(smem <= 40 * 1024, "spline evaluation: too many rasters (%d)", n);
+    ScratchGuard sg(ctx);
+    SplineRaster *dev = nullptr;
+    OCSB_TRY(sg.get(&dev, (size_t)n));
+    // pageable source: staged before cudaMemcpyAsync returns
+    OCSB_CUDA(cudaMemcpyAsync(dev, host.data(), smem, cudaMemcpyHostToDevice,
+                              ctx->stream));
     int64_t blocks = (K + 255) / 256;
     int64_t cap = (int64_t)ctx->num_sms * 16;
     if (blocks > cap) blocks = cap;
     OCSB_TIME(ctx, KC_SPLINE_EVAL);
-    spline_eval_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(
-        gx, gy, fmin(x_a, x_b), fmax(x_a, x_b), fmin(y_a, y_b), fmax(y_a, y_b),
-        coef, reinterpret_cast<const double2 *>(xy), K, touched, values);
+    spline_eval_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>(
+        dev, n, reinterpret_cast<const double2 *>(xy), K, touched, values);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;
+}
+
+int32_t k_spline_eval(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const double *coef,
+                      const double *xy, int64_t K, uint8_t *touched,
+                      double *values) {
+    SplineEvalRaster r{ax, ay, coef};
+    return k_spline_eval_multi(ctx, &r, 1, xy, K, touched, values);
 }

@@ -944,16 +944,71 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
     OCSB_REQUIRE(rasters && xy && touched && values,
                  "ocsb_interp_multi: NULL buffers");
     if (method == OCSB_INTERP_SPLINE) {
-        // per-raster coefficient arrays: one prefilter + evaluation per entry;
-        // `source` follows from the touched flags of each pass
-        for (int32_t i = 0; i < n_rasters; ++i) {
-            const ocsb_interp_raster &r = rasters[i];
-            OCSB_TRY(ocsb_interp(ctx, &r.win, r.dem, r.dem_dtype, r.dem_stride,
-                                 nullptr, 0, xy, K, method, touched, values));
-        }
+        // groups of consecutive rasters whose coefficient arrays (8 B/px) fit
+        // a budget: prefilter each member, then ONE evaluation launch per
+        // group in which every node takes the last member containing it;
+        // later groups overwrite earlier ones, so list order still decides
         OCSB_REQUIRE(source == nullptr && perm == nullptr,
                      "ocsb_interp_multi: source / perm are not available for "
                      "spline");
+        for (int32_t i = 0; i < n_rasters; ++i) {
+            const ocsb_interp_raster &r = rasters[i];
+            OCSB_TRY(check_win(&r.win, "ocsb_interp_multi"));
+            OCSB_REQUIRE(r.dem_dtype == OCSB_F32 || r.dem_dtype == OCSB_F64,
+                         "ocsb_interp_multi: unsupported DEM dtype %d", r.dem_dtype);
+            OCSB_REQUIRE(r.win.width >= 4 && r.win.height >= 4,
+                         "ocsb_interp: cubic spline needs >= 4 points per axis");
+            OCSB_REQUIRE(r.dem && r.dem_stride >= r.win.width,
+                         "ocsb_interp_multi: bad raster %d", i);
+            OCSB_REQUIRE(r.win.x0 != r.win.x1 && r.win.y0 != r.win.y1,
+                         "ocsb_interp_multi: degenerate window bounds");
+        }
+        Staged sxy, st, sval;
+        OCSB_TRY(sxy.init(ctx, xy, 1, K * 2, K * 2, 8, STAGE_IN));
+        OCSB_TRY(st.init(ctx, touched, 1, K, K, 1, STAGE_INOUT));
+        OCSB_TRY(sval.init(ctx, values, 1, K, K, 8, STAGE_INOUT));
+        const size_t budget = (size_t)16 << 30;   // coefficient bytes per group
+        const int32_t max_group = 64;
+        int32_t g0 = 0;
+        while (g0 < n_rasters) {
+            size_t bytes = 0;
+            int32_t g1 = g0;
+            while (g1 < n_rasters && g1 - g0 < max_group) {
+                const size_t need = (size_t)rasters[g1].win.width *
+                                    rasters[g1].win.height * sizeof(double);
+                if (g1 > g0 && bytes + need > budget) break;
+                bytes += need;
+                ++g1;
+            }
+            {
+                ScratchGuard sg(ctx);
+                std::vector<Staged> sz(g1 - g0);
+                std::vector<SplineEvalRaster> rs(g1 - g0);
+                for (int32_t i = g0; i < g1; ++i) {
+                    const ocsb_interp_raster &r = rasters[i];
+                    const int w = r.win.width, h = r.win.height;
+                    const size_t es = r.dem_dtype == OCSB_F32 ? 4 : 8;
+                    Staged &z = sz[i - g0];
+                    OCSB_TRY(z.init(ctx, r.dem, h, w, r.dem_stride, es, STAGE_IN));
+                    double *coef = nullptr;
+                    OCSB_TRY(sg.get(&coef, (size_t)w * h));
+                    SplineEvalRaster &e = rs[i - g0];
+                    win_axes(&r.win, &e.ax, &e.ay);
+                    OCSB_TRY(k_spline_prefilter(ctx, e.ax, e.ay, z.dev, r.dem_dtype,
+                                                z.dev_stride, coef));
+                    e.coef = coef;
+                }
+                OCSB_TRY(k_spline_eval_multi(ctx, rs.data(), g1 - g0,
+                                             (const double *)sxy.dev, K,
+                                             (uint8_t *)st.dev, (double *)sval.dev));
+                // the coefficient arrays are released in stream order
+            }
+            g0 = g1;
+        }
+        OCSB_TRY(st.finish());
+        OCSB_TRY(sval.finish());
+        if (sxy.staged || st.staged || sval.staged)
+            OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
         return OCSB_OK;
     }
     std::vector<Staged> sz(n_rasters), sm(n_rasters);

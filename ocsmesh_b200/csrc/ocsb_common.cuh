@@ -330,6 +330,14 @@ int32_t k_bucket_nodes(ocsb_ctx *ctx, const double *xy, int64_t K,
 int32_t k_spline_prefilter(ocsb_ctx *ctx, LinAxis ax, LinAxis ay,
                            const void *dem, int dem_dtype, int64_t dem_stride,
                            double *coef);
+struct SplineEvalRaster {
+    LinAxis ax, ay;
+    const double *coef;   // (nx, ny) coefficients of k_spline_prefilter
+};
+// rasters in list order, the last one whose window contains a node wins
+int32_t k_spline_eval_multi(ocsb_ctx *ctx, const SplineEvalRaster *rs, int n,
+                            const double *xy, int64_t K, uint8_t *touched,
+                            double *values);
 int32_t k_spline_eval(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const double *coef,
                       const double *xy, int64_t K, uint8_t *touched,
                       double *values);
