@@ -566,8 +566,7 @@ def bench_interp(args, rank, world, dev, ctx, peak):
             x2 = xy_host.to(f"cuda:{dev}", non_blocking=True)
             v2 = torch.full((n,), float("nan"), dtype=torch.float64, device=f"cuda:{dev}")
             t2 = torch.zeros(n, dtype=torch.uint8, device=f"cuda:{dev}")
-            x2, p2 = EuclideanMesh2D.bucket_nodes(ctx, rasters, x2, dev)
-            EuclideanMesh2D._interp_device(ctx, rasters, x2, v2, t2, method, 1, dev, perm=p2)
+            EuclideanMesh2D._interp_device(ctx, rasters, x2, v2, t2, method, 1, dev)
             vh.copy_(v2)
         a1.record()
         torch.cuda.synchronize(dev)
@@ -591,12 +590,37 @@ def bench_interp(args, rank, world, dev, ctx, peak):
                        "algorithmic_bytes_per_node": bpn,
                        "ms_per_step_mesh_order_outputs": ms_mesh_order,
                        "bucket_pass_ms": bucket_ms}
+    # spline (the reference's default method): prefilter of every tile + one
+    # evaluation launch, nodes in mesh order; no bucket / scatter variants
+    def spline_call():
+        EuclideanMesh2D._interp_device(ctx, rasters, xy_raw, vals, touched, "spline", 1, dev)
+    spline_call()
+    torch.cuda.synchronize(dev)
+    ctx.reset_timing()
+    ctx.set_timing(True)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(3):
+        spline_call()
+    s1.record()
+    torch.cuda.synchronize(dev)
+    ctx.set_timing(False)
+    sms = s0.elapsed_time(s1) / 3
+    skt = {k: v[0] / 3 for k, v in ctx.get_timing().items() if k.startswith("spline")}
+    if world > 1:
+        tt = torch.tensor([sms], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        sms = float(tt[0])
+    out["spline"] = {"Mnodes_per_s": K / (sms * 1e-3) / 1e6, "ms_per_step": sms,
+                     "kernel_ms_per_step": skt,
+                     "note": "prefilter of all 16 tiles (one-off per raster, "
+                             "16 B/px) inside every step + evaluation (88 B/node)"}
     out["config"] = (f"BASELINE.json configs[3]: {K} nodes ({args.nodes}/GPU), "
                      f"16 tiles {T}x{T} (4x4, {ovl}-px overlap), last wins; "
                      "nodes (and their values) resident in spatial-bucket order "
-                     "(ocsb_bucket_nodes, 64-px cells); e2e = H2D of mesh-order "
-                     "coordinates + bucketing + gather with scatter back to mesh "
-                     "order + D2H of the values")
+                     "(ocsb_bucket_nodes, 64-px cells); e2e = what Mesh.interpolate "
+                     "does: H2D of mesh-order coordinates + gather in mesh order "
+                     "+ D2H of the values")
     return out
 
 

@@ -175,17 +175,15 @@ class EuclideanMesh2D:
             xy = torch.from_numpy(np.ascontiguousarray(coords[k0:k1])).to(f"cuda:{dev}")
             vals = torch.from_numpy(np.ascontiguousarray(values[k0:k1])).to(f"cuda:{dev}")
             touched = torch.zeros(K, dtype=torch.uint8, device=f"cuda:{dev}")
-            perm = None
-            if method != "spline" and K >= self.BUCKET_MIN_NODES:
-                # spatial buckets: a warp's gathers then hit neighbouring texels
-                xy, perm = self.bucket_nodes(ctx, raster, xy, dev)
-            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev,
-                                perm=perm)
+            # one-shot call: gather in mesh order.  Bucketing the nodes first
+            # (bucket_nodes) only pays when coordinates AND values stay resident
+            # in bucket order over several interpolations: scattering the values
+            # back costs what the ordered gather saves (0.52 ms per 10 M nodes
+            # either way, profiles/r1h_interp_ncu_summary.txt) and the counting
+            # sort adds 0.9 ms
+            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev)
             values[k0:k1] = vals.cpu().numpy()
         self.meshdata.values = values.reshape((values.shape[0], 1))
-
-    #: below this many nodes the bucketing pass costs more than it saves
-    BUCKET_MIN_NODES = 200_000
 
     @staticmethod
     def bucket_nodes(ctx, rasters, xy, dev, cell_px: int = 64):
