@@ -42,7 +42,7 @@ extern "C" {
 #define OCSB_ENCCL      (-4)
 #define OCSB_EOVERFLOW  (-5)
 
-#define OCSB_ABI_VERSION 3
+#define OCSB_ABI_VERSION 4
 
 /* DEM element types (the hfun raster itself is always float32,
  * ocsmesh/hfun/raster.py:76) */
@@ -374,6 +374,28 @@ int32_t ocsb_hfun_pass(ocsb_ctx *ctx, const ocsb_win *win,
                        double dx, double dy, double ghmin, double ghmax,
                        const ocsb_hfun_op *ops, int32_t n_ops,
                        int32_t band_rows);
+
+/* One op of the list above on a LIST of semantic windows -- the window loops of
+ * HfunRaster.add_feature (ocsmesh/hfun/raster.py:1212-1260) and
+ * add_subtidal_flow_limiter (:1393-1436) over Raster.iter_windows
+ * (ocsmesh/raster.py:1577-1608) -- with every buffer resident on the device.
+ * Window k is wins[k]; its (virtual) row-0 / column-0 pixel lies dem_off[k]
+ * elements into `dem` and hfun_off[k] elements into hfun_old / hfun_new (which
+ * share one layout).  Windows are independent, so their launches are spread
+ * over internal worker streams and overlap; results are those of n_wins
+ * single-window calls.  hfun_old NULL = initial state.  Overlapping windows
+ * (overlap > 0) must be given distinct old / new buffers by the caller, as for
+ * the single-window calls, and in_order = 1: pixels shared by two windows are
+ * then written in list order (the later window wins, as in the reference's
+ * sequential loop) at the price of running the windows one after another.    */
+int32_t ocsb_hfun_op_windows(ocsb_ctx *ctx, const ocsb_win *wins,
+                             const int64_t *dem_off, const int64_t *hfun_off,
+                             int32_t n_wins,
+                             const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                             const float *hfun_old, int64_t old_stride,
+                             float *hfun_new, int64_t new_stride,
+                             double dx, double dy, double ghmin, double ghmax,
+                             const ocsb_hfun_op *op, int32_t in_order);
 
 /* ---- A12: pixel-wise min of co-registered hfun windows (build-defined) ---- */
 int32_t ocsb_min_combine(ocsb_ctx *ctx, float *dst, int64_t dst_stride,

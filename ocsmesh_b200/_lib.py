@@ -89,6 +89,10 @@ SIGNATURES = {
     "ocsb_hfun_pass": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                                c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64,
                                c_f64, C.POINTER(ocsb_hfun_op), c_i32, c_i32]),
+    "ocsb_hfun_op_windows": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_vp, c_i32,
+                                     c_vp, c_i32, c_i64, c_vp, c_i64, c_vp, c_i64,
+                                     c_f64, c_f64, c_f64, c_f64,
+                                     C.POINTER(ocsb_hfun_op), c_i32]),
     "ocsb_hfun_constant_value": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                          c_i64, c_vp, c_i64, c_vp, c_i64,
                                          c_f64, c_f64, c_f64, c_f64, c_f64,
@@ -315,10 +319,32 @@ class Context:
             float(dy), opt(hmin), opt(hmax), opt(lower_bound), opt(upper_bound),
             opt(ghmin), opt(ghmax), int(bool(fuse_clamp))))
 
+    def hfun_op_windows(self, wins, dem_off, hfun_off, dem, dem_dtype, dem_stride,
+                        hfun_old, old_stride, hfun_new, new_stride, dx, dy, ghmin,
+                        ghmax, op, in_order=False):
+        """One op tuple (see :meth:`hfun_pass`) on a list of windows of
+        device-resident buffers: ``wins`` an ``ocsb_win`` ctypes array,
+        ``dem_off`` / ``hfun_off`` int64 numpy arrays of element offsets."""
+        arr = self._op_array([op])
+        check(self.lib.ocsb_hfun_op_windows(
+            self.handle, wins, ptr(dem_off), ptr(hfun_off), len(wins), ptr(dem),
+            int(dem_dtype), int(dem_stride), ptr(hfun_old), int(old_stride),
+            ptr(hfun_new), int(new_stride), float(dx), float(dy), opt(ghmin),
+            opt(ghmax), arr, int(bool(in_order))))
+
     def hfun_pass(self, win, dem, dem_dtype, dem_stride, hfun_in, in_stride,
                   hfun_out, out_stride, dx, dy, ghmin, ghmax, ops, band_rows=0):
         """``ops``: list of ("feature", verts, nv, rate, target, fuse) /
         ("limiter", hmin, hmax, lower_bound, upper_bound, fuse) tuples."""
+        arr = self._op_array(ops)
+        check(self.lib.ocsb_hfun_pass(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(hfun_in), int(in_stride), ptr(hfun_out), int(out_stride),
+            float(dx), float(dy), opt(ghmin), opt(ghmax), arr, len(ops),
+            int(band_rows)))
+
+    @staticmethod
+    def _op_array(ops):
         arr = (ocsb_hfun_op * len(ops))()
         for o, t in zip(arr, ops):
             if t[0] == "feature":
@@ -334,11 +360,7 @@ class Context:
                 o.expansion_rate = o.target_size = NONE
                 o.hmin, o.hmax = opt(hmin), opt(hmax)
                 o.lower_bound, o.upper_bound = opt(lb), opt(ub)
-        check(self.lib.ocsb_hfun_pass(
-            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
-            ptr(hfun_in), int(in_stride), ptr(hfun_out), int(out_stride),
-            float(dx), float(dy), opt(ghmin), opt(ghmax), arr, len(ops),
-            int(band_rows)))
+        return arr
 
     def hfun_constant_value(self, win, dem, dem_dtype, dem_stride, old,
                             old_stride, new, new_stride, value, lower_bound,

@@ -178,6 +178,10 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
         cudaEventDestroy(r.b);
     }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
+    for (int i = 0; i < OCSB_WIN_STREAMS; ++i) {
+        if (ctx->s_win[i]) cudaStreamDestroy(ctx->s_win[i]);
+        if (ctx->ev_win[i]) cudaEventDestroy(ctx->ev_win[i]);
+    }
     if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
     if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
     for (int i = 0; i < OCSB_PASS_SETS; ++i) {
@@ -1438,4 +1442,130 @@ extern "C" int32_t ocsb_hfun_pass(
         }
     }
     return OCSB_OK;
+}
+
+
+// ---------------------------------------------------------------------------
+// One op over a LIST of semantic windows (the window loops of
+// hfun/raster.py:1212-1260 and :1393-1436), buffers resident on the device.
+// Windows are independent units of work (own coordinates, own search radius,
+// own one-sided borders), so they are spread over OCSB_WIN_STREAMS worker
+// streams: the small per-window launches (8 pyramid kernels + evaluation, or
+// one stencil launch) of different windows overlap instead of each running
+// alone on a fraction of the SMs.
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_hfun_op_windows(
+    ocsb_ctx *ctx, const ocsb_win *wins, const int64_t *dem_off,
+    const int64_t *hfun_off, int32_t n_wins, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, const float *hfun_old, int64_t old_stride,
+    float *hfun_new, int64_t new_stride, double dx, double dy, double ghmin,
+    double ghmax, const ocsb_hfun_op *op, int32_t in_order) {
+    CTX_ENTER("ocsb_hfun_op_windows");
+    OCSB_REQUIRE(n_wins >= 0, "ocsb_hfun_op_windows: negative window count");
+    if (n_wins == 0) return OCSB_OK;
+    OCSB_REQUIRE(wins && hfun_off && op && hfun_new,
+                 "ocsb_hfun_op_windows: NULL arguments");
+    OCSB_REQUIRE(op->kind == OCSB_OP_FEATURE || op->kind == OCSB_OP_LIMITER,
+                 "ocsb_hfun_op_windows: unknown op kind %d", op->kind);
+    OCSB_REQUIRE(ocsb_is_device_ptr(hfun_new) &&
+                     (!hfun_old || ocsb_is_device_ptr(hfun_old)),
+                 "ocsb_hfun_op_windows: the size raster must be device memory");
+    const bool lim = op->kind == OCSB_OP_LIMITER;
+    if (lim) {
+        OCSB_REQUIRE(dem && dem_off && ocsb_is_device_ptr(dem) &&
+                         (dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64),
+                     "ocsb_hfun_op_windows: a limiter op needs the device DEM");
+        OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
+                     "ocsb_hfun_op_windows: dx/dy is NaN");
+    } else {
+        OCSB_REQUIRE(op->verts_xy && op->nv > 0 && op->nv < (int64_t)2147483647,
+                     "ocsb_hfun_op_windows: bad vertex set");
+        OCSB_REQUIRE(!ocsb_is_none(op->target_size) && op->target_size > 0,
+                     "Argument target_size must be greater than zero.");
+        OCSB_REQUIRE(!ocsb_is_none(op->expansion_rate),
+                     "ocsb_hfun_op_windows: expansion_rate is NaN");
+        if (!ocsb_is_none(ghmax) && ghmax != 0.0)
+            OCSB_REQUIRE(op->expansion_rate * op->target_size != 0.0,
+                         "ocsb_hfun_op_windows: float division by zero "
+                         "(expansion_rate * target_size == 0 with hmax set)");
+    }
+    std::vector<int> rb(n_wins), re(n_wins);
+    for (int32_t k = 0; k < n_wins; ++k) {
+        OCSB_TRY(check_win(&wins[k], "ocsb_hfun_op_windows"));
+        OCSB_TRY(win_band(&wins[k], "ocsb_hfun_op_windows", &rb[k], &re[k]));
+        OCSB_REQUIRE(new_stride >= wins[k].width &&
+                         (!hfun_old || old_stride >= wins[k].width) &&
+                         (!lim || dem_stride >= wins[k].width),
+                     "ocsb_hfun_op_windows: window %d wider than a stride", k);
+        if (lim)
+            OCSB_REQUIRE(wins[k].width >= 2 && wins[k].height >= 2,
+                         "Shape of array too small to calculate a numerical gradient, "
+                         "at least (edge_order + 1) elements are required.");
+    }
+    // vertices: staged once on the context's stream, before the fork
+    Staged sv;
+    std::vector<const double *> verts(1, nullptr);
+    if (!lim) {
+        OCSB_TRY(sv.init(ctx, op->verts_xy, 1, op->nv * 2, op->nv * 2, 8, STAGE_IN));
+        verts[0] = (const double *)sv.dev;
+    }
+    // overlapping windows write shared pixels: list order must decide, as in
+    // the reference's sequential loop -> one worker stream
+    const int ns = in_order ? 1 : (n_wins < OCSB_WIN_STREAMS ? n_wins : OCSB_WIN_STREAMS);
+    for (int i = 0; i < ns; ++i) {
+        if (!ctx->s_win[i])
+            OCSB_CUDA(cudaStreamCreateWithFlags(&ctx->s_win[i], cudaStreamNonBlocking));
+        if (!ctx->ev_win[i])
+            OCSB_CUDA(cudaEventCreateWithFlags(&ctx->ev_win[i], cudaEventDisableTiming));
+    }
+    OCSB_TRY(pass_streams(ctx));     // ev_alloc doubles as the fork event
+    ScratchGuard sg(ctx);
+    int *flags = nullptr;
+    OCSB_TRY(sg.get(&flags, (size_t)n_wins));
+    OCSB_CUDA(cudaMemsetAsync(flags, 0, (size_t)n_wins * sizeof(int), ctx->stream));
+    OCSB_CUDA(cudaEventRecord(ctx->ev_alloc, ctx->stream));
+    for (int i = 0; i < ns; ++i)
+        OCSB_CUDA(cudaStreamWaitEvent(ctx->s_win[i], ctx->ev_alloc, 0));
+    const size_t es = dem_dtype == OCSB_F64 ? 8 : 4;
+    auto ptrs = [&](int32_t k, const void **zp, const float **ip, float **op_) {
+        *zp = lim ? (const void *)((const char *)dem + (size_t)dem_off[k] * es) : nullptr;
+        *ip = hfun_old ? hfun_old + hfun_off[k] : nullptr;
+        *op_ = hfun_new + hfun_off[k];
+    };
+    cudaStream_t main_stream = ctx->stream;
+    int32_t status = OCSB_OK;
+    for (int32_t k = 0; k < n_wins && status == OCSB_OK; ++k) {
+        const void *zp; const float *ip; float *opp;
+        ptrs(k, &zp, &ip, &opp);
+        ctx->stream = ctx->s_win[k % ns];        // everything below enqueues here
+        status = pass_ops(ctx, &wins[k], rb[k], re[k], zp, dem_dtype, dem_stride, ip,
+                          old_stride, opp, new_stride, dx, dy, ghmin, ghmax, op, 1,
+                          verts, flags + k);
+    }
+    ctx->stream = main_stream;
+    for (int i = 0; i < ns; ++i) {               // join
+        cudaEventRecord(ctx->ev_win[i], ctx->s_win[i]);
+        cudaStreamWaitEvent(ctx->stream, ctx->ev_win[i], 0);
+    }
+    if (status != OCSB_OK) {
+        cudaStreamSynchronize(ctx->stream);
+        return status;
+    }
+    if (!lim) {
+        // windows whose candidate pools overflowed left their pixels untouched:
+        // redo them through the synchronous, retrying path
+        std::vector<int> hflags((size_t)n_wins, 0);
+        OCSB_CUDA(cudaMemcpyAsync(hflags.data(), flags, hflags.size() * sizeof(int),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+        OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int32_t k = 0; k < n_wins; ++k) {
+            if (!hflags[k]) continue;
+            const void *zp; const float *ip; float *opp;
+            ptrs(k, &zp, &ip, &opp);
+            OCSB_TRY(pass_ops(ctx, &wins[k], rb[k], re[k], zp, dem_dtype, dem_stride,
+                              ip, old_stride, opp, new_stride, dx, dy, ghmin, ghmax,
+                              op, 1, verts, nullptr));
+        }
+    }
+    return finish_call(ctx, {&sv});
 }

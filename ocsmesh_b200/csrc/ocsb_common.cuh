@@ -62,6 +62,7 @@ struct KTimeRec {
     int kclass;
     cudaEvent_t a, b;
 };
+#define OCSB_WIN_STREAMS 8
 struct ocsb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -80,6 +81,9 @@ struct ocsb_ctx {
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
     cudaEvent_t ev_in[OCSB_PASS_SETS] = {}, ev_comp[OCSB_PASS_SETS] = {},
                 ev_out[OCSB_PASS_SETS] = {}, ev_alloc = nullptr;
+    // worker streams of ocsb_hfun_op_windows (created on first use)
+    cudaStream_t s_win[OCSB_WIN_STREAMS] = {};
+    cudaEvent_t ev_win[OCSB_WIN_STREAMS] = {};
     // one-time cudaFuncSetAttribute calls already made on this device
     unsigned func_attr_done = 0;
     // spline coefficient cache (one raster window)

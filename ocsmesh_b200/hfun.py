@@ -244,6 +244,32 @@ class HfunRaster:
         return t.data_ptr() + ((window.row_off - self._band[0]) * self.width
                                + window.col_off) * 4
 
+    def _window_batch(self, windows, dem_origin: Optional[int] = None):
+        """ctypes window array + element offsets of every window that
+        intersects the owned rows (arguments of ``ocsb_hfun_op_windows``);
+        cached: the window list of an object rarely changes."""
+        key = (tuple(windows), self._band, dem_origin)
+        hit = getattr(self, "_batch_cache", None)
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        recs = []
+        for win in windows:
+            band = self._band_of(win)
+            if band is None:
+                continue
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            zoff = 0 if dem_origin is None else \
+                (win.row_off - dem_origin) * self.width + win.col_off
+            hoff = (win.row_off - self._band[0]) * self.width + win.col_off
+            recs.append((cw, zoff, hoff))
+        wins = (_lib.ocsb_win * len(recs))(*[r[0] for r in recs])
+        dem_off = np.array([r[1] for r in recs], dtype=np.int64)
+        hfun_off = np.array([r[2] for r in recs], dtype=np.int64)
+        out = (wins, dem_off, hfun_off)
+        self._batch_cache = (key, out)
+        return out
+
     def _needs_double_buffer(self, windows) -> bool:
         return len(windows) > 1 and (self._overlap or 0) > 0
 
@@ -631,6 +657,19 @@ class HfunRaster:
         new = old
         if not self._pristine and self._needs_double_buffer(windows):
             new = old.clone()
+        if len(windows) > 1:
+            # the window loop as ONE library call: windows overlap on the
+            # library's worker streams (ocsb_hfun_op_windows)
+            wins, dem_off, hfun_off = self._window_batch(windows)
+            if len(wins):
+                ctx.hfun_op_windows(
+                    wins, None, hfun_off, None, _lib.OCSB_F32, w,
+                    None if self._pristine else old, w, new, w,
+                    self._raster.dx, self._raster.dy, self._hmin, self._hmax,
+                    ("feature", verts, nv, float(expansion_rate),
+                     float(target_size), fuse),
+                    in_order=(self._overlap or 0) > 0)
+            windows = []
         for win in windows:
             band = self._band_of(win)
             if band is None:
@@ -678,6 +717,21 @@ class HfunRaster:
         if not self._pristine and self._needs_double_buffer(windows):
             new = old.clone()
         dx, dy = self._raster.dx, self._raster.dy
+        if len(windows) > 1:
+            for win in windows:
+                if self._band_of(win) is not None and (win.width < 2 or win.height < 2):
+                    raise ValueError(
+                        "Shape of array too small to calculate a numerical "
+                        "gradient, at least (edge_order + 1) elements are required.")
+            wins, dem_off, hfun_off = self._window_batch(windows, dem_origin)
+            if len(wins):
+                ctx.hfun_op_windows(
+                    wins, dem_off, hfun_off, dem, code, w,
+                    None if self._pristine else old, w, new, w, dx, dy,
+                    self._hmin, self._hmax,
+                    ("limiter", hmin, hmax, lower_bound, upper_bound, fuse),
+                    in_order=(self._overlap or 0) > 0)
+            windows = []
         for win in windows:
             band = self._band_of(win)
             if band is None:

@@ -172,3 +172,25 @@ def test_config3_eight_rasters_min_combined(ctx):
     coll.min_combine_overlaps()
     for (r, c), h in zip(offs, coll.hfuns):
         np.testing.assert_array_equal(h.get_values(), G[r:r + th, c:c + tw])
+
+
+@pytest.mark.parametrize("chunk,overlap", [(128, 0), (300, 5)])
+def test_many_windows_one_library_call(ctx, chunk, overlap):
+    """The window loop of add_feature / add_subtidal_flow_limiter as one
+    ocsb_hfun_op_windows call (windows spread over the library's worker
+    streams; in list order when they overlap): 99 windows of a 1100 x 1300
+    raster against the oracle's sequential window loop, every pixel."""
+    gr, orr = both(1100, 1300, 3, chunk, overlap)
+    nwin = len(list(gr.iter_windows()))
+    assert nwin >= 16
+    hf = ob.Hfun(gr, hmin=100, hmax=1500)
+    oh = O.OracleHfun(orr, hmin=100, hmax=1500)
+    lines = gr.get_contour(0)
+    for _ in range(2):          # pristine first op, then a read-modify-write op
+        hf.add_feature(lines, 0.001, 100)
+        oh.add_feature(lines, 0.001, 100)
+        np.testing.assert_array_equal(hf.get_values(), oh.values)
+        lines = gr.get_contour(5)
+    hf.add_subtidal_flow_limiter(hmin=50, hmax=1500, lower_bound=-30, upper_bound=0)
+    oh.add_subtidal_flow_limiter(50, 1500, -30, 0)
+    np.testing.assert_array_equal(hf.get_values(), oh.values)
