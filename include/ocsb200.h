@@ -268,7 +268,8 @@ int32_t ocsb_hfun_constant_value(ocsb_ctx *ctx, const ocsb_win *win,
  *            by the caller; values_dtype OCSB_F32 / OCSB_F64)
  * hfun     : read-modify-written in place (the global [hmin, hmax] clamp of
  *            apply_constraints is a separate ocsb_hfun_clamp call)
- * A rate needs the whole window on one device (row_begin/row_end unset).      */
+ * A rate needs the whole window on one device (row_begin/row_end unset); for a
+ * row band use ocsb_hfun_topo_mask_band + ocsb_hfun_apply_rate below.           */
 #define OCSB_VT_MIN 0
 #define OCSB_VT_MAX 1
 int32_t ocsb_hfun_topo_constraint(ocsb_ctx *ctx, const ocsb_win *win,
@@ -279,6 +280,40 @@ int32_t ocsb_hfun_topo_constraint(ocsb_ctx *ctx, const ocsb_win *win,
                                   int64_t values_stride, double value,
                                   double lower_bound, double upper_bound,
                                   int32_t value_type, double rate);
+
+/* The same constraint WITH a rate when the window is split into row bands over
+ * several devices: the nearest mask pixel of a band pixel may lie in another
+ * band, so the call is split around an exchange of mask-boundary pixels.
+ *   1. ocsb_hfun_topo_mask_band on every band: applies the mask step to the band
+ *      (hfun[mask] = val), writes the band's mask (device, (row_end-row_begin) x
+ *      width, compact) and returns the band's mask-boundary pixels as vertices
+ *      (window coordinates, row-major) with their values.  Mask pixels on a band
+ *      edge that is not a window edge count as boundary (their outer neighbour
+ *      is unknown) -- a superset that cannot change a nearest-pixel answer.
+ *      verts_out / vals_out NULL: count only (*n_out); cap < *n_out:
+ *      OCSB_EOVERFLOW.  The call is idempotent.
+ *   2. the caller concatenates all bands' vertices and values in band order
+ *      (an all-gather over ranks, ocsmesh_b200.distributed.all_gather_ragged)
+ *   3. ocsb_hfun_apply_rate on every band with the full vertex set: the
+ *      _apply_rate step (ocsmesh/features/constraint.py:99-117) for the band's
+ *      non-mask pixels.  nv == 0 (no mask pixel anywhere): no-op
+ *      (`if not np.any(mask): return values`, :87-88).
+ * hfun: (virtual) address of window row 0, device memory in step 3.             */
+int32_t ocsb_hfun_topo_mask_band(ocsb_ctx *ctx, const ocsb_win *win,
+                                 const void *dem, int32_t dem_dtype,
+                                 int64_t dem_stride,
+                                 float *hfun, int64_t hfun_stride,
+                                 const void *values, int32_t values_dtype,
+                                 int64_t values_stride, double value,
+                                 double lower_bound, double upper_bound,
+                                 int32_t value_type, uint8_t *mask_out,
+                                 double *verts_out, float *vals_out, int64_t cap,
+                                 int64_t *n_out);
+int32_t ocsb_hfun_apply_rate(ocsb_ctx *ctx, const ocsb_win *win,
+                             float *hfun, int64_t hfun_stride,
+                             const uint8_t *mask, const double *verts_xy,
+                             const float *vert_values, int64_t nv, double rate,
+                             int32_t value_type);
 
 /* CourantNumConstraint.apply                               ocsmesh/features/constraint.py:254-313
  * (utils.py:1677-1835: linear-wave particle velocity, characteristic

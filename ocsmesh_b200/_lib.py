@@ -100,6 +100,12 @@ SIGNATURES = {
     "ocsb_hfun_topo_constraint": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                           c_i64, c_vp, c_i64, c_vp, c_i32, c_i64,
                                           c_f64, c_f64, c_f64, c_i32, c_f64]),
+    "ocsb_hfun_topo_mask_band": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
+                                         c_i64, c_vp, c_i64, c_vp, c_i32, c_i64,
+                                         c_f64, c_f64, c_f64, c_i32, c_vp, c_vp,
+                                         c_vp, c_i64, C.POINTER(c_i64)]),
+    "ocsb_hfun_apply_rate": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64, c_vp,
+                                     c_vp, c_vp, c_i64, c_f64, c_i32]),
     "ocsb_hfun_courant_constraint": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp,
                                              c_i32, c_i64, c_vp, c_i64, c_f64,
                                              c_f64, c_f64, c_i32]),
@@ -380,6 +386,27 @@ class Context:
             ptr(hfun), int(hfun_stride), ptr(values), int(values_dtype),
             int(values_stride), opt(value), float(lower_bound),
             float(upper_bound), int(value_type), opt(rate)))
+
+    def hfun_topo_mask_band(self, win, dem, dem_dtype, dem_stride, hfun,
+                            hfun_stride, values, values_dtype, values_stride,
+                            value, lower_bound, upper_bound, value_type, mask_out,
+                            verts_out=None, vals_out=None, cap=0) -> int:
+        """Step 1 of a rate constraint on a row band; returns the number of
+        mask-boundary pixels of the band."""
+        n = c_i64(0)
+        check(self.lib.ocsb_hfun_topo_mask_band(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            ptr(hfun), int(hfun_stride), ptr(values), int(values_dtype),
+            int(values_stride), opt(value), float(lower_bound),
+            float(upper_bound), int(value_type), ptr(mask_out), ptr(verts_out),
+            ptr(vals_out), int(cap), C.byref(n)))
+        return n.value
+
+    def hfun_apply_rate(self, win, hfun, hfun_stride, mask, verts, vals, nv, rate,
+                        value_type):
+        check(self.lib.ocsb_hfun_apply_rate(
+            self.handle, C.byref(win), ptr(hfun), int(hfun_stride), ptr(mask),
+            ptr(verts), ptr(vals), int(nv), float(rate), int(value_type)))
 
     def hfun_courant_constraint(self, win, dem, dem_dtype, dem_stride, hfun,
                                 hfun_stride, courant, timestep, wave_amplitude,

@@ -66,10 +66,43 @@ class Constraint:
             "constraints run on the device through HfunRaster."
             "apply_constraints; ocsmesh_b200 has no host implementation")
 
+    # ---- a rate on a row band of the window (multi-GPU) ----------------------
+    def _apply_rate_band(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                         hfun_stride, values, values_code, values_stride, value,
+                         device, gather):
+        """``ocsb_hfun_topo_mask_band`` on this band, ``gather`` of every band's
+        mask-boundary pixels (rank order = row order), ``ocsb_hfun_apply_rate``
+        on this band: bit-identical to the whole window on one device."""
+        import torch
+        rb = cwin.row_begin
+        re = cwin.row_end if cwin.row_end > 0 else cwin.height
+        mask = torch.empty((re - rb, cwin.width), dtype=torch.uint8, device=device)
+        args = (cwin, dem, dem_code, dem_stride, hfun, hfun_stride, values,
+                values_code, values_stride, value, float(self._lb), float(self._ub),
+                self._vt_code, mask)
+        n = ctx.hfun_topo_mask_band(*args)
+        verts = torch.empty((n, 2), dtype=torch.float64, device=device)
+        vals = torch.empty((n,), dtype=torch.float32, device=device)
+        if n:
+            ctx.hfun_topo_mask_band(*args, verts, vals, n)
+        verts, vals = gather(verts), gather(vals)
+        ctx.hfun_apply_rate(cwin, hfun, hfun_stride, mask, verts, vals,
+                            int(verts.shape[0]), float(self._rate), self._vt_code)
+        ctx.sync()      # mask / verts / vals are freed on return
+
+    def _join_rate_band(self, device, gather) -> None:
+        """A rank that owns no row of a window still takes part in the two
+        gathers of :meth:`_apply_rate_band` (with nothing to contribute)."""
+        import torch
+        if self._rate is None:
+            return
+        gather(torch.empty((0, 2), dtype=torch.float64, device=device))
+        gather(torch.empty((0,), dtype=torch.float32, device=device))
+
     # one (semantic window, device tile) of an HfunRaster; ``dem`` / ``hfun``
     # are (address of the window's top-left pixel, row stride in elements)
     def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
-                      hfun_stride, dem_view):
+                      hfun_stride, dem_view, gather=None):
         raise NotImplementedError
 
 
@@ -95,7 +128,12 @@ class TopoConstConstraint(Constraint):
         return self._lb, self._ub
 
     def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
-                      hfun_stride, dem_view):
+                      hfun_stride, dem_view, gather=None):
+        if self._rate is not None and gather is not None:
+            self._apply_rate_band(ctx, cwin, dem, dem_code, dem_stride, hfun,
+                                  hfun_stride, None, _lib.OCSB_F32, 0,
+                                  float(self._val), dem_view.device, gather)
+            return
         ctx.hfun_topo_constraint(
             cwin, dem, dem_code, dem_stride, hfun, hfun_stride, None,
             _lib.OCSB_F32, 0, float(self._val), float(self._lb),
@@ -138,13 +176,18 @@ class TopoFuncConstraint(Constraint):
         return vals.contiguous()
 
     def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
-                      hfun_stride, dem_view):
+                      hfun_stride, dem_view, gather=None):
         import torch
         vals = self._values(dem_view)
         code = _lib.OCSB_F32 if vals.dtype == torch.float32 else _lib.OCSB_F64
         # `vals` covers the device tile only; the ABI wants window row 0
         rb = cwin.row_begin
         base = vals.data_ptr() - rb * vals.shape[1] * vals.element_size()
+        if self._rate is not None and gather is not None:
+            self._apply_rate_band(ctx, cwin, dem, dem_code, dem_stride, hfun,
+                                  hfun_stride, base, code, vals.shape[1], None,
+                                  dem_view.device, gather)
+            return
         ctx.hfun_topo_constraint(
             cwin, dem, dem_code, dem_stride, hfun, hfun_stride, base, code,
             vals.shape[1], None, float(self._lb), float(self._ub),
@@ -163,7 +206,7 @@ class CourantNumConstraint(Constraint):
         self._nu = wave_amplitude
 
     def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
-                      hfun_stride, dem_view):
+                      hfun_stride, dem_view, gather=None):
         ctx.hfun_courant_constraint(
             cwin, dem, dem_code, dem_stride, hfun, hfun_stride,
             float(self._value), float(self._dt), float(self._nu),

@@ -219,10 +219,15 @@ constexpr int kCompPx = 1024;        // = 1024 consecutive pixels of ONE row,
                                      // CTAs in row-major order (so is the output)
 
 // boundary flags (bit k = pixel col + k) of 4 consecutive pixels of one row
+// open_top / open_bot: the rows beyond the first / last row belong to another
+// rank's band (unknown here), so mask pixels on that edge count as boundary --
+// a superset of the true boundary, which cannot change a nearest-pixel answer
 __device__ __forceinline__ unsigned boundary4(const uint8_t *__restrict__ mask, int w,
-                                              int h, int row, int col, bool vec) {
+                                              int h, int row, int col, bool vec,
+                                              int open_top, int open_bot) {
     const uint8_t *p = mask + (int64_t)row * w + col;
-    unsigned c = 0, up = 0xf, dn = 0xf;      // bit k: pixel is a mask pixel
+    unsigned c = 0;                          // bit k: pixel is a mask pixel
+    unsigned up = open_top ? 0u : 0xfu, dn = open_bot ? 0u : 0xfu;
     if (vec && col + 4 <= w) {
         const uchar4 m = *reinterpret_cast<const uchar4 *>(p);
         c = (m.x ? 1u : 0u) | (m.y ? 2u : 0u) | (m.z ? 4u : 0u) | (m.w ? 8u : 0u);
@@ -239,8 +244,8 @@ __device__ __forceinline__ unsigned boundary4(const uint8_t *__restrict__ mask, 
         up = dn = 0u;
         for (int k = 0; k < 4 && col + k < w; ++k) {
             c |= (p[k] ? 1u : 0u) << k;
-            up |= ((row > 0) ? (p[k - w] ? 1u : 0u) : 1u) << k;
-            dn |= ((row + 1 < h) ? (p[k + w] ? 1u : 0u) : 1u) << k;
+            up |= ((row > 0) ? (p[k - w] ? 1u : 0u) : (open_top ? 0u : 1u)) << k;
+            dn |= ((row + 1 < h) ? (p[k + w] ? 1u : 0u) : (open_bot ? 0u : 1u)) << k;
         }
         if (!c) return 0u;
     }
@@ -257,12 +262,12 @@ __device__ __forceinline__ unsigned boundary4(const uint8_t *__restrict__ mask, 
 
 __global__ void __launch_bounds__(kCompThreads)
 boundary_count_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
-                      int vec, int *__restrict__ counts) {
+                      int vec, int open_top, int open_bot, int *__restrict__ counts) {
     __shared__ int s_warp[kCompThreads / 32];
     const int row = blockIdx.x / nbx;
     const int col = (blockIdx.x - row * nbx) * kCompPx + threadIdx.x * 4;
     int n = 0;
-    if (col < w) n = __popc(boundary4(mask, w, h, row, col, vec != 0));
+    if (col < w) n = __popc(boundary4(mask, w, h, row, col, vec != 0, open_top, open_bot));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
     if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = n;
@@ -277,6 +282,7 @@ boundary_count_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx,
 
 __global__ void __launch_bounds__(kCompThreads)
 boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx, int vec,
+                     int open_top, int open_bot, int row0,
                      const int *__restrict__ offsets, LinAxis ax, LinAxis ay,
                      const float *__restrict__ hfun, int64_t hs,
                      double2 *__restrict__ verts, float *__restrict__ vals) {
@@ -284,7 +290,7 @@ boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx, in
     const int row = blockIdx.x / nbx;
     const int col = (blockIdx.x - row * nbx) * kCompPx + threadIdx.x * 4;
     unsigned f = 0;
-    if (col < w) f = boundary4(mask, w, h, row, col, vec != 0);
+    if (col < w) f = boundary4(mask, w, h, row, col, vec != 0, open_top, open_bot);
     const int n = __popc(f);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int x = n;
@@ -298,7 +304,7 @@ boundary_emit_kernel(const uint8_t *__restrict__ mask, int w, int h, int nbx, in
     if (!f) return;
     int pos = offsets[blockIdx.x] + (x - n);
     for (int k = 0; k < wid; ++k) pos += s_warp[k];
-    const double y = lin_at(ay, row);
+    const double y = lin_at(ay, row0 + row);     // window row of band row `row`
 #pragma unroll
     for (int k = 0; k < 4; ++k)
         if ((f >> k) & 1u) {
@@ -388,12 +394,13 @@ int32_t k_courant(ocsb_ctx *ctx, int w, int h, const void *dem, int dem_dtype,
     return OCSB_OK;
 }
 
-// boundary pixels of `mask` (h x w, compact) -> verts[*nv], vals[*nv]
-// (stream-ordered scratch owned by `sg`); synchronises once for the count
+// boundary pixels of `mask` (h x w, compact; its row 0 is window row `row0`,
+// hfun points at that row too) -> verts[*nv], vals[*nv] (stream-ordered scratch
+// owned by `sg`); synchronises once for the count
 int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
                         int w, int h, LinAxis ax, LinAxis ay, const float *hfun,
                         int64_t hs, double **verts_out, float **vals_out,
-                        int64_t *nv_out) {
+                        int64_t *nv_out, int row0, int open_top, int open_bot) {
     const int nbx = (w + kCompPx - 1) / kCompPx;
     const int64_t nblk = (int64_t)nbx * h;
     const int vec = (((uintptr_t)mask & 3) == 0 && (w & 3) == 0) ? 1 : 0;
@@ -404,7 +411,8 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
     OCSB_TRY(sg.get(&sums, (size_t)((nblk + 1023) / 1024)));
     OCSB_TRY(sg.get(&total, 1));
     OCSB_TIME(ctx, KC_CONSTRAINT);
-    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(mask, w, h, nbx, vec, counts);
+    boundary_count_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(
+        mask, w, h, nbx, vec, open_top, open_bot, counts);
     OCSB_LAUNCHED(ctx);
     OCSB_TIME(ctx, KC_CONSTRAINT);
     scan_counts(counts, nblk, sums, total, ctx->stream);
@@ -429,7 +437,8 @@ int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
     OCSB_TRY(sg.get(&vals, (size_t)host_total));
     OCSB_TIME(ctx, KC_CONSTRAINT);
     boundary_emit_kernel<<<(unsigned)nblk, kCompThreads, 0, ctx->stream>>>(
-        mask, w, h, nbx, vec, counts, ax, ay, hfun, hs, verts, vals);
+        mask, w, h, nbx, vec, open_top, open_bot, row0, counts, ax, ay, hfun, hs, verts,
+        vals);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     *verts_out = reinterpret_cast<double *>(verts);

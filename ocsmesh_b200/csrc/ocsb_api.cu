@@ -709,6 +709,125 @@ extern "C" int32_t ocsb_hfun_topo_constraint(
     return finish_call(ctx, {&sz, &sh, &sv});
 }
 
+// ---- the same constraint with a rate on a ROW BAND of the window (one rank of
+// a multi-GPU run): the nearest mask pixel of a band pixel may live in another
+// rank's band, so the call is split around an all-gather of the ranks'
+// mask-boundary pixels (ocsmesh_b200/distributed.py:all_gather_vertices) -----
+extern "C" int32_t ocsb_hfun_topo_mask_band(
+    ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
+    int64_t dem_stride, float *hfun, int64_t hfun_stride, const void *values,
+    int32_t values_dtype, int64_t values_stride, double value,
+    double lower_bound, double upper_bound, int32_t value_type,
+    uint8_t *mask_out, double *verts_out, float *vals_out, int64_t cap,
+    int64_t *n_out) {
+    CTX_ENTER("ocsb_hfun_topo_mask_band");
+    OCSB_TRY(check_win(win, "ocsb_hfun_topo_mask_band"));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "ocsb_hfun_topo_mask_band: unsupported DEM dtype %d", dem_dtype);
+    OCSB_REQUIRE(value_type == OCSB_VT_MIN || value_type == OCSB_VT_MAX,
+                 "Invalid value type for constraint!");
+    OCSB_REQUIRE(dem && hfun && mask_out && n_out && dem_stride >= win->width &&
+                     hfun_stride >= win->width && cap >= 0,
+                 "ocsb_hfun_topo_mask_band: bad buffers");
+    OCSB_REQUIRE(!values || ((values_dtype == OCSB_F32 || values_dtype == OCSB_F64) &&
+                             values_stride >= win->width),
+                 "ocsb_hfun_topo_mask_band: bad values array");
+    OCSB_REQUIRE(values || !ocsb_is_none(value),
+                 "ocsb_hfun_topo_mask_band: value is NaN");
+    OCSB_REQUIRE(!ocsb_is_none(lower_bound) && !ocsb_is_none(upper_bound),
+                 "ocsb_hfun_topo_mask_band: NaN bound");
+    OCSB_REQUIRE(ocsb_is_device_ptr(mask_out),
+                 "ocsb_hfun_topo_mask_band: mask_out must be device memory");
+    const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_topo_mask_band", &rb, &re));
+    const int hb = re - rb;
+    const size_t es = dem_dtype == OCSB_F32 ? 4 : 8;
+    const size_t vs = values_dtype == OCSB_F64 ? 8 : 4;
+    Staged sz, sh, sv;
+    OCSB_TRY(sz.init(ctx, dem, hb, w, dem_stride, es, STAGE_IN, rb));
+    OCSB_TRY(sh.init(ctx, hfun, hb, w, hfun_stride, 4, STAGE_INOUT, rb));
+    if (values)
+        OCSB_TRY(sv.init(ctx, values, hb, w, values_stride, vs, STAGE_IN, rb));
+    const int is_min = value_type == OCSB_VT_MIN;
+    float *hb_ptr = (float *)row_ptr(sh.dev, rb, sh.dev_stride, 4);
+    // idempotent: pixels set to `val` fail satisfies(val, val) again, so the
+    // count call and the emit call produce the same mask
+    OCSB_TRY(k_topo_mask(ctx, w, hb, row_ptr(sz.dev, rb, sz.dev_stride, es),
+                         dem_dtype, sz.dev_stride, hb_ptr, sh.dev_stride,
+                         row_ptr(sv.dev, rb, sv.dev_stride, vs), values_dtype,
+                         sv.dev_stride, value, lower_bound, upper_bound, is_min,
+                         mask_out, nullptr));
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    ScratchGuard sg(ctx);
+    double *verts = nullptr;
+    float *vals = nullptr;
+    int64_t nvb = 0;
+    OCSB_TRY(k_mask_boundary(ctx, sg, mask_out, w, hb, ax, ay, hb_ptr, sh.dev_stride,
+                             &verts, &vals, &nvb, rb, rb > 0, re < h));
+    *n_out = nvb;
+    if (verts_out && vals_out && nvb > 0) {
+        if (nvb > cap) {
+            OCSB_TRY(finish_call(ctx, {&sz, &sh, &sv}));
+            ocsb_set_error("ocsb_hfun_topo_mask_band: %lld boundary pixels, "
+                           "capacity %lld", (long long)nvb, (long long)cap);
+            return OCSB_EOVERFLOW;
+        }
+        const cudaMemcpyKind kv = ocsb_is_device_ptr(verts_out)
+                                      ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+        const cudaMemcpyKind kl = ocsb_is_device_ptr(vals_out)
+                                      ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+        OCSB_CUDA(cudaMemcpyAsync(verts_out, verts, (size_t)nvb * 16, kv, ctx->stream));
+        OCSB_CUDA(cudaMemcpyAsync(vals_out, vals, (size_t)nvb * 4, kl, ctx->stream));
+        OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return finish_call(ctx, {&sz, &sh, &sv});
+}
+
+extern "C" int32_t ocsb_hfun_apply_rate(
+    ocsb_ctx *ctx, const ocsb_win *win, float *hfun, int64_t hfun_stride,
+    const uint8_t *mask, const double *verts_xy, const float *vert_values,
+    int64_t nv, double rate, int32_t value_type) {
+    CTX_ENTER("ocsb_hfun_apply_rate");
+    OCSB_TRY(check_win(win, "ocsb_hfun_apply_rate"));
+    OCSB_REQUIRE(value_type == OCSB_VT_MIN || value_type == OCSB_VT_MAX,
+                 "Invalid value type for constraint!");
+    OCSB_REQUIRE(nv >= 0 && nv < (int64_t)2147483647, "ocsb_hfun_apply_rate: bad nv");
+    // `if not np.any(mask): return values` (constraint.py:87-88)
+    if (nv == 0) return OCSB_OK;
+    OCSB_REQUIRE(hfun && mask && verts_xy && vert_values &&
+                     hfun_stride >= win->width && !ocsb_is_none(rate),
+                 "ocsb_hfun_apply_rate: bad arguments");
+    OCSB_REQUIRE(ocsb_is_device_ptr(mask) && ocsb_is_device_ptr(hfun),
+                 "ocsb_hfun_apply_rate: hfun and mask must be device memory");
+    const int w = win->width;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_hfun_apply_rate", &rb, &re));
+    Staged sv, sl;
+    OCSB_TRY(sv.init(ctx, verts_xy, 1, nv * 2, nv * 2, 8, STAGE_IN));
+    OCSB_TRY(sl.init(ctx, vert_values, 1, nv, nv, 4, STAGE_IN));
+    const int is_min = value_type == OCSB_VT_MIN;
+    FeatureArgs fa;
+    win_axes(win, &fa.ax, &fa.ay);
+    fa.rate_target = 0.0; fa.target = 1.0;
+    fa.has_hmin = fa.has_hmax = 0;
+    fa.hmin_f = fa.hmax_f = 0.f;
+    fa.fuse_clamp = 0;
+    fa.r = std::numeric_limits<double>::infinity();
+    fa.row_begin = rb; fa.row_end = re;
+    fa.rate_vals = (const float *)sl.dev;
+    // both indexed by WINDOW row: hand over the (virtual) row-0 addresses
+    fa.rate_mask = mask - (int64_t)rb * w;
+    fa.rate = rate;
+    fa.rate_sign = is_min ? -1.0 : 1.0;
+    fa.rate_is_min = is_min;
+    // hfun is the caller's (virtual) window-row-0 pointer already
+    OCSB_TRY(k_hfun_feature(ctx, fa, (const double *)sv.dev, nv, hfun, hfun_stride,
+                            hfun, hfun_stride, nullptr, nullptr));
+    return finish_call(ctx, {&sv, &sl});
+}
+
 extern "C" int32_t ocsb_hfun_courant_constraint(
     ocsb_ctx *ctx, const ocsb_win *win, const void *dem, int32_t dem_dtype,
     int64_t dem_stride, float *hfun, int64_t hfun_stride, double courant,

@@ -308,7 +308,8 @@ int32_t k_courant(ocsb_ctx *ctx, int w, int h, const void *dem, int dem_dtype,
 int32_t k_mask_boundary(ocsb_ctx *ctx, ScratchGuard &sg, const uint8_t *mask,
                         int w, int h, LinAxis ax, LinAxis ay, const float *hfun,
                         int64_t hs, double **verts_out, float **vals_out,
-                        int64_t *nv_out);
+                        int64_t *nv_out, int row0 = 0, int open_top = 0,
+                        int open_bot = 0);
 
 int32_t k_interp(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const void *dem,
                  int dem_dtype, int64_t dem_stride, const uint8_t *mask,

@@ -117,28 +117,35 @@ def exchange_dem_halo(raster, part: RowBands, rank: int, device: Optional[int] =
                        raster.device_band_origin(band, device), part, rank, group)
 
 
-def all_gather_vertices(verts_local, group=None):
-    """All ranks' ``(n_i, 2)`` float64 vertex arrays concatenated in rank
-    order -> ``(sum n_i, 2)`` on every rank (the contour-vertex all-gather).
-    Ragged sizes are handled by padding to the maximum."""
+def all_gather_ragged(local, group=None):
+    """All ranks' ``(n_i, ...)`` tensors (same dtype and trailing shape, any
+    ``n_i`` including 0) concatenated in rank order on every rank.  Ragged
+    sizes are handled by padding to the maximum."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
     if world == 1:
-        return verts_local
-    n = torch.tensor([verts_local.shape[0]], dtype=torch.int64,
-                     device=verts_local.device)
-    sizes = torch.empty(world, dtype=torch.int64, device=verts_local.device)
+        return local
+    n = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
+    sizes = torch.empty(world, dtype=torch.int64, device=local.device)
     dist.all_gather_into_tensor(sizes, n, group=group)
     sizes_h = sizes.tolist()
     m = max(sizes_h)
-    pad = torch.zeros((m, 2), dtype=verts_local.dtype, device=verts_local.device)
-    pad[:verts_local.shape[0]] = verts_local
-    out = torch.empty((world * m, 2), dtype=verts_local.dtype,
-                      device=verts_local.device)
+    tail = tuple(local.shape[1:])
+    if m == 0:
+        return local.new_empty((0,) + tail)
+    pad = torch.zeros((m,) + tail, dtype=local.dtype, device=local.device)
+    pad[:local.shape[0]] = local
+    out = torch.empty((world * m,) + tail, dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(out, pad, group=group)
     parts = [out[r * m:r * m + sizes_h[r]] for r in range(world)]
     return torch.cat(parts, dim=0).contiguous()
+
+
+def all_gather_vertices(verts_local, group=None):
+    """All ranks' ``(n_i, 2)`` float64 vertex arrays concatenated in rank
+    order -> ``(sum n_i, 2)`` on every rank (the contour-vertex all-gather)."""
+    return all_gather_ragged(verts_local, group)
 
 
 def min_combine_strip(strip, group=None):

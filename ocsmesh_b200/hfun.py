@@ -448,9 +448,15 @@ class HfunRaster:
         if self._needs_double_buffer(windows):
             # every window reads the PRE-pass raster, the later window wins
             new = old.clone()
+        gather = self._rate_gather()
         for win in windows:
             band = self._band_of(win)
             if band is None:
+                # no row of this window here: still join the other ranks'
+                # exchange of mask-boundary pixels (rate constraints)
+                if gather is not None:
+                    for c in constraint_list:
+                        c._join_rate_band(f"cuda:{self._device}", gather)
                 continue
             r0 = win.row_off + band[0] - rb
             r1 = win.row_off + band[1] - rb
@@ -464,12 +470,28 @@ class HfunRaster:
             dem_view = dem[d0:d0 + (band[1] - band[0]), cs]
             for c in constraint_list:
                 c._apply_device(ctx, cw, dem.data_ptr() + poff * es, code, w,
-                                self._hfun_ptr(new, win), w, dem_view)
+                                self._hfun_ptr(new, win), w, dem_view, gather=gather)
             if self._hmin is not None or self._hmax is not None:
                 ctx.hfun_clamp(self._hfun_ptr(new, win) + band[0] * w * 4, w,
                                win.width, band[1] - band[0], self._hmin,
                                self._hmax)
         self._hfun = new
+
+    def _rate_gather(self):
+        """Row-band object inside a multi-rank run: the all-gather a rate
+        constraint needs (every rank must run the same constraint list);
+        None for an object that holds whole windows."""
+        if self._band == (0, self.height):
+            return None
+        try:
+            import torch.distributed as dist
+        except ImportError:       # pragma: no cover
+            return None
+        if not (dist.is_available() and dist.is_initialized()) or \
+                dist.get_world_size() == 1:
+            return None
+        from . import distributed as _dist
+        return _dist.all_gather_ragged
 
     def _fuse_clamp(self) -> bool:
         """The decorator's clamp re-pass is folded into the op's own kernel

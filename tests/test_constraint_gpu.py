@@ -227,3 +227,50 @@ def test_golden_constraints(ctx):
                 hf.add_subtidal_flow_limiter(30.0, 900.0, None, None)
                 np.testing.assert_array_equal(
                     hf.get_values(), gold[f"{name}_topo_min_rate_then_limiter"])
+
+
+# ---- a rate constraint on row bands (multi-GPU split of one window) -----------
+@pytest.mark.parametrize("value_type,value", [("min", 400.0), ("max", 90.0)])
+@pytest.mark.parametrize("cuts", [(0, 165, 330), (0, 97, 98, 250, 330)])
+def test_rate_on_row_bands_equals_whole_window(ctx, value_type, value, cuts):
+    """ocsb_hfun_topo_mask_band on every band, the bands' mask-boundary pixels
+    concatenated in band order (what the ranks all-gather), ocsb_hfun_apply_rate
+    on every band == ocsb_hfun_topo_constraint on the whole window, bit for bit
+    (the nearest mask pixel of a band pixel often lies in another band)."""
+    import torch
+    gr, orr = both(330, 290, 8)
+    hf, _ = seeded(gr, orr)
+    H, W = gr.height, gr.width
+    base = hf.device_values.clone()
+    dem = gr.device_band(1, 0)
+    bounds = gr.get_window_bounds(ob.Window(0, 0, W, H))
+    vt = _lib.VT_MIN if value_type == "min" else _lib.VT_MAX
+    lb, ub, rate = -8.0, 3.0, 0.02
+    want = base.clone()
+    ctx.hfun_topo_constraint(_lib.make_win(bounds, W, H), dem, _lib.OCSB_F32, W,
+                             want, W, None, _lib.OCSB_F32, 0, value, lb, ub, vt, rate)
+    got = base.clone()
+    wins, masks, verts, vals = [], [], [], []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        cw = _lib.make_win(bounds, W, H, a, b)
+        mask = torch.empty((b - a, W), dtype=torch.uint8, device="cuda")
+        args = (cw, dem, _lib.OCSB_F32, W, got, W, None, _lib.OCSB_F32, 0, value,
+                lb, ub, vt, mask)
+        n = ctx.hfun_topo_mask_band(*args)
+        v = torch.empty((n, 2), dtype=torch.float64, device="cuda")
+        l = torch.empty((n,), dtype=torch.float32, device="cuda")
+        if n:
+            assert ctx.hfun_topo_mask_band(*args, v, l, n) == n
+            with pytest.raises(_lib.OcsbError):      # capacity protocol
+                ctx.hfun_topo_mask_band(*args, v, l, n - 1)
+        wins.append(cw); masks.append(mask); verts.append(v); vals.append(l)
+    allv, alll = torch.cat(verts), torch.cat(vals)
+    assert len(allv) > 100
+    for cw, mask in zip(wins, masks):
+        ctx.hfun_apply_rate(cw, got, W, mask, allv, alll, len(allv), rate, vt)
+    ctx.sync()
+    assert torch.equal(got, want)
+    assert not torch.equal(got, base)
+    # no mask pixel anywhere: nothing happens (constraint.py:87-88)
+    ctx.hfun_apply_rate(wins[0], got, W, masks[0], allv[:0], alll[:0], 0, rate, vt)
+    assert torch.equal(got, want)

@@ -224,3 +224,25 @@ def test_overlap_windows_geometry():
     bad = (tuple(np.array(g[1][0]) + [0, 0, 3.0, 0, 0, 0]), 50, 40)
     with pytest.raises(ValueError, match="co-registered"):
         overlap_windows(g[0], bad)
+
+
+def _ragged_case(rank, world):
+    # rank r contributes r values (rank 0: none) and (2 r + 1, 2) vertices
+    vals = torch.arange(rank, dtype=torch.float32) + 10.0 * rank
+    verts = torch.full((2 * rank + 1, 2), float(rank), dtype=torch.float64)
+    none = torch.empty((0, 2), dtype=torch.float64)
+    return (D.all_gather_ragged(vals).numpy(), D.all_gather_ragged(verts).numpy(),
+            D.all_gather_ragged(none).numpy())
+
+
+def test_all_gather_ragged_any_rank_and_empty_contributions():
+    """The exchange behind a rate constraint on row bands: 1-D values and (n, 2)
+    vertices, ranks with nothing to contribute, nobody contributing."""
+    world = 3
+    want_vals = np.concatenate([np.arange(r, dtype=np.float32) + 10.0 * r
+                                for r in range(world)])
+    want_verts = np.concatenate([np.full((2 * r + 1, 2), float(r)) for r in range(world)])
+    for vals, verts, none in run_ranks(_ragged_case, world):
+        np.testing.assert_array_equal(vals, want_vals)
+        np.testing.assert_array_equal(verts, want_verts)
+        assert none.shape == (0, 2)
