@@ -82,12 +82,18 @@ __host__ __device__ __forceinline__ void bspl3(KnotF t, int l, double x,
     double hh[3];
     h[0] = 1.0;
     h[1] = h[2] = h[3] = 0.0;
-#pragma unroll
+    // (the host pass of this __host__ __device__ function has no `unroll`)
+#ifdef __CUDA_ARCH__
+#define OCSB_UNROLL _Pragma("unroll")
+#else
+#define OCSB_UNROLL
+#endif
+    OCSB_UNROLL
     for (int j = 1; j <= 3; ++j) {
-#pragma unroll
+        OCSB_UNROLL
         for (int i = 0; i < j; ++i) hh[i] = h[i];
         h[0] = 0.0;
-#pragma unroll
+        OCSB_UNROLL
         for (int i = 0; i < j; ++i) {
             const int li = l + i + 1, lj = li - j;
             const double tli = t(li), tlj = t(lj);
@@ -96,6 +102,7 @@ __host__ __device__ __forceinline__ void bspl3(KnotF t, int l, double x,
             h[i + 1] = f * (x - tlj);
         }
     }
+#undef OCSB_UNROLL
 }
 
 // LU factors of the collocation matrix, 5 doubles per row:
@@ -165,6 +172,8 @@ solve_fwd_kernel(const T *__restrict__ src, int64_t ss, int src_flip,
     const int b = min(n, a + R);
     const int s = max(0, a - kWarm);
     double y1 = 0.0, y2 = 0.0;  // y[i-1], y[i-2]
+    // (issuing 8 or 16 rows of loads ahead of the FMA chain was measured
+    // SLOWER: 0.75 / 0.79 vs 0.54 ms per 5000^2 tile, profiles/r1h_spline.txt)
 #pragma unroll 4
     for (int i = s; i < b; ++i) {
         const int64_t si = src_flip ? (n - 1 - i) : i;

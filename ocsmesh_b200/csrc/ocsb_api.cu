@@ -1529,9 +1529,6 @@ extern "C" int32_t ocsb_hfun_pass(
         if (!bad) continue;
         int a, b;
         band_of(k, &a, &b);
-        ocsb_win bw = *win;
-        bw.row_begin = a;
-        bw.row_end = b;
         // the single-band call: everything resident, or one streamed band
         // (rows == b - a) through the synchronous retrying path
         if (!bz.host && !bi.host && !bo.host) {
