@@ -422,7 +422,8 @@ int32_t ocsb_hfun_pass(ocsb_ctx *ctx, const ocsb_win *win,
  * (overlap > 0) must be given distinct old / new buffers by the caller, as for
  * the single-window calls, and in_order = 1: pixels shared by two windows are
  * then written in list order (the later window wins, as in the reference's
- * sequential loop) at the price of running the windows one after another.    */
+ * sequential loop): a window waits for the earlier windows it overlaps, the
+ * others still run side by side.                                             */
 int32_t ocsb_hfun_op_windows(ocsb_ctx *ctx, const ocsb_win *wins,
                              const int64_t *dem_off, const int64_t *hfun_off,
                              int32_t n_wins,

@@ -1625,9 +1625,28 @@ extern "C" int32_t ocsb_hfun_op_windows(
         OCSB_TRY(sv.init(ctx, op->verts_xy, 1, op->nv * 2, op->nv * 2, 8, STAGE_IN));
         verts[0] = (const double *)sv.dev;
     }
-    // overlapping windows write shared pixels: list order must decide, as in
-    // the reference's sequential loop -> one worker stream
-    const int ns = in_order ? 1 : (n_wins < OCSB_WIN_STREAMS ? n_wins : OCSB_WIN_STREAMS);
+    // overlapping windows write shared pixels: list order must decide there, as
+    // in the reference's sequential loop.  Only windows that really share
+    // pixels are ordered (window k waits for the event of every earlier window
+    // it overlaps); the rest still run side by side, a wavefront over the grid.
+    const int ns = n_wins < OCSB_WIN_STREAMS ? n_wins : OCSB_WIN_STREAMS;
+    struct Rect { int64_t r0, r1, c0, c1; };
+    std::vector<Rect> rect;
+    struct EventList {
+        std::vector<cudaEvent_t> ev;
+        ~EventList() { for (auto e : ev) if (e) cudaEventDestroy(e); }
+    } done;
+    if (in_order && n_wins > 1) {
+        rect.resize(n_wins);
+        done.ev.assign(n_wins, nullptr);
+        for (int32_t k = 0; k < n_wins; ++k) {
+            // (virtual) row 0 / column 0 of the window in the hfun buffer
+            int64_t row = hfun_off[k] / new_stride, col = hfun_off[k] % new_stride;
+            if (col < 0) { col += new_stride; --row; }
+            rect[k] = {row + rb[k], row + re[k], col, col + wins[k].width};
+            OCSB_CUDA(cudaEventCreateWithFlags(&done.ev[k], cudaEventDisableTiming));
+        }
+    }
     for (int i = 0; i < ns; ++i) {
         if (!ctx->s_win[i])
             OCSB_CUDA(cudaStreamCreateWithFlags(&ctx->s_win[i], cudaStreamNonBlocking));
@@ -1654,9 +1673,17 @@ extern "C" int32_t ocsb_hfun_op_windows(
         const void *zp; const float *ip; float *opp;
         ptrs(k, &zp, &ip, &opp);
         ctx->stream = ctx->s_win[k % ns];        // everything below enqueues here
+        if (!rect.empty())
+            for (int32_t j = 0; j < k; ++j)
+                if (rect[j].r0 < rect[k].r1 && rect[k].r0 < rect[j].r1 &&
+                    rect[j].c0 < rect[k].c1 && rect[k].c0 < rect[j].c1 &&
+                    (j % ns) != (k % ns))        // same stream: already ordered
+                    cudaStreamWaitEvent(ctx->stream, done.ev[j], 0);
         status = pass_ops(ctx, &wins[k], rb[k], re[k], zp, dem_dtype, dem_stride, ip,
                           old_stride, opp, new_stride, dx, dy, ghmin, ghmax, op, 1,
                           verts, flags + k);
+        if (!rect.empty() && status == OCSB_OK)
+            cudaEventRecord(done.ev[k], ctx->stream);
     }
     ctx->stream = main_stream;
     for (int i = 0; i < ns; ++i) {               // join
@@ -1674,8 +1701,13 @@ extern "C" int32_t ocsb_hfun_op_windows(
         OCSB_CUDA(cudaMemcpyAsync(hflags.data(), flags, hflags.size() * sizeof(int),
                                   cudaMemcpyDeviceToHost, ctx->stream));
         OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        bool redo_rest = false;
         for (int32_t k = 0; k < n_wins; ++k) {
-            if (!hflags[k]) continue;
+            // ordered lists: a redone window rewrites pixels it shares with
+            // later windows, so everything after the first overflow is redone
+            // in list order (old / new are distinct buffers: idempotent)
+            if (!hflags[k] && !redo_rest) continue;
+            if (!rect.empty()) redo_rest = true;
             const void *zp; const float *ip; float *opp;
             ptrs(k, &zp, &ip, &opp);
             OCSB_TRY(pass_ops(ctx, &wins[k], rb[k], re[k], zp, dem_dtype, dem_stride,
