@@ -583,6 +583,13 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
     const double r2lim = bounded ? (a.r > 0 ? r2 * (1.0 + kDomEps) : -1.0) : inf;
 
     ScratchGuard sg(ctx);
+    {
+        // counters + per-level offset / count tables in one allocation
+        size_t fixed = ScratchGuard::piece((kMaxLevels + 2) * sizeof(unsigned long long));
+        for (int i = 0; i <= top; ++i)
+            fixed += 2 * ScratchGuard::piece((size_t)lv[i].ntiles * sizeof(int));
+        OCSB_TRY(sg.reserve(fixed));
+    }
     unsigned long long *ctrs = nullptr;   // [kMaxLevels] + overflow flag behind
     OCSB_TRY(sg.get(&ctrs, kMaxLevels + 2));
     int *overflow = reinterpret_cast<int *>(ctrs + kMaxLevels);
@@ -617,6 +624,7 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
             sw.swap(a.refine_stream);
         }
         std::vector<unsigned long long> cap(top + 1);
+        size_t pool_bytes = 0;
         for (int i = 0; i <= top; ++i) {
             unsigned long long c = 4ull * (unsigned long long)nv +
                                    48ull * (unsigned long long)lv[i].ntiles +
@@ -625,8 +633,13 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a, const double *verts,
             if (async_mode) c <<= 1;   // one shot: start with doubled pools
             if (c > 0x7fffffffull) c = 0x7fffffffull;  // int offsets
             cap[i] = c;
-            OCSB_TRY(pools.get(&dev[i].ids, (size_t)c));
+            pool_bytes += ScratchGuard::piece((size_t)c * sizeof(*dev[i].ids));
         }
+        // all candidate pools of this attempt in one allocation (+ room for
+        // the split scratch of a typical level)
+        OCSB_TRY(pools.reserve(pool_bytes + (1u << 20)));
+        for (int i = 0; i <= top; ++i)
+            OCSB_TRY(pools.get(&dev[i].ids, (size_t)cap[i]));
         for (int i = top; i >= 0; --i) {
             RefineArgs A;
             A.g = g;

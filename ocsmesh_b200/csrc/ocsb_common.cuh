@@ -62,7 +62,9 @@ struct KTimeRec {
     int kclass;
     cudaEvent_t a, b;
 };
+#ifndef OCSB_WIN_STREAMS
 #define OCSB_WIN_STREAMS 8
+#endif
 struct ocsb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -99,11 +101,33 @@ void ocsb_free(ocsb_ctx *ctx, void *p);
 struct ScratchGuard {
     ocsb_ctx *ctx;
     std::vector<void *> ptrs;
+    char *arena = nullptr;      // reserve(): one block that get() carves up
+    size_t arena_left = 0;
     explicit ScratchGuard(ocsb_ctx *c) : ctx(c) {}
     ~ScratchGuard() {
         for (void *p : ptrs) ocsb_free(ctx, p);
     }
+    // One allocation for the next get() calls (256-byte aligned pieces): the
+    // per-window launches of a many-window op are bound by host call count.
+    // Requests that do not fit fall back to their own allocation.
+    int32_t reserve(size_t bytes) {
+        void *p = nullptr;
+        int32_t s = ocsb_alloc(ctx, &p, bytes);
+        if (s != OCSB_OK) return s;
+        ptrs.push_back(p);
+        arena = reinterpret_cast<char *>(p);
+        arena_left = bytes;
+        return OCSB_OK;
+    }
+    static size_t piece(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
     template <typename T> int32_t get(T **out, size_t count) {
+        const size_t need = piece(count * sizeof(T) ? count * sizeof(T) : 16);
+        if (need <= arena_left) {
+            *out = reinterpret_cast<T *>(arena);
+            arena += need;
+            arena_left -= need;
+            return OCSB_OK;
+        }
         void *p = nullptr;
         int32_t s = ocsb_alloc(ctx, &p, count * sizeof(T));
         if (s != OCSB_OK) return s;

@@ -194,3 +194,46 @@ def test_many_windows_one_library_call(ctx, chunk, overlap):
     hf.add_subtidal_flow_limiter(hmin=50, hmax=1500, lower_bound=-30, upper_bound=0)
     oh.add_subtidal_flow_limiter(50, 1500, -30, 0)
     np.testing.assert_array_equal(hf.get_values(), oh.values)
+
+
+def test_op_windows_argument_checks(ctx):
+    """ocsb_hfun_op_windows: resident buffers only, empty list is a no-op,
+    bad ops are refused with the reference's messages."""
+    import torch
+    from ocsmesh_b200 import _lib
+    gr, _ = both(300, 320, 4, 100, 0)
+    W, H = gr.width, gr.height
+    wins_l = list(gr.iter_windows())
+    wins = (_lib.ocsb_win * len(wins_l))(*[
+        _lib.make_win(gr.get_window_bounds(w), w.width, w.height) for w in wins_l])
+    off = np.array([w.row_off * W + w.col_off for w in wins_l], dtype=np.int64)
+    dev = torch.full((H, W), 3.0e38, dtype=torch.float32, device="cuda")
+    host = np.zeros((H, W), np.float32)
+    pts = torch.tensor([[S.X0 + 500.0, S.Y0 + 700.0]], dtype=torch.float64, device="cuda")
+    op = ("feature", pts, 1, 0.001, 100.0, True)
+    with pytest.raises(_lib.OcsbError, match="device memory"):
+        ctx.hfun_op_windows(wins, None, off, None, _lib.OCSB_F32, W, None, W, host, W,
+                            10.0, 10.0, 100.0, 1500.0, op)
+    with pytest.raises(_lib.OcsbError, match="greater than zero"):
+        ctx.hfun_op_windows(wins, None, off, None, _lib.OCSB_F32, W, None, W, dev, W,
+                            10.0, 10.0, 100.0, 1500.0,
+                            ("feature", pts, 1, 0.001, 0.0, True))
+    with pytest.raises(_lib.OcsbError, match="device DEM"):
+        ctx.hfun_op_windows(wins, None, off, None, _lib.OCSB_F32, W, None, W, dev, W,
+                            10.0, 10.0, 100.0, 1500.0,
+                            ("limiter", 50.0, 1500.0, None, None, True))
+    before = dev.clone()
+    empty = (_lib.ocsb_win * 0)()
+    ctx.hfun_op_windows(empty, None, off[:0], None, _lib.OCSB_F32, W, None, W, dev, W,
+                        10.0, 10.0, 100.0, 1500.0, op)
+    assert torch.equal(dev, before)
+    # and the real thing equals the per-window calls
+    ctx.hfun_op_windows(wins, None, off, None, _lib.OCSB_F32, W, None, W, dev, W,
+                        10.0, 10.0, 100.0, 1500.0, op)
+    ref = torch.empty_like(dev)
+    for w, cw in zip(wins_l, wins):
+        ctx.hfun_feature(cw, pts, 1, None, W,
+                         ref.data_ptr() + (w.row_off * W + w.col_off) * 4, W,
+                         0.001, 100.0, 100.0, 1500.0, fuse_clamp=True)
+    ctx.sync()
+    assert torch.equal(dev, ref)
