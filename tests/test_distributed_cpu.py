@@ -246,3 +246,22 @@ def test_all_gather_ragged_any_rank_and_empty_contributions():
         np.testing.assert_array_equal(vals, want_vals)
         np.testing.assert_array_equal(verts, want_verts)
         assert none.shape == (0, 2)
+
+
+def _ragged_plan_case(rank, world):
+    verts = torch.full((3 * rank + 2, 2), float(rank), dtype=torch.float64)
+    sizes = D.gather_sizes(verts.shape[0], verts.device)
+    a = D.all_gather_vertices(verts).numpy()
+    b = D.all_gather_vertices(verts, sizes=sizes).numpy()
+    bad = False
+    try:
+        D.all_gather_vertices(verts, sizes=[1] * world)
+    except ValueError:
+        bad = True
+    return sizes, a, b, bad
+
+
+def test_all_gather_with_pre_exchanged_sizes():
+    for sizes, a, b, bad in run_ranks(_ragged_plan_case, 2):
+        assert sizes == [2, 5] and bad
+        np.testing.assert_array_equal(a, b)
