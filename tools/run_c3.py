@@ -74,8 +74,11 @@ def main():
     def combine(i, w, t):
         hfuns[i].min_combine_values(w, t)
 
+    vsizes = D.gather_sizes(len(pts), f"cuda:{dev}") if world > 1 else None
+
     def step():
-        verts = D.all_gather_vertices(verts_local) if world > 1 else verts_local
+        verts = (D.all_gather_vertices(verts_local, sizes=vsizes) if world > 1
+                 else verts_local)
         for k in sorted(hfuns):
             h = hfuns[k]
             h.reset()
