@@ -179,8 +179,8 @@ def test_config1_whole_case_every_pixel_and_node(ctx):
     import importlib.util
     import os
     spec = importlib.util.spec_from_file_location(
-        "run_c1", os.path.join(os.path.dirname(os.path.dirname(
-            os.path.abspath(__file__))), "tools", "run_c1.py"))
+        "run_c1", os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                               "tools", "run_c1.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     res = mod.run(2000, 200_000, repeat=1)

@@ -10,7 +10,9 @@ every one of the 4 M pixels and 200 k nodes is compared, and both are timed by
 wall clock through their public calls (the product's time includes the DEM
 upload and the result download).  Prints one JSON line.
 
-    python tools/run_c1.py [--size 2000] [--nodes 200000]
+    python tests/tools/run_c1.py [--size 2000] [--nodes 200000]
+
+Test infrastructure (uses the oracle as the checker): lives under tests/.
 """
 import argparse
 import json
@@ -21,7 +23,7 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import ocsmesh_b200 as ob
 from ocsmesh_b200 import synthetic as S
 from oracle import ocsmesh_oracle as O

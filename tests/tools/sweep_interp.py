@@ -1,18 +1,20 @@
 """Interpolation gather (K3) timing + parity sweep over library builds.
 
-    python tools/sweep_interp.py [lib.so ...]
+    python tests/tools/sweep_interp.py [lib.so ...]
 
 Each library (default: the product one) is loaded in a fresh process through
 OCSB_LIB.  Workload = BASELINE.json configs[3]: 10 M nodes, 16 tiles 5000x5000
 (4x4, 100-px overlap), nodes resident in bucket order.  A 200 k-node sample is
 checked bit-for-bit against the scipy oracle before anything is timed.
+
+Test infrastructure (uses the oracle as the checker): lives under tests/.
 """
 import json
 import os
 import subprocess
 import sys
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 

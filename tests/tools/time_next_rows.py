@@ -5,9 +5,11 @@ add_constant_value / topo constraint with rate / Courant constraint (next-2).
 Prints one JSON line per op: CUDA-event ms per call (median of 5 after 2
 warm-ups), per-kernel-class ms, algorithmic bytes/px and the resulting
 fraction of the measured HBM peak; the host marching-squares sweep and the
-numpy oracle are timed beside them on a crop for scale."""
+numpy oracle are timed beside them on a crop for scale.
+
+Test infrastructure (uses the oracle as the checker): lives under tests/."""
 import json, os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import torch
 import ocsmesh_b200 as ob

@@ -3,14 +3,16 @@ BASELINE.json configs[3] scale: 16 tiles 5000 x 5000, 10 M nodes.  Kernel
 times (prefilter per tile, evaluation) from the library's own events, and the
 agreement with scipy's RectBivariateSpline on one tile's sample.
 
-    python tools/time_spline.py [lib.so ...]     (OCSB_LIB variants, as sweep_interp)
+    python tests/tools/time_spline.py [lib.so ...]     (OCSB_LIB variants, as sweep_interp)
+
+Test infrastructure (uses the oracle as the checker): lives under tests/.
 """
 import json
 import os
 import subprocess
 import sys
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 
