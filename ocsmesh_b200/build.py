@@ -28,6 +28,7 @@ SOURCES = [
     "k_bucket.cu",
     "k_spline.cu",
     "k_feature.cu",
+    "k_pass.cu",
     "k_nearest.cu",
     "k_constraint.cu",
     "k_contour.cu",

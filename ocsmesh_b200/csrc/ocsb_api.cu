@@ -287,7 +287,8 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
     static const char *names[OCSB_KC_COUNT] = {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
-        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour", "sample"};
+        "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour", "sample",
+        "pass_tile"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 
@@ -1234,6 +1235,55 @@ int32_t pass_ops(ocsb_ctx *ctx, const ocsb_win *win, int a, int b,
                  double ghmax, const ocsb_hfun_op *ops, int n_ops,
                  const std::vector<const double *> &verts,
                  int *flags /* device, n_ops ints; nullptr = synchronous */) {
+    // ---- one tiled sweep for the whole list (k_pass.cu) when it qualifies -----
+    {
+        static const bool tiled_on = [] {
+            const char *e = getenv("OCSB_PASS_TILED");
+            return !(e && atoi(e) == 0);
+        }();
+        const int w = win->width, h = win->height;
+        PassWin pw;
+        win_axes(win, &pw.ax, &pw.ay);
+        pw.rb = a; pw.re = b;
+        pw.keep_w = w; pw.keep_h = h;
+        pw.hoff = 0;
+        const int za = a > 0 ? a - 1 : 0, zb = b < h ? b + 1 : h;
+        pw.dem_c = 0; pw.dem_r = -za;
+        std::vector<PassFeat> pf;
+        std::vector<PassLim> pl;
+        for (int i = 0; i < n_ops; ++i) {
+            const ocsb_hfun_op &op = ops[i];
+            if (op.kind == OCSB_OP_FEATURE) {
+                PassFeat f;
+                f.verts = verts[i]; f.nv = op.nv;
+                f.rate_target = op.expansion_rate * op.target_size;
+                f.target = op.target_size;
+                f.r = (!ocsb_is_none(ghmax) && ghmax != 0.0)
+                          ? (ghmax - op.target_size) / f.rate_target
+                          : std::numeric_limits<double>::infinity();
+                f.fuse_clamp = op.fuse_clamp;
+                pf.push_back(f);
+            } else {
+                pl.push_back(PassLim{op.hmin, op.hmax, op.lower_bound, op.upper_bound,
+                                     op.fuse_clamp});
+            }
+        }
+        PassDesc d;
+        d.wins = &pw; d.n_wins = 1;
+        if (!pl.empty()) {
+            d.dem = (const char *)dem + (size_t)za * (size_t)dem_stride *
+                                            (dem_dtype == OCSB_F64 ? 8 : 4);
+            d.dem_dtype = dem_dtype; d.dem_stride = dem_stride;
+            d.dem_rows = zb - za; d.dem_cols = w;
+        }
+        d.in = in; d.in_stride = in_stride;
+        d.out = out; d.out_stride = out_stride;
+        d.dx = dx; d.dy = dy; d.ghmin = ghmin; d.ghmax = ghmax;
+        d.feats = pf.data(); d.nf = (int)pf.size();
+        d.lims = pl.data(); d.nl = (int)pl.size();
+        d.ext_overflow = flags;
+        if (tiled_on && k_pass_supported(d)) return k_pass_tiled(ctx, d);
+    }
     const float *oldp = in;
     int64_t olds = in_stride;
     // Resident lists that start with a feature op: every op is a monotone

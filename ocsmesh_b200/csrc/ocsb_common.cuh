@@ -20,7 +20,8 @@ enum {
     KC_SPLINE_PREFILTER = OCSB_KC_SPLINE_PREFILTER,
     KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
     KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT,
-    KC_CONTOUR = OCSB_KC_CONTOUR, KC_SAMPLE = OCSB_KC_SAMPLE
+    KC_CONTOUR = OCSB_KC_CONTOUR, KC_SAMPLE = OCSB_KC_SAMPLE,
+    KC_PASS_TILE = OCSB_KC_PASS_TILE
 };
 
 // ---------------------------------------------------------------------------
@@ -297,6 +298,47 @@ int32_t k_hfun_feature(ocsb_ctx *ctx, const FeatureArgs &a,
                        const double *verts, int64_t nv, const float *old_,
                        int64_t old_stride, float *new_, int64_t new_stride,
                        double *dist_out, int64_t *idx_out);
+// k_pass.cu: the op list of a pass as ONE tiled sweep over a table of semantic
+// windows (feature ops first, then limiter ops: with one fuse_clamp setting the
+// ops commute bit for bit)
+struct PassWin {
+    LinAxis ax, ay;         // np.linspace axes of the window
+    int rb, re;             // window rows [rb, re) processed by this call
+    int keep_w, keep_h;     // window pixels (r < keep_h, c < keep_w) are written
+    int64_t hoff;           // element offset of window pixel (0, 0) in in / out
+    int dem_c, dem_r;       // DEM block column / row of window pixel (0, 0)
+};
+struct PassFeat {
+    const double *verts;
+    int64_t nv;
+    double rate_target, target, r;
+    int fuse_clamp;
+};
+struct PassLim {
+    double hmin, hmax, lb, ub;   // NaN = None
+    int fuse_clamp;
+};
+struct PassDesc {
+    const PassWin *wins = nullptr;
+    int n_wins = 0;
+    const void *dem = nullptr;   // element (0, 0) of the stored DEM block
+    int dem_dtype = OCSB_F32;
+    int64_t dem_stride = 0;
+    int dem_rows = 0, dem_cols = 0;
+    const float *in = nullptr;   // nullptr: initial state (finfo(float32).max)
+    int64_t in_stride = 0;
+    float *out = nullptr;
+    int64_t out_stride = 0;
+    double dx = 0, dy = 0, ghmin = 0, ghmax = 0;
+    const PassFeat *feats = nullptr;
+    int nf = 0;
+    const PassLim *lims = nullptr;
+    int nl = 0;
+    int *ext_overflow = nullptr; // non-null: asynchronous (see FeatureArgs)
+};
+bool k_pass_supported(const PassDesc &d);
+int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d);
+
 int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
                          const double *q, int64_t nq, double r, double *dist,
                          int64_t *idx);
