@@ -57,6 +57,22 @@ constexpr int kDemRows = kT0 + 2;
 constexpr int kMaxFeat = 4, kMaxLim = 4;
 constexpr double kBig = 1e300;       // "no candidate" squared distance (finite)
 
+#ifdef OCSB_PASS_STATS
+// tuning build only (tools/pass_lab.py): list lengths and per-phase clocks
+// (one slot row per SM: no contention between SMs)
+__device__ unsigned long long g_pass_stats[160][32];
+__device__ __forceinline__ unsigned pstat_smid() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+    return r;
+}
+#define PSTAT_ADD(i, v) atomicAdd(&g_pass_stats[pstat_smid()][i], (unsigned long long)(v))
+#define PSTAT_CLK(var) const long long var = clock64()
+#else
+#define PSTAT_ADD(i, v)
+#define PSTAT_CLK(var)
+#endif
+
 // ---------------------------------------------------------------------------
 // window table
 // ---------------------------------------------------------------------------
@@ -230,6 +246,7 @@ __device__ __forceinline__ void dom_combine(const unsigned key[5], unsigned (*s_
 // ---------------------------------------------------------------------------
 struct ListDev {
     int *off, *cnt, *ids;
+    double2 *xy;            // level 1 only: the listed vertices themselves
 };
 
 struct BuildArgs {
@@ -436,7 +453,9 @@ __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
                 const int p = atomicAdd(&s_col.count, 1);
                 if (p < kL1Cap) s_col.buf[p] = id;
             } else {
-                A.l1.ids[s_col.base + atomicAdd(&s_col.pos, 1)] = id;
+                const int p = atomicAdd(&s_col.pos, 1);
+                A.l1.ids[s_col.base + p] = id;
+                A.l1.xy[s_col.base + p] = v;
             }
         }
     };
@@ -458,8 +477,11 @@ __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
     const int total = s_col.count;
     if (total == 0) return;
     if (total <= kL1Cap) {
-        for (int i = threadIdx.x; i < total; i += kL1Threads)
-            A.l1.ids[s_col.base + i] = s_col.buf[i];
+        for (int i = threadIdx.x; i < total; i += kL1Threads) {
+            const int id = s_col.buf[i];
+            A.l1.ids[s_col.base + i] = id;
+            A.l1.xy[s_col.base + i] = A.verts[id];
+        }
     } else {
         sweep(true);
     }
@@ -702,6 +724,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
     __shared__ int s_n;
     __shared__ __align__(8) unsigned long long s_bar;
 
+    PSTAT_CLK(st0);
     const int2 flags = *reinterpret_cast<const int2 *>(A.overflow);   // {overflow, far}
     if (flags.x) return;
     const bool far = flags.y != 0;
@@ -756,6 +779,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
         }
     }
     __syncthreads();
+    PSTAT_CLK(st1);
     const PWin &W = s_win;
     const int bw = W.ax.n, rb = W.rb, bh = W.re - rb;
 
@@ -782,6 +806,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
         const FeatDev &F = A.feat[f];
         int ntile = 0, poff = 0, ns = 0;
         bool in_smem = true, refilter = false;
+        PSTAT_CLK(st2);
         if (nf > 0) {
             const int t1 = W.base1 + (ty >> 2) * W.n1x + (tx >> 2);
             const int pcnt = F.cnt1[t1];
@@ -844,7 +869,12 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                 ntile = s_n;
                 if (ntile > kListCap) { in_smem = false; ntile = pcnt; }
             }
+            if (threadIdx.x == 0) {
+                PSTAT_ADD(0, 1); PSTAT_ADD(1, pcnt); PSTAT_ADD(2, ntile);
+                PSTAT_ADD(3, pcnt > 32); PSTAT_ADD(4, ntile > 32);
+            }
         }
+        PSTAT_CLK(st3);
         auto cand = [&](int i) -> double2 {
             return in_smem ? s_v[i] : F.verts[F.ids1[poff + i]];
         };
@@ -893,6 +923,13 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                 }
                 __syncwarp();
             }
+            PSTAT_CLK(st4);
+            if (lane == 0) {
+                PSTAT_ADD(5, 1); PSTAT_ADD(6, ns); PSTAT_ADD(7, refilter);
+                PSTAT_ADD(8, ns == 0); PSTAT_ADD(9, ns == 1); PSTAT_ADD(10, ns == 2);
+                PSTAT_ADD(11, ns >= 3 && ns < 5); PSTAT_ADD(12, ns >= 5);
+                PSTAT_ADD(16, st1 - st0); PSTAT_ADD(17, st3 - st2); PSTAT_ADD(18, st4 - st3);
+            }
             if (last && A.nl && A.use_tma) {
                 // the DEM box has had the whole list stage to land
                 uint32_t done = 0;
@@ -906,10 +943,13 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
             }
 
             // ---- lane: 4x4 pixels, two rows at a time ----------------------------------
+            PSTAT_CLK(st5);
+            if (lane == 0) PSTAT_ADD(19, st5 - st4);
 #pragma unroll 1
             for (int half = 0; half < 2; ++half) {
                 const int hr = grow + half * 2;            // first row of the pair
                 if (hr > sr1 || gcol > sc1) break;
+                PSTAT_CLK(sh0);
                 // ---- feature op: nearest vertex + size law -------------------------------
                 float vf[8];
                 if (nf > 0) {
@@ -967,6 +1007,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                         size_law8(best, F, far ? 0xffffffffu : F.hi_lo, vf);
                     }
                 }
+                PSTAT_CLK(sh1);
                 // ---- pre-op values (loaded late: not live during the search) ------------
                 float o[8];
 #pragma unroll
@@ -1004,6 +1045,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                             o[k] = min_nan_f32(o[k], clamp_nan(fminf(vf[k], F.v_far_f), A.lo, A.hi));
                     }
                 }
+                PSTAT_CLK(sh2);
                 // ---- limiter ops ---------------------------------------------------------
                 if (last && A.nl) {
                     const int H = W.ay.n;
@@ -1062,6 +1104,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                         }
                     }
                 }
+                PSTAT_CLK(sh3);
                 // ---- store -----------------------------------------------------------------
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
@@ -1076,6 +1119,11 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                             if (gcol + k <= wc1) nrow[k] = o[j * 4 + k];
                     }
                 }
+                PSTAT_CLK(sh4);
+                if (lane == 0) {
+                    PSTAT_ADD(20, sh1 - sh0); PSTAT_ADD(21, sh2 - sh1);
+                    PSTAT_ADD(22, sh3 - sh2); PSTAT_ADD(23, sh4 - sh3);
+                }
             }
         } else if (last && A.nl && A.use_tma) {
             // a CTA must not retire with its bulk copy in flight
@@ -1089,8 +1137,17 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
             }
         }
         if (!last) __syncthreads();   // s_v / s_w are reused by the next op
+#ifdef OCSB_PASS_STATS
+        if (last && lane == 0) {
+            const long long dur = clock64() - st0;
+            PSTAT_ADD(ntile > 0 ? 24 : 25, dur);
+            PSTAT_ADD(ntile > 0 ? 26 : 27, 1);
+        }
+#endif
     }
 }
+
+#include "k_pass2.cuh"
 
 // ---------------------------------------------------------------------------
 // host side
@@ -1111,6 +1168,49 @@ EncodeTiledFn encode_tiled_fn() {
         return (EncodeTiledFn)p;
     }();
     return fn;
+}
+
+// one instantiation of the persistent kernel: resident grid, opt-in shared memory
+template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND>
+int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P) {
+    auto kern = pass2_kernel<HAS_OLD, HAS_FEAT, HAS_LIM, BAND>;
+    static int resident[64] = {};     // per device: CTAs that fit the whole GPU
+    int dev = 0;
+    OCSB_CUDA(cudaGetDevice(&dev));
+    OCSB_REQUIRE(dev >= 0 && dev < 64, "launch_pass2: device index out of range");
+    if (resident[dev] == 0) {
+        OCSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(P2Smem)));
+        int n = 0, sms = 0;
+        OCSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kP2Threads,
+                                                                sizeof(P2Smem)));
+        OCSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        OCSB_REQUIRE(n > 0 && sms > 0, "pass2_kernel does not fit an SM");
+        resident[dev] = n * sms;
+    }
+    const int grid = (int)std::min<long long>(P.n_tiles, (long long)resident[dev]);
+    kern<<<grid, kP2Threads, sizeof(P2Smem), ctx->stream>>>(tmap, P);
+    return OCSB_OK;
+}
+
+int32_t launch_pass2(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P, bool old,
+                     bool feat, bool lim, bool band) {
+#define P2_CASE(O, F, L, B)                                                        \
+    if (old == O && feat == F && lim == L && band == B)                            \
+        return launch_pass2_t<O, F, L, B>(ctx, tmap, P);
+    P2_CASE(false, true, true, false)
+    P2_CASE(false, true, true, true)
+    P2_CASE(true, true, true, false)
+    P2_CASE(true, true, true, true)
+    P2_CASE(false, true, false, false)
+    P2_CASE(true, true, false, false)
+    P2_CASE(false, false, true, false)
+    P2_CASE(false, false, true, true)
+    P2_CASE(true, false, true, false)
+    P2_CASE(true, false, true, true)
+#undef P2_CASE
+    ocsb_set_error("launch_pass2: no such variant");
+    return OCSB_EINVAL;
 }
 
 }  // namespace
@@ -1217,6 +1317,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (nctr + 8) * sizeof(*ctrs), ctx->stream));
         TileArgs T;
         memset(&T, 0, sizeof(T));
+        const double2 *l1xy[kMaxFeat] = {};
         T.wins = d_wins; T.n_wins = d.n_wins;
         T.in = d.in; T.out = d.out;
         T.in_stride = d.in_stride; T.out_stride = d.out_stride;
@@ -1281,6 +1382,8 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             OCSB_TRY(pools.get(&B.l1.off, (size_t)n1));
             OCSB_TRY(pools.get(&B.l1.cnt, (size_t)n1));
             OCSB_TRY(pools.get(&B.l1.ids, (size_t)cap1));
+            OCSB_TRY(pools.get(&B.l1.xy, (size_t)cap1));
+            B.l2.xy = nullptr;
             B.ctr2 = ctrs + 2 * f; B.ctr1 = ctrs + 2 * f + 1;
             B.cap2 = cap2; B.cap1 = cap1;
             B.overflow = overflow;
@@ -1296,6 +1399,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             FeatDev &F = T.feat[f];
             F.verts = verts;
             F.off1 = B.l1.off; F.cnt1 = B.l1.cnt; F.ids1 = B.l1.ids;
+            l1xy[f] = B.l1.xy;
             F.rt = pf.rate_target; F.target = pf.target;
             F.r2 = (bounded && pf.r <= 0) ? -1.0 : r2;
             F.r2lim = r2lim;
@@ -1330,13 +1434,55 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             p.fuse_clamp = pl.fuse_clamp;
             T.lim_band[l] = (!ocsb_is_none(pl.lb) || !ocsb_is_none(pl.ub)) ? 1 : 0;
         }
+        // ---- persistent pipeline (k_pass2.cuh) for the common shape of a pass:
+        //      at most one feature and one limiter op, fused clamps, TMA-able DEM
+        static const bool v2_on = [] {
+            const char *e = getenv("OCSB_PASS_V2");
+            return !(e && atoi(e) == 0);
+        }();
+        bool v2 = v2_on && d.nf <= 1 && d.nl <= 1 && (d.nl == 0 || use_tma) &&
+                  n0 + 4096 < 0x7fffffffll;
+        for (int f = 0; f < d.nf; ++f) v2 = v2 && d.feats[f].fuse_clamp;
+        for (int l = 0; l < d.nl; ++l) v2 = v2 && d.lims[l].fuse_clamp;
         OCSB_TIME(ctx, KC_PASS_TILE);
-        const dim3 tgrid = d.n_wins == 1 ? dim3((unsigned)wins[0].n0x, (unsigned)wins[0].n0y)
-                                         : dim3((unsigned)n0);
-        if (d.in) tile_kernel<true><<<tgrid, kPassThreads, 0, ctx->stream>>>(tmap, T);
-        else tile_kernel<false><<<tgrid, kPassThreads, 0, ctx->stream>>>(tmap, T);
+        if (v2) {
+            P2Args P;
+            memset(&P, 0, sizeof(P));
+            P.wins = d_wins; P.n_wins = d.n_wins; P.n_tiles = (int)n0;
+            P.in = d.in; P.out = d.out;
+            P.in_stride = d.in_stride; P.out_stride = d.out_stride;
+            if (d.nf) { P.feat = T.feat[0]; P.xy1 = l1xy[0]; }
+            if (d.nl) P.lim = T.lim[0];
+            P.lo = T.lo; P.hi = T.hi;
+            P.counter = reinterpret_cast<int *>(ctrs + nctr) + 4;
+            P.overflow = overflow;
+            const bool band = d.nl && T.lim_band[0];
+            OCSB_TRY(launch_pass2(ctx, tmap, P, d.in != nullptr, d.nf > 0, d.nl > 0, band));
+        } else {
+            const dim3 tgrid = d.n_wins == 1
+                                   ? dim3((unsigned)wins[0].n0x, (unsigned)wins[0].n0y)
+                                   : dim3((unsigned)n0);
+            if (d.in) tile_kernel<true><<<tgrid, kPassThreads, 0, ctx->stream>>>(tmap, T);
+            else tile_kernel<false><<<tgrid, kPassThreads, 0, ctx->stream>>>(tmap, T);
+        }
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
+#ifdef OCSB_PASS_STATS
+        if (getenv("OCSB_PASS_STATS_PRINT")) {
+            static unsigned long long hs[160][32];
+            cudaStreamSynchronize(ctx->stream);
+            cudaMemcpyFromSymbol(hs, g_pass_stats, sizeof(hs));
+            fprintf(stderr, "PASS_STATS");
+            for (int i = 0; i < 32; ++i) {
+                unsigned long long t = 0;
+                for (int m = 0; m < 160; ++m) t += hs[m][i];
+                fprintf(stderr, " %llu", t);
+            }
+            fprintf(stderr, "\n");
+            memset(hs, 0, sizeof(hs));
+            cudaMemcpyToSymbol(g_pass_stats, hs, sizeof(hs));
+        }
+#endif
 
         if (d.nf == 0) return OCSB_OK;
         if (async_mode) {
