@@ -76,7 +76,7 @@ __device__ __forceinline__ unsigned pstat_smid() {
 // ---------------------------------------------------------------------------
 // window table
 // ---------------------------------------------------------------------------
-struct PWin {
+struct __align__(16) PWin {     // 144 bytes: bulk-copied into shared memory
     LinAxis ax, ay;
     int rb, re;             // rows [rb, re) of the window live on this device
     int keep_w, keep_h;     // window pixels (r < keep_h, c < keep_w) are written
@@ -86,7 +86,9 @@ struct PWin {
     int n1x, n1y, base1;
     int n2x, n2y, base2;
     int vec;                // 16-byte hfun accesses are aligned in this window
+    int pad_[2];
 };
+static_assert(sizeof(PWin) % 16 == 0, "PWin is moved by cp.async.bulk");
 
 __device__ __forceinline__ int find_win(const PWin *wins, int n, int t, int level) {
     int lo = 0, hi = n - 1;
@@ -1188,7 +1190,8 @@ int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P) 
         OCSB_REQUIRE(n > 0 && sms > 0, "pass2_kernel does not fit an SM");
         resident[dev] = n * sms;
     }
-    const int grid = (int)std::min<long long>(P.n_tiles, (long long)resident[dev]);
+    const int grid = (int)std::min<long long>((P.n_tiles + kChunk - 1) / kChunk,
+                                              (long long)resident[dev]);
     kern<<<grid, kP2Threads, sizeof(P2Smem), ctx->stream>>>(tmap, P);
     return OCSB_OK;
 }
@@ -1312,12 +1315,23 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     // ---- vertex grid geometry (shared by the feature ops) ------------------------------
     const double ext_x = std::max(xmax - xmin, pix), ext_y = std::max(ymax - ymin, pix);
 
+    // ---- persistent pipeline (k_pass2.cuh) for the common shape of a pass: at
+    //      most one feature and one limiter op, fused clamps, TMA-able DEM
+    static const bool v2_on = [] {
+        const char *e = getenv("OCSB_PASS_V2");
+        return !(e && atoi(e) == 0);
+    }();
+    bool v2 = v2_on && d.nf <= 1 && d.nl <= 1 && (d.nl == 0 || use_tma) &&
+              n0 + 4096 < 0x7fffffffll;
+    for (int f = 0; f < d.nf; ++f) v2 = v2 && d.feats[f].fuse_clamp;
+    for (int l = 0; l < d.nl; ++l) v2 = v2 && d.lims[l].fuse_clamp;
+
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (nctr + 8) * sizeof(*ctrs), ctx->stream));
         TileArgs T;
         memset(&T, 0, sizeof(T));
-        const double2 *l1xy[kMaxFeat] = {};
+        double2 *slots0 = nullptr, *pool0 = nullptr;
         T.wins = d_wins; T.n_wins = d.n_wins;
         T.in = d.in; T.out = d.out;
         T.in_stride = d.in_stride; T.out_stride = d.out_stride;
@@ -1399,7 +1413,26 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             FeatDev &F = T.feat[f];
             F.verts = verts;
             F.off1 = B.l1.off; F.cnt1 = B.l1.cnt; F.ids1 = B.l1.ids;
-            l1xy[f] = B.l1.xy;
+            if (v2) {
+                // 64-px level: one slot per tile (+ overflow pool) for the persistent kernel
+                unsigned long long cap0 = 4ull * nv + 8ull * (unsigned long long)n0 + (1ull << 16);
+                cap0 <<= (2 * attempt);
+                if (async_mode) cap0 <<= 1;
+                cap0 = std::min<unsigned long long>(cap0, 0x7fffffffull);
+                OCSB_TRY(pools.get(&slots0, (size_t)n0 * kSlot));
+                OCSB_TRY(pools.get(&pool0, (size_t)cap0));
+                L0Args L;
+                L.wins = d_wins; L.n_wins = d.n_wins; L.n_tiles = (int)n0;
+                L.cnt1 = B.l1.cnt; L.off1 = B.l1.off; L.xy1 = B.l1.xy;
+                L.r2lim = r2lim;
+                L.slots = slots0; L.pool = pool0;
+                L.ctr = ctrs + 2 * kMaxFeat; L.cap = cap0;
+                L.overflow = overflow;
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                l0_kernel<<<(unsigned)((n0 + 7) / 8), 256, 0, ctx->stream>>>(L);
+                OCSB_LAUNCHED(ctx);
+                OCSB_CHECK_LAUNCH();
+            }
             F.rt = pf.rate_target; F.target = pf.target;
             F.r2 = (bounded && pf.r <= 0) ? -1.0 : r2;
             F.r2lim = r2lim;
@@ -1434,16 +1467,6 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             p.fuse_clamp = pl.fuse_clamp;
             T.lim_band[l] = (!ocsb_is_none(pl.lb) || !ocsb_is_none(pl.ub)) ? 1 : 0;
         }
-        // ---- persistent pipeline (k_pass2.cuh) for the common shape of a pass:
-        //      at most one feature and one limiter op, fused clamps, TMA-able DEM
-        static const bool v2_on = [] {
-            const char *e = getenv("OCSB_PASS_V2");
-            return !(e && atoi(e) == 0);
-        }();
-        bool v2 = v2_on && d.nf <= 1 && d.nl <= 1 && (d.nl == 0 || use_tma) &&
-                  n0 + 4096 < 0x7fffffffll;
-        for (int f = 0; f < d.nf; ++f) v2 = v2 && d.feats[f].fuse_clamp;
-        for (int l = 0; l < d.nl; ++l) v2 = v2 && d.lims[l].fuse_clamp;
         OCSB_TIME(ctx, KC_PASS_TILE);
         if (v2) {
             P2Args P;
@@ -1451,7 +1474,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             P.wins = d_wins; P.n_wins = d.n_wins; P.n_tiles = (int)n0;
             P.in = d.in; P.out = d.out;
             P.in_stride = d.in_stride; P.out_stride = d.out_stride;
-            if (d.nf) { P.feat = T.feat[0]; P.xy1 = l1xy[0]; }
+            if (d.nf) { P.feat = T.feat[0]; P.slots = slots0; P.pool0 = pool0; }
             if (d.nl) P.lim = T.lim[0];
             P.lo = T.lo; P.hi = T.hi;
             P.counter = reinterpret_cast<int *>(ctrs + nctr) + 4;

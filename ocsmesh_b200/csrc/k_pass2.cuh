@@ -1,27 +1,46 @@
 // K-pass, persistent form -- included INSIDE k_pass.cu's anonymous namespace.
 //
 // Same arithmetic as tile_kernel (one feature op and / or one limiter op, fused
-// clamp), organised as a persistent producer / consumer pipeline:
+// clamp), organised as a persistent producer / consumer pipeline in which the
+// eight warps of a CTA never meet at a CTA barrier:
 //
-//   * grid = resident CTAs only; tiles are handed out by one atomic counter
-//     (heavy tiles -- those with candidates -- cost ~2x a light one);
-//   * thread 0 is the producer: two tiles ahead it decodes the tile and looks
-//     up its parent list, one tile ahead it issues ONE mbarrier-tracked
-//     transaction per stage = the DEM box (cp.async.bulk.tensor.2d) plus the
-//     tile's parent candidate list (cp.async.bulk of cnt x double2).  So neither
-//     the DEM latency (light tiles used to expose all of it: nothing else to
-//     do) nor the dependent list loads (heavy tiles) are waited for;
-//   * one CTA barrier per light tile; interior tiles run a variant without any
-//     per-pixel bound or border test.
+//   * grid = resident CTAs only; 64x64-px tiles are handed out in chunks of 8
+//     by one atomic counter (a tile with candidates costs ~2x a tile without;
+//     one atomic per chunk: its latency is the producer's only stall);
+//   * thread 0 is the producer.  Two tiles ahead it issues ONE mbarrier-tracked
+//     transaction per stage (3-stage ring): the DEM box
+//     (cp.async.bulk.tensor.2d), the tile's candidate slot (512 B: header + up
+//     to 31 vertices, built by l0_kernel from the 256-px lists) and the window
+//     record (cp.async.bulk), so neither the DEM latency (light tiles have
+//     nothing else to hide it behind) nor dependent list loads are waited for;
+//   * consumers: a warp owns a 32x16 rect of the tile -- own coordinates, own
+//     filter of the slot to the rect, own pixels -- and hands the stage back
+//     through an "empty" mbarrier (8 arrivals).  Interior tiles run a variant
+//     without any per-pixel bound or border test.
 //
 // Reference: the window loops of ocsmesh/hfun/raster.py:1212-1260, 1393-1436.
 
+constexpr int kStages = 3;
 constexpr int kDemStage = 5024;      // floats per stage: 66 x 76 = 5016, padded to 128 B
-constexpr int kCand = 256;           // prefetched parent list (vertices)
+constexpr int kSlot = 32;            // double2 per tile slot: header + 31 candidates
+constexpr int kSlotCap = kSlot - 1;
+constexpr int kSurv2 = 32;           // survivors of a warp's rect kept in shared memory
 constexpr int kP2Threads = 256;
+constexpr int kP2Warps = kP2Threads / 32;
+#ifndef OCSB_PASS2_CHUNK
+#define OCSB_PASS2_CHUNK 8
+#endif
+constexpr int kChunk = OCSB_PASS2_CHUNK;   // consecutive tiles per fetch of the tile counter
+
+// slot header (16 bytes): candidates of the tile; more than kSlotCap live in the
+// overflow pool at element `off`
+struct SlotHead {
+    int cnt, pad;
+    long long off;
+};
 
 struct P2Info {
-    int t, wi, tx, ty, cnt, off, pad0, pad1;
+    int t, tx, ty, pad;
 };
 
 struct P2Args {
@@ -31,35 +50,34 @@ struct P2Args {
     float *out;
     long long in_stride, out_stride;
     FeatDev feat;
-    const double2 *xy1;     // level-1 lists as coordinates (same offsets as ids1)
+    const double2 *slots;   // n_tiles x kSlot
+    const double2 *pool0;   // overflow lists of the 64-px level
     LimiterDev<float> lim;
     float lo, hi;
     int *counter;           // zeroed before the launch
     const int *overflow;
 };
 
-struct __align__(128) P2Smem {
-    float dem[2][kDemStage];
-    double2 cand[2][kCand];
-    double2 v[kListCap];
-    WarpScr w[kP2Threads / 32];
-    double x[2][kT0], y[2][kT0];
-    PWin win[2];
-    P2Info info[2];
-    DomTable fin;
-    unsigned key[kP2Threads / 32][5];
-    int n;
-    int pend;
-    unsigned long long bar[2];
+struct W2Scr {
+    DomTable dom;           // 160 B
+    double2 sv[kSurv2];     // survivors of the warp's rect
+    double x[32], y[16];    // coordinates of the rect's columns / rows
 };
 
-__device__ __forceinline__ void p2_decode(const PWin *wins, int n_wins, int t, int &wi,
-                                          int &tx, int &ty) {
-    wi = n_wins == 1 ? 0 : find_win(wins, n_wins, t, 0);
-    const int lt = t - wins[wi].base0, n0x = wins[wi].n0x;
-    ty = lt / n0x;
-    tx = lt - ty * n0x;
-}
+struct __align__(128) P2Smem {
+    float dem[kStages][kDemStage];
+    double2 slot[kStages][kSlot];
+    PWin win[kStages];
+    P2Info info[kStages];
+    W2Scr w[kP2Warps];
+    unsigned long long full[kStages], empty[kStages];
+    // producer state: the chunk [q_next, q_end) being handed out, the decode of
+    // q_next (q_tx < 0: not decoded) and a cache of its window (tile -> window
+    // is monotone)
+    int q_next, q_end, q_tx, q_ty, ended;
+    int cur_wi, cur_base0, cur_n0x, cur_next;
+    int cur_demc, cur_demr;
+};
 
 __device__ __forceinline__ void p2_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
@@ -72,54 +90,81 @@ __device__ __forceinline__ void p2_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
-// the loads of one stage (producer thread): DEM box + parent candidate list
+__device__ __forceinline__ void p2_bulk(void *dst_smem, const void *src, uint32_t bytes,
+                                        uint32_t bar) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(dst_smem);
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1], %2, [%3];"
+        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// producer: the next tile -> stage (info, window record, slot, DEM box); past
+// the last tile it publishes the end marker instead
 template <bool HAS_FEAT, bool HAS_LIM>
-__device__ __forceinline__ void p2_issue(const CUtensorMap *tmap, const P2Args &A,
-                                         P2Smem &S, int stage) {
-    const P2Info I = S.info[stage];
-    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.bar[stage]);
-    const bool list = HAS_FEAT && I.cnt > 0 && I.cnt <= kCand;
-    uint32_t bytes = 0;
+__device__ __forceinline__ void p2_produce(const CUtensorMap *tmap, const P2Args &A,
+                                           P2Smem &S, int stage) {
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.full[stage]);
+    int t = S.q_next, tx = S.q_tx, ty = S.q_ty;
+    if (t == S.q_end) {
+        t = atomicAdd(A.counter, kChunk) + (int)gridDim.x * kChunk;
+        S.q_end = t + kChunk;
+        tx = -1;
+    }
+    if (t >= A.n_tiles) {
+        S.ended = 1;
+        S.info[stage].t = -1;
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        return;
+    }
+    if (t >= S.cur_next) {
+        int wi = S.cur_wi;
+        while (wi + 1 < A.n_wins && t >= A.wins[wi + 1].base0) ++wi;
+        const PWin &G = A.wins[wi];
+        S.cur_wi = wi; S.cur_base0 = G.base0; S.cur_n0x = G.n0x;
+        S.cur_next = wi + 1 < A.n_wins ? A.wins[wi + 1].base0 : 0x7fffffff;
+        S.cur_demc = G.dem_c; S.cur_demr = G.dem_r + G.rb;
+        tx = -1;
+    }
+    const int n0x = S.cur_n0x;
+    if (tx < 0) {
+        const int lt = t - S.cur_base0;
+        ty = lt / n0x;
+        tx = lt - ty * n0x;
+    }
+    P2Info I;
+    I.t = t; I.tx = tx; I.ty = ty; I.pad = 0;
+    S.info[stage] = I;
+    uint32_t bytes = (uint32_t)sizeof(PWin);
+    if (HAS_FEAT) bytes += (uint32_t)(kSlot * 16);
     if (HAS_LIM) bytes += (uint32_t)(kDemRows * kDemPitch * 4);
-    if (list) bytes += (uint32_t)I.cnt * 16u;
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                  ::"r"(bar), "r"(bytes) : "memory");
+    p2_bulk(&S.win[stage], &A.wins[S.cur_wi], (uint32_t)sizeof(PWin), bar);
+    if (HAS_FEAT) p2_bulk(&S.slot[stage][0], A.slots + (size_t)t * kSlot, kSlot * 16, bar);
     if (HAS_LIM) {
-        const PWin &G = A.wins[I.wi];
-        const int cx = G.dem_c + I.tx * kT0 - 4, cy = G.dem_r + G.rb + I.ty * kT0 - 1;
+        const int cx = S.cur_demc + tx * kT0 - 4, cy = S.cur_demr + ty * kT0 - 1;
         const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&S.dem[stage][0]);
         asm volatile(
             "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
             " [%0], [%1, {%2, %3}], [%4];"
             ::"r"(dst), "l"(tmap), "r"(cx), "r"(cy), "r"(bar) : "memory");
     }
-    if (list) {
-        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&S.cand[stage][0]);
-        asm volatile(
-            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes"
-            " [%0], [%1], %2, [%3];"
-            ::"r"(dst), "l"(A.xy1 + I.off), "r"((uint32_t)I.cnt * 16u), "r"(bar) : "memory");
-    }
-}
-
-// parent list of a tile: {cnt, off} (0, 0 without a feature op)
-template <bool HAS_FEAT>
-__device__ __forceinline__ int2 p2_parent(const P2Args &A, int wi, int tx, int ty) {
-    if (!HAS_FEAT) return make_int2(0, 0);
-    const PWin &G = A.wins[wi];
-    const int t1 = G.base1 + (ty >> 2) * G.n1x + (tx >> 2);
-    return make_int2(A.feat.cnt1[t1], A.feat.off1[t1]);
+    // the tile after this one (a window change re-decodes it)
+    S.q_next = t + 1;
+    if (++tx == n0x) { tx = 0; ++ty; }
+    S.q_tx = tx; S.q_ty = ty;
 }
 
 // ---- the pixels of one lane: 4 columns x 4 rows, two rows at a time -----------
 // FULL: the tile lies strictly inside its window (no border pixel, everything
 // written, 16-byte accesses aligned): no per-pixel test survives.
 template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND, bool FULL>
-__device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin &W,
-                                          int b, int c0t, int r0t, int lcol, int lrow,
-                                          int ntile, int ns, bool refilter, bool in_smem,
-                                          const double2 *glist, bool far, int lane,
-                                          WarpScr &WS, int sc0, int sr0, int sc1, int sr1) {
+__device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
+                                          const PWin &W, int c0t, int r0t, int lcol,
+                                          int lrow, int ntile, int ns, bool refilter,
+                                          const double2 *list, bool far, int lane,
+                                          W2Scr &WS, int sc0, int sr0, int sc1, int sr1) {
     const FeatDev &F = A.feat;
     const int bw = W.ax.n, rb = W.rb;
     const int gcol = c0t + lcol, grow = r0t + lrow;
@@ -130,7 +175,8 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin
     float *const out0 = A.out + W.hoff + (long long)(rb + grow) * A.out_stride + gcol;
     const float *const in0 =
         HAS_OLD ? A.in + W.hoff + (long long)(rb + grow) * A.in_stride + gcol : nullptr;
-    const double *sx = S.x[b], *sy = S.y[b];
+    // the warp's own coordinates: column sc0 + i -> WS.x[i], row sr0 + j -> WS.y[j]
+    const double *sx = WS.x + (lane & 7) * 4, *sy = WS.y + (lane >> 3) * 4;
 
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
@@ -144,11 +190,11 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin
             } else {
                 double px[4];
                 {
-                    const double2 a = *reinterpret_cast<const double2 *>(&sx[lcol]);
-                    const double2 c = *reinterpret_cast<const double2 *>(&sx[lcol + 2]);
+                    const double2 a = *reinterpret_cast<const double2 *>(&sx[0]);
+                    const double2 c = *reinterpret_cast<const double2 *>(&sx[2]);
                     px[0] = a.x; px[1] = a.y; px[2] = c.x; px[3] = c.y;
                 }
-                const double2 py = *reinterpret_cast<const double2 *>(&sy[lrow + half * 2]);
+                const double2 py = *reinterpret_cast<const double2 *>(&sy[half * 2]);
                 double best[8];
                 auto eval_one = [&](const double2 sv, bool first) {
                     double dx2[4];
@@ -176,13 +222,13 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin
                     }
                     for (int s = 1; s < ns; ++s) eval_one(WS.sv[s], false);
                 } else {
-                    // more than kSurv survivors: filter and evaluate chunk-wise
+                    // more than kSurv2 survivors: filter and evaluate chunk-wise
 #pragma unroll
                     for (int k = 0; k < 8; ++k) best[k] = kBig;
                     Rect q;
                     {
-                        const double xa = sx[sc0 - c0t], xb = sx[sc1 - c0t];
-                        const double ya = sy[sr0 - r0t], yb = sy[sr1 - r0t];
+                        const double xa = WS.x[0], xb = WS.x[sc1 - sc0];
+                        const double ya = WS.y[0], yb = WS.y[sr1 - sr0];
                         q.xlo = xa < xb ? xa : xb; q.xhi = xa < xb ? xb : xa;
                         q.ylo = ya < yb ? ya : yb; q.yhi = ya < yb ? yb : ya;
                     }
@@ -190,7 +236,7 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin
                         const int i = b0 + lane;
                         const bool valid = i < ntile;
                         double2 v = make_double2(0.0, 0.0);
-                        if (valid) v = in_smem ? S.v[i] : glist[i];
+                        if (valid) v = list[i];
                         const bool keep = valid && !(rect_d2(q, v) > F.r2lim) &&
                                           !dominated_tab(WS.dom, corner_d2(q, v));
                         const unsigned m = __ballot_sync(0xffffffffu, keep);
@@ -234,7 +280,7 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, P2Smem &S, const PWin
         // ---- limiter op ------------------------------------------------------------------
         if (HAS_LIM) {
             const int H = W.ay.n;
-            const float *sd = &S.dem[b][0] + (lrow + half * 2) * kDemPitch + 4 + lcol;
+            const float *sd = sdem + (lrow + half * 2) * kDemPitch + 4 + lcol;
             float4 rowv[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -319,162 +365,71 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int lcol = (wid & 1) * 32 + (lane & 7) * 4;      // tile-local
     const int lrow = (wid >> 1) * 16 + (lane >> 3) * 4;
-    WarpScr &WS = S.w[wid];
+    W2Scr &WS = S.w[wid];
     const FeatDev &F = A.feat;
-    const int grid = gridDim.x;
 
-    // ---- producer prologue: tiles of iterations 0 and 1, loads of iteration 0 ---------
+    // ---- producer prologue: stages of iterations 0 and 1 --------------------------------
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.bar[s]);
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        for (int s = 0; s < kStages; ++s) {
+            const uint32_t fb = (uint32_t)__cvta_generic_to_shared(&S.full[s]);
+            const uint32_t eb = (uint32_t)__cvta_generic_to_shared(&S.empty[s]);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(fb));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(eb), "r"(kP2Warps));
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            P2Info I;
-            I.t = (int)blockIdx.x + s * grid;
-            I.wi = I.tx = I.ty = I.cnt = I.off = I.pad0 = I.pad1 = 0;
-            if (I.t < A.n_tiles) {
-                p2_decode(A.wins, A.n_wins, I.t, I.wi, I.tx, I.ty);
-                const int2 pl = p2_parent<HAS_FEAT>(A, I.wi, I.tx, I.ty);
-                I.cnt = pl.x; I.off = pl.y;
-            } else {
-                I.t = -1;
-            }
-            S.info[s] = I;
-        }
-        S.pend = atomicAdd(A.counter, 1) + 2 * grid;
-        p2_issue<HAS_FEAT, HAS_LIM>(&tmap, A, S, 0);
+        S.cur_wi = 0; S.cur_next = -1;       // forces the first window lookup
+        S.q_next = (int)blockIdx.x * kChunk;   // the first chunk is static
+        S.q_end = S.q_next + kChunk;
+        S.q_tx = -1; S.q_ty = 0; S.ended = 0;
+        p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 0);
+        if (!S.ended) p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 1);
     }
-    __syncthreads();
+    __syncthreads();         // barrier words initialised before anyone polls them
 
     for (int it = 0;; ++it) {
-        const int b = it & 1;
-        const P2Info I = S.info[b];
+        const int s = it % kStages;
+        const uint32_t use = (uint32_t)(it / kStages);
+        // ---- producer: stage of iteration it + 2 ------------------------------------------------
+        if (threadIdx.x == 0 && !S.ended) {
+            const int s2 = (it + 2) % kStages;
+            if (it >= 1) {
+                // its previous use was iteration it - 1: wait until all warps left it
+                const uint32_t eb = (uint32_t)__cvta_generic_to_shared(&S.empty[s2]);
+                p2_wait(eb, (uint32_t)((it - 1) / kStages) & 1u);
+            }
+            p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, s2);
+        }
+        __syncwarp();
+        // ---- consumer: wait for the stage ----------------------------------------------------
+        p2_wait((uint32_t)__cvta_generic_to_shared(&S.full[s]), use & 1u);
+        const P2Info I = S.info[s];
         if (I.t < 0) break;
+        const PWin &W = S.win[s];
         const int c0t = I.tx * kT0, r0t = I.ty * kT0;
-        // ---- window record + coordinates of the tile's columns / rows -----------------
-        {
-            const PWin &G = A.wins[I.wi];
-            if (threadIdx.x < kT0) {
-                S.x[b][threadIdx.x] = lin_at(G.ax, min(c0t + (int)threadIdx.x, G.ax.n - 1));
-            } else if (threadIdx.x < 2 * kT0) {
-                const int j = threadIdx.x - kT0;
-                S.y[b][j] = lin_at(G.ay, G.rb + min(r0t + j, G.re - G.rb - 1));
-            } else if (threadIdx.x < 2 * kT0 + (int)(sizeof(PWin) / 4)) {
-                const int i = threadIdx.x - 2 * kT0;
-                reinterpret_cast<int *>(&S.win[b])[i] = reinterpret_cast<const int *>(&G)[i];
-            }
-        }
-        __syncthreads();                                   // (1)
-        // ---- producer: loads of iteration it+1, tile of iteration it+2 ---------------
-        if (threadIdx.x == 0) {
-            if (S.info[b ^ 1].t >= 0) p2_issue<HAS_FEAT, HAS_LIM>(&tmap, A, S, b ^ 1);
-            P2Info N;
-            N.t = S.pend;
-            N.wi = N.tx = N.ty = N.cnt = N.off = N.pad0 = N.pad1 = 0;
-            if (N.t < A.n_tiles) {
-                p2_decode(A.wins, A.n_wins, N.t, N.wi, N.tx, N.ty);
-                const int2 pl = p2_parent<HAS_FEAT>(A, N.wi, N.tx, N.ty);
-                S.pend = atomicAdd(A.counter, 1) + 2 * grid;
-                N.cnt = pl.x; N.off = pl.y;
-            } else {
-                N.t = -1;
-            }
-            // slot b: every thread has read I (they all passed barrier 1)
-            S.info[b] = N;
-        }
-        const PWin &W = S.win[b];
         const int bw = W.ax.n, rb = W.rb, bh = W.re - rb;
-        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.bar[b]);
-        const uint32_t parity = (uint32_t)(it >> 1) & 1u;
-        bool waited = false;
-
-        // ---- feature op: parent list -> tile list ------------------------------------------
-        int ntile = 0;
-        bool in_smem = true;
-        const double2 *glist = nullptr;
-        if (HAS_FEAT && I.cnt > 0) {
-            const int pcnt = I.cnt;
-            const bool staged = pcnt <= kCand;
-            const double2 *gsrc = A.xy1 + I.off;
-            if (staged) { p2_wait(bar, parity); waited = true; }
-            auto pcand = [&](int i) -> double2 { return staged ? S.cand[b][i] : gsrc[i]; };
-            Rect qT;
-            {
-                const int tc1 = min(bw, c0t + kT0) - 1 - c0t;
-                const int tr1 = min(bh, r0t + kT0) - 1 - r0t;
-                const double xa = S.x[b][0], xb = S.x[b][tc1];
-                const double ya = S.y[b][0], yb = S.y[b][tr1];
-                qT.xlo = xa < xb ? xa : xb; qT.xhi = xa < xb ? xb : xa;
-                qT.ylo = ya < yb ? ya : yb; qT.yhi = ya < yb ? yb : ya;
-            }
-            unsigned key[5];
-#pragma unroll
-            for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
-            for (int b0 = wid * 32; b0 < pcnt; b0 += kP2Threads) {
-                const int i = b0 + lane;
-                const bool valid = i < pcnt;
-                double2 v = make_double2(0.0, 0.0);
-                if (valid) v = pcand(i);
-                dom_step(qT, valid, v, key, WS.dom, lane);
-            }
-            __syncwarp();
-            if (threadIdx.x == 0) S.n = 0;
-            if (lane < 5) {
-                unsigned k = 0;
-#pragma unroll
-                for (int j = 0; j < 5; ++j) if (lane == j) k = key[j];
-                S.key[wid][lane] = k;
-            }
-            __syncthreads();                               // (2)
-            if (threadIdx.x < 5) {
-                unsigned best = 0xffffffffu;
-                int bwp = 0;
-                for (int w = 0; w < kP2Threads / 32; ++w)
-                    if (S.key[w][threadIdx.x] < best) { best = S.key[w][threadIdx.x]; bwp = w; }
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    S.fin.c[threadIdx.x][c] = S.w[bwp].dom.c[threadIdx.x][c];
-            }
-            __syncthreads();                               // (3)
-            for (int b0 = wid * 32; b0 < pcnt; b0 += kP2Threads) {
-                const int i = b0 + lane;
-                const bool valid = i < pcnt;
-                double2 v = make_double2(0.0, 0.0);
-                if (valid) v = pcand(i);
-                const bool keep = valid && !(rect_d2(qT, v) > F.r2lim) &&
-                                  !dominated_tab(S.fin, corner_d2(qT, v));
-                const unsigned m = __ballot_sync(0xffffffffu, keep);
-                int base = 0;
-                if (lane == 0 && m) base = atomicAdd(&S.n, __popc(m));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                const int pos = base + __popc(m & ((1u << lane) - 1u));
-                if (keep && pos < kListCap) S.v[pos] = v;
-            }
-            __syncthreads();                               // (4)
-            ntile = S.n;
-            if (ntile > kListCap) {
-                // the parent list itself (its coordinates are in global memory)
-                in_smem = false; ntile = pcnt; glist = gsrc;
-            }
-        }
-
-        // ---- this warp's 32x16 rect -------------------------------------------------------
         const int sc0 = c0t + (wid & 1) * 32, sr0 = r0t + (wid >> 1) * 16;
         const bool sub_valid = sc0 < bw && sr0 < bh;
-        const int sc1 = min(bw, sc0 + 32) - 1, sr1 = min(bh, sr0 + 16) - 1;
         if (sub_valid) {
-            int ns = 0;
+            const int sc1 = min(bw, sc0 + 32) - 1, sr1 = min(bh, sr0 + 16) - 1;
+            int ntile = 0, ns = 0;
             bool refilter = false;
+            const double2 *list = &S.slot[s][1];
+            if (HAS_FEAT) {
+                const SlotHead hd = *reinterpret_cast<const SlotHead *>(&S.slot[s][0]);
+                ntile = hd.cnt;
+                if (ntile > kSlotCap) list = A.pool0 + hd.off;
+            }
             if (HAS_FEAT && ntile > 0) {
+                // the rect's coordinates (the linspace of the window, bit-exact)
+                WS.x[lane] = lin_at(W.ax, min(sc0 + lane, bw - 1));
+                if (lane < 16) WS.y[lane] = lin_at(W.ay, rb + min(sr0 + lane, bh - 1));
+                __syncwarp();
                 Rect q;
                 {
-                    const double xa = S.x[b][sc0 - c0t], xb = S.x[b][sc1 - c0t];
-                    const double ya = S.y[b][sr0 - r0t], yb = S.y[b][sr1 - r0t];
+                    const double xa = WS.x[0], xb = WS.x[sc1 - sc0];
+                    const double ya = WS.y[0], yb = WS.y[sr1 - sr0];
                     q.xlo = xa < xb ? xa : xb; q.xhi = xa < xb ? xb : xa;
                     q.ylo = ya < yb ? ya : yb; q.yhi = ya < yb ? yb : ya;
                 }
@@ -485,7 +440,7 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
                     const int i = b0 + lane;
                     const bool valid = i < ntile;
                     double2 v = make_double2(0.0, 0.0);
-                    if (valid) v = in_smem ? S.v[i] : glist[i];
+                    if (valid) v = list[i];
                     dom_step(q, valid, v, key, WS.dom, lane);
                 }
                 __syncwarp();
@@ -493,33 +448,125 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
                     const int i = b0 + lane;
                     const bool valid = i < ntile;
                     double2 v = make_double2(0.0, 0.0);
-                    if (valid) v = in_smem ? S.v[i] : glist[i];
+                    if (valid) v = list[i];
                     const bool keep = valid && !(rect_d2(q, v) > F.r2lim) &&
                                       !dominated_tab(WS.dom, corner_d2(q, v));
                     const unsigned m = __ballot_sync(0xffffffffu, keep);
                     const int n = __popc(m);
-                    if (ns + n > kSurv) { refilter = true; break; }
+                    if (ns + n > kSurv2) { refilter = true; break; }
                     if (keep) WS.sv[ns + __popc(m & ((1u << lane) - 1u))] = v;
                     ns += n;
                 }
                 __syncwarp();
             }
-            if (HAS_LIM && !waited) { p2_wait(bar, parity); waited = true; }
             // strictly inside the window, fully written, aligned
             const bool full = W.vec && c0t >= 1 && c0t + kT0 <= min(bw - 1, W.keep_w) &&
                               rb + r0t >= 1 && r0t + kT0 <= bh &&
                               rb + r0t + kT0 <= min(W.ay.n - 1, W.keep_h);
             if (full)
                 p2_pixels<HAS_OLD, HAS_FEAT, HAS_LIM, BAND, true>(
-                    A, S, W, b, c0t, r0t, lcol, lrow, ntile, ns, refilter, in_smem, glist,
-                    far, lane, WS, sc0, sr0, sc1, sr1);
+                    A, &S.dem[s][0], W, c0t, r0t, lcol, lrow, ntile, ns, refilter, list, far,
+                    lane, WS, sc0, sr0, sc1, sr1);
             else
                 p2_pixels<HAS_OLD, HAS_FEAT, HAS_LIM, BAND, false>(
-                    A, S, W, b, c0t, r0t, lcol, lrow, ntile, ns, refilter, in_smem, glist,
-                    far, lane, WS, sc0, sr0, sc1, sr1);
+                    A, &S.dem[s][0], W, c0t, r0t, lcol, lrow, ntile, ns, refilter, list, far,
+                    lane, WS, sc0, sr0, sc1, sr1);
         }
-        // every thread observes the stage's phase (a thread that skipped the wait
-        // could otherwise run a whole phase ahead of the barrier)
-        if (!waited) p2_wait(bar, parity);
+        // ---- hand the stage back -------------------------------------------------------------------
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t eb = (uint32_t)__cvta_generic_to_shared(&S.empty[s]);
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(eb) : "memory");
+        }
     }
+}
+
+// ---------------------------------------------------------------------------
+// level 0: the slot of every 64-px tile from its 256-px parent list (one warp
+// per tile; tiles without a parent list get an empty header)
+// ---------------------------------------------------------------------------
+struct L0Args {
+    const PWin *wins;
+    int n_wins, n_tiles;
+    const int *cnt1, *off1;
+    const double2 *xy1;
+    double r2lim;
+    double2 *slots, *pool;
+    unsigned long long *ctr;
+    unsigned long long cap;
+    int *overflow;
+};
+
+__global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
+    __shared__ DomTable s_tab[8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int t = blockIdx.x * 8 + wid;
+    if (t >= A.n_tiles || *A.overflow) return;
+    const int wi = A.n_wins == 1 ? 0 : find_win(A.wins, A.n_wins, t, 0);
+    const PWin &W = A.wins[wi];
+    const int lt = t - W.base0;
+    const int ty = lt / W.n0x, tx = lt - ty * W.n0x;
+    const int t1 = W.base1 + (ty >> 2) * W.n1x + (tx >> 2);
+    const int pcnt = A.cnt1[t1], poff = A.off1[t1];
+    double2 *slot = A.slots + (size_t)t * kSlot;
+    SlotHead hd;
+    hd.cnt = 0; hd.pad = 0; hd.off = 0;
+    if (pcnt == 0) {
+        if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
+        return;
+    }
+    const int bw = W.ax.n, bh = W.re - W.rb;
+    const int c0 = tx * kT0, r0 = ty * kT0;
+    const Rect q = win_rect(W, c0, min(bw, c0 + kT0) - 1, r0, min(bh, r0 + kT0) - 1);
+    const double2 *src = A.xy1 + poff;
+    DomTable &tab = s_tab[wid];
+    unsigned key[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
+    for (int b0 = 0; b0 < pcnt; b0 += 32) {
+        const int i = b0 + lane;
+        const bool valid = i < pcnt;
+        double2 v = make_double2(0.0, 0.0);
+        if (valid) v = src[i];
+        dom_step(q, valid, v, key, tab, lane);
+    }
+    __syncwarp();
+    int total = 0;
+    for (int b0 = 0; b0 < pcnt; b0 += 32) {
+        const int i = b0 + lane;
+        const bool valid = i < pcnt;
+        double2 v = make_double2(0.0, 0.0);
+        if (valid) v = src[i];
+        const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                          !dominated_tab(tab, corner_d2(q, v));
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        const int pos = total + __popc(m & ((1u << lane) - 1u));
+        if (keep && pos < kSlotCap) slot[1 + pos] = v;
+        total += __popc(m);
+    }
+    if (total > kSlotCap) {
+        // the whole list goes to the overflow pool (contiguous)
+        unsigned long long base = 0;
+        if (lane == 0) {
+            base = atomicAdd(A.ctr, (unsigned long long)total);
+            if (base + total > A.cap) { *A.overflow = 1; base = ~0ull; }
+        }
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base == ~0ull) return;
+        int w = 0;
+        for (int b0 = 0; b0 < pcnt; b0 += 32) {
+            const int i = b0 + lane;
+            const bool valid = i < pcnt;
+            double2 v = make_double2(0.0, 0.0);
+            if (valid) v = src[i];
+            const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                              !dominated_tab(tab, corner_d2(q, v));
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) A.pool[base + w + __popc(m & ((1u << lane) - 1u))] = v;
+            w += __popc(m);
+        }
+        hd.off = (long long)base;
+    }
+    hd.cnt = total;
+    if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
 }
