@@ -3,26 +3,32 @@
 
     python bench.py --gpus N --steps K --warmup W [--impl reference]
 
-Workload (BASELINE.json configs[1], per GPU): synthetic 20000 x 20000 float32
-DEM (10 m pixels, projected CRS), one "step" = one full HfunRaster pass:
-FLT_MAX init fill + add_contour at 3 levels (-5, 0, 5; expansion_rate 0.001,
-target_size 100, hmin 100, hmax 1500) + add_gradient_delimiter (hmin 50, hmax
-1500).  The contour polylines are traced and resampled once on the host before
-the timed region: the accelerated path starts at the resampled vertex array
-(reference ocsmesh/hfun/raster.py:1230), contour tracing is the CPU step
-before it.
+Workload (BASELINE.json configs[1]): ONE synthetic 20000 x 20000 float32 DEM
+(10 m pixels, projected CRS); one "step" = one full HfunRaster pass: FLT_MAX
+init + add_contour at 3 levels (-5, 0, 5; expansion_rate 0.001, target_size
+100, hmin 100, hmax 1500) + add_gradient_delimiter (hmin 50, hmax 1500), run as
+ONE tiled sweep over the raster (HfunRaster(deferred=True): the add_* calls are
+queued, flush() enqueues the sweep).  The contour polylines are traced and
+resampled once on the host before the timed region: the accelerated path starts
+at the resampled vertex array (reference ocsmesh/hfun/raster.py:1230), contour
+tracing is the CPU step before it.
 
   value : Mpx/s, whole job, DEM + vertices + hfun resident in HBM
   e2e   : Mpx/s through the public API (ocsmesh_b200.Raster / Hfun) with HOST
           buffers: DEM and vertices H2D from pinned memory and the size raster
           D2H inside the timed region
-  secondary.interp : Mesh.interpolate of a 10 M-node cloud from 16 DEM tiles
-          (BASELINE.json configs[3]) in Mnodes/s, linear and nearest
+  secondary.interp  : Mesh.interpolate of a 10 M-node cloud from 16 DEM tiles
+          (BASELINE.json configs[3]) in Mnodes/s, linear / nearest / spline
+  secondary.windows : the same pass on the raster chunked into semantic windows
+  secondary.weak    : (N > 1) the round-1 weak-scaling run, 20000 rows per GPU
 
-N > 1 (weak scaling): the raster is N x 20000 rows tall, each rank owns one
-20000-row band (one semantic window = the whole raster, so coordinates and
-radius law are global); per step the ranks all-gather their contour vertices
-and exchange 1-row DEM halos over NCCL, then run the same kernels on their band.
+N > 1 is STRONG scaling: the same 20000 x 20000 raster split into N row bands
+(2500 rows per GPU at N = 8; one semantic window = the whole raster, so
+coordinates and radius law are global).  Every step the ranks all-gather the
+contour vertices they traced on their own bands and their boundary DEM rows
+over NCCL (two collectives into persistent buffers), then run the sweep on
+their band.  After the timed region every rank checks sampled rows of its band
+bit-exactly against the oracle (cKDTree + numpy stencil): "parity_checked".
 """
 from __future__ import annotations
 
@@ -43,8 +49,10 @@ LEVELS = [-5.0, 0.0, 5.0]
 RATE, TARGET, HMIN, HMAX = 0.001, 100.0, 100.0, 1500.0
 LIM_HMIN, LIM_HMAX = 50.0, 1500.0
 SEED = 2
+# algorithmic bytes per pixel
 BYTES_PER_PX = {"feature_eval": 8.0, "flow_limiter": 12.0, "fill": 4.0,
-                "clamp": 8.0}
+                "clamp": 8.0, "pass_tile": 12.0}
+PASS_BYTES_PER_PX = 12.0
 
 
 def parse_args():
@@ -54,19 +62,23 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--size", type=int, default=20000,
-                    help="DEM rows per GPU and columns")
+                    help="DEM rows and columns (the whole raster)")
     ap.add_argument("--nodes", type=int, default=10_000_000)
     ap.add_argument("--tile", type=int, default=5000, help="interp DEM tile size")
-    ap.add_argument("--cpu-sample", type=int, default=3000,
-                    help="edge of the square crop timed on the CPU")
+    ap.add_argument("--cpu-sample", type=int, default=8000,
+                    help="edge of the square crop timed on the CPU (>= 8000: "
+                         "SURVEY.md 8(d) asks for a >= 64 Mpx crop)")
     ap.add_argument("--no-interp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-windows", action="store_true")
+    ap.add_argument("--no-weak", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-numa", action="store_true",
                     help="do not bind ranks to their GPU's local CPUs")
-    ap.add_argument("--deferred", action="store_true",
-                    help="device-resident leg through the queued op list "
-                         "(ocsb_hfun_pass) instead of the eager add_* calls")
+    ap.add_argument("--eager", action="store_true",
+                    help="device-resident leg through the eager add_* calls "
+                         "(one sweep per op) instead of the queued op list")
     return ap.parse_args()
 
 
@@ -90,21 +102,24 @@ def host_dem(height, width, seed, rows=None, pin=True, full_height=None):
     return t
 
 
-def contour_points(z, transform, row0=0):
-    """Contours at LEVELS of the DEM block z (whose first row is raster row
-    row0), resampled to TARGET spacing: the (N, 2) vertex array."""
+def contour_points(z, transform, full_height, row0=0, native=True):
+    """Contours at LEVELS of the DEM rows z = raster rows [row0, row0 + len(z))
+    of a raster full_height rows tall, placed with the coordinates of the
+    WHOLE raster (Raster.get_x / get_y of the full window), resampled to TARGET
+    spacing: the (N, 2) vertex array.  A rank that owns rows [b0, b1) passes
+    rows [b0, b1 + 1) (one halo row), so the cell rows of the bands partition
+    the cell rows of the raster: the union of the ranks' polylines is the
+    whole-raster contour cut at the band boundaries (each piece is resampled
+    on its own, which is the vertex-set definition of an N-rank run)."""
     from ocsmesh_b200 import features as F
     h, w = z.shape
     a, _, c, _, e, f = transform
-    # the coordinates Raster.get_x / get_y give for a whole-raster window
-    # restricted to these rows are only needed to place the crossings: use
-    # pixel-centre style linspace over the block's edge bounds like get_x/get_y
     x = np.linspace(c, c + a * w, w)
-    y = np.linspace(f + e * row0, f + e * (row0 + h), h)
+    y = np.linspace(f, f + e * full_height, full_height)[row0:row0 + h]
     lines = []
     for lv in LEVELS:
         lines.extend(F.marching_squares(x, y, z, lv))
-    return F.feature_points(lines, TARGET)
+    return F.feature_points(lines, TARGET, native=native)
 
 
 class ClockSampler:
@@ -215,20 +230,29 @@ def cpu_hfun_sample(z, transform, points, sample, repeats=1):
     return n * n / best / 1e6, best, cores, oh.values
 
 
+def cpu_sample_text(n, nv, dt=None):
+    s = (f"top-left {n}x{n} crop of the DEM as its own raster, the FULL "
+         f"{nv}-vertex contour set of the 20000^2 raster, "
+         "scipy cKDTree.query(workers=-1) + numpy stencil")
+    if dt is not None:
+        s += f", one pass {dt:.2f} s"
+    return s
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (oracle port) on the host
-    cores; under torchrun rank 0 alone runs it."""
+    """--impl reference: the reference's CPU path (oracle port: the same
+    scipy / numpy calls with the same arguments) on the host cores; under
+    torchrun rank 0 alone runs it.  Nothing here loads libocsb200.so: the
+    vertex set comes from the numpy prologue."""
     if rank != 0:
         return
     size = args.size
     from ocsmesh_b200 import synthetic as S
-    tr = S.dem_transform(size * world)
+    tr = S.dem_transform(size)
     n = min(args.cpu_sample, size)
-    # the sample is the top-left n x n crop of rank 0's band; contours come
-    # from a (n + 2000)-row strip so the crop sees realistic vertex density
-    strip = min(size, n + 2000)
-    z = host_dem(size * world, size, SEED, rows=(0, strip), pin=False).numpy()
-    pts = contour_points(z, tr)
+    z = host_dem(size, size, SEED, pin=False).numpy()
+    pts = contour_points(z, tr, size, native=False)
+    z = np.ascontiguousarray(z[:n, :n])
     times = []
     for i in range(args.warmup + args.steps):
         mpx, dt, cores, _ = cpu_hfun_sample(z, tr, pts, n)
@@ -240,14 +264,12 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "hfun_raster_pass_throughput",
         "value": val, "unit": "Mpx/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64 distance / f32 size",
-        "data": "synthetic",
-        "config": workload_config(args, world, sample=f"{n}x{n} crop"),
+        "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64 distance / f32 size", "data": "synthetic",
+        "config": workload_config(args, world),
+        "n_vertices": int(len(pts)),
         "cpu_baseline": {"value": val, "unit": "Mpx/s", "cores": cores,
-                         "kind": "port",
-                         "sample": f"top-left {n}x{n} crop of the DEM, "
-                                   f"{len(pts)} contour vertices of a "
-                                   f"{strip}-row strip, scipy cKDTree workers=-1"},
+                         "kind": "port", "sample": cpu_sample_text(n, len(pts))},
         "e2e": {"value": val, "unit": "Mpx/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -255,28 +277,140 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, world, sample=None):
-    cfg = {
-        "workload": (f"BASELINE.json configs[1]: synthetic {args.size * world}x"
-                     f"{args.size} f32 DEM ({args.size} rows per GPU), "
-                     "HfunRaster full pass = init fill + add_contour(levels "
-                     f"{LEVELS}, rate {RATE}, target {TARGET}, hmin {HMIN}, "
-                     f"hmax {HMAX}) + add_gradient_delimiter(hmin {LIM_HMIN}, "
-                     f"hmax {LIM_HMAX})"),
-        "px_per_gpu": args.size * args.size,
-        "parallelism": f"row bands x{world}",
-        "l2": "inputs (DEM + hfun, 3.2 GB per GPU) exceed the 126 MB L2",
+def workload_config(args, world):
+    """Identical in both arms (the reference arm times a bounded sample of the
+    same workload; the sample is described in its cpu_baseline)."""
+    return {
+        "workload": (f"BASELINE.json configs[1]: synthetic {args.size}x"
+                     f"{args.size} f32 DEM, HfunRaster full pass = init fill + "
+                     f"add_contour(levels {LEVELS}, rate {RATE}, target {TARGET}, "
+                     f"hmin {HMIN}, hmax {HMAX}) + add_gradient_delimiter(hmin "
+                     f"{LIM_HMIN}, hmax {LIM_HMAX})"),
+        "px": args.size * args.size,
+        "l2": "inputs (DEM + hfun, 3.2 GB) exceed the 126 MB L2",
         "contours": "traced + resampled on the host once, outside the timed "
                     "region (parity boundary hfun/raster.py:1230)",
     }
-    if sample:
-        cfg["sample"] = sample
-    return cfg
 
 
 # ---------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------
+class BandRun:
+    """One rank's share of an H x W raster split into `world` row bands: host
+    and device inputs, the exchange buffers, the queued-op HfunRaster."""
+
+    def __init__(self, args, H, W, rank, world, dev, eager=False, chunk=None,
+                 overlap=None):
+        import torch
+        import ocsmesh_b200 as ob
+        from ocsmesh_b200 import synthetic as S, distributed as D
+        self.H, self.W, self.rank, self.world, self.dev = H, W, rank, world, dev
+        self.tr = S.dem_transform(H)
+        self.part = D.RowBands(H, world)
+        self.b0, self.b1 = self.part.band(rank)
+        self.s0, self.s1 = self.part.stored(rank)
+        # host: the band plus one halo row per side (what a rank reading its
+        # rows of the GeoTIFF would over-read)
+        self.z_host = host_dem(H, W, SEED, rows=(self.s0, self.s1), full_height=H)
+        zb = self.z_host.numpy()
+        c1 = min(self.b1 + 1, H)
+        self.pts_local = contour_points(zb[self.b0 - self.s0:c1 - self.s0], self.tr,
+                                        H, row0=self.b0)
+        self.pts_pinned = torch.from_numpy(self.pts_local).pin_memory()
+        self.raster = D.band_raster(zb[self.b0 - self.s0:self.b1 - self.s0], self.tr,
+                                    H, self.part, rank, crs=32618, device=dev)
+        if chunk is not None:
+            self.raster.chunk_size = chunk
+            self.raster.overlap = overlap
+        self.hfun = ob.HfunRaster(self.raster, hmin=HMIN, hmax=HMAX, device=dev,
+                                  row_band=(self.b0, self.b1), deferred=not eager)
+        self.verts_local = self.pts_pinned.to(f"cuda:{dev}")
+        self.exch = D.BandExchange(len(self.pts_local), W, torch.float32,
+                                   f"cuda:{dev}", self.part, rank)
+        self.nv_total = int(sum(self.exch.sizes))
+
+    def step(self):
+        """A4 init, vertex all-gather, DEM halo rows, A6/A7 + A8(A9): one sweep."""
+        h = self.hfun
+        h.reset()
+        verts = self.exch.gather_vertices(self.verts_local)
+        self.exch.exchange_halo(self.raster.device_band(1, self.dev),
+                                self.raster.device_band_origin(1, self.dev))
+        h.add_feature_points(verts, RATE, TARGET)
+        h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+        h.flush()
+
+    def check_parity(self, n_rows=4, seed=0):
+        """Sampled rows of this rank's band against the oracle, bit-exact: the
+        nearest-vertex distance of every pixel of the row from an exact
+        cKDTree query over the REAL gathered vertices, the size law and clamps
+        restated from hfun/raster.py:1240-1257, then the numpy stencil on the
+        3-row strip (np.gradient is local).  Returns the number of pixels."""
+        import torch
+        from oracle import ocsmesh_oracle as O
+        self.hfun.sync()
+        got_all = self.hfun.device_values
+        verts = self.exch.gather_vertices(self.verts_local)
+        pts = self.exch.real_vertices(verts).cpu().numpy()
+        H, W = self.H, self.W
+        b = O.array_bounds(H, W, self.tr)
+        x = np.linspace(b[0], b[2], W)
+        y = np.linspace(b[3], b[1], H)
+        rng = np.random.default_rng(seed + 17 * self.rank)
+        lo, hi = max(self.b0, 1), min(self.b1, H - 1)
+        rows = sorted(set(rng.integers(lo, hi, n_rows).tolist()) |
+                      {lo, hi - 1})          # incl. the rows next to the band edges
+        zb = self.z_host.numpy()
+        n_px = 0
+        for r in rows:
+            strip = zb[r - 1 - self.s0:r + 2 - self.s0]
+            yy = y[r - 1:r + 2]
+            xy = np.stack([np.tile(x, 3), np.repeat(yy, W)], axis=1)
+            old = np.full((3, W), np.finfo(np.float32).max, np.float32)
+            feat = O.add_feature_window(old, pts, xy, 3, W, RATE, TARGET, HMIN, HMAX)
+            feat = O.apply_constraints_clamp(feat, HMIN, HMAX)
+            ref = O.flow_limiter_window(strip, feat, self.raster.dx, self.raster.dy,
+                                        LIM_HMIN, LIM_HMAX, None, None, HMIN, HMAX)
+            ref = O.apply_constraints_clamp(np.ma.getdata(ref), HMIN, HMAX)[1]
+            got = got_all[r - self.b0].cpu().numpy()
+            if not np.array_equal(got, ref):
+                bad = int(np.flatnonzero(got != ref)[0])
+                raise AssertionError(
+                    f"rank {self.rank}: row {r} differs from the oracle at column "
+                    f"{bad}: {got[bad]!r} vs {ref[bad]!r}")
+            n_px += W
+        return n_px
+
+
+def time_steps(fn, n, dev, world):
+    """ms per step: CUDA events around n steps, barrier + synchronize on both
+    sides, max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    barrier()
+    t1 = time.perf_counter()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        tt = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    return ms / n, t0, t1
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -288,45 +422,13 @@ def run_ours(args, rank, world, local_rank):
     # multi-rank: pinned staging buffers on the NUMA node of the rank's GPU
     numa = D.bind_to_gpu_numa(dev) if (world > 1 and not args.no_numa) else None
     ctx = _lib.default_context(dev)
-    size, W = args.size, args.size
-    H = size * world
-    tr = S.dem_transform(H)
-    r0, r1 = rank * size, (rank + 1) * size
+    size = args.size
+    H = W = size
 
-    # ---- inputs (outside the timed region) --------------------------------
-    z_host = host_dem(H, W, SEED, rows=(r0, r1), full_height=H)
-    pts_local = contour_points(z_host.numpy(), tr, row0=r0)
-    pts_pinned = torch.from_numpy(pts_local).pin_memory()
-
-    part = D.RowBands(H, world)
-    raster = D.band_raster(z_host.numpy(), tr, H, part, rank, crs=32618,
-                           device=dev)
-    hfun = ob.HfunRaster(raster, hmin=HMIN, hmax=HMAX, device=dev,
-                         row_band=part.band(rank), deferred=args.deferred)
-    verts_local = pts_pinned.to(f"cuda:{dev}")
-    # the ranks' vertex counts are fixed by the (untimed) contour tracing: they
-    # are exchanged once; the vertex all-gather itself stays inside every step
-    vsizes = D.gather_sizes(len(pts_local), f"cuda:{dev}") if world > 1 else None
-
-    def step():
-        # A4 init fill, vertex all-gather, DEM halo rows, A6/A7, A8(A9)
-        hfun.reset()
-        verts = (D.all_gather_vertices(verts_local, sizes=vsizes) if world > 1
-                 else verts_local)
-        if world > 1:
-            D.exchange_dem_halo(raster, part, rank, dev)
-        hfun.add_feature_points(verts, RATE, TARGET)
-        hfun.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
-        hfun.flush()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
+    run = BandRun(args, H, W, rank, world, dev, eager=args.eager)
+    nv_total = run.nv_total
     for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
+        run.step()
 
     # ---- timed: device-resident -------------------------------------------
     sampler = ClockSampler(dev)
@@ -335,27 +437,26 @@ def run_ours(args, rank, world, local_rank):
     ctx.reset_timing()
     ctx.set_timing(True)
     launches0 = ctx.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t0 = time.perf_counter()
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    barrier()
-    t1 = time.perf_counter()
+    ms_step, t0, t1 = time_steps(run.step, args.steps, dev, world)
     ctx.set_timing(False)
     clocks = sampler.stop(t0, t1)
-    ms_total = e0.elapsed_time(e1)
     launches = ctx.launch_count - launches0
     ktimes = ctx.get_timing()
-    if world > 1:
-        tt = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_total = float(tt.item())
-    ms_step = ms_total / args.steps
     px_total = float(H) * W
+    px_rank = float(run.b1 - run.b0) * W
     value = px_total / (ms_step * 1e-3) / 1e6
+
+    # ---- parity at this rank count (outside the timed region) ---------------
+    parity = None
+    if not args.no_parity:
+        n_px = run.check_parity()
+        tot = torch.tensor([n_px], dtype=torch.int64, device=f"cuda:{dev}")
+        if world > 1:
+            dist.all_reduce(tot)
+        parity = {"checked": True, "pixels": int(tot.item()),
+                  "how": "per rank: 4 random rows + the 2 rows next to its band "
+                         "edges, every pixel bit-exact against cKDTree + size law "
+                         "+ numpy stencil on the 3-row strip"}
 
     # ---- roofline of the dominant kernel -----------------------------------
     peak, peak_src = measured_peaks()
@@ -365,143 +466,178 @@ def run_ours(args, rank, world, local_rank):
         ms, n = ktimes[dom]
         avg = ms / n
         bpp = BYTES_PER_PX.get(dom, 8.0)
-        bytes_launch = bpp * size * W * (args.steps / n) if n else 0.0
-        ach = bytes_launch / (avg * 1e-3) / 1e9
+        px_launch = px_rank * (args.steps / n) if n else 0.0
+        ach = bpp * px_launch / (avg * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak,
                     "unit": "GB/s", "frac": ach / peak,
-                    "traffic": ncu_traffic(dom, size * W * (args.steps / n) if n else 0),
+                    "traffic": ncu_traffic(dom, px_launch),
                     "peak_source": peak_src,
                     "algorithmic_bytes_per_px": bpp,
                     "avg_launch_ms": avg,
+                    # the north-star figure: the WHOLE pass (every kernel, gaps
+                    # and collectives of a step) at 12 B/px per GPU
+                    "pass_frac": (PASS_BYTES_PER_PX * px_rank / (ms_step * 1e-3)
+                                  / 1e9 / peak),
+                    "pass_achieved": PASS_BYTES_PER_PX * px_rank / (ms_step * 1e-3) / 1e9,
                     "kernel_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
-                    "kernel_roofline_frac": {
-                        k: (BYTES_PER_PX[k] * size * W / (v[0] / args.steps * 1e-3) / 1e9 / peak)
-                        for k, v in ktimes.items() if k in BYTES_PER_PX}}
+                    "note": "algorithmic bytes per SURVEY.md 8(d): fused pass = DEM "
+                            "read + hfun read + hfun write; the first op of a fresh "
+                            "raster takes the initial state as a NULL pointer, so "
+                            "the real traffic (`traffic`) is below it"}
 
     # ---- e2e: public API, host buffers -------------------------------------
     e2e = None
     if not args.no_e2e:
-        out_pinned = torch.empty((size, W), dtype=torch.float32).pin_memory()
-        # each rank holds its band plus one halo row per side on the HOST (what
-        # a rank reading its rows of the GeoTIFF would over-read: no collective)
-        s0, s1 = part.stored(rank)
-        z_e2e = z_host if world == 1 else host_dem(H, W, SEED, rows=(s0, s1),
-                                                   full_height=H)
-
-        def e2e_step():
-            # public API in deferred mode: add_* are queued, get_values(out=)
-            # streams the pass band by band (ocsb_hfun_pass): DEM H2D, kernels
-            # and hfun D2H overlap on three streams
-            r = ob.Raster.from_numpy(z_e2e.numpy(), tr, crs=32618,
-                                     row_origin=s0, full_height=H)
-            h = ob.HfunRaster(r, hmin=HMIN, hmax=HMAX, device=dev,
-                              row_band=part.band(rank), deferred=True)
-            v = pts_pinned                                         # host vertices
-            if world > 1:
-                v = D.all_gather_vertices(
-                    pts_pinned.to(f"cuda:{dev}", non_blocking=True), sizes=vsizes)
-            h.add_feature_points(v, RATE, TARGET)
-            h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
-            h.get_values(out=out_pinned)             # DEM H2D + pass + hfun D2H
-            return float(out_pinned[0, 0])
-
-        def e2e_step_phased():
-            # same public API, eager mode: the whole band goes up, the ops run
-            # on the resident band, the whole size band comes down.  With the
-            # ranks in step (one barrier between the phases) the host never
-            # carries both directions at once -- on a host whose duplex copy
-            # bandwidth is below its one-way bandwidth (profiles/r1h_diag_pcie_n8.txt)
-            # that beats the overlapped stream once several ranks share it.
-            if world > 1:
-                dist.barrier()        # nobody uploads while a peer still downloads
-            r = D.band_raster(z_host.numpy(), tr, H, part, rank, crs=32618,
-                              device=dev)                          # DEM H2D
-            h = ob.HfunRaster(r, hmin=HMIN, hmax=HMAX, device=dev,
-                              row_band=part.band(rank))
-            v = pts_pinned.to(f"cuda:{dev}", non_blocking=True)
-            if world > 1:
-                v = D.all_gather_vertices(v, sizes=vsizes)
-                D.exchange_dem_halo(r, part, rank, dev)
-            h.add_feature_points(v, RATE, TARGET)
-            h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
-            if world > 1:
-                torch.cuda.synchronize(dev)
-                dist.barrier()
-            h.get_values(out=out_pinned)                           # hfun D2H
-            return float(out_pinned[0, 0])
-
-        def time_e2e(fn, n):
-            barrier()
-            a0 = torch.cuda.Event(enable_timing=True)
-            a1 = torch.cuda.Event(enable_timing=True)
-            a0.record()
-            for _ in range(n):
-                fn()
-            a1.record()
-            barrier()
-            ms = a0.elapsed_time(a1)
-            if world > 1:
-                tt = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{dev}")
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-                ms = float(tt.item())
-            return ms
-
-        e2e_steps = max(2, min(args.steps, 5))
-        # calibration outside the timed region: one warm-up and one timed step
-        # of each transfer schedule; every rank sees the same max-over-ranks
-        # times, so all pick the same one
-        calib = {}
-        for name, fn in (("streamed", e2e_step), ("phased", e2e_step_phased)):
-            fn()
-            calib[name] = time_e2e(fn, 1)
-        mode = min(calib, key=calib.get)
-        ems = time_e2e(e2e_step if mode == "streamed" else e2e_step_phased, e2e_steps)
-        e2e = {"value": px_total / (ems / e2e_steps * 1e-3) / 1e6, "unit": "Mpx/s",
-               "h2d_bytes_per_step": int(z_e2e.numel() * 4 + pts_pinned.numel() * 8),
-               "path": ("HfunRaster(deferred=True) -> ocsb_hfun_pass: row bands "
-                        "streamed host->device->host, copies overlapped with "
-                        "the kernels") if mode == "streamed" else
-                       ("HfunRaster eager: band H2D, ops on the resident band, "
-                        "band D2H; ranks phase-locked so the host carries one "
-                        "direction at a time"),
-               "schedule": mode,
-               "calibration_ms_per_step": calib,
-               "d2h_bytes_per_step": int(out_pinned.numel() * 4),
-               "steps": e2e_steps, "ms_per_step": ems / e2e_steps,
-               "host_placement": numa}
-        del out_pinned
-
-    # ---- secondary: Mesh.interpolate ---------------------------------------
-    secondary = {}
-    if not args.no_interp:
-        secondary["interp"] = bench_interp(args, rank, world, dev, ctx, peak)
+        e2e = bench_e2e(args, run, rank, world, dev, numa, px_total)
 
     # ---- CPU baseline (rank 0, N == 1) --------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         n = min(args.cpu_sample, size)
-        mpx, dt, cores, ref_vals = cpu_hfun_sample(z_host.numpy(), tr, pts_local, n)
+        zc = np.ascontiguousarray(run.z_host.numpy()[:n, :n])
+        mpx, dt, cores, _ = cpu_hfun_sample(zc, run.tr, run.pts_local, n)
         # the GPU result on the same crop is NOT comparable pixel-for-pixel (a
         # crop is its own semantic window), so this leg only times the oracle
         cpu = {"value": mpx, "unit": "Mpx/s", "cores": cores, "kind": "port",
-               "sample": f"top-left {n}x{n} crop of the DEM with the full "
-                         f"{len(pts_local)}-vertex contour set, one pass "
-                         f"({dt:.2f} s), scipy cKDTree workers=-1"}
+               "sample": cpu_sample_text(n, len(run.pts_local), dt)}
+
+    # ---- secondary legs -----------------------------------------------------
+    secondary = {}
+    if not args.no_windows:
+        secondary["windows"] = bench_windows(args, run, rank, world, dev, ms_step)
+    if world > 1 and not args.no_weak:
+        del run
+        torch.cuda.empty_cache()
+        secondary["weak"] = bench_weak(args, rank, world, dev)
+        run = None
+    if not args.no_interp:
+        secondary["interp"] = bench_interp(args, rank, world, dev, ctx, peak)
 
     if rank == 0:
+        cfg = workload_config(args, world)
         line = {
             "metric": "hfun_raster_pass_throughput", "value": value,
             "unit": "Mpx/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64 distance / f32 size", "data": "synthetic",
-            "config": workload_config(args, world),
-            "n_vertices": int(len(pts_local)),
+            "config": cfg,
+            "parallelism": (f"row bands x{world} of ONE {H}x{W} raster "
+                            f"({H // world} rows per GPU); per step: vertex "
+                            "all-gather + boundary-row all-gather (NCCL), then "
+                            "one tiled sweep per band"),
+            "vertex_set": ("contours of each rank's band (cell rows partition the "
+                           "raster's), each piece resampled on its own; all-"
+                           "gathered every step"),
+            "n_vertices": nv_total,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "parity_checked": bool(parity), "parity": parity,
             "gpu_launches": int(launches), "clocks": clocks,
             "secondary": secondary,
         }
         print(json.dumps(line), flush=True)
+
+
+def bench_e2e(args, run, rank, world, dev, numa, px_total):
+    """The same pass through the public API with HOST buffers: per step the
+    rank's DEM rows and vertices go up from pinned memory, the size band comes
+    down (ocsb_hfun_pass streams row bands: H2D, kernels and D2H overlap)."""
+    import torch
+    import torch.distributed as dist
+    import ocsmesh_b200 as ob
+    H, W = run.H, run.W
+    rows = run.b1 - run.b0
+    out_pinned = torch.empty((rows, W), dtype=torch.float32).pin_memory()
+    z_e2e = run.z_host
+    pts_pinned = run.pts_pinned
+
+    def e2e_step():
+        r = ob.Raster.from_numpy(z_e2e.numpy(), run.tr, crs=32618,
+                                 row_origin=run.s0, full_height=H)
+        h = ob.HfunRaster(r, hmin=HMIN, hmax=HMAX, device=dev,
+                          row_band=(run.b0, run.b1), deferred=True)
+        v = pts_pinned                                         # host vertices
+        if world > 1:
+            v = run.exch.gather_vertices(
+                pts_pinned.to(f"cuda:{dev}", non_blocking=True))
+        h.add_feature_points(v, RATE, TARGET)
+        h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+        h.get_values(out=out_pinned)             # DEM H2D + pass + hfun D2H
+        return float(out_pinned[0, 0])
+
+    e2e_step()
+    e2e_steps = max(2, min(args.steps, 5))
+    ems, _, _ = time_steps(e2e_step, e2e_steps, dev, world)
+    res = {"value": px_total / (ems * 1e-3) / 1e6, "unit": "Mpx/s",
+           "h2d_bytes_per_step": int(z_e2e.numel() * 4 + pts_pinned.numel() * 8),
+           "d2h_bytes_per_step": int(out_pinned.numel() * 4),
+           "path": "HfunRaster(deferred=True).get_values(out=pinned) -> "
+                   "ocsb_hfun_pass: row bands streamed host->device->host, copies "
+                   "overlapped with the kernels",
+           "steps": e2e_steps, "ms_per_step": ems,
+           "bound": "PCIe on one GPU (1.6 GB up + 1.6 GB down per 400 Mpx); beyond "
+                    "two ranks the host's copy bandwidth (DESIGN.md 6)",
+           "host_placement": numa}
+    del out_pinned
+    return res
+
+
+def bench_windows(args, run, rank, world, dev, ms_single):
+    """configs[1] "tiled by raster windows": the same pass with the raster cut
+    into semantic windows (own linspace coordinates, radius and border rules
+    per window); the window table is consumed by the same launches."""
+    import torch
+    import ocsmesh_b200 as ob
+    out = {"single_window_ms": ms_single}
+    steps = max(3, min(args.steps, 10))
+    cases = [("chunk5000_overlap0", 5000, 0), ("chunk1000_overlap0", 1000, 0),
+             ("chunk5000_overlap2", 5000, 2)]
+    for name, chunk, ovl in cases:
+        if chunk >= run.W:
+            continue
+        raster = run.raster
+        raster.chunk_size, raster.overlap = chunk, ovl
+        hf = ob.HfunRaster(raster, hmin=HMIN, hmax=HMAX, device=dev,
+                           row_band=(run.b0, run.b1), deferred=True)
+        verts = run.exch.gather_vertices(run.verts_local)
+
+        def step():
+            hf.reset()
+            hf.add_feature_points(verts, RATE, TARGET)
+            hf.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
+            hf.flush()
+        for _ in range(2):
+            step()
+        ms, _, _ = time_steps(step, steps, dev, world)
+        hf.sync()
+        n_win = len([w for w in hf._windows() if hf._band_of(w) is not None])
+        out[name] = {"ms_per_step": ms, "windows_on_rank0": n_win,
+                     "vs_single_window": ms / ms_single,
+                     "mode": "one sweep for the op list" if hf._can_defer()
+                             else "one sweep per op (overlapping windows: every "
+                                  "window must see the pre-op raster)"}
+        del hf
+    run.raster.chunk_size, run.raster.overlap = None, None
+    return out
+
+
+def bench_weak(args, rank, world, dev):
+    """Round-1 layout kept as a secondary: the raster grows with N (20000 rows
+    per GPU), same exchanges per step."""
+    import torch
+    H, W = args.size * world, args.size
+    run = BandRun(args, H, W, rank, world, dev)
+    for _ in range(3):
+        run.step()
+    steps = max(3, min(args.steps, 10))
+    ms, _, _ = time_steps(run.step, steps, dev, world)
+    run.hfun.sync()
+    res = {"scaling": "weak", "raster": f"{H}x{W}", "ms_per_step": ms,
+           "value": float(H) * W / (ms * 1e-3) / 1e6, "unit": "Mpx/s",
+           "n_vertices": run.nv_total}
+    del run
+    torch.cuda.empty_cache()
+    return res
 
 
 def bench_interp(args, rank, world, dev, ctx, peak):

@@ -42,7 +42,7 @@ extern "C" {
 #define OCSB_ENCCL      (-4)
 #define OCSB_EOVERFLOW  (-5)
 
-#define OCSB_ABI_VERSION 4
+#define OCSB_ABI_VERSION 5
 
 /* DEM element types (the hfun raster itself is always float32,
  * ocsmesh/hfun/raster.py:76) */
@@ -410,6 +410,43 @@ int32_t ocsb_hfun_pass(ocsb_ctx *ctx, const ocsb_win *win,
                        double dx, double dy, double ghmin, double ghmax,
                        const ocsb_hfun_op *ops, int32_t n_ops,
                        int32_t band_rows);
+
+/* The whole op list over a LIST of semantic windows, every buffer resident on
+ * the device: ONE tiled sweep (12 B/px for the list: DEM read, hfun read, hfun
+ * write) in which the window table is a table of units of work of the same
+ * launches -- the window loops of ocsmesh/hfun/raster.py:1212-1260, 1393-1436
+ * over Raster.iter_windows (ocsmesh/raster.py:1577-1608) without a launch per
+ * window.  Every window keeps its own np.linspace coordinates, search radius
+ * and one-sided border differences.
+ *   wins[k]     : window k (row_begin/row_end = the rows this device owns)
+ *   dem         : element (0, 0) of the stored DEM block (dem_rows x dem_cols,
+ *                 row stride dem_stride); window k's pixel (0, 0) lies
+ *                 dem_off[k] elements into it (may be negative: a window that
+ *                 starts above a band's stored rows)
+ *   hfun_off[k] : element offset of window k's pixel (0, 0) in hfun_in /
+ *                 hfun_out (one layout: in_stride == out_stride)
+ *   keep_wh     : optional [n_wins][2]: only pixels (r < keep_h, c < keep_w) of
+ *                 window k are written -- for overlapping windows (overlap > 0,
+ *                 where the later window wins) with ONE op and distinct in /
+ *                 out buffers; NULL = whole windows
+ *   status_dev  : NULL = synchronous (candidate-pool overflow is retried inside
+ *                 the call).  Device int32: ASYNCHRONOUS -- nothing waits on the
+ *                 host; the pass is a no-op on the device if *status_dev != 0
+ *                 on entry and sets it to 1 if a pool overflowed (the size
+ *                 raster is then untouched), so a sequence of passes stops at
+ *                 its first failure and can be redone from there.
+ * Vertex sets must be device memory.  Bit-identical to the per-window,
+ * per-op calls (tests/test_pass_gpu.py).                                     */
+int32_t ocsb_hfun_pass_windows(ocsb_ctx *ctx, const ocsb_win *wins,
+                               const int64_t *dem_off, const int64_t *hfun_off,
+                               const int32_t *keep_wh, int32_t n_wins,
+                               const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                               int32_t dem_rows, int32_t dem_cols,
+                               const float *hfun_in, int64_t in_stride,
+                               float *hfun_out, int64_t out_stride,
+                               double dx, double dy, double ghmin, double ghmax,
+                               const ocsb_hfun_op *ops, int32_t n_ops,
+                               int32_t *status_dev);
 
 /* One op of the list above on a LIST of semantic windows -- the window loops of
  * HfunRaster.add_feature (ocsmesh/hfun/raster.py:1212-1260) and

@@ -93,6 +93,11 @@ SIGNATURES = {
                                      c_vp, c_i32, c_i64, c_vp, c_i64, c_vp, c_i64,
                                      c_f64, c_f64, c_f64, c_f64,
                                      C.POINTER(ocsb_hfun_op), c_i32]),
+    "ocsb_hfun_pass_windows": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_vp, c_vp,
+                                       c_i32, c_vp, c_i32, c_i64, c_i32, c_i32,
+                                       c_vp, c_i64, c_vp, c_i64,
+                                       c_f64, c_f64, c_f64, c_f64,
+                                       C.POINTER(ocsb_hfun_op), c_i32, c_vp]),
     "ocsb_hfun_constant_value": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                          c_i64, c_vp, c_i64, c_vp, c_i64,
                                          c_f64, c_f64, c_f64, c_f64, c_f64,
@@ -337,6 +342,23 @@ class Context:
             int(dem_dtype), int(dem_stride), ptr(hfun_old), int(old_stride),
             ptr(hfun_new), int(new_stride), float(dx), float(dy), opt(ghmin),
             opt(ghmax), arr, int(bool(in_order))))
+
+    def hfun_pass_windows(self, wins, dem_off, hfun_off, dem, dem_dtype, dem_stride,
+                          dem_rows, dem_cols, hfun_in, in_stride, hfun_out,
+                          out_stride, dx, dy, ghmin, ghmax, ops, keep_wh=None,
+                          status=None, op_array=None):
+        """The op list (tuples as in :meth:`hfun_pass`) over a list of windows
+        of device-resident buffers in one tiled sweep.  ``status``: None =
+        synchronous; a device int32 tensor = asynchronous with the sticky
+        failure flag (see ocsb200.h).  ``op_array``: a prebuilt ctypes op array
+        (``_op_array(ops)``) to skip the marshalling on a hot path."""
+        arr = op_array if op_array is not None else self._op_array(ops)
+        check(self.lib.ocsb_hfun_pass_windows(
+            self.handle, wins, ptr(dem_off), ptr(hfun_off), ptr(keep_wh), len(wins),
+            ptr(dem), int(dem_dtype), int(dem_stride), int(dem_rows), int(dem_cols),
+            ptr(hfun_in), int(in_stride), ptr(hfun_out), int(out_stride),
+            float(dx), float(dy), opt(ghmin), opt(ghmax), arr, len(arr),
+            ptr(status)))
 
     def hfun_pass(self, win, dem, dem_dtype, dem_stride, hfun_in, in_stride,
                   hfun_out, out_stride, dx, dy, ghmin, ghmax, ops, band_rows=0):

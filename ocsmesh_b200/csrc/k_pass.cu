@@ -706,6 +706,13 @@ __device__ __forceinline__ void tails4_dyn(const float (&h)[4], const float (&zz
     }
 }
 
+// four staged DEM values of a row; `shift` (dem_c & 3, uniform) != 0 when the
+// window does not start on a 16-byte boundary of the DEM rows
+__device__ __forceinline__ float4 dem_row4(const float *p, int shift) {
+    if (shift == 0) return *reinterpret_cast<const float4 *>(p);
+    return make_float4(p[0], p[1], p[2], p[3]);
+}
+
 // Pixel ownership: warp = 32x16 rect of the tile (2 x 4 warps), lane = 4 columns
 // x 4 rows of it, processed two rows ("half") at a time so that only 8 running
 // size values live in registers.  Per feature op: CTA filter, warp filter, then
@@ -750,7 +757,8 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_dem);
-        const int cx = G.dem_c + c0t - 4, cy = G.dem_r + G.rb + r0t - 1;
+        // the box starts on a 16-byte boundary of the DEM rows (TMA requirement)
+        const int cx = (G.dem_c + c0t - 4) & ~3, cy = G.dem_r + G.rb + r0t - 1;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                      ::"r"(bar), "r"((uint32_t)(kDemRows * kDemPitch * 4)) : "memory");
         asm volatile(
@@ -770,7 +778,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
     }
     if (A.nl && !A.use_tma) {
         // unaligned DEM buffers: plain loads of the same box, zeros outside
-        const int gr0 = G.dem_r + G.rb + r0t - 1, gc0 = G.dem_c + c0t - 4;
+        const int gr0 = G.dem_r + G.rb + r0t - 1, gc0 = (G.dem_c + c0t - 4) & ~3;
         for (int i = threadIdx.x; i < kDemRows * kDemPitch; i += kPassThreads) {
             const int rr = i / kDemPitch, cc = i - rr * kDemPitch;
             const int gr = gr0 + rr, gc = gc0 + cc;
@@ -950,7 +958,8 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
 #pragma unroll 1
             for (int half = 0; half < 2; ++half) {
                 const int hr = grow + half * 2;            // first row of the pair
-                if (hr > sr1 || gcol > sc1) break;
+                // (not with the chunk-wise path: its warp-wide votes need every lane)
+                if (!refilter && (hr > sr1 || gcol > sc1)) break;
                 PSTAT_CLK(sh0);
                 // ---- feature op: nearest vertex + size law -------------------------------
                 float vf[8];
@@ -1052,11 +1061,11 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
                 if (last && A.nl) {
                     const int H = W.ay.n;
                     // staged row of tile row j is j + 1, staged column of tile column c is c + 4
-                    const float *sd = s_dem + (lrow + half * 2) * kDemPitch + 4 + lcol;
+                    const int shift = W.dem_c & 3;
+                    const float *sd = s_dem + (lrow + half * 2) * kDemPitch + 4 + lcol + shift;
                     float4 rowv[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        rowv[j] = *reinterpret_cast<const float4 *>(sd + j * kDemPitch);
+                    for (int j = 0; j < 4; ++j) rowv[j] = dem_row4(sd + j * kDemPitch, shift);
 #pragma unroll
                     for (int j = 0; j < 2; ++j) {
                         if (hr + j > sr1) continue;
@@ -1278,8 +1287,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     ScratchGuard sg(ctx);
     PWin *d_wins = nullptr;
     OCSB_TRY(sg.get(&d_wins, (size_t)d.n_wins));
-    OCSB_CUDA(cudaMemcpyAsync(d_wins, wins.data(), sizeof(PWin) * d.n_wins,
-                              cudaMemcpyHostToDevice, ctx->stream));
+    OCSB_TRY(ocsb_stage_upload(ctx, d_wins, wins.data(), sizeof(PWin) * d.n_wins));
 
     // ---- counters / flags --------------------------------------------------------
     // [0..2*nf): pool counters; then per feature a far flag; then the overflow flag
@@ -1329,6 +1337,9 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (nctr + 8) * sizeof(*ctrs), ctx->stream));
+        if (d.sticky)   // an earlier pass of the sequence failed: this one must not run
+            OCSB_CUDA(cudaMemcpyAsync(overflow, d.ext_overflow, sizeof(int),
+                                      cudaMemcpyDeviceToDevice, ctx->stream));
         TileArgs T;
         memset(&T, 0, sizeof(T));
         double2 *slots0 = nullptr, *pool0 = nullptr;

@@ -143,7 +143,9 @@ __device__ __forceinline__ void p2_produce(const CUtensorMap *tmap, const P2Args
     p2_bulk(&S.win[stage], &A.wins[S.cur_wi], (uint32_t)sizeof(PWin), bar);
     if (HAS_FEAT) p2_bulk(&S.slot[stage][0], A.slots + (size_t)t * kSlot, kSlot * 16, bar);
     if (HAS_LIM) {
-        const int cx = S.cur_demc + tx * kT0 - 4, cy = S.cur_demr + ty * kT0 - 1;
+        // the box starts on a 16-byte boundary of the DEM rows (TMA requirement):
+        // up to 3 columns further left, the consumers shift by dem_c & 3
+        const int cx = (S.cur_demc + tx * kT0 - 4) & ~3, cy = S.cur_demr + ty * kT0 - 1;
         const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&S.dem[stage][0]);
         asm volatile(
             "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
@@ -181,7 +183,9 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
         const int hr = grow + half * 2;
-        if (!FULL && (hr > sr1 || gcol > sc1)) break;
+        // lanes outside a partial rect leave early -- unless the chunk-wise path
+        // with its warp-wide votes follows (their loads / stores are masked)
+        if (!FULL && !refilter && (hr > sr1 || gcol > sc1)) break;
         float vf[8];
         if (HAS_FEAT) {
             if (ntile == 0) {
@@ -280,11 +284,11 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
         // ---- limiter op ------------------------------------------------------------------
         if (HAS_LIM) {
             const int H = W.ay.n;
-            const float *sd = sdem + (lrow + half * 2) * kDemPitch + 4 + lcol;
+            const int shift = FULL ? 0 : (W.dem_c & 3);
+            const float *sd = sdem + (lrow + half * 2) * kDemPitch + 4 + lcol + shift;
             float4 rowv[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                rowv[j] = *reinterpret_cast<const float4 *>(sd + j * kDemPitch);
+            for (int j = 0; j < 4; ++j) rowv[j] = dem_row4(sd + j * kDemPitch, shift);
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 if (!FULL && hr + j > sr1) continue;
@@ -460,7 +464,7 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
                 __syncwarp();
             }
             // strictly inside the window, fully written, aligned
-            const bool full = W.vec && c0t >= 1 && c0t + kT0 <= min(bw - 1, W.keep_w) &&
+            const bool full = W.vec && (W.dem_c & 3) == 0 && c0t >= 1 && c0t + kT0 <= min(bw - 1, W.keep_w) &&
                               rb + r0t >= 1 && r0t + kT0 <= bh &&
                               rb + r0t + kT0 <= min(W.ay.n - 1, W.keep_h);
             if (full)

@@ -173,6 +173,10 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->spl_coef) cudaFree(ctx->spl_coef);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto &sl : ctx->stage_ring) {
+        if (sl.host) cudaFreeHost(sl.host);
+        if (sl.ev) cudaEventDestroy(sl.ev);
+    }
     for (auto &r : ctx->time_recs) {
         cudaEventDestroy(r.a);
         cudaEventDestroy(r.b);
@@ -192,6 +196,27 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
     if (ctx->ev_alloc) cudaEventDestroy(ctx->ev_alloc);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+    return OCSB_OK;
+}
+
+int32_t ocsb_stage_upload(ocsb_ctx *ctx, void *dst_dev, const void *src, size_t bytes) {
+    if (bytes == 0) return OCSB_OK;
+    ocsb_ctx::StageSlot &sl = ctx->stage_ring[ctx->stage_next];
+    ctx->stage_next = (ctx->stage_next + 1) % 8;
+    if (sl.used) OCSB_CUDA(cudaEventSynchronize(sl.ev));   // its last upload has left
+    if (!sl.ev) OCSB_CUDA(cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming));
+    if (sl.bytes < bytes) {
+        if (sl.host) cudaFreeHost(sl.host);
+        sl.host = nullptr;
+        sl.bytes = 0;
+        const size_t want = bytes < 4096 ? 4096 : bytes;
+        OCSB_CUDA(cudaMallocHost(&sl.host, want));
+        sl.bytes = want;
+    }
+    memcpy(sl.host, src, bytes);
+    OCSB_CUDA(cudaMemcpyAsync(dst_dev, sl.host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    OCSB_CUDA(cudaEventRecord(sl.ev, ctx->stream));
+    sl.used = true;
     return OCSB_OK;
 }
 
@@ -1610,6 +1635,132 @@ extern "C" int32_t ocsb_hfun_pass(
     return OCSB_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// The op list over a LIST of semantic windows in one tiled sweep, every buffer
+// resident (see ocsb200.h).  The window table is a unit-of-work table of the
+// SAME launches: no per-window launch, no host loop.
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_hfun_pass_windows(
+    ocsb_ctx *ctx, const ocsb_win *wins, const int64_t *dem_off,
+    const int64_t *hfun_off, const int32_t *keep_wh, int32_t n_wins,
+    const void *dem, int32_t dem_dtype, int64_t dem_stride, int32_t dem_rows,
+    int32_t dem_cols, const float *hfun_in, int64_t in_stride, float *hfun_out,
+    int64_t out_stride, double dx, double dy, double ghmin, double ghmax,
+    const ocsb_hfun_op *ops, int32_t n_ops, int32_t *status_dev) {
+    CTX_ENTER("ocsb_hfun_pass_windows");
+    OCSB_REQUIRE(n_wins >= 0, "ocsb_hfun_pass_windows: negative window count");
+    if (n_wins == 0) return OCSB_OK;
+    OCSB_REQUIRE(wins && hfun_off && ops && n_ops > 0 && hfun_out,
+                 "ocsb_hfun_pass_windows: NULL arguments");
+    OCSB_REQUIRE(ocsb_is_device_ptr(hfun_out) && (!hfun_in || ocsb_is_device_ptr(hfun_in)),
+                 "ocsb_hfun_pass_windows: the size raster must be device memory");
+    OCSB_REQUIRE(!hfun_in || in_stride == out_stride,
+                 "ocsb_hfun_pass_windows: hfun_in and hfun_out must share one layout");
+    OCSB_REQUIRE(!status_dev || ocsb_is_device_ptr(status_dev),
+                 "ocsb_hfun_pass_windows: status_dev must be device memory");
+    bool need_dem = false;
+    std::vector<PassFeat> pf;
+    std::vector<PassLim> pl;
+    for (int i = 0; i < n_ops; ++i) {
+        const ocsb_hfun_op &op = ops[i];
+        if (op.kind == OCSB_OP_FEATURE) {
+            OCSB_REQUIRE(op.verts_xy && op.nv > 0 && op.nv < (int64_t)2147483647,
+                         "ocsb_hfun_pass_windows: op %d: bad vertex set", i);
+            OCSB_REQUIRE(ocsb_is_device_ptr(op.verts_xy),
+                         "ocsb_hfun_pass_windows: op %d: vertices must be device memory", i);
+            OCSB_REQUIRE(!ocsb_is_none(op.target_size) && op.target_size > 0,
+                         "Argument target_size must be greater than zero.");
+            OCSB_REQUIRE(!ocsb_is_none(op.expansion_rate),
+                         "ocsb_hfun_pass_windows: op %d: expansion_rate is NaN", i);
+            if (!ocsb_is_none(ghmax) && ghmax != 0.0)
+                OCSB_REQUIRE(op.expansion_rate * op.target_size != 0.0,
+                             "ocsb_hfun_pass_windows: op %d: float division by zero "
+                             "(expansion_rate * target_size == 0 with hmax set)", i);
+            PassFeat f;
+            f.verts = op.verts_xy; f.nv = op.nv;
+            f.rate_target = op.expansion_rate * op.target_size;
+            f.target = op.target_size;
+            f.r = (!ocsb_is_none(ghmax) && ghmax != 0.0)
+                      ? (ghmax - op.target_size) / f.rate_target
+                      : std::numeric_limits<double>::infinity();
+            f.fuse_clamp = op.fuse_clamp;
+            pf.push_back(f);
+        } else if (op.kind == OCSB_OP_LIMITER) {
+            need_dem = true;
+            pl.push_back(PassLim{op.hmin, op.hmax, op.lower_bound, op.upper_bound,
+                                 op.fuse_clamp});
+        } else {
+            OCSB_REQUIRE(false, "ocsb_hfun_pass_windows: op %d: unknown kind %d", i, op.kind);
+        }
+    }
+    if (need_dem) {
+        OCSB_REQUIRE(dem && dem_off && ocsb_is_device_ptr(dem) && dem_stride > 0 &&
+                         dem_rows > 0 && dem_cols > 0 && dem_cols <= dem_stride &&
+                         (dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64),
+                     "ocsb_hfun_pass_windows: a limiter op needs the resident DEM block");
+        OCSB_REQUIRE(!ocsb_is_none(dx) && !ocsb_is_none(dy),
+                     "ocsb_hfun_pass_windows: dx/dy is NaN");
+    }
+    std::vector<PassWin> pw(n_wins);
+    for (int k = 0; k < n_wins; ++k) {
+        OCSB_TRY(check_win(&wins[k], "ocsb_hfun_pass_windows"));
+        int rb, re;
+        OCSB_TRY(win_band(&wins[k], "ocsb_hfun_pass_windows", &rb, &re));
+        const int w = wins[k].width, h = wins[k].height;
+        if (need_dem)
+            OCSB_REQUIRE(w >= 2 && h >= 2,
+                         "Shape of array too small to calculate a numerical gradient, "
+                         "at least (edge_order + 1) elements are required.");
+        PassWin &p = pw[k];
+        win_axes(&wins[k], &p.ax, &p.ay);
+        p.rb = rb; p.re = re;
+        p.keep_w = keep_wh ? keep_wh[2 * k] : w;
+        p.keep_h = keep_wh ? keep_wh[2 * k + 1] : h;
+        OCSB_REQUIRE(p.keep_w >= 0 && p.keep_w <= w && p.keep_h >= 0 && p.keep_h <= h,
+                     "ocsb_hfun_pass_windows: bad keep size of window %d", k);
+        p.hoff = hfun_off[k];
+        p.dem_c = 0; p.dem_r = 0;
+        if (need_dem) {
+            // floor division: a window may start above the stored block
+            int64_t r = dem_off[k] / dem_stride, c = dem_off[k] - r * dem_stride;
+            if (c < 0) { c += dem_stride; --r; }
+            p.dem_c = (int)c; p.dem_r = (int)r;
+        }
+    }
+    PassDesc d;
+    d.wins = pw.data(); d.n_wins = n_wins;
+    if (need_dem) {
+        d.dem = dem; d.dem_dtype = dem_dtype; d.dem_stride = dem_stride;
+        d.dem_rows = dem_rows; d.dem_cols = dem_cols;
+    }
+    d.in = hfun_in; d.in_stride = in_stride;
+    d.out = hfun_out; d.out_stride = out_stride;
+    d.dx = dx; d.dy = dy; d.ghmin = ghmin; d.ghmax = ghmax;
+    d.feats = pf.data(); d.nf = (int)pf.size();
+    d.lims = pl.data(); d.nl = (int)pl.size();
+    d.ext_overflow = status_dev;
+    d.sticky = status_dev != nullptr;
+    if (k_pass_supported(d)) return k_pass_tiled(ctx, d);
+    // ---- op lists the tiled sweep does not take (float64 DEM, mixed clamp
+    //      fusing, more than 4 ops of a kind): window by window, op by op ------
+    OCSB_REQUIRE(!status_dev, "ocsb_hfun_pass_windows: this op list only runs "
+                              "synchronously (status_dev must be NULL)");
+    std::vector<const double *> verts(n_ops, nullptr);
+    for (int i = 0; i < n_ops; ++i) verts[i] = ops[i].verts_xy;
+    const size_t es = dem_dtype == OCSB_F64 ? 8 : 4;
+    for (int k = 0; k < n_wins; ++k) {
+        const PassWin &p = pw[k];
+        OCSB_REQUIRE(p.keep_w == wins[k].width && p.keep_h == wins[k].height,
+                     "ocsb_hfun_pass_windows: partial windows need the tiled sweep");
+        const char *zp = need_dem ? (const char *)dem + dem_off[k] * (int64_t)es : nullptr;
+        OCSB_TRY(pass_ops(ctx, &wins[k], p.rb, p.re, zp, dem_dtype, dem_stride,
+                          hfun_in ? hfun_in + hfun_off[k] : nullptr, in_stride,
+                          hfun_out + hfun_off[k], out_stride, dx, dy, ghmin, ghmax,
+                          ops, n_ops, verts, nullptr));
+    }
+    return OCSB_OK;
+}
 
 // ---------------------------------------------------------------------------
 // One op over a LIST of semantic windows (the window loops of

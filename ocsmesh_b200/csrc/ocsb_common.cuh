@@ -80,6 +80,15 @@ struct ocsb_ctx {
     // pinned bounce buffer for small D2H reads (flags, counters)
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
+    // pinned staging ring for small host -> device uploads that must not wait
+    // for the stream (window tables of the asynchronous pass)
+    struct StageSlot {
+        void *host = nullptr;
+        size_t bytes = 0;
+        cudaEvent_t ev = nullptr;
+        bool used = false;
+    } stage_ring[8];
+    int stage_next = 0;
     // copy streams + events of ocsb_hfun_pass (created on first use)
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
     cudaEvent_t ev_in[OCSB_PASS_SETS] = {}, ev_comp[OCSB_PASS_SETS] = {},
@@ -94,6 +103,10 @@ struct ocsb_ctx {
     double *spl_coef = nullptr;
     size_t spl_bytes = 0;
 };
+
+// host -> device upload through the pinned ring: returns without waiting for
+// earlier work of the stream (a pageable cudaMemcpyAsync would)
+int32_t ocsb_stage_upload(ocsb_ctx *ctx, void *dst_dev, const void *src, size_t bytes);
 
 // stream-ordered scratch allocation (cudaMallocAsync pool, reused across calls)
 int32_t ocsb_alloc(ocsb_ctx *ctx, void **p, size_t bytes);
@@ -335,6 +348,9 @@ struct PassDesc {
     const PassLim *lims = nullptr;
     int nl = 0;
     int *ext_overflow = nullptr; // non-null: asynchronous (see FeatureArgs)
+    // asynchronous AND sticky: the pass is a no-op on the device when
+    // *ext_overflow is already non-zero on entry (ocsb_hfun_pass_windows)
+    bool sticky = false;
 };
 bool k_pass_supported(const PassDesc &d);
 int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d);

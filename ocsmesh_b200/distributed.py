@@ -165,6 +165,83 @@ def all_gather_vertices(verts_local, group=None, sizes: Optional[Sequence[int]] 
     return all_gather_ragged(verts_local, group, sizes)
 
 
+class BandExchange:
+    """Per-step exchanges of a row-band run with persistent buffers: nothing is
+    allocated, padded or concatenated inside a step.
+
+    * vertices: every rank contributes its ``(n_i, 2)`` float64 contour vertices
+      in a fixed-capacity block (``cap`` = the largest ``n_i``, exchanged once);
+      the unused tail of a block repeats the rank's last vertex -- duplicates
+      cannot change a nearest-vertex distance -- or, for a rank without
+      vertices, a far-away finite point that every candidate test drops.  ONE
+      ``all_gather_into_tensor`` fills the ``(world * cap, 2)`` array the
+      kernels read in place.
+    * DEM halo rows: every rank contributes its first and last owned row
+      (``2 x W`` elements) to ONE ``all_gather_into_tensor``; the two rows a rank
+      needs are then copied into the halo slots of its stored band.
+    """
+
+    FAR = 1.0e13    # |coordinate| of the filler vertex of an empty rank (< 1e14)
+
+    def __init__(self, n_local: int, width: int, dem_dtype, device, part: RowBands,
+                 rank: int, group=None):
+        import torch
+        import torch.distributed as dist
+        self.group = group
+        self.part, self.rank = part, int(rank)
+        self.world = part.world
+        self.device = device
+        self.sizes = gather_sizes(n_local, device, group) if self.world > 1 \
+            else [int(n_local)]
+        self.cap = max(max(self.sizes), 1)
+        self.block = torch.empty((self.cap, 2), dtype=torch.float64, device=device)
+        self.verts = torch.empty((self.world * self.cap, 2), dtype=torch.float64,
+                                 device=device)
+        self.rows_out = torch.empty((2, width), dtype=dem_dtype, device=device)
+        self.rows_all = torch.empty((self.world * 2, width), dtype=dem_dtype,
+                                    device=device)
+
+    def gather_vertices(self, verts_local):
+        """All ranks' vertices, (world * cap, 2), rank order (padded blocks)."""
+        import torch.distributed as dist
+        n = int(verts_local.shape[0])
+        if n != self.sizes[self.rank]:
+            raise ValueError("vertex count differs from the exchanged size")
+        if n:
+            self.block[:n].copy_(verts_local)
+            if n < self.cap:
+                self.block[n:].copy_(verts_local[n - 1:n].expand(self.cap - n, 2))
+        else:
+            self.block.fill_(self.FAR)
+        if self.world == 1:
+            return self.block
+        dist.all_gather_into_tensor(self.verts, self.block, group=self.group)
+        return self.verts
+
+    def real_vertices(self, gathered):
+        """The gathered array without the filler entries (host-side checks)."""
+        import torch
+        if self.world == 1:
+            return gathered[:self.sizes[0]]
+        return torch.cat([gathered[r * self.cap:r * self.cap + self.sizes[r]]
+                          for r in range(self.world)], dim=0)
+
+    def exchange_halo(self, buf, origin: int) -> None:
+        """``buf`` = raster rows ``[origin, origin + len(buf))`` of this rank
+        (band + halo slots): fill the halo slots from the neighbours."""
+        import torch.distributed as dist
+        if self.world == 1:
+            return
+        r0, r1 = self.part.band(self.rank)
+        self.rows_out[0].copy_(buf[r0 - origin])
+        self.rows_out[1].copy_(buf[r1 - 1 - origin])
+        dist.all_gather_into_tensor(self.rows_all, self.rows_out, group=self.group)
+        if self.rank > 0:                       # last row of the rank above
+            buf[r0 - 1 - origin].copy_(self.rows_all[2 * (self.rank - 1) + 1])
+        if self.rank < self.world - 1:          # first row of the rank below
+            buf[r1 - origin].copy_(self.rows_all[2 * (self.rank + 1)])
+
+
 def min_combine_strip(strip, group=None):
     """Pixel-wise min of a co-registered overlap strip over all ranks of the
     group, in place (multi-raster combine)."""

@@ -85,6 +85,11 @@ class HfunRaster:
         self._keep: List = []
         self._host_vals = None      # result of a host-bound pass not yet on the device
         self._hfun_buf = None
+        # asynchronous resident passes (deferred mode): device status word of the
+        # sequence (sticky failure flag, see ocsb_hfun_pass_windows) and the
+        # passes enqueued since it was last looked at
+        self._status = None
+        self._pending: List = []
         if initial_value is not None:
             if isinstance(initial_value, (str, pathlib.Path, os.PathLike)):
                 info, bands = geotiff.read_geotiff(initial_value)
@@ -142,6 +147,28 @@ class HfunRaster:
         self._queue = []
         self._keep = []
         self._host_vals = None
+        if self._pending:
+            # whatever the enqueued passes did is discarded with the raster: a
+            # failure among them must not block the passes that follow
+            self._pending = []
+            self._status.zero_()
+
+    def _verify(self) -> None:
+        """Synchronisation point of the asynchronous passes: look at the status
+        word; if a candidate pool overflowed somewhere, every pass from that
+        one on was a no-op on the device (sticky flag), and since each op is
+        ``clamp(min(old, f(pixel)))`` -- idempotent -- the whole sequence is
+        simply run again in order, synchronously (the library then retries with
+        larger pools)."""
+        if not self._pending:
+            return
+        pending, self._pending = self._pending, []
+        if int(self._status[0].item()) == 0:
+            return
+        self._status.zero_()
+        for ops, was_pristine in pending:
+            buf = self._hfun
+            self._tiled_pass(ops, None if was_pristine else buf, buf, status=None)
 
     def _materialize(self) -> None:
         """Make the device raster current: run queued ops, upload a result
@@ -149,6 +176,7 @@ class HfunRaster:
         fill (A4) if no op has absorbed it."""
         if self._queue:
             self._run_pass(None)
+        self._verify()
         if self._host_vals is not None:
             import torch
             self._hfun.copy_(torch.from_numpy(self._host_vals))
@@ -166,9 +194,57 @@ class HfunRaster:
         return not ((self._overlap or 0) > 0 and len(self._windows()) > 1)
 
     def flush(self) -> None:
-        """Run the queued ops now (into the device raster)."""
+        """Enqueue the queued ops now (into the device raster).  With a
+        device-resident DEM nothing waits on the host: the pass is checked at
+        the next point that looks at the raster (``get_values``, ``save``, an
+        eager op, ``sync``)."""
         if self._queue:
             self._run_pass(None)
+
+    def sync(self) -> None:
+        """Run what is queued and wait until the device raster is final."""
+        self._materialize()
+        import torch
+        torch.cuda.current_stream(self._device).synchronize()
+
+    def _tiled_pass(self, ops, old, new, status=None, op_array=None) -> None:
+        """The op list over every window of the raster in ONE tiled sweep on
+        resident buffers (``ocsb_hfun_pass_windows``): ``old`` None = initial
+        state, ``new`` the float32 band tensor that receives the result."""
+        import torch
+        ctx = self._ctx()
+        w = self.width
+        windows = self._windows()
+        need_dem = any(o[0] == "limiter" for o in ops)
+        dem, code, origin, rows, cols = None, _lib.OCSB_F32, None, 0, 0
+        if need_dem:
+            dem = self._raster.device_band(1, self._device)
+            origin = self._raster.device_band_origin(1, self._device)
+            code = _dem_dtype_code(dem)
+            rows, cols = int(dem.shape[0]), int(dem.shape[1])
+            for win in windows:
+                if self._band_of(win) is not None and (win.width < 2 or win.height < 2):
+                    raise ValueError(
+                        "Shape of array too small to calculate a numerical "
+                        "gradient, at least (edge_order + 1) elements are required.")
+        wins, dem_off, hfun_off, keep = self._window_batch(windows, origin)
+        if not len(wins):
+            return
+        # vertex sets live on the device for this call
+        dev_ops, hold = [], []
+        for o in ops:
+            if o[0] == "feature" and not (isinstance(o[1], torch.Tensor) and o[1].is_cuda):
+                t = o[1] if isinstance(o[1], torch.Tensor) else torch.from_numpy(o[1])
+                t = t.to(f"cuda:{self._device}")
+                hold.append(t)
+                o = (o[0], t) + tuple(o[2:])
+                op_array = None
+            dev_ops.append(o)
+        ctx.hfun_pass_windows(
+            wins, dem_off if need_dem else None, hfun_off, dem, code, w, rows, cols,
+            old, w, new, w, self._raster.dx, self._raster.dy, self._hmin, self._hmax,
+            dev_ops, keep_wh=keep, status=status, op_array=op_array)
+        self._last_verts = hold or getattr(self, "_last_verts", None)
 
     def _dem_source(self):
         """(address of raster row `origin`, dtype code, element size, origin)
@@ -190,11 +266,31 @@ class HfunRaster:
         """ocsb_hfun_pass over every window.  ``dst``: None = the device
         raster, else a C-contiguous float32 host array (numpy or CPU torch
         tensor, ideally pinned) of the owned rows that receives the result."""
-        ops, self._queue = self._queue, []
+        ops = self._queue
+        need_dem = any(o[0] == "limiter" for o in ops)
+        r = self._raster
+        resident = dst is None and self._host_vals is None and (
+            not need_dem or r._dev_cache.get((1, self._device)) is not None)
+        if resident and (not need_dem or
+                         r._dev_cache[(1, self._device)].dtype == __import__("torch").float32):
+            # everything on the device: one asynchronous tiled sweep
+            import torch
+            self._queue = []
+            if self._status is None:
+                self._status = torch.zeros(2, dtype=torch.int32,
+                                           device=f"cuda:{self._device}")
+            buf = self._hfun
+            self._tiled_pass(ops, None if self._pristine else buf, buf,
+                             status=self._status)
+            self._pending.append((ops, self._pristine))
+            self._pending_keep = self._keep
+            self._keep = []
+            self._pristine = False
+            return
+        self._verify()
         ctx = self._ctx()
         w = self.width
         b0 = self._band[0]
-        need_dem = any(o[0] == "limiter" for o in ops)
         dem_keep, dem_addr, code, es, origin = (None, 0, _lib.OCSB_F32, 4, 0)
         if need_dem:
             dem_keep, dem_addr, code, es, origin = self._dem_source()
@@ -222,12 +318,15 @@ class HfunRaster:
                 None if in_addr is None else in_addr + off, w, out_addr + off, w,
                 dx, dy, self._hmin, self._hmax, ops)
         del dem_keep
-        self._keep = []
-        self._pristine = False
         if dst is None:
+            self._queue = []
+            self._keep = []
+            self._pristine = False
             self._host_vals = None
-        else:
-            self._host_vals = dst.numpy() if hasattr(dst, "numpy") else dst
+        # a host-bound pass leaves the object as it was (pre-pass raster + the
+        # queued ops): the result lives in the CALLER's buffer only, so nothing
+        # the caller does to that buffer can change the size function; the
+        # device raster is produced by running the queue again when needed
 
     def _materialize_queue(self) -> None:
         """Eager ops need the queue drained and the raster on the device."""
@@ -266,7 +365,20 @@ class HfunRaster:
         wins = (_lib.ocsb_win * len(recs))(*[r[0] for r in recs])
         dem_off = np.array([r[1] for r in recs], dtype=np.int64)
         hfun_off = np.array([r[2] for r in recs], dtype=np.int64)
-        out = (wins, dem_off, hfun_off)
+        # overlapping windows (overlap > 0): the later window wins, so window k
+        # keeps the pixels left of / above where the next window of its row /
+        # the next window row starts (get_iter_windows lays out a regular grid)
+        keep = None
+        if self._needs_double_buffer(windows):
+            cols = sorted({wn.col_off for wn in windows})
+            rows = sorted({wn.row_off for wn in windows})
+            ncol = dict(zip(cols[:-1], cols[1:]))
+            nrow = dict(zip(rows[:-1], rows[1:]))
+            keep = np.array(
+                [[min(wn.width, ncol.get(wn.col_off, 1 << 60) - wn.col_off),
+                  min(wn.height, nrow.get(wn.row_off, 1 << 60) - wn.row_off)]
+                 for wn in windows if self._band_of(wn) is not None], dtype=np.int32)
+        out = (wins, dem_off, hfun_off, keep)
         self._batch_cache = (key, out)
         return out
 
@@ -366,7 +478,8 @@ class HfunRaster:
         ``out``: optional (pinned) CPU torch tensor to receive the values."""
         if band not in (None, 1):
             raise IndexError("the hfun raster has a single band")
-        if window is None and (self._queue or self._host_vals is not None):
+        if window is None and self._queue and (
+                out is not None or self._raster._dev_cache.get((1, self._device)) is None):
             # deferred mode: stream the pass straight into the host buffer
             import torch
             h, w = self._band[1] - self._band[0], self.width
@@ -375,10 +488,7 @@ class HfunRaster:
             elif tuple(out.shape) != (h, w):
                 raise ValueError("out does not match the owned rows")
             arr = out.numpy() if isinstance(out, torch.Tensor) else out
-            if self._queue:
-                self._run_pass(out)
-            elif arr is not self._host_vals:
-                np.copyto(arr, self._host_vals)
+            self._run_pass(out)
             return arr
         self._materialize()
         t = self._hfun
@@ -679,10 +789,17 @@ class HfunRaster:
         new = old
         if not self._pristine and self._needs_double_buffer(windows):
             new = old.clone()
+        if True:
+            # the window loop inside the kernels: one tiled sweep whose units
+            # of work come from the window table (ocsb_hfun_pass_windows)
+            self._tiled_pass([("feature", verts, nv, float(expansion_rate),
+                               float(target_size), fuse)],
+                             None if self._pristine else old, new)
+            windows = []
         if len(windows) > 1:
             # the window loop as ONE library call: windows overlap on the
             # library's worker streams (ocsb_hfun_op_windows)
-            wins, dem_off, hfun_off = self._window_batch(windows)
+            wins, dem_off, hfun_off, _ = self._window_batch(windows)
             if len(wins):
                 ctx.hfun_op_windows(
                     wins, None, hfun_off, None, _lib.OCSB_F32, w,
@@ -739,13 +856,19 @@ class HfunRaster:
         if not self._pristine and self._needs_double_buffer(windows):
             new = old.clone()
         dx, dy = self._raster.dx, self._raster.dy
+        if code == _lib.OCSB_F32 or not self._needs_double_buffer(windows):
+            # one tiled sweep over the window table (a float64 DEM runs window
+            # by window inside the same call)
+            self._tiled_pass([("limiter", hmin, hmax, lower_bound, upper_bound, fuse)],
+                             None if self._pristine else old, new)
+            windows = []
         if len(windows) > 1:
             for win in windows:
                 if self._band_of(win) is not None and (win.width < 2 or win.height < 2):
                     raise ValueError(
                         "Shape of array too small to calculate a numerical "
                         "gradient, at least (edge_order + 1) elements are required.")
-            wins, dem_off, hfun_off = self._window_batch(windows, dem_origin)
+            wins, dem_off, hfun_off, _ = self._window_batch(windows, dem_origin)
             if len(wins):
                 ctx.hfun_op_windows(
                     wins, dem_off, hfun_off, dem, code, w,

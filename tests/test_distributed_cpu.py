@@ -265,3 +265,45 @@ def test_all_gather_with_pre_exchanged_sizes():
     for sizes, a, b, bad in run_ranks(_ragged_plan_case, 2):
         assert sizes == [2, 5] and bad
         np.testing.assert_array_equal(a, b)
+
+
+def _band_exchange_case(rank, world):
+    """BandExchange: padded-block vertex all-gather (the filler entries repeat a
+    real vertex or are far away) and the boundary-row all-gather that fills the
+    DEM halo slots, both into persistent buffers."""
+    from scipy.spatial import cKDTree
+    H, W = 41, 37
+    z = S.synth_dem(H, W, seed=3)
+    part = D.RowBands(H, world)
+    r0, r1 = part.band(rank)
+    s0, s1 = part.stored(rank)
+    rng = np.random.default_rng(7 + rank)
+    n = [5, 0, 9][rank % 3]               # ragged; rank 1 contributes nothing
+    v = torch.from_numpy(rng.random((n, 2)) * 100.0)
+    ex = D.BandExchange(n, W, torch.float32, "cpu", part, rank)
+    out = {}
+    for rep in range(2):                  # persistent buffers: a second step too
+        g = ex.gather_vertices(v)
+        real = ex.real_vertices(g).numpy()
+        buf = torch.zeros((s1 - s0, W), dtype=torch.float32)
+        buf[r0 - s0:r1 - s0] = torch.from_numpy(z[r0:r1])
+        ex.exchange_halo(buf, s0)
+        out[rep] = (np.array_equal(buf.numpy(), z[s0:s1]), real.copy(),
+                    g.numpy().copy())
+    # nearest-vertex distances over the padded array == over the real vertices
+    q = rng.random((200, 2)) * 100.0
+    d_pad = cKDTree(out[1][2]).query(q)[0]
+    d_real = cKDTree(out[1][1]).query(q)[0]
+    return (out[0][0] and out[1][0], v.numpy(), out[1][1],
+            bool(np.array_equal(d_pad, d_real)), list(ex.sizes))
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_band_exchange_persistent_buffers(world):
+    res = run_ranks(_band_exchange_case, world)
+    expect = np.concatenate([r[1] for r in res])
+    for ok, _, real, same_d, sizes in res:
+        assert ok
+        np.testing.assert_array_equal(real, expect)
+        assert same_d
+        assert sizes == [len(r[1]) for r in res]

@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol(lib):
         assert hasattr(lib, n), f"libocsb200.so does not export {n}"
     # ... and the ctypes binding covers the whole header
     assert sorted(_lib.SIGNATURES) == names
-    assert lib.ocsb_abi_version() == 4
+    assert lib.ocsb_abi_version() == 5
     assert lib.ocsb_kernel_class_name(6) == b"feature_eval"
 
 
