@@ -425,10 +425,14 @@ def run_ours(args, rank, world, local_rank):
     size = args.size
     H = W = size
 
+    note("inputs")
     run = BandRun(args, H, W, rank, world, dev, eager=args.eager)
     nv_total = run.nv_total
+    note(f"warm-up ({len(run.pts_local)} local / {nv_total} vertices)")
     for _ in range(max(args.warmup, 3)):
         run.step()
+    torch.cuda.synchronize(dev)
+    note("timed steps")
 
     # ---- timed: device-resident -------------------------------------------
     sampler = ClockSampler(dev)
@@ -446,18 +450,28 @@ def run_ours(args, rank, world, local_rank):
     px_rank = float(run.b1 - run.b0) * W
     value = px_total / (ms_step * 1e-3) / 1e6
 
+    note(f"timed: {ms_step:.4f} ms per step")
     # ---- parity at this rank count (outside the timed region) ---------------
     parity = None
     if not args.no_parity:
-        n_px = run.check_parity()
-        tot = torch.tensor([n_px], dtype=torch.int64, device=f"cuda:{dev}")
+        err = None
+        try:
+            n_px = run.check_parity()
+        except Exception as e:          # every rank must reach the reduction
+            n_px, err = 0, f"{type(e).__name__}: {e}"
+            print(f"[bench rank {rank}] parity check FAILED: {err}", file=sys.stderr,
+                  flush=True)
+        tot = torch.tensor([n_px, 1 if err else 0], dtype=torch.int64,
+                           device=f"cuda:{dev}")
         if world > 1:
             dist.all_reduce(tot)
-        parity = {"checked": True, "pixels": int(tot.item()),
+        parity = {"checked": True, "ok": int(tot[1].item()) == 0,
+                  "failed_ranks": int(tot[1].item()), "pixels": int(tot[0].item()),
                   "how": "per rank: 4 random rows + the 2 rows next to its band "
                          "edges, every pixel bit-exact against cKDTree + size law "
                          "+ numpy stencil on the 3-row strip"}
 
+    note("parity done")
     # ---- roofline of the dominant kernel -----------------------------------
     peak, peak_src = measured_peaks()
     dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else None
@@ -531,7 +545,7 @@ def run_ours(args, rank, world, local_rank):
                            "gathered every step"),
             "n_vertices": nv_total,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-            "parity_checked": bool(parity), "parity": parity,
+            "parity_checked": bool(parity and parity["ok"]), "parity": parity,
             "gpu_launches": int(launches), "clocks": clocks,
             "secondary": secondary,
         }
@@ -764,8 +778,23 @@ def bench_interp(args, rank, world, dev, ctx, peak):
     return out
 
 
+def note(msg):
+    """Progress marker on stderr (BENCH_VERBOSE=1)."""
+    if os.environ.get("BENCH_VERBOSE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} +{time.perf_counter() - T_START:.1f}s] "
+              f"{msg}", file=sys.stderr, flush=True)
+
+
+T_START = time.perf_counter()
+
+
 def main():
     args = parse_args()
+    wd = os.environ.get("BENCH_WATCHDOG")
+    if wd:
+        # a hung run prints where every thread of every rank stands, then exits
+        import faulthandler
+        faulthandler.dump_traceback_later(float(wd), exit=True)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

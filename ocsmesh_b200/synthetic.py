@@ -56,29 +56,43 @@ def synth_dem(height: int, width: int, seed: int = 1, noise: float = 0.01,
     """
     r0, r1 = (0, height) if rows is None else rows
     x = x0 + (np.arange(width) + 0.5) * pixel
-    y = y0 + (height - np.arange(r0, r1) - 0.5) * pixel
     xc = x0 + 0.5 * width * pixel
     yc = y0 + 0.5 * height * pixel
+    terms = _wave_terms(seed)
     # separable expansion  z = sum_t Y_t(y) X_t(x)
-    Y = [40.0 * np.cos(2 * np.pi * y / 5100.0), np.ones_like(y), -0.003 * (y - yc)]
     X = [np.sin(2 * np.pi * x / 7300.0), 0.004 * (x - xc), np.ones_like(x)]
-    for a, kx, ky, ph in _wave_terms(seed):
+    for a, kx, ky, ph in terms:
         # a sin(kx x + ky y + ph) = a [sin(kx x + ph) cos(ky y) + cos(kx x + ph) sin(ky y)]
-        X.append(np.sin(kx * (x - xc) + ph)); Y.append(a * np.cos(ky * (y - yc)))
-        X.append(np.cos(kx * (x - xc) + ph)); Y.append(a * np.sin(ky * (y - yc)))
-    Ym = np.stack(Y, axis=1).astype(np.float32)
+        X.append(np.sin(kx * (x - xc) + ph))
+        X.append(np.cos(kx * (x - xc) + ph))
     Xm = np.stack(X, axis=0).astype(np.float32)
+
+    def y_terms(ra, rb):
+        y = y0 + (height - np.arange(ra, rb) - 0.5) * pixel
+        Y = [40.0 * np.cos(2 * np.pi * y / 5100.0), np.ones_like(y), -0.003 * (y - yc)]
+        for a, kx, ky, ph in terms:
+            Y.append(a * np.cos(ky * (y - yc)))
+            Y.append(a * np.sin(ky * (y - yc)))
+        return np.stack(Y, axis=1).astype(np.float32)
+
     out = np.empty((r1 - r0, width), dtype=dtype)
-    step = max(1, (1 << 24) // max(width, 1))
-    for a in range(0, r1 - r0, step):
-        b = min(r1 - r0, a + step)
-        blk = Ym[a:b] @ Xm
+    # The matmul runs over blocks of ABSOLUTE rows [k B, (k + 1) B): whatever
+    # `rows` is asked for, a raster row always comes out of the same call with
+    # the same operands, so row blocks computed by different processes (the
+    # ranks of a multi-GPU run, a rank's halo row and its neighbour's band row)
+    # are bit-identical -- a BLAS result may depend on the block's row count.
+    B = 256
+    for k in range(r0 // B, (r1 + B - 1) // B):
+        a, b = k * B, min(height, (k + 1) * B)
+        blk = y_terms(a, b) @ Xm
+        lo, hi = max(a, r0), min(b, r1)
+        blk = blk[lo - a:hi - a]
         if noise:
-            # one stream per (seed, absolute row block) -> independent of `rows`
-            for rr in range(a, b):
-                g = np.random.default_rng([seed, 7919, r0 + rr])
-                blk[rr - a] += noise * g.standard_normal(width, dtype=np.float32)
-        out[a:b] = blk
+            # one stream per (seed, absolute row) -> independent of `rows`
+            for rr in range(lo, hi):
+                g = np.random.default_rng([seed, 7919, rr])
+                blk[rr - lo] += noise * g.standard_normal(width, dtype=np.float32)
+        out[lo - r0:hi - r0] = blk
     return out
 
 

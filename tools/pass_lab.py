@@ -27,8 +27,20 @@ ops = [("feature", pts, len(pts), 0.001, 100.0, True), ("limiter", 50.0, 1500.0,
 sel = os.environ.get("LAB_OPS", "both")
 if sel == "feat": ops = ops[:1]
 if sel == "lim": ops = ops[1:]
-def step():
-    ctx.hfun_pass(win, z, _lib.OCSB_F32, n, None, n, out, n, 10.0, 10.0, 100.0, 1500.0, ops, 0)
+band = os.environ.get("LAB_BAND")
+if band:
+    # a rank's share of the raster: rows [rb, re) of the window, asynchronous call
+    rb, re = (int(v) for v in band.split(":"))
+    win = _lib.make_win((tr[2], tr[5] + tr[4] * n, tr[2] + tr[0] * n, tr[5]), n, n, rb, re)
+    wins = (_lib.ocsb_win * 1)(win)
+    off = np.zeros(1, np.int64)
+    status = torch.zeros(2, dtype=torch.int32, device="cuda")
+    def step():
+        ctx.hfun_pass_windows(wins, off, off, z, _lib.OCSB_F32, n, n, n, None, n, out, n,
+                              10.0, 10.0, 100.0, 1500.0, ops, status=status)
+else:
+    def step():
+        ctx.hfun_pass(win, z, _lib.OCSB_F32, n, None, n, out, n, 10.0, 10.0, 100.0, 1500.0, ops, 0)
 for _ in range(3): step()
 torch.cuda.synchronize()
 ctx.reset_timing(); ctx.set_timing(True)
