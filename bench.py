@@ -26,7 +26,7 @@ N > 1 is STRONG scaling: the same 20000 x 20000 raster split into N row bands
 (2500 rows per GPU at N = 8; one semantic window = the whole raster, so
 coordinates and radius law are global).  Every step the ranks all-gather the
 contour vertices they traced on their own bands and their boundary DEM rows
-over NCCL (two collectives into persistent buffers), then run the sweep on
+over NCCL (one collective into persistent buffers), then run the sweep on
 their band.  After the timed region every rank checks sampled rows of its band
 bit-exactly against the oracle (cKDTree + numpy stencil): "parity_checked".
 """
@@ -334,9 +334,9 @@ class BandRun:
         """A4 init, vertex all-gather, DEM halo rows, A6/A7 + A8(A9): one sweep."""
         h = self.hfun
         h.reset()
-        verts = self.exch.gather_vertices(self.verts_local)
-        self.exch.exchange_halo(self.raster.device_band(1, self.dev),
-                                self.raster.device_band_origin(1, self.dev))
+        verts = self.exch.exchange(self.verts_local,
+                                   self.raster.device_band(1, self.dev),
+                                   self.raster.device_band_origin(1, self.dev))
         h.add_feature_points(verts, RATE, TARGET)
         h.add_gradient_delimiter(hmin=LIM_HMIN, hmax=LIM_HMAX)
         h.flush()
@@ -538,8 +538,8 @@ def run_ours(args, rank, world, local_rank):
             "config": cfg,
             "parallelism": (f"row bands x{world} of ONE {H}x{W} raster "
                             f"({H // world} rows per GPU); per step: vertex "
-                            "all-gather + boundary-row all-gather (NCCL), then "
-                            "one tiled sweep per band"),
+                            "all-gather + boundary DEM rows in one NCCL "
+                            "collective, then one tiled sweep per band"),
             "vertex_set": ("contours of each rank's band (cell rows partition the "
                            "raster's), each piece resampled on its own; all-"
                            "gathered every step"),

@@ -177,6 +177,57 @@ __global__ void vg_scatter_kernel(VGrid G, const double2 *verts, int nv, int *cu
     G.sid[pos] = i;
 }
 
+// very small vertex sets: histogram, scan and scatter in ONE launch of one CTA
+// -- the three launches above are pure launch latency at that size
+constexpr int kVgSmallCells = 8192;
+constexpr int kVgSmallVerts = 4096;   // beyond that one CTA's shared-memory atomics
+                                      // on a few populated cells are slower (measured)
+
+__global__ void __launch_bounds__(1024) vg_build_small_kernel(VGrid G, const double2 *verts,
+                                                              int nv, int *far_flag) {
+    __shared__ int s_cnt[kVgSmallCells];
+    __shared__ int s_part[1024];
+    const int NX = G.ncx + 2, ncell = NX * (G.ncy + 2);
+    for (int i = threadIdx.x; i < ncell; i += 1024) s_cnt[i] = 0;
+    __syncthreads();
+    bool far = false;
+    for (int i = threadIdx.x; i < nv; i += 1024) {
+        const double2 v = verts[i];
+        atomicAdd(&s_cnt[vg_cy(G, v.y) * NX + vg_cx(G, v.x)], 1);
+        far = far || !(fabs(v.x) <= 1e14 && fabs(v.y) <= 1e14);
+    }
+    if (far) *far_flag = 1;
+    __syncthreads();
+    // exclusive scan: each thread owns a contiguous run of cells
+    const int per = (ncell + 1023) / 1024;
+    const int lo = min(ncell, (int)threadIdx.x * per), hi = min(ncell, lo + per);
+    int sum = 0;
+    for (int i = lo; i < hi; ++i) sum += s_cnt[i];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = threadIdx.x >= o ? s_part[threadIdx.x - o] : 0;
+        __syncthreads();
+        s_part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int run = s_part[threadIdx.x] - sum;
+    for (int i = lo; i < hi; ++i) {
+        const int c = s_cnt[i];
+        G.start[i] = run;
+        s_cnt[i] = run;                 // becomes the scatter cursor
+        run += c;
+    }
+    if (threadIdx.x == 1023) G.start[ncell] = s_part[1023];
+    __syncthreads();
+    for (int i = threadIdx.x; i < nv; i += 1024) {
+        const double2 v = verts[i];
+        const int pos = atomicAdd(&s_cnt[vg_cy(G, v.y) * NX + vg_cx(G, v.x)], 1);
+        G.sv[pos] = v;
+        G.sid[pos] = i;
+    }
+}
+
 // ---------------------------------------------------------------------------
 // dominators of a rect, found by the warps of a block (lane = candidate)
 // ---------------------------------------------------------------------------
@@ -371,7 +422,9 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
                     const int p = atomicAdd(&s_col.count, 1);
                     if (p < kRootCap) s_col.buf[p] = id;
                 } else {
-                    A.l2.ids[s_col.base + atomicAdd(&s_col.pos, 1)] = id;
+                    const int p = atomicAdd(&s_col.pos, 1);
+                    A.l2.ids[s_col.base + p] = id;
+                    A.l2.xy[s_col.base + p] = v;
                 }
             }
         }
@@ -394,8 +447,11 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
     const int total = s_col.count;
     if (total == 0) return;
     if (total <= kRootCap) {
-        for (int i = threadIdx.x; i < total; i += kRootThreads)
-            A.l2.ids[s_col.base + i] = s_col.buf[i];
+        for (int i = threadIdx.x; i < total; i += kRootThreads) {
+            const int id = s_col.buf[i];
+            A.l2.ids[s_col.base + i] = id;
+            A.l2.xy[s_col.base + i] = A.verts[id];
+        }
     } else {
         sweep(true);
     }
@@ -404,7 +460,7 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
 // ---------------------------------------------------------------------------
 // level 1: 256-px tiles from their 1024-px parent list
 // ---------------------------------------------------------------------------
-constexpr int kL1Threads = 128;
+constexpr int kL1Threads = 256;
 constexpr int kL1Cap = 1024;
 
 __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
@@ -438,7 +494,7 @@ __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
         const int i = b0 + lane;
         const bool valid = i < pcnt;
         double2 v = make_double2(0.0, 0.0);
-        if (valid) v = A.verts[A.l2.ids[poff + i]];
+        if (valid) v = A.l2.xy[poff + i];
         dom_step(q, valid, v, key, s_tab[wid], lane);
     }
     __syncwarp();
@@ -447,10 +503,10 @@ __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
     __syncthreads();
     auto sweep = [&](bool write) {
         for (int i = threadIdx.x; i < pcnt; i += kL1Threads) {
-            const int id = A.l2.ids[poff + i];
-            const double2 v = A.verts[id];
+            const double2 v = A.l2.xy[poff + i];
             if (rect_d2(q, v) > A.r2lim) continue;
             if (dominated_tab(s_fin, corner_d2(q, v))) continue;
+            const int id = A.l2.ids[poff + i];
             if (!write) {
                 const int p = atomicAdd(&s_col.count, 1);
                 if (p < kL1Cap) s_col.buf[p] = id;
@@ -1183,7 +1239,7 @@ EncodeTiledFn encode_tiled_fn() {
 
 // one instantiation of the persistent kernel: resident grid, opt-in shared memory
 template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND>
-int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P) {
+int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P) {
     auto kern = pass2_kernel<HAS_OLD, HAS_FEAT, HAS_LIM, BAND>;
     static int resident[64] = {};     // per device: CTAs that fit the whole GPU
     int dev = 0;
@@ -1199,7 +1255,13 @@ int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P) 
         OCSB_REQUIRE(n > 0 && sms > 0, "pass2_kernel does not fit an SM");
         resident[dev] = n * sms;
     }
-    const int grid = (int)std::min<long long>((P.n_tiles + kChunk - 1) / kChunk,
+    // chunk: 8 tiles per counter fetch, fewer when that would leave a CTA with
+    // less than ~8 fetches (a band of a multi-GPU run): the tail of a launch is
+    // one chunk long
+    int chunk = (int)(P.n_tiles / ((long long)resident[dev] * 8));
+    chunk = std::max(1, std::min(kChunkMax, chunk));
+    P.chunk = chunk;
+    const int grid = (int)std::min<long long>((P.n_tiles + chunk - 1) / chunk,
                                               (long long)resident[dev]);
     kern<<<grid, kP2Threads, sizeof(P2Smem), ctx->stream>>>(tmap, P);
     return OCSB_OK;
@@ -1378,17 +1440,23 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             OCSB_TRY(pools.get(&G.start, (size_t)ncell + 1));
             OCSB_TRY(pools.get(&G.sv, (size_t)nv));
             OCSB_TRY(pools.get(&G.sid, (size_t)nv));
-            OCSB_CUDA(cudaMemsetAsync(counts, 0, (size_t)ncell * sizeof(int), ctx->stream));
             const double2 *verts = reinterpret_cast<const double2 *>(pf.verts);
-            OCSB_TIME(ctx, KC_FEATURE_REFINE);
-            vg_hist_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, counts, far_flag);
-            OCSB_LAUNCHED(ctx);
-            OCSB_TIME(ctx, KC_FEATURE_REFINE);
-            vg_scan_kernel<<<1, 1024, 0, ctx->stream>>>(counts, ncell, G.start, cursor);
-            OCSB_LAUNCHED(ctx);
-            OCSB_TIME(ctx, KC_FEATURE_REFINE);
-            vg_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, cursor);
-            OCSB_LAUNCHED(ctx);
+            if (ncell <= kVgSmallCells && nv <= kVgSmallVerts) {
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                vg_build_small_kernel<<<1, 1024, 0, ctx->stream>>>(G, verts, nv, far_flag);
+                OCSB_LAUNCHED(ctx);
+            } else {
+                OCSB_CUDA(cudaMemsetAsync(counts, 0, (size_t)ncell * sizeof(int), ctx->stream));
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                vg_hist_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, counts, far_flag);
+                OCSB_LAUNCHED(ctx);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                vg_scan_kernel<<<1, 1024, 0, ctx->stream>>>(counts, ncell, G.start, cursor);
+                OCSB_LAUNCHED(ctx);
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                vg_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, cursor);
+                OCSB_LAUNCHED(ctx);
+            }
             OCSB_CHECK_LAUNCH();
 
             BuildArgs B;
@@ -1408,7 +1476,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             OCSB_TRY(pools.get(&B.l1.cnt, (size_t)n1));
             OCSB_TRY(pools.get(&B.l1.ids, (size_t)cap1));
             OCSB_TRY(pools.get(&B.l1.xy, (size_t)cap1));
-            B.l2.xy = nullptr;
+            OCSB_TRY(pools.get(&B.l2.xy, (size_t)cap2));
             B.ctr2 = ctrs + 2 * f; B.ctr1 = ctrs + 2 * f + 1;
             B.cap2 = cap2; B.cap1 = cap1;
             B.overflow = overflow;
@@ -1440,7 +1508,8 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 L.ctr = ctrs + 2 * kMaxFeat; L.cap = cap0;
                 L.overflow = overflow;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
-                l0_kernel<<<(unsigned)((n0 + 7) / 8), 256, 0, ctx->stream>>>(L);
+                L.n_parents = (int)n1;
+                l0_kernel<<<(unsigned)n1, 256, 0, ctx->stream>>>(L);
                 OCSB_LAUNCHED(ctx);
                 OCSB_CHECK_LAUNCH();
             }

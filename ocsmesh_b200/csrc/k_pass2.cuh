@@ -30,7 +30,8 @@ constexpr int kP2Warps = kP2Threads / 32;
 #ifndef OCSB_PASS2_CHUNK
 #define OCSB_PASS2_CHUNK 8
 #endif
-constexpr int kChunk = OCSB_PASS2_CHUNK;   // consecutive tiles per fetch of the tile counter
+constexpr int kChunkMax = OCSB_PASS2_CHUNK; // consecutive tiles per fetch of the tile counter
+                                            // (fewer when a CTA only gets a few tiles)
 
 // slot header (16 bytes): candidates of the tile; more than kSlotCap live in the
 // overflow pool at element `off`
@@ -55,6 +56,7 @@ struct P2Args {
     LimiterDev<float> lim;
     float lo, hi;
     int *counter;           // zeroed before the launch
+    int chunk;              // tiles per fetch of the counter
     const int *overflow;
 };
 
@@ -107,8 +109,8 @@ __device__ __forceinline__ void p2_produce(const CUtensorMap *tmap, const P2Args
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.full[stage]);
     int t = S.q_next, tx = S.q_tx, ty = S.q_ty;
     if (t == S.q_end) {
-        t = atomicAdd(A.counter, kChunk) + (int)gridDim.x * kChunk;
-        S.q_end = t + kChunk;
+        t = atomicAdd(A.counter, A.chunk) + (int)gridDim.x * A.chunk;
+        S.q_end = t + A.chunk;
         tx = -1;
     }
     if (t >= A.n_tiles) {
@@ -384,8 +386,8 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         S.cur_wi = 0; S.cur_next = -1;       // forces the first window lookup
-        S.q_next = (int)blockIdx.x * kChunk;   // the first chunk is static
-        S.q_end = S.q_next + kChunk;
+        S.q_next = (int)blockIdx.x * A.chunk;  // the first chunk is static
+        S.q_end = S.q_next + A.chunk;
         S.q_tx = -1; S.q_ty = 0; S.ended = 0;
         p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 0);
         if (!S.ended) p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 1);
@@ -486,12 +488,13 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
 }
 
 // ---------------------------------------------------------------------------
-// level 0: the slot of every 64-px tile from its 256-px parent list (one warp
-// per tile; tiles without a parent list get an empty header)
+// level 0: the slots of the (up to 16) 64-px tiles of one 256-px parent tile per
+// CTA: the parent's list is read ONCE into shared memory, a warp filters two
+// children from there; a parent without a list only writes empty headers
 // ---------------------------------------------------------------------------
 struct L0Args {
     const PWin *wins;
-    int n_wins, n_tiles;
+    int n_wins, n_tiles, n_parents;
     const int *cnt1, *off1;
     const double2 *xy1;
     double r2lim;
@@ -501,63 +504,59 @@ struct L0Args {
     int *overflow;
 };
 
+constexpr int kL0Stage = 1024;       // parent candidates staged in shared memory
+
 __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
     __shared__ DomTable s_tab[8];
+    __shared__ __align__(16) double2 s_xy[kL0Stage];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int t = blockIdx.x * 8 + wid;
-    if (t >= A.n_tiles || *A.overflow) return;
-    const int wi = A.n_wins == 1 ? 0 : find_win(A.wins, A.n_wins, t, 0);
+    const int t1 = blockIdx.x;
+    if (t1 >= A.n_parents || *A.overflow) return;
+    const int wi = A.n_wins == 1 ? 0 : find_win(A.wins, A.n_wins, t1, 1);
     const PWin &W = A.wins[wi];
-    const int lt = t - W.base0;
-    const int ty = lt / W.n0x, tx = lt - ty * W.n0x;
-    const int t1 = W.base1 + (ty >> 2) * W.n1x + (tx >> 2);
+    const int lt1 = t1 - W.base1;
+    const int ty1 = lt1 / W.n1x, tx1 = lt1 - ty1 * W.n1x;
     const int pcnt = A.cnt1[t1], poff = A.off1[t1];
-    double2 *slot = A.slots + (size_t)t * kSlot;
+    const int ncx = min(4, W.n0x - 4 * tx1), ncy = min(4, W.n0y - 4 * ty1);
     SlotHead hd;
     hd.cnt = 0; hd.pad = 0; hd.off = 0;
     if (pcnt == 0) {
-        if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
+        if ((int)threadIdx.x < 16) {
+            const int cx = threadIdx.x & 3, cy = threadIdx.x >> 2;
+            if (cx < ncx && cy < ncy) {
+                const int t = W.base0 + (4 * ty1 + cy) * W.n0x + 4 * tx1 + cx;
+                *reinterpret_cast<SlotHead *>(A.slots + (size_t)t * kSlot) = hd;
+            }
+        }
         return;
     }
+    const bool staged = pcnt <= kL0Stage;
+    if (staged)
+        for (int i = threadIdx.x; i < pcnt; i += 256) s_xy[i] = A.xy1[poff + i];
+    __syncthreads();
+    const double2 *src = staged ? s_xy : A.xy1 + poff;
     const int bw = W.ax.n, bh = W.re - W.rb;
-    const int c0 = tx * kT0, r0 = ty * kT0;
-    const Rect q = win_rect(W, c0, min(bw, c0 + kT0) - 1, r0, min(bh, r0 + kT0) - 1);
-    const double2 *src = A.xy1 + poff;
     DomTable &tab = s_tab[wid];
-    unsigned key[5];
+    for (int child = wid; child < 16; child += 8) {
+        const int cx = child & 3, cy = child >> 2;
+        if (cx >= ncx || cy >= ncy) continue;           // warp-uniform
+        const int tx = 4 * tx1 + cx, ty = 4 * ty1 + cy;
+        const int t = W.base0 + ty * W.n0x + tx;
+        double2 *slot = A.slots + (size_t)t * kSlot;
+        const int c0 = tx * kT0, r0 = ty * kT0;
+        const Rect q = win_rect(W, c0, min(bw, c0 + kT0) - 1, r0, min(bh, r0 + kT0) - 1);
+        unsigned key[5];
 #pragma unroll
-    for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
-    for (int b0 = 0; b0 < pcnt; b0 += 32) {
-        const int i = b0 + lane;
-        const bool valid = i < pcnt;
-        double2 v = make_double2(0.0, 0.0);
-        if (valid) v = src[i];
-        dom_step(q, valid, v, key, tab, lane);
-    }
-    __syncwarp();
-    int total = 0;
-    for (int b0 = 0; b0 < pcnt; b0 += 32) {
-        const int i = b0 + lane;
-        const bool valid = i < pcnt;
-        double2 v = make_double2(0.0, 0.0);
-        if (valid) v = src[i];
-        const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
-                          !dominated_tab(tab, corner_d2(q, v));
-        const unsigned m = __ballot_sync(0xffffffffu, keep);
-        const int pos = total + __popc(m & ((1u << lane) - 1u));
-        if (keep && pos < kSlotCap) slot[1 + pos] = v;
-        total += __popc(m);
-    }
-    if (total > kSlotCap) {
-        // the whole list goes to the overflow pool (contiguous)
-        unsigned long long base = 0;
-        if (lane == 0) {
-            base = atomicAdd(A.ctr, (unsigned long long)total);
-            if (base + total > A.cap) { *A.overflow = 1; base = ~0ull; }
+        for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
+        for (int b0 = 0; b0 < pcnt; b0 += 32) {
+            const int i = b0 + lane;
+            const bool valid = i < pcnt;
+            double2 v = make_double2(0.0, 0.0);
+            if (valid) v = src[i];
+            dom_step(q, valid, v, key, tab, lane);
         }
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base == ~0ull) return;
-        int w = 0;
+        __syncwarp();
+        int total = 0;
         for (int b0 = 0; b0 < pcnt; b0 += 32) {
             const int i = b0 + lane;
             const bool valid = i < pcnt;
@@ -566,11 +565,35 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
             const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
                               !dominated_tab(tab, corner_d2(q, v));
             const unsigned m = __ballot_sync(0xffffffffu, keep);
-            if (keep) A.pool[base + w + __popc(m & ((1u << lane) - 1u))] = v;
-            w += __popc(m);
+            const int pos = total + __popc(m & ((1u << lane) - 1u));
+            if (keep && pos < kSlotCap) slot[1 + pos] = v;
+            total += __popc(m);
         }
-        hd.off = (long long)base;
+        hd.cnt = total; hd.off = 0;
+        if (total > kSlotCap) {
+            // the whole list goes to the overflow pool (contiguous)
+            unsigned long long base = 0;
+            if (lane == 0) {
+                base = atomicAdd(A.ctr, (unsigned long long)total);
+                if (base + total > A.cap) { *A.overflow = 1; base = ~0ull; }
+            }
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base == ~0ull) continue;
+            int w = 0;
+            for (int b0 = 0; b0 < pcnt; b0 += 32) {
+                const int i = b0 + lane;
+                const bool valid = i < pcnt;
+                double2 v = make_double2(0.0, 0.0);
+                if (valid) v = src[i];
+                const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                                  !dominated_tab(tab, corner_d2(q, v));
+                const unsigned m = __ballot_sync(0xffffffffu, keep);
+                if (keep) A.pool[base + w + __popc(m & ((1u << lane) - 1u))] = v;
+                w += __popc(m);
+            }
+            hd.off = (long long)base;
+        }
+        __syncwarp();
+        if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
     }
-    hd.cnt = total;
-    if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
 }

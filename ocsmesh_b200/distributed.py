@@ -200,6 +200,19 @@ class BandExchange:
         self.rows_out = torch.empty((2, width), dtype=dem_dtype, device=device)
         self.rows_all = torch.empty((self.world * 2, width), dtype=dem_dtype,
                                     device=device)
+        # packed form (one collective per step for both): per rank
+        # [first / last owned DEM row | vertex block] as raw bytes
+        es = torch.empty((), dtype=dem_dtype).element_size()
+        self._row_bytes = 2 * int(width) * es
+        self._row_bytes += (-self._row_bytes) % 8            # float64 view behind it
+        blk = self._row_bytes + self.cap * 16
+        self._send = torch.zeros(blk, dtype=torch.uint8, device=device)
+        self._recv = torch.zeros((self.world, blk), dtype=torch.uint8, device=device)
+        self._send_rows = self._send[:2 * int(width) * es].view(dem_dtype).view(2, width)
+        self._send_verts = self._send[self._row_bytes:].view(torch.float64).view(self.cap, 2)
+        self._recv_rows = self._recv[:, :2 * int(width) * es].view(dem_dtype)   # (world, 2 W)
+        self._recv_verts = self._recv[:, self._row_bytes:].view(torch.float64)  # (world, 2 cap)
+        self._width = int(width)
 
     def gather_vertices(self, verts_local):
         """All ranks' vertices, (world * cap, 2), rank order (padded blocks)."""
@@ -216,6 +229,35 @@ class BandExchange:
         if self.world == 1:
             return self.block
         dist.all_gather_into_tensor(self.verts, self.block, group=self.group)
+        return self.verts
+
+    def exchange(self, verts_local, buf, origin: int):
+        """Both exchanges of a step in ONE collective: returns the gathered
+        (padded) vertex array and fills the halo slots of ``buf`` (raster rows
+        ``[origin, origin + len(buf))``: band + halo slots)."""
+        import torch.distributed as dist
+        if self.world == 1:
+            return self.gather_vertices(verts_local)
+        n = int(verts_local.shape[0])
+        if n != self.sizes[self.rank]:
+            raise ValueError("vertex count differs from the exchanged size")
+        sv = self._send_verts
+        if n:
+            sv[:n].copy_(verts_local)
+            if n < self.cap:
+                sv[n:].copy_(verts_local[n - 1:n].expand(self.cap - n, 2))
+        else:
+            sv.fill_(self.FAR)
+        r0, r1 = self.part.band(self.rank)
+        self._send_rows[0].copy_(buf[r0 - origin])
+        self._send_rows[1].copy_(buf[r1 - 1 - origin])
+        dist.all_gather_into_tensor(self._recv.view(-1), self._send, group=self.group)
+        self.verts.view(self.world, 2 * self.cap).copy_(self._recv_verts)
+        w = self._width
+        if self.rank > 0:                       # last row of the rank above
+            buf[r0 - 1 - origin].copy_(self._recv_rows[self.rank - 1, w:])
+        if self.rank < self.world - 1:          # first row of the rank below
+            buf[r1 - origin].copy_(self._recv_rows[self.rank + 1, :w])
         return self.verts
 
     def real_vertices(self, gathered):

@@ -288,7 +288,12 @@ def _band_exchange_case(rank, world):
         buf = torch.zeros((s1 - s0, W), dtype=torch.float32)
         buf[r0 - s0:r1 - s0] = torch.from_numpy(z[r0:r1])
         ex.exchange_halo(buf, s0)
-        out[rep] = (np.array_equal(buf.numpy(), z[s0:s1]), real.copy(),
+        # the packed form: both exchanges in one collective
+        buf2 = torch.zeros((s1 - s0, W), dtype=torch.float32)
+        buf2[r0 - s0:r1 - s0] = torch.from_numpy(z[r0:r1])
+        g2 = ex.exchange(v, buf2, s0)
+        same = bool(torch.equal(g2, g)) and bool(torch.equal(buf2, buf))
+        out[rep] = (np.array_equal(buf.numpy(), z[s0:s1]) and same, real.copy(),
                     g.numpy().copy())
     # nearest-vertex distances over the padded array == over the real vertices
     q = rng.random((200, 2)) * 100.0
