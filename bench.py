@@ -708,10 +708,14 @@ def bench_interp(args, rank, world, dev, ctx, peak):
             e1.record()
             torch.cuda.synchronize(dev)
             return e0.elapsed_time(e1) / steps
-        # resident layout = bucket order (values live in bucket order too);
-        # with `perm` the kernel scatters the values back to mesh order
+        # bucket-resident layout: nodes AND values live in bucket order; with
+        # `perm` the kernel scatters the values back to mesh order; the headline
+        # is what the public Mesh.interpolate runs: a gather in mesh order
+        ms_bucket = timed(None)
+        ms_unpermute = timed(perm)
+        xy_save, xy = xy, xy_raw
         ms = timed(None)
-        ms_mesh_order = timed(perm)
+        xy = xy_save
         # e2e: coords H2D + values D2H through Mesh.interpolate
         vh = torch.empty(n, dtype=torch.float64).pin_memory()
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -731,25 +735,44 @@ def bench_interp(args, rank, world, dev, ctx, peak):
             ms, ems = float(tt[0]), float(tt[1])
         # one launch serves all tiles: coordinates read once, 4 (1) texels and
         # one value per node
-        ach = (bpn * n) / (ms * 1e-3) / 1e9
+        ach = (bpn * n) / (ms * 1e-3) / 1e9      # headline: the mesh-order path
         # what the gather really moves (committed ncu capture): a touched DEM
         # row costs a 64-byte DRAM access whatever part of it is used
         traffic = ncu_traffic("interp_" + method, n)
         out[method] = {"Mnodes_per_s": K / (ms * 1e-3) / 1e6, "ms_per_step": ms,
-                       "traffic": traffic,
-                       "traffic_frac_of_peak": (traffic / (ms * 1e-3) / 1e9 / peak
-                                                if traffic else None),
-                       "e2e_Mnodes_per_s": K / (ems * 1e-3) / 1e6,
+                       "path": "mesh-order gather (what Mesh.interpolate runs), "
+                               "device-timed",
                        "roofline_frac": ach / peak,
+                       "roofline_bound": "sectors: one node per ~40 px, so every "
+                                         "texel row of a node costs its own 64-byte "
+                                         "DRAM access (profiles/r1h_interp_ncu_"
+                                         "summary.txt: 151 / 110 B per node moved "
+                                         "for 40 / 28 algorithmic)",
                        "algorithmic_bytes_per_node": bpn,
-                       "ms_per_step_mesh_order_outputs": ms_mesh_order,
-                       "bucket_pass_ms": bucket_ms}
+                       "bucket_resident": {
+                           "ms_per_step": ms_bucket,
+                           "roofline_frac": (bpn * n) / (ms_bucket * 1e-3) / 1e9 / peak,
+                           "traffic": traffic,
+                           "traffic_frac_of_peak": (traffic / (ms_bucket * 1e-3) / 1e9
+                                                    / peak if traffic else None),
+                           "ms_with_unpermuted_outputs": ms_unpermute,
+                           "bucket_pass_ms": bucket_ms},
+                       "e2e_Mnodes_per_s": K / (ems * 1e-3) / 1e6}
     # spline (the reference's default method): prefilter of every tile + one
     # evaluation launch, nodes in mesh order; no bucket / scatter variants
     def spline_call():
         EuclideanMesh2D._interp_device(ctx, rasters, xy_raw, vals, touched, "spline", 1, dev)
-    spline_call()
+    for r in rasters:                       # forget cached spline coefficients
+        for k in [k for k in r._dev_cache if isinstance(k, tuple) and k and
+                  k[0] == "spline_coef"]:
+            del r._dev_cache[k]
     torch.cuda.synchronize(dev)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    spline_call()                           # first call: prefilter of all tiles
+    f1.record()
+    torch.cuda.synchronize(dev)
+    first_ms = f0.elapsed_time(f1)
     ctx.reset_timing()
     ctx.set_timing(True)
     s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -766,9 +789,15 @@ def bench_interp(args, rank, world, dev, ctx, peak):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         sms = float(tt[0])
     out["spline"] = {"Mnodes_per_s": K / (sms * 1e-3) / 1e6, "ms_per_step": sms,
+                     "first_call_ms": first_ms,
+                     "roofline_frac": 88.0 * n / (sms * 1e-3) / 1e9 / peak,
+                     "algorithmic_bytes_per_node": 88.0,
                      "kernel_ms_per_step": skt,
-                     "note": "prefilter of all 16 tiles (one-off per raster, "
-                             "16 B/px) inside every step + evaluation (88 B/node)"}
+                     "note": "the B-spline coefficients of a raster window are "
+                             "computed by the first call (prefilter of all 16 "
+                             "tiles, 16 B/px: first_call_ms) and kept with the "
+                             "raster's device band; later calls only evaluate "
+                             "(88 B/node), nodes in mesh order"}
     out["config"] = (f"BASELINE.json configs[3]: {K} nodes ({args.nodes}/GPU), "
                      f"16 tiles {T}x{T} (4x4, {ovl}-px overlap), last wins; "
                      "nodes (and their values) resident in spatial-bucket order "

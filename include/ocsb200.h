@@ -504,6 +504,11 @@ typedef struct ocsb_interp_raster {
     int64_t        dem_stride;
     const uint8_t *nodata_mask;   /* NULL = no nodata */
     int64_t        mask_stride;
+    /* spline only, optional: the window's coefficients from an earlier
+     * ocsb_spline_prefilter call (device memory, height x width doubles): the
+     * prefilter (16 B/px, the bulk of a spline call) is then skipped.  The
+     * coefficients depend on the window's DEM values and shape only.          */
+    const double  *spline_coef;
 } ocsb_interp_raster;
 
 /* Equivalent to calling ocsb_interp once per entry in list order, but the node

@@ -37,7 +37,7 @@ class ocsb_win(C.Structure):
 class ocsb_interp_raster(C.Structure):
     _fields_ = [("win", ocsb_win), ("dem", c_vp), ("dem_dtype", c_i32),
                 ("dem_stride", c_i64), ("nodata_mask", c_vp),
-                ("mask_stride", c_i64)]
+                ("mask_stride", c_i64), ("spline_coef", c_vp)]
 
 
 class ocsb_hfun_op(C.Structure):
@@ -494,15 +494,17 @@ class Context:
     def interp_multi(self, entries, xy, K, method, touched, values, source=None,
                      perm=None):
         """``entries``: list of (win, dem, dem_dtype, dem_stride, mask,
-        mask_stride) in raster-list order (last valid hit wins)."""
+        mask_stride[, spline_coef]) in raster-list order (last valid hit wins)."""
         arr = (ocsb_interp_raster * len(entries))()
-        for a, (win, dem, dt, ds, mask, ms) in zip(arr, entries):
+        for a, e in zip(arr, entries):
+            win, dem, dt, ds, mask, ms = e[:6]
             a.win = win
             a.dem = ptr(dem)
             a.dem_dtype = int(dt)
             a.dem_stride = int(ds)
             a.nodata_mask = ptr(mask)
             a.mask_stride = int(ms)
+            a.spline_coef = ptr(e[6]) if len(e) > 6 else None
         check(self.lib.ocsb_interp_multi(self.handle, arr, len(entries), ptr(xy),
                                          int(K), int(method), ptr(touched),
                                          ptr(values), ptr(source), ptr(perm)))

@@ -311,8 +311,16 @@ struct BuildArgs {
     unsigned long long *ctr2, *ctr1;
     unsigned long long cap2, cap1;
     int *overflow;
+    int *sticky;            // status word of a pass sequence (or nullptr): a pass is a
+                            // no-op when it is set, and sets it when a pool overflows
     double r, r2lim;        // search radius (+inf: unbounded) and r^2 (1 + eps)
 };
+
+// pool overflow: this pass is void (and, in a sequence, every later one)
+__device__ __forceinline__ void flag_overflow(int *overflow, int *sticky) {
+    *overflow = 1;
+    if (sticky) *sticky = 1;
+}
 
 // survivors of a block are collected in shared memory first (one pass over the
 // parent), the pool chunk is reserved with ONE atomic so a list is contiguous
@@ -336,6 +344,12 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
     __shared__ DomTable s_fin;
     __shared__ unsigned s_key0;
     __shared__ Collect<kRootCap> s_col;
+    if (A.sticky && *A.sticky) {
+        // an earlier pass of the sequence failed: void this one (the kernels
+        // after this one look at the overflow flag only)
+        if (threadIdx.x == 0) *A.overflow = 1;
+        return;
+    }
     if (*A.overflow) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int t = blockIdx.x;
@@ -436,7 +450,7 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
         int total = s_col.count;
         if (total) {
             base = atomicAdd(A.ctr2, (unsigned long long)total);
-            if (base + total > A.cap2) { *A.overflow = 1; total = 0; }
+            if (base + total > A.cap2) { flag_overflow(A.overflow, A.sticky); total = 0; }
         }
         s_col.base = base;
         s_col.count = total;
@@ -524,7 +538,7 @@ __global__ void __launch_bounds__(kL1Threads) l1_kernel(BuildArgs A) {
         int total = s_col.count;
         if (total) {
             base = atomicAdd(A.ctr1, (unsigned long long)total);
-            if (base + total > A.cap1) { *A.overflow = 1; total = 0; }
+            if (base + total > A.cap1) { flag_overflow(A.overflow, A.sticky); total = 0; }
         }
         s_col.base = base;
         s_col.count = total;
@@ -574,6 +588,7 @@ struct TileArgs {
     int dem_rows, dem_cols;
     int use_tma;
     const int *overflow;    // int2 {pool overflow, a vertex beyond 1e14}
+    const int *sticky;      // status word of a pass sequence (or nullptr)
 };
 
 struct WarpScr {
@@ -791,7 +806,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs A) {
 
     PSTAT_CLK(st0);
     const int2 flags = *reinterpret_cast<const int2 *>(A.overflow);   // {overflow, far}
-    if (flags.x) return;
+    if (flags.x || (A.sticky && *A.sticky)) return;
     const bool far = flags.y != 0;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int wi = 0, tx, ty;
@@ -1353,9 +1368,30 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
 
     // ---- counters / flags --------------------------------------------------------
     // [0..2*nf): pool counters; then per feature a far flag; then the overflow flag
+    // ... followed by the cell histograms of the feature ops' vertex grids: ONE
+    // memset per attempt clears everything
+    const double ext_x = std::max(xmax - xmin, pix), ext_y = std::max(ymax - ymin, pix);
+    std::vector<VGrid> grids(d.nf);
+    std::vector<size_t> cnt_off(d.nf);
+    size_t n_counts = 0;
+    for (int f = 0; f < d.nf; ++f) {
+        // grid: ~1024-px cells, finer for dense vertex sets (<= ~512 per cell)
+        VGrid &G = grids[f];
+        double cell = kT2 * pix;
+        const double dense = sqrt(ext_x * ext_y * 512.0 / (double)d.feats[f].nv);
+        if (dense < cell) cell = std::max(dense, 16.0 * pix);
+        while ((ext_x / cell + 1) * (ext_y / cell + 1) > 1048576.0) cell *= 2.0;
+        G.cell = cell; G.inv = 1.0 / cell;
+        G.x0 = xmin; G.y0 = ymin;
+        G.ncx = (int)(ext_x / cell) + 1; G.ncy = (int)(ext_y / cell) + 1;
+        cnt_off[f] = n_counts;
+        n_counts += (size_t)(G.ncx + 2) * (G.ncy + 2);
+    }
     unsigned long long *ctrs = nullptr;
     const size_t nctr = 2 * kMaxFeat + 2;
-    OCSB_TRY(sg.get(&ctrs, nctr + 8));
+    const size_t zero_words = nctr + 8 + (n_counts + 1) / 2;
+    OCSB_TRY(sg.get(&ctrs, zero_words));
+    int *counts_all = reinterpret_cast<int *>(ctrs + nctr + 8);
     // {pool overflow, far vertex}: one 8-byte word the tile kernel reads at once
     int *overflow = reinterpret_cast<int *>(ctrs + nctr);
     int *far_flag = overflow + 1;
@@ -1382,8 +1418,6 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         }
     }
 
-    // ---- vertex grid geometry (shared by the feature ops) ------------------------------
-    const double ext_x = std::max(xmax - xmin, pix), ext_y = std::max(ymax - ymin, pix);
 
     // ---- persistent pipeline (k_pass2.cuh) for the common shape of a pass: at
     //      most one feature and one limiter op, fused clamps, TMA-able DEM
@@ -1398,10 +1432,8 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
 
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
-        OCSB_CUDA(cudaMemsetAsync(ctrs, 0, (nctr + 8) * sizeof(*ctrs), ctx->stream));
-        if (d.sticky)   // an earlier pass of the sequence failed: this one must not run
-            OCSB_CUDA(cudaMemcpyAsync(overflow, d.ext_overflow, sizeof(int),
-                                      cudaMemcpyDeviceToDevice, ctx->stream));
+        OCSB_CUDA(cudaMemsetAsync(ctrs, 0, zero_words * sizeof(*ctrs), ctx->stream));
+        int *sticky = d.sticky ? d.ext_overflow : nullptr;
         TileArgs T;
         memset(&T, 0, sizeof(T));
         double2 *slots0 = nullptr, *pool0 = nullptr;
@@ -1415,6 +1447,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         T.dem_rows = d.dem_rows; T.dem_cols = d.dem_cols;
         T.use_tma = use_tma;
         T.overflow = overflow;
+        T.sticky = sticky;
 
         for (int f = 0; f < d.nf; ++f) {
             const PassFeat &pf = d.feats[f];
@@ -1424,18 +1457,9 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             const bool bounded = pf.r < inf;
             const double r2 = bounded ? pf.r * pf.r : inf;
             const double r2lim = bounded ? (pf.r > 0 ? r2 * (1.0 + kDomEps) : -1.0) : inf;
-            // grid: ~1024-px cells, finer for dense vertex sets (<= ~512 per cell)
-            VGrid G;
-            double cell = kT2 * pix;
-            const double dense = sqrt(ext_x * ext_y * 512.0 / (double)nv);
-            if (dense < cell) cell = std::max(dense, 16.0 * pix);
-            while ((ext_x / cell + 1) * (ext_y / cell + 1) > 1048576.0) cell *= 2.0;
-            G.cell = cell; G.inv = 1.0 / cell;
-            G.x0 = xmin; G.y0 = ymin;
-            G.ncx = (int)(ext_x / cell) + 1; G.ncy = (int)(ext_y / cell) + 1;
+            VGrid G = grids[f];
             const int ncell = (G.ncx + 2) * (G.ncy + 2);
-            int *counts = nullptr, *cursor = nullptr;
-            OCSB_TRY(pools.get(&counts, (size_t)ncell));
+            int *counts = counts_all + cnt_off[f], *cursor = nullptr;
             OCSB_TRY(pools.get(&cursor, (size_t)ncell));
             OCSB_TRY(pools.get(&G.start, (size_t)ncell + 1));
             OCSB_TRY(pools.get(&G.sv, (size_t)nv));
@@ -1446,7 +1470,6 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 vg_build_small_kernel<<<1, 1024, 0, ctx->stream>>>(G, verts, nv, far_flag);
                 OCSB_LAUNCHED(ctx);
             } else {
-                OCSB_CUDA(cudaMemsetAsync(counts, 0, (size_t)ncell * sizeof(int), ctx->stream));
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 vg_hist_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, counts, far_flag);
                 OCSB_LAUNCHED(ctx);
@@ -1480,6 +1503,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             B.ctr2 = ctrs + 2 * f; B.ctr1 = ctrs + 2 * f + 1;
             B.cap2 = cap2; B.cap1 = cap1;
             B.overflow = overflow;
+            B.sticky = sticky;
             B.r = pf.r; B.r2lim = r2lim;
             OCSB_TIME(ctx, KC_FEATURE_REFINE);
             root_kernel<<<(unsigned)n2, kRootThreads, 0, ctx->stream>>>(B);
@@ -1507,6 +1531,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 L.slots = slots0; L.pool = pool0;
                 L.ctr = ctrs + 2 * kMaxFeat; L.cap = cap0;
                 L.overflow = overflow;
+                L.sticky = sticky;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 L.n_parents = (int)n1;
                 l0_kernel<<<(unsigned)n1, 256, 0, ctx->stream>>>(L);
@@ -1559,6 +1584,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             P.lo = T.lo; P.hi = T.hi;
             P.counter = reinterpret_cast<int *>(ctrs + nctr) + 4;
             P.overflow = overflow;
+            P.sticky = sticky;
             const bool band = d.nl && T.lim_band[0];
             OCSB_TRY(launch_pass2(ctx, tmap, P, d.in != nullptr, d.nf > 0, d.nl > 0, band));
         } else {
@@ -1589,9 +1615,11 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
 
         if (d.nf == 0) return OCSB_OK;
         if (async_mode) {
-            // the caller looks at its own flag later (and redoes the band)
-            OCSB_CUDA(cudaMemcpyAsync(d.ext_overflow, overflow, sizeof(int),
-                                      cudaMemcpyDeviceToDevice, ctx->stream));
+            // the caller looks at its own flag later (and redoes the band); a
+            // sticky status word was written by the kernels themselves
+            if (!d.sticky)
+                OCSB_CUDA(cudaMemcpyAsync(d.ext_overflow, overflow, sizeof(int),
+                                          cudaMemcpyDeviceToDevice, ctx->stream));
             return OCSB_OK;
         }
         int *flag_h = reinterpret_cast<int *>(ctx->pinned);

@@ -58,6 +58,7 @@ struct P2Args {
     int *counter;           // zeroed before the launch
     int chunk;              // tiles per fetch of the counter
     const int *overflow;
+    const int *sticky;      // status word of a pass sequence (or nullptr)
 };
 
 struct W2Scr {
@@ -366,7 +367,7 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
     P2Smem &S = *reinterpret_cast<P2Smem *>(p2_raw);
 
     const int2 flags = *reinterpret_cast<const int2 *>(A.overflow);   // {overflow, far}
-    if (flags.x) return;
+    if (flags.x || (A.sticky && *A.sticky)) return;
     const bool far = flags.y != 0;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int lcol = (wid & 1) * 32 + (lane & 7) * 4;      // tile-local
@@ -502,6 +503,7 @@ struct L0Args {
     unsigned long long *ctr;
     unsigned long long cap;
     int *overflow;
+    int *sticky;
 };
 
 constexpr int kL0Stage = 1024;       // parent candidates staged in shared memory
@@ -575,7 +577,7 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
             unsigned long long base = 0;
             if (lane == 0) {
                 base = atomicAdd(A.ctr, (unsigned long long)total);
-                if (base + total > A.cap) { *A.overflow = 1; base = ~0ull; }
+                if (base + total > A.cap) { flag_overflow(A.overflow, A.sticky); base = ~0ull; }
             }
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base == ~0ull) continue;

@@ -1123,7 +1123,8 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
             size_t bytes = 0;
             int32_t g1 = g0;
             while (g1 < n_rasters && g1 - g0 < max_group) {
-                const size_t need = (size_t)rasters[g1].win.width *
+                const size_t need = rasters[g1].spline_coef ? 0 :
+                                    (size_t)rasters[g1].win.width *
                                     rasters[g1].win.height * sizeof(double);
                 if (g1 > g0 && bytes + need > budget) break;
                 bytes += need;
@@ -1137,12 +1138,20 @@ extern "C" int32_t ocsb_interp_multi(ocsb_ctx *ctx,
                     const ocsb_interp_raster &r = rasters[i];
                     const int w = r.win.width, h = r.win.height;
                     const size_t es = r.dem_dtype == OCSB_F32 ? 4 : 8;
+                    SplineEvalRaster &e = rs[i - g0];
+                    win_axes(&r.win, &e.ax, &e.ay);
+                    if (r.spline_coef) {
+                        // the caller kept this window's coefficients
+                        OCSB_REQUIRE(ocsb_is_device_ptr(r.spline_coef),
+                                     "ocsb_interp_multi: spline_coef of raster %d "
+                                     "must be device memory", i);
+                        e.coef = const_cast<double *>(r.spline_coef);
+                        continue;
+                    }
                     Staged &z = sz[i - g0];
                     OCSB_TRY(z.init(ctx, r.dem, h, w, r.dem_stride, es, STAGE_IN));
                     double *coef = nullptr;
                     OCSB_TRY(sg.get(&coef, (size_t)w * h));
-                    SplineEvalRaster &e = rs[i - g0];
-                    win_axes(&r.win, &e.ax, &e.ay);
                     OCSB_TRY(k_spline_prefilter(ctx, e.ax, e.ay, z.dev, r.dem_dtype,
                                                 z.dev_stride, coef));
                     e.coef = coef;

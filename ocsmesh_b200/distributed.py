@@ -236,11 +236,12 @@ class BandExchange:
         (padded) vertex array and fills the halo slots of ``buf`` (raster rows
         ``[origin, origin + len(buf))``: band + halo slots)."""
         import torch.distributed as dist
-        if self.world == 1:
-            return self.gather_vertices(verts_local)
         n = int(verts_local.shape[0])
         if n != self.sizes[self.rank]:
             raise ValueError("vertex count differs from the exchanged size")
+        if self.world == 1:
+            # nothing to exchange: the local vertices are the whole set
+            return verts_local if n else self.gather_vertices(verts_local)
         sv = self._send_verts
         if n:
             sv[:n].copy_(verts_local)

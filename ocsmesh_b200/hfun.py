@@ -149,9 +149,14 @@ class HfunRaster:
         self._host_vals = None
         if self._pending:
             # whatever the enqueued passes did is discarded with the raster: a
-            # failure among them must not block the passes that follow
+            # failure among them must not block the passes that follow, so the
+            # next sequence gets a fresh status word (a ring of 64, cleared
+            # with one fill per turn instead of one per reset)
             self._pending = []
-            self._status.zero_()
+            self._status_i = (self._status_i + 1) % self._status_ring.shape[0]
+            if self._status_i == 0:
+                self._status_ring.zero_()
+            self._status = self._status_ring[self._status_i]
 
     def _verify(self) -> None:
         """Synchronisation point of the asynchronous passes: look at the status
@@ -277,8 +282,10 @@ class HfunRaster:
             import torch
             self._queue = []
             if self._status is None:
-                self._status = torch.zeros(2, dtype=torch.int32,
-                                           device=f"cuda:{self._device}")
+                self._status_ring = torch.zeros((64, 2), dtype=torch.int32,
+                                                device=f"cuda:{self._device}")
+                self._status_i = 0
+                self._status = self._status_ring[0]
             buf = self._hfun
             self._tiled_pass(ops, None if self._pristine else buf, buf,
                              status=self._status)

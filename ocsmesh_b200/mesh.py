@@ -221,9 +221,23 @@ class EuclideanMesh2D:
                 cw = _lib.make_win(r.get_window_bounds(win), win.width, win.height)
                 poff = (win.row_off - r.device_band_origin(band, dev)) * r.width \
                     + win.col_off
+                coef = None
+                if method == "spline":
+                    # not-a-knot B-spline coefficients of the window: computed
+                    # once per raster window and device (16 B/px, the bulk of a
+                    # spline call), kept with the raster's device band
+                    key = ("spline_coef", band, dev, win.col_off, win.row_off,
+                           win.width, win.height)
+                    coef = r._dev_cache.get(key)
+                    if coef is None:
+                        coef = torch.empty(win.width * win.height, dtype=torch.float64,
+                                           device=f"cuda:{dev}")
+                        ctx.spline_prefilter(cw, dem.data_ptr() + poff * es, dcode,
+                                             r.width, coef)
+                        r._dev_cache[key] = coef
                 entries.append((cw, dem.data_ptr() + poff * es, dcode, r.width,
                                 None if mask is None else mask.data_ptr() + poff,
-                                r.width))
+                                r.width, coef))
         # one launch for the whole list (linear / nearest): every node walks the
         # entries from last to first and stops at its first valid hit
         ctx.interp_multi(entries, xy, K, code, touched, vals, perm=perm)

@@ -141,3 +141,33 @@ def test_bucketed_nodes_give_identical_results(ctx):
     xh = np.zeros((1000, 2))
     ctx.bucket_nodes(xy[:1000].copy(), 1000, bbox, 640.0, ph, xh)
     np.testing.assert_array_equal(np.sort(ph), np.arange(1000))
+
+
+def test_spline_coefficients_are_kept_with_the_raster(ctx):
+    """Mesh.interpolate(method='spline') twice from the same rasters: the second
+    call reuses the window coefficients computed by the first (ocsb_interp_raster
+    .spline_coef) and gives the same values; dropping the device cache and
+    interpolating again reproduces them too."""
+    import ocsmesh_b200 as ob
+    from ocsmesh_b200 import synthetic as S
+    rasters = []
+    for k in range(2):
+        z = S.synth_dem(90, 110, seed=40 + k)
+        tr = list(S.dem_transform(90))
+        tr[2] += 600.0 * k
+        rasters.append(ob.Raster.from_numpy(z, tr, crs=32618))
+    bbox = (S.X0, S.Y0, S.X0 + 1700.0, S.Y0 + 900.0)
+    xy = S.synth_nodes(5000, bbox, seed=9, outside_frac=0.05)
+    out = []
+    for rep in range(3):
+        if rep == 2:
+            for r in rasters:
+                r.drop_device_cache()
+        mesh = ob.Mesh(ob.MeshData(xy, values=np.full(len(xy), np.nan)))
+        mesh.interpolate(rasters, method="spline")
+        out.append(mesh.value.copy())
+        keys = [k for k in rasters[0]._dev_cache if isinstance(k, tuple) and k[0] == "spline_coef"]
+        assert len(keys) == 1
+    np.testing.assert_array_equal(out[0], out[1])
+    np.testing.assert_array_equal(out[0], out[2])
+    assert np.isfinite(out[0]).sum() > 2000

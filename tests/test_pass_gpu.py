@@ -200,3 +200,104 @@ def test_resident_pass_overlap_equals_eager(ops_order, pristine, monkeypatch):
     got = build(True)
     monkeypatch.setenv("OCSB_PASS_OVERLAP", "0")
     np.testing.assert_array_equal(got, build(False))
+
+
+def _windows_case(ctx, h, w, chunk, seed, ops_of, n_reps=1):
+    """ocsb_hfun_pass_windows over the window list of a chunked raster vs the
+    same op list applied window by window through ocsb_hfun_pass."""
+    import torch
+    z, r, pts, pts2 = make_inputs(h, w, seed)
+    wins_py = list(ob.get_iter_windows(w, h, chunk, 0))
+    bounds = lambda wn: O.OracleRaster(z, S.dem_transform(h)).get_window_bounds(wn)
+    zd = torch.from_numpy(z).cuda()
+    ptd, pt2d = torch.from_numpy(pts).cuda(), torch.from_numpy(pts2).cuda()
+    ops_dev = ops_of(ptd, pt2d)
+    ops_host = ops_of(pts, pts2)
+    cws = [_lib.make_win(bounds(wn), wn.width, wn.height) for wn in wins_py]
+    arr = (_lib.ocsb_win * len(cws))(*cws)
+    off = np.array([wn.row_off * w + wn.col_off for wn in wins_py], dtype=np.int64)
+    # reference: one synchronous single-window pass per window (host buffers)
+    ref = np.full((h, w), -1.0, np.float32)
+    for wn, cw in zip(wins_py, cws):
+        sub = ref[wn.row_off:, wn.col_off:]
+        ctx.hfun_pass(cw, z[wn.row_off:, wn.col_off:], _lib.OCSB_F32, w, None, w, sub, w,
+                      10.0, 10.0, 100.0, 1500.0, ops_host)
+    return z, zd, arr, off, ops_dev, ref
+
+
+@pytest.mark.parametrize("chunk", [64, 150, 257])
+def test_pass_windows_equals_per_window_passes(ctx, chunk):
+    import torch
+    h, w = 300, 517
+    mk = lambda a, b: [("feature", a, len(a), 0.001, 100.0, True),
+                       ("limiter", 50.0, 1500.0, -30.0, 0.0, True)]
+    z, zd, arr, off, ops, ref = _windows_case(ctx, h, w, chunk, 5, mk)
+    out = torch.full((h, w), -1.0, dtype=torch.float32, device="cuda")
+    ctx.hfun_pass_windows(arr, off, off, zd, _lib.OCSB_F32, w, h, w, None, w, out, w,
+                          10.0, 10.0, 100.0, 1500.0, ops)
+    np.testing.assert_array_equal(out.cpu().numpy(), ref)
+    # the op list the tiled sweep does not take (two limiters with different
+    # clamp fusing) runs window by window inside the same call
+    mk2 = lambda a, b: [("feature", a, len(a), 0.001, 100.0, True),
+                        ("limiter", 50.0, 1500.0, -30.0, 0.0, False)]
+    z, zd, arr, off, ops, ref = _windows_case(ctx, h, w, chunk, 5, mk2)
+    out.fill_(-1.0)
+    ctx.hfun_pass_windows(arr, off, off, zd, _lib.OCSB_F32, w, h, w, None, w, out, w,
+                          10.0, 10.0, 100.0, 1500.0, ops)
+    np.testing.assert_array_equal(out.cpu().numpy(), ref)
+
+
+def test_pass_windows_async_status_is_sticky(ctx):
+    """Asynchronous mode: with the status word clear the pass runs and leaves it
+    clear; with the status word set (an earlier pass of the sequence failed) the
+    pass must not touch the raster, and the word stays set."""
+    import torch
+    h, w = 200, 260
+    mk = lambda a, b: [("feature", a, len(a), 0.001, 100.0, True),
+                       ("limiter", 50.0, 1500.0, None, None, True)]
+    z, zd, arr, off, ops, ref = _windows_case(ctx, h, w, 128, 7, mk)
+    status = torch.zeros(2, dtype=torch.int32, device="cuda")
+    out = torch.full((h, w), -1.0, dtype=torch.float32, device="cuda")
+    ctx.hfun_pass_windows(arr, off, off, zd, _lib.OCSB_F32, w, h, w, None, w, out, w,
+                          10.0, 10.0, 100.0, 1500.0, ops, status=status)
+    torch.cuda.synchronize()
+    assert status.tolist() == [0, 0]
+    np.testing.assert_array_equal(out.cpu().numpy(), ref)
+    status[0] = 1
+    out.fill_(-2.0)
+    for these in (ops, ops[1:]):            # with and without a feature op
+        ctx.hfun_pass_windows(arr, off, off, zd, _lib.OCSB_F32, w, h, w, None, w, out, w,
+                              10.0, 10.0, 100.0, 1500.0, these, status=status)
+        torch.cuda.synchronize()
+        assert int(status[0]) == 1
+        assert bool((out == -2.0).all())
+
+
+def test_deferred_hfun_async_flush_and_verify(ctx):
+    """HfunRaster(deferred=True) on a resident DEM: flush() only enqueues; the
+    values are final at get_values(); a set status word (simulated pool
+    overflow) makes _verify() redo the sequence synchronously."""
+    h, w = 240, 300
+    z = S.synth_dem(h, w, seed=4)
+    tr = S.dem_transform(h)
+    r = ob.Raster.from_numpy(z, tr, crs=32618)
+    r.device_band(1, 0)
+    lines = S.synth_shoreline(h, w, seed=4, n_lines=2)
+    pts = F.feature_points(lines, 100.0)
+    eager = ob.HfunRaster(r, hmin=100.0, hmax=1500.0)
+    eager.add_feature_points(pts, 0.001, 100.0)
+    eager.add_subtidal_flow_limiter(50.0, 1500.0, -30.0, 0.0)
+    want = eager.get_values()
+    hf = ob.HfunRaster(r, hmin=100.0, hmax=1500.0, deferred=True)
+    for fail in (False, True):
+        hf.reset()
+        hf.add_feature_points(pts, 0.001, 100.0)
+        hf.add_subtidal_flow_limiter(50.0, 1500.0, -30.0, 0.0)
+        hf.flush()
+        assert len(hf._pending) == 1
+        if fail:
+            # as if a pool had overflowed: the device raster is then stale
+            hf._status[0] = 1
+            hf._hfun.fill_(-3.0)
+        np.testing.assert_array_equal(hf.get_values(), want)
+        assert not hf._pending and int(hf._status[0]) == 0
