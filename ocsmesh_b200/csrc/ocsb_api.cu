@@ -528,6 +528,33 @@ extern "C" int32_t ocsb_hfun_feature(
     OCSB_TRY(si.init(ctx, idx_out, h, w, w, 8, STAGE_OUT, rb));
     const float *oldp = alias ? (const float *)sn.dev : (const float *)so.dev;
     int64_t olds = alias ? sn.dev_stride : so.dev_stride;
+    if (!dist_out && !idx_out) {
+        // sizes only: the tiled sweep (vertex-grid pyramid + persistent pass
+        // kernel, k_pass.cu) -- same arithmetic, bit-identical
+        static const bool tiled_on = [] {
+            const char *e = getenv("OCSB_PASS_TILED");
+            return !(e && atoi(e) == 0);
+        }();
+        PassWin pw;
+        pw.ax = a.ax; pw.ay = a.ay;
+        pw.rb = rb; pw.re = re;
+        pw.keep_w = w; pw.keep_h = win->height;
+        pw.hoff = 0; pw.dem_c = 0; pw.dem_r = 0;
+        PassFeat pf;
+        pf.verts = (const double *)sv.dev; pf.nv = nv;
+        pf.rate_target = a.rate_target; pf.target = a.target; pf.r = a.r;
+        pf.fuse_clamp = fuse_clamp;
+        PassDesc d;
+        d.wins = &pw; d.n_wins = 1;
+        d.in = oldp; d.in_stride = olds;
+        d.out = (float *)sn.dev; d.out_stride = sn.dev_stride;
+        d.ghmin = hmin; d.ghmax = hmax;
+        d.feats = &pf; d.nf = 1;
+        if (tiled_on && k_pass_supported(d)) {
+            OCSB_TRY(k_pass_tiled(ctx, d));
+            return finish_call(ctx, {&sv, &so, &sn, &sd, &si});
+        }
+    }
     OCSB_TRY(k_hfun_feature(ctx, a, (const double *)sv.dev, nv, oldp, olds,
                             (float *)sn.dev, sn.dev_stride, (double *)sd.dev,
                             (int64_t *)si.dev));

@@ -190,3 +190,44 @@ def test_config1_whole_case_every_pixel_and_node(ctx):
         assert res[f"interp_{m}_same_untouched_set"]
     assert res["interp_spline_same_untouched_set"]
     assert res["interp_spline_max_rel_err"] <= 1e-9
+
+
+def test_config5_dense_vertex_set_sampled(ctx):
+    """BASELINE.json configs[4]: add_feature distance sizing against a 5 M-vertex
+    synthetic shoreline set (2000 random-walk polylines x 2500 points, 40 m
+    steps, fed at the parity boundary hfun/raster.py:1230) on a 40000 x 40000
+    raster (20000 x 20000 when less than 12 GB of device memory is free): 20000
+    sampled pixels bit-exact against an exact cKDTree query + the size law of
+    hfun/raster.py:1240-1257; the vertex-set stress case of the candidate
+    pyramid (vertex grid -> 1024 -> 256 -> 64 px lists)."""
+    import torch
+    from scipy.spatial import cKDTree
+    free, _ = torch.cuda.mem_get_info()
+    n = 40000 if free > 12e9 else 20000
+    if free < 4e9:
+        pytest.skip("needs 4 GB of free device memory")
+    tr = S.dem_transform(n)
+    x0, y1 = tr[2], tr[5]
+    x1, y0 = x0 + tr[0] * n, y1 + tr[4] * n
+    pts = S.synth_random_walk_features(2000, 2500, 40.0, (x0, y0, x1, y1), seed=5)
+    assert len(pts) > 4_000_000
+    vd = torch.from_numpy(pts).cuda()
+    out = torch.empty((n, n), dtype=torch.float32, device="cuda")
+    win = _lib.make_win((x0, y0, x1, y1), n, n)
+    ctx.hfun_feature(win, vd, len(pts), None, n, out, n, RATE, TARGET, HMIN, HMAX, True)
+    rng = np.random.default_rng(0)
+    rows, cols = rng.integers(0, n, 20000), rng.integers(0, n, 20000)
+    x = np.linspace(x0, x1, n)
+    y = np.linspace(y1, y0, n)
+    xy = np.stack([x[cols], y[rows]], axis=1)
+    r = (HMAX - TARGET) / (RATE * TARGET)
+    d, _ = cKDTree(pts).query(xy, distance_upper_bound=r, workers=-1)
+    d = np.where(np.isinf(d), r, d)
+    v = (RATE * TARGET * d + TARGET).astype(np.float32)
+    v[v < HMIN] = HMIN
+    v[v > HMAX] = HMAX
+    got = out[rows, cols].cpu().numpy()
+    np.testing.assert_array_equal(got, v)
+    assert float((d < r).mean()) > 0.2          # the set reaches a good part of it
+    del out
+    torch.cuda.empty_cache()
