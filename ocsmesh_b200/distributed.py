@@ -82,6 +82,8 @@ def band_raster(band_values: np.ndarray, transform, full_height: int,
         src = torch.from_numpy(np.ascontiguousarray(band_values))
         buf[r0 - s0:r1 - s0].copy_(src, non_blocking=True)
         r.set_device_band(buf, s0, band=1, device=device)
+        # halo slots are zeros until the first exchange (get_contour refuses)
+        r._halo_pending[(1, int(device))] = (s1 - s0) != (r1 - r0)
     return r
 
 
@@ -115,6 +117,8 @@ def exchange_dem_halo(raster, part: RowBands, rank: int, device: Optional[int] =
         device = torch.cuda.current_device()
     exchange_halo_rows(raster.device_band(band, device),
                        raster.device_band_origin(band, device), part, rank, group)
+    if hasattr(raster, "_halo_pending"):
+        raster._halo_pending[(int(band), int(device))] = False
 
 
 def gather_sizes(n_local: int, device, group=None) -> List[int]:
@@ -231,11 +235,15 @@ class BandExchange:
         dist.all_gather_into_tensor(self.verts, self.block, group=self.group)
         return self.verts
 
-    def exchange(self, verts_local, buf, origin: int):
+    def exchange(self, verts_local, buf, origin: int, raster=None):
         """Both exchanges of a step in ONE collective: returns the gathered
         (padded) vertex array and fills the halo slots of ``buf`` (raster rows
-        ``[origin, origin + len(buf))``: band + halo slots)."""
+        ``[origin, origin + len(buf))``: band + halo slots).  ``raster``: the
+        band raster ``buf`` belongs to (its halo rows are then known valid)."""
         import torch.distributed as dist
+        if raster is not None and hasattr(raster, "_halo_pending"):
+            for k in raster._halo_pending:
+                raster._halo_pending[k] = False
         n = int(verts_local.shape[0])
         if n != self.sizes[self.rank]:
             raise ValueError("vertex count differs from the exchanged size")

@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import logging
 import os
+import warnings
 import pathlib
 from contextlib import contextmanager
 from typing import List, Optional, Sequence, Union
@@ -841,6 +842,18 @@ class HfunRaster:
         self._check_projected()
         hmin = float(hmin) if hmin is not None else hmin
         hmax = float(hmax) if hmax is not None else hmax
+        lo = max(v for v in (hmin, self._hmin, 0.0) if v is not None)
+        if lo <= 1.0 / 3.0:
+            # |grad z| == 0 pixels (flat water, filled plateaus): the reference
+            # leaves them MASKED (what lands in the file depends on rasterio's
+            # fill); here the data under the mask, 1/3, goes
+            # through the clamps -- harmless when a bound above 1/3 exists
+            # (the pixel then gets that bound), a 0.33 m target size otherwise
+            warnings.warn(
+                "add_subtidal_flow_limiter without a local or global hmin above "
+                "1/3: pixels with a zero elevation gradient get the size 1/3 "
+                "(the reference leaves them masked); set hmin", RuntimeWarning,
+                stacklevel=2)
         if self._can_defer():
             if self.width < 2 or self.height < 2:
                 raise ValueError(

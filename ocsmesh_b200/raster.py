@@ -462,6 +462,14 @@ class Raster:
         dev = ctx.device
         dem = self.device_band(1, dev)
         origin = self.device_band_origin(1, dev)
+        if getattr(self, "_halo_pending", {}).get((1, dev)):
+            # a band raster of a multi-rank run (distributed.band_raster) whose
+            # halo rows have not been exchanged yet: tracing now would run the
+            # level against rows of zeros along the band edges
+            raise RuntimeError(
+                "the DEM band's halo rows have not been exchanged yet: call "
+                "distributed.exchange_dem_halo (or BandExchange.exchange) before "
+                "tracing contours on a band raster")
         code = _lib.OCSB_F32 if dem.element_size() == 4 else _lib.OCSB_F64
         w = self.width
         rows = dem.shape[0]
@@ -522,6 +530,9 @@ class Raster:
             device = tensor.device.index
         key = (int(band), int(device))
         self._dev_cache[key] = tensor
+        if not hasattr(self, "_halo_pending"):
+            self._halo_pending = {}
+        self._halo_pending[key] = False
         self._dev_origin[key] = int(row_origin)
 
     def device_mask(self, band: int = 1, device=None):

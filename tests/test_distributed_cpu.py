@@ -312,3 +312,22 @@ def test_band_exchange_persistent_buffers(world):
         np.testing.assert_array_equal(real, expect)
         assert same_d
         assert sizes == [len(r[1]) for r in res]
+
+
+def test_band_raster_refuses_contours_before_the_halo_exchange(monkeypatch):
+    """get_contour on a band raster whose halo slots are still zeros
+    would trace the level along the band edges; the raster knows its halo state
+    (set by band_raster, cleared by exchange_dem_halo / BandExchange.exchange)."""
+    from ocsmesh_b200.raster import Raster
+    r = Raster.from_numpy(S.synth_dem(8, 9, seed=1), S.dem_transform(20), crs=32618,
+                          row_origin=4, full_height=20)
+    r._halo_pending = {(1, 0): True}
+    r._dev_cache[(1, 0)] = torch.zeros((10, 9))
+    r._dev_origin = {(1, 0): 3}
+
+    class Ctx:
+        device = 0
+    import ocsmesh_b200._lib as L
+    monkeypatch.setattr(L, "default_context", lambda d=None: Ctx())
+    with pytest.raises(RuntimeError, match="halo rows have not been exchanged"):
+        r.get_contour(0.0)
