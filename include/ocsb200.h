@@ -348,6 +348,38 @@ int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
                               int64_t dem_stride, double level, int64_t cap,
                               int64_t *edges, double *pts, int64_t *n);
 
+/* ---- 8(f) next-1 on the device: polylines and the feature prologue ---------
+ * Raster.get_contour (ocsmesh/raster.py:1340-1372, 1426-1470: contourpy +
+ * shapely linemerge) and the resampling prologue of add_feature
+ * (utils.repartition_features / transform_linestring, ocsmesh/utils.py:247-312,
+ * called at ocsmesh/hfun/raster.py:1219-1225) without leaving the device: the
+ * segments of ocsb_contour_segments are joined by list ranking (pointer
+ * jumping over half-edges) into the SAME polylines, vertex for vertex, as
+ * ocsb_stitch_segments gives on the host, and resampled chunk by chunk into the
+ * SAME vertex array as ocsb_feature_points (running sums in np.cumsum order).
+ * The tracing rules themselves (cell-mean saddles, "on the level is not
+ * above") restate contourpy's documented behaviour; contourpy / shapely are not
+ * importable here, so polyline parity with the reference is UNPINNED.
+ *   dem : device memory.  win->row_begin/row_end: the cell rows of a device band.
+ * Results stay on the device until taken:
+ *   ocsb_contour_lines  -> slot 0: n_xy x 2 float64 vertices, slot 1:
+ *                          n_lines + 1 int64 offsets (open lines by start edge
+ *                          id first, then rings; a ring repeats its first vertex)
+ *   ocsb_contour_points -> slot 0: n_points x 2 float64 = the array handed to
+ *                          the nearest-vertex search (hfun/raster.py:1230), all
+ *                          levels in order
+ *   ocsb_take_result(slot, dst, dst_bytes): copy the kept array to dst (host
+ *                          or device memory) and release it.                   */
+int32_t ocsb_contour_lines(ocsb_ctx *ctx, const ocsb_win *win,
+                           const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                           double level, int64_t *n_xy, int64_t *n_lines);
+int32_t ocsb_contour_points(ocsb_ctx *ctx, const ocsb_win *win,
+                            const void *dem, int32_t dem_dtype, int64_t dem_stride,
+                            const double *levels, int32_t n_levels,
+                            double target_size, int32_t max_verts,
+                            int64_t *n_points);
+int32_t ocsb_take_result(ocsb_ctx *ctx, int32_t slot, void *dst, int64_t dst_bytes);
+
 /* ---- 8(f) next-3: sampling side of HfunRaster.msh_t ---------------------------
  * source points of the background size mesh                 ocsmesh/hfun/raster.py:345-377
  *   coords = get_xy(window)[::stride, ::stride]  (row-major, (ny*nx, 2) float64)

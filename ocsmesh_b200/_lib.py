@@ -117,6 +117,11 @@ SIGNATURES = {
     "ocsb_contour_segments": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_f64, c_i64, c_vp, c_vp,
                                       C.POINTER(c_i64)]),
+    "ocsb_contour_lines": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
+                                   c_f64, C.POINTER(c_i64), C.POINTER(c_i64)]),
+    "ocsb_contour_points": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
+                                    c_vp, c_i32, c_f64, c_i32, C.POINTER(c_i64)]),
+    "ocsb_take_result": (c_i32, [c_vp, c_i32, c_vp, c_i64]),
     "ocsb_hfun_sample_source": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
                                         c_i32, c_f64, c_f64, c_vp, c_vp]),
     "ocsb_hfun_sample_nearest": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
@@ -460,6 +465,36 @@ class Context:
             check(rc)
             break
         return edges[:n.value], pts[:n.value]
+
+    def contour_lines(self, win, dem, dem_dtype, dem_stride, level):
+        """Polylines of one level, traced, stitched and ordered on the device
+        -> (xy (n, 2) float64, offsets (n_lines + 1,) int64) host arrays."""
+        n_xy, n_lines = c_i64(0), c_i64(0)
+        check(self.lib.ocsb_contour_lines(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            float(level), C.byref(n_xy), C.byref(n_lines)))
+        xy = np.empty((n_xy.value, 2), dtype=np.float64)
+        off = np.zeros(n_lines.value + 1 if n_lines.value else 0, dtype=np.int64)
+        check(self.lib.ocsb_take_result(self.handle, 0, xy.ctypes.data, xy.nbytes))
+        check(self.lib.ocsb_take_result(self.handle, 1, off.ctypes.data, off.nbytes))
+        return xy, off
+
+    def contour_points(self, win, dem, dem_dtype, dem_stride, levels, target_size,
+                       max_verts=200, device=None):
+        """The resampled contour vertices of ``levels`` (the array of
+        hfun/raster.py:1230) as an (N, 2) float64 CUDA tensor: trace, stitch
+        and resample all run on the device."""
+        import torch
+        lv = np.ascontiguousarray(np.asarray(levels, dtype=np.float64).ravel())
+        n = c_i64(0)
+        check(self.lib.ocsb_contour_points(
+            self.handle, C.byref(win), ptr(dem), int(dem_dtype), int(dem_stride),
+            lv.ctypes.data, len(lv), float(target_size), int(max_verts), C.byref(n)))
+        dev = self.device if device is None else device
+        out = torch.empty((n.value, 2), dtype=torch.float64, device=f"cuda:{dev}")
+        check(self.lib.ocsb_take_result(self.handle, 0, ptr(out) if n.value else None,
+                                        out.numel() * 8))
+        return out
 
     def hfun_sample_source(self, win, hfun, hfun_stride, stride, hmin, hmax,
                            coords_out, values_out):

@@ -173,6 +173,8 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->spl_coef) cudaFree(ctx->spl_coef);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto &k : ctx->kept)
+        if (k) cudaFree(k);
     for (auto &sl : ctx->stage_ring) {
         if (sl.host) cudaFreeHost(sl.host);
         if (sl.ev) cudaEventDestroy(sl.ev);
@@ -952,6 +954,138 @@ extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
     se.width = *n * 2;
     sp.width = *n * 4;
     return finish_call(ctx, {&sz, &se, &sp});
+}
+
+// ---------------------------------------------------------------------------
+// next-1, device side: polylines and the resampled vertex array
+// ---------------------------------------------------------------------------
+namespace {
+
+int32_t keep_result(ocsb_ctx *ctx, int slot, const void *dev, size_t bytes) {
+    if (ctx->kept[slot]) { cudaFree(ctx->kept[slot]); ctx->kept[slot] = nullptr; }
+    ctx->kept_bytes[slot] = bytes;
+    if (bytes == 0) return OCSB_OK;
+    OCSB_CUDA(cudaMalloc(&ctx->kept[slot], bytes));
+    OCSB_CUDA(cudaMemcpyAsync(ctx->kept[slot], dev, bytes, cudaMemcpyDeviceToDevice,
+                              ctx->stream));
+    return OCSB_OK;
+}
+
+// segments of one level on the device (carved from sg): one count + emit call
+// when the capacity guess holds, a second call with the exact size otherwise
+int32_t level_segments(ocsb_ctx *ctx, ScratchGuard &sg, const ocsb_win *win, const void *dem,
+                       int dem_dtype, int64_t dem_stride, double level, int64_t **edges,
+                       double **pts, int64_t *n) {
+    const int w = win->width, h = win->height;
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_contour", &rb, &re));
+    *n = 0; *edges = nullptr; *pts = nullptr;
+    const int je = re < h - 1 ? re : h - 1;   // cell rows [rb, je)
+    if (w < 2 || je <= rb) return OCSB_OK;
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    int64_t cap = 64ll * (w + (je - rb)) + 4096;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        OCSB_TRY(sg.get(edges, (size_t)cap * 2));
+        OCSB_TRY(sg.get(pts, (size_t)cap * 4));
+        const int32_t rc = k_contour_segments(ctx, dem, dem_dtype, dem_stride, w, rb, je, level,
+                                              ax, ay, cap, *edges, *pts, n);
+        if (rc == OCSB_EOVERFLOW && *n > cap && attempt == 0) { cap = *n; continue; }
+        return rc;
+    }
+    return OCSB_OK;
+}
+
+int32_t check_contour_args(const ocsb_win *win, const void *dem, int32_t dem_dtype,
+                           int64_t dem_stride, const char *who) {
+    OCSB_TRY(check_win(win, who));
+    OCSB_REQUIRE(dem_dtype == OCSB_F32 || dem_dtype == OCSB_F64,
+                 "%s: unsupported DEM dtype %d", who, dem_dtype);
+    OCSB_REQUIRE(dem && dem_stride >= win->width, "%s: bad buffers", who);
+    OCSB_REQUIRE(ocsb_is_device_ptr(dem), "%s: the DEM must be device memory", who);
+    return OCSB_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t ocsb_contour_lines(ocsb_ctx *ctx, const ocsb_win *win, const void *dem,
+                                      int32_t dem_dtype, int64_t dem_stride, double level,
+                                      int64_t *n_xy, int64_t *n_lines) {
+    CTX_ENTER("ocsb_contour_lines");
+    OCSB_TRY(check_contour_args(win, dem, dem_dtype, dem_stride, "ocsb_contour_lines"));
+    OCSB_REQUIRE(n_xy && n_lines && !ocsb_is_none(level), "ocsb_contour_lines: bad arguments");
+    ScratchGuard sg(ctx);
+    int64_t *edges = nullptr, n = 0, *off = nullptr;
+    double *pts = nullptr, *xy = nullptr;
+    OCSB_TRY(level_segments(ctx, sg, win, dem, dem_dtype, dem_stride, level, &edges, &pts, &n));
+    OCSB_TRY(k_stitch_segments(ctx, sg, edges, pts, n, &xy, &off, n_xy, n_lines));
+    OCSB_TRY(keep_result(ctx, 0, xy, (size_t)*n_xy * 16));
+    OCSB_TRY(keep_result(ctx, 1, off, *n_lines ? (size_t)(*n_lines + 1) * 8 : 0));
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_contour_points(ocsb_ctx *ctx, const ocsb_win *win, const void *dem,
+                                       int32_t dem_dtype, int64_t dem_stride,
+                                       const double *levels, int32_t n_levels,
+                                       double target_size, int32_t max_verts,
+                                       int64_t *n_points) {
+    CTX_ENTER("ocsb_contour_points");
+    OCSB_TRY(check_contour_args(win, dem, dem_dtype, dem_stride, "ocsb_contour_points"));
+    OCSB_REQUIRE(levels && n_levels > 0 && n_points, "ocsb_contour_points: bad arguments");
+    OCSB_REQUIRE(target_size > 0 && target_size == target_size,
+                 "Argument target_size must be greater than zero.");
+    OCSB_REQUIRE(max_verts >= 2, "ocsb_contour_points: max_verts must be >= 2");
+    ScratchGuard sg(ctx);
+    std::vector<double *> parts;
+    std::vector<int64_t> counts;
+    int64_t total = 0;
+    for (int l = 0; l < n_levels; ++l) {
+        OCSB_REQUIRE(!ocsb_is_none(levels[l]), "ocsb_contour_points: level is NaN");
+        int64_t *edges = nullptr, n = 0, *off = nullptr, n_xy = 0, n_lines = 0, np = 0;
+        double *pts = nullptr, *xy = nullptr, *rs = nullptr;
+        OCSB_TRY(level_segments(ctx, sg, win, dem, dem_dtype, dem_stride, levels[l], &edges,
+                                &pts, &n));
+        OCSB_TRY(k_stitch_segments(ctx, sg, edges, pts, n, &xy, &off, &n_xy, &n_lines));
+        OCSB_TRY(k_resample_lines(ctx, sg, xy, off, n_lines, target_size, max_verts, &rs, &np));
+        parts.push_back(rs);
+        counts.push_back(np);
+        total += np;
+    }
+    *n_points = total;
+    if (ctx->kept[0]) { cudaFree(ctx->kept[0]); ctx->kept[0] = nullptr; }
+    ctx->kept_bytes[0] = (size_t)total * 16;
+    if (total) {
+        OCSB_CUDA(cudaMalloc(&ctx->kept[0], (size_t)total * 16));
+        size_t at = 0;
+        for (size_t i = 0; i < parts.size(); ++i) {
+            if (counts[i])
+                OCSB_CUDA(cudaMemcpyAsync((char *)ctx->kept[0] + at, parts[i],
+                                          (size_t)counts[i] * 16, cudaMemcpyDeviceToDevice,
+                                          ctx->stream));
+            at += (size_t)counts[i] * 16;
+        }
+    }
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OCSB_OK;
+}
+
+extern "C" int32_t ocsb_take_result(ocsb_ctx *ctx, int32_t slot, void *dst, int64_t dst_bytes) {
+    CTX_ENTER("ocsb_take_result");
+    OCSB_REQUIRE(slot == 0 || slot == 1, "ocsb_take_result: slot must be 0 or 1");
+    OCSB_REQUIRE(dst_bytes >= 0 && (size_t)dst_bytes >= ctx->kept_bytes[slot],
+                 "ocsb_take_result: the kept result has %lld bytes, dst holds %lld",
+                 (long long)ctx->kept_bytes[slot], (long long)dst_bytes);
+    if (ctx->kept_bytes[slot]) {
+        OCSB_REQUIRE(dst, "ocsb_take_result: NULL destination");
+        OCSB_CUDA(cudaMemcpyAsync(dst, ctx->kept[slot], ctx->kept_bytes[slot],
+                                  cudaMemcpyDefault, ctx->stream));
+        OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->kept[slot]);
+        ctx->kept[slot] = nullptr;
+        ctx->kept_bytes[slot] = 0;
+    }
+    return OCSB_OK;
 }
 
 // ---------------------------------------------------------------------------

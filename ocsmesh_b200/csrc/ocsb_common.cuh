@@ -98,6 +98,10 @@ struct ocsb_ctx {
     cudaEvent_t ev_win[OCSB_WIN_STREAMS] = {};
     // one-time cudaFuncSetAttribute calls already made on this device
     unsigned func_attr_done = 0;
+    // results kept on the device until the caller takes them (ocsb_take_result):
+    // slot 0 = points / polyline vertices, slot 1 = polyline offsets
+    void *kept[2] = {nullptr, nullptr};
+    size_t kept_bytes[2] = {0, 0};
     // spline coefficient cache (one raster window)
     const void *spl_key = nullptr;
     double *spl_coef = nullptr;
@@ -372,6 +376,14 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
                            int64_t zs, int w, int jb, int je, double level,
                            LinAxis ax, LinAxis ay, int64_t cap, int64_t *edges,
                            double *pts, int64_t *n_out);
+
+// k_stitch.cu (results are carved from the caller's ScratchGuard)
+int32_t k_stitch_segments(ocsb_ctx *ctx, ScratchGuard &sg, const int64_t *edges,
+                          const double *pts, int64_t n, double **xy_out, int64_t **off_out,
+                          int64_t *n_xy, int64_t *n_lines);
+int32_t k_resample_lines(ocsb_ctx *ctx, ScratchGuard &sg, const double *xy, const int64_t *off,
+                         int64_t n_lines, double target, int max_verts, double **out,
+                         int64_t *n_out);
 
 // k_constraint.cu
 int32_t k_constant_value(ocsb_ctx *ctx, int w, int h, const void *dem,

@@ -721,13 +721,24 @@ class HfunRaster:
         become features; returns silently when there is no contour."""
         if not isinstance(level, list):
             level = [level]
-        contours = []
-        for _level in level:
-            contours.extend(self._raster.get_contour(_level))
-        if len(contours) == 0:
-            _logger.info('No contours found!')
-            return
-        self.add_feature(contours, expansion_rate, target_size, nprocs=nprocs)
+        ts = self._hmin if target_size is None else target_size
+        if ts is not None and ts > 0:
+            # trace -> stitch -> repartition -> resample on the device: the
+            # vertex array goes straight into the nearest-vertex search
+            pts = self._raster.get_contour_points(level, ts, 200, device=self._device)
+            if int(pts.shape[0]) == 0:
+                _logger.info('No contours found!')
+                return
+            self.add_feature_points(pts, expansion_rate, target_size)
+        else:
+            contours = []
+            for _level in level:
+                contours.extend(self._raster.get_contour(_level))
+            if len(contours) == 0:
+                _logger.info('No contours found!')
+                return
+            # raises the reference's errors for a missing / non-positive target
+            self.add_feature(contours, expansion_rate, target_size, nprocs=nprocs)
         # outer decorator layer (idempotent clamp) -- only observable when
         # constraints are being held
         if self._hold_const:

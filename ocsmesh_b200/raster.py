@@ -448,14 +448,10 @@ class Raster:
         data = self._src.read(band, masked=masked, window=window)
         return x, y, data
 
-    def get_contour(self, level: float, window: Optional[Window] = None,
-                    device: Optional[int] = None) -> List[np.ndarray]:
-        """Iso-lines of band 1 at ``level`` as a list of ``(n, 2)`` polylines
-        (stands in for ``Raster.get_contour`` ``ocsmesh/raster.py:1340-1372``,
-        which returns a shapely (Multi)LineString traced by matplotlib).
-        The sweep over the pixels runs on the device (``ocsb_contour_segments``:
-        cell classification, crossing points, ordered compaction); the host
-        stitches the O(segments) list into polylines."""
+    def _contour_window(self, window, device):
+        """(ctx, ocsb_win restricted to the cell rows held on the device, DEM
+        address, dtype code) for the contour calls; None when the device holds
+        no cell row of the window."""
         from . import _lib
         window = self._full(window)
         ctx = _lib.default_context(device)
@@ -478,7 +474,7 @@ class Raster:
         rb = max(0, origin - window.row_off)
         re = min(window.height, origin + rows - window.row_off)
         if re - rb < 2 or window.width < 2:
-            return []
+            return None
         # cell row j needs DEM rows j and j + 1: a band that stops short of
         # the window's last row gives up its last row of cells
         cw = _lib.make_win(self.get_window_bounds(window), window.width,
@@ -486,8 +482,45 @@ class Raster:
                            re - 1 if re < window.height else 0)
         addr = dem.data_ptr() + ((window.row_off - origin) * w
                                  + window.col_off) * dem.element_size()
-        edges, pts = ctx.contour_segments(cw, addr, code, w, level)
-        return _features.stitch_segments(edges, pts)
+        return ctx, cw, addr, code
+
+    def get_contour(self, level: float, window: Optional[Window] = None,
+                    device: Optional[int] = None, stitch: str = "device") -> List[np.ndarray]:
+        """Iso-lines of band 1 at ``level`` as a list of ``(n, 2)`` polylines
+        (stands in for ``Raster.get_contour`` ``ocsmesh/raster.py:1340-1372``,
+        which returns a shapely (Multi)LineString traced by matplotlib; the
+        tracer restates contourpy's documented rules, parity with it is
+        unpinned: neither library is importable here).  Sweep, stitching and
+        ordering all run on the device (``ocsb_contour_lines``);
+        ``stitch="host"`` joins the device segments on the host instead
+        (``ocsb_stitch_segments``: the same polylines, vertex for vertex)."""
+        cw = self._contour_window(window, device)
+        if cw is None:
+            return []
+        ctx, win, addr, code = cw
+        if stitch == "host":
+            edges, pts = ctx.contour_segments(win, addr, code, self.width, level)
+            return _features.stitch_segments(edges, pts)
+        xy, off = ctx.contour_lines(win, addr, code, self.width, level)
+        return [xy[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+    def get_contour_points(self, levels, target_size: float, max_verts: int = 200,
+                           window: Optional[Window] = None, device: Optional[int] = None):
+        """The resampled vertex array of the contours at ``levels`` -- what
+        ``HfunRaster.add_contour`` hands to the nearest-vertex search
+        (``ocsmesh/hfun/raster.py:991-1002, 1219-1230``) -- as an ``(N, 2)``
+        float64 CUDA tensor that never leaves the device: trace, stitch,
+        repartition and arc-length resampling are all kernels
+        (``ocsb_contour_points``).  Equal to ``feature_points(get_contour(l) for
+        l in levels)`` bit for bit."""
+        import torch
+        cw = self._contour_window(window, device)
+        if cw is None:
+            dev = torch.cuda.current_device() if device is None else int(device)
+            return torch.empty((0, 2), dtype=torch.float64, device=f"cuda:{dev}")
+        ctx, win, addr, code = cw
+        lv = list(levels) if isinstance(levels, (list, tuple, np.ndarray)) else [levels]
+        return ctx.contour_points(win, addr, code, self.width, lv, target_size, max_verts)
 
     def save(self, path):
         epsg = self.crs.to_epsg() if self.crs is not None else None

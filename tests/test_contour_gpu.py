@@ -107,3 +107,55 @@ def test_overflow_and_count_only(ctx):
                                    _lib.OCSB_F32, 64, 0.0, 1, e.ctypes.data,
                                    p.ctypes.data, C.byref(n))
     assert rc != 0 and b"capacity" in lib.ocsb_last_error()
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (257, 515), (600, 800)])
+def test_device_stitch_equals_host_stitch(ctx, shape):
+    """ocsb_contour_lines (list ranking on the device) vs the host stitch of the
+    same device segments: identical polylines, order and orientation included."""
+    h, w = shape
+    z = S.synth_dem(h, w, seed=h + 3 * w)
+    r = ob.Raster.from_numpy(z, S.dem_transform(h), crs=32618)
+    for level in (0.0, 3.0, -7.5):
+        dev = r.get_contour(level)
+        host = r.get_contour(level, stitch="host")
+        assert len(dev) == len(host)
+        for p, q in zip(dev, host):
+            np.testing.assert_array_equal(p, q)
+
+
+@pytest.mark.parametrize("target,max_verts", [(100.0, 200), (35.0, 7), (5000.0, 200)])
+def test_contour_points_equal_host_prologue(ctx, target, max_verts):
+    """ocsb_contour_points == feature_points(get_contour(l) for l in levels):
+    repartition into max_verts chunks + arc-length stations, bit for bit."""
+    z = S.synth_dem(500, 640, seed=11)
+    r = ob.Raster.from_numpy(z, S.dem_transform(500), crs=32618)
+    levels = [-5.0, 0.0, 5.0]
+    lines = []
+    for lv in levels:
+        lines.extend(r.get_contour(lv, stitch="host"))
+    want = F.feature_points(lines, target, max_verts=max_verts, native=False)
+    got = r.get_contour_points(levels, target, max_verts).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+    # a level without any contour contributes nothing; only such levels: empty
+    assert r.get_contour_points([1e6], target).shape == (0, 2)
+    got2 = r.get_contour_points([1e6, 0.0], target, max_verts).cpu().numpy()
+    want2 = F.feature_points(r.get_contour(0.0, stitch="host"), target,
+                             max_verts=max_verts, native=False)
+    np.testing.assert_array_equal(got2, want2)
+
+
+def test_rings_and_tiny_lines(ctx):
+    """Closed rings (bumps inside the raster), two-vertex lines at corners and
+    many saddles: the device ranking must order and orient them like the host."""
+    g = np.arange(40.0)
+    zz = (np.sin(g[:, None] * 0.9) * np.cos(g[None, :] * 0.7)).astype(np.float32)
+    zz[0, 0] = 1.0; zz[0, 1] = -1.0; zz[1, 0] = -1.0      # corner cut: 2-vertex line
+    r = ob.Raster.from_numpy(zz, S.dem_transform(40), crs=32618)
+    for level in (0.0, 0.4, -0.8):
+        dev = r.get_contour(level)
+        host = F.marching_squares(r.get_x(), r.get_y(), zz, level)
+        assert len(dev) == len(host) and len(dev) > 3
+        assert any(np.array_equal(p[0], p[-1]) for p in dev)       # rings present
+        for p, q in zip(dev, host):
+            np.testing.assert_array_equal(p, q)
