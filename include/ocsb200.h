@@ -348,6 +348,27 @@ int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
                               int64_t dem_stride, double level, int64_t cap,
                               int64_t *edges, double *pts, int64_t *n);
 
+/* ---- 8(f) next-2: polygon regions on the raster grid -----------------------
+ * The 0 / 1 raster of a polygon set on a window, as float32:
+ *   all_touched = 0 : pixel (r, c) is 1 when its window coordinate
+ *       (np.linspace, Raster.get_xy) lies inside the rings -- even-odd crossing
+ *       number over ALL edges (holes, several polygons) -- what
+ *       RegionConstraint.apply tests with geopandas sjoin(predicate='within')
+ *       (ocsmesh/features/constraint.py:357-380).  A RegionConstraint is then a
+ *       TopoConstConstraint on this raster (0.5 < raster).
+ *   all_touched = 1 : pixel is 1 when its AREA (edge-to-edge rectangle of the
+ *       window) is touched: centre inside or a ring edge intersects the closed
+ *       rectangle -- the mask of HfunRaster.add_patch
+ *       (rasterio.mask.raster_geometry_mask(all_touched=True),
+ *       ocsmesh/hfun/raster.py:890-897).
+ * shapely / GDAL are not importable here: both rules are restatements, parity
+ * with the reference UNPINNED.
+ *   edges    : n_edges x 4 float64 (x0, y0, x1, y1), every ring closed
+ *   mask_out : (virtual) address of window row 0, rows row_begin..row_end written */
+int32_t ocsb_region_mask(ocsb_ctx *ctx, const ocsb_win *win,
+                         const double *edges, int64_t n_edges, int32_t all_touched,
+                         float *mask_out, int64_t mask_stride);
+
 /* ---- 8(f) next-1 on the device: polylines and the feature prologue ---------
  * Raster.get_contour (ocsmesh/raster.py:1340-1372, 1426-1470: contourpy +
  * shapely linemerge) and the resampling prologue of add_feature

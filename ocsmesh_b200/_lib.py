@@ -117,6 +117,8 @@ SIGNATURES = {
     "ocsb_contour_segments": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_f64, c_i64, c_vp, c_vp,
                                       C.POINTER(c_i64)]),
+    "ocsb_region_mask": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64, c_i32, c_vp,
+                                 c_i64]),
     "ocsb_contour_lines": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
                                    c_f64, C.POINTER(c_i64), C.POINTER(c_i64)]),
     "ocsb_contour_points": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
@@ -465,6 +467,12 @@ class Context:
             check(rc)
             break
         return edges[:n.value], pts[:n.value]
+
+    def region_mask(self, win, edges, n_edges, all_touched, mask_out, mask_stride):
+        """0 / 1 float32 raster of a polygon set (``edges``: (n, 4) float64)."""
+        check(self.lib.ocsb_region_mask(self.handle, C.byref(win), ptr(edges),
+                                        int(n_edges), int(bool(all_touched)),
+                                        ptr(mask_out), int(mask_stride)))
 
     def contour_lines(self, win, dem, dem_dtype, dem_stride, level):
         """Polylines of one level, traced, stitched and ordered on the device

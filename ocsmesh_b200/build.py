@@ -33,6 +33,7 @@ SOURCES = [
     "k_constraint.cu",
     "k_contour.cu",
     "k_stitch.cu",
+    "k_region.cu",
     "k_sample.cu",
     "h_stitch.cu",
 ]

@@ -5,8 +5,10 @@ arguments and ``value_type`` / ``rate`` semantics.  ``HfunRaster`` applies them
 window by window on the device (``apply_constraints``,
 ``ocsmesh/hfun/raster.py:509-568``) through ``ocsb_hfun_topo_constraint`` /
 ``ocsb_hfun_courant_constraint``; there is no host implementation here.
-``RegionConstraint`` needs shapely's point-in-polygon test and is outside this
-build.
+``RegionConstraint`` is a ``TopoConstConstraint`` on the 0 / 1 raster of its
+polygon (``ocsb_region_mask``: even-odd point-in-polygon of the pixel
+coordinates; shapely is absent here, so that predicate is a restatement of
+``within`` and its parity with the reference is unpinned).
 """
 from __future__ import annotations
 
@@ -211,3 +213,50 @@ class CourantNumConstraint(Constraint):
             cwin, dem, dem_code, dem_stride, hfun, hfun_stride,
             float(self._value), float(self._dt), float(self._nu),
             self._vt_code)
+
+
+class RegionConstraint(Constraint):
+    """``features/constraint.py:318-395``: a fixed value where the pixel
+    coordinate lies within ``shape`` and the size does not satisfy it, relaxed
+    outside with ``rate``.  ``shape``: a shapely-style (Multi)Polygon or ring
+    arrays (``features.polygon_rings``), in the raster's CRS (no reprojection
+    here: pyproj is absent)."""
+
+    def __init__(self, value: float, shape, crs=None, value_type: str = 'max',
+                 rate: float = 0.1):
+        super().__init__(value_type, rate)
+        from . import features as _features
+        try:
+            self._rings = _features.polygon_rings(shape)
+        except TypeError as e:
+            raise ValueError("Invalid input shape type for region constraint: "
+                             f"{type(shape)}") from e
+        self._edges = _features.ring_edges(self._rings)
+        self._val = value
+        self._region = shape
+        self._crs = crs
+        # the region raster is 1 inside: a topo-const constraint with 0.5 < "z"
+        self._lb, self._ub = 0.5, np.inf
+
+    @property
+    def value(self):
+        return self._val
+
+    def _apply_device(self, ctx, cwin, dem, dem_code, dem_stride, hfun,
+                      hfun_stride, dem_view, gather=None):
+        import torch
+        rb = cwin.row_begin
+        re = cwin.row_end if cwin.row_end > 0 else cwin.height
+        w = cwin.width
+        reg = torch.empty((re - rb, w), dtype=torch.float32, device=dem_view.device)
+        base = reg.data_ptr() - rb * w * 4          # (virtual) window row 0
+        ctx.region_mask(cwin, self._edges, len(self._edges), False, base, w)
+        if self._rate is not None and gather is not None:
+            self._apply_rate_band(ctx, cwin, base, _lib.OCSB_F32, w, hfun, hfun_stride,
+                                  None, _lib.OCSB_F32, 0, float(self._val),
+                                  dem_view.device, gather)
+            return
+        ctx.hfun_topo_constraint(
+            cwin, base, _lib.OCSB_F32, w, hfun, hfun_stride, None, _lib.OCSB_F32, 0,
+            float(self._val), self._lb, self._ub, self._vt_code, self._rate)
+        ctx.sync()      # `reg` is freed on return

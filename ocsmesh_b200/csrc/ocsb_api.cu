@@ -957,6 +957,48 @@ extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
 }
 
 // ---------------------------------------------------------------------------
+// next-2: polygon regions (RegionConstraint / add_patch masks)
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_region_mask(ocsb_ctx *ctx, const ocsb_win *win, const double *edges,
+                                    int64_t n_edges, int32_t all_touched, float *mask_out,
+                                    int64_t mask_stride) {
+    CTX_ENTER("ocsb_region_mask");
+    OCSB_TRY(check_win(win, "ocsb_region_mask"));
+    OCSB_REQUIRE(n_edges >= 0 && (n_edges == 0 || edges), "ocsb_region_mask: bad edge list");
+    OCSB_REQUIRE(mask_out && mask_stride >= win->width, "ocsb_region_mask: bad mask buffer");
+    int rb, re;
+    OCSB_TRY(win_band(win, "ocsb_region_mask", &rb, &re));
+    const int w = win->width, h = win->height;
+    Staged se, sm;
+    OCSB_TRY(se.init(ctx, edges, 1, n_edges * 4, n_edges * 4, 8, STAGE_IN));
+    OCSB_TRY(sm.init(ctx, mask_out, re - rb, w, mask_stride, 4, STAGE_OUT, rb));
+    // bounding box of the rings (host copy of the edge list: small)
+    std::vector<double> eh((size_t)n_edges * 4);
+    if (n_edges)
+        OCSB_CUDA(cudaMemcpyAsync(eh.data(), se.dev, eh.size() * 8, cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    double bbox[4] = {INFINITY, INFINITY, -INFINITY, -INFINITY};
+    for (int64_t i = 0; i < n_edges; ++i) {
+        for (int k = 0; k < 2; ++k) {
+            const double x = eh[4 * i + 2 * k], y = eh[4 * i + 2 * k + 1];
+            OCSB_REQUIRE(std::isfinite(x) && std::isfinite(y),
+                         "ocsb_region_mask: non-finite ring coordinate");
+            bbox[0] = fmin(bbox[0], x); bbox[2] = fmax(bbox[2], x);
+            bbox[1] = fmin(bbox[1], y); bbox[3] = fmax(bbox[3], y);
+        }
+    }
+    LinAxis ax, ay;
+    win_axes(win, &ax, &ay);
+    const double ylo = fmin(win->y0, win->y1), yhi = fmax(win->y0, win->y1);
+    OCSB_TRY(k_region_mask(ctx, ax, ay, win->x0, yhi, (win->x1 - win->x0) / w,
+                           (yhi - ylo) / h, rb, re, w, all_touched ? 1 : 0,
+                           (const double *)se.dev, n_edges, bbox, (float *)sm.dev,
+                           sm.dev_stride));
+    return finish_call(ctx, {&se, &sm});
+}
+
+// ---------------------------------------------------------------------------
 // next-1, device side: polylines and the resampled vertex array
 // ---------------------------------------------------------------------------
 namespace {

@@ -385,6 +385,11 @@ int32_t k_resample_lines(ocsb_ctx *ctx, ScratchGuard &sg, const double *xy, cons
                          int64_t n_lines, double target, int max_verts, double **out,
                          int64_t *n_out);
 
+// k_region.cu
+int32_t k_region_mask(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, double x0, double ytop, double pw,
+                      double ph, int rb, int re, int w, int touched, const double *edges,
+                      int64_t n_edges, const double bbox[4], float *out, int64_t stride);
+
 // k_constraint.cu
 int32_t k_constant_value(ocsb_ctx *ctx, int w, int h, const void *dem,
                          int dem_dtype, int64_t zs, const float *old_,

@@ -60,6 +60,66 @@ def as_linestrings(feature) -> List[np.ndarray]:
         f"(or (n, 2) arrays), not type {type(feature)}.")
 
 
+def _is_polygon_like(obj) -> bool:
+    return hasattr(obj, "exterior") and hasattr(obj, "interiors")
+
+
+def polygon_rings(shape) -> List[np.ndarray]:
+    """Rings of a polygon input as closed ``(n, 2)`` float64 arrays: a shapely
+    style Polygon (``.exterior`` / ``.interiors``) or MultiPolygon (``.geoms``),
+    one ``(n, 2)`` array (a polygon without holes), or a list of those / of
+    ``(exterior, [holes])`` pairs.  The masks built from them use the even-odd
+    rule over ALL rings, so holes need no marking."""
+    rings: List[np.ndarray] = []
+
+    def add(r):
+        a = np.asarray(r, dtype=np.float64)
+        if a.ndim != 2 or a.shape[1] < 2 or len(a) < 3:
+            raise TypeError("a polygon ring must be an (n >= 3, 2) coordinate array")
+        a = np.ascontiguousarray(a[:, :2])
+        if not np.array_equal(a[0], a[-1]):
+            a = np.vstack([a, a[:1]])
+        rings.append(a)
+
+    def walk(o):
+        if _is_polygon_like(o):
+            add(o.exterior.coords)
+            for i in o.interiors:
+                add(i.coords)
+        elif hasattr(o, "geoms"):
+            for g in o.geoms:
+                walk(g)
+        elif isinstance(o, np.ndarray):
+            add(o)
+        elif isinstance(o, (list, tuple)):
+            def is_pair(p):
+                return isinstance(p, (list, tuple)) and len(p) in (2, 3) and \
+                    all(np.isscalar(v) for v in p)
+            if len(o) == 2 and isinstance(o[0], np.ndarray) and \
+                    isinstance(o[1], (list, tuple)):
+                add(o[0])                      # (exterior, [holes])
+                for hole in o[1]:
+                    add(hole)
+            elif len(o) and is_pair(o[0]):
+                add(o)                         # a plain list of (x, y) pairs
+            else:
+                for g in o:
+                    walk(g)
+        else:
+            raise TypeError(f"Wrong type \"{type(o)}\" for multipolygon input.")
+
+    walk(shape)
+    if not rings:
+        raise TypeError("empty polygon input")
+    return rings
+
+
+def ring_edges(rings: Sequence[np.ndarray]) -> np.ndarray:
+    """``(n, 4)`` float64 edges (x0, y0, x1, y1) of closed rings."""
+    return np.ascontiguousarray(np.concatenate(
+        [np.hstack([r[:-1], r[1:]]) for r in rings], axis=0))
+
+
 def repartition_features(linestring: np.ndarray, max_verts: int) -> List[np.ndarray]:
     """``ocsmesh/utils.py:247-277``: cut a line into chunks of at most
     ``max_verts`` vertices that share their end vertex."""

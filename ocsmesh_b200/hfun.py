@@ -665,15 +665,76 @@ class HfunRaster:
                 wave_amplitude=wave_amplitude, value_type='min'))
         self.apply_added_constraints()
 
-    def add_region_constraint(self, *args, **kwargs) -> None:
-        raise NotImplementedError(
-            "RegionConstraint needs shapely's point-in-polygon test "
-            "(hfun/raster.py:738-800); outside this build")
+    def add_region_constraint(self, value, shape, crs=None,
+                              value_type: str = 'min', rate: float = 0.01) -> None:
+        """``hfun/raster.py:739-800``: a fixed-value constraint inside a
+        polygon region (shapely-style object or ring arrays, in the raster's
+        CRS), relaxed outside with ``rate``."""
+        if crs is None:
+            warnings.warn(
+                "No CRS is provided for the contraint shape."
+                " Assuming CRS is the same as size function's raster",
+                category=UserWarning)
+            crs = self.crs
+        self._register(_constraint.RegionConstraint(
+            value=value, shape=shape, crs=crs, value_type=value_type, rate=rate))
 
-    def add_patch(self, *args, **kwargs) -> None:
-        raise NotImplementedError(
-            "add_patch rasterises polygons with GDAL (rasterio.mask."
-            "raster_geometry_mask, hfun/raster.py:890-933); outside this build")
+    def add_patch(self, multipolygon, expansion_rate: Optional[float] = None,
+                  target_size: Optional[float] = None,
+                  nprocs: Optional[int] = None) -> None:
+        """``hfun/raster.py:803-933``: a region of fixed size ``target_size``
+        (every pixel whose area the polygons touch: the reference's
+        ``all_touched=True`` mask, restated by ``ocsb_region_mask``), optionally
+        expanded outside with ``expansion_rate`` (the rings go through
+        ``add_feature``)."""
+        del nprocs
+        try:
+            rings = _features.polygon_rings(multipolygon)
+        except TypeError as e:
+            raise TypeError(f"Wrong type \"{type(multipolygon)}\""
+                            " for multipolygon input.") from e
+        target_size = self._hmin if target_size is None else target_size
+        if target_size is None:
+            raise ValueError('Argument target_size must be specified if no '
+                             'global hmin has been set.')
+        if target_size <= 0:
+            raise ValueError("Argument target_size must be greater than zero.")
+        if expansion_rate is not None:
+            self.add_feature(rings, expansion_rate, target_size)
+        import torch
+        self._materialize()
+        ctx = self._ctx()
+        edges = _features.ring_edges(rings)
+        fuse = self._fuse_clamp()
+        buf = self._hfun
+        b0 = self._band[0]
+        for win in self._windows():
+            band = self._band_of(win)
+            if band is None:
+                continue
+            cw = _lib.make_win(self._raster.get_window_bounds(win), win.width,
+                               win.height, band[0], band[1])
+            rows = band[1] - band[0]
+            mask = torch.empty((rows, win.width), dtype=torch.float32,
+                               device=buf.device)
+            ctx.region_mask(cw, edges, len(edges), True,
+                            mask.data_ptr() - band[0] * win.width * 4, win.width)
+            r0 = win.row_off + band[0] - b0
+            view = buf[r0:r0 + rows, win.col_off:win.col_off + win.width]
+            vals = torch.where(mask > 0.5, torch.tensor(float(target_size),
+                                                        dtype=torch.float32,
+                                                        device=buf.device), view)
+            if self._hmin is not None:
+                vals = torch.where(vals < self._hmin, torch.tensor(
+                    self._hmin, dtype=torch.float32, device=buf.device), vals)
+            if self._hmax is not None:
+                vals = torch.where(vals > self._hmax, torch.tensor(
+                    self._hmax, dtype=torch.float32, device=buf.device), vals)
+            view.copy_(torch.minimum(view, vals))
+        if fuse and (self._hmin is not None or self._hmax is not None):
+            # the decorator's clamp re-pass (apply_constraints with no constraint)
+            self.apply_constraints([])
+        self._after_op(fuse)
 
     # ---- add_constant_value -------------------------------------------------
     def add_constant_value(self, value: float,

@@ -494,6 +494,21 @@ class Raster:
         ordering all run on the device (``ocsb_contour_lines``);
         ``stitch="host"`` joins the device segments on the host instead
         (``ocsb_stitch_segments``: the same polylines, vertex for vertex)."""
+        if window is None:
+            wins = list(self.iter_windows())
+            if len(wins) > 1:
+                # chunked raster: the reference traces every window on its own
+                # (own np.linspace coordinates, no cell between two windows) and
+                # hands the pieces to shapely's linemerge
+                # (_get_raster_contour_feathered, ocsmesh/raster.py:1471-1575).
+                # Pieces of different windows only merge where end points
+                # coincide exactly, which per-window linspaces do not produce:
+                # the result is the list of the windows' polylines, in window
+                # order
+                lines = []
+                for wn in wins:
+                    lines.extend(self.get_contour(level, wn, device, stitch))
+                return lines
         cw = self._contour_window(window, device)
         if cw is None:
             return []
@@ -514,6 +529,17 @@ class Raster:
         (``ocsb_contour_points``).  Equal to ``feature_points(get_contour(l) for
         l in levels)`` bit for bit."""
         import torch
+        if window is None:
+            wins = list(self.iter_windows())
+            if len(wins) > 1:
+                # chunked raster: window by window, like get_contour; the
+                # reference's add_contour flattens level by level, so the
+                # levels are the outer loop
+                lv = list(levels) if isinstance(levels, (list, tuple, np.ndarray)) \
+                    else [levels]
+                parts = [self.get_contour_points([l], target_size, max_verts, wn, device)
+                         for l in lv for wn in wins]
+                return torch.cat(parts, dim=0)
         cw = self._contour_window(window, device)
         if cw is None:
             dev = torch.cuda.current_device() if device is None else int(device)

@@ -942,3 +942,89 @@ def get_contour(raster: OracleRaster, level: float) -> List[np.ndarray]:
     x, y = raster.get_x(), raster.get_y()
     values = raster.get_values(band=1)
     return marching_squares(x, y, values, level)
+
+
+# ---------------------------------------------------------------------------
+# polygon regions (RegionConstraint / add_patch).  shapely / GDAL are absent:
+# the two predicates below RESTATE `within` (geopandas sjoin,
+# ocsmesh/features/constraint.py:375-380) and all_touched rasterisation
+# (rasterio.mask.raster_geometry_mask, ocsmesh/hfun/raster.py:890-897) --
+# parity with the reference is unpinned for them.
+# ---------------------------------------------------------------------------
+def points_in_rings(xy: np.ndarray, rings) -> np.ndarray:
+    """Even-odd crossing number of the +x ray over all ring edges."""
+    px, py = xy[:, 0], xy[:, 1]
+    cnt = np.zeros(len(xy), dtype=np.int64)
+    for r in rings:
+        r = np.asarray(r, dtype=np.float64)
+        for (x0, y0), (x1, y1) in zip(r[:-1], r[1:]):
+            span = (y0 > py) != (y1 > py)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                xint = x0 + (py - y0) * (x1 - x0) / (y1 - y0)
+            cnt += (span & (px < xint)).astype(np.int64)
+    return (cnt & 1).astype(bool)
+
+
+def _seg_hits_rects(e, xa, ya, xb, yb):
+    x0, y0, x1, y1 = e
+    dx, dy = x1 - x0, y1 - y0
+    t0 = np.zeros_like(xa)
+    t1 = np.ones_like(xa)
+    ok = np.ones(xa.shape, dtype=bool)
+    for p, q in ((-dx, x0 - xa), (dx, xb - x0), (-dy, y0 - ya), (dy, yb - y0)):
+        if p == 0.0:
+            ok &= ~(q < 0.0)
+        else:
+            r = q / p
+            if p < 0.0:
+                ok &= ~(r > t1)
+                t0 = np.where(r > t0, r, t0)
+            else:
+                ok &= ~(r < t0)
+                t1 = np.where(r < t1, r, t1)
+    return ok & (t0 <= t1)
+
+
+def touched_mask(bounds, height: int, width: int, rings) -> np.ndarray:
+    """all_touched: pixel area (edge-to-edge rectangles of the window bounds
+    (x0, y0, x1, y1)) touched = centre inside or a ring edge meets the closed
+    rectangle."""
+    x0, y0, x1, y1 = bounds
+    pw, ph = (x1 - x0) / width, (y1 - y0) / height
+    c = np.arange(width)
+    r = np.arange(height)
+    xa = np.tile(x0 + c * pw, height)
+    xb = np.tile(x0 + (c + 1) * pw, height)
+    yb = np.repeat(y1 - r * ph, width)
+    ya = np.repeat(y1 - (r + 1) * ph, width)
+    ctr = np.stack([0.5 * (xa + xb), 0.5 * (ya + yb)], axis=1)
+    m = points_in_rings(ctr, rings)
+    for rg in rings:
+        rg = np.asarray(rg, dtype=np.float64)
+        for a, b in zip(rg[:-1], rg[1:]):
+            m |= _seg_hits_rects((a[0], a[1], b[0], b[1]), xa, ya, xb, yb)
+    return m.reshape(height, width)
+
+
+class RegionConstraint(TopoConstConstraint):
+    """features/constraint.py:318-395 with the restated `within`."""
+
+    def __init__(self, value, rings, value_type='max', rate=0.1):
+        super().__init__(value, np.inf, 0.5, value_type, rate)
+        self._rings = rings
+
+    def apply(self, ref_values, old_values, locations=None, crs=None):
+        inside = points_in_rings(locations, self._rings).reshape(old_values.shape)
+        return super().apply(inside.astype(np.float32), old_values, locations, crs)
+
+
+def add_patch_window(old: np.ndarray, mask: np.ndarray, target_size, hmin, hmax):
+    """hfun/raster.py:917-926 for one window."""
+    values = old.copy()
+    if mask.any():
+        values[mask] = target_size
+    if hmin is not None:
+        values[np.where(values < hmin)] = hmin
+    if hmax is not None:
+        values[np.where(values > hmax)] = hmax
+    return np.minimum(old, values)

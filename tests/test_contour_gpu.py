@@ -159,3 +159,24 @@ def test_rings_and_tiny_lines(ctx):
         assert any(np.array_equal(p[0], p[-1]) for p in dev)       # rings present
         for p, q in zip(dev, host):
             np.testing.assert_array_equal(p, q)
+
+
+def test_chunked_raster_traces_window_by_window(ctx):
+    """Reference Raster.get_contour on a chunked raster
+    (_get_raster_contour_feathered, ocsmesh/raster.py:1471-1575): every window
+    is traced on its own coordinates, the pieces are concatenated."""
+    z = S.synth_dem(300, 420, seed=17)
+    r = ob.Raster.from_numpy(z, S.dem_transform(300), crs=32618, chunk_size=128, overlap=2)
+    wins = list(r.iter_windows())
+    assert len(wins) > 4
+    got = r.get_contour(0.0)
+    want = []
+    for wn in wins:
+        sub = z[wn.row_off:wn.row_off + wn.height, wn.col_off:wn.col_off + wn.width]
+        want.extend(F.marching_squares(r.get_x(wn), r.get_y(wn), sub, 0.0))
+    assert len(got) == len(want)
+    for p, q in zip(got, want):
+        np.testing.assert_array_equal(p, q)
+    pts = r.get_contour_points([0.0, 5.0], 100.0).cpu().numpy()
+    lines = r.get_contour(0.0) + r.get_contour(5.0)
+    np.testing.assert_array_equal(pts, F.feature_points(lines, 100.0, native=False))
