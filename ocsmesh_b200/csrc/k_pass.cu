@@ -241,13 +241,18 @@ __device__ __forceinline__ void dom_step(const Rect &q, bool valid, double2 v,
                                          unsigned key[5], DomTable &tab, int lane) {
     const CornerD2 c = corner_d2(q, v);
     const double dd[5] = {center_d2(q, v), c.d00, c.d01, c.d10, c.d11};
+    // the five warp minima first (independent reductions in flight together),
+    // then the rare table updates
+    unsigned k[5], m[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) k[j] = valid ? __float_as_uint((float)dd[j]) : 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) m[j] = __reduce_min_sync(0xffffffffu, k[j]);
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
-        const unsigned k = valid ? __float_as_uint((float)dd[j]) : 0xffffffffu;
-        const unsigned m = __reduce_min_sync(0xffffffffu, k);
-        if (m < key[j]) {   // warp-uniform
-            key[j] = m;
-            const int src = __ffs(__ballot_sync(0xffffffffu, k == m)) - 1;
+        if (m[j] < key[j]) {   // warp-uniform
+            key[j] = m[j];
+            const int src = __ffs(__ballot_sync(0xffffffffu, k[j] == m[j])) - 1;
             if (lane == src) {
                 const double mg = 1.0 + kDomEps;
                 tab.c[j][0] = c.d00 * mg; tab.c[j][1] = c.d01 * mg;
@@ -1508,9 +1513,13 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             OCSB_TIME(ctx, KC_FEATURE_REFINE);
             root_kernel<<<(unsigned)n2, kRootThreads, 0, ctx->stream>>>(B);
             OCSB_LAUNCHED(ctx);
-            OCSB_TIME(ctx, KC_FEATURE_REFINE);
-            l1_kernel<<<(unsigned)n1, kL1Threads, 0, ctx->stream>>>(B);
-            OCSB_LAUNCHED(ctx);
+            if (!v2) {
+                // (the persistent kernel's slots come from l10_kernel below, which
+                //  filters the 1024-px lists itself)
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                l1_kernel<<<(unsigned)n1, kL1Threads, 0, ctx->stream>>>(B);
+                OCSB_LAUNCHED(ctx);
+            }
             OCSB_CHECK_LAUNCH();
 
             FeatDev &F = T.feat[f];
@@ -1518,7 +1527,10 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             F.off1 = B.l1.off; F.cnt1 = B.l1.cnt; F.ids1 = B.l1.ids;
             if (v2) {
                 // 64-px level: one slot per tile (+ overflow pool) for the persistent kernel
-                unsigned long long cap0 = 4ull * nv + 8ull * (unsigned long long)n0 + (1ull << 16);
+                // overflow lists of 64-px tiles + the 256-px lists too long for
+                // shared memory (dense vertex sets)
+                unsigned long long cap0 = 8ull * nv + 8ull * (unsigned long long)n0 +
+                                          48ull * (unsigned long long)n1 + (1ull << 17);
                 cap0 <<= (2 * attempt);
                 if (async_mode) cap0 <<= 1;
                 cap0 = std::min<unsigned long long>(cap0, 0x7fffffffull);
@@ -1526,7 +1538,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 OCSB_TRY(pools.get(&pool0, (size_t)cap0));
                 L0Args L;
                 L.wins = d_wins; L.n_wins = d.n_wins; L.n_tiles = (int)n0;
-                L.cnt1 = B.l1.cnt; L.off1 = B.l1.off; L.xy1 = B.l1.xy;
+                L.cnt2 = B.l2.cnt; L.off2 = B.l2.off; L.xy2 = B.l2.xy;
                 L.r2lim = r2lim;
                 L.slots = slots0; L.pool = pool0;
                 L.ctr = ctrs + 2 * kMaxFeat; L.cap = cap0;
@@ -1534,7 +1546,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 L.sticky = sticky;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 L.n_parents = (int)n1;
-                l0_kernel<<<(unsigned)n1, 256, 0, ctx->stream>>>(L);
+                l10_kernel<<<(unsigned)n1, 256, 0, ctx->stream>>>(L);
                 OCSB_LAUNCHED(ctx);
                 OCSB_CHECK_LAUNCH();
             }

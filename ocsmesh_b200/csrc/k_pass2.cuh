@@ -489,15 +489,17 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
 }
 
 // ---------------------------------------------------------------------------
-// level 0: the slots of the (up to 16) 64-px tiles of one 256-px parent tile per
-// CTA: the parent's list is read ONCE into shared memory, a warp filters two
-// children from there; a parent without a list only writes empty headers
+// levels 1 + 0 in one launch: one CTA per 256-px tile filters its 1024-px parent
+// list down to the tile (the work of l1_kernel) INTO SHARED MEMORY and goes
+// straight on to the slots of its (up to 16) 64-px children, a warp per two
+// children; a tile without candidates only writes empty headers.  The 256-px
+// lists never go to global memory and one launch of the chain is gone.
 // ---------------------------------------------------------------------------
 struct L0Args {
     const PWin *wins;
     int n_wins, n_tiles, n_parents;
-    const int *cnt1, *off1;
-    const double2 *xy1;
+    const int *cnt2, *off2;         // 1024-px lists (coordinates)
+    const double2 *xy2;
     double r2lim;
     double2 *slots, *pool;
     unsigned long long *ctr;
@@ -506,11 +508,17 @@ struct L0Args {
     int *sticky;
 };
 
-constexpr int kL0Stage = 1024;       // parent candidates staged in shared memory
+constexpr int kL0Stage = 1024;       // tile candidates held in shared memory
 
-__global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
-    __shared__ DomTable s_tab[8];
+__global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
+    constexpr int NW = 8;
+    __shared__ unsigned s_key[NW][5];
+    __shared__ DomTable s_tab[NW];
+    __shared__ DomTable s_fin;
+    __shared__ unsigned s_key0;
     __shared__ __align__(16) double2 s_xy[kL0Stage];
+    __shared__ int s_cnt;
+    __shared__ unsigned long long s_base;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int t1 = blockIdx.x;
     if (t1 >= A.n_parents || *A.overflow) return;
@@ -518,11 +526,12 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
     const PWin &W = A.wins[wi];
     const int lt1 = t1 - W.base1;
     const int ty1 = lt1 / W.n1x, tx1 = lt1 - ty1 * W.n1x;
-    const int pcnt = A.cnt1[t1], poff = A.off1[t1];
+    const int pt = W.base2 + (ty1 >> 2) * W.n2x + (tx1 >> 2);
+    const int pcnt2 = A.cnt2[pt], poff2 = A.off2[pt];
     const int ncx = min(4, W.n0x - 4 * tx1), ncy = min(4, W.n0y - 4 * ty1);
     SlotHead hd;
     hd.cnt = 0; hd.pad = 0; hd.off = 0;
-    if (pcnt == 0) {
+    auto empty_headers = [&]() {
         if ((int)threadIdx.x < 16) {
             const int cx = threadIdx.x & 3, cy = threadIdx.x >> 2;
             if (cx < ncx && cy < ncy) {
@@ -530,15 +539,78 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
                 *reinterpret_cast<SlotHead *>(A.slots + (size_t)t * kSlot) = hd;
             }
         }
-        return;
-    }
-    const bool staged = pcnt <= kL0Stage;
-    if (staged)
-        for (int i = threadIdx.x; i < pcnt; i += 256) s_xy[i] = A.xy1[poff + i];
-    __syncthreads();
-    const double2 *src = staged ? s_xy : A.xy1 + poff;
+    };
+    if (pcnt2 == 0) { empty_headers(); return; }
     const int bw = W.ax.n, bh = W.re - W.rb;
+    // ---- level 1: the 1024-px list -> this 256-px tile ----------------------------
+    const double2 *src2 = A.xy2 + poff2;
+    {
+        const int c0 = tx1 * kT1, r0 = ty1 * kT1;
+        const Rect q = win_rect(W, c0, min(bw, c0 + kT1) - 1, r0, min(bh, r0 + kT1) - 1);
+        unsigned key[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
+        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
+            const int i = b0 + lane;
+            const bool valid = i < pcnt2;
+            double2 v = make_double2(0.0, 0.0);
+            if (valid) v = src2[i];
+            dom_step(q, valid, v, key, s_tab[wid], lane);
+        }
+        __syncwarp();
+        if (threadIdx.x == 0) s_cnt = 0;
+        dom_combine<NW>(key, s_key, s_tab, &s_fin, &s_key0);
+        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
+            const int i = b0 + lane;
+            const bool valid = i < pcnt2;
+            double2 v = make_double2(0.0, 0.0);
+            if (valid) v = src2[i];
+            const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                              !dominated_tab(s_fin, corner_d2(q, v));
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            int base = 0;
+            if (lane == 0 && m) base = atomicAdd(&s_cnt, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            const int pos = base + __popc(m & ((1u << lane) - 1u));
+            if (keep && pos < kL0Stage) s_xy[pos] = v;
+        }
+        __syncthreads();
+    }
+    const int pcnt = s_cnt;
+    if (pcnt == 0) { empty_headers(); return; }
+    // more survivors than the staging holds (dense vertex sets): the tile's list
+    // goes through the overflow pool instead of shared memory
+    const bool staged = pcnt <= kL0Stage;
+    if (!staged) {
+        if (threadIdx.x == 0) {
+            unsigned long long base = atomicAdd(A.ctr, (unsigned long long)pcnt);
+            if (base + pcnt > A.cap) { flag_overflow(A.overflow, A.sticky); base = ~0ull; }
+            s_base = base;
+            s_cnt = 0;
+        }
+        __syncthreads();
+        if (s_base == ~0ull) return;
+        const int c0 = tx1 * kT1, r0 = ty1 * kT1;
+        const Rect q = win_rect(W, c0, min(bw, c0 + kT1) - 1, r0, min(bh, r0 + kT1) - 1);
+        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
+            const int i = b0 + lane;
+            const bool valid = i < pcnt2;
+            double2 v = make_double2(0.0, 0.0);
+            if (valid) v = src2[i];
+            const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
+                              !dominated_tab(s_fin, corner_d2(q, v));
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            int base = 0;
+            if (lane == 0 && m) base = atomicAdd(&s_cnt, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) A.pool[s_base + base + __popc(m & ((1u << lane) - 1u))] = v;
+        }
+        __syncthreads();
+    }
+    const double2 *src = staged ? s_xy : A.pool + s_base;
+    const int nsrc = pcnt;
     DomTable &tab = s_tab[wid];
+    __syncthreads();        // s_tab[] is reused per warp below
     for (int child = wid; child < 16; child += 8) {
         const int cx = child & 3, cy = child >> 2;
         if (cx >= ncx || cy >= ncy) continue;           // warp-uniform
@@ -550,18 +622,18 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
         unsigned key[5];
 #pragma unroll
         for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
-        for (int b0 = 0; b0 < pcnt; b0 += 32) {
+        for (int b0 = 0; b0 < nsrc; b0 += 32) {
             const int i = b0 + lane;
-            const bool valid = i < pcnt;
+            const bool valid = i < nsrc;
             double2 v = make_double2(0.0, 0.0);
             if (valid) v = src[i];
             dom_step(q, valid, v, key, tab, lane);
         }
         __syncwarp();
         int total = 0;
-        for (int b0 = 0; b0 < pcnt; b0 += 32) {
+        for (int b0 = 0; b0 < nsrc; b0 += 32) {
             const int i = b0 + lane;
-            const bool valid = i < pcnt;
+            const bool valid = i < nsrc;
             double2 v = make_double2(0.0, 0.0);
             if (valid) v = src[i];
             const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
@@ -582,9 +654,9 @@ __global__ void __launch_bounds__(256) l0_kernel(L0Args A) {
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base == ~0ull) continue;
             int w = 0;
-            for (int b0 = 0; b0 < pcnt; b0 += 32) {
+            for (int b0 = 0; b0 < nsrc; b0 += 32) {
                 const int i = b0 + lane;
-                const bool valid = i < pcnt;
+                const bool valid = i < nsrc;
                 double2 v = make_double2(0.0, 0.0);
                 if (valid) v = src[i];
                 const bool keep = valid && !(rect_d2(q, v) > A.r2lim) &&
