@@ -348,6 +348,24 @@ int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
                               int64_t dem_stride, double level, int64_t cap,
                               int64_t *edges, double *pts, int64_t *n);
 
+/* ---- multi-GPU: blocks of the per-step exchange of a row-band run -----------
+ * (contour-vertex all-gather + 1-row DEM halo.)  Every rank
+ * contributes ONE fixed-size block to ONE all-gather per step:
+ *   [first owned DEM row | last owned DEM row] (2 x width float32, padded to
+ *   16 bytes) followed by cap vertices (its n contour vertices, then repeats of
+ *   the last one -- duplicates cannot change a nearest-vertex distance; a rank
+ *   without vertices fills with (far_coord, far_coord), |far_coord| < 1e14).
+ * ocsb_band_pack builds a rank's block, ocsb_band_unpack turns the gathered
+ * world x block array into the contiguous (world * cap, 2) vertex array and the
+ * two halo rows (NULL where the rank has no neighbour).  The collective itself
+ * is the caller's (torch.distributed / NCCL).  Device memory only.             */
+int32_t ocsb_band_pack(ocsb_ctx *ctx, const double *verts_xy, int64_t n, int64_t cap,
+                       const float *row_first, const float *row_last, int32_t width,
+                       void *send_block, double far_coord);
+int32_t ocsb_band_unpack(ocsb_ctx *ctx, const void *recv_blocks, int32_t world,
+                         int32_t rank, int64_t cap, int32_t width, double *verts_out,
+                         float *halo_above, float *halo_below);
+
 /* ---- 8(f) next-2: polygon regions on the raster grid -----------------------
  * The 0 / 1 raster of a polygon set on a window, as float32:
  *   all_touched = 0 : pixel (r, c) is 1 when its window coordinate

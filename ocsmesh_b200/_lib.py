@@ -117,6 +117,8 @@ SIGNATURES = {
     "ocsb_contour_segments": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                       c_i64, c_f64, c_i64, c_vp, c_vp,
                                       C.POINTER(c_i64)]),
+    "ocsb_band_pack": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_i32, c_vp, c_f64]),
+    "ocsb_band_unpack": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "ocsb_region_mask": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64, c_i32, c_vp,
                                  c_i64]),
     "ocsb_contour_lines": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32, c_i64,
@@ -467,6 +469,16 @@ class Context:
             check(rc)
             break
         return edges[:n.value], pts[:n.value]
+
+    def band_pack(self, verts, n, cap, row_first, row_last, width, send, far):
+        check(self.lib.ocsb_band_pack(self.handle, ptr(verts), int(n), int(cap),
+                                      ptr(row_first), ptr(row_last), int(width),
+                                      ptr(send), float(far)))
+
+    def band_unpack(self, recv, world, rank, cap, width, verts_out, halo_above, halo_below):
+        check(self.lib.ocsb_band_unpack(self.handle, ptr(recv), int(world), int(rank),
+                                        int(cap), int(width), ptr(verts_out),
+                                        ptr(halo_above), ptr(halo_below)))
 
     def region_mask(self, win, edges, n_edges, all_touched, mask_out, mask_stride):
         """0 / 1 float32 raster of a polygon set (``edges``: (n, 4) float64)."""

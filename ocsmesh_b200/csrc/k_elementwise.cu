@@ -140,3 +140,75 @@ int32_t k_coords(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, double *x, double *y) {
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;
 }
+
+
+// ---------------------------------------------------------------------------
+// per-step exchange of a row-band run (ocsmesh_b200.distributed.BandExchange):
+// ONE launch packs a rank's block [first owned DEM row | last owned DEM row |
+// its contour vertices, padded to the block capacity with repeats of the last
+// vertex (or a far point when it has none)], ONE launch unpacks the gathered
+// blocks into the contiguous vertex array and the two halo rows.
+// ---------------------------------------------------------------------------
+namespace {
+
+__global__ void band_pack_kernel(const double2 *verts, long long n, long long cap,
+                                 const float *row_first, const float *row_last, int w,
+                                 long long row_bytes, unsigned char *send, double far) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nrow = 2ll * w;
+    if (i < nrow) {
+        float *dst = reinterpret_cast<float *>(send);
+        dst[i] = i < w ? row_first[i] : row_last[i - w];
+    }
+    if (i < cap) {
+        double2 *dv = reinterpret_cast<double2 *>(send + row_bytes);
+        dv[i] = n > 0 ? verts[i < n ? i : n - 1] : make_double2(far, far);
+    }
+}
+
+__global__ void band_unpack_kernel(const unsigned char *recv, int world, int rank,
+                                   long long blk_bytes, long long row_bytes, long long cap,
+                                   int w, double2 *verts_out, float *halo_above,
+                                   float *halo_below) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (long long)world * cap) {
+        const long long r = i / cap, k = i - r * cap;
+        verts_out[i] = reinterpret_cast<const double2 *>(recv + r * blk_bytes + row_bytes)[k];
+    }
+    if (i < w) {
+        if (halo_above)     // last owned row of the rank above
+            halo_above[i] = reinterpret_cast<const float *>(recv + (rank - 1) * blk_bytes)[w + i];
+        if (halo_below)     // first owned row of the rank below
+            halo_below[i] = reinterpret_cast<const float *>(recv + (rank + 1) * blk_bytes)[i];
+    }
+}
+
+}  // namespace
+
+int32_t k_band_pack(ocsb_ctx *ctx, const double *verts, int64_t n, int64_t cap,
+                    const float *row_first, const float *row_last, int w, int64_t row_bytes,
+                    void *send, double far) {
+    const long long items = std::max<long long>(2ll * w, cap);
+    if (items <= 0) return OCSB_OK;
+    OCSB_TIME(ctx, KC_COORDS);
+    band_pack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, ctx->stream>>>(
+        reinterpret_cast<const double2 *>(verts), n, cap, row_first, row_last, w, row_bytes,
+        reinterpret_cast<unsigned char *>(send), far);
+    OCSB_LAUNCHED(ctx);
+    OCSB_CHECK_LAUNCH();
+    return OCSB_OK;
+}
+
+int32_t k_band_unpack(ocsb_ctx *ctx, const void *recv, int world, int rank, int64_t blk_bytes,
+                      int64_t row_bytes, int64_t cap, int w, double *verts_out,
+                      float *halo_above, float *halo_below) {
+    const long long items = std::max<long long>((long long)world * cap, w);
+    if (items <= 0) return OCSB_OK;
+    OCSB_TIME(ctx, KC_COORDS);
+    band_unpack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, ctx->stream>>>(
+        reinterpret_cast<const unsigned char *>(recv), world, rank, blk_bytes, row_bytes, cap, w,
+        reinterpret_cast<double2 *>(verts_out), halo_above, halo_below);
+    OCSB_LAUNCHED(ctx);
+    OCSB_CHECK_LAUNCH();
+    return OCSB_OK;
+}

@@ -1275,11 +1275,16 @@ int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P) {
         OCSB_REQUIRE(n > 0 && sms > 0, "pass2_kernel does not fit an SM");
         resident[dev] = n * sms;
     }
-    // chunk: 8 tiles per counter fetch, fewer when that would leave a CTA with
+    // chunk: up to kChunkMax tiles per counter fetch, fewer when that would leave a CTA with
     // less than ~8 fetches (a band of a multi-GPU run): the tail of a launch is
     // one chunk long
     int chunk = (int)(P.n_tiles / ((long long)resident[dev] * 8));
     chunk = std::max(1, std::min(kChunkMax, chunk));
+    static const int chunk_env = [] {
+        const char *e = getenv("OCSB_PASS_CHUNK");      // tuning override
+        return e ? atoi(e) : 0;
+    }();
+    if (chunk_env > 0) chunk = std::min(kChunkMax, chunk_env);
     P.chunk = chunk;
     const int grid = (int)std::min<long long>((P.n_tiles + chunk - 1) / chunk,
                                               (long long)resident[dev]);

@@ -4,7 +4,7 @@
 // clamp), organised as a persistent producer / consumer pipeline in which the
 // eight warps of a CTA never meet at a CTA barrier:
 //
-//   * grid = resident CTAs only; 64x64-px tiles are handed out in chunks of 8
+//   * grid = resident CTAs only; 64x64-px tiles are handed out in chunks of up to 4
 //     by one atomic counter (a tile with candidates costs ~2x a tile without;
 //     one atomic per chunk: its latency is the producer's only stall);
 //   * thread 0 is the producer.  Two tiles ahead it issues ONE mbarrier-tracked
@@ -28,7 +28,7 @@ constexpr int kSurv2 = 32;           // survivors of a warp's rect kept in share
 constexpr int kP2Threads = 256;
 constexpr int kP2Warps = kP2Threads / 32;
 #ifndef OCSB_PASS2_CHUNK
-#define OCSB_PASS2_CHUNK 8
+#define OCSB_PASS2_CHUNK 4
 #endif
 constexpr int kChunkMax = OCSB_PASS2_CHUNK; // consecutive tiles per fetch of the tile counter
                                             // (fewer when a CTA only gets a few tiles)

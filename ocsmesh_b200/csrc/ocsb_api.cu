@@ -957,6 +957,37 @@ extern "C" int32_t ocsb_contour_segments(ocsb_ctx *ctx, const ocsb_win *win,
 }
 
 // ---------------------------------------------------------------------------
+// multi-GPU: the blocks of the per-step band exchange (device memory only)
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_band_pack(ocsb_ctx *ctx, const double *verts_xy, int64_t n, int64_t cap,
+                                  const float *row_first, const float *row_last, int32_t width,
+                                  void *send_block, double far_coord) {
+    CTX_ENTER("ocsb_band_pack");
+    OCSB_REQUIRE(n >= 0 && cap >= n && cap >= 1 && width >= 1 && send_block && row_first &&
+                     row_last && (n == 0 || verts_xy),
+                 "ocsb_band_pack: bad arguments");
+    OCSB_REQUIRE(ocsb_is_device_ptr(send_block) && ocsb_is_device_ptr(row_first),
+                 "ocsb_band_pack: device memory only");
+    const int64_t row_bytes = ((2ll * width * 4) + 15) / 16 * 16;
+    return k_band_pack(ctx, verts_xy, n, cap, row_first, row_last, width, row_bytes, send_block,
+                       far_coord);
+}
+
+extern "C" int32_t ocsb_band_unpack(ocsb_ctx *ctx, const void *recv_blocks, int32_t world,
+                                    int32_t rank, int64_t cap, int32_t width, double *verts_out,
+                                    float *halo_above, float *halo_below) {
+    CTX_ENTER("ocsb_band_unpack");
+    OCSB_REQUIRE(recv_blocks && world >= 1 && rank >= 0 && rank < world && cap >= 1 &&
+                     width >= 1 && verts_out,
+                 "ocsb_band_unpack: bad arguments");
+    OCSB_REQUIRE((!halo_above || rank > 0) && (!halo_below || rank < world - 1),
+                 "ocsb_band_unpack: no neighbour on that side");
+    const int64_t row_bytes = ((2ll * width * 4) + 15) / 16 * 16;
+    return k_band_unpack(ctx, recv_blocks, world, rank, row_bytes + cap * 16, row_bytes, cap,
+                         width, verts_out, halo_above, halo_below);
+}
+
+// ---------------------------------------------------------------------------
 // next-2: polygon regions (RegionConstraint / add_patch masks)
 // ---------------------------------------------------------------------------
 extern "C" int32_t ocsb_region_mask(ocsb_ctx *ctx, const ocsb_win *win, const double *edges,

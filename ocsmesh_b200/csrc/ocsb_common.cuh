@@ -385,6 +385,14 @@ int32_t k_resample_lines(ocsb_ctx *ctx, ScratchGuard &sg, const double *xy, cons
                          int64_t n_lines, double target, int max_verts, double **out,
                          int64_t *n_out);
 
+// k_elementwise.cu: band exchange blocks
+int32_t k_band_pack(ocsb_ctx *ctx, const double *verts, int64_t n, int64_t cap,
+                    const float *row_first, const float *row_last, int w, int64_t row_bytes,
+                    void *send, double far);
+int32_t k_band_unpack(ocsb_ctx *ctx, const void *recv, int world, int rank, int64_t blk_bytes,
+                      int64_t row_bytes, int64_t cap, int w, double *verts_out,
+                      float *halo_above, float *halo_below);
+
 // k_region.cu
 int32_t k_region_mask(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, double x0, double ytop, double pw,
                       double ph, int rb, int re, int w, int touched, const double *edges,

@@ -87,3 +87,42 @@ def test_two_gpu_bench_smoke():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert out.returncode == 0, out.stderr[-2000:]
     assert '"n_gpus": 2' in out.stdout
+
+
+def test_band_pack_unpack_blocks(ctx):
+    """ocsb_band_pack / ocsb_band_unpack: the blocks of the one-collective
+    exchange, emulated for 3 ranks on one device (the collective is a torch.cat)."""
+    import torch
+    W, cap, world = 37, 9, 3
+    rng = np.random.default_rng(3)
+    rows = [torch.from_numpy(rng.random((2, W)).astype(np.float32)).cuda() for _ in range(world)]
+    verts = [torch.from_numpy(rng.random((n, 2))).cuda() for n in (5, 0, 9)]
+    row_bytes = (2 * W * 4 + 15) // 16 * 16
+    blk = row_bytes + cap * 16
+    blocks = []
+    for r in range(world):
+        send = torch.zeros(blk, dtype=torch.uint8, device="cuda")
+        ctx.band_pack(verts[r], len(verts[r]), cap, rows[r][0], rows[r][1], W, send, 1e13)
+        blocks.append(send)
+    recv = torch.stack(blocks)
+    for rank in range(world):
+        out = torch.empty((world * cap, 2), dtype=torch.float64, device="cuda")
+        above = torch.full((W,), -1.0, dtype=torch.float32, device="cuda")
+        below = torch.full((W,), -1.0, dtype=torch.float32, device="cuda")
+        ctx.band_unpack(recv, world, rank, cap, W, out,
+                        above if rank > 0 else None, below if rank < world - 1 else None)
+        torch.cuda.synchronize()
+        for r in range(world):
+            n = len(verts[r])
+            got = out[r * cap:(r + 1) * cap].cpu().numpy()
+            if n:
+                np.testing.assert_array_equal(got[:n], verts[r].cpu().numpy())
+                assert (got[n:] == verts[r][-1].cpu().numpy()).all()
+            else:
+                assert (got == 1e13).all()
+        if rank > 0:
+            assert torch.equal(above, rows[rank - 1][1])
+        else:
+            assert bool((above == -1.0).all())
+        if rank < world - 1:
+            assert torch.equal(below, rows[rank + 1][0])
