@@ -290,12 +290,12 @@ class HfunRaster:
             buf = self._hfun
             self._tiled_pass(ops, None if self._pristine else buf, buf,
                              status=self._status)
-            if len(self._pending) >= 32:
-                self._verify()      # bound the replay log of an unverified sequence
             self._pending.append((ops, self._pristine))
             self._pending_keep = self._keep
             self._keep = []
             self._pristine = False
+            if len(self._pending) > 32:
+                self._verify()      # bound the replay log of an unverified sequence
             return
         self._verify()
         ctx = self._ctx()
