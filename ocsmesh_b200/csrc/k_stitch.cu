@@ -279,24 +279,102 @@ __device__ __forceinline__ void rs_locate(const long long *off, const long long 
     *cm = l - f + 1;
 }
 
-__global__ void rs_count_kernel(const double2 *xy, const long long *off, const long long *chunk_base,
-                                int nl, long long nchunks, int max_verts, double target,
-                                long long *cnt) {
-    const long long g = (long long)blockIdx.x * kT + threadIdx.x;
-    if (g >= nchunks) return;
-    long long first, cm;
-    rs_locate(off, chunk_base, nl, max_verts, g, &first, &cm);
-    cnt[g] = rs_chunk(xy + first, cm, target, nullptr);
-}
+// One WARP per chunk.  Segment lengths are independent (lanes, coalesced
+// loads); the running sums that decide the stations are taken by lane 0 in
+// np.cumsum order from shared memory (bit-identical to the sequential walk,
+// without its chain of dependent global loads); the stations themselves are
+// independent again (binary search in the running sums).  Chunks longer than
+// kRsSeg segments or with more than kRsSt stations take the sequential walk.
+constexpr int kRsSeg = 256, kRsSt = 256, kRsWarps = 4;
 
-__global__ void rs_write_kernel(const double2 *xy, const long long *off, const long long *chunk_base,
-                                int nl, long long nchunks, int max_verts, double target,
-                                const long long *out_off, double2 *out) {
-    const long long g = (long long)blockIdx.x * kT + threadIdx.x;
+struct RsScr {
+    double len[kRsSeg], cum[kRsSeg], st[kRsSt];
+};
+
+template <bool WRITE>
+__global__ void __launch_bounds__(kRsWarps * 32)
+rs_kernel(const double2 *xy, const long long *off, const long long *chunk_base, int nl,
+          long long nchunks, int max_verts, double target, long long *cnt,
+          const long long *out_off, double2 *out) {
+    __shared__ RsScr s_scr[kRsWarps];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long g = (long long)blockIdx.x * kRsWarps + wid;
     if (g >= nchunks) return;
-    long long first, cm;
-    rs_locate(off, chunk_base, nl, max_verts, g, &first, &cm);
-    rs_chunk(xy + first, cm, target, out + out_off[g]);
+    long long first, m;
+    rs_locate(off, chunk_base, nl, max_verts, g, &first, &m);
+    const double2 *c = xy + first;
+    double2 *o = WRITE ? out + out_off[g] : nullptr;
+    RsScr &S = s_scr[wid];
+    if (m < 2 || m - 1 > kRsSeg) {
+        if (lane == 0) {
+            const long long n = rs_chunk(c, m, target, o);
+            if (!WRITE) cnt[g] = n;
+        }
+        return;
+    }
+    const int ns = (int)(m - 1);
+    for (int k = lane; k < ns; k += 32) {
+        const double dx = __dsub_rn(c[k + 1].x, c[k].x), dy = __dsub_rn(c[k + 1].y, c[k].y);
+        S.len[k] = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    }
+    __syncwarp();
+    long long nst = 0;
+    int extra = 0;
+    if (lane == 0) {
+        double acc = 0.0;
+        for (int k = 0; k < ns; ++k) {
+            acc = (k == 0) ? S.len[0] : __dadd_rn(acc, S.len[k]);
+            S.cum[k] = acc;
+        }
+        const double total = acc;
+        const double q = py_floordiv_dev(total, target);
+        nst = (q > 0.0 && q < 9e15) ? (long long)q : 0;
+        if (nst > 0 && nst <= kRsSt) {
+            // stations: cumsum(ones(nst) * target), then `total` if the last is short
+            double d = 0.0;
+            for (int k = 0; k < (int)nst; ++k) {
+                d = (k == 0) ? target : __dadd_rn(d, target);
+                S.st[k] = d;
+            }
+            extra = d < total ? 1 : 0;
+        }
+    }
+    nst = __shfl_sync(0xffffffffu, nst, 0);
+    extra = __shfl_sync(0xffffffffu, extra, 0);
+    if (nst > kRsSt) {                      // very fine target: sequential walk
+        if (lane == 0) {
+            const long long n = rs_chunk(c, m, target, o);
+            if (!WRITE) cnt[g] = n;
+        }
+        return;
+    }
+    if (!WRITE) {
+        if (lane == 0) cnt[g] = nst == 0 ? m : 1 + nst + extra;
+        return;
+    }
+    __syncwarp();
+    if (nst == 0) {                          // shorter than target: unchanged
+        for (long long k = lane; k < m; k += 32) o[k] = c[k];
+        return;
+    }
+    if (lane == 0) o[0] = c[0];
+    const int nstations = (int)nst + extra;
+    const double total = S.cum[ns - 1];
+    for (int k = lane; k < nstations; k += 32) {
+        const double dist = k < (int)nst ? S.st[k] : total;
+        // np.searchsorted(cum_len, dist, 'left'), clipped to the last segment
+        int lo = 0, hi = ns - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (S.cum[mid] < dist) lo = mid + 1; else hi = mid;
+        }
+        const int seg = lo;
+        const double ratio = __ddiv_rn(__dsub_rn(S.cum[seg], dist), S.len[seg]);
+        const double om = __dsub_rn(1.0, ratio);
+        o[1 + k] = make_double2(
+            __dadd_rn(__dmul_rn(c[seg].x, ratio), __dmul_rn(c[seg + 1].x, om)),
+            __dadd_rn(__dmul_rn(c[seg].y, ratio), __dmul_rn(c[seg + 1].y, om)));
+    }
 }
 
 __global__ void widen_kernel(const int *a, int n, long long *b) {
@@ -470,8 +548,9 @@ int32_t k_resample_lines(ocsb_ctx *ctx, ScratchGuard &sg, const double *xy, cons
     OCSB_TRY(sg.get(&out_off, (size_t)nchunks + 1));
     OCSB_CUDA(cudaMemsetAsync(cnt + nchunks, 0, sizeof(long long), st));
     OCSB_TIME(ctx, KC_CONTOUR);
-    rs_count_kernel<<<nblk(nchunks), kT, 0, st>>>((const double2 *)xy, (const long long *)off,
-                                                  chunk_base, nl, nchunks, max_verts, target, cnt);
+    rs_kernel<false><<<(unsigned)((nchunks + kRsWarps - 1) / kRsWarps), kRsWarps * 32, 0, st>>>(
+        (const double2 *)xy, (const long long *)off, chunk_base, nl, nchunks, max_verts, target,
+        cnt, nullptr, nullptr);
     OCSB_LAUNCHED(ctx);
     OCSB_TRY(excl_sum(ctx, sg, cnt, out_off, nchunks + 1));
     long long total = 0;
@@ -479,9 +558,9 @@ int32_t k_resample_lines(ocsb_ctx *ctx, ScratchGuard &sg, const double *xy, cons
     double2 *o = nullptr;
     OCSB_TRY(sg.get(&o, (size_t)std::max<long long>(total, 1)));
     OCSB_TIME(ctx, KC_CONTOUR);
-    rs_write_kernel<<<nblk(nchunks), kT, 0, st>>>((const double2 *)xy, (const long long *)off,
-                                                  chunk_base, nl, nchunks, max_verts, target,
-                                                  out_off, o);
+    rs_kernel<true><<<(unsigned)((nchunks + kRsWarps - 1) / kRsWarps), kRsWarps * 32, 0, st>>>(
+        (const double2 *)xy, (const long long *)off, chunk_base, nl, nchunks, max_verts, target,
+        nullptr, out_off, o);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     *out = reinterpret_cast<double *>(o);

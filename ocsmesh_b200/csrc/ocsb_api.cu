@@ -174,7 +174,7 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
     if (ctx->spl_coef) cudaFree(ctx->spl_coef);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto &k : ctx->kept)
-        if (k) cudaFree(k);
+        if (k) ocsb_free(ctx, k);
     for (auto &sl : ctx->stage_ring) {
         if (sl.host) cudaFreeHost(sl.host);
         if (sl.ev) cudaEventDestroy(sl.ev);
@@ -1035,10 +1035,11 @@ extern "C" int32_t ocsb_region_mask(ocsb_ctx *ctx, const ocsb_win *win, const do
 namespace {
 
 int32_t keep_result(ocsb_ctx *ctx, int slot, const void *dev, size_t bytes) {
-    if (ctx->kept[slot]) { cudaFree(ctx->kept[slot]); ctx->kept[slot] = nullptr; }
+    // (stream-ordered pool: cudaMalloc / cudaFree would synchronise the device)
+    if (ctx->kept[slot]) { ocsb_free(ctx, ctx->kept[slot]); ctx->kept[slot] = nullptr; }
     ctx->kept_bytes[slot] = bytes;
     if (bytes == 0) return OCSB_OK;
-    OCSB_CUDA(cudaMalloc(&ctx->kept[slot], bytes));
+    OCSB_TRY(ocsb_alloc(ctx, &ctx->kept[slot], bytes));
     OCSB_CUDA(cudaMemcpyAsync(ctx->kept[slot], dev, bytes, cudaMemcpyDeviceToDevice,
                               ctx->stream));
     return OCSB_OK;
@@ -1126,10 +1127,10 @@ extern "C" int32_t ocsb_contour_points(ocsb_ctx *ctx, const ocsb_win *win, const
         total += np;
     }
     *n_points = total;
-    if (ctx->kept[0]) { cudaFree(ctx->kept[0]); ctx->kept[0] = nullptr; }
+    if (ctx->kept[0]) { ocsb_free(ctx, ctx->kept[0]); ctx->kept[0] = nullptr; }
     ctx->kept_bytes[0] = (size_t)total * 16;
     if (total) {
-        OCSB_CUDA(cudaMalloc(&ctx->kept[0], (size_t)total * 16));
+        OCSB_TRY(ocsb_alloc(ctx, &ctx->kept[0], (size_t)total * 16));
         size_t at = 0;
         for (size_t i = 0; i < parts.size(); ++i) {
             if (counts[i])
@@ -1154,7 +1155,7 @@ extern "C" int32_t ocsb_take_result(ocsb_ctx *ctx, int32_t slot, void *dst, int6
         OCSB_CUDA(cudaMemcpyAsync(dst, ctx->kept[slot], ctx->kept_bytes[slot],
                                   cudaMemcpyDefault, ctx->stream));
         OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
-        cudaFree(ctx->kept[slot]);
+        ocsb_free(ctx, ctx->kept[slot]);
         ctx->kept[slot] = nullptr;
         ctx->kept_bytes[slot] = 0;
     }

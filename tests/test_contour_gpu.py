@@ -124,7 +124,7 @@ def test_device_stitch_equals_host_stitch(ctx, shape):
             np.testing.assert_array_equal(p, q)
 
 
-@pytest.mark.parametrize("target,max_verts", [(100.0, 200), (35.0, 7), (5000.0, 200)])
+@pytest.mark.parametrize("target,max_verts", [(100.0, 200), (35.0, 7), (5000.0, 200), (0.7, 200), (12.0, 400)])
 def test_contour_points_equal_host_prologue(ctx, target, max_verts):
     """ocsb_contour_points == feature_points(get_contour(l) for l in levels):
     repartition into max_verts chunks + arc-length stations, bit for bit."""
