@@ -189,6 +189,25 @@ int32_t ocsb_nearest_vertex(ocsb_ctx *ctx, const double *verts_xy, int64_t nv,
                             const double *query_xy, int64_t nq, double r,
                             double *dist_out, int64_t *idx_out);
 
+/* The same query without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The vertex grid lives in one fixed file-scope device array (~4 MiB, held
+ * by every GPU that loads the library until the process exits), so:
+ *   - nv <= OCSB_STATIC_MAX_VERTS, more -> OCSB_EINVAL with a message;
+ *   - every buffer must be DEVICE memory (nothing is staged), verts_xy and
+ *     query_xy 16-byte aligned;
+ *   - no cudaMalloc / cudaFree / pool or library allocation on any path;
+ *   - all calls share the array (it keeps the last call's contents; what must
+ *     start at zero is cleared by each call): calls that overlap on the GPU
+ *     (two streams or two contexts of one device) race -- serialise them.
+ * Results are bit-identical to ocsb_nearest_vertex; the call is stream-ordered
+ * after one internal wait for the vertices' bounding box.                      */
+#define OCSB_STATIC_MAX_VERTS 262144
+int32_t ocsb_nearest_vertex_static(ocsb_ctx *ctx, const double *verts_xy, int64_t nv,
+                                   const double *query_xy, int64_t nq, double r,
+                                   double *dist_out, int64_t *idx_out);
+
 /* ---- A8 (+A9): subtidal flow limiter / gradient stencil --------------------
  * Body of the window loop of HfunRaster.add_subtidal_flow_limiter
  *                                                         ocsmesh/hfun/raster.py:1396-1435

@@ -82,6 +82,8 @@ SIGNATURES = {
                                   c_f64, c_f64, c_i32, c_vp, c_vp]),
     "ocsb_nearest_vertex": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64,
                                     c_vp, c_vp]),
+    "ocsb_nearest_vertex_static": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64,
+                                           c_vp, c_vp]),
     "ocsb_hfun_flow_limiter": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i32,
                                        c_i64, c_vp, c_i64, c_vp, c_i64,
                                        c_f64, c_f64, c_f64, c_f64, c_f64,
@@ -327,6 +329,13 @@ class Context:
 
     def nearest_vertex(self, verts, nv, query, nq, r, dist_out, idx_out):
         check(self.lib.ocsb_nearest_vertex(
+            self.handle, ptr(verts), int(nv), ptr(query), int(nq), opt(r),
+            ptr(dist_out), ptr(idx_out)))
+
+    def nearest_vertex_static(self, verts, nv, query, nq, r, dist_out, idx_out):
+        """ocsb_nearest_vertex without any allocation (device buffers only,
+        nv <= OCSB_STATIC_MAX_VERTS; calls share one fixed device array)."""
+        check(self.lib.ocsb_nearest_vertex_static(
             self.handle, ptr(verts), int(nv), ptr(query), int(nq), opt(r),
             ptr(dist_out), ptr(idx_out)))
 

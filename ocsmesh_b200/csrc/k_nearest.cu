@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cmath>
 #include <limits>
+#include <mutex>
 
 namespace {
 
@@ -251,5 +252,152 @@ int32_t k_nearest_vertex(ocsb_ctx *ctx, const double *verts, int64_t nv,
         v2, nv, G, start, ids, reinterpret_cast<const double2 *>(q), nq, r2, dist, idx);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
+    return OCSB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// ocsb_nearest_vertex_static: the same query with NO allocation of any kind.
+// No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+// loops, harnesses that forbid it).
+//
+// The vertex grid (bounding-box keys, cell counts, cell starts, cursors, sorted
+// ids) lives in ONE file-scope device array of fixed size; every GPU that loads
+// the library holds these ~4 MiB until the process exits.  All calls share the
+// array and it keeps the last call's contents: what must start at zero (the
+// bounding-box keys, the cell counts) is cleared by every call, and two calls
+// that overlap on the GPU (different streams, different contexts on one device)
+// race on it -- serialise them.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr int64_t kStaticMaxVerts = OCSB_STATIC_MAX_VERTS;     // vertices per call
+constexpr int kStaticMaxCells = 262144;         // grid cells per call
+// layout in ints: [bb: 4 x int64, padded to 256 B][cnt][start (+1, padded)][cursor][ids]
+constexpr size_t kStOffCnt = 64;
+constexpr size_t kStOffStart = kStOffCnt + (size_t)kStaticMaxCells;
+constexpr size_t kStOffCursor = kStOffStart + (size_t)kStaticMaxCells + 64;
+constexpr size_t kStOffIds = kStOffCursor + (size_t)kStaticMaxCells;
+constexpr size_t kStaticInts = kStOffIds + (size_t)kStaticMaxVerts;
+
+static __device__ __align__(256) int g_nn_static[kStaticInts];
+
+// In host code `g_nn_static` is only a stand-in for the symbol, not a device
+// address: the address is asked for once per device, with that device current.
+constexpr int kStaticMaxDev = 64;
+int *g_nn_static_ptr[kStaticMaxDev] = {};
+std::mutex g_nn_static_mu;
+
+int32_t nn_static_scratch(int device, int **out) {
+    OCSB_REQUIRE(device >= 0 && device < kStaticMaxDev,
+                 "ocsb_nearest_vertex_static: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_nn_static_mu);
+    if (!g_nn_static_ptr[device]) {
+        void *p = nullptr;
+        OCSB_CUDA(cudaGetSymbolAddress(&p, g_nn_static));
+        OCSB_REQUIRE(p != nullptr, "ocsb_nearest_vertex_static: no address for the scratch array");
+        g_nn_static_ptr[device] = static_cast<int *>(p);
+    }
+    *out = g_nn_static_ptr[device];
+    return OCSB_OK;
+}
+
+// bounding-box keys back to the identities of min / max (device code may name
+// the array directly)
+__global__ void nn_static_init_kernel() {
+    long long *k = reinterpret_cast<long long *>(g_nn_static);
+    const long long kmax = 0x7ff0000000000000LL, kmin = -0x7ff0000000000000LL;
+    if (threadIdx.x < 4) k[threadIdx.x] = threadIdx.x < 2 ? kmax : kmin;
+}
+
+}  // namespace
+
+extern "C" int32_t ocsb_nearest_vertex_static(ocsb_ctx *ctx, const double *verts_xy,
+                                              int64_t nv, const double *query_xy,
+                                              int64_t nq, double r, double *dist_out,
+                                              int64_t *idx_out) {
+    const char *who = "ocsb_nearest_vertex_static";
+    OCSB_REQUIRE(ctx != nullptr, "%s: ctx is NULL", who);
+    OCSB_CUDA(cudaSetDevice(ctx->device));
+    OCSB_REQUIRE(verts_xy && nv > 0, "%s: empty vertex set", who);
+    OCSB_REQUIRE(nv <= kStaticMaxVerts,
+                 "%s: %lld vertices exceed the fixed scratch array (at most %lld); "
+                 "use ocsb_nearest_vertex",
+                 who, (long long)nv, (long long)kStaticMaxVerts);
+    OCSB_REQUIRE(nq >= 0, "%s: negative nq", who);
+    if (nq == 0) return OCSB_OK;
+    OCSB_REQUIRE(query_xy && (dist_out || idx_out), "%s: NULL buffers", who);
+    // nothing is staged here: staging would allocate
+    OCSB_REQUIRE(ocsb_is_device_ptr(verts_xy) && ocsb_is_device_ptr(query_xy) &&
+                     (!dist_out || ocsb_is_device_ptr(dist_out)) &&
+                     (!idx_out || ocsb_is_device_ptr(idx_out)),
+                 "%s: inputs and outputs must be device memory (this entry point "
+                 "allocates no staging buffers)", who);
+    OCSB_REQUIRE((((uintptr_t)verts_xy | (uintptr_t)query_xy) & 15) == 0,
+                 "%s: coordinate arrays must be 16-byte aligned", who);
+    int *scr = nullptr;
+    OCSB_TRY(nn_static_scratch(ctx->device, &scr));
+    double *bb = reinterpret_cast<double *>(scr);
+    int *cnt = scr + kStOffCnt, *start = scr + kStOffStart;
+    int *cursor = scr + kStOffCursor, *ids = scr + kStOffIds;
+
+    const double inf = std::numeric_limits<double>::infinity();
+    const double rr = ocsb_is_none(r) ? inf : r;
+    const double r2 = rr < inf ? (rr > 0 ? rr * rr : -1.0) : inf;
+    const double2 *v2 = reinterpret_cast<const double2 *>(verts_xy);
+    const int sweep = ctx->num_sms * 8;
+    const int vgrid = (int)std::min<int64_t>(sweep, (nv + 255) / 256);
+
+    nn_static_init_kernel<<<1, 32, 0, ctx->stream>>>();
+    OCSB_LAUNCHED(ctx);
+    bbox_kernel<<<vgrid, 256, 0, ctx->stream>>>(v2, nv, bb);
+    OCSB_LAUNCHED(ctx);
+    OCSB_CHECK_LAUNCH();
+    long long keys[4];
+    OCSB_CUDA(cudaMemcpyAsync(keys, bb, sizeof(keys), cudaMemcpyDeviceToHost, ctx->stream));
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    double box[4];
+    for (int i = 0; i < 4; ++i) {
+        long long b = keys[i] >= 0 ? keys[i]
+                                   : (long long)(0x8000000000000000ull - (unsigned long long)keys[i]);
+        memcpy(&box[i], &b, 8);
+    }
+    OCSB_REQUIRE(std::isfinite(box[0]) && std::isfinite(box[1]) &&
+                     std::isfinite(box[2]) && std::isfinite(box[3]),
+                 "%s: non-finite vertex coordinates", who);
+    // ~2 vertices per cell, at most 2048 cells per axis, and never more cells
+    // than the array holds (the grid only orders the search: results do not
+    // depend on it)
+    NGrid G;
+    const double wx = box[2] - box[0], wy = box[3] - box[1];
+    const double ncell_want = std::max<double>(1.0, (double)nv / 2.0);
+    double cell;
+    if (wx > 0 && wy > 0) cell = sqrt(wx * wy / ncell_want);
+    else cell = std::max(wx, wy) / ncell_want;
+    if (!(cell > 0)) cell = 1.0;
+    cell = std::max(cell, std::max(wx, wy) / 2048.0);
+    for (int it = 0;; ++it) {
+        G.gx = (int)std::min(2048.0, floor(wx / cell) + 1.0);
+        G.gy = (int)std::min(2048.0, floor(wy / cell) + 1.0);
+        if ((int64_t)G.gx * G.gy <= kStaticMaxCells) break;
+        OCSB_REQUIRE(it < 64, "%s: vertex grid does not fit the scratch array", who);
+        cell *= 1.25;
+    }
+    G.x0 = box[0]; G.y0 = box[1]; G.cell = cell; G.inv = 1.0 / cell;
+    const int ncell = G.gx * G.gy;
+    OCSB_CUDA(cudaMemsetAsync(cnt, 0, (size_t)ncell * sizeof(int), ctx->stream));
+    cell_hist_kernel<<<vgrid, 256, 0, ctx->stream>>>(v2, nv, G, cnt);
+    OCSB_LAUNCHED(ctx);
+    cell_scan_kernel<<<1, 1024, 0, ctx->stream>>>(cnt, start, cursor, ncell);
+    OCSB_LAUNCHED(ctx);
+    cell_scatter_kernel<<<vgrid, 256, 0, ctx->stream>>>(v2, nv, G, cursor, ids);
+    OCSB_LAUNCHED(ctx);
+    query_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, ctx->stream>>>(
+        v2, nv, G, start, ids, reinterpret_cast<const double2 *>(query_xy), nq, r2,
+        dist_out, idx_out);
+    OCSB_LAUNCHED(ctx);
+    OCSB_CHECK_LAUNCH();
+    // device buffers: stream-ordered like the other entry points (the one host
+    // wait above is for the bounding box, as in ocsb_nearest_vertex)
     return OCSB_OK;
 }
