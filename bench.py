@@ -401,6 +401,9 @@ def time_steps(fn, n, dev, world):
     for _ in range(n):
         fn()
     e1.record()
+    # host time to enqueue the steps: if it is close to the device time the
+    # launches, not the kernels, set the pace
+    time_steps.host_ms = (time.perf_counter() - t0) * 1e3 / n
     barrier()
     t1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
@@ -442,6 +445,7 @@ def run_ours(args, rank, world, local_rank):
     ctx.set_timing(True)
     launches0 = ctx.launch_count
     ms_step, t0, t1 = time_steps(run.step, args.steps, dev, world)
+    host_ms_step = time_steps.host_ms
     ctx.set_timing(False)
     clocks = sampler.stop(t0, t1)
     launches = ctx.launch_count - launches0
@@ -450,7 +454,7 @@ def run_ours(args, rank, world, local_rank):
     px_rank = float(run.b1 - run.b0) * W
     value = px_total / (ms_step * 1e-3) / 1e6
 
-    note(f"timed: {ms_step:.4f} ms per step")
+    note(f"timed: {ms_step:.4f} ms per step (host enqueue {host_ms_step:.4f} ms per step)")
     # ---- parity at this rank count (outside the timed region) ---------------
     parity = None
     if not args.no_parity:
@@ -549,6 +553,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "parity_checked": bool(parity and parity["ok"]), "parity": parity,
             "gpu_launches": int(launches), "clocks": clocks,
+            "host_enqueue_ms_per_step": round(host_ms_step, 4),
             "secondary": secondary,
         }
         print(json.dumps(line), flush=True)

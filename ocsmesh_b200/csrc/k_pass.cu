@@ -262,6 +262,55 @@ __device__ __forceinline__ void dom_step(const Rect &q, bool valid, double2 v,
     }
 }
 
+// The same search for LONG candidate runs: every lane keeps the minima of its
+// own candidates (no warp reduction per 32 candidates -- that reduction is two
+// thirds of dom_step's instructions) and the warp reduces once at the end.
+// Which of several equally near vertices becomes a dominator may differ from
+// dom_step; any vertex is a valid dominator, the lists stay supersets of the
+// nearest vertices and the sizes do not change.
+struct DomAcc {
+    unsigned key[5];
+    int idx[5];
+};
+
+__device__ __forceinline__ void dom_acc_init(DomAcc &a) {
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { a.key[j] = 0xffffffffu; a.idx[j] = 0; }
+}
+
+__device__ __forceinline__ void dom_acc_step(const Rect &q, double2 v, int i, DomAcc &a) {
+    const CornerD2 c = corner_d2(q, v);
+    const double dd[5] = {center_d2(q, v), c.d00, c.d01, c.d10, c.d11};
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const unsigned k = __float_as_uint((float)dd[j]);
+        if (k < a.key[j]) { a.key[j] = k; a.idx[j] = i; }
+    }
+}
+
+// warp-level end of a run: key[] / tab as dom_step leaves them; fetch(i) returns
+// candidate i of the run again
+template <class Fetch>
+__device__ __forceinline__ void dom_acc_finish(const Rect &q, const DomAcc &a, unsigned key[5],
+                                               DomTable &tab, int lane, Fetch fetch) {
+    unsigned m[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) m[j] = __reduce_min_sync(0xffffffffu, a.key[j]);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        if (m[j] < key[j]) {   // warp-uniform
+            key[j] = m[j];
+            const int src = __ffs(__ballot_sync(0xffffffffu, a.key[j] == m[j])) - 1;
+            if (lane == src) {
+                const CornerD2 c = corner_d2(q, fetch(a.idx[j]));
+                const double mg = 1.0 + kDomEps;
+                tab.c[j][0] = c.d00 * mg; tab.c[j][1] = c.d01 * mg;
+                tab.c[j][2] = c.d10 * mg; tab.c[j][3] = c.d11 * mg;
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ bool dominated_tab(const DomTable &D, const CornerD2 &v) {
     bool dom = false;
 #pragma unroll
@@ -339,7 +388,10 @@ struct Collect {
 // ---------------------------------------------------------------------------
 // level 2: 1024-px tiles from the vertex grid
 // ---------------------------------------------------------------------------
-constexpr int kRootThreads = 256;
+#ifndef OCSB_ROOT_THREADS
+#define OCSB_ROOT_THREADS 256
+#endif
+constexpr int kRootThreads = OCSB_ROOT_THREADS;
 constexpr int kRootCap = 2048;
 
 __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
@@ -379,6 +431,8 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
     for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
     const int kmax = max(max(ccx, NX - 1 - ccx), max(ccy, NY - 1 - ccy));
     bool found = false;
+    DomAcc acc;
+    dom_acc_init(acc);
     for (int k = 0; k <= kmax; ++k) {
         // cells of Chebyshev ring k, as contiguous slices of the sorted array
         const int j0 = max(0, ccy - k), j1 = min(NY - 1, ccy + k);
@@ -392,15 +446,11 @@ __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
                     if (i0 < 0 || i0 > NX - 1) continue;
                 }
                 const int lo = G.start[j * NX + i0], hi = G.start[j * NX + i1 + 1];
-                for (int b0 = lo + wid * 32; b0 < hi; b0 += kRootThreads) {
-                    const int i = b0 + lane;
-                    const bool valid = i < hi;
-                    double2 v = make_double2(0.0, 0.0);
-                    if (valid) v = G.sv[i];
-                    dom_step(q, valid, v, key, s_tab[wid], lane);
-                }
+                for (int i = lo + (int)threadIdx.x; i < hi; i += kRootThreads)
+                    dom_acc_step(q, G.sv[i], i, acc);
             }
         }
+        dom_acc_finish(q, acc, key, s_tab[wid], lane, [&](int i) { return G.sv[i]; });
         __syncwarp();
         dom_combine<NW>(key, s_key, s_tab, &s_fin, &s_key0);
         const unsigned k0 = s_key0;
@@ -1551,7 +1601,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 L.sticky = sticky;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 L.n_parents = (int)n1;
-                l10_kernel<<<(unsigned)n1, 256, 0, ctx->stream>>>(L);
+                l10_kernel<<<(unsigned)n1, kL10Threads, 0, ctx->stream>>>(L);
                 OCSB_LAUNCHED(ctx);
                 OCSB_CHECK_LAUNCH();
             }

@@ -508,10 +508,14 @@ struct L0Args {
     int *sticky;
 };
 
+#ifndef OCSB_L10_THREADS
+#define OCSB_L10_THREADS 256
+#endif
+constexpr int kL10Threads = OCSB_L10_THREADS;
 constexpr int kL0Stage = 1024;       // tile candidates held in shared memory
 
-__global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
-    constexpr int NW = 8;
+__global__ void __launch_bounds__(kL10Threads) l10_kernel(L0Args A) {
+    constexpr int NW = kL10Threads / 32;
     __shared__ unsigned s_key[NW][5];
     __shared__ DomTable s_tab[NW];
     __shared__ DomTable s_fin;
@@ -550,17 +554,17 @@ __global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
         unsigned key[5];
 #pragma unroll
         for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
-        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
-            const int i = b0 + lane;
-            const bool valid = i < pcnt2;
-            double2 v = make_double2(0.0, 0.0);
-            if (valid) v = src2[i];
-            dom_step(q, valid, v, key, s_tab[wid], lane);
+        {
+            DomAcc acc;
+            dom_acc_init(acc);
+            for (int i = threadIdx.x; i < pcnt2; i += kL10Threads)
+                dom_acc_step(q, src2[i], i, acc);
+            dom_acc_finish(q, acc, key, s_tab[wid], lane, [&](int i) { return src2[i]; });
         }
         __syncwarp();
         if (threadIdx.x == 0) s_cnt = 0;
         dom_combine<NW>(key, s_key, s_tab, &s_fin, &s_key0);
-        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
+        for (int b0 = wid * 32; b0 < pcnt2; b0 += kL10Threads) {
             const int i = b0 + lane;
             const bool valid = i < pcnt2;
             double2 v = make_double2(0.0, 0.0);
@@ -592,7 +596,7 @@ __global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
         if (s_base == ~0ull) return;
         const int c0 = tx1 * kT1, r0 = ty1 * kT1;
         const Rect q = win_rect(W, c0, min(bw, c0 + kT1) - 1, r0, min(bh, r0 + kT1) - 1);
-        for (int b0 = wid * 32; b0 < pcnt2; b0 += 256) {
+        for (int b0 = wid * 32; b0 < pcnt2; b0 += kL10Threads) {
             const int i = b0 + lane;
             const bool valid = i < pcnt2;
             double2 v = make_double2(0.0, 0.0);
@@ -611,7 +615,7 @@ __global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
     const int nsrc = pcnt;
     DomTable &tab = s_tab[wid];
     __syncthreads();        // s_tab[] is reused per warp below
-    for (int child = wid; child < 16; child += 8) {
+    for (int child = wid; child < 16; child += NW) {
         const int cx = child & 3, cy = child >> 2;
         if (cx >= ncx || cy >= ncy) continue;           // warp-uniform
         const int tx = 4 * tx1 + cx, ty = 4 * ty1 + cy;
@@ -622,12 +626,11 @@ __global__ void __launch_bounds__(256) l10_kernel(L0Args A) {
         unsigned key[5];
 #pragma unroll
         for (int j = 0; j < 5; ++j) key[j] = 0xffffffffu;
-        for (int b0 = 0; b0 < nsrc; b0 += 32) {
-            const int i = b0 + lane;
-            const bool valid = i < nsrc;
-            double2 v = make_double2(0.0, 0.0);
-            if (valid) v = src[i];
-            dom_step(q, valid, v, key, tab, lane);
+        {
+            DomAcc acc;
+            dom_acc_init(acc);
+            for (int i = lane; i < nsrc; i += 32) dom_acc_step(q, src[i], i, acc);
+            dom_acc_finish(q, acc, key, tab, lane, [&](int i) { return src[i]; });
         }
         __syncwarp();
         int total = 0;
