@@ -460,6 +460,32 @@ int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
                                  const double *xy, int64_t K,
                                  double *values_out);
 
+/* ---- 8(f) next-4: nearest warp onto the "fast" collector's big raster ---------
+ * HfunCollector._create_big_raster -> rasterio.warp.reproject(source,
+ * destination, resampling=Resampling.nearest, init_dest_nodata=False)
+ *                                           ocsmesh/hfun/collector.py:2419-2438
+ * for two north-up rasters of the SAME projected CRS (the geographic / UTM
+ * reprojection branch is out of scope with the rest of the pyproj paths).
+ * Rule (restated from GDAL's nearest warp kernel; GDAL is absent here, parity
+ * UNPINNED): the centre of destination pixel (r, c) is mapped through the two
+ * affine transforms to source pixel coordinates (u, v); the pixel takes
+ * float32(src[floor(v + 1e-10), floor(u + 1e-10)]) when that lies inside the
+ * source and is not masked, and is left untouched otherwise.
+ *   src            : source band (OCSB_F32 / OCSB_F64), src_stride elements per row
+ *   src_transform  : affine (a, b, c, d, e, f): x = a*col + c, y = e*row + f; b = d = 0
+ *                    (host array of 6 doubles, like dst_transform)
+ *   src_mask       : optional uint8 nodata mask of the source (non-zero = nodata)
+ *   dst            : float32 destination, updated in place
+ * Host or device pointers.                                                      */
+int32_t ocsb_resample_nearest(ocsb_ctx *ctx,
+                              const void *src, int32_t src_dtype, int64_t src_stride,
+                              int32_t src_width, int32_t src_height,
+                              const double *src_transform,
+                              const uint8_t *src_mask, int64_t mask_stride,
+                              float *dst, int64_t dst_stride,
+                              int32_t dst_width, int32_t dst_height,
+                              const double *dst_transform);
+
 /* ---- A4 + A6..A10 as ONE streamed pass --------------------------------------
  * The reference applies every add_* to the whole raster before the next one
  * starts, rewriting a GeoTIFF each time (ocsmesh/hfun/raster.py:1257-1260,

@@ -132,6 +132,8 @@ SIGNATURES = {
                                         c_i32, c_f64, c_f64, c_vp, c_vp]),
     "ocsb_hfun_sample_nearest": (c_i32, [c_vp, C.POINTER(ocsb_win), c_vp, c_i64,
                                          c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
+    "ocsb_resample_nearest": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_i32, c_i32, c_vp, c_vp,
+                                      c_i64, c_vp, c_i64, c_i32, c_i32, c_vp]),
     "ocsb_stitch_segments": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64,
                                      C.POINTER(c_i64), C.POINTER(c_i64)]),
     "ocsb_feature_points": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i64,
@@ -536,6 +538,18 @@ class Context:
         check(self.lib.ocsb_hfun_sample_nearest(
             self.handle, C.byref(win), ptr(hfun), int(hfun_stride), int(stride),
             opt(hmin), opt(hmax), ptr(xy), int(K), ptr(values_out)))
+
+    def resample_nearest(self, src, src_dtype, src_stride, src_w, src_h, src_transform,
+                         src_mask, mask_stride, dst, dst_stride, dst_w, dst_h,
+                         dst_transform):
+        """Nearest warp of a north-up raster onto another of the same CRS
+        (transforms: affine six-tuples ``(a, b, c, d, e, f)``)."""
+        sgt = (c_f64 * 6)(*[float(v) for v in tuple(src_transform)[:6]])
+        dgt = (c_f64 * 6)(*[float(v) for v in tuple(dst_transform)[:6]])
+        check(self.lib.ocsb_resample_nearest(
+            self.handle, ptr(src), int(src_dtype), int(src_stride), int(src_w),
+            int(src_h), C.cast(sgt, c_vp), ptr(src_mask), int(mask_stride), ptr(dst),
+            int(dst_stride), int(dst_w), int(dst_h), C.cast(dgt, c_vp)))
 
     def min_combine(self, dst, dst_stride, src, src_stride, width, height):
         check(self.lib.ocsb_min_combine(self.handle, ptr(dst), int(dst_stride),

@@ -31,6 +31,7 @@ SOURCES = [
     "k_pass.cu",
     "k_nearest.cu",
     "k_constraint.cu",
+    "k_warp.cu",
     "k_contour.cu",
     "k_stitch.cu",
     "k_region.cu",

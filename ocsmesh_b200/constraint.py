@@ -114,9 +114,17 @@ class TopoConstConstraint(Constraint):
     def __init__(self, value, upper_bound=np.inf, lower_bound=-np.inf,
                  value_type: str = 'min', rate=None):
         super().__init__(value_type, rate)
+        # ``return_values[mask] = self.value`` (features/constraint.py:171):
+        # numpy only takes a scalar or a one-element array there -- a full
+        # (h, w) matrix fails with "boolean array indexing assignment cannot
+        # assign ..." unless its size happens to equal the mask count
         if np.ndim(value) != 0:
-            raise NotImplementedError(
-                "matrix-valued TopoConstConstraint is outside this build")
+            if np.size(value) != 1:
+                raise ValueError(
+                    "NumPy boolean array indexing assignment cannot assign "
+                    f"{np.size(value)} input values to the output values where "
+                    "the mask is true: TopoConstConstraint takes a scalar value")
+            value = np.asarray(value).reshape(()).item()
         self._lb = lower_bound
         self._ub = upper_bound
         self._val = value

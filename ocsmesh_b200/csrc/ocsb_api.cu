@@ -1217,6 +1217,41 @@ extern "C" int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
 }
 
 // ---------------------------------------------------------------------------
+// next-4: nearest warp onto the fast collector's big raster
+// ---------------------------------------------------------------------------
+extern "C" int32_t ocsb_resample_nearest(
+    ocsb_ctx *ctx, const void *src, int32_t src_dtype, int64_t src_stride, int32_t src_width,
+    int32_t src_height, const double *src_transform, const uint8_t *src_mask,
+    int64_t mask_stride, float *dst, int64_t dst_stride, int32_t dst_width,
+    int32_t dst_height, const double *dst_transform) {
+    CTX_ENTER("ocsb_resample_nearest");
+    OCSB_REQUIRE(src_dtype == OCSB_F32 || src_dtype == OCSB_F64,
+                 "ocsb_resample_nearest: unsupported source dtype %d", src_dtype);
+    OCSB_REQUIRE(src && dst && src_transform && dst_transform && src_width > 0 &&
+                     src_height > 0 && dst_width > 0 && dst_height > 0 &&
+                     src_stride >= src_width && dst_stride >= dst_width &&
+                     (!src_mask || mask_stride >= src_width),
+                 "ocsb_resample_nearest: bad buffers");
+    for (const double *t : {src_transform, dst_transform}) {
+        OCSB_REQUIRE(t[1] == 0.0 && t[3] == 0.0,
+                     "ocsb_resample_nearest: rotated / sheared rasters are not supported");
+        OCSB_REQUIRE(t[0] != 0.0 && t[4] != 0.0 && std::isfinite(t[0]) &&
+                         std::isfinite(t[4]) && std::isfinite(t[2]) && std::isfinite(t[5]),
+                     "ocsb_resample_nearest: degenerate transform");
+    }
+    const int es = src_dtype == OCSB_F32 ? 4 : 8;
+    Staged ss, sm, sd;
+    OCSB_TRY(ss.init(ctx, src, src_height, src_width, src_stride, es, STAGE_IN));
+    OCSB_TRY(sm.init(ctx, src_mask, src_height, src_width, mask_stride, 1, STAGE_IN));
+    OCSB_TRY(sd.init(ctx, dst, dst_height, dst_width, dst_stride, 4, STAGE_INOUT));
+    OCSB_TRY(k_warp_nearest(ctx, ss.dev, src_dtype, ss.dev_stride, src_width, src_height,
+                            src_transform, (const uint8_t *)sm.dev, sm.dev_stride,
+                            (float *)sd.dev, sd.dev_stride, dst_width, dst_height,
+                            dst_transform));
+    return finish_call(ctx, {&ss, &sm, &sd});
+}
+
+// ---------------------------------------------------------------------------
 // A14 interpolate
 // ---------------------------------------------------------------------------
 extern "C" int32_t ocsb_spline_prefilter(ocsb_ctx *ctx, const ocsb_win *win,

@@ -371,6 +371,11 @@ int32_t k_sample_source(ocsb_ctx *ctx, LinAxis ax, LinAxis ay, const float *hfun
                         int64_t hs, int step, double hmin, double hmax,
                         double *coords, double *values);
 
+// k_warp.cu: nearest-neighbour warp between north-up rasters of one CRS
+int32_t k_warp_nearest(ocsb_ctx *ctx, const void *src, int src_dtype, int64_t ss, int sw,
+                       int sh, const double sgt[6], const uint8_t *mask, int64_t ms,
+                       float *dst, int64_t ds, int dw, int dh, const double dgt[6]);
+
 // k_contour.cu
 int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
                            int64_t zs, int w, int jb, int je, double level,

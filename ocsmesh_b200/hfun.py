@@ -1122,18 +1122,31 @@ def overlap_windows(geom_a, geom_b, tol: float = 1e-6):
 
 
 class HfunCollector:
-    """Minimal multi-raster size function: one ``HfunRaster`` per input
-    raster, every ``add_*`` applied to every raster -- the call order of the
-    reference's exact collector (``ocsmesh/hfun/collector.py:1536-1563,
-    1590-1655``): every contour of every raster goes to every hfun."""
+    """Multi-raster size function (``ocsmesh/hfun/collector.py:736-884``).
+
+    ``method='exact'``: one ``HfunRaster`` per input raster, every ``add_*``
+    applied to every raster -- the call order of the reference's exact
+    collector (``collector.py:1536-1563, 1590-1655``): every contour of every
+    raster goes to every hfun.
+
+    ``method='fast'`` (``collector.py:2296-2571``): the ``add_*`` calls are
+    only recorded; :meth:`apply` builds ONE lower-resolution raster covering
+    all inputs (``_create_big_raster``: -99999 everywhere, then the inputs some
+    limiter / constant value / constraint refers to are warped onto it with
+    nearest resampling, the last input winning on overlaps) and applies
+    everything to a single ``HfunRaster`` on it (``_apply_features_fast``).
+    Contours are still extracted from the INPUT rasters at their own
+    resolution.  All rasters must share one projected CRS: the reference's
+    EPSG:4326 -> UTM step is then the identity (the pyproj branch is out of
+    scope like everywhere else on this path)."""
 
     def __init__(self, in_list, base_mesh=None, hmin=None, hmax=None,
                  nprocs=None, verbosity=0, method='exact', base_as_hfun=True,
                  base_shape=None, base_shape_crs=None):
-        del base_mesh, nprocs, base_as_hfun, base_shape, base_shape_crs
-        if method not in ('exact',):
-            raise NotImplementedError("only the 'exact' collector method is "
-                                      "part of the accelerated path")
+        del base_mesh, base_as_hfun, base_shape, base_shape_crs
+        if method not in ('exact', 'fast'):
+            raise ValueError(f"Invalid method specified <{method}>")
+        self._method = method
         self._hfuns = []
         for r in in_list:
             if isinstance(r, HfunRaster):
@@ -1143,14 +1156,48 @@ class HfunCollector:
             else:
                 raise TypeError(f"unsupported collector input {type(r)}")
         self._hmin, self._hmax = hmin, hmax
+        self._verbosity = verbosity
+        # collector.py:868-870: nprocs None / -1 -> every core; it only enters
+        # the fast method's window-size rule here
+        self._nprocs = (os.cpu_count() or 1) if nprocs in (None, -1) else int(nprocs)
+        # fast method: recorded refinements, in call order per kind
+        self._contour_info = []      # (level, expansion_rate, target_size)
+        self._feature_info = []      # (feature, expansion_rate, target_size, max_verts)
+        self._patch_info = []        # (shape, expansion_rate, target_size)
+        self._flow_lim_info = []     # (src_idx, hmin, hmax, upper_bound, lower_bound)
+        self._const_val_info = []    # (src_idx, lower_bound, upper_bound, value)
+        self._constraint_info = []   # (src_idx, method name, args, kwargs)
+        self._applied = False
+        self._big_hfun = None
+        self._big_device = None
 
     @property
     def hfuns(self):
         return self._hfuns
 
-    def add_contour(self, level, expansion_rate, target_size=None, **_kw):
-        if not isinstance(level, list):
+    @property
+    def method(self):
+        return self._method
+
+    @staticmethod
+    def _src_idx(source_index):
+        if source_index is not None and not isinstance(source_index, (tuple, list)):
+            source_index = [source_index]
+        return source_index
+
+    def _fast(self) -> bool:
+        if self._method == 'fast':
+            self._applied = False
+            return True
+        return False
+
+    def add_contour(self, level=None, expansion_rate=0.01, target_size=None, **_kw):
+        if not isinstance(level, (list, tuple)):
             level = [level]
+        if self._fast():
+            for lv in level:
+                self._contour_info.append((lv, expansion_rate, target_size))
+            return
         contours = []
         for h in self._hfuns:
             for lv in level:
@@ -1162,17 +1209,219 @@ class HfunCollector:
 
     def add_feature(self, feature, expansion_rate, target_size=None,
                     max_verts=200, **_kw):
+        if self._fast():
+            self._feature_info.append((feature, expansion_rate, target_size, max_verts))
+            return
         for h in self._hfuns:
             h.add_feature(feature, expansion_rate, target_size, max_verts)
 
+    def add_patch(self, shape=None, expansion_rate=None, target_size=None, **_kw):
+        if self._fast():
+            self._patch_info.append((shape, expansion_rate, target_size))
+            return
+        for h in self._hfuns:
+            h.add_patch(shape, expansion_rate, target_size)
+
     def add_subtidal_flow_limiter(self, hmin=None, hmax=None,
-                                  lower_bound=None, upper_bound=None, **_kw):
+                                  lower_bound=None, upper_bound=None,
+                                  source_index=None, **_kw):
+        if self._fast():
+            self._flow_lim_info.append((self._src_idx(source_index), hmin, hmax,
+                                        upper_bound, lower_bound))
+            return
         for h in self._hfuns:
             h.add_subtidal_flow_limiter(hmin, hmax, lower_bound, upper_bound)
 
-    def add_gradient_delimiter(self, hmin=None, hmax=None, **_kw):
+    def add_gradient_delimiter(self, hmin=None, hmax=None, source_index=None, **_kw):
+        if self._fast():
+            self._flow_lim_info.append((self._src_idx(source_index), hmin, hmax,
+                                        None, None))
+            return
         for h in self._hfuns:
             h.add_gradient_delimiter(hmin=hmin, hmax=hmax)
+
+    def add_constant_value(self, value, lower_bound=None, upper_bound=None,
+                           source_index=None):
+        """``collector.py:1346-1389``."""
+        if self._fast():
+            self._const_val_info.append((self._src_idx(source_index), lower_bound,
+                                         upper_bound, value))
+            return
+        for h in self._hfuns:
+            h.add_constant_value(value, lower_bound, upper_bound)
+
+    def _add_constraint(self, name, source_index, *args, **kwargs):
+        if self._fast():
+            self._constraint_info.append((self._src_idx(source_index), name, args, kwargs))
+            return
+        for h in self._hfuns:
+            getattr(h, name)(*args, **kwargs)
+
+    def add_topo_bound_constraint(self, value, upper_bound=np.inf, lower_bound=-np.inf,
+                                  value_type='min', rate=0.01, source_index=None):
+        """``collector.py:930-984``."""
+        self._add_constraint('add_topo_bound_constraint', source_index, value,
+                             upper_bound, lower_bound, value_type, rate)
+
+    def add_topo_func_constraint(self, func=lambda i: i / 2.0, upper_bound=np.inf,
+                                 lower_bound=-np.inf, value_type='min', rate=0.01,
+                                 source_index=None):
+        """``collector.py:986-1041``."""
+        self._add_constraint('add_topo_func_constraint', source_index, func,
+                             upper_bound, lower_bound, value_type, rate)
+
+    def add_courant_num_constraint(self, upper_bound=0.9, lower_bound=None,
+                                   timestep=150, wave_amplitude=2, source_index=None):
+        """``collector.py:1043-1104``."""
+        self._add_constraint('add_courant_num_constraint', source_index, upper_bound,
+                             lower_bound, timestep, wave_amplitude)
+
+    def add_region_constraint(self, value, shape, crs=None, value_type='min',
+                              rate=0.01, source_index=None):
+        """``collector.py:1106-1155``."""
+        self._add_constraint('add_region_constraint', source_index, value, shape, crs,
+                             value_type, rate)
+
+    # ---- the fast method (8f next-4) -----------------------------------------
+    def _big_raster_geometry(self):
+        """``collector.py:2318-2400`` for rasters of one projected CRS (the
+        4326 -> UTM transformer is the identity, ``ratio`` is 1): ``(transform,
+        width, height, window_size)``."""
+        from .raster import Affine, array_bounds
+        all_bounds = []
+        n_cell_lim = 0
+        for h in self._hfuns:
+            shape = h.raster.src.shape
+            n_cell_lim = max(shape[0] * shape[1], n_cell_lim)
+            all_bounds.append(array_bounds(shape[0], shape[1], h.raster.src.transform))
+        # 3 is the reference's arbitrary tolerance for its memory limit
+        n_cell_lim = n_cell_lim * self._nprocs / 3
+        all_bounds = np.array(all_bounds)
+        x0, y0 = np.min(all_bounds[:, [0, 1]], axis=0)
+        x1, y1 = np.max(all_bounds[:, [2, 3]], axis=0)
+        worst_res = 0
+        for h in self._hfuns:
+            t = h.raster.src.transform
+            worst_res = np.max([worst_res, t[0] * 1.0, -t[4] * 1.0])
+        # reference TODO (``:2362``): without a global hmin the worst source
+        # resolution is used
+        res = worst_res if self._hmin is None else np.max([self._hmin / 2, worst_res])
+        shape0 = int(np.ceil(abs(x1 - x0) / res))
+        shape1 = int(np.ceil(abs(y1 - y0) / res))
+        approx = int(np.sqrt(n_cell_lim))
+        window_size = None
+        if approx < max(shape0, shape1):
+            window_size = int(np.min([shape0, shape1, approx]))
+        transform = Affine(float(res), 0.0, float(x0 - res / 2), 0.0, -float(res),
+                           float(y1 + res / 2))
+        return transform, shape0, shape1, window_size
+
+    def _needs_warp(self, in_idx: int) -> bool:
+        """``collector.py:2410-2426``: an input is only warped onto the big
+        raster when a constant value, limiter or constraint refers to it."""
+        for coll in (self._const_val_info, self._flow_lim_info, self._constraint_info):
+            for entry in coll:
+                if entry[0] is None or in_idx in entry[0]:
+                    return True
+        return False
+
+    def _create_big_raster(self, out_path=None, device=None) -> Optional[Raster]:
+        """``collector.py:2296-2442``.  The big raster is built in device
+        memory (fill + one nearest-warp launch per input,
+        ``ocsb_resample_nearest``) and stays resident as the DEM of the hfun
+        built on it; ``out_path``, when given, also receives it as
+        ``big_raster.tif`` like the reference's temporary directory."""
+        import torch
+        if not self._hfuns:
+            return None
+        crs0 = self._hfuns[0].crs
+        for h in self._hfuns:
+            h._check_projected()
+            if not (h.crs == crs0):
+                raise NotImplementedError(
+                    "the fast collector needs all rasters in one projected CRS "
+                    "(reprojection is out of scope with the pyproj branch)")
+            t = h.raster.src.transform
+            if t[1] or t[3] or t[0] <= 0 or t[4] >= 0:
+                raise ValueError("the fast collector needs north-up rasters")
+        transform, width, height, window_size = self._big_raster_geometry()
+        dev = self._hfuns[0]._device if device is None else int(device)
+        ctx = _lib.default_context(dev)
+        with torch.cuda.device(dev):
+            z = torch.empty((height, width), dtype=torch.float32, device=f"cuda:{dev}")
+            # where no DEM is provided deep ocean is assumed (``:2394-2408``)
+            ctx.fill_f32(z, height * width, -99999.0)
+            for k, h in enumerate(self._hfuns):
+                if not self._needs_warp(k):
+                    continue
+                r = h.raster
+                if r.src.row_origin != 0 or r.src.full_height != r.src.bands.shape[1]:
+                    raise ValueError("the fast collector needs whole rasters, not bands")
+                src = r.device_band(1, dev)
+                mask = r.device_mask(1, dev)
+                # the last input implicitly has the highest priority (``:2427``)
+                ctx.resample_nearest(
+                    src, _dem_dtype_code(src), r.width, r.width, r.height,
+                    r.src.transform, mask, r.width, z, width, width, height, transform)
+            ctx.sync()
+            host = z.cpu().numpy()
+        big = Raster.from_numpy(host, transform, crs=crs0, chunk_size=window_size)
+        big.set_device_band(z, 0, device=dev)
+        self._big_device = dev
+        if out_path is not None:
+            big.save(pathlib.Path(out_path) / 'big_raster.tif')
+        return big
+
+    def _apply_features_fast(self, big_raster: Optional[Raster]) -> Optional[HfunRaster]:
+        """``collector.py:2444-2495`` (raster part): contours, flow limiters,
+        constant values, line features, patches, constraints -- in that order,
+        all on the one big raster."""
+        if big_raster is None:
+            return None
+        hfun_rast = HfunRaster(big_raster, hmin=self._hmin, hmax=self._hmax,
+                               verbosity=self._verbosity, device=self._big_device)
+        # contours come from the inputs at their own resolution (``:1620-1646``)
+        for level, rate, target in self._contour_info:
+            for h in self._hfuns:
+                lines = h.raster.get_contour(level)
+                if lines:
+                    hfun_rast.add_feature(lines, rate, target)
+        # ``_apply_flow_limiters_fast`` (``:2497-2530``)
+        for _src, hmin, hmax, zmax, zmin in self._flow_lim_info:
+            hmin = self._hmin if hmin is None else hmin
+            hmax = self._hmax if hmax is None else hmax
+            # no sharp gradient where no raster was projected
+            zmin = -99990 if zmin is None else max(zmin, -99990)
+            hfun_rast.add_subtidal_flow_limiter(hmin, hmax, zmin, zmax)
+        # ``_apply_const_val_fast`` (``:2532-2554``)
+        for _src, level0, level1, value in self._const_val_info:
+            if level0 is not None and np.isinf(level0):
+                level0 = None
+            if level1 is not None and np.isinf(level1):
+                level1 = None
+            hfun_rast.add_constant_value(value, level0, level1)
+        for feature, rate, target, max_verts in self._feature_info:
+            hfun_rast.add_feature(feature, rate, target, max_verts)
+        for shape, rate, target in self._patch_info:
+            hfun_rast.add_patch(shape, rate, target)
+        # ``_apply_constraints_fast`` (``:2557-2571``)
+        for _src, name, args, kwargs in self._constraint_info:
+            getattr(hfun_rast, name)(*args, **kwargs)
+        return hfun_rast
+
+    def apply(self, out_path=None) -> Optional[HfunRaster]:
+        """The raster half of ``msh_t()`` for the fast method
+        (``collector.py:814-884``): build the big raster, apply every recorded
+        refinement, return the ``HfunRaster`` (kept until the next ``add_*``).
+        Its :meth:`HfunRaster.sizing_source` / :meth:`HfunRaster.sample_nearest`
+        are the hand-over to the mesh engine."""
+        if self._method != 'fast':
+            raise ValueError("apply() belongs to the 'fast' method; the exact "
+                             "collector applies every add_* at once")
+        if not self._applied or self._big_hfun is None:
+            self._big_hfun = self._apply_features_fast(self._create_big_raster(out_path))
+            self._applied = True
+        return self._big_hfun
 
     def min_combine_overlaps(self) -> int:
         """Pixel-wise min over the co-registered overlaps of the member rasters

@@ -46,7 +46,8 @@ __all__ = [
     "OracleHfun", "marching_squares", "get_contour", "nearest_vertex",
     "min_combine", "apply_rate", "add_constant_value_window",
     "TopoConstConstraint", "TopoFuncConstraint", "CourantNumConstraint",
-    "msh_t_source", "interpolate_nearest",
+    "msh_t_source", "interpolate_nearest", "big_raster_geometry",
+    "resample_nearest", "create_big_raster",
 ]
 
 FLT_MAX = np.finfo(np.float32).max
@@ -1028,3 +1029,86 @@ def add_patch_window(old: np.ndarray, mask: np.ndarray, target_size, hmin, hmax)
     if hmax is not None:
         values[np.where(values > hmax)] = hmax
     return np.minimum(old, values)
+
+
+# --------------------------------------------------------------------------
+# 8(f) next-4: the "fast" collector's big raster
+# --------------------------------------------------------------------------
+def big_raster_geometry(rasters: Sequence[OracleRaster], hmin, nprocs: int):
+    """``HfunCollector._create_big_raster`` (hfun/collector.py:2318-2400) for
+    rasters that share ONE projected CRS: the EPSG:4326 -> UTM transformer of
+    the reference is then the identity, the densified bbox polygon keeps its
+    bounds (``:2341-2348``) and ``ratio`` is 1 (``:2352-2357``).  Returns
+    ``(transform, width, height, window_size)``; ``window_size`` is the
+    ``chunk_size`` the big ``Raster`` is opened with (``:2373-2378, 2442``)."""
+    all_bounds = []
+    n_cell_lim = 0
+    for r in rasters:
+        n_cell_lim = max(r.height * r.width, n_cell_lim)
+        all_bounds.append(array_bounds(r.height, r.width, r.transform))
+    n_cell_lim = n_cell_lim * nprocs / 3
+    all_bounds = np.array(all_bounds)
+    x0, y0 = np.min(all_bounds[:, [0, 1]], axis=0)
+    x1, y1 = np.max(all_bounds[:, [2, 3]], axis=0)
+    worst_res = 0
+    for r in rasters:
+        worst_res = np.max([worst_res, r.transform[0] * 1.0, -r.transform[4] * 1.0])
+    # the reference has a TODO for a missing global hmin (``:2362``); the build
+    # then uses the worst source resolution
+    res = worst_res if hmin is None else np.max([hmin / 2, worst_res])
+    shape0 = int(np.ceil(abs(x1 - x0) / res))
+    shape1 = int(np.ceil(abs(y1 - y0) / res))
+    approx = int(np.sqrt(n_cell_lim))
+    window_size = None
+    if approx < max(shape0, shape1):
+        window_size = int(np.min([shape0, shape1, approx]))
+    # rasterio.transform.from_origin(west, north, xsize, ysize)   (``:2383``)
+    transform = (float(res), 0.0, float(x0 - res / 2), 0.0, -float(res),
+                 float(y1 + res / 2))
+    return transform, shape0, shape1, window_size
+
+
+def resample_nearest(dst: np.ndarray, dst_transform, src: np.ndarray, src_transform,
+                     src_mask: Optional[np.ndarray] = None) -> None:
+    """``rasterio.warp.reproject(..., resampling=nearest, init_dest_nodata=
+    False)`` (hfun/collector.py:2431-2437) for north-up rasters of one CRS, in
+    place.  GDAL is a third-party dependency of rasterio that is absent here
+    (**parity unpinned**); the rule is restated from its nearest warp kernel:
+    destination pixel centre -> source pixel coordinates -> ``floor(u + 1e-10)``;
+    pixels outside the source or on source nodata keep their value."""
+    da, _, dc, _, de, df = [float(t) for t in tuple(dst_transform)[:6]]
+    sa, _, sc, _, se, sf = [float(t) for t in tuple(src_transform)[:6]]
+    h, w = dst.shape
+    X = dc + (np.arange(w, dtype=np.float64) + 0.5) * da
+    Y = df + (np.arange(h, dtype=np.float64) + 0.5) * de
+    u = np.floor((X - sc) / sa + 1e-10)
+    v = np.floor((Y - sf) / se + 1e-10)
+    cols = np.nonzero((u >= 0) & (u < src.shape[1]))[0]
+    rows = np.nonzero((v >= 0) & (v < src.shape[0]))[0]
+    if cols.size == 0 or rows.size == 0:
+        return
+    ui = u[cols].astype(np.int64)
+    vi = v[rows].astype(np.int64)
+    vals = src[np.ix_(vi, ui)].astype(np.float32)
+    sub = dst[np.ix_(rows, cols)]
+    if src_mask is not None:
+        keep = ~np.asarray(src_mask, dtype=bool)[np.ix_(vi, ui)]
+        sub[keep] = vals[keep]
+    else:
+        sub = vals
+    dst[np.ix_(rows, cols)] = sub
+
+
+def create_big_raster(rasters: Sequence[OracleRaster], hmin, nprocs: int,
+                      warp: Optional[Sequence[bool]] = None) -> OracleRaster:
+    """hfun/collector.py:2296-2442: -99999 everywhere ("deep ocean", ``:2396-
+    2408``), then the selected source rasters warped in list order, the last
+    one winning on overlaps (``:2427-2437``)."""
+    transform, width, height, window_size = big_raster_geometry(rasters, hmin, nprocs)
+    z = np.full((height, width), -99999, dtype=np.float32)
+    for k, r in enumerate(rasters):
+        if warp is not None and not warp[k]:
+            continue
+        resample_nearest(z, transform, r.bands[0], r.transform,
+                         None if r.mask is None else r.mask[0])
+    return OracleRaster(z, transform, chunk_size=window_size)

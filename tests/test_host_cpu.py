@@ -239,3 +239,13 @@ def test_stitch_is_order_independent():
         for p, q in zip(got, ref):
             np.testing.assert_array_equal(p, q)
     assert F.stitch_segments(np.empty((0, 2), np.int64), np.empty((0, 4))) == []
+
+
+def test_topo_const_constraint_value_shapes():
+    """features/constraint.py:171 `return_values[mask] = self.value`: numpy takes
+    a scalar or a one-element array there, nothing else."""
+    from ocsmesh_b200.constraint import TopoConstConstraint
+    assert TopoConstConstraint(np.array([5.0])).value == 5.0
+    assert TopoConstConstraint(np.float32(7)).value == 7
+    with pytest.raises(ValueError, match="scalar"):
+        TopoConstConstraint(np.ones((3, 3)))
