@@ -460,6 +460,15 @@ int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
                                  const double *xy, int64_t K,
                                  double *values_out);
 
+/* ---- 8(f) next-4: byte decoders of the windowed GeoTIFF read -----------------
+ * Raster.get_values -> rasterio windowed read                ocsmesh/raster.py:502-531
+ * (GDAL / libtiff, outside the reference tree: restated from the TIFF 6.0
+ * specification).  compression: 5 = LZW (MSB-first codes, early change),
+ * 32773 = PackBits.  One strip or tile per call; *n_out = decoded bytes
+ * (<= cap).  Pure host code, no ctx.                                           */
+int32_t ocsb_tiff_decode(int32_t compression, const uint8_t *src, int64_t n,
+                         uint8_t *dst, int64_t cap, int64_t *n_out);
+
 /* ---- 8(f) next-4: nearest warp onto the "fast" collector's big raster ---------
  * HfunCollector._create_big_raster -> rasterio.warp.reproject(source,
  * destination, resampling=Resampling.nearest, init_dest_nodata=False)

@@ -134,6 +134,7 @@ SIGNATURES = {
                                          c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
     "ocsb_resample_nearest": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_i32, c_i32, c_vp, c_vp,
                                       c_i64, c_vp, c_i64, c_i32, c_i32, c_vp]),
+    "ocsb_tiff_decode": (c_i32, [c_i32, c_vp, c_i64, c_vp, c_i64, C.POINTER(c_i64)]),
     "ocsb_stitch_segments": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64,
                                      C.POINTER(c_i64), C.POINTER(c_i64)]),
     "ocsb_feature_points": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i64,
@@ -214,6 +215,17 @@ def windows(width: int, height: int, chunk_size: int, overlap: int) -> np.ndarra
     check(lib.ocsb_windows(width, height, chunk_size, overlap, out.ctypes.data,
                            n.value, C.byref(n)))
     return out
+
+
+def tiff_decode(compression: int, raw: bytes, cap: int) -> np.ndarray:
+    """One LZW (5) / PackBits (32773) strip or tile -> uint8 array (<= cap bytes)."""
+    lib = load()
+    src = np.frombuffer(raw, dtype=np.uint8)
+    dst = np.empty(int(cap), dtype=np.uint8)
+    n = c_i64(0)
+    check(lib.ocsb_tiff_decode(int(compression), src.ctypes.data, src.size,
+                               dst.ctypes.data, dst.size, C.byref(n)))
+    return dst[:n.value]
 
 
 def stitch_segments(edges: np.ndarray, pts: np.ndarray):

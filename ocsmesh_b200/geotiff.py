@@ -1,20 +1,26 @@
-"""Minimal GeoTIFF / BigTIFF reader and writer (uncompressed strips).
+"""GeoTIFF / BigTIFF reader and writer.
 
 rasterio/GDAL are what the reference uses for raster I/O
 (``ocsmesh/raster.py:502-531``, ``ocsmesh/utils.py:1932-1971``); they are not
 available to this package, and raster I/O is off the accelerated path, so this
-module implements just the subset the path needs: north-up, uncompressed,
-strip-organised float32 / float64 / int16 / int32 / uint8 rasters with the
-GeoTIFF georeferencing tags (ModelPixelScale 33550, ModelTiepoint 33922,
-ModelTransformation 34264, GeoKeyDirectory 34735) and GDAL_NODATA (42113).
-Files above 4 GB are written as BigTIFF.  Pixel data are exposed as
-``numpy.memmap`` so a 40000 x 40000 DEM never has to be resident on the host
-twice.
+module implements the subset DEM files use: north-up float32 / float64 / int16
+/ int32 / uint8 rasters, organised in strips or tiles, uncompressed or with
+DEFLATE (8, 32946: zlib), LZW (5) or PackBits (32773) (both decoded by
+``ocsb_tiff_decode``, host C), predictors 1 / 2 (horizontal differencing) / 3
+(floating point), chunky or planar samples, with the GeoTIFF georeferencing
+tags (ModelPixelScale 33550, ModelTiepoint 33922, ModelTransformation 34264,
+GeoKeyDirectory 34735) and GDAL_NODATA (42113).  Files above 4 GB are written
+as BigTIFF.  Uncompressed contiguous strips are exposed as ``numpy.memmap`` so
+a 40000 x 40000 DEM never has to be resident on the host twice; everything
+else is decoded segment by segment into one array.  The writer produces
+uncompressed single-strip files by default and tiled and / or DEFLATE files on
+request (what GDAL's ``TILED=YES COMPRESS=DEFLATE PREDICTOR=n`` creates).
 """
 from __future__ import annotations
 
 import os
 import struct
+import zlib
 from dataclasses import dataclass
 from typing import Optional, Tuple
 
@@ -79,9 +85,75 @@ def _read_ifd(f, bo: str, big: bool):
     return tags
 
 
+def _decode(raw: bytes, compression: int, cap: int) -> np.ndarray:
+    """One strip / tile -> its bytes (uint8 array)."""
+    if compression == 1:
+        return np.frombuffer(raw, dtype=np.uint8)
+    if compression in (8, 32946):
+        return np.frombuffer(zlib.decompress(raw), dtype=np.uint8)
+    from . import _lib        # LZW / PackBits: host C in libocsb200
+    return _lib.tiff_decode(compression, raw, cap)
+
+
+def _unpredict(seg: np.ndarray, predictor: int, rows: int, cols: int, spp: int,
+               dtype: np.dtype) -> np.ndarray:
+    """Bytes of one segment -> ``(rows, cols, spp)`` samples in native order."""
+    isz = dtype.itemsize
+    native = dtype.newbyteorder("=")
+    if predictor == 3:
+        # TIFF Technical Note 3: per row, the bytes of all samples are grouped by
+        # significance (most significant first) and differenced with stride spp
+        b = seg.reshape(rows, cols * isz, spp)
+        b = np.cumsum(b, axis=1, dtype=np.uint8).reshape(rows, isz, cols * spp)
+        b = np.ascontiguousarray(np.moveaxis(b, 1, 2))
+        return b.view(np.dtype(">f%d" % isz)).reshape(rows, cols, spp).astype(native)
+    a = seg.view(dtype).reshape(rows, cols, spp)
+    if predictor == 2:
+        # horizontal differencing, modulo 2^bits (floats are differenced as the
+        # integers of their width, which is how GDAL writes them)
+        u = np.dtype("u%d" % isz)
+        ai = a.astype(native).view(u)
+        return np.cumsum(ai, axis=1, dtype=u).view(native)
+    return a.astype(native, copy=False)
+
+
+def _read_segments(path, offsets, counts, width, height, spp, dtype, planar, seg_w, seg_h,
+                   tiled, compression, predictor) -> np.ndarray:
+    """Strips (``seg_w == width``) or tiles -> ``(spp, height, width)``."""
+    across = -(-width // seg_w)
+    down = -(-height // seg_h)
+    per_plane = across * down
+    planes = spp if planar == 2 else 1
+    seg_spp = 1 if planar == 2 else spp
+    if len(offsets) < per_plane * planes:
+        raise ValueError(f"{path}: {len(offsets)} segments, {per_plane * planes} expected")
+    out = np.empty((spp, height, width), dtype=dtype.newbyteorder("="))
+    with open(path, "rb") as f:
+        for p in range(planes):
+            for k in range(per_plane):
+                i = p * per_plane + k
+                r0, c0 = (k // across) * seg_h, (k % across) * seg_w
+                # tiles are stored whole; the last strip only holds the rows left
+                rows = seg_h if tiled else min(seg_h, height - r0)
+                full = rows * seg_w * seg_spp * dtype.itemsize
+                f.seek(offsets[i])
+                seg = _decode(f.read(counts[i]), compression, full)
+                if seg.size < full:
+                    raise ValueError(f"{path}: segment {i} is short "
+                                     f"({seg.size} of {full} bytes)")
+                a = _unpredict(seg[:full], predictor, rows, seg_w, seg_spp, dtype)
+                nr, nc = min(rows, height - r0), min(seg_w, width - c0)
+                if planar == 2:
+                    out[p, r0:r0 + nr, c0:c0 + nc] = a[:nr, :nc, 0]
+                else:
+                    out[:, r0:r0 + nr, c0:c0 + nc] = np.moveaxis(a[:nr, :nc], 2, 0)
+    return out
+
+
 def read_geotiff(path) -> Tuple[GeoTiffInfo, np.ndarray]:
     """Open ``path``; returns ``(info, bands)`` with ``bands`` a ``(count, h,
-    w)`` array (a read-only memmap whenever the strips are contiguous)."""
+    w)`` array (a read-only memmap whenever the file is uncompressed with
+    contiguous strips)."""
     path = os.fspath(path)
     with open(path, "rb") as f:
         head = f.read(4)
@@ -104,21 +176,27 @@ def read_geotiff(path) -> Tuple[GeoTiffInfo, np.ndarray]:
     spp = int(t.get(277, (1,))[0])
     bits = int(t.get(258, (1,))[0])
     sfmt = int(t.get(339, (1,))[0])
-    if int(t.get(259, (1,))[0]) != 1:
-        raise NotImplementedError(f"{path}: compressed TIFFs are not supported")
-    if 322 in t or 324 in t:
-        raise NotImplementedError(f"{path}: tiled TIFFs are not supported")
+    compression = int(t.get(259, (1,))[0])
+    if compression not in (1, 5, 8, 32946, 32773):
+        raise NotImplementedError(f"{path}: TIFF compression {compression} is not supported")
+    predictor = int(t.get(317, (1,))[0])
+    if predictor not in (1, 2, 3):
+        raise NotImplementedError(f"{path}: TIFF predictor {predictor}")
     key = (sfmt, bits)
     if key not in _SAMPLE_DTYPES:
         raise NotImplementedError(f"{path}: sample format {key}")
     dtype = np.dtype(bo + _SAMPLE_DTYPES[key])
+    if predictor == 3 and dtype.kind != "f":
+        raise ValueError(f"{path}: floating point predictor on {dtype} samples")
     planar = int(t.get(284, (1,))[0])
-    rps = int(t.get(278, (height,))[0])
-    offsets = [int(o) for o in t[273]]
-    counts = [int(c) for c in t[279]]
-    contiguous = all(offsets[i] + counts[i] == offsets[i + 1]
-                     for i in range(len(offsets) - 1))
-    if contiguous:
+    tiled = 322 in t or 324 in t
+    if not tiled:
+        rps = min(int(t.get(278, (height,))[0]), height)
+        offsets = [int(o) for o in t[273]]
+        counts = [int(c) for c in t[279]]
+        contiguous = all(offsets[i] + counts[i] == offsets[i + 1]
+                         for i in range(len(offsets) - 1))
+    if not tiled and compression == 1 and predictor == 1 and contiguous:
         mm = np.memmap(path, dtype=dtype, mode="r", offset=offsets[0],
                        shape=(sum(counts) // dtype.itemsize,))
         if planar == 2 or spp == 1:
@@ -126,17 +204,14 @@ def read_geotiff(path) -> Tuple[GeoTiffInfo, np.ndarray]:
         else:
             bands = np.moveaxis(mm.reshape(height, width, spp), 2, 0)
     else:
-        with open(path, "rb") as f:
-            chunks = []
-            for o, c in zip(offsets, counts):
-                f.seek(o)
-                chunks.append(f.read(c))
-        flat = np.frombuffer(b"".join(chunks), dtype=dtype)
-        if planar == 2 or spp == 1:
-            bands = flat.reshape(spp, height, width)
+        if tiled:
+            seg_w, seg_h = int(t[322][0]), int(t[323][0])
+            offsets = [int(o) for o in t[324]]
+            counts = [int(c) for c in t[325]]
         else:
-            bands = np.moveaxis(flat.reshape(height, width, spp), 2, 0)
-    del rps
+            seg_w, seg_h = width, rps
+        bands = _read_segments(path, offsets, counts, width, height, spp, dtype,
+                               planar, seg_w, seg_h, tiled, compression, predictor)
     # georeferencing
     if 34264 in t:
         m = t[34264]
@@ -172,10 +247,35 @@ def read_geotiff(path) -> Tuple[GeoTiffInfo, np.ndarray]:
     return info, bands
 
 
+def _predict(a: np.ndarray, predictor: int) -> bytes:
+    """Inverse of :func:`_unpredict` for one ``(rows, cols)`` little-endian
+    segment of one band."""
+    rows, cols = a.shape
+    isz = a.dtype.itemsize
+    if predictor == 2:
+        u = a.view(np.dtype("<u%d" % isz))
+        d = u.copy()
+        d[:, 1:] = u[:, 1:] - u[:, :-1]
+        return d.tobytes()
+    if predictor == 3:
+        b = a.astype(np.dtype(">f%d" % isz)).view(np.uint8).reshape(rows, cols, isz)
+        b = np.ascontiguousarray(np.moveaxis(b, 2, 1)).reshape(rows, isz * cols)
+        d = b.copy()
+        d[:, 1:] = b[:, 1:] - b[:, :-1]
+        return d.tobytes()
+    return a.tobytes()
+
+
 def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
-                  is_geographic: bool = False, nodata: Optional[float] = None):
-    """Write ``data`` (``(h, w)`` or ``(count, h, w)``) as an uncompressed,
-    single-strip-per-band, band-sequential (Big)TIFF."""
+                  is_geographic: bool = False, nodata: Optional[float] = None,
+                  tile: Optional[int] = None, compress: Optional[str] = None,
+                  predictor: int = 1):
+    """Write ``data`` (``(h, w)`` or ``(count, h, w)``) as a band-sequential
+    (Big)TIFF.  Default: uncompressed, one strip per band (the file can be
+    memory-mapped back).  ``tile`` (a multiple of 16): square tiles of that
+    size; ``compress='deflate'``: zlib per strip / tile, with ``predictor`` 1, 2
+    or 3 (floating point) -- GDAL's ``TILED=YES BLOCKXSIZE=tile
+    COMPRESS=DEFLATE PREDICTOR=n``."""
     data = np.asarray(data)
     if data.ndim == 2:
         data = data[None]
@@ -185,8 +285,38 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
     bits = dt.itemsize * 8
     if (kind, bits) not in _SAMPLE_DTYPES:
         raise NotImplementedError(f"dtype {dt}")
+    if compress not in (None, "deflate"):
+        raise NotImplementedError(f"compression {compress!r}")
+    if predictor not in (1, 2, 3) or (predictor == 3 and dt.kind != "f"):
+        raise ValueError(f"predictor {predictor} on {dt} samples")
+    if predictor != 1 and compress is None:
+        raise ValueError("a predictor needs compress='deflate'")
+    if tile is not None and (tile <= 0 or tile % 16):
+        raise ValueError("tile must be a positive multiple of 16")
+    plain = tile is None and compress is None
     band_bytes = height * width * dt.itemsize
-    big = band_bytes * count + 4096 >= (1 << 32) - 1
+    # segments of the non-plain layouts are built in memory (they are meant for
+    # files of ordinary size; the plain layout streams band by band)
+    segments = []
+    if not plain:
+        th, tw = (tile, tile) if tile else (min(height, max(1, (1 << 20) // max(
+            1, width * dt.itemsize))), width)
+        for b in range(count):
+            band = np.ascontiguousarray(data[b], dtype=dt)
+            for r0 in range(0, height, th):
+                for c0 in range(0, width, tw):
+                    blk = band[r0:r0 + th, c0:c0 + tw]
+                    if tile and blk.shape != (th, tw):      # tiles are stored whole
+                        pad = np.zeros((th, tw), dtype=dt)
+                        pad[:blk.shape[0], :blk.shape[1]] = blk
+                        blk = pad
+                    raw = _predict(np.ascontiguousarray(blk), predictor)
+                    segments.append(zlib.compress(raw, 6) if compress else raw)
+        total = sum(len(sg) for sg in segments)
+    else:
+        th, tw = height, width
+        total = band_bytes * count
+    big = total + 4096 + 16 * len(segments) >= (1 << 32) - 1
     a, b, c, d, e, f_ = (float(v) for v in transform)
     if b != 0.0 or d != 0.0:
         raise NotImplementedError("rotated rasters are not supported")
@@ -201,18 +331,28 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
         nkeys += 1
     geokeys[3] = nkeys
 
+    nseg = count if plain else len(segments)
+    seg_sizes = [band_bytes] * count if plain else [len(sg) for sg in segments]
     entries = []  # (tag, type, values)
     entries.append((256, 4, [width]))
     entries.append((257, 4, [height]))
     entries.append((258, 3, [bits] * count))
-    entries.append((259, 3, [1]))
+    entries.append((259, 3, [8 if compress else 1]))
     entries.append((262, 3, [1]))
     offs_type = 16 if big else 4
-    entries.append((273, offs_type, None))  # filled below
+    if tile:
+        entries.append((322, 4, [tw]))
+        entries.append((323, 4, [th]))
+        entries.append((324, offs_type, None))  # filled below
+        entries.append((325, offs_type, seg_sizes))
+    else:
+        entries.append((273, offs_type, None))  # filled below
+        entries.append((278, 4, [th]))
+        entries.append((279, offs_type, seg_sizes))
     entries.append((277, 3, [count]))
-    entries.append((278, 4, [height]))
-    entries.append((279, offs_type, [band_bytes] * count))
     entries.append((284, 3, [2]))
+    if predictor != 1:
+        entries.append((317, 3, [predictor]))
     entries.append((339, 3, [kind] * count))
     if e < 0 and a > 0:
         entries.append((33550, 12, [a, -e, 0.0]))
@@ -243,13 +383,17 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
     blobs = {}
     pos = overflow_pos
     for tag, typ, vals in entries:
-        n = count if vals is None else len(vals)
+        n = nseg if vals is None else len(vals)
         size = _TYPES[typ][1] * n
         if size > inline:
             blobs[tag] = pos
             pos += size + (size & 1)
     data_pos = (pos + 63) // 64 * 64
-    strip_offsets = [data_pos + i * band_bytes for i in range(count)]
+    seg_offsets = []
+    p = data_pos
+    for sz in seg_sizes:
+        seg_offsets.append(p)
+        p += sz
 
     with open(os.fspath(path), "wb") as f:
         if big:
@@ -260,7 +404,7 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
         tail = []
         for tag, typ, vals in entries:
             if vals is None:
-                vals = strip_offsets
+                vals = seg_offsets
             n = len(vals)
             payload = pack_vals(typ, vals)
             f.write(struct.pack("<HH", tag, typ))
@@ -275,5 +419,9 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
             f.seek(off)
             f.write(payload)
         f.seek(data_pos)
-        for i in range(count):
-            np.ascontiguousarray(data[i], dtype=dt).tofile(f)
+        if plain:
+            for i in range(count):
+                np.ascontiguousarray(data[i], dtype=dt).tofile(f)
+        else:
+            for sg in segments:
+                f.write(sg)
