@@ -117,7 +117,9 @@ int32_t ocsb_ctx_trim(ocsb_ctx *ctx);
 #define OCSB_KC_CONTOUR          13
 #define OCSB_KC_SAMPLE           14
 #define OCSB_KC_PASS_TILE        15
-#define OCSB_KC_COUNT            16
+#define OCSB_KC_PASS_LIMITER     16   /* split pass: limiter sweep of all tiles     */
+#define OCSB_KC_PASS_FEATURE     17   /* split pass: feature op on candidate tiles  */
+#define OCSB_KC_COUNT            18
 int32_t     ocsb_ctx_set_timing(ocsb_ctx *ctx, int32_t enabled);
 int32_t     ocsb_ctx_get_timing(ocsb_ctx *ctx, int32_t kclass, double *total_ms,
                                 int64_t *launches);

@@ -21,7 +21,7 @@ OCSB_OK = 0
 OCSB_EINVAL, OCSB_ENOMEM, OCSB_ECUDA, OCSB_ENCCL, OCSB_EOVERFLOW = -1, -2, -3, -4, -5
 OCSB_F32, OCSB_F64 = 0, 1
 INTERP_LINEAR, INTERP_NEAREST, INTERP_SPLINE = 0, 1, 2
-KC_COUNT = 16
+KC_COUNT = 18
 VT_MIN, VT_MAX = 0, 1
 NONE = float("nan")
 

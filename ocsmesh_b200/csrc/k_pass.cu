@@ -1308,9 +1308,12 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 // one instantiation of the persistent kernel: resident grid, opt-in shared memory
-template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND>
-int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P) {
-    auto kern = pass2_kernel<HAS_OLD, HAS_FEAT, HAS_LIM, BAND>;
+// `reserve` > 0: that many of the resident CTA slots are left free (the limiter
+// sweep of a split pass leaves room for the pyramid's launches); LIST:
+// P.active / P.n_active
+template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND, bool LIST>
+int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P, int reserve) {
+    auto kern = pass2_kernel<HAS_OLD, HAS_FEAT, HAS_LIM, BAND, LIST>;
     static int resident[64] = {};     // per device: CTAs that fit the whole GPU
     int dev = 0;
     OCSB_CUDA(cudaGetDevice(&dev));
@@ -1325,10 +1328,13 @@ int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P) {
         OCSB_REQUIRE(n > 0 && sms > 0, "pass2_kernel does not fit an SM");
         resident[dev] = n * sms;
     }
+    int res = resident[dev];
+    if (reserve > 0) res = std::max(ctx->num_sms, res - reserve);
     // chunk: up to kChunkMax tiles per counter fetch, fewer when that would leave a CTA with
     // less than ~8 fetches (a band of a multi-GPU run): the tail of a launch is
-    // one chunk long
-    int chunk = (int)(P.n_tiles / ((long long)resident[dev] * 8));
+    // one chunk long.  A list's length is only known on the device: a quarter
+    // of the tiles is assumed
+    int chunk = (int)((LIST ? P.n_tiles / 4 : P.n_tiles) / ((long long)res * 8));
     chunk = std::max(1, std::min(kChunkMax, chunk));
     static const int chunk_env = [] {
         const char *e = getenv("OCSB_PASS_CHUNK");      // tuning override
@@ -1336,17 +1342,21 @@ int32_t launch_pass2_t(ocsb_ctx *ctx, const CUtensorMap &tmap, P2Args P) {
     }();
     if (chunk_env > 0) chunk = std::min(kChunkMax, chunk_env);
     P.chunk = chunk;
-    const int grid = (int)std::min<long long>((P.n_tiles + chunk - 1) / chunk,
-                                              (long long)resident[dev]);
+    const int grid = (int)std::min<long long>((P.n_tiles + chunk - 1) / chunk, (long long)res);
     kern<<<grid, kP2Threads, sizeof(P2Smem), ctx->stream>>>(tmap, P);
     return OCSB_OK;
 }
 
 int32_t launch_pass2(ocsb_ctx *ctx, const CUtensorMap &tmap, const P2Args &P, bool old,
-                     bool feat, bool lim, bool band) {
+                     bool feat, bool lim, bool band, int reserve = 0) {
+    if (P.active) {
+        // the feature half of a split pass: in place, tiles from the list
+        OCSB_REQUIRE(old && feat && !lim, "launch_pass2: bad list variant");
+        return launch_pass2_t<true, true, false, false, true>(ctx, tmap, P, reserve);
+    }
 #define P2_CASE(O, F, L, B)                                                        \
     if (old == O && feat == F && lim == L && band == B)                            \
-        return launch_pass2_t<O, F, L, B>(ctx, tmap, P);
+        return launch_pass2_t<O, F, L, B, false>(ctx, tmap, P, reserve);
     P2_CASE(false, true, true, false)
     P2_CASE(false, true, true, true)
     P2_CASE(true, true, true, false)
@@ -1490,6 +1500,53 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     for (int f = 0; f < d.nf; ++f) v2 = v2 && d.feats[f].fuse_clamp;
     for (int l = 0; l < d.nl; ++l) v2 = v2 && d.lims[l].fuse_clamp;
 
+    // ---- split form of a (feature, limiter) pass ------------------------------------
+    // The ops commute bit for bit (one fuse_clamp setting), so the limiter may go
+    // first: its sweep needs no candidate lists and runs on a second stream
+    // BESIDE the pyramid's chain of latency-bound launches; the feature op then
+    // only visits the tiles that ended with candidates (l10_kernel lists them),
+    // in place.  Skipping a tile without candidates is exact when the op's miss
+    // value cannot lower a clamped pixel: min(x, v_far) = x for every x <= ghmax.
+    static const int split_env = [] {
+        const char *e = getenv("OCSB_PASS_SPLIT");
+        return e ? atoi(e) : 1;
+    }();
+    bool split = split_env != 0 && v2 && d.nf == 1 && d.nl == 1 &&
+                 (d.in == nullptr || (d.in == d.out && d.in_stride == d.out_stride));
+    if (split) {
+        const PassFeat &pf = d.feats[0];
+        volatile double m = pf.rate_target * pf.r;       // as F.v_far_f below
+        volatile double sfar = m + pf.target;
+        const float v_far = pf.r < inf ? (float)sfar : finf;
+        const float hi = ocsb_is_none(d.ghmax) ? finf : (float)d.ghmax;
+        split = v_far >= hi;
+        for (int k = 0; k < d.n_wins; ++k)      // every window writes all of its pixels
+            split = split && d.wins[k].keep_w >= d.wins[k].ax.n &&
+                    d.wins[k].keep_h >= d.wins[k].re;
+    }
+    if (split && !ctx->s_split) {
+        // an SM runs ONE shared-memory carveout at a time: the pyramid's launches
+        // only fit beside the sweep's resident CTAs (which take the largest one)
+        // when they ask for the same split of L1 / shared memory
+        OCSB_CUDA(cudaFuncSetAttribute(root_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       (int)cudaSharedmemCarveoutMaxShared));
+        OCSB_CUDA(cudaFuncSetAttribute(l10_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       (int)cudaSharedmemCarveoutMaxShared));
+        int lo_pri = 0, hi_pri = 0;
+        OCSB_CUDA(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+        OCSB_CUDA(cudaStreamCreateWithPriority(&ctx->s_split, cudaStreamNonBlocking, lo_pri));
+        for (auto &e : ctx->ev_split)
+            OCSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    static const int split_reserve = [] {
+        // CTA slots the sweep leaves free.  Measured (profiles/r2c_split_lab.txt):
+        // the pyramid needs the whole machine for ~0.16 ms rather than a few slots
+        // for longer, so leaving slots free only slows the sweep down; with 0 the
+        // pyramid's CTAs move in as the sweep's CTAs retire (its tail)
+        const char *e = getenv("OCSB_PASS_SPLIT_RESERVE");
+        return e ? atoi(e) : 0;
+    }();
+
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, zero_words * sizeof(*ctrs), ctx->stream));
@@ -1508,6 +1565,23 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         T.use_tma = use_tma;
         T.overflow = overflow;
         T.sticky = sticky;
+        for (int l = 0; l < d.nl; ++l) {
+            const PassLim &pl = d.lims[l];
+            LimiterDev<float> &p = T.lim[l];
+            p.hmin = ocsb_is_none(pl.hmin) ? -finf : (float)pl.hmin;
+            p.hmax = ocsb_is_none(pl.hmax) ? finf : (float)pl.hmax;
+            p.ghmin = T.lo; p.ghmax = T.hi;
+            p.lb = ocsb_is_none(pl.lb) ? -finf : (float)pl.lb;
+            p.ub = ocsb_is_none(pl.ub) ? finf : (float)pl.ub;
+            p.d1_0 = make_cdiv<float>(d.dx);
+            p.d2_0 = make_cdiv<float>(2.0 * d.dx);
+            p.d1_1 = make_cdiv<float>(d.dy);
+            p.d2_1 = make_cdiv<float>(2.0 * d.dy);
+            p.fuse_clamp = pl.fuse_clamp;
+            T.lim_band[l] = (!ocsb_is_none(pl.lb) || !ocsb_is_none(pl.ub)) ? 1 : 0;
+        }
+        int *active = nullptr, *n_active = reinterpret_cast<int *>(ctrs + nctr) + 8;
+        if (split) OCSB_TRY(pools.get(&active, (size_t)n0));
 
         for (int f = 0; f < d.nf; ++f) {
             const PassFeat &pf = d.feats[f];
@@ -1541,6 +1615,34 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 OCSB_LAUNCHED(ctx);
             }
             OCSB_CHECK_LAUNCH();
+            if (split) {
+                // fork: the limiter sweep goes to the second stream, after the
+                // memset (its tile counter, the flags), the window table and the
+                // vertex-grid launches (their 1024-thread CTAs would not fit an
+                // SM beside the sweep's resident CTAs and would wait for its end)
+                OCSB_CUDA(cudaEventRecord(ctx->ev_split[0], ctx->stream));
+                OCSB_CUDA(cudaStreamWaitEvent(ctx->s_split, ctx->ev_split[0], 0));
+                P2Args P;
+                memset(&P, 0, sizeof(P));
+                P.wins = d_wins; P.n_wins = d.n_wins; P.n_tiles = (int)n0;
+                P.in = d.in; P.out = d.out;
+                P.in_stride = d.in_stride; P.out_stride = d.out_stride;
+                P.lim = T.lim[0];
+                P.lo = T.lo; P.hi = T.hi;
+                P.counter = reinterpret_cast<int *>(ctrs + nctr) + 6;
+                P.overflow = overflow;
+                P.sticky = sticky;
+                cudaStream_t main_stream = ctx->stream;
+                ctx->stream = ctx->s_split;        // launch + timing events on that stream
+                OCSB_TIME(ctx, KC_PASS_LIMITER);
+                const int32_t st = launch_pass2(ctx, tmap, P, d.in != nullptr, false, true,
+                                                T.lim_band[0] != 0, split_reserve);
+                OCSB_LAUNCHED(ctx);
+                ctx->stream = main_stream;
+                OCSB_TRY(st);
+                OCSB_CHECK_LAUNCH();
+                OCSB_CUDA(cudaEventRecord(ctx->ev_split[1], ctx->s_split));
+            }
 
             BuildArgs B;
             B.wins = d_wins; B.n_wins = d.n_wins;
@@ -1599,6 +1701,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 L.ctr = ctrs + 2 * kMaxFeat; L.cap = cap0;
                 L.overflow = overflow;
                 L.sticky = sticky;
+                L.active = active; L.n_active = n_active;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 L.n_parents = (int)n1;
                 l10_kernel<<<(unsigned)n1, kL10Threads, 0, ctx->stream>>>(L);
@@ -1624,23 +1727,24 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 F.hi_lo = fast_ok ? (uint32_t)(b >> 32) + 1 : 0xffffffffu;
             }
         }
-        for (int l = 0; l < d.nl; ++l) {
-            const PassLim &pl = d.lims[l];
-            LimiterDev<float> &p = T.lim[l];
-            p.hmin = ocsb_is_none(pl.hmin) ? -finf : (float)pl.hmin;
-            p.hmax = ocsb_is_none(pl.hmax) ? finf : (float)pl.hmax;
-            p.ghmin = T.lo; p.ghmax = T.hi;
-            p.lb = ocsb_is_none(pl.lb) ? -finf : (float)pl.lb;
-            p.ub = ocsb_is_none(pl.ub) ? finf : (float)pl.ub;
-            p.d1_0 = make_cdiv<float>(d.dx);
-            p.d2_0 = make_cdiv<float>(2.0 * d.dx);
-            p.d1_1 = make_cdiv<float>(d.dy);
-            p.d2_1 = make_cdiv<float>(2.0 * d.dy);
-            p.fuse_clamp = pl.fuse_clamp;
-            T.lim_band[l] = (!ocsb_is_none(pl.lb) || !ocsb_is_none(pl.ub)) ? 1 : 0;
-        }
-        OCSB_TIME(ctx, KC_PASS_TILE);
-        if (v2) {
+        if (split) {
+            // join: the feature op reads what the sweep wrote
+            OCSB_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_split[1], 0));
+            P2Args P;
+            memset(&P, 0, sizeof(P));
+            P.wins = d_wins; P.n_wins = d.n_wins; P.n_tiles = (int)n0;
+            P.in = d.out; P.out = d.out;
+            P.in_stride = d.out_stride; P.out_stride = d.out_stride;
+            P.feat = T.feat[0]; P.slots = slots0; P.pool0 = pool0;
+            P.lo = T.lo; P.hi = T.hi;
+            P.counter = reinterpret_cast<int *>(ctrs + nctr) + 4;
+            P.overflow = overflow;
+            P.sticky = sticky;
+            P.active = active; P.n_active = n_active;
+            OCSB_TIME(ctx, KC_PASS_FEATURE);
+            OCSB_TRY(launch_pass2(ctx, tmap, P, true, true, false, false));
+        } else if (v2) {
+            OCSB_TIME(ctx, KC_PASS_TILE);
             P2Args P;
             memset(&P, 0, sizeof(P));
             P.wins = d_wins; P.n_wins = d.n_wins; P.n_tiles = (int)n0;
@@ -1655,6 +1759,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
             const bool band = d.nl && T.lim_band[0];
             OCSB_TRY(launch_pass2(ctx, tmap, P, d.in != nullptr, d.nf > 0, d.nl > 0, band));
         } else {
+            OCSB_TIME(ctx, KC_PASS_TILE);
             const dim3 tgrid = d.n_wins == 1
                                    ? dim3((unsigned)wins[0].n0x, (unsigned)wins[0].n0y)
                                    : dim3((unsigned)n0);

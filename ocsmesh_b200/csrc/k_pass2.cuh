@@ -57,6 +57,10 @@ struct P2Args {
     float lo, hi;
     int *counter;           // zeroed before the launch
     int chunk;              // tiles per fetch of the counter
+    // LIST form (the feature half of a split pass): the units of work are the
+    // entries of `active` (tiles with candidates, any order), *n_active of them
+    const int *active;
+    const int *n_active;
     const int *overflow;
     const int *sticky;      // status word of a pass sequence (or nullptr)
 };
@@ -78,6 +82,7 @@ struct __align__(128) P2Smem {
     // q_next (q_tx < 0: not decoded) and a cache of its window (tile -> window
     // is monotone)
     int q_next, q_end, q_tx, q_ty, ended;
+    int n_work;             // tiles (or list entries) of this launch
     int cur_wi, cur_base0, cur_n0x, cur_next;
     int cur_demc, cur_demr;
 };
@@ -104,25 +109,28 @@ __device__ __forceinline__ void p2_bulk(void *dst_smem, const void *src, uint32_
 
 // producer: the next tile -> stage (info, window record, slot, DEM box); past
 // the last tile it publishes the end marker instead
-template <bool HAS_FEAT, bool HAS_LIM>
+template <bool HAS_FEAT, bool HAS_LIM, bool LIST>
 __device__ __forceinline__ void p2_produce(const CUtensorMap *tmap, const P2Args &A,
                                            P2Smem &S, int stage) {
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S.full[stage]);
-    int t = S.q_next, tx = S.q_tx, ty = S.q_ty;
-    if (t == S.q_end) {
-        t = atomicAdd(A.counter, A.chunk) + (int)gridDim.x * A.chunk;
-        S.q_end = t + A.chunk;
+    int u = S.q_next, tx = S.q_tx, ty = S.q_ty;
+    if (u == S.q_end) {
+        u = atomicAdd(A.counter, A.chunk) + (int)gridDim.x * A.chunk;
+        S.q_end = u + A.chunk;
         tx = -1;
     }
-    if (t >= A.n_tiles) {
+    if (u >= S.n_work) {
         S.ended = 1;
         S.info[stage].t = -1;
         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
         return;
     }
-    if (t >= S.cur_next) {
+    int t = u;
+    if (LIST) { t = A.active[u]; tx = -1; }     // list entries are in no order
+    if (t >= S.cur_next || (LIST && t < S.cur_base0)) {
         int wi = S.cur_wi;
-        while (wi + 1 < A.n_wins && t >= A.wins[wi + 1].base0) ++wi;
+        if (LIST) wi = find_win(A.wins, A.n_wins, t, 0);
+        else while (wi + 1 < A.n_wins && t >= A.wins[wi + 1].base0) ++wi;
         const PWin &G = A.wins[wi];
         S.cur_wi = wi; S.cur_base0 = G.base0; S.cur_n0x = G.n0x;
         S.cur_next = wi + 1 < A.n_wins ? A.wins[wi + 1].base0 : 0x7fffffff;
@@ -156,7 +164,7 @@ __device__ __forceinline__ void p2_produce(const CUtensorMap *tmap, const P2Args
             ::"r"(dst), "l"(tmap), "r"(cx), "r"(cy), "r"(bar) : "memory");
     }
     // the tile after this one (a window change re-decodes it)
-    S.q_next = t + 1;
+    S.q_next = u + 1;
     if (++tx == n0x) { tx = 0; ++ty; }
     S.q_tx = tx; S.q_ty = ty;
 }
@@ -360,7 +368,7 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
 #define OCSB_PASS2_MIN_CTAS 3
 #endif
 
-template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND>
+template <bool HAS_OLD, bool HAS_FEAT, bool HAS_LIM, bool BAND, bool LIST>
 __global__ void __launch_bounds__(kP2Threads, OCSB_PASS2_MIN_CTAS)
 pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
     extern __shared__ __align__(128) unsigned char p2_raw[];
@@ -390,8 +398,10 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
         S.q_next = (int)blockIdx.x * A.chunk;  // the first chunk is static
         S.q_end = S.q_next + A.chunk;
         S.q_tx = -1; S.q_ty = 0; S.ended = 0;
-        p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 0);
-        if (!S.ended) p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, 1);
+        S.cur_base0 = 0;
+        S.n_work = LIST ? min(*A.n_active, A.n_tiles) : A.n_tiles;
+        p2_produce<HAS_FEAT, HAS_LIM, LIST>(&tmap, A, S, 0);
+        if (!S.ended) p2_produce<HAS_FEAT, HAS_LIM, LIST>(&tmap, A, S, 1);
     }
     __syncthreads();         // barrier words initialised before anyone polls them
 
@@ -406,7 +416,7 @@ pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
                 const uint32_t eb = (uint32_t)__cvta_generic_to_shared(&S.empty[s2]);
                 p2_wait(eb, (uint32_t)((it - 1) / kStages) & 1u);
             }
-            p2_produce<HAS_FEAT, HAS_LIM>(&tmap, A, S, s2);
+            p2_produce<HAS_FEAT, HAS_LIM, LIST>(&tmap, A, S, s2);
         }
         __syncwarp();
         // ---- consumer: wait for the stage ----------------------------------------------------
@@ -506,6 +516,8 @@ struct L0Args {
     unsigned long long cap;
     int *overflow;
     int *sticky;
+    // split pass: the tiles that end with candidates (nullptr: not wanted)
+    int *active, *n_active;
 };
 
 #ifndef OCSB_L10_THREADS
@@ -523,6 +535,7 @@ __global__ void __launch_bounds__(kL10Threads) l10_kernel(L0Args A) {
     __shared__ __align__(16) double2 s_xy[kL0Stage];
     __shared__ int s_cnt;
     __shared__ unsigned long long s_base;
+    __shared__ int s_nact, s_act[16];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int t1 = blockIdx.x;
     if (t1 >= A.n_parents || *A.overflow) return;
@@ -562,7 +575,7 @@ __global__ void __launch_bounds__(kL10Threads) l10_kernel(L0Args A) {
             dom_acc_finish(q, acc, key, s_tab[wid], lane, [&](int i) { return src2[i]; });
         }
         __syncwarp();
-        if (threadIdx.x == 0) s_cnt = 0;
+        if (threadIdx.x == 0) { s_cnt = 0; s_nact = 0; }
         dom_combine<NW>(key, s_key, s_tab, &s_fin, &s_key0);
         for (int b0 = wid * 32; b0 < pcnt2; b0 += kL10Threads) {
             const int i = b0 + lane;
@@ -671,6 +684,16 @@ __global__ void __launch_bounds__(kL10Threads) l10_kernel(L0Args A) {
             hd.off = (long long)base;
         }
         __syncwarp();
-        if (lane == 0) *reinterpret_cast<SlotHead *>(slot) = hd;
+        if (lane == 0) {
+            *reinterpret_cast<SlotHead *>(slot) = hd;
+            if (A.active && total > 0) s_act[atomicAdd(&s_nact, 1)] = t;
+        }
+    }
+    if (A.active) {
+        __syncthreads();
+        if (threadIdx.x == 0 && s_nact > 0) {
+            const int base = atomicAdd(A.n_active, s_nact);
+            for (int i = 0; i < s_nact; ++i) A.active[base + i] = s_act[i];
+        }
     }
 }

@@ -188,6 +188,9 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
         if (ctx->s_win[i]) cudaStreamDestroy(ctx->s_win[i]);
         if (ctx->ev_win[i]) cudaEventDestroy(ctx->ev_win[i]);
     }
+    if (ctx->s_split) cudaStreamDestroy(ctx->s_split);
+    for (auto &e : ctx->ev_split)
+        if (e) cudaEventDestroy(e);
     if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
     if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
     for (int i = 0; i < OCSB_PASS_SETS; ++i) {
@@ -315,7 +318,7 @@ extern "C" const char *ocsb_kernel_class_name(int32_t kclass) {
         "fill", "clamp", "min_combine", "coords", "flow_limiter",
         "feature_refine", "feature_eval", "interp", "spline_prefilter",
         "spline_eval", "nearest_vertex", "bucket_nodes", "constraint", "contour", "sample",
-        "pass_tile"};
+        "pass_tile", "pass_limiter", "pass_feature"};
     return (kclass >= 0 && kclass < OCSB_KC_COUNT) ? names[kclass] : "?";
 }
 

@@ -21,7 +21,8 @@ enum {
     KC_SPLINE_EVAL = OCSB_KC_SPLINE_EVAL, KC_NEAREST = OCSB_KC_NEAREST,
     KC_BUCKET = OCSB_KC_BUCKET, KC_CONSTRAINT = OCSB_KC_CONSTRAINT,
     KC_CONTOUR = OCSB_KC_CONTOUR, KC_SAMPLE = OCSB_KC_SAMPLE,
-    KC_PASS_TILE = OCSB_KC_PASS_TILE
+    KC_PASS_TILE = OCSB_KC_PASS_TILE, KC_PASS_LIMITER = OCSB_KC_PASS_LIMITER,
+    KC_PASS_FEATURE = OCSB_KC_PASS_FEATURE
 };
 
 // ---------------------------------------------------------------------------
@@ -96,6 +97,9 @@ struct ocsb_ctx {
     // worker streams of ocsb_hfun_op_windows (created on first use)
     cudaStream_t s_win[OCSB_WIN_STREAMS] = {};
     cudaEvent_t ev_win[OCSB_WIN_STREAMS] = {};
+    // second stream of the split pass (limiter sweep beside the candidate pyramid)
+    cudaStream_t s_split = nullptr;
+    cudaEvent_t ev_split[2] = {nullptr, nullptr};
     // one-time cudaFuncSetAttribute calls already made on this device
     unsigned func_attr_done = 0;
     // results kept on the device until the caller takes them (ocsb_take_result):
