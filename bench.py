@@ -333,6 +333,10 @@ class BandRun:
                                    f"cuda:{dev}", self.part, rank)
         self.nv_total = int(sum(self.exch.sizes))
 
+    def close(self):
+        """Release the peer-memory exchange buffers (every rank calls it)."""
+        self.exch.close()
+
     def step(self):
         """A4 init, vertex all-gather, DEM halo rows, A6/A7 + A8(A9): one sweep."""
         h = self.hfun
@@ -537,7 +541,10 @@ def run_ours(args, rank, world, local_rank):
         secondary["windows"] = bench_windows(args, run, rank, world, dev, ms_step)
     if world == 1 and not args.no_windows:
         secondary["add_contour_api"] = bench_add_contour(args, run, dev)
+    exchange_mode = run.exch.mode if world > 1 else "none (one rank)"
+    exchange_failed = run.exch.p2p_failed()
     if world > 1 and not args.no_weak:
+        run.close()
         del run
         torch.cuda.empty_cache()
         secondary["weak"] = bench_weak(args, rank, world, dev)
@@ -556,8 +563,15 @@ def run_ours(args, rank, world, local_rank):
             "config": cfg,
             "parallelism": (f"row bands x{world} of ONE {H}x{W} raster "
                             f"({H // world} rows per GPU); per step: vertex "
-                            "all-gather + boundary DEM rows in one NCCL "
-                            "collective, then one tiled sweep per band"),
+                            "all-gather + boundary DEM rows in one exchange (see "
+                            "`exchange`), then the sweep of the band"),
+            "exchange": {"mode": exchange_mode,
+                         "p2p": "ocsb_band_push / ocsb_band_pull: stores into the "
+                                "peers' CUDA-IPC buffers over NVLink + epoch flags, "
+                                "no collective inside the step",
+                         "nccl": "ocsb_band_pack + one all_gather_into_tensor + "
+                                 "ocsb_band_unpack",
+                         "gave_up_waiting": bool(exchange_failed)},
             "vertex_set": ("contours of each rank's band (cell rows partition the "
                            "raster's), each piece resampled on its own; all-"
                            "gathered every step"),
@@ -702,7 +716,8 @@ def bench_weak(args, rank, world, dev):
     run.hfun.sync()
     res = {"scaling": "weak", "raster": f"{H}x{W}", "ms_per_step": ms,
            "value": float(H) * W / (ms * 1e-3) / 1e6, "unit": "Mpx/s",
-           "n_vertices": run.nv_total}
+           "n_vertices": run.nv_total, "exchange": run.exch.mode}
+    run.close()
     del run
     torch.cuda.empty_cache()
     return res

@@ -462,6 +462,42 @@ int32_t ocsb_hfun_sample_nearest(ocsb_ctx *ctx, const ocsb_win *win,
                                  const double *xy, int64_t K,
                                  double *values_out);
 
+/* ---- 8(e): the per-step band exchange as stores into peer memory -------------
+ * A row-band run exchanges, every step, each rank's contour vertices (the
+ * vertex all-gather of the north star; the reference computes them in one
+ * process, ocsmesh/hfun/raster.py:991-1002) and its first / last owned DEM row
+ * (the 1-row halos of np.gradient, ocsmesh/hfun/raster.py:1399).
+ * ocsb_band_pack + NCCL all-gather + ocsb_band_unpack do that with a
+ * collective; these entry points do it with NVLink stores from a kernel:
+ *   ocsb_band_p2p_bytes : size of a rank's exchange buffer (two generations of
+ *                         `world` slots [2 rows | cap vertices] + 256 B of flags)
+ *   ocsb_p2p_alloc      : cudaMalloc + zero + CUDA IPC handle (64 bytes) to hand
+ *                         to the other ranks; ocsb_p2p_open maps a peer's buffer,
+ *                         ocsb_p2p_close / ocsb_p2p_free undo the two
+ *   ocsb_band_push      : pack this rank's block into slot `rank` of EVERY
+ *                         rank's buffer (peer_bufs_dev: device array of `world`
+ *                         buffer addresses, own buffer at index `rank`), then
+ *                         publish `epoch` (1, 2, 3, ... one per step) in every
+ *                         rank's flag word; done_counter_dev: one zeroed device
+ *                         word kept by the caller across steps
+ *   ocsb_band_pull      : wait (bounded, ~2 s -> *status_dev = 1) until all ranks
+ *                         published `epoch` in own_buf, then unpack as
+ *                         ocsb_band_unpack does
+ * Same results as the collective form, bit for bit (bench.py parity check at
+ * N > 1).  A rank may run one step ahead of a peer, never two.                  */
+int64_t ocsb_band_p2p_bytes(int32_t world, int64_t cap, int32_t width);
+int32_t ocsb_p2p_alloc(ocsb_ctx *ctx, int64_t bytes, void **ptr, uint8_t *handle64);
+int32_t ocsb_p2p_open(ocsb_ctx *ctx, const uint8_t *handle64, void **ptr);
+int32_t ocsb_p2p_close(ocsb_ctx *ctx, void *ptr);
+int32_t ocsb_p2p_free(ocsb_ctx *ctx, void *ptr);
+int32_t ocsb_band_push(ocsb_ctx *ctx, const double *verts, int64_t n, int64_t cap,
+                       const float *row_first, const float *row_last, int32_t width,
+                       const void *const *peer_bufs_dev, int32_t world, int32_t rank,
+                       int64_t epoch, double far, unsigned long long *done_counter_dev);
+int32_t ocsb_band_pull(ocsb_ctx *ctx, const void *own_buf, int32_t world, int32_t rank,
+                       int64_t cap, int32_t width, int64_t epoch, double *verts_out,
+                       float *halo_above, float *halo_below, int32_t *status_dev);
+
 /* ---- 8(f) next-4: byte decoders of the windowed GeoTIFF read -----------------
  * Raster.get_values -> rasterio windowed read                ocsmesh/raster.py:502-531
  * (GDAL / libtiff, outside the reference tree: restated from the TIFF 6.0

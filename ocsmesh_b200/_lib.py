@@ -134,6 +134,15 @@ SIGNATURES = {
                                          c_i32, c_f64, c_f64, c_vp, c_i64, c_vp]),
     "ocsb_resample_nearest": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_i32, c_i32, c_vp, c_vp,
                                       c_i64, c_vp, c_i64, c_i32, c_i32, c_vp]),
+    "ocsb_band_p2p_bytes": (c_i64, [c_i32, c_i64, c_i32]),
+    "ocsb_p2p_alloc": (c_i32, [c_vp, c_i64, C.POINTER(c_vp), c_vp]),
+    "ocsb_p2p_open": (c_i32, [c_vp, c_vp, C.POINTER(c_vp)]),
+    "ocsb_p2p_close": (c_i32, [c_vp, c_vp]),
+    "ocsb_p2p_free": (c_i32, [c_vp, c_vp]),
+    "ocsb_band_push": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_i32, c_vp, c_i32,
+                               c_i32, c_i64, c_f64, c_vp]),
+    "ocsb_band_pull": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i64, c_i32, c_i64, c_vp, c_vp,
+                               c_vp, c_vp]),
     "ocsb_tiff_decode": (c_i32, [c_i32, c_vp, c_i64, c_vp, c_i64, C.POINTER(c_i64)]),
     "ocsb_stitch_segments": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64,
                                      C.POINTER(c_i64), C.POINTER(c_i64)]),
@@ -502,6 +511,39 @@ class Context:
         check(self.lib.ocsb_band_unpack(self.handle, ptr(recv), int(world), int(rank),
                                         int(cap), int(width), ptr(verts_out),
                                         ptr(halo_above), ptr(halo_below)))
+
+    # ---- band exchange over peer memory (CUDA IPC buffers) -------------------
+    def p2p_alloc(self, nbytes: int):
+        """-> (device address, 64-byte IPC handle) of a zeroed exchange buffer."""
+        p = c_vp(0)
+        h = (C.c_uint8 * 64)()
+        check(self.lib.ocsb_p2p_alloc(self.handle, int(nbytes), C.byref(p), C.cast(h, c_vp)))
+        return int(p.value), bytes(h)
+
+    def p2p_open(self, handle: bytes) -> int:
+        p = c_vp(0)
+        h = (C.c_uint8 * 64).from_buffer_copy(handle)
+        check(self.lib.ocsb_p2p_open(self.handle, C.cast(h, c_vp), C.byref(p)))
+        return int(p.value)
+
+    def p2p_close(self, addr: int):
+        check(self.lib.ocsb_p2p_close(self.handle, c_vp(addr)))
+
+    def p2p_free(self, addr: int):
+        check(self.lib.ocsb_p2p_free(self.handle, c_vp(addr)))
+
+    def band_push(self, verts, n, cap, row_first, row_last, width, peers_dev, world, rank,
+                  epoch, far, done_counter):
+        check(self.lib.ocsb_band_push(
+            self.handle, ptr(verts) if n else None, int(n), int(cap), ptr(row_first),
+            ptr(row_last), int(width), ptr(peers_dev), int(world), int(rank), int(epoch),
+            float(far), ptr(done_counter)))
+
+    def band_pull(self, own_addr, world, rank, cap, width, epoch, verts_out, halo_above,
+                  halo_below, status):
+        check(self.lib.ocsb_band_pull(
+            self.handle, c_vp(own_addr), int(world), int(rank), int(cap), int(width),
+            int(epoch), ptr(verts_out), ptr(halo_above), ptr(halo_below), ptr(status)))
 
     def region_mask(self, win, edges, n_edges, all_touched, mask_out, mask_stride):
         """0 / 1 float32 raster of a polygon set (``edges``: (n, 4) float64)."""

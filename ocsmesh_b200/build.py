@@ -32,6 +32,7 @@ SOURCES = [
     "k_nearest.cu",
     "k_constraint.cu",
     "k_warp.cu",
+    "k_p2p.cu",
     "h_tiff.cu",
     "k_contour.cu",
     "k_stitch.cu",

@@ -22,9 +22,13 @@ Nothing here touches pixel data on the host.
 """
 from __future__ import annotations
 
+import logging
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
+
+_logger = logging.getLogger(__name__)
 
 
 class RowBands:
@@ -217,6 +221,85 @@ class BandExchange:
         self._recv_rows = self._recv[:, :2 * int(width) * es].view(dem_dtype)   # (world, 2 W)
         self._recv_verts = self._recv[:, self._row_bytes:].view(torch.float64)  # (world, 2 cap)
         self._width = int(width)
+        # peer-memory form of exchange() (ocsb_band_push / ocsb_band_pull): set up
+        # when every rank can map every other rank's buffer, else the collective
+        self.mode = "nccl"
+        self._p2p = None
+        if (self.world > 1 and dem_dtype == torch.float32 and torch.device(device).type == "cuda"
+                and os.environ.get("OCSB_BAND_P2P", "1") != "0"):
+            self._init_p2p()
+
+    def _init_p2p(self) -> None:
+        """Allocate this rank's exchange buffer, swap CUDA IPC handles, map the
+        peers' buffers.  All ranks agree on the outcome (one all-gather of a
+        success flag): anything short of everybody succeeding keeps the
+        collective path."""
+        import torch
+        import torch.distributed as dist
+        from . import _lib
+        dev = torch.device(self.device)
+        ctx = _lib.default_context(dev.index)
+        own = None
+        opened = {}
+        ok = True
+        try:
+            nbytes = _lib.load().ocsb_band_p2p_bytes(self.world, self.cap, self._width)
+            if nbytes <= 0:
+                raise RuntimeError("ocsb_band_p2p_bytes refused the geometry")
+            own, handle = ctx.p2p_alloc(nbytes)
+        except Exception as e:      # pylint: disable=broad-except
+            _logger.info("band exchange: no peer-memory buffer (%s)", e)
+            ok, handle = False, b""
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle if ok else None, group=self.group)
+        if ok and all(h is not None for h in handles):
+            try:
+                for r, h in enumerate(handles):
+                    if r != self.rank:
+                        opened[r] = ctx.p2p_open(h)
+            except Exception as e:  # pylint: disable=broad-except
+                _logger.info("band exchange: cannot map a peer buffer (%s)", e)
+                ok = False
+        else:
+            ok = False
+        flags = [None] * self.world
+        dist.all_gather_object(flags, bool(ok), group=self.group)
+        if not all(flags):
+            for a in opened.values():
+                ctx.p2p_close(a)
+            if own is not None:
+                dist.barrier(group=self.group)      # nobody maps it any more
+                ctx.p2p_free(own)
+            return
+        addrs = [own if r == self.rank else opened[r] for r in range(self.world)]
+        self._p2p = {
+            "own": own, "opened": opened,
+            "peers": torch.tensor(addrs, dtype=torch.int64, device=dev),
+            "done": torch.zeros(1, dtype=torch.int64, device=dev),
+            "status": torch.zeros(1, dtype=torch.int32, device=dev),
+            "epoch": 0,
+        }
+        self.mode = "p2p"
+
+    def close(self) -> None:
+        """Unmap the peers' buffers and free this rank's (collective: every rank
+        calls it)."""
+        import torch
+        import torch.distributed as dist
+        if self._p2p is None:
+            return
+        from . import _lib
+        ctx = _lib.default_context(torch.device(self.device).index)
+        torch.cuda.synchronize(torch.device(self.device))
+        p, self._p2p, self.mode = self._p2p, None, "nccl"
+        for a in p["opened"].values():
+            ctx.p2p_close(a)
+        dist.barrier(group=self.group)
+        ctx.p2p_free(p["own"])
+
+    def p2p_failed(self) -> bool:
+        """True when a pull gave up waiting for a peer (host sync)."""
+        return self._p2p is not None and bool(self._p2p["status"].item())
 
     def gather_vertices(self, verts_local):
         """All ranks' vertices, (world * cap, 2), rank order (padded blocks)."""
@@ -257,6 +340,19 @@ class BandExchange:
             # small tensor ops (a 0.4 ms step notices every one of them)
             from . import _lib
             ctx = _lib.default_context(buf.device.index)
+            if self._p2p is not None:
+                # stores into the peers' buffers + epoch flags: no collective
+                p = self._p2p
+                p["epoch"] += 1
+                ctx.band_push(verts_local, n, self.cap, buf[r0 - origin],
+                              buf[r1 - 1 - origin], self._width, p["peers"], self.world,
+                              self.rank, p["epoch"], self.FAR, p["done"])
+                ctx.band_pull(p["own"], self.world, self.rank, self.cap, self._width,
+                              p["epoch"], self.verts,
+                              buf[r0 - 1 - origin] if self.rank > 0 else None,
+                              buf[r1 - origin] if self.rank < self.world - 1 else None,
+                              p["status"])
+                return self.verts
             ctx.band_pack(verts_local, n, self.cap, buf[r0 - origin], buf[r1 - 1 - origin],
                           self._width, self._send, self.FAR)
             dist.all_gather_into_tensor(self._recv.view(-1), self._send, group=self.group)

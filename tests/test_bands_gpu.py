@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 import ocsmesh_b200 as ob
-from ocsmesh_b200 import distributed as D, features as F, synthetic as S
+from ocsmesh_b200 import _lib, distributed as D, features as F, synthetic as S
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -126,3 +126,65 @@ def test_band_pack_unpack_blocks(ctx):
             assert bool((above == -1.0).all())
         if rank < world - 1:
             assert torch.equal(below, rows[rank + 1][0])
+
+
+def test_band_push_pull_peer_memory_emulated(ctx):
+    """ocsb_band_push / ocsb_band_pull (the exchange as stores into the peers'
+    buffers + epoch flags), 3 ranks emulated on one device: the 'peer' buffers
+    are three local ocsb_p2p_alloc buffers.  Two steps check the two slot
+    generations; a pull before a peer's push gives up (bounded wait) and says so."""
+    import torch
+    W, cap, world = 41, 7, 3
+    lib = _lib.load()
+    nbytes = lib.ocsb_band_p2p_bytes(world, cap, W)
+    assert nbytes == 2 * world * ((2 * W * 4 + 15) // 16 * 16 + cap * 16) + 256
+    bufs = [ctx.p2p_alloc(nbytes) for _ in range(world)]
+    assert all(len(h) == 64 for _, h in bufs)
+    peers = torch.tensor([a for a, _ in bufs], dtype=torch.int64, device="cuda")
+    done = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rng = np.random.default_rng(5)
+    try:
+        for epoch in (1, 2, 3):
+            rows = [torch.from_numpy(rng.random((2, W)).astype(np.float32)).cuda()
+                    for _ in range(world)]
+            verts = [torch.from_numpy(rng.random((n, 2))).cuda() for n in (4, 0, 7)]
+            for r in range(world):
+                ctx.band_push(verts[r], len(verts[r]), cap, rows[r][0], rows[r][1], W, peers,
+                              world, r, epoch, 1e13, done[r])
+            for rank in range(world):
+                out = torch.empty((world * cap, 2), dtype=torch.float64, device="cuda")
+                above = torch.full((W,), -1.0, dtype=torch.float32, device="cuda")
+                below = torch.full((W,), -1.0, dtype=torch.float32, device="cuda")
+                ctx.band_pull(bufs[rank][0], world, rank, cap, W, epoch, out,
+                              above if rank > 0 else None,
+                              below if rank < world - 1 else None, status)
+                torch.cuda.synchronize()
+                for r in range(world):
+                    n = len(verts[r])
+                    got = out[r * cap:(r + 1) * cap].cpu().numpy()
+                    if n:
+                        np.testing.assert_array_equal(got[:n], verts[r].cpu().numpy())
+                        assert (got[n:] == verts[r][-1].cpu().numpy()).all()
+                    else:
+                        assert (got == 1e13).all()
+                if rank > 0:
+                    assert torch.equal(above, rows[rank - 1][1])
+                if rank < world - 1:
+                    assert torch.equal(below, rows[rank + 1][0])
+            assert int(status.item()) == 0
+        # epoch 4: rank 1 never pushes -> rank 0's pull gives up after ~2 s
+        ctx.band_push(verts[0], len(verts[0]), cap, rows[0][0], rows[0][1], W, peers, world, 0,
+                      4, 1e13, done[0])
+        out = torch.empty((world * cap, 2), dtype=torch.float64, device="cuda")
+        ctx.band_pull(bufs[0][0], world, 0, cap, W, 4, out, None,
+                      torch.empty(W, dtype=torch.float32, device="cuda"), status)
+        torch.cuda.synchronize()
+        assert int(status.item()) == 1
+        with pytest.raises(_lib.OcsbError):
+            ctx.band_pull(bufs[0][0], world, 0, cap, W, 4, out,
+                          torch.empty(W, dtype=torch.float32, device="cuda"), None, status)
+    finally:
+        torch.cuda.synchronize()
+        for a, _ in bufs:
+            ctx.p2p_free(a)
