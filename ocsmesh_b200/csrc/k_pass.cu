@@ -57,6 +57,29 @@ constexpr int kDemRows = kT0 + 2;
 constexpr int kMaxFeat = 4, kMaxLim = 4;
 constexpr double kBig = 1e300;       // "no candidate" squared distance (finite)
 
+#ifdef OCSB_TIMELINE
+// tuning build only: first CTA start / last CTA end of each launch of a pass on
+// the GPU's global timer (ns) -- which launches really overlap
+__device__ unsigned long long g_timeline[8][2];
+__device__ __forceinline__ unsigned long long tl_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+struct TlScope {
+    int k;
+    __device__ explicit TlScope(int k_) : k(k_) {
+        if (threadIdx.x == 0) atomicMin(&g_timeline[k][0], tl_now());
+    }
+    __device__ ~TlScope() {
+        if (threadIdx.x == 0) atomicMax(&g_timeline[k][1], tl_now());
+    }
+};
+#define TL_SCOPE(k) TlScope tl_scope__(k)
+#else
+#define TL_SCOPE(k)
+#endif
+
 #ifdef OCSB_PASS_STATS
 // tuning build only (tools/pass_lab.py): list lengths and per-phase clocks
 // (one slot row per SM: no contention between SMs)
@@ -136,6 +159,7 @@ __device__ __forceinline__ int vg_cy(const VGrid &G, double y) {
 
 __global__ void vg_hist_kernel(VGrid G, const double2 *verts, int nv, int *counts,
                                int *far_flag) {
+    TL_SCOPE(0);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nv) return;
     const double2 v = verts[i];
@@ -169,6 +193,7 @@ __global__ void __launch_bounds__(1024) vg_scan_kernel(const int *counts, int n,
 }
 
 __global__ void vg_scatter_kernel(VGrid G, const double2 *verts, int nv, int *cursor) {
+    TL_SCOPE(1);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nv) return;
     const double2 v = verts[i];
@@ -395,6 +420,7 @@ constexpr int kRootThreads = OCSB_ROOT_THREADS;
 constexpr int kRootCap = 2048;
 
 __global__ void __launch_bounds__(kRootThreads) root_kernel(BuildArgs A) {
+    TL_SCOPE(2);
     constexpr int NW = kRootThreads / 32;
     __shared__ unsigned s_key[NW][5];
     __shared__ DomTable s_tab[NW];
@@ -1528,10 +1554,17 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         // an SM runs ONE shared-memory carveout at a time: the pyramid's launches
         // only fit beside the sweep's resident CTAs (which take the largest one)
         // when they ask for the same split of L1 / shared memory
-        OCSB_CUDA(cudaFuncSetAttribute(root_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                       (int)cudaSharedmemCarveoutMaxShared));
-        OCSB_CUDA(cudaFuncSetAttribute(l10_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                       (int)cudaSharedmemCarveoutMaxShared));
+        // (measured, profiles/r2c_split_lab.txt: with the preference set the root
+        //  launch runs slower beside the sweep and nothing is gained -- opt-in)
+        const char *cv = getenv("OCSB_PASS_SPLIT_CARVEOUT");
+        if (cv && atoi(cv) != 0) {
+            OCSB_CUDA(cudaFuncSetAttribute(root_kernel,
+                                           cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           (int)cudaSharedmemCarveoutMaxShared));
+            OCSB_CUDA(cudaFuncSetAttribute(l10_kernel,
+                                           cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           (int)cudaSharedmemCarveoutMaxShared));
+        }
         int lo_pri = 0, hi_pri = 0;
         OCSB_CUDA(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
         OCSB_CUDA(cudaStreamCreateWithPriority(&ctx->s_split, cudaStreamNonBlocking, lo_pri));
@@ -1768,6 +1801,26 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         }
         OCSB_LAUNCHED(ctx);
         OCSB_CHECK_LAUNCH();
+#ifdef OCSB_TIMELINE
+        if (getenv("OCSB_TIMELINE_PRINT")) {
+            static unsigned long long tl[8][2];
+            static int calls = 0;
+            cudaStreamSynchronize(ctx->stream);
+            cudaMemcpyFromSymbol(tl, g_timeline, sizeof(tl));
+            if (++calls % 8 == 0) {
+                unsigned long long t0 = ~0ull;
+                for (int i = 0; i < 8; ++i)
+                    if (tl[i][1]) t0 = std::min(t0, tl[i][0]);
+                fprintf(stderr, "PASS_STATS timeline(us) vg_hist,vg_scatter,root,l10,A,B:");
+                for (int i = 0; i < 6; ++i)
+                    fprintf(stderr, " [%.1f %.1f]", tl[i][1] ? (tl[i][0] - t0) * 1e-3 : -1.0,
+                            tl[i][1] ? (tl[i][1] - t0) * 1e-3 : -1.0);
+                fprintf(stderr, "\n");
+            }
+            for (int i = 0; i < 8; ++i) { tl[i][0] = ~0ull; tl[i][1] = 0; }
+            cudaMemcpyToSymbol(g_timeline, tl, sizeof(tl));
+        }
+#endif
 #ifdef OCSB_PASS_STATS
         if (getenv("OCSB_PASS_STATS_PRINT")) {
             static unsigned long long hs[160][32];

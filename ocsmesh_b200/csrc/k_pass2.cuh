@@ -373,6 +373,7 @@ __global__ void __launch_bounds__(kP2Threads, OCSB_PASS2_MIN_CTAS)
 pass2_kernel(const __grid_constant__ CUtensorMap tmap, const P2Args A) {
     extern __shared__ __align__(128) unsigned char p2_raw[];
     P2Smem &S = *reinterpret_cast<P2Smem *>(p2_raw);
+    TL_SCOPE(LIST ? 5 : 4);
 
     const int2 flags = *reinterpret_cast<const int2 *>(A.overflow);   // {overflow, far}
     if (flags.x || (A.sticky && *A.sticky)) return;
@@ -538,6 +539,7 @@ __global__ void __launch_bounds__(kL10Threads) l10_kernel(L0Args A) {
     __shared__ int s_nact, s_act[16];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int t1 = blockIdx.x;
+    TL_SCOPE(3);
     if (t1 >= A.n_parents || *A.overflow) return;
     const int wi = A.n_wins == 1 ? 0 : find_win(A.wins, A.n_wins, t1, 1);
     const PWin &W = A.wins[wi];
