@@ -202,6 +202,53 @@ __global__ void vg_scatter_kernel(VGrid G, const double2 *verts, int nv, int *cu
     G.sid[pos] = i;
 }
 
+// scan + scatter in one launch for grids of up to kVgFusedCells cells: every CTA
+// redoes the exclusive scan of the (small) histogram in shared memory instead of
+// waiting for a one-CTA scan launch of its own (that launch and the gaps around
+// it were ~25 us of the chain every step, profiles/r2c_split_lab.txt run 5);
+// positions inside a cell come from a zeroed fill counter
+constexpr int kVgFusedCells = 4096;
+
+__global__ void __launch_bounds__(256) vg_scan_scatter_kernel(VGrid G, const double2 *verts,
+                                                              int nv, const int *counts,
+                                                              int *fill) {
+    TL_SCOPE(1);
+    __shared__ int s_start[kVgFusedCells + 1];
+    __shared__ int s_warp[8];
+    const int ncell = (G.ncx + 2) * (G.ncy + 2);
+    const int per = (ncell + 255) / 256;
+    const int lo = min(ncell, (int)threadIdx.x * per), hi = min(ncell, lo + per);
+    int sum = 0;
+    for (int i = lo; i < hi; ++i) sum += counts[i];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    int base = 0;
+    for (int w = 0; w < wid; ++w) base += s_warp[w];
+    int run = base + inc - sum;
+    for (int i = lo; i < hi; ++i) {
+        s_start[i] = run;
+        run += counts[i];
+    }
+    if (threadIdx.x == 255) s_start[ncell] = run;
+    __syncthreads();
+    if (blockIdx.x == 0)
+        for (int i = threadIdx.x; i <= ncell; i += 256) G.start[i] = s_start[i];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    const double2 v = verts[i];
+    const int c = vg_cy(G, v.y) * (G.ncx + 2) + vg_cx(G, v.x);
+    const int pos = s_start[c] + atomicAdd(&fill[c], 1);
+    G.sv[pos] = v;
+    G.sid[pos] = i;
+}
+
 // very small vertex sets: histogram, scan and scatter in ONE launch of one CTA
 // -- the three launches above are pure launch latency at that size
 constexpr int kVgSmallCells = 8192;
@@ -1481,7 +1528,8 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         G.x0 = xmin; G.y0 = ymin;
         G.ncx = (int)(ext_x / cell) + 1; G.ncy = (int)(ext_y / cell) + 1;
         cnt_off[f] = n_counts;
-        n_counts += (size_t)(G.ncx + 2) * (G.ncy + 2);
+        // histogram + (fused scan / scatter) the fill counters behind it
+        n_counts += 2 * (size_t)(G.ncx + 2) * (G.ncy + 2);
     }
     unsigned long long *ctrs = nullptr;
     const size_t nctr = 2 * kMaxFeat + 2;
@@ -1640,12 +1688,20 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 vg_hist_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, counts, far_flag);
                 OCSB_LAUNCHED(ctx);
-                OCSB_TIME(ctx, KC_FEATURE_REFINE);
-                vg_scan_kernel<<<1, 1024, 0, ctx->stream>>>(counts, ncell, G.start, cursor);
-                OCSB_LAUNCHED(ctx);
-                OCSB_TIME(ctx, KC_FEATURE_REFINE);
-                vg_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, cursor);
-                OCSB_LAUNCHED(ctx);
+                if (ncell <= kVgFusedCells) {
+                    OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                    vg_scan_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
+                        G, verts, nv, counts, counts + ncell);
+                    OCSB_LAUNCHED(ctx);
+                } else {
+                    OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                    vg_scan_kernel<<<1, 1024, 0, ctx->stream>>>(counts, ncell, G.start, cursor);
+                    OCSB_LAUNCHED(ctx);
+                    OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                    vg_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv,
+                                                                               cursor);
+                    OCSB_LAUNCHED(ctx);
+                }
             }
             OCSB_CHECK_LAUNCH();
             if (split) {
