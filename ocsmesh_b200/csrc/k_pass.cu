@@ -1504,11 +1504,6 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     const bool coords_ok = std::max(std::max(fabs(xmin), fabs(xmax)),
                                     std::max(fabs(ymin), fabs(ymax))) <= 1e14;
 
-    ScratchGuard sg(ctx);
-    PWin *d_wins = nullptr;
-    OCSB_TRY(sg.get(&d_wins, (size_t)d.n_wins));
-    OCSB_TRY(ocsb_stage_upload(ctx, d_wins, wins.data(), sizeof(PWin) * d.n_wins));
-
     // ---- counters / flags --------------------------------------------------------
     // [0..2*nf): pool counters; then per feature a far flag; then the overflow flag
     // ... followed by the cell histograms of the feature ops' vertex grids: ONE
@@ -1531,9 +1526,35 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
         // histogram + (fused scan / scatter) the fill counters behind it
         n_counts += 2 * (size_t)(G.ncx + 2) * (G.ncy + 2);
     }
-    unsigned long long *ctrs = nullptr;
+    ScratchGuard sg(ctx);
     const size_t nctr = 2 * kMaxFeat + 2;
     const size_t zero_words = nctr + 8 + (n_counts + 1) / 2;
+    {
+        // every piece of scratch of a first attempt from ONE kept arena (the sizes
+        // restate the get() calls below; a later attempt's larger pools that do
+        // not fit fall back to their own allocations): a band step of a multi-GPU
+        // run is bound by host time, most of it stream-ordered malloc / free calls
+        auto pc = [](size_t count, size_t size) { return ScratchGuard::piece(count * size); };
+        size_t total = pc((size_t)d.n_wins, sizeof(PWin)) + pc(zero_words, 8) + 4096;
+        const bool amode = d.ext_overflow != nullptr;
+        for (int f = 0; f < d.nf; ++f) {
+            const size_t nv = (size_t)d.feats[f].nv;
+            const size_t ncell = (size_t)(grids[f].ncx + 2) * (grids[f].ncy + 2);
+            size_t cap2 = 4 * nv + 48 * (size_t)n2 + (1 << 16);
+            size_t cap1 = 4 * nv + 48 * (size_t)n1 + (1 << 16);
+            size_t cap0 = 8 * nv + 8 * (size_t)n0 + 48 * (size_t)n1 + (1 << 17);
+            if (amode) { cap2 <<= 1; cap1 <<= 1; cap0 <<= 1; }
+            total += pc(ncell, 4) + pc(ncell + 1, 4) + pc(nv, 16) + pc(nv, 4);  // vertex grid
+            total += 2 * pc((size_t)n2, 4) + pc(cap2, 4) + 2 * pc((size_t)n1, 4) + pc(cap1, 4) +
+                     pc(cap1, 16) + pc(cap2, 16);                                // 1024 / 256 px
+            total += pc((size_t)n0 * kSlot, 16) + pc(cap0, 16) + pc((size_t)n0, 4);  // 64 px
+        }
+        OCSB_TRY(sg.reserve_kept(total));
+    }
+    PWin *d_wins = nullptr;
+    OCSB_TRY(sg.get(&d_wins, (size_t)d.n_wins));
+    OCSB_TRY(ocsb_stage_upload(ctx, d_wins, wins.data(), sizeof(PWin) * d.n_wins));
+    unsigned long long *ctrs = nullptr;
     OCSB_TRY(sg.get(&ctrs, zero_words));
     int *counts_all = reinterpret_cast<int *>(ctrs + nctr + 8);
     // {pool overflow, far vertex}: one 8-byte word the tile kernel reads at once
@@ -1630,6 +1651,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
 
     for (int attempt = 0; attempt < 6; ++attempt) {
         ScratchGuard pools(ctx);
+        pools.share(sg);        // carve on from where the call-level pieces end
         OCSB_CUDA(cudaMemsetAsync(ctrs, 0, zero_words * sizeof(*ctrs), ctx->stream));
         int *sticky = d.sticky ? d.ext_overflow : nullptr;
         TileArgs T;

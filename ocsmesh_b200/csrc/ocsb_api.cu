@@ -188,6 +188,7 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
         if (ctx->s_win[i]) cudaStreamDestroy(ctx->s_win[i]);
         if (ctx->ev_win[i]) cudaEventDestroy(ctx->ev_win[i]);
     }
+    if (ctx->keep_arena) cudaFree(ctx->keep_arena);
     if (ctx->s_split) cudaStreamDestroy(ctx->s_split);
     for (auto &e : ctx->ev_split)
         if (e) cudaEventDestroy(e);
@@ -207,7 +208,7 @@ extern "C" int32_t ocsb_ctx_destroy(ocsb_ctx *ctx) {
 int32_t ocsb_stage_upload(ocsb_ctx *ctx, void *dst_dev, const void *src, size_t bytes) {
     if (bytes == 0) return OCSB_OK;
     ocsb_ctx::StageSlot &sl = ctx->stage_ring[ctx->stage_next];
-    ctx->stage_next = (ctx->stage_next + 1) % 8;
+    ctx->stage_next = (ctx->stage_next + 1) % 32;
     if (sl.used) OCSB_CUDA(cudaEventSynchronize(sl.ev));   // its last upload has left
     if (!sl.ev) OCSB_CUDA(cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming));
     if (sl.bytes < bytes) {
@@ -227,6 +228,13 @@ int32_t ocsb_stage_upload(ocsb_ctx *ctx, void *dst_dev, const void *src, size_t 
 
 extern "C" int32_t ocsb_ctx_set_stream(ocsb_ctx *ctx, void *stream) {
     OCSB_REQUIRE(ctx, "ctx is NULL");
+    if ((cudaStream_t)stream != ctx->stream && ctx->keep_arena) {
+        // the kept scratch arena is only ordered on the old stream
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(ctx->keep_arena);
+        ctx->keep_arena = nullptr;
+        ctx->keep_arena_bytes = 0;
+    }
     if (ctx->own_stream) {
         cudaStreamSynchronize(ctx->stream);
         cudaStreamDestroy(ctx->stream);
@@ -330,6 +338,11 @@ extern "C" int32_t ocsb_ctx_trim(ocsb_ctx *ctx) {
         ctx->spl_coef = nullptr;
         ctx->spl_key = nullptr;
         ctx->spl_bytes = 0;
+    }
+    if (ctx->keep_arena) {
+        cudaFree(ctx->keep_arena);
+        ctx->keep_arena = nullptr;
+        ctx->keep_arena_bytes = 0;
     }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess)
@@ -2152,6 +2165,7 @@ extern "C" int32_t ocsb_hfun_op_windows(
     };
     cudaStream_t main_stream = ctx->stream;
     int32_t status = OCSB_OK;
+    ctx->keep_ok = false;       // the windows' passes run side by side: own scratch each
     for (int32_t k = 0; k < n_wins && status == OCSB_OK; ++k) {
         const void *zp; const float *ip; float *opp;
         ptrs(k, &zp, &ip, &opp);
@@ -2169,6 +2183,7 @@ extern "C" int32_t ocsb_hfun_op_windows(
             cudaEventRecord(done.ev[k], ctx->stream);
     }
     ctx->stream = main_stream;
+    ctx->keep_ok = true;
     for (int i = 0; i < ns; ++i) {               // join
         cudaEventRecord(ctx->ev_win[i], ctx->s_win[i]);
         cudaStreamWaitEvent(ctx->stream, ctx->ev_win[i], 0);

@@ -88,7 +88,7 @@ struct ocsb_ctx {
         size_t bytes = 0;
         cudaEvent_t ev = nullptr;
         bool used = false;
-    } stage_ring[8];
+    } stage_ring[32];
     int stage_next = 0;
     // copy streams + events of ocsb_hfun_pass (created on first use)
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
@@ -97,6 +97,12 @@ struct ocsb_ctx {
     // worker streams of ocsb_hfun_op_windows (created on first use)
     cudaStream_t s_win[OCSB_WIN_STREAMS] = {};
     cudaEvent_t ev_win[OCSB_WIN_STREAMS] = {};
+    // scratch arena kept between passes (k_pass_tiled): a band step of a multi-GPU
+    // run is bound by HOST time, and ~40 stream-ordered malloc / free calls per
+    // pass were most of it.  Only ever used by work ordered on `stream`
+    void *keep_arena = nullptr;
+    size_t keep_arena_bytes = 0;
+    bool keep_ok = true;        // false while `stream` is swapped to a worker stream
     // second stream of the split pass (limiter sweep beside the candidate pyramid)
     cudaStream_t s_split = nullptr;
     cudaEvent_t ev_split[2] = {nullptr, nullptr};
@@ -141,6 +147,28 @@ struct ScratchGuard {
         arena_left = bytes;
         return OCSB_OK;
     }
+    // The same from the context's kept arena (grown when too small, never freed
+    // by the guard).  Larger requests than kKeepMax take a plain reserve().
+    static constexpr size_t kKeepMax = (size_t)384 << 20;
+    int32_t reserve_kept(size_t bytes) {
+        if (bytes > kKeepMax || !ctx->keep_ok) return reserve(bytes);
+        if (bytes > ctx->keep_arena_bytes) {
+            if (ctx->keep_arena) ocsb_free(ctx, ctx->keep_arena);
+            ctx->keep_arena = nullptr;
+            ctx->keep_arena_bytes = 0;
+            void *p = nullptr;
+            const size_t want = bytes + bytes / 4;
+            int32_t s = ocsb_alloc(ctx, &p, want);
+            if (s != OCSB_OK) return s;
+            ctx->keep_arena = p;
+            ctx->keep_arena_bytes = want;
+        }
+        arena = reinterpret_cast<char *>(ctx->keep_arena);
+        arena_left = ctx->keep_arena_bytes;
+        return OCSB_OK;
+    }
+    // carve from where another guard stands, without owning anything
+    void share(const ScratchGuard &o) { arena = o.arena; arena_left = o.arena_left; }
     static size_t piece(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
     template <typename T> int32_t get(T **out, size_t count) {
         const size_t need = piece(count * sizeof(T) ? count * sizeof(T) : 16);
