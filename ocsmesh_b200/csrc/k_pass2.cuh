@@ -197,6 +197,32 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
         // lanes outside a partial rect leave early -- unless the chunk-wise path
         // with its warp-wide votes follows (their loads / stores are masked)
         if (!FULL && !refilter && (hr > sr1 || gcol > sc1)) break;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = 3.402823466e+38f;
+        auto load_old = [&]() {
+            if (!HAS_OLD) return;
+            const float *src = in0 + (long long)(half * 2) * A.in_stride;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                if (!FULL && hr + j > sr1) continue;
+                const float *orow = src + j * A.in_stride;
+                if (vec_r) {
+                    const float4 v4 = __ldcs(reinterpret_cast<const float4 *>(orow));
+                    o[j * 4 + 0] = v4.x; o[j * 4 + 1] = v4.y;
+                    o[j * 4 + 2] = v4.z; o[j * 4 + 3] = v4.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (gcol + k <= sc1) o[j * 4 + k] = orow[k];
+                }
+            }
+        };
+        // the feature-only form (second half of a split pass) is bound by the
+        // latency of these loads when they follow the distance evaluation
+        // (long-scoreboard stalls, profiles/r2h_ncu_full_summary.txt): issue them first
+        constexpr bool EARLY_OLD = HAS_OLD && HAS_FEAT && !HAS_LIM;
+        if (EARLY_OLD) load_old();
         float vf[8];
         if (HAS_FEAT) {
             if (ntile == 0) {
@@ -266,26 +292,7 @@ __device__ __forceinline__ void p2_pixels(const P2Args &A, const float *sdem,
             }
         }
         // ---- pre-op values -------------------------------------------------------------
-        float o[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = 3.402823466e+38f;
-        if (HAS_OLD) {
-            const float *src = in0 + (long long)(half * 2) * A.in_stride;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                if (!FULL && hr + j > sr1) continue;
-                const float *orow = src + j * A.in_stride;
-                if (vec_r) {
-                    const float4 v4 = __ldcs(reinterpret_cast<const float4 *>(orow));
-                    o[j * 4 + 0] = v4.x; o[j * 4 + 1] = v4.y;
-                    o[j * 4 + 2] = v4.z; o[j * 4 + 3] = v4.w;
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (gcol + k <= sc1) o[j * 4 + k] = orow[k];
-                }
-            }
-        }
+        if (!EARLY_OLD) load_old();
         if (HAS_FEAT) {
             // clamp(vf); min(old, .); A10 clamp: fused (monotone, idempotent)
 #pragma unroll
