@@ -209,17 +209,37 @@ __global__ void vg_scatter_kernel(VGrid G, const double2 *verts, int nv, int *cu
 // positions inside a cell come from a zeroed fill counter
 constexpr int kVgFusedCells = 4096;
 
+// WITH_HIST: the histogram too, in the same launch -- the CTAs meet at a counter
+// (`bar`, zeroed with the histogram).  Only launched with a grid that is resident
+// as a whole (<= 2 CTAs per SM of 256 threads), so the spin cannot starve anybody.
+template <bool WITH_HIST>
 __global__ void __launch_bounds__(256) vg_scan_scatter_kernel(VGrid G, const double2 *verts,
-                                                              int nv, const int *counts,
-                                                              int *fill) {
+                                                              int nv, int *counts, int *fill,
+                                                              int *far_flag, int *bar) {
     TL_SCOPE(1);
     __shared__ int s_start[kVgFusedCells + 1];
     __shared__ int s_warp[8];
+    if (WITH_HIST) {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i < nv) {
+            const double2 v = verts[i];
+            atomicAdd(&counts[vg_cy(G, v.y) * (G.ncx + 2) + vg_cx(G, v.x)], 1);
+            if (!(fabs(v.x) <= 1e14 && fabs(v.y) <= 1e14)) *far_flag = 1;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(bar, 1);
+            while (*(volatile int *)bar < (int)gridDim.x) {}
+            __threadfence();
+        }
+        __syncthreads();
+    }
     const int ncell = (G.ncx + 2) * (G.ncy + 2);
     const int per = (ncell + 255) / 256;
     const int lo = min(ncell, (int)threadIdx.x * per), hi = min(ncell, lo + per);
     int sum = 0;
-    for (int i = lo; i < hi; ++i) sum += counts[i];
+    for (int i = lo; i < hi; ++i) sum += __ldcg(counts + i);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int inc = sum;
 #pragma unroll
@@ -234,7 +254,7 @@ __global__ void __launch_bounds__(256) vg_scan_scatter_kernel(VGrid G, const dou
     int run = base + inc - sum;
     for (int i = lo; i < hi; ++i) {
         s_start[i] = run;
-        run += counts[i];
+        run += __ldcg(counts + i);
     }
     if (threadIdx.x == 255) s_start[ncell] = run;
     __syncthreads();
@@ -1553,7 +1573,19 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
     }
     PWin *d_wins = nullptr;
     OCSB_TRY(sg.get(&d_wins, (size_t)d.n_wins));
-    OCSB_TRY(ocsb_stage_upload(ctx, d_wins, wins.data(), sizeof(PWin) * d.n_wins));
+    {
+        const size_t wb = sizeof(PWin) * (size_t)d.n_wins;
+        const bool at_head = (void *)d_wins == ctx->keep_arena;
+        if (at_head && ctx->wins_cache.size() == wb &&
+            memcmp(ctx->wins_cache.data(), wins.data(), wb) == 0) {
+            // the same table is already there (uploaded by an earlier pass of this stream)
+        } else {
+            OCSB_TRY(ocsb_stage_upload(ctx, d_wins, wins.data(), wb));
+            if (at_head)
+                ctx->wins_cache.assign((const unsigned char *)wins.data(),
+                                       (const unsigned char *)wins.data() + wb);
+        }
+    }
     unsigned long long *ctrs = nullptr;
     OCSB_TRY(sg.get(&ctrs, zero_words));
     int *counts_all = reinterpret_cast<int *>(ctrs + nctr + 8);
@@ -1706,14 +1738,22 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 vg_build_small_kernel<<<1, 1024, 0, ctx->stream>>>(G, verts, nv, far_flag);
                 OCSB_LAUNCHED(ctx);
+            } else if (ncell <= kVgFusedCells && (nv + 255) / 256 <= 2 * ctx->num_sms &&
+                       ctx->keep_ok) {      // (not while passes run side by side on worker streams)
+                // histogram, scan and scatter in ONE launch (grid-wide counter barrier)
+                int *bar = reinterpret_cast<int *>(ctrs + nctr) + 10 + f;
+                OCSB_TIME(ctx, KC_FEATURE_REFINE);
+                vg_scan_scatter_kernel<true><<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
+                    G, verts, nv, counts, counts + ncell, far_flag, bar);
+                OCSB_LAUNCHED(ctx);
             } else {
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 vg_hist_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(G, verts, nv, counts, far_flag);
                 OCSB_LAUNCHED(ctx);
                 if (ncell <= kVgFusedCells) {
                     OCSB_TIME(ctx, KC_FEATURE_REFINE);
-                    vg_scan_scatter_kernel<<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
-                        G, verts, nv, counts, counts + ncell);
+                    vg_scan_scatter_kernel<false><<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
+                        G, verts, nv, counts, counts + ncell, far_flag, nullptr);
                     OCSB_LAUNCHED(ctx);
                 } else {
                     OCSB_TIME(ctx, KC_FEATURE_REFINE);

@@ -234,6 +234,7 @@ extern "C" int32_t ocsb_ctx_set_stream(ocsb_ctx *ctx, void *stream) {
         cudaFree(ctx->keep_arena);
         ctx->keep_arena = nullptr;
         ctx->keep_arena_bytes = 0;
+        ctx->wins_cache.clear();
     }
     if (ctx->own_stream) {
         cudaStreamSynchronize(ctx->stream);
@@ -343,6 +344,7 @@ extern "C" int32_t ocsb_ctx_trim(ocsb_ctx *ctx) {
         cudaFree(ctx->keep_arena);
         ctx->keep_arena = nullptr;
         ctx->keep_arena_bytes = 0;
+        ctx->wins_cache.clear();
     }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess)

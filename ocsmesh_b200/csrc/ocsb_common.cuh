@@ -103,6 +103,9 @@ struct ocsb_ctx {
     void *keep_arena = nullptr;
     size_t keep_arena_bytes = 0;
     bool keep_ok = true;        // false while `stream` is swapped to a worker stream
+    // the window table last uploaded to the head of the kept arena (a step that
+    // repeats the previous table skips the upload)
+    std::vector<unsigned char> wins_cache;
     // second stream of the split pass (limiter sweep beside the candidate pyramid)
     cudaStream_t s_split = nullptr;
     cudaEvent_t ev_split[2] = {nullptr, nullptr};
@@ -156,6 +159,7 @@ struct ScratchGuard {
             if (ctx->keep_arena) ocsb_free(ctx, ctx->keep_arena);
             ctx->keep_arena = nullptr;
             ctx->keep_arena_bytes = 0;
+            ctx->wins_cache.clear();
             void *p = nullptr;
             const size_t want = bytes + bytes / 4;
             int32_t s = ocsb_alloc(ctx, &p, want);
