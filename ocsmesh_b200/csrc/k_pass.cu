@@ -215,7 +215,8 @@ constexpr int kVgFusedCells = 4096;
 template <bool WITH_HIST>
 __global__ void __launch_bounds__(256) vg_scan_scatter_kernel(VGrid G, const double2 *verts,
                                                               int nv, int *counts, int *fill,
-                                                              int *far_flag, int *bar) {
+                                                              int *far_flag, int *bar,
+                                                              int *overflow, int *sticky) {
     TL_SCOPE(1);
     __shared__ int s_start[kVgFusedCells + 1];
     __shared__ int s_warp[8];
@@ -230,7 +231,17 @@ __global__ void __launch_bounds__(256) vg_scan_scatter_kernel(VGrid G, const dou
         if (threadIdx.x == 0) {
             __threadfence();
             atomicAdd(bar, 1);
-            while (*(volatile int *)bar < (int)gridDim.x) {}
+            // bounded (~1 s): if the grid is ever not resident as a whole the pass
+            // is flagged like a pool overflow (the host redoes it) instead of hanging
+            long long spins = 0;
+            while (*(volatile int *)bar < (int)gridDim.x) {
+                if (++spins > 10000000ll) {
+                    *overflow = 1;
+                    if (sticky) *sticky = 1;
+                    break;
+                }
+                __nanosleep(100);
+            }
             __threadfence();
         }
         __syncthreads();
@@ -1744,7 +1755,7 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 int *bar = reinterpret_cast<int *>(ctrs + nctr) + 10 + f;
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
                 vg_scan_scatter_kernel<true><<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
-                    G, verts, nv, counts, counts + ncell, far_flag, bar);
+                    G, verts, nv, counts, counts + ncell, far_flag, bar, overflow, sticky);
                 OCSB_LAUNCHED(ctx);
             } else {
                 OCSB_TIME(ctx, KC_FEATURE_REFINE);
@@ -1753,7 +1764,8 @@ int32_t k_pass_tiled(ocsb_ctx *ctx, const PassDesc &d) {
                 if (ncell <= kVgFusedCells) {
                     OCSB_TIME(ctx, KC_FEATURE_REFINE);
                     vg_scan_scatter_kernel<false><<<(nv + 255) / 256, 256, 0, ctx->stream>>>(
-                        G, verts, nv, counts, counts + ncell, far_flag, nullptr);
+                        G, verts, nv, counts, counts + ncell, far_flag, nullptr, overflow,
+                        sticky);
                     OCSB_LAUNCHED(ctx);
                 } else {
                     OCSB_TIME(ctx, KC_FEATURE_REFINE);

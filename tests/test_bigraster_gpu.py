@@ -180,3 +180,49 @@ def test_fast_collector_errors(ctx):
     coll.add_constant_value(50.0)
     with pytest.raises(NotImplementedError, match="one projected CRS"):
         coll.apply()
+
+
+def test_fast_collector_dispatches_every_kind_in_reference_order(ctx):
+    """Line features, patches and the constraint kinds go to the ONE big hfun in
+    the order of collector.py:2444-2495 (contours, limiters, constant values,
+    line features, patches, constraints): same raster as applying the calls by
+    hand to an HfunRaster on the same big raster (each op is pinned to the
+    oracle in its own test file)."""
+    (za, ta, _), (zb, tb, mb) = _inputs()
+    ga = ob.Raster.from_numpy(za, ta, crs=32618)
+    gb = ob.Raster.from_numpy(zb, tb, crs=32618, mask=mb)
+    x0, ytop = ta[2], ta[5]
+    line = np.array([[x0 + 300.0, ytop - 400.0], [x0 + 2500.0, ytop - 900.0],
+                     [x0 + 4200.0, ytop - 2100.0]])
+    ring = np.array([[x0 + 800.0, ytop - 600.0], [x0 + 2200.0, ytop - 650.0],
+                     [x0 + 2000.0, ytop - 1900.0], [x0 + 900.0, ytop - 1700.0]])
+    coll = ob.Hfun([ga, gb], hmin=30.0, hmax=900.0, method='fast', nprocs=64)
+    # recorded in an order that differs from the order of application
+    coll.add_region_constraint(70.0, [ring], crs=32618, value_type='max', rate=0.02)
+    coll.add_patch([ring], target_size=45.0)
+    coll.add_feature([line], 0.004, 50.0)
+    coll.add_topo_bound_constraint(300.0, upper_bound=-10.0, value_type='max', rate=0.01)
+    coll.add_constant_value(200.0, lower_bound=0.0)
+    coll.add_gradient_delimiter(hmin=40.0, hmax=700.0, source_index=1)
+    coll.add_contour(0.0, 0.003, 40.0)
+    big = coll.apply()
+
+    ref = ob.HfunRaster(big.raster, hmin=30.0, hmax=900.0)
+    for src in (ga, gb):
+        lines = src.get_contour(0.0)
+        if lines:
+            ref.add_feature(lines, 0.003, 40.0)
+    ref.add_subtidal_flow_limiter(40.0, 700.0, -99990, None)
+    ref.add_constant_value(200.0, 0.0, None)
+    ref.add_feature([line], 0.004, 50.0)
+    ref.add_patch([ring], None, 45.0)
+    ref.add_region_constraint(70.0, [ring], crs=32618, value_type='max', rate=0.02)
+    ref.add_topo_bound_constraint(300.0, upper_bound=-10.0, value_type='max', rate=0.01)
+    np.testing.assert_array_equal(big.get_values(), ref.get_values())
+    vals = big.get_values()
+    assert (vals < 900.0).any() and len(np.unique(vals)) > 50
+    # only raster 1 is referred to by index, but the constant value and the
+    # constraints name no source: both inputs were warped
+    dem = big.raster.get_values(band=1)
+    X = big.raster.transform[2] + (np.arange(big.raster.width) + 0.5) * big.raster.transform[0]
+    assert (dem[:, X < tb[2]] != -99999).any()
