@@ -127,6 +127,54 @@ contour_count_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int n
     }
 }
 
+// the same for up to kMaxLevels levels in ONE sweep of the DEM (add_contour with
+// a level list: the count sweep is the O(pixels) part, the emit sweep skips the
+// chunks without segments): counts[l * nblk + b]
+constexpr int kMaxLevels = 4;
+template <typename T> struct LevelSet { T lt[kMaxLevels]; int n; };
+
+template <typename T>
+__global__ void __launch_bounds__(kCellThreads)
+contour_count_multi_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
+                           int nblk, LevelSet<T> L, int vec, int *__restrict__ counts) {
+    __shared__ int s_warp[2][kMaxLevels][kCellThreads / 32];
+    int buf = 0;
+    for (int b = blockIdx.x; b < nblk; b += gridDim.x, buf ^= 1) {
+        const int jr = b / nbx;
+        const int j = jb + jr;
+        const int i = (b - jr * nbx) * kCellsPerCta + threadIdx.x * kCellsPerThread;
+        int n[kMaxLevels];
+#pragma unroll
+        for (int l = 0; l < kMaxLevels; ++l) n[l] = 0;
+        if (i < w - 1) {
+            T r0[5], r1[5];
+            load_rows(dem, zs, j, i, w, vec != 0, r0, r1);
+#pragma unroll
+            for (int l = 0; l < kMaxLevels; ++l)
+                if (l < L.n) {
+#pragma unroll
+                    for (int k = 0; k < kCellsPerThread; ++k)
+                        if (i + k < w - 1)
+                            n[l] += code_count(
+                                cell_code(r0[k], r0[k + 1], r1[k], r1[k + 1], L.lt[l]));
+                }
+        }
+#pragma unroll
+        for (int l = 0; l < kMaxLevels; ++l) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) n[l] += __shfl_xor_sync(0xffffffffu, n[l], o);
+            if ((threadIdx.x & 31) == 0) s_warp[buf][l][threadIdx.x >> 5] = n[l];
+        }
+        __syncthreads();   // double-buffered: one barrier per chunk is enough
+        if ((int)threadIdx.x < L.n) {
+            int t = 0;
+#pragma unroll
+            for (int k = 0; k < kCellThreads / 32; ++k) t += s_warp[buf][threadIdx.x][k];
+            counts[(int64_t)threadIdx.x * nblk + b] = t;
+        }
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kCellThreads)
 contour_emit_kernel(const T *__restrict__ dem, int64_t zs, int w, int jb, int nbx,
@@ -291,6 +339,99 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
         contour_emit_kernel<double><<<grid, kCellThreads, 0, ctx->stream>>>(
             (const double *)dem, zs, w, jb, nbx, (int)nblk, level, level, vec, ax, ay, counts, total,
             edges, pts);
+    OCSB_LAUNCHED(ctx);
+    OCSB_CHECK_LAUNCH();
+    return OCSB_OK;
+}
+
+
+// ---- level lists: one count sweep for all levels, one emit launch per level ----
+int k_contour_max_levels() { return kMaxLevels; }
+
+static float level_threshold_f32(double level) {
+    // largest float <= level: z > ltf  <=>  (double)z > level for every float z
+    float ltf = (float)level;
+    if ((double)ltf > level) ltf = nextafterf(ltf, -INFINITY);
+    return ltf;
+}
+
+// counts / offsets of `nl` levels (nl <= k_contour_max_levels()): after the call
+// offsets[l * nblk + b] is the exclusive scan of level l's chunk counts,
+// totals_dev[l] / totals[l] its number of segments.  One host sync.
+int32_t k_contour_count_levels(ocsb_ctx *ctx, ScratchGuard &sg, const void *dem, int dem_dtype,
+                               int64_t zs, int w, int jb, int je, const double *levels, int nl,
+                               int **offsets, unsigned long long **totals_dev,
+                               int64_t *totals, int64_t *nblk_out) {
+    OCSB_REQUIRE(nl >= 1 && nl <= kMaxLevels, "k_contour_count_levels: bad level count");
+    const int nbx = (w - 1 + kCellsPerCta - 1) / kCellsPerCta;
+    const int vec = (((uintptr_t)dem & 15) == 0 && zs % 4 == 0) ? 1 : 0;
+    const int64_t nblk = (int64_t)nbx * (je - jb);
+    OCSB_REQUIRE(nblk * nl < 2147483647ll, "ocsb_contour: window too large");
+    *nblk_out = nblk;
+    const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)ctx->num_sms * 8);
+    int *counts = nullptr, *sums = nullptr;
+    unsigned long long *tot = nullptr;
+    OCSB_TRY(sg.get(&counts, (size_t)(nblk * nl)));
+    OCSB_TRY(sg.get(&sums, (size_t)((nblk + 1023) / 1024)));
+    OCSB_TRY(sg.get(&tot, (size_t)kMaxLevels));
+    OCSB_TIME(ctx, KC_CONTOUR);
+    if (dem_dtype == OCSB_F32) {
+        LevelSet<float> L;
+        L.n = nl;
+        for (int l = 0; l < kMaxLevels; ++l) L.lt[l] = level_threshold_f32(levels[l < nl ? l : 0]);
+        contour_count_multi_kernel<float><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const float *)dem, zs, w, jb, nbx, (int)nblk, L, vec, counts);
+    } else {
+        LevelSet<double> L;
+        L.n = nl;
+        for (int l = 0; l < kMaxLevels; ++l) L.lt[l] = levels[l < nl ? l : 0];
+        contour_count_multi_kernel<double><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const double *)dem, zs, w, jb, nbx, (int)nblk, L, vec, counts);
+    }
+    OCSB_LAUNCHED(ctx);
+    for (int l = 0; l < nl; ++l) {
+        OCSB_TIME(ctx, KC_CONTOUR);
+        scan_counts(counts + (int64_t)l * nblk, nblk, sums, tot + l, ctx->stream);
+        OCSB_LAUNCHED(ctx);
+        ctx->launches += 2;
+    }
+    OCSB_CHECK_LAUNCH();
+    unsigned long long host_tot[kMaxLevels] = {};
+    unsigned long long *bounce = ctx->pinned ? (unsigned long long *)ctx->pinned : host_tot;
+    OCSB_CUDA(cudaMemcpyAsync(bounce, tot, sizeof(*tot) * nl, cudaMemcpyDeviceToHost,
+                              ctx->stream));
+    OCSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int l = 0; l < nl; ++l) {
+        OCSB_REQUIRE(bounce[l] < 2147483647ull,
+                     "ocsb_contour_segments: %llu segments exceed the limit", bounce[l]);
+        totals[l] = (int64_t)bounce[l];
+    }
+    *offsets = counts;
+    *totals_dev = tot;
+    return OCSB_OK;
+}
+
+// emit launch of one level from its scanned chunk offsets (edges / pts hold
+// `total` segments)
+int32_t k_contour_emit_level(ocsb_ctx *ctx, const void *dem, int dem_dtype, int64_t zs, int w,
+                             int jb, int je, double level, LinAxis ax, LinAxis ay,
+                             const int *offsets, const unsigned long long *total_dev,
+                             int64_t *edges, double *pts) {
+    OCSB_REQUIRE((((uintptr_t)edges | (uintptr_t)pts) & 15) == 0,
+                 "ocsb_contour_segments: edges / pts must be 16-byte aligned");
+    const int nbx = (w - 1 + kCellsPerCta - 1) / kCellsPerCta;
+    const int vec = (((uintptr_t)dem & 15) == 0 && zs % 4 == 0) ? 1 : 0;
+    const int64_t nblk = (int64_t)nbx * (je - jb);
+    const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)ctx->num_sms * 8);
+    OCSB_TIME(ctx, KC_CONTOUR);
+    if (dem_dtype == OCSB_F32)
+        contour_emit_kernel<float><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const float *)dem, zs, w, jb, nbx, (int)nblk, level, level_threshold_f32(level), vec,
+            ax, ay, offsets, total_dev, edges, pts);
+    else
+        contour_emit_kernel<double><<<grid, kCellThreads, 0, ctx->stream>>>(
+            (const double *)dem, zs, w, jb, nbx, (int)nblk, level, level, vec, ax, ay, offsets,
+            total_dev, edges, pts);
     OCSB_LAUNCHED(ctx);
     OCSB_CHECK_LAUNCH();
     return OCSB_OK;

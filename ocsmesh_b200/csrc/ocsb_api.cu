@@ -1132,10 +1132,38 @@ extern "C" int32_t ocsb_contour_points(ocsb_ctx *ctx, const ocsb_win *win, const
     std::vector<double *> parts;
     std::vector<int64_t> counts;
     int64_t total = 0;
-    for (int l = 0; l < n_levels; ++l) {
+    for (int l = 0; l < n_levels; ++l)
         OCSB_REQUIRE(!ocsb_is_none(levels[l]), "ocsb_contour_points: level is NaN");
+    // a level list: ONE count sweep of the DEM for all levels (the O(pixels)
+    // part), then an emit launch per level that only visits chunks with segments
+    const int w_ = win->width, h_ = win->height;
+    int rb_ = 0, re_ = 0;
+    OCSB_TRY(win_band(win, "ocsb_contour", &rb_, &re_));
+    const int je_ = re_ < h_ - 1 ? re_ : h_ - 1;
+    const bool multi = n_levels >= 2 && n_levels <= k_contour_max_levels() && w_ >= 2 &&
+                       je_ > rb_;
+    int *lvl_offsets = nullptr;
+    unsigned long long *lvl_totals_dev = nullptr;
+    int64_t lvl_totals[8] = {}, lvl_nblk = 0;
+    LinAxis cax, cay;
+    win_axes(win, &cax, &cay);
+    if (multi)
+        OCSB_TRY(k_contour_count_levels(ctx, sg, dem, dem_dtype, dem_stride, w_, rb_, je_, levels,
+                                        n_levels, &lvl_offsets, &lvl_totals_dev, lvl_totals,
+                                        &lvl_nblk));
+    for (int l = 0; l < n_levels; ++l) {
         int64_t *edges = nullptr, n = 0, *off = nullptr, n_xy = 0, n_lines = 0, np = 0;
         double *pts = nullptr, *xy = nullptr, *rs = nullptr;
+        if (multi) {
+            n = lvl_totals[l];
+            if (n > 0) {
+                OCSB_TRY(sg.get(&edges, (size_t)n * 2));
+                OCSB_TRY(sg.get(&pts, (size_t)n * 4));
+                OCSB_TRY(k_contour_emit_level(ctx, dem, dem_dtype, dem_stride, w_, rb_, je_,
+                                              levels[l], cax, cay, lvl_offsets + l * lvl_nblk,
+                                              lvl_totals_dev + l, edges, pts));
+            }
+        } else
         OCSB_TRY(level_segments(ctx, sg, win, dem, dem_dtype, dem_stride, levels[l], &edges,
                                 &pts, &n));
         OCSB_TRY(k_stitch_segments(ctx, sg, edges, pts, n, &xy, &off, &n_xy, &n_lines));

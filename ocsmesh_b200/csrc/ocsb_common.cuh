@@ -418,6 +418,17 @@ int32_t k_contour_segments(ocsb_ctx *ctx, const void *dem, int dem_dtype,
                            LinAxis ax, LinAxis ay, int64_t cap, int64_t *edges,
                            double *pts, int64_t *n_out);
 
+// k_contour.cu, level lists: ONE count sweep for all levels, an emit launch per level
+int k_contour_max_levels();
+int32_t k_contour_count_levels(ocsb_ctx *ctx, ScratchGuard &sg, const void *dem, int dem_dtype,
+                               int64_t zs, int w, int jb, int je, const double *levels, int nl,
+                               int **offsets, unsigned long long **totals_dev,
+                               int64_t *totals, int64_t *nblk_out);
+int32_t k_contour_emit_level(ocsb_ctx *ctx, const void *dem, int dem_dtype, int64_t zs, int w,
+                             int jb, int je, double level, LinAxis ax, LinAxis ay,
+                             const int *offsets, const unsigned long long *total_dev,
+                             int64_t *edges, double *pts);
+
 // k_stitch.cu (results are carved from the caller's ScratchGuard)
 int32_t k_stitch_segments(ocsb_ctx *ctx, ScratchGuard &sg, const int64_t *edges,
                           const double *pts, int64_t n, double **xy_out, int64_t **off_out,
