@@ -47,7 +47,7 @@ __all__ = [
     "min_combine", "apply_rate", "add_constant_value_window",
     "TopoConstConstraint", "TopoFuncConstraint", "CourantNumConstraint",
     "msh_t_source", "interpolate_nearest", "big_raster_geometry",
-    "resample_nearest", "create_big_raster",
+    "resample_nearest", "create_big_raster", "big_raster_selection",
 ]
 
 FLT_MAX = np.finfo(np.float32).max
@@ -1066,6 +1066,25 @@ def big_raster_geometry(rasters: Sequence[OracleRaster], hmin, nprocs: int):
     transform = (float(res), 0.0, float(x0 - res / 2), 0.0, -float(res),
                  float(y1 + res / 2))
     return transform, shape0, shape1, window_size
+
+
+def big_raster_selection(n_inputs: int, const_val_src, flow_lim_src, constraint_src):
+    """hfun/collector.py:2410-2426: input ``k`` is warped onto the big raster
+    only when some constant value, flow limiter or constraint refers to it
+    (source index ``None`` = every input).  Arguments: the source-index entry of
+    every recorded refinement of each kind.  Returns one flag per input."""
+    flags = []
+    for k in range(n_inputs):
+        ignore = True
+        for coll in (const_val_src, flow_lim_src, constraint_src):
+            for src_idx in coll:
+                if src_idx is None or k in src_idx:
+                    ignore = False
+                    break
+            if not ignore:
+                break
+        flags.append(not ignore)
+    return flags
 
 
 def resample_nearest(dst: np.ndarray, dst_transform, src: np.ndarray, src_transform,

@@ -93,3 +93,50 @@ def test_create_big_raster_selection():
     X = big.transform[2] + (np.arange(big.width) + 0.5) * big.transform[0]
     assert (only_b[:, X < 400.0] == -99999).all()
     np.testing.assert_array_equal(only_b[:, X >= 400.0], v[:, X >= 400.0])
+
+
+# ---- pinned to the reference's own source (tests/golden/make_golden_bigraster.py) ----
+import json
+import os
+from types import SimpleNamespace
+
+import pytest
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden",
+                                   "reference_golden_bigraster.json")))
+
+
+@pytest.mark.parametrize("g", GOLD, ids=[g["name"] for g in GOLD])
+def test_geometry_and_selection_equal_reference_source(g):
+    """Outputs of HfunCollector._create_big_raster (collector.py:2296-2442) run
+    from its lifted source: profile, transform, window size, fill, warped inputs."""
+    rasters = [O.OracleRaster(np.zeros(r["shape"], np.float32), r["transform"])
+               for r in g["rasters"]]
+    tr, w, h, ws = O.big_raster_geometry(rasters, g["hmin"], g["nprocs"])
+    assert (w, h) == (g["width"], g["height"])
+    assert list(tr) == g["transform"]
+    assert ws == g["chunk_size"]
+    assert g["dtype"] == "float32" and g["count"] == 1
+    assert all(fw["value"] == -99999.0 and fw["dtype"] == "float32" for fw in g["fill_writes"])
+    sel = O.big_raster_selection(len(rasters), g["const_val_src"], g["flow_lim_src"],
+                                 g["constraint_src"])
+    # warped in list order (the last one wins on overlaps)
+    assert [k for k, f in enumerate(sel) if f] == g["warped_in_order"]
+
+
+@pytest.mark.parametrize("g", GOLD, ids=[g["name"] for g in GOLD])
+def test_product_collector_logic_equals_reference_source(g):
+    """The product's host logic (no device work in these two methods)."""
+    from ocsmesh_b200.hfun import HfunCollector
+    from ocsmesh_b200.raster import Affine
+    coll = HfunCollector.__new__(HfunCollector)
+    coll._hfuns = [SimpleNamespace(raster=SimpleNamespace(src=SimpleNamespace(
+        shape=tuple(r["shape"]), transform=Affine(*r["transform"])))) for r in g["rasters"]]
+    coll._nprocs, coll._hmin = g["nprocs"], g["hmin"]
+    coll._const_val_info = [(s, None, None, 1.0) for s in g["const_val_src"]]
+    coll._flow_lim_info = [(s, None, None, None, None) for s in g["flow_lim_src"]]
+    coll._constraint_info = [(s, "add_topo_bound_constraint", (), {}) for s in g["constraint_src"]]
+    tr, w, h, ws = coll._big_raster_geometry()
+    assert (w, h, ws) == (g["width"], g["height"], g["chunk_size"])
+    assert list(tr) == g["transform"]
+    assert [k for k in range(len(g["rasters"])) if coll._needs_warp(k)] == g["warped_in_order"]
