@@ -128,25 +128,38 @@ def _read_segments(path, offsets, counts, width, height, spp, dtype, planar, seg
     if len(offsets) < per_plane * planes:
         raise ValueError(f"{path}: {len(offsets)} segments, {per_plane * planes} expected")
     out = np.empty((spp, height, width), dtype=dtype.newbyteorder("="))
-    with open(path, "rb") as f:
-        for p in range(planes):
-            for k in range(per_plane):
-                i = p * per_plane + k
-                r0, c0 = (k // across) * seg_h, (k % across) * seg_w
-                # tiles are stored whole; the last strip only holds the rows left
-                rows = seg_h if tiled else min(seg_h, height - r0)
-                full = rows * seg_w * seg_spp * dtype.itemsize
-                f.seek(offsets[i])
-                seg = _decode(f.read(counts[i]), compression, full)
-                if seg.size < full:
-                    raise ValueError(f"{path}: segment {i} is short "
-                                     f"({seg.size} of {full} bytes)")
-                a = _unpredict(seg[:full], predictor, rows, seg_w, seg_spp, dtype)
-                nr, nc = min(rows, height - r0), min(seg_w, width - c0)
-                if planar == 2:
-                    out[p, r0:r0 + nr, c0:c0 + nc] = a[:nr, :nc, 0]
-                else:
-                    out[:, r0:r0 + nr, c0:c0 + nc] = np.moveaxis(a[:nr, :nc], 2, 0)
+
+    def one(i: int) -> None:
+        # segments are independent and write disjoint parts of `out`; zlib and
+        # the C decoders release the GIL, so a thread per core decodes them
+        p, k = divmod(i, per_plane)
+        r0, c0 = (k // across) * seg_h, (k % across) * seg_w
+        # tiles are stored whole; the last strip only holds the rows left
+        rows = seg_h if tiled else min(seg_h, height - r0)
+        full = rows * seg_w * seg_spp * dtype.itemsize
+        with open(path, "rb") as f:
+            f.seek(offsets[i])
+            raw = f.read(counts[i])
+        seg = _decode(raw, compression, full)
+        if seg.size < full:
+            raise ValueError(f"{path}: segment {i} is short ({seg.size} of {full} bytes)")
+        a = _unpredict(seg[:full], predictor, rows, seg_w, seg_spp, dtype)
+        nr, nc = min(rows, height - r0), min(seg_w, width - c0)
+        if planar == 2:
+            out[p, r0:r0 + nr, c0:c0 + nc] = a[:nr, :nc, 0]
+        else:
+            out[:, r0:r0 + nr, c0:c0 + nc] = np.moveaxis(a[:nr, :nc], 2, 0)
+
+    n_seg = per_plane * planes
+    workers = min(n_seg, os.cpu_count() or 1, 32)
+    if workers <= 1 or compression == 1:
+        for i in range(n_seg):
+            one(i)
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=workers) as ex:
+            for _ in ex.map(one, range(n_seg)):
+                pass
     return out
 
 
@@ -301,17 +314,27 @@ def write_geotiff(path, data: np.ndarray, transform, epsg: Optional[int] = None,
     if not plain:
         th, tw = (tile, tile) if tile else (min(height, max(1, (1 << 20) // max(
             1, width * dt.itemsize))), width)
-        for b in range(count):
-            band = np.ascontiguousarray(data[b], dtype=dt)
-            for r0 in range(0, height, th):
-                for c0 in range(0, width, tw):
-                    blk = band[r0:r0 + th, c0:c0 + tw]
-                    if tile and blk.shape != (th, tw):      # tiles are stored whole
-                        pad = np.zeros((th, tw), dtype=dt)
-                        pad[:blk.shape[0], :blk.shape[1]] = blk
-                        blk = pad
-                    raw = _predict(np.ascontiguousarray(blk), predictor)
-                    segments.append(zlib.compress(raw, 6) if compress else raw)
+        bands_c = [np.ascontiguousarray(data[b], dtype=dt) for b in range(count)]
+        jobs = [(b, r0, c0) for b in range(count) for r0 in range(0, height, th)
+                for c0 in range(0, width, tw)]
+
+        def encode(job):
+            b, r0, c0 = job
+            blk = bands_c[b][r0:r0 + th, c0:c0 + tw]
+            if tile and blk.shape != (th, tw):      # tiles are stored whole
+                pad = np.zeros((th, tw), dtype=dt)
+                pad[:blk.shape[0], :blk.shape[1]] = blk
+                blk = pad
+            raw = _predict(np.ascontiguousarray(blk), predictor)
+            return zlib.compress(raw, 6) if compress else raw
+
+        workers = min(len(jobs), os.cpu_count() or 1, 32)
+        if workers > 1 and compress:
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=workers) as ex:
+                segments = list(ex.map(encode, jobs))      # in job order
+        else:
+            segments = [encode(j) for j in jobs]
         total = sum(len(sg) for sg in segments)
     else:
         th, tw = height, width
