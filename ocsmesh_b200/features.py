@@ -368,3 +368,68 @@ def _stitch(ea, eb, ids, px, py) -> List[np.ndarray]:
         e = np.asarray(path)
         out.append(np.stack([px[e], py[e]], axis=1))
     return out
+
+
+def valid_region_contains(x: np.ndarray, y: np.ndarray, mask: np.ndarray,
+                          xy: np.ndarray) -> np.ndarray:
+    """``points.intersects(Raster.get_multipolygon())`` for one unchunked raster
+    (``ocsmesh/raster.py:560-640`` called at ``ocsmesh/mesh/mesh.py:2299-2301``):
+    the multipolygon is matplotlib's filled contour between the levels 0 and 1
+    of the field that is +1 on valid and -1 on nodata pixels, i.e. the region
+    bounded by the piecewise-linear zero line of that field -- it cuts every
+    cell edge between a valid and a nodata pixel at its midpoint.
+
+    matplotlib is not importable here (**parity unpinned**); the rule is restated
+    per cell: a point is outside when it lies strictly inside the corner
+    triangle (midpoint to midpoint) of a nodata corner, or strictly on the
+    nodata side of the mid line when two neighbouring corners are nodata; a
+    saddle cell (its mean is 0, not below the level) keeps its centre.
+    ``x`` (ascending or descending) and ``y`` are the raster's ``get_x`` /
+    ``get_y`` axes, ``mask`` is ``(len(y), len(x))`` with True = nodata.
+    Boundary points count as inside (``intersects``)."""
+    xy = np.asarray(xy, dtype=np.float64)
+    x = np.asarray(x, dtype=np.float64)
+    y = np.asarray(y, dtype=np.float64)
+    mask = np.asarray(mask, dtype=bool)
+    px, py = xy[:, 0], xy[:, 1]
+    inside = ((px >= min(x[0], x[-1])) & (px <= max(x[0], x[-1])) &
+              (py >= min(y[0], y[-1])) & (py <= max(y[0], y[-1])))
+    if len(x) < 2 or len(y) < 2:
+        return inside & ~mask.any()
+    if not mask.any():
+        return inside
+
+    def locate(axis, p):
+        asc = axis if axis[0] <= axis[-1] else axis[::-1]
+        k = np.clip(np.searchsorted(asc, p, side="right") - 1, 0, len(asc) - 2)
+        t = (p - asc[k]) / (asc[k + 1] - asc[k])
+        if axis[0] > axis[-1]:                    # back to the stored direction
+            k = len(axis) - 2 - k
+            t = 1.0 - t
+        return k, np.clip(t, 0.0, 1.0)
+
+    idx = np.nonzero(inside)[0]
+    i, u = locate(x, px[idx])
+    j, v = locate(y, py[idx])
+    m00, m01 = mask[j, i], mask[j, i + 1]
+    m10, m11 = mask[j + 1, i], mask[j + 1, i + 1]
+    out = np.zeros(idx.shape, dtype=bool)
+    # one corner (or two diagonal ones: the saddle keeps its centre): its triangle
+    out |= m00 & ~m01 & ~m10 & (u + v < 0.5)
+    out |= m01 & ~m00 & ~m11 & ((1 - u) + v < 0.5)
+    out |= m10 & ~m00 & ~m11 & (u + (1 - v) < 0.5)
+    out |= m11 & ~m01 & ~m10 & ((1 - u) + (1 - v) < 0.5)
+    # two neighbouring corners: the mid line
+    out |= m00 & m01 & ~m10 & ~m11 & (v < 0.5)
+    out |= m10 & m11 & ~m00 & ~m01 & (v > 0.5)
+    out |= m00 & m10 & ~m01 & ~m11 & (u < 0.5)
+    out |= m01 & m11 & ~m00 & ~m10 & (u > 0.5)
+    # three corners: only the triangle of the valid corner is inside
+    out |= m01 & m10 & m11 & ~m00 & (u + v > 0.5)
+    out |= m00 & m10 & m11 & ~m01 & ((1 - u) + v > 0.5)
+    out |= m00 & m01 & m11 & ~m10 & (u + (1 - v) > 0.5)
+    out |= m00 & m01 & m10 & ~m11 & ((1 - u) + (1 - v) > 0.5)
+    out |= m00 & m01 & m10 & m11
+    res = inside.copy()
+    res[idx] = ~out
+    return res

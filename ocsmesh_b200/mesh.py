@@ -161,10 +161,21 @@ class EuclideanMesh2D:
             raster = [raster]
         if method not in _METHODS:
             raise ValueError(f"Invalid value method specified <{method}>!")
-        if filter_by_shape:
-            raise NotImplementedError("filter_by_shape needs shapely")
         if info_out_path is not None:
+            # mesh/mesh.py:378-421 dereferences the raster's VERTICAL CRS
+            # (``vert_cs.name``) and reprojects to EPSG:4326: pyproj, with the
+            # rest of the geographic-CRS branch out of scope
             raise NotImplementedError("info_out_path needs pyproj/pandas glue")
+        if filter_by_shape:
+            for r in raster:
+                if len(list(r.iter_windows(chunk_size=r.chunk_size, overlap=2))) > 1:
+                    # the reference hands every node inside the WHOLE raster's
+                    # shape to every window's interpolator (mesh/mesh.py:2299-
+                    # 2301 inside the window loop); scipy's RegularGridInterpolator
+                    # then raises for the nodes outside that window
+                    raise NotImplementedError(
+                        "filter_by_shape on a chunked raster: in the reference "
+                        "RegularGridInterpolator raises 'out of bounds' there")
         dev = torch.cuda.current_device() if device is None else int(device)
         ctx = _lib.default_context(dev)
         coords = self.vert2
@@ -181,7 +192,37 @@ class EuclideanMesh2D:
             # back costs what the ordered gather saves (0.52 ms per 10 M nodes
             # either way, profiles/r1h_interp_ncu_summary.txt) and the counting
             # sort adds 0.9 ms
-            self._interp_device(ctx, raster, xy, vals, touched, method, band, dev)
+            shaped = filter_by_shape and any(
+                r.src.band_mask(band) is not None and np.any(r.src.band_mask(band))
+                for r in raster)
+            if not shaped:
+                # (filter_by_shape on rasters without nodata: the shape is the
+                #  raster's linspace box, which is the bbox test of the worker)
+                self._interp_device(ctx, raster, xy, vals, touched, method, band, dev)
+            else:
+                # raster by raster, in list order (the last one wins): only the
+                # nodes inside the raster's valid-data region go to the device
+                from . import features as _features
+                pts = np.ascontiguousarray(coords[k0:k1])
+                for r in raster:
+                    m = r.src.band_mask(band)
+                    if m is None or not np.any(m):
+                        sel = None
+                    else:
+                        sel = _features.valid_region_contains(
+                            r.get_x(), r.get_y(), np.asarray(m), pts)
+                    if sel is None:
+                        self._interp_device(ctx, [r], xy, vals, touched, method, band, dev)
+                        continue
+                    idx = torch.from_numpy(np.nonzero(sel)[0]).to(f"cuda:{dev}")
+                    if idx.numel() == 0:
+                        continue
+                    sub_xy = xy.index_select(0, idx).contiguous()
+                    sub_v = vals.index_select(0, idx).contiguous()
+                    sub_t = torch.zeros(idx.numel(), dtype=torch.uint8, device=f"cuda:{dev}")
+                    self._interp_device(ctx, [r], sub_xy, sub_v, sub_t, method, band, dev)
+                    vals.index_copy_(0, idx, sub_v)
+                    touched.index_copy_(0, idx, torch.maximum(touched.index_select(0, idx), sub_t))
             values[k0:k1] = vals.cpu().numpy()
         self.meshdata.values = values.reshape((values.shape[0], 1))
 
