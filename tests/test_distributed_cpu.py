@@ -281,6 +281,9 @@ def _band_exchange_case(rank, world):
     n = [5, 0, 9][rank % 3]               # ragged; rank 1 contributes nothing
     v = torch.from_numpy(rng.random((n, 2)) * 100.0)
     ex = D.BandExchange(n, W, torch.float32, "cpu", part, rank)
+    # host tensors: the collective form (the peer-memory form needs CUDA IPC)
+    assert ex.mode == "nccl" and not ex.p2p_failed()
+    ex.close()                            # nothing to release: a no-op
     out = {}
     for rep in range(2):                  # persistent buffers: a second step too
         g = ex.gather_vertices(v)
