@@ -1185,6 +1185,12 @@ class HfunCollector:
             source_index = [source_index]
         return source_index
 
+    def _selected(self, source_index):
+        """Exact method: the member hfuns a ``source_index`` names
+        (``collector.py:1783-1786, 1951-1954``: ``None`` = all of them)."""
+        src = self._src_idx(source_index)
+        return [h for k, h in enumerate(self._hfuns) if src is None or k in src]
+
     def _fast(self) -> bool:
         if self._method == 'fast':
             self._applied = False
@@ -1229,7 +1235,7 @@ class HfunCollector:
             self._flow_lim_info.append((self._src_idx(source_index), hmin, hmax,
                                         upper_bound, lower_bound))
             return
-        for h in self._hfuns:
+        for h in self._selected(source_index):
             h.add_subtidal_flow_limiter(hmin, hmax, lower_bound, upper_bound)
 
     def add_gradient_delimiter(self, hmin=None, hmax=None, source_index=None, **_kw):
@@ -1237,7 +1243,7 @@ class HfunCollector:
             self._flow_lim_info.append((self._src_idx(source_index), hmin, hmax,
                                         None, None))
             return
-        for h in self._hfuns:
+        for h in self._selected(source_index):
             h.add_gradient_delimiter(hmin=hmin, hmax=hmax)
 
     def add_constant_value(self, value, lower_bound=None, upper_bound=None,
@@ -1247,14 +1253,14 @@ class HfunCollector:
             self._const_val_info.append((self._src_idx(source_index), lower_bound,
                                          upper_bound, value))
             return
-        for h in self._hfuns:
+        for h in self._selected(source_index):
             h.add_constant_value(value, lower_bound, upper_bound)
 
     def _add_constraint(self, name, source_index, *args, **kwargs):
         if self._fast():
             self._constraint_info.append((self._src_idx(source_index), name, args, kwargs))
             return
-        for h in self._hfuns:
+        for h in self._selected(source_index):
             getattr(h, name)(*args, **kwargs)
 
     def add_topo_bound_constraint(self, value, upper_bound=np.inf, lower_bound=-np.inf,

@@ -249,3 +249,30 @@ def test_topo_const_constraint_value_shapes():
     assert TopoConstConstraint(np.float32(7)).value == 7
     with pytest.raises(ValueError, match="scalar"):
         TopoConstConstraint(np.ones((3, 3)))
+
+
+def test_exact_collector_honours_source_index():
+    """hfun/collector.py:1783-1786, 1951-1954: a refinement with a source index
+    only goes to the member rasters it names (host logic, no device work)."""
+    from ocsmesh_b200.hfun import HfunCollector
+    calls = []
+
+    class H:
+        def __init__(self, k):
+            self.k = k
+
+        def add_constant_value(self, *a):
+            calls.append((self.k, "cv", a))
+
+        def add_subtidal_flow_limiter(self, *a):
+            calls.append((self.k, "fl", a))
+
+    c = HfunCollector.__new__(HfunCollector)
+    c._method = "exact"
+    c._hfuns = [H(0), H(1), H(2)]
+    c.add_constant_value(5.0, source_index=1)
+    c.add_subtidal_flow_limiter(1, 2, 3, 4, source_index=[0, 2])
+    c.add_constant_value(7.0)
+    assert calls == [(1, "cv", (5.0, None, None)), (0, "fl", (1, 2, 3, 4)),
+                     (2, "fl", (1, 2, 3, 4)), (0, "cv", (7.0, None, None)),
+                     (1, "cv", (7.0, None, None)), (2, "cv", (7.0, None, None))]
